@@ -1,0 +1,56 @@
+"""Shared helpers for the tests: tiny-model construction, synthetic weights in every storage type."""
+import ast
+
+import numpy as np
+
+from oracle import orc
+
+GGUF_LAYER = {"self_attn.q_proj": "attn_q", "self_attn.k_proj": "attn_k", "self_attn.v_proj": "attn_v",
+              "self_attn.o_proj": "attn_output", "mlp.gate_proj": "ffn_gate", "mlp.up_proj": "ffn_up",
+              "mlp.down_proj": "ffn_down", "input_layernorm": "attn_norm", "post_attention_layernorm": "ffn_norm"}
+
+
+def make_cfg(n_layers, d_model, n_heads, n_kv_heads, head_dim, d_ffn, vocab, max_ctx, rms_eps=1e-5,
+             rope_theta=500000.0, rope_factor=8.0, rope_low=1.0, rope_high=4.0, rope_orig_ctx=8192, kv_bf16=1):
+    c = orc.Config()
+    c.n_layers, c.d_model, c.n_heads, c.n_kv_heads, c.head_dim = n_layers, d_model, n_heads, n_kv_heads, head_dim
+    c.d_ffn, c.vocab, c.max_ctx, c.rms_eps, c.rope_theta = d_ffn, vocab, max_ctx, rms_eps, rope_theta
+    c.rope_factor, c.rope_low_freq_factor, c.rope_high_freq_factor = rope_factor, rope_low, rope_high
+    c.rope_orig_ctx, c.kv_bf16 = rope_orig_ctx, kv_bf16
+    return c
+
+
+def hf_to_pairs(w, n_heads, head_dim):
+    """HF rotate-half row order -> GGUF adjacent-pair row order (row 2i <- i, row 2i+1 <- i + hd/2)."""
+    w = w.reshape(n_heads, 2, head_dim // 2, -1)
+    return np.ascontiguousarray(w.transpose(0, 2, 1, 3)).reshape(n_heads * head_dim, -1)
+
+
+def tiny_from_hf_fixture(z, kv_bf16):
+    t = ast.literal_eval(str(z["config"][0]))
+    cfg = make_cfg(t["n_layers"], t["d_model"], t["n_heads"], t["n_kv_heads"], t["head_dim"], t["d_ffn"],
+                   t["vocab"], t["max_ctx"], t["rms_eps"], t["rope_theta"], t["rope_factor"], t["rope_low"],
+                   t["rope_high"], t["rope_orig_ctx"], kv_bf16)
+    m = orc.Model(cfg)
+    for key in z.files:
+        if not key.startswith("w:"):
+            continue
+        name, arr = key[2:], z[key]
+        if name == "model.embed_tokens.weight":
+            g = "token_embd.weight"
+        elif name == "model.norm.weight":
+            g = "output_norm.weight"
+        elif name == "lm_head.weight":
+            g = "output.weight"
+        else:
+            parts = name.split(".")          # model.layers.N.<...>.weight
+            g = f"blk.{parts[2]}.{GGUF_LAYER['.'.join(parts[3:-1])]}.weight"
+        if arr.dtype == np.uint16:
+            if g.endswith("attn_q.weight"):
+                arr = hf_to_pairs(arr, cfg.n_heads, cfg.head_dim)
+            elif g.endswith("attn_k.weight"):
+                arr = hf_to_pairs(arr, cfg.n_kv_heads, cfg.head_dim)
+            m.set_tensor(g, orc.BF16, arr, arr.shape[0], arr.shape[1])
+        else:
+            m.set_tensor(g, orc.F32, arr.astype(np.float32), 1, arr.size)
+    return m, cfg
