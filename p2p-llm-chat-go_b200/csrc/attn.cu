@@ -1,0 +1,165 @@
+// attn.cu — paged GQA decode attention for one query position (batch-1 decode), sm_100a.
+//
+// grid = (n_kv_heads, n_splits), 128 threads.  A CTA owns one KV head (its G = n_heads/n_kv_heads query
+// heads share every K/V row it reads) and the 32-token tiles  split, split+n_splits, ...  of the context,
+// so the grid is fixed (CUDA-graph friendly) while the context grows.  Per tile: K and V rows are gathered
+// through the block table into shared memory (bf16), scores and the online-softmax update are computed
+// one head per warp (lane = token), P.V one output dim per thread.  Each CTA leaves an un-normalised
+// partial (acc, m, l) in scratch; the last CTA of a KV head to finish (atomic ticket) merges the splits and
+// writes the attention output, so no second launch is needed.  The ticket counters reset themselves.
+//
+// HBM traffic: ctx * 2 * 256 B per KV head (bf16 K and V rows, read once) — 4 KiB per context token per
+// layer for Llama-3.1 (8 KV heads); the kernel is latency-, not bandwidth-bound at ctx <= 640.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200 {
+namespace {
+
+constexpr int kTile = 32;
+constexpr int kKStride = 65;  // words per K row in smem (64 data + 1 pad): lane=token reads are conflict-free
+constexpr int kPart = kHeadDim + 2;  // acc[128], m, l
+
+template <int G>
+__global__ void __launch_bounds__(128) attn_decode_kernel(const AttnArgs a) {
+  __shared__ uint32_t Ks[kTile * kKStride];
+  __shared__ __align__(16) uint16_t Vs[kTile * kHeadDim];
+  __shared__ __align__(16) float qs[G * kHeadDim];
+  __shared__ float P[G][kTile];
+  __shared__ float m_run[G], l_run[G], corr_s[G];
+  __shared__ int s_last;
+
+  const int kvh = blockIdx.x, split = blockIdx.y, S = gridDim.y;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  pdl_wait();
+  pdl_launch_dependents();
+  const int ctx = a.fixed_ctx > 0 ? a.fixed_ctx : a.st->pos + 1;
+  const float scale = 1.0f / sqrtf((float)kHeadDim);
+
+  for (int i = tid; i < G * kHeadDim; i += 128) qs[i] = a.q[(size_t)kvh * G * kHeadDim + i];
+  if (tid < G) {
+    m_run[tid] = -INFINITY;
+    l_run[tid] = 0.f;
+  }
+  float acc[G];
+#pragma unroll
+  for (int h = 0; h < G; ++h) acc[h] = 0.f;
+  __syncthreads();
+
+  for (int tile = split; tile * kTile < ctx; tile += S) {
+    const int t0 = tile * kTile;
+    // gather K and V rows of this tile (zero-fill past the context end)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int item = tid + 128 * j, t = item >> 4, seg = item & 15;
+      const int tok = t0 + t;
+      uint4 kv = make_uint4(0, 0, 0, 0), vv = make_uint4(0, 0, 0, 0);
+      if (tok < ctx) {
+        const int page = a.block_table[tok / kPageTokens];
+        const size_t row = (((size_t)page * a.n_kv_heads + kvh) * kPageTokens + (tok % kPageTokens)) * kHeadDim;
+        kv = *reinterpret_cast<const uint4*>(a.k_cache + row + seg * 8);
+        vv = *reinterpret_cast<const uint4*>(a.v_cache + row + seg * 8);
+      }
+      uint32_t* kd = Ks + t * kKStride + seg * 4;
+      kd[0] = kv.x; kd[1] = kv.y; kd[2] = kv.z; kd[3] = kv.w;
+      *reinterpret_cast<uint4*>(Vs + t * kHeadDim + seg * 8) = vv;
+    }
+    __syncthreads();
+    // scores + online softmax: one head per warp, lane = token
+    for (int h = warp; h < G; h += 4) {
+      const uint32_t* kr = Ks + lane * kKStride;
+      const float* qh = qs + h * kHeadDim;
+      float s = 0.f;
+#pragma unroll 16
+      for (int w = 0; w < kHeadDim / 2; ++w) {
+        const uint32_t kw = kr[w];
+        const float2 q2 = *reinterpret_cast<const float2*>(qh + 2 * w);
+        s = fmaf(q2.x, bf16lo(kw), s);
+        s = fmaf(q2.y, bf16hi(kw), s);
+      }
+      const bool valid = (t0 + lane) < ctx;
+      s = valid ? s * scale : -INFINITY;
+      const float m_old = m_run[h];
+      const float m_new = fmaxf(m_old, warp_max(s));
+      const float p = valid ? expf(s - m_new) : 0.f;
+      const float l_tile = warp_sum(p);
+      P[h][lane] = p;
+      if (lane == 0) {
+        const float corr = (m_old == -INFINITY) ? 0.f : expf(m_old - m_new);
+        corr_s[h] = corr;
+        l_run[h] = l_run[h] * corr + l_tile;
+        m_run[h] = m_new;
+      }
+    }
+    __syncthreads();
+    // P.V: thread = output dim
+#pragma unroll
+    for (int h = 0; h < G; ++h) acc[h] *= corr_s[h];
+#pragma unroll 8
+    for (int t = 0; t < kTile; ++t) {
+      const float v = __uint_as_float((uint32_t)Vs[t * kHeadDim + tid] << 16);
+#pragma unroll
+      for (int h = 0; h < G; ++h) acc[h] = fmaf(P[h][t], v, acc[h]);
+    }
+    __syncthreads();
+  }
+
+  float* part = a.partial + ((size_t)kvh * S + split) * G * kPart;
+#pragma unroll
+  for (int h = 0; h < G; ++h) part[h * kPart + tid] = acc[h];
+  if (tid < G) {
+    part[tid * kPart + kHeadDim] = m_run[tid];
+    part[tid * kPart + kHeadDim + 1] = l_run[tid];
+  }
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) s_last = (atomicAdd(a.counters + kvh, 1u) == (unsigned)(S - 1));
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const float* base = a.partial + (size_t)kvh * S * G * kPart;
+#pragma unroll
+  for (int h = 0; h < G; ++h) {
+    float M = -INFINITY;
+    for (int s = 0; s < S; ++s) M = fmaxf(M, __ldcg(base + ((size_t)s * G + h) * kPart + kHeadDim));
+    float num = 0.f, den = 0.f;
+    for (int s = 0; s < S; ++s) {
+      const float* ps = base + ((size_t)s * G + h) * kPart;
+      const float ms = __ldcg(ps + kHeadDim);
+      if (ms == -INFINITY) continue;
+      const float w = expf(ms - M);
+      num = fmaf(__ldcg(ps + tid), w, num);
+      den = fmaf(__ldcg(ps + kHeadDim + 1), w, den);
+    }
+    a.out[((size_t)kvh * G + h) * kHeadDim + tid] = num / den;
+  }
+  if (tid == 0) a.counters[kvh] = 0u;
+}
+
+}  // namespace
+
+size_t attn_partial_floats(int n_heads, int n_kv_heads, int n_splits) {
+  return (size_t)n_kv_heads * n_splits * (n_heads / n_kv_heads) * kPart;
+}
+
+cudaError_t launch_attn_decode(const AttnArgs& a, cudaStream_t s, bool pdl) {
+  if (a.n_kv_heads <= 0 || a.n_heads % a.n_kv_heads || a.n_splits <= 0) return cudaErrorInvalidValue;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(a.n_kv_heads, a.n_splits);
+  cfg.blockDim = dim3(128);
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl ? 1 : 0;
+  switch (a.n_heads / a.n_kv_heads) {
+    case 1: return cudaLaunchKernelEx(&cfg, attn_decode_kernel<1>, a);
+    case 2: return cudaLaunchKernelEx(&cfg, attn_decode_kernel<2>, a);
+    case 4: return cudaLaunchKernelEx(&cfg, attn_decode_kernel<4>, a);
+    case 8: return cudaLaunchKernelEx(&cfg, attn_decode_kernel<8>, a);
+  }
+  return cudaErrorInvalidValue;
+}
+
+}  // namespace b200

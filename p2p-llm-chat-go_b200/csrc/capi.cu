@@ -1,0 +1,470 @@
+// capi.cu — the extern "C" surface declared in include/b200llm.h.  Thin: argument checks, host<->device
+// staging for the parity hooks, and forwarding into Engine.  No arithmetic happens on the host.
+#include <cstdio>
+#include <cstring>
+
+#include "engine.h"
+
+namespace b200 {
+const char* last_error();
+int tokenizer_encode(const b200_config& cfg, const char* utf8, size_t n, int add_bos, int32_t* ids, size_t cap, size_t* n_out);
+int tokenizer_decode(const b200_config& cfg, const int32_t* ids, size_t n, char* buf, size_t cap, size_t* n_out);
+}  // namespace b200
+
+using namespace b200;
+
+namespace {
+
+struct DevBuf {  // RAII device scratch for the stand-alone hooks
+  void* p = nullptr;
+  ~DevBuf() { if (p) cudaFree(p); }
+  int alloc(size_t n) {
+    cudaError_t e = cudaMalloc(&p, n ? n : 16);
+    return e == cudaSuccess ? 0 : cuda_fail(e, "cudaMalloc(hook)");
+  }
+  template <class T> T* as() { return reinterpret_cast<T*>(p); }
+};
+
+int have_device() {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) {
+    set_error("no CUDA device available (%s); libb200llm has no CPU fallback", cudaGetErrorString(e));
+    (void)cudaGetLastError();
+    return B200_ENODEV;
+  }
+  return 0;
+}
+
+int sm_count_now() {
+  int dev = 0, n = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  return n;
+}
+
+// Upload a GGUF-layout matrix and bring it into the device layout of its type.
+int upload_matrix(int type, const void* w, int64_t rows, int64_t cols, DevBuf& out) {
+  const size_t bytes = (size_t)rows * gemv_row_bytes(type, cols);
+  int rc = out.alloc(bytes);
+  if (rc) return rc;
+  if (type == T_Q6_K) {
+    DevBuf tmp;
+    if ((rc = tmp.alloc(bytes))) return rc;
+    B200_CUDA(cudaMemcpy(tmp.p, w, bytes, cudaMemcpyHostToDevice));
+    B200_CUDA(launch_q6k_repack(tmp.as<uint8_t>(), out.as<uint8_t>(), rows, cols / QK_K, 1, 0));
+    B200_CUDA(cudaDeviceSynchronize());
+  } else {
+    B200_CUDA(cudaMemcpy(out.p, w, bytes, cudaMemcpyHostToDevice));
+  }
+  return 0;
+}
+
+int gemv_hook(int type, const void* w, int64_t rows, int64_t cols, const float* x, const float* norm_w, float eps, float* y) {
+  int rc = have_device();
+  if (rc) return rc;
+  if (!w || !x || !y) { set_error("null argument"); return B200_EINVAL; }
+  if (!gemv_shape_ok(type, rows, cols, EPI_STORE)) {
+    set_error("gemv shape %lldx%lld unsupported for type %d", (long long)rows, (long long)cols, type);
+    return B200_EINVAL;
+  }
+  DevBuf dw, dx, dn, dy;
+  if ((rc = upload_matrix(type, w, rows, cols, dw)) || (rc = dx.alloc((size_t)cols * 4)) || (rc = dy.alloc((size_t)rows * 4))) return rc;
+  B200_CUDA(cudaMemcpy(dx.p, x, (size_t)cols * 4, cudaMemcpyHostToDevice));
+  if (norm_w) {
+    if ((rc = dn.alloc((size_t)cols * 4))) return rc;
+    B200_CUDA(cudaMemcpy(dn.p, norm_w, (size_t)cols * 4, cudaMemcpyHostToDevice));
+  }
+  GemvArgs a = {};
+  a.W = dw.as<uint8_t>(); a.N = (int)rows; a.K = (int)cols; a.x = dx.as<float>(); a.norm_w = dn.as<float>(); a.eps = eps; a.y = dy.as<float>();
+  B200_CUDA(launch_gemv(type, norm_w ? PRO_RMSNORM : PRO_COPY, EPI_STORE, a, 0, false, sm_count_now()));
+  B200_CUDA(cudaDeviceSynchronize());
+  B200_CUDA(cudaMemcpy(y, dy.p, (size_t)rows * 4, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* b200_last_error(void) { return last_error(); }
+const char* b200_version(void) { return "b200llm 0.1 (sm_100a)"; }
+
+int b200_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { (void)cudaGetLastError(); return 0; }
+  return n;
+}
+
+void b200_default_sampling(b200_sampling* s) {
+  if (!s) return;
+  memset(s, 0, sizeof *s);
+  s->temperature = 0.8f; s->top_p = 0.9f; s->repeat_penalty = 1.1f; s->top_k = 40; s->repeat_last_n = 64;
+  s->seed = 0; s->num_predict = 128; s->prefill_mode = B200_MODE_GEMM;
+}
+
+static void llama31(b200_config* c, int layers, int d, int heads, int ff) {
+  memset(c, 0, sizeof *c);
+  c->n_layers = layers; c->d_model = d; c->n_heads = heads; c->n_kv_heads = 8; c->head_dim = 128; c->d_ffn = ff;
+  c->vocab = 128256; c->max_ctx = 1024; c->rms_eps = 1e-5f; c->rope_theta = 500000.0f; c->rope_factor = 8.0f;
+  c->rope_low_freq_factor = 1.0f; c->rope_high_freq_factor = 4.0f; c->rope_orig_ctx = 8192;
+  c->weight_format = B200_WEIGHTS_BF16; c->device = 0; c->max_seqs = 1; c->seed = 0; c->eos_token = 128009;
+}
+void b200_llama31_8b(b200_config* c) { if (c) llama31(c, 32, 4096, 32, 14336); }
+void b200_llama31_70b(b200_config* c) { if (c) llama31(c, 80, 8192, 64, 28672); }
+
+int b200_init(const b200_config* cfg, b200_engine** out) {
+  if (!cfg || !out) { set_error("null argument"); return B200_EINVAL; }
+  *out = nullptr;
+  Engine* e = new (std::nothrow) Engine();
+  if (!e) return B200_ENOMEM;
+  int rc = e->init(*cfg);
+  if (rc) { delete e; return rc; }
+  *out = reinterpret_cast<b200_engine*>(e);
+  return 0;
+}
+
+void b200_shutdown(b200_engine* h) { delete reinterpret_cast<Engine*>(h); }
+
+int b200_get_config(const b200_engine* h, b200_config* out) {
+  if (!h || !out) { set_error("null argument"); return B200_EINVAL; }
+  *out = reinterpret_cast<const Engine*>(h)->cfg;
+  return 0;
+}
+
+int b200_set_tensor(b200_engine* h, const char* name, int type, const void* data, int64_t rows, int64_t cols) {
+  Engine* e = reinterpret_cast<Engine*>(h);
+  if (!e || !name || !data) { set_error("null argument"); return B200_EINVAL; }
+  std::lock_guard<std::mutex> lk(e->mu);
+  auto it = e->slots.find(name);
+  if (it == e->slots.end()) { set_error("unknown tensor '%s'", name); return B200_EINVAL; }
+  Slot& s = it->second;
+  if (s.type != type || s.rows * s.cols != rows * cols || (s.rows != 1 && (s.rows != rows || s.cols != cols))) {
+    set_error("tensor '%s' expects type %d shape %lldx%lld, got type %d shape %lldx%lld", name, s.type, (long long)s.rows,
+              (long long)s.cols, type, (long long)rows, (long long)cols);
+    return B200_EINVAL;
+  }
+  B200_CUDA(cudaSetDevice(e->cfg.device));
+  const size_t bytes = (size_t)s.rows * (s.type == T_F32 ? (size_t)s.cols * 4 : gemv_row_bytes(s.type, s.cols));
+  DevBuf tmp;
+  int rc = tmp.alloc(bytes);
+  if (rc) return rc;
+  B200_CUDA(cudaMemcpyAsync(tmp.p, data, bytes, cudaMemcpyHostToDevice, e->stream));
+  if ((rc = e->place_tensor(s, tmp.as<uint8_t>()))) return rc;
+  B200_CUDA(cudaStreamSynchronize(e->stream));
+  s.set = true;
+  return 0;
+}
+
+int b200_tensor_info(const b200_engine* h, const char* name, int* type, int64_t* rows, int64_t* cols, int64_t* nbytes) {
+  const Engine* e = reinterpret_cast<const Engine*>(h);
+  if (!e || !name) { set_error("null argument"); return B200_EINVAL; }
+  auto it = e->slots.find(name);
+  if (it == e->slots.end()) { set_error("unknown tensor '%s'", name); return B200_EINVAL; }
+  const Slot& s = it->second;
+  if (type) *type = s.type;
+  if (rows) *rows = s.rows;
+  if (cols) *cols = s.cols;
+  if (nbytes) *nbytes = (int64_t)s.rows * (int64_t)(s.type == T_F32 ? (size_t)s.cols * 4 : gemv_row_bytes(s.type, s.cols));
+  return 0;
+}
+
+int b200_get_tensor(b200_engine* h, const char* name, void* buf, int64_t cap) {
+  Engine* e = reinterpret_cast<Engine*>(h);
+  if (!e || !name || !buf) { set_error("null argument"); return B200_EINVAL; }
+  std::lock_guard<std::mutex> lk(e->mu);
+  auto it = e->slots.find(name);
+  if (it == e->slots.end()) { set_error("unknown tensor '%s'", name); return B200_EINVAL; }
+  const Slot& s = it->second;
+  if (!s.set) { set_error("tensor '%s' has not been set", name); return B200_ESTATE; }
+  const size_t bytes = (size_t)s.rows * (s.type == T_F32 ? (size_t)s.cols * 4 : gemv_row_bytes(s.type, s.cols));
+  if ((int64_t)bytes > cap) { set_error("buffer too small: need %zu bytes", bytes); return B200_ERANGE; }
+  B200_CUDA(cudaSetDevice(e->cfg.device));
+  DevBuf tmp;
+  int rc = tmp.alloc(bytes);
+  if (rc) return rc;
+  if ((rc = e->fetch_tensor(s, tmp.as<uint8_t>()))) return rc;
+  B200_CUDA(cudaMemcpyAsync(buf, tmp.p, bytes, cudaMemcpyDeviceToHost, e->stream));
+  B200_CUDA(cudaStreamSynchronize(e->stream));
+  return 0;
+}
+
+int64_t b200_weight_bytes(const b200_engine* h) { return h ? reinterpret_cast<const Engine*>(h)->weight_bytes : 0; }
+
+int b200_tokenize(b200_engine* h, const char* utf8, size_t n, int add_bos, int32_t* ids, size_t cap, size_t* n_out) {
+  Engine* e = reinterpret_cast<Engine*>(h);
+  if (!e || (!utf8 && n) || !n_out) { set_error("null argument"); return B200_EINVAL; }
+  return tokenizer_encode(e->cfg, utf8, n, add_bos, ids, cap, n_out);
+}
+int b200_detokenize(b200_engine* h, const int32_t* ids, size_t n, char* buf, size_t cap, size_t* n_out) {
+  Engine* e = reinterpret_cast<Engine*>(h);
+  if (!e || (!ids && n) || !n_out) { set_error("null argument"); return B200_EINVAL; }
+  return tokenizer_decode(e->cfg, ids, n, buf, cap, n_out);
+}
+
+int b200_submit(b200_engine* h, const int32_t* prompt_ids, size_t n, const b200_sampling* s, b200_req** out) {
+  Engine* e = reinterpret_cast<Engine*>(h);
+  if (!e || !prompt_ids || !out || n == 0) { set_error("null/empty argument"); return B200_EINVAL; }
+  if (n > (size_t)e->cfg.max_ctx) { set_error("prompt of %zu tokens exceeds max_ctx %d", n, e->cfg.max_ctx); return B200_EINVAL; }
+  for (size_t i = 0; i < n; ++i)
+    if (prompt_ids[i] < 0 || prompt_ids[i] >= e->cfg.vocab) { set_error("token id %d out of range", prompt_ids[i]); return B200_EINVAL; }
+  if (!e->all_set()) { set_error("not all tensors are set"); return B200_ESTATE; }
+  Request* r = new (std::nothrow) Request();
+  if (!r) return B200_ENOMEM;
+  r->e = e;
+  r->prompt.assign(prompt_ids, prompt_ids + n);  // copied: the caller's buffer is free after return
+  if (s) r->sp = *s; else b200_default_sampling(&r->sp);
+  {
+    std::lock_guard<std::mutex> lk(e->qmu);
+    e->queue.push_back(r);
+  }
+  e->qcv.notify_one();
+  *out = reinterpret_cast<b200_req*>(r);
+  return 0;
+}
+
+int b200_next(b200_req* h, int32_t* id, int* done, int timeout_ms) {
+  Request* r = reinterpret_cast<Request*>(h);
+  if (!r || !id || !done) { set_error("null argument"); return B200_EINVAL; }
+  std::unique_lock<std::mutex> lk(r->mu);
+  if (r->done_delivered) { set_error("request already finished"); return B200_ESTATE; }
+  auto ready = [&] { return !r->tokens.empty() || r->finished; };
+  if (timeout_ms < 0) r->cv.wait(lk, ready);
+  else if (!r->cv.wait_for(lk, std::chrono::milliseconds(timeout_ms), ready)) { set_error("timeout"); return B200_ETIMEOUT; }
+  if (r->tokens.empty()) {  // finished without (more) tokens: error or cancellation
+    r->done_delivered = true;
+    *done = 1;
+    *id = -1;
+    if (r->error) return r->error;
+    set_error("request ended without a token");
+    return B200_ESTATE;
+  }
+  *id = r->tokens.front();
+  r->tokens.pop_front();
+  *done = (r->finished && r->tokens.empty()) ? 1 : 0;
+  if (*done) r->done_delivered = true;
+  return 0;
+}
+
+int b200_stats_get(b200_req* h, b200_stats* out) {
+  Request* r = reinterpret_cast<Request*>(h);
+  if (!r || !out) { set_error("null argument"); return B200_EINVAL; }
+  std::lock_guard<std::mutex> lk(r->mu);
+  *out = r->stats;
+  return 0;
+}
+
+void b200_cancel(b200_req* h) {
+  Request* r = reinterpret_cast<Request*>(h);
+  if (!r) return;
+  std::lock_guard<std::mutex> lk(r->mu);
+  r->cancelled = true;
+}
+
+void b200_free(b200_req* h) {
+  Request* r = reinterpret_cast<Request*>(h);
+  if (!r) return;
+  {
+    std::unique_lock<std::mutex> lk(r->mu);
+    r->cancelled = true;
+    r->cv.wait(lk, [&] { return r->finished; });
+  }
+  delete r;
+}
+
+int b200_forward_logits(b200_engine* h, const int32_t* ids, size_t n, int mode, float* logits) {
+  Engine* e = reinterpret_cast<Engine*>(h);
+  if (!e || !ids || !logits || n == 0) { set_error("null/empty argument"); return B200_EINVAL; }
+  std::lock_guard<std::mutex> lk(e->mu);
+  B200_CUDA(cudaSetDevice(e->cfg.device));
+  return e->forward_logits(ids, (int)n, mode, logits);
+}
+
+int b200_generate_greedy(b200_engine* h, const int32_t* prompt, size_t n_prompt, int32_t* ids, size_t n_new, int prefill_mode,
+                         float* ttft_ms, float* decode_ms) {
+  Engine* e = reinterpret_cast<Engine*>(h);
+  if (!e || !prompt || !ids || n_prompt == 0 || n_new == 0) { set_error("null/empty argument"); return B200_EINVAL; }
+  std::lock_guard<std::mutex> lk(e->mu);
+  B200_CUDA(cudaSetDevice(e->cfg.device));
+  return e->generate_greedy(prompt, (int)n_prompt, ids, (int)n_new, prefill_mode, ttft_ms, decode_ms);
+}
+
+int b200_dequant(int type, const void* blocks, int64_t n_blocks, float* out) {
+  int rc = have_device();
+  if (rc) return rc;
+  if (type != T_Q4_K && type != T_Q6_K) { set_error("b200_dequant: type must be Q4_K or Q6_K"); return B200_EINVAL; }
+  if (n_blocks < 0 || (n_blocks && (!blocks || !out))) { set_error("null argument"); return B200_EINVAL; }
+  if (n_blocks == 0) return 0;
+  const size_t inb = (size_t)n_blocks * (type == T_Q4_K ? Q4K_BYTES : Q6K_BYTES);
+  DevBuf din, dout;
+  if ((rc = din.alloc(inb)) || (rc = dout.alloc((size_t)n_blocks * QK_K * 4))) return rc;
+  B200_CUDA(cudaMemcpy(din.p, blocks, inb, cudaMemcpyHostToDevice));
+  B200_CUDA(launch_dequant(type, din.p, n_blocks, dout.as<float>(), nullptr, 0));
+  B200_CUDA(cudaDeviceSynchronize());
+  B200_CUDA(cudaMemcpy(out, dout.p, (size_t)n_blocks * QK_K * 4, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int b200_quant_q16(const float* x, int64_t n, int16_t* q, float* d) {
+  int rc = have_device();
+  if (rc) return rc;
+  if (n < 0 || n % 32 || (n && (!x || !q || !d))) { set_error("b200_quant_q16: n must be a multiple of 32"); return B200_EINVAL; }
+  if (n == 0) return 0;
+  DevBuf dx, dq, dd;
+  if ((rc = dx.alloc((size_t)n * 4)) || (rc = dq.alloc((size_t)n * 2)) || (rc = dd.alloc((size_t)n / 32 * 4))) return rc;
+  B200_CUDA(cudaMemcpy(dx.p, x, (size_t)n * 4, cudaMemcpyHostToDevice));
+  B200_CUDA(launch_quant_q16(dx.as<float>(), n, dq.as<int16_t>(), dd.as<float>(), 0));
+  B200_CUDA(cudaDeviceSynchronize());
+  B200_CUDA(cudaMemcpy(q, dq.p, (size_t)n * 2, cudaMemcpyDeviceToHost));
+  B200_CUDA(cudaMemcpy(d, dd.p, (size_t)n / 32 * 4, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int b200_gemv(int type, const void* w, int64_t rows, int64_t cols, const float* x, float* y) {
+  return gemv_hook(type, w, rows, cols, x, nullptr, 0.f, y);
+}
+int b200_gemv_rmsnorm(int type, const void* w, int64_t rows, int64_t cols, const float* x, const float* norm_w, float eps, float* y) {
+  if (!norm_w) { set_error("null norm_w"); return B200_EINVAL; }
+  return gemv_hook(type, w, rows, cols, x, norm_w, eps, y);
+}
+
+int b200_attn_decode(const float* q, const float* k, const float* v, int n_ctx, int n_heads, int n_kv_heads, float* out) {
+  int rc = have_device();
+  if (rc) return rc;
+  if (!q || !k || !v || !out || n_ctx < 1 || n_kv_heads < 1 || n_heads % n_kv_heads) { set_error("bad argument"); return B200_EINVAL; }
+  const int G = n_heads / n_kv_heads;
+  if (G != 1 && G != 2 && G != 4 && G != 8) { set_error("GQA group %d unsupported", G); return B200_EINVAL; }
+  const int kvd = n_kv_heads * kHeadDim, n_pages = (n_ctx + kPageTokens - 1) / kPageTokens, S = 20;
+  // build a paged bf16 cache with a shuffled (non-identity) block table so the indirection is exercised
+  std::vector<int32_t> bt(n_pages);
+  for (int i = 0; i < n_pages; ++i) bt[i] = (int32_t)((i * 7 + 3) % n_pages);
+  if (n_pages % 7 == 0) for (int i = 0; i < n_pages; ++i) bt[i] = n_pages - 1 - i;
+  const size_t cache_elems = (size_t)n_pages * n_kv_heads * kPageTokens * kHeadDim;
+  DevBuf dkf, dvf, dkc, dvc, dq, dout, dbt, dpart, dcnt;
+  std::vector<float> kp(cache_elems, 0.f), vp(cache_elems, 0.f);
+  for (int t = 0; t < n_ctx; ++t)
+    for (int hh = 0; hh < n_kv_heads; ++hh) {
+      const size_t dst = (((size_t)bt[t / kPageTokens] * n_kv_heads + hh) * kPageTokens + (t % kPageTokens)) * kHeadDim;
+      memcpy(&kp[dst], k + (size_t)t * kvd + (size_t)hh * kHeadDim, kHeadDim * 4);
+      memcpy(&vp[dst], v + (size_t)t * kvd + (size_t)hh * kHeadDim, kHeadDim * 4);
+    }
+  if ((rc = dkf.alloc(cache_elems * 4)) || (rc = dvf.alloc(cache_elems * 4)) || (rc = dkc.alloc(cache_elems * 2)) || (rc = dvc.alloc(cache_elems * 2)) ||
+      (rc = dq.alloc((size_t)n_heads * kHeadDim * 4)) || (rc = dout.alloc((size_t)n_heads * kHeadDim * 4)) || (rc = dbt.alloc((size_t)n_pages * 4)) ||
+      (rc = dpart.alloc(attn_partial_floats(n_heads, n_kv_heads, S) * 4)) || (rc = dcnt.alloc((size_t)n_kv_heads * 4)))
+    return rc;
+  B200_CUDA(cudaMemcpy(dkf.p, kp.data(), cache_elems * 4, cudaMemcpyHostToDevice));
+  B200_CUDA(cudaMemcpy(dvf.p, vp.data(), cache_elems * 4, cudaMemcpyHostToDevice));
+  B200_CUDA(launch_f32_to_bf16(dkf.as<float>(), dkc.as<uint16_t>(), (int64_t)cache_elems, 0));
+  B200_CUDA(launch_f32_to_bf16(dvf.as<float>(), dvc.as<uint16_t>(), (int64_t)cache_elems, 0));
+  B200_CUDA(cudaMemcpy(dq.p, q, (size_t)n_heads * kHeadDim * 4, cudaMemcpyHostToDevice));
+  B200_CUDA(cudaMemcpy(dbt.p, bt.data(), (size_t)n_pages * 4, cudaMemcpyHostToDevice));
+  B200_CUDA(cudaMemset(dcnt.p, 0, (size_t)n_kv_heads * 4));
+  AttnArgs a = {};
+  a.q = dq.as<float>(); a.k_cache = dkc.as<uint16_t>(); a.v_cache = dvc.as<uint16_t>(); a.block_table = dbt.as<int32_t>();
+  a.n_heads = n_heads; a.n_kv_heads = n_kv_heads; a.out = dout.as<float>(); a.partial = dpart.as<float>();
+  a.counters = dcnt.as<unsigned int>(); a.n_splits = S; a.fixed_ctx = n_ctx;
+  B200_CUDA(launch_attn_decode(a, 0, false));
+  B200_CUDA(cudaDeviceSynchronize());
+  B200_CUDA(cudaMemcpy(out, dout.p, (size_t)n_heads * kHeadDim * 4, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int b200_gemm(int type, const void* w, int64_t rows, int64_t cols, const float* x, int64_t n, float* y) {
+  (void)type; (void)w; (void)rows; (void)cols; (void)x; (void)n; (void)y;
+  int rc = have_device();
+  if (rc) return rc;
+  set_error("b200_gemm: tcgen05 GEMM not linked into this build");
+  return B200_ESTATE;
+}
+
+int b200_sample(const float* logits, int vocab, const b200_sampling* s, const int32_t* history, int n_hist, uint64_t step, int32_t* id) {
+  (void)logits; (void)vocab; (void)s; (void)history; (void)n_hist; (void)step; (void)id;
+  int rc = have_device();
+  if (rc) return rc;
+  set_error("b200_sample: sampler kernel not linked into this build");
+  return B200_ESTATE;
+}
+
+int b200_bench_decode(b200_engine* h, int ctx, int n_steps, float* ms_per_step, int* launches_per_step) {
+  Engine* e = reinterpret_cast<Engine*>(h);
+  if (!e || ctx < 1 || n_steps < 1 || ctx + n_steps > e->cfg.max_ctx) { set_error("bad argument (ctx + n_steps must fit max_ctx)"); return B200_EINVAL; }
+  std::lock_guard<std::mutex> lk(e->mu);
+  B200_CUDA(cudaSetDevice(e->cfg.device));
+  int rc = e->ensure_graph();
+  if (rc) return rc;
+  // Start from a context of `ctx` tokens already "in" the cache (its contents do not change the bytes moved).
+  std::vector<int32_t> p(1, 1);
+  if ((rc = e->begin_sequence(p.data(), 1, n_steps + 3, 1))) return rc;
+  StepState s0 = {};
+  s0.pos = ctx - 1; s0.cur_token = 1; s0.n_prompt = 1; s0.max_out = n_steps + 3; s0.eos = -1; s0.greedy = 1;
+  B200_CUDA(cudaMemcpy(e->st, &s0, sizeof s0, cudaMemcpyHostToDevice));
+  if ((rc = e->launch_steps(3))) return rc;  // warm-up
+  cudaEvent_t e0, e1;
+  B200_CUDA(cudaEventCreate(&e0));
+  B200_CUDA(cudaEventCreate(&e1));
+  B200_CUDA(cudaEventRecord(e0, e->stream));
+  rc = e->launch_steps(n_steps);
+  cudaEventRecord(e1, e->stream);
+  cudaError_t ce = cudaStreamSynchronize(e->stream);
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  if (rc) return rc;
+  if (ce != cudaSuccess) return cuda_fail(ce, "bench_decode sync");
+  if (ms_per_step) *ms_per_step = ms / n_steps;
+  if (launches_per_step) *launches_per_step = e->launches_per_step;
+  return 0;
+}
+
+int b200_bench_kernel(b200_engine* h, const char* which, int iters, float* ms, int64_t* bytes) {
+  Engine* e = reinterpret_cast<Engine*>(h);
+  if (!e || !which || iters < 1) { set_error("bad argument"); return B200_EINVAL; }
+  std::lock_guard<std::mutex> lk(e->mu);
+  B200_CUDA(cudaSetDevice(e->cfg.device));
+  const b200_config& c = e->cfg;
+  const int d = c.d_model, qd = c.n_heads * kHeadDim, ff = c.d_ffn;
+  Layer& L = e->layers[0];
+  GemvArgs a = {};
+  int type, pro, epi;
+  if (!strcmp(which, "gate_up")) {
+    a.W = L.gate_up; a.N = 2 * ff; a.K = d; a.x = e->x; a.norm_w = L.ffn_norm; a.eps = c.rms_eps; a.y = e->h;
+    type = L.gu_type; pro = PRO_RMSNORM; epi = EPI_SWIGLU;
+  } else if (!strcmp(which, "down")) {
+    a.W = L.down; a.N = d; a.K = ff; a.x = e->h; a.y = e->att;  // y: scratch, never the live residual
+    type = L.down_type; pro = PRO_COPY; epi = EPI_STORE;
+  } else if (!strcmp(which, "attn_output")) {
+    a.W = L.o; a.N = d; a.K = qd; a.x = e->att; a.y = e->q;
+    type = L.o_type; pro = PRO_COPY; epi = EPI_STORE;
+  } else if (!strcmp(which, "lm_head")) {
+    a.W = e->output; a.N = c.vocab; a.K = d; a.x = e->x; a.norm_w = e->output_norm; a.eps = c.rms_eps; a.y = e->logits;
+    type = e->output_type; pro = PRO_RMSNORM; epi = EPI_STORE;
+  } else {
+    set_error("unknown kernel '%s' (gate_up, down, attn_output, lm_head)", which);
+    return B200_EINVAL;
+  }
+  if (!e->flush_buf) {
+    e->flush_bytes = (size_t)256 << 20;  // 2x the 126 MB L2
+    int rc = e->alloc(&e->flush_buf, e->flush_bytes);
+    if (rc) return rc;
+  }
+  cudaEvent_t e0, e1;
+  B200_CUDA(cudaEventCreate(&e0));
+  B200_CUDA(cudaEventCreate(&e1));
+  float total = 0.f;
+  for (int i = -3; i < iters; ++i) {
+    B200_CUDA(launch_l2_flush(e->flush_buf, e->flush_bytes, e->stream));
+    B200_CUDA(cudaEventRecord(e0, e->stream));
+    B200_CUDA(launch_gemv(type, pro, epi, a, e->stream, false, e->sm_count));
+    B200_CUDA(cudaEventRecord(e1, e->stream));
+    B200_CUDA(cudaStreamSynchronize(e->stream));
+    float t = 0.f;
+    cudaEventElapsedTime(&t, e0, e1);
+    if (i >= 0) total += t;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  if (ms) *ms = total / iters;
+  if (bytes) *bytes = (int64_t)a.N * (int64_t)gemv_row_bytes(type, a.K);
+  return 0;
+}
+
+}  // extern "C"

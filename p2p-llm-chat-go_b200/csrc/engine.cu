@@ -1,0 +1,512 @@
+// engine.cu — Engine: weights (fused, GPU-friendly layouts), paged KV pool, the CUDA-graph decode step,
+// greedy generation and the request worker.  Host code only; every number is produced by the kernels in
+// gemv.cu / attn.cu / misc.cu / gemm.cu / sampler.cu.
+#include "engine.h"
+
+#include <chrono>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+namespace b200 {
+
+static thread_local char g_err[512] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof g_err, fmt, ap);
+  va_end(ap);
+}
+const char* last_error() { return g_err; }
+int cuda_fail(cudaError_t e, const char* what) {
+  set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
+  (void)cudaGetLastError();
+  return (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) ? B200_ENODEV
+         : (e == cudaErrorMemoryAllocation)                           ? B200_ENOMEM
+                                                                      : B200_ECUDA;
+}
+
+static size_t tensor_row_bytes(int type, int64_t cols) {
+  return type == T_F32 ? (size_t)cols * 4 : gemv_row_bytes(type, cols);
+}
+
+// llama.cpp's Q4_K_M recipe (llama_tensor_get_type, use_more_bits): which layers keep attn_v / ffn_down in Q6_K
+static bool more_bits(int i, int n) { return i < n / 8 || i >= 7 * n / 8 || (i - n / 8) % 3 == 2; }
+
+Engine::~Engine() {
+  {
+    std::lock_guard<std::mutex> lk(qmu);
+    stopping = true;
+  }
+  qcv.notify_all();
+  if (worker.joinable()) worker.join();
+  if (stream) cudaStreamSynchronize(stream);
+  if (step_graph) cudaGraphExecDestroy(step_graph);
+  for (void* p : allocs) cudaFree(p);
+  if (out_tokens) cudaFreeHost(out_tokens);
+  if (host_n_out) cudaFreeHost((void*)host_n_out);
+  if (stream) cudaStreamDestroy(stream);
+}
+
+int Engine::alloc(void** p, size_t bytes) {
+  if (bytes == 0) bytes = 16;
+  cudaError_t e = cudaMalloc(p, bytes);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+  allocs.push_back(*p);
+  return 0;
+}
+
+int Engine::init(const b200_config& c) {
+  cfg = c;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    set_error("no CUDA device available (%s); libb200llm has no CPU fallback", cudaGetErrorString(e));
+    (void)cudaGetLastError();
+    return B200_ENODEV;
+  }
+  if (c.device < 0 || c.device >= ndev) {
+    set_error("device %d out of range (%d devices)", c.device, ndev);
+    return B200_EINVAL;
+  }
+  B200_CUDA(cudaSetDevice(c.device));
+  cudaDeviceProp prop;
+  B200_CUDA(cudaGetDeviceProperties(&prop, c.device));
+  if (prop.major != 10) {
+    set_error("device %d is sm_%d%d; this library only contains sm_100a code", c.device, prop.major, prop.minor);
+    return B200_ENODEV;
+  }
+  sm_count = prop.multiProcessorCount;
+  use_pdl = getenv("B200_NO_PDL") == nullptr;
+  use_graph = getenv("B200_NO_GRAPH") == nullptr;
+
+  const int d = c.d_model, qd = c.n_heads * c.head_dim, kvd = c.n_kv_heads * c.head_dim, ff = c.d_ffn;
+  if (c.head_dim != kHeadDim || c.n_layers <= 0 || c.n_kv_heads <= 0 || c.n_heads % c.n_kv_heads ||
+      c.max_ctx <= 0 || c.vocab <= 0 || c.max_seqs < 1) {
+    set_error("unsupported config (head_dim must be 128, n_heads %% n_kv_heads == 0, sizes > 0)");
+    return B200_EINVAL;
+  }
+  const int G = c.n_heads / c.n_kv_heads;
+  if (G != 1 && G != 2 && G != 4 && G != 8) {
+    set_error("GQA group %d unsupported (1,2,4,8)", G);
+    return B200_EINVAL;
+  }
+  const bool q4 = c.weight_format == B200_WEIGHTS_Q4_K_M;
+  if (!q4 && c.weight_format != B200_WEIGHTS_BF16) {
+    set_error("unknown weight_format %d", c.weight_format);
+    return B200_EINVAL;
+  }
+  const int tmat = q4 ? T_Q4_K : T_BF16, tbig = q4 ? T_Q6_K : T_BF16;
+  B200_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+
+  auto need = [&](int type, int64_t N, int64_t K, const char* what) -> int {
+    if (!gemv_shape_ok(type, N, K, 0)) {
+      set_error("shape %lldx%lld of %s not supported for tensor type %d (bf16: K%%256, Q4_K: K%%1024, Q6_K: K%%2048, N%%4)",
+                (long long)N, (long long)K, what, type);
+      return B200_EINVAL;
+    }
+    return 0;
+  };
+  auto add_slot = [&](const std::string& name, int type, int64_t rows, int64_t cols, uint8_t* base, int64_t row0,
+                      int64_t step) {
+    Slot s;
+    s.type = type; s.rows = rows; s.cols = cols; s.base = base; s.row0 = row0; s.row_step = step;
+    slots[name] = s;
+  };
+
+  layers.resize(c.n_layers);
+  weight_bytes = 0;
+  for (int l = 0; l < c.n_layers; ++l) {
+    Layer& L = layers[l];
+    const int tv = (q4 && more_bits(l, c.n_layers)) ? T_Q6_K : tmat;
+    const int tdown = tv;
+    int rc;
+    if ((rc = need(tmat, qd + kvd, d, "attn_q/k")) || (rc = need(tv, kvd, d, "attn_v")) || (rc = need(tmat, d, qd, "attn_output")) ||
+        (rc = need(tmat, 2 * ff, d, "ffn_gate/up")) || (rc = need(tdown, d, ff, "ffn_down")))
+      return rc;
+    const std::string p = "blk." + std::to_string(l) + ".";
+    L.qkv_type = tmat;
+    const size_t rb = gemv_row_bytes(tmat, d);
+    if (tv == tmat) {
+      if ((rc = alloc((void**)&L.qkv, (size_t)(qd + 2 * kvd) * rb))) return rc;
+      add_slot(p + "attn_v.weight", tv, kvd, d, L.qkv, qd + kvd, 1);
+    } else {
+      if ((rc = alloc((void**)&L.qkv, (size_t)(qd + kvd) * rb))) return rc;
+      if ((rc = alloc((void**)&L.v, (size_t)kvd * gemv_row_bytes(tv, d)))) return rc;
+      L.v_type = tv;
+      add_slot(p + "attn_v.weight", tv, kvd, d, L.v, 0, 1);
+    }
+    add_slot(p + "attn_q.weight", tmat, qd, d, L.qkv, 0, 1);
+    add_slot(p + "attn_k.weight", tmat, kvd, d, L.qkv, qd, 1);
+    L.o_type = tmat;
+    if ((rc = alloc((void**)&L.o, (size_t)d * gemv_row_bytes(tmat, qd)))) return rc;
+    add_slot(p + "attn_output.weight", tmat, d, qd, L.o, 0, 1);
+    L.gu_type = tmat;
+    if ((rc = alloc((void**)&L.gate_up, (size_t)2 * ff * rb))) return rc;
+    add_slot(p + "ffn_gate.weight", tmat, ff, d, L.gate_up, 0, 2);
+    add_slot(p + "ffn_up.weight", tmat, ff, d, L.gate_up, 1, 2);
+    L.down_type = tdown;
+    if ((rc = alloc((void**)&L.down, (size_t)d * gemv_row_bytes(tdown, ff)))) return rc;
+    add_slot(p + "ffn_down.weight", tdown, d, ff, L.down, 0, 1);
+    if ((rc = alloc((void**)&L.attn_norm, (size_t)d * 4)) || (rc = alloc((void**)&L.ffn_norm, (size_t)d * 4))) return rc;
+    add_slot(p + "attn_norm.weight", T_F32, 1, d, (uint8_t*)L.attn_norm, 0, 1);
+    add_slot(p + "ffn_norm.weight", T_F32, 1, d, (uint8_t*)L.ffn_norm, 0, 1);
+    weight_bytes += (int64_t)(qd + kvd) * rb + (int64_t)kvd * gemv_row_bytes(tv, d) + (int64_t)d * gemv_row_bytes(tmat, qd) +
+                    (int64_t)2 * ff * rb + (int64_t)d * gemv_row_bytes(tdown, ff) + 2 * (int64_t)d * 4;
+  }
+  {
+    int rc;
+    embd_type = tmat;
+    if (tmat == T_Q4_K && d % QK_K) { set_error("d_model must be a multiple of 256 for Q4_K embeddings"); return B200_EINVAL; }
+    if ((rc = need(tbig, c.vocab, d, "output"))) return rc;
+    if ((rc = alloc((void**)&token_embd, (size_t)c.vocab * tensor_row_bytes(tmat, d)))) return rc;
+    add_slot("token_embd.weight", tmat, c.vocab, d, token_embd, 0, 1);
+    output_type = tbig;
+    if ((rc = alloc((void**)&output, (size_t)c.vocab * gemv_row_bytes(tbig, d)))) return rc;
+    add_slot("output.weight", tbig, c.vocab, d, output, 0, 1);
+    if ((rc = alloc((void**)&output_norm, (size_t)d * 4))) return rc;
+    add_slot("output_norm.weight", T_F32, 1, d, (uint8_t*)output_norm, 0, 1);
+    weight_bytes += (int64_t)c.vocab * gemv_row_bytes(tbig, d) + (int64_t)d * 4;
+  }
+
+  // paged KV pool: page = 16 tokens of one kv head; static ownership (sequence slot s owns a page run)
+  pages_per_seq = (c.max_ctx + kPageTokens - 1) / kPageTokens;
+  const size_t n_pages = (size_t)pages_per_seq * c.max_seqs;
+  const size_t layer_kv = n_pages * c.n_kv_heads * kPageTokens * kHeadDim * 2;
+  for (auto& L : layers) {
+    int rc;
+    if ((rc = alloc((void**)&L.k_cache, layer_kv)) || (rc = alloc((void**)&L.v_cache, layer_kv))) return rc;
+  }
+  {
+    int rc;
+    if ((rc = alloc((void**)&block_table, n_pages * 4))) return rc;
+    std::vector<int32_t> bt(n_pages);
+    for (size_t i = 0; i < n_pages; ++i) bt[i] = (int32_t)i;
+    B200_CUDA(cudaMemcpy(block_table, bt.data(), n_pages * 4, cudaMemcpyHostToDevice));
+  }
+  // activations + sequence state
+  n_splits = 20;
+  {
+    int rc;
+    if ((rc = alloc((void**)&x, (size_t)d * 4)) || (rc = alloc((void**)&q, (size_t)qd * 4)) || (rc = alloc((void**)&att, (size_t)qd * 4)) ||
+        (rc = alloc((void**)&h, (size_t)ff * 4)) || (rc = alloc((void**)&logits, (size_t)c.vocab * 4)) ||
+        (rc = alloc((void**)&rope, (size_t)c.max_ctx * (kHeadDim / 2) * 2 * 4)) ||
+        (rc = alloc((void**)&attn_partial, attn_partial_floats(c.n_heads, c.n_kv_heads, n_splits) * 4)) ||
+        (rc = alloc((void**)&attn_counters, (size_t)c.n_kv_heads * 4)) || (rc = alloc((void**)&st, sizeof(StepState))) ||
+        (rc = alloc((void**)&prompt_dev, (size_t)c.max_ctx * 4)))
+      return rc;
+    B200_CUDA(cudaMemset(attn_counters, 0, (size_t)c.n_kv_heads * 4));
+    B200_CUDA(cudaMemset(st, 0, sizeof(StepState)));
+  }
+  B200_CUDA(cudaHostAlloc((void**)&out_tokens, (size_t)c.max_ctx * 4, cudaHostAllocMapped));
+  B200_CUDA(cudaHostGetDevicePointer((void**)&out_tokens_dev, out_tokens, 0));
+  B200_CUDA(cudaHostAlloc((void**)&host_n_out, 64, cudaHostAllocMapped));
+  B200_CUDA(cudaHostGetDevicePointer((void**)&host_n_out_dev, (void*)host_n_out, 0));
+  *host_n_out = 0;
+
+  {  // RoPE table in double on the host ("llama3" scaling), stored fp32: [max_ctx][64][2]
+    const int half = kHeadDim / 2;
+    std::vector<double> inv(half);
+    for (int i = 0; i < half; ++i) {
+      double f = 1.0 / std::pow((double)c.rope_theta, (2.0 * i) / kHeadDim);
+      if (c.rope_factor > 1.0f) {
+        const double lo_wl = (double)c.rope_orig_ctx / c.rope_low_freq_factor, hi_wl = (double)c.rope_orig_ctx / c.rope_high_freq_factor;
+        const double wl = 2.0 * M_PI / f;
+        if (wl > lo_wl) f = f / c.rope_factor;
+        else if (wl >= hi_wl) {
+          const double sm = ((double)c.rope_orig_ctx / wl - c.rope_low_freq_factor) / ((double)c.rope_high_freq_factor - c.rope_low_freq_factor);
+          f = (1.0 - sm) * f / c.rope_factor + sm * f;
+        }
+      }
+      inv[i] = f;
+    }
+    std::vector<float> tab((size_t)c.max_ctx * half * 2);
+    for (int p = 0; p < c.max_ctx; ++p)
+      for (int i = 0; i < half; ++i) {
+        const double a = (double)p * inv[i];
+        tab[((size_t)p * half + i) * 2] = (float)std::cos(a);
+        tab[((size_t)p * half + i) * 2 + 1] = (float)std::sin(a);
+      }
+    B200_CUDA(cudaMemcpy(rope, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice));
+  }
+  if (c.seed >= 0) {
+    int rc = synthesize();
+    if (rc) return rc;
+  }
+  B200_CUDA(cudaStreamSynchronize(stream));
+  worker = std::thread([this] { worker_loop(); });
+  return 0;
+}
+
+int Engine::place_tensor(const Slot& s, const uint8_t* src) {
+  const size_t rb = tensor_row_bytes(s.type, s.cols);
+  uint8_t* dst = s.base + (size_t)s.row0 * rb;
+  if (s.type == T_Q6_K && s.base != token_embd) {
+    B200_CUDA(launch_q6k_repack(src, dst, s.rows, s.cols / QK_K, 1, stream));
+  } else {
+    B200_CUDA(cudaMemcpy2DAsync(dst, (size_t)s.row_step * rb, src, rb, rb, (size_t)s.rows, cudaMemcpyDeviceToDevice, stream));
+  }
+  return 0;
+}
+
+int Engine::fetch_tensor(const Slot& s, uint8_t* dst) {
+  const size_t rb = tensor_row_bytes(s.type, s.cols);
+  const uint8_t* src = s.base + (size_t)s.row0 * rb;
+  if (s.type == T_Q6_K && s.base != token_embd) {
+    B200_CUDA(launch_q6k_repack(src, dst, s.rows, s.cols / QK_K, 0, stream));
+  } else {
+    B200_CUDA(cudaMemcpy2DAsync(dst, rb, src, (size_t)s.row_step * rb, rb, (size_t)s.rows, cudaMemcpyDeviceToDevice, stream));
+  }
+  return 0;
+}
+
+bool Engine::all_set() const {
+  for (auto& kv : slots)
+    if (!kv.second.set) return false;
+  return true;
+}
+
+int Engine::synthesize() {
+  size_t maxb = 0;
+  for (auto& kv : slots) maxb = std::max(maxb, (size_t)kv.second.rows * tensor_row_bytes(kv.second.type, kv.second.cols));
+  uint8_t* tmp = nullptr;
+  B200_CUDA(cudaMalloc((void**)&tmp, maxb));
+  uint32_t tid = 0;
+  int rc = 0;
+  for (auto& kv : slots) {  // std::map: deterministic (name-sorted) tensor ids
+    Slot& s = kv.second;
+    const float sigma = kv.first == "token_embd.weight" ? 1.0f : 1.0f / sqrtf((float)s.cols);
+    cudaError_t e = launch_synth(s.type, tmp, s.rows, s.cols, (uint64_t)cfg.seed, tid++, sigma, stream);
+    if (e != cudaSuccess) { rc = cuda_fail(e, "synth"); break; }
+    if ((rc = place_tensor(s, tmp))) break;
+    s.set = true;
+  }
+  cudaError_t e = cudaStreamSynchronize(stream);
+  cudaFree(tmp);
+  if (!rc && e != cudaSuccess) rc = cuda_fail(e, "synthesize sync");
+  return rc;
+}
+
+int Engine::enqueue_step(cudaStream_t s) {
+  const b200_config& c = cfg;
+  const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn;
+  int n = 0;
+  for (int l = 0; l < c.n_layers; ++l) {
+    Layer& L = layers[l];
+    GemvArgs a = {};
+    a.W = L.qkv; a.N = L.v ? qd + kvd : qd + 2 * kvd; a.K = d; a.x = x; a.norm_w = L.attn_norm; a.eps = c.rms_eps; a.y = q;
+    a.row_base = 0; a.q_rows = qd; a.kv_rows = kvd; a.n_kv_heads = c.n_kv_heads; a.rope = rope;
+    a.k_cache = L.k_cache; a.v_cache = L.v_cache; a.block_table = block_table; a.st = st;
+    B200_CUDA(launch_gemv(L.qkv_type, PRO_RMSNORM, EPI_QKV, a, s, use_pdl, sm_count)); ++n;
+    if (L.v) {
+      a.W = L.v; a.N = kvd; a.row_base = qd + kvd;
+      B200_CUDA(launch_gemv(L.v_type, PRO_RMSNORM, EPI_QKV, a, s, use_pdl, sm_count)); ++n;
+    }
+    AttnArgs t = {};
+    t.q = q; t.k_cache = L.k_cache; t.v_cache = L.v_cache; t.block_table = block_table; t.st = st;
+    t.n_heads = c.n_heads; t.n_kv_heads = c.n_kv_heads; t.out = att; t.partial = attn_partial; t.counters = attn_counters;
+    t.n_splits = n_splits; t.fixed_ctx = 0;
+    B200_CUDA(launch_attn_decode(t, s, use_pdl)); ++n;
+    GemvArgs o = {};
+    o.W = L.o; o.N = d; o.K = qd; o.x = att; o.y = x;
+    B200_CUDA(launch_gemv(L.o_type, PRO_COPY, EPI_RESID, o, s, use_pdl, sm_count)); ++n;
+    GemvArgs g = {};
+    g.W = L.gate_up; g.N = 2 * ff; g.K = d; g.x = x; g.norm_w = L.ffn_norm; g.eps = c.rms_eps; g.y = h;
+    B200_CUDA(launch_gemv(L.gu_type, PRO_RMSNORM, EPI_SWIGLU, g, s, use_pdl, sm_count)); ++n;
+    GemvArgs dn = {};
+    dn.W = L.down; dn.N = d; dn.K = ff; dn.x = h; dn.y = x;
+    B200_CUDA(launch_gemv(L.down_type, PRO_COPY, EPI_RESID, dn, s, use_pdl, sm_count)); ++n;
+  }
+  GemvArgs lm = {};
+  lm.W = output; lm.N = c.vocab; lm.K = d; lm.x = x; lm.norm_w = output_norm; lm.eps = c.rms_eps; lm.y = logits;
+  lm.st = st; lm.store_logits = 1; lm.argmax_key = &st->argmax_key;
+  B200_CUDA(launch_gemv(output_type, PRO_RMSNORM, EPI_LOGITS, lm, s, use_pdl, sm_count)); ++n;
+  FinishArgs f = {};
+  f.st = st; f.prompt = prompt_dev; f.out_tokens = out_tokens_dev; f.host_n_out = host_n_out_dev; f.embd = token_embd;
+  f.embd_type = embd_type; f.d_model = d; f.x = x; f.max_ctx = c.max_ctx;
+  B200_CUDA(launch_finish_step(f, s, use_pdl)); ++n;
+  launches_per_step = n;
+  return 0;
+}
+
+int Engine::ensure_graph() {
+  if (!use_graph || step_graph) return 0;
+  if (!all_set()) { set_error("not all tensors are set"); return B200_ESTATE; }
+  for (int attempt = 0; attempt < 2; ++attempt) {
+    cudaGraph_t g = nullptr;
+    cudaError_t e = cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaStreamBeginCapture");
+    int rc = enqueue_step(stream);
+    e = cudaStreamEndCapture(stream, &g);
+    if (rc == 0 && e == cudaSuccess) {
+      e = cudaGraphInstantiate(&step_graph, g, 0);
+      cudaGraphDestroy(g);
+      if (e == cudaSuccess) return 0;
+    } else if (g) {
+      cudaGraphDestroy(g);
+    }
+    (void)cudaGetLastError();
+    step_graph = nullptr;
+    if (use_pdl) {
+      use_pdl = false;  // retry the capture with plain stream-order edges
+      continue;
+    }
+    return rc ? rc : cuda_fail(e, "graph capture/instantiate");
+  }
+  return B200_ECUDA;
+}
+
+int Engine::launch_steps(int n) {
+  if (!all_set()) { set_error("not all tensors are set"); return B200_ESTATE; }
+  int rc = ensure_graph();
+  if (rc) return rc;
+  for (int i = 0; i < n; ++i) {
+    if (step_graph) B200_CUDA(cudaGraphLaunch(step_graph, stream));
+    else if ((rc = enqueue_step(stream))) return rc;
+  }
+  return 0;
+}
+
+int Engine::begin_sequence(const int32_t* prompt, int n_prompt, int max_out, int greedy) {
+  if (n_prompt < 1 || n_prompt > cfg.max_ctx || max_out < 1 || n_prompt + max_out - 1 > cfg.max_ctx) {
+    set_error("prompt of %d tokens + %d new tokens does not fit max_ctx %d", n_prompt, max_out, cfg.max_ctx);
+    return B200_EINVAL;
+  }
+  for (int i = 0; i < n_prompt; ++i)
+    if (prompt[i] < 0 || prompt[i] >= cfg.vocab) { set_error("token id %d out of range", prompt[i]); return B200_EINVAL; }
+  B200_CUDA(cudaMemcpyAsync(prompt_dev, prompt, (size_t)n_prompt * 4, cudaMemcpyHostToDevice, stream));
+  StepState s0 = {};
+  s0.pos = 0; s0.cur_token = prompt[0]; s0.n_prompt = n_prompt; s0.n_out = 0; s0.max_out = max_out; s0.eos = cfg.eos_token;
+  s0.done = 0; s0.greedy = greedy; s0.argmax_key = 0ull;
+  B200_CUDA(cudaMemcpyAsync(st, &s0, sizeof s0, cudaMemcpyHostToDevice, stream));
+  B200_CUDA(cudaStreamSynchronize(stream));  // s0 / prompt are stack / caller memory
+  *host_n_out = 0;
+  B200_CUDA(launch_embed(token_embd, embd_type, cfg.d_model, &st->cur_token, x, stream));
+  return 0;
+}
+
+int Engine::generate_greedy(const int32_t* prompt, int n_prompt, int32_t* ids, int n_new, int prefill_mode, float* ttft_ms,
+                            float* decode_ms) {
+  (void)prefill_mode;
+  int rc = ensure_graph();
+  if (rc) return rc;
+  if ((rc = begin_sequence(prompt, n_prompt, n_new, 1))) return rc;
+  cudaEvent_t e0, e1, e2;
+  B200_CUDA(cudaEventCreate(&e0));
+  B200_CUDA(cudaEventCreate(&e1));
+  B200_CUDA(cudaEventCreate(&e2));
+  B200_CUDA(cudaEventRecord(e0, stream));
+  rc = launch_steps(n_prompt);  // after these the first generated token exists
+  if (!rc) {
+    cudaEventRecord(e1, stream);
+    rc = launch_steps(n_new - 1);
+    cudaEventRecord(e2, stream);
+  }
+  cudaError_t e = cudaStreamSynchronize(stream);
+  if (!rc && e != cudaSuccess) rc = cuda_fail(e, "generate sync");
+  if (!rc) {
+    float a = 0, b = 0;
+    cudaEventElapsedTime(&a, e0, e1);
+    cudaEventElapsedTime(&b, e1, e2);
+    if (ttft_ms) *ttft_ms = a;
+    if (decode_ms) *decode_ms = b;
+    const int got = *host_n_out;
+    for (int i = 0; i < n_new; ++i) ids[i] = i < got ? out_tokens[i] : -1;
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
+  return rc;
+}
+
+int Engine::forward_logits(const int32_t* ids, int n, int mode, float* logits_host) {
+  (void)mode;
+  int rc = begin_sequence(ids, n, 1, 1);
+  if (rc) return rc;
+  if ((rc = launch_steps(n))) return rc;
+  B200_CUDA(cudaMemcpyAsync(logits_host, logits, (size_t)cfg.vocab * 4, cudaMemcpyDeviceToHost, stream));
+  B200_CUDA(cudaStreamSynchronize(stream));
+  return 0;
+}
+
+// One request at a time (batch-1 path): prefill, then decode in small launch windows while the host polls
+// the mapped token counter, so the GPU never waits on the host and EOS wastes at most `window` steps.
+void Engine::worker_loop() {
+  cudaSetDevice(cfg.device);
+  for (;;) {
+    Request* r;
+    {
+      std::unique_lock<std::mutex> lk(qmu);
+      qcv.wait(lk, [&] { return stopping || !queue.empty(); });
+      if (stopping) {
+        for (Request* p : queue) {
+          std::lock_guard<std::mutex> l2(p->mu);
+          p->finished = true; p->error = B200_ESTATE; p->cv.notify_all();
+        }
+        queue.clear();
+        return;
+      }
+      r = queue.front();
+      queue.pop_front();
+    }
+    using clk = std::chrono::steady_clock;
+    const auto t0 = clk::now();
+    int rc = 0, delivered = 0, reason = 0;
+    {
+      std::lock_guard<std::mutex> lk(mu);
+      const int n_prompt = (int)r->prompt.size();
+      int max_out = r->sp.num_predict > 0 ? r->sp.num_predict : cfg.max_ctx;
+      if (n_prompt + max_out - 1 > cfg.max_ctx) max_out = cfg.max_ctx - n_prompt + 1;
+      const int greedy = 1;  // sampler hook: set from r->sp once sample_kernel is in the graph
+      rc = max_out < 1 ? B200_EINVAL : begin_sequence(r->prompt.data(), n_prompt, max_out, greedy);
+      if (rc == B200_EINVAL && max_out < 1) set_error("prompt fills the whole context");
+      const auto t_load = clk::now();
+      auto t_first = t_load;
+      if (!rc) rc = launch_steps(n_prompt);
+      int launched = 1;  // decode steps launched that can produce tokens (the prefill's last step makes #1)
+      const int window = 4;
+      while (!rc) {
+        bool cancelled;
+        {
+          std::lock_guard<std::mutex> l2(r->mu);
+          cancelled = r->cancelled;
+        }
+        const int avail = *host_n_out;
+        if (avail > delivered) {
+          if (delivered == 0) t_first = clk::now();
+          std::lock_guard<std::mutex> l2(r->mu);
+          for (; delivered < avail; ++delivered) r->tokens.push_back(out_tokens[delivered]);
+          r->cv.notify_all();
+        }
+        if (cancelled) { reason = 3; break; }
+        if (delivered > 0 && (out_tokens[delivered - 1] == cfg.eos_token)) { reason = 1; break; }
+        if (delivered >= max_out) { reason = 2; break; }
+        if (launched < max_out && launched - delivered < window) {
+          rc = launch_steps(1);
+          ++launched;
+        } else {
+          std::this_thread::sleep_for(std::chrono::microseconds(20));
+        }
+      }
+      cudaStreamSynchronize(stream);
+      const auto t_end = clk::now();
+      auto ns = [](clk::time_point a, clk::time_point b) { return (int64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(b - a).count(); };
+      std::lock_guard<std::mutex> l2(r->mu);
+      r->stats.load_ns = ns(t0, t_load);
+      r->stats.prompt_eval_ns = ns(t_load, t_first);
+      r->stats.eval_ns = ns(t_first, t_end);
+      r->stats.total_ns = ns(t0, t_end);
+      r->stats.prompt_eval_count = n_prompt;
+      r->stats.eval_count = delivered;
+      r->stats.done_reason = rc ? 3 : reason;
+    }
+    {
+      std::lock_guard<std::mutex> l2(r->mu);
+      r->error = rc;
+      r->finished = true;
+      r->cv.notify_all();
+    }
+  }
+}
+
+}  // namespace b200

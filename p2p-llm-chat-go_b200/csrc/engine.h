@@ -1,0 +1,124 @@
+// engine.h — the host-side runtime of libb200llm: weights, paged KV pool, the captured decode-step graph,
+// and the request worker.  One Engine drives one GPU (data-parallel replicas = one Engine per process/GPU).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <condition_variable>
+#include <deque>
+#include <map>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/b200llm.h"
+#include "kernels.h"
+
+namespace b200 {
+
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what);  // records the message, returns B200_ECUDA
+
+#define B200_CUDA(expr)                                   \
+  do {                                                    \
+    cudaError_t _e = (expr);                              \
+    if (_e != cudaSuccess) return cuda_fail(_e, #expr);   \
+  } while (0)
+
+// Where a GGUF-named tensor lives on the device: a row range of a (possibly fused) buffer.
+struct Slot {
+  int type = -1;
+  int64_t rows = 0, cols = 0;
+  uint8_t* base = nullptr;  // device buffer holding this tensor's rows
+  int64_t row0 = 0;         // first row inside the buffer
+  int64_t row_step = 1;     // 2 for the interleaved gate/up buffer
+  bool set = false;
+};
+
+struct Layer {
+  // fused projection buffers (device layout of their type)
+  uint8_t* qkv = nullptr;  int qkv_type = -1;   // [q;k;v] rows, or [q;k] when V has another type
+  uint8_t* v = nullptr;    int v_type = -1;     // only when split from qkv
+  uint8_t* o = nullptr;    int o_type = -1;
+  uint8_t* gate_up = nullptr; int gu_type = -1; // rows interleaved gate_i, up_i
+  uint8_t* down = nullptr; int down_type = -1;
+  float* attn_norm = nullptr;
+  float* ffn_norm = nullptr;
+  uint16_t* k_cache = nullptr;  // [n_pages][n_kv][16][128]
+  uint16_t* v_cache = nullptr;
+};
+
+struct Request;
+
+struct Engine {
+  b200_config cfg{};
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  std::mutex mu;  // serialises every device-touching entry point
+
+  std::map<std::string, Slot> slots;
+  std::vector<Layer> layers;
+  uint8_t* token_embd = nullptr; int embd_type = -1;
+  uint8_t* output = nullptr;     int output_type = -1;
+  float* output_norm = nullptr;
+  std::vector<void*> allocs;
+  int64_t weight_bytes = 0;  // bytes streamed per decoded token (matrices + norms)
+
+  // activations and per-sequence state (batch-1 path)
+  float *x = nullptr, *q = nullptr, *att = nullptr, *h = nullptr, *logits = nullptr, *rope = nullptr;
+  float* attn_partial = nullptr;
+  unsigned int* attn_counters = nullptr;
+  int n_splits = 20;
+  StepState* st = nullptr;
+  int32_t* prompt_dev = nullptr;
+  int32_t* block_table = nullptr;  // [max_seqs][pages_per_seq]
+  int pages_per_seq = 0;
+  int32_t* out_tokens = nullptr;       // mapped pinned host
+  int32_t* out_tokens_dev = nullptr;   // device alias of the above
+  volatile int32_t* host_n_out = nullptr;
+  int32_t* host_n_out_dev = nullptr;
+
+  cudaGraphExec_t step_graph = nullptr;
+  bool use_pdl = true, use_graph = true;
+  int launches_per_step = 0;
+  void* flush_buf = nullptr;
+  size_t flush_bytes = 0;
+
+  // request worker
+  std::thread worker;
+  std::mutex qmu;
+  std::condition_variable qcv;
+  std::deque<Request*> queue;
+  bool stopping = false;
+
+  ~Engine();
+  int init(const b200_config& c);
+  int alloc(void** p, size_t bytes);
+  int place_tensor(const Slot& s, const uint8_t* dev_src);      // GGUF-layout rows on device -> slot
+  int fetch_tensor(const Slot& s, uint8_t* dev_dst);            // slot -> GGUF-layout rows on device
+  int synthesize();
+  bool all_set() const;
+
+  int enqueue_step(cudaStream_t s);          // launches the kernels of one decode step (capturable)
+  int ensure_graph();
+  int launch_steps(int n);                   // n graph replays (or direct launches)
+  int begin_sequence(const int32_t* prompt, int n_prompt, int max_out, int greedy);
+  int generate_greedy(const int32_t* prompt, int n_prompt, int32_t* ids, int n_new, int prefill_mode, float* ttft_ms,
+                      float* decode_ms);
+  int forward_logits(const int32_t* ids, int n, int mode, float* logits_host);
+  void worker_loop();
+};
+
+struct Request {
+  Engine* e = nullptr;
+  std::vector<int32_t> prompt;
+  b200_sampling sp{};
+  std::mutex mu;
+  std::condition_variable cv;
+  std::deque<int32_t> tokens;
+  bool finished = false, cancelled = false, done_delivered = false;
+  int error = 0;
+  b200_stats stats{};
+};
+
+}  // namespace b200

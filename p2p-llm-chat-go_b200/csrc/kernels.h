@@ -1,0 +1,108 @@
+// kernels.h — host-callable launchers of the sm_100a kernels (decode path + helpers).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200 {
+
+constexpr int kHeadDim = 128;    // Llama-3.1 8B and 70B
+constexpr int kPageTokens = 16;  // KV page = 16 tokens of one kv head = 4 KB (bf16)
+constexpr int QK_K = 256, Q4K_BYTES = 144, Q6K_BYTES = 210;  // GGUF k-quant super-block
+
+// ggml type ids (== B200_TYPE_*)
+enum { T_F32 = 0, T_Q4_K = 12, T_Q6_K = 14, T_BF16 = 30 };
+
+enum { PRO_COPY = 0, PRO_RMSNORM = 1 };
+enum { EPI_STORE = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_QKV = 3, EPI_LOGITS = 4 };
+
+// Device-resident state of the sequence being decoded; every kernel of a step reads it, the last kernel
+// of the step (finish_step) advances it, so one captured CUDA graph serves every position.
+struct StepState {
+  int32_t pos;        // position of the token being processed (== tokens already in the KV cache)
+  int32_t cur_token;  // token id at `pos`
+  int32_t n_prompt;   // prompt length; while pos+1 < n_prompt the next token is forced from the prompt
+  int32_t n_out;      // tokens generated so far
+  int32_t max_out;    // stop after this many generated tokens
+  int32_t eos;        // stop token (<0: none)
+  int32_t done;       // 0 running, 1 stop (EOS), 2 length
+  int32_t greedy;     // 1: token = argmax key; 0: token comes from sample_kernel via `sampled`
+  int32_t sampled;
+  int32_t pad_;
+  unsigned long long argmax_key;  // packed (ordered logit, ~index); reset every step
+};
+
+struct GemvArgs {
+  const uint8_t* W;  // weights, device layout of the tensor's type
+  int N, K;          // rows, cols
+  const float* x;    // input vector [K], fp32
+  const float* norm_w;  // PRO_RMSNORM: weight [K]
+  float eps;
+  float* y;  // STORE: y[N]; RESID: y[N] += W.x; SWIGLU: y[N/2]; QKV: q[q_rows]; LOGITS: logits[N]
+  // EPI_QKV
+  int row_base;  // logical row of W's row 0 in the fused [q;k;v] row space
+  int q_rows, kv_rows, n_kv_heads;
+  const float* rope;      // [max_ctx][64][2] cos,sin
+  uint16_t* k_cache;      // this layer: [n_pages][n_kv][16][128] bf16 bits
+  uint16_t* v_cache;
+  const int32_t* block_table;  // physical page of each logical page of the active sequence
+  const StepState* st;         // QKV: position; LOGITS: skip while prefilling
+  // EPI_LOGITS
+  int store_logits;
+  unsigned long long* argmax_key;
+};
+
+struct GemvPlan {  // launch geometry chosen on the host
+  int grid, block;
+  size_t smem;
+};
+
+// pdl: launch with programmatic stream serialization (kernel N+1 prefetches weights under kernel N's tail)
+cudaError_t launch_gemv(int wtype, int pro, int epi, const GemvArgs& a, cudaStream_t s, bool pdl, int sm_count);
+size_t gemv_row_bytes(int wtype, int64_t K);
+bool gemv_shape_ok(int wtype, int64_t N, int64_t K, int epi);
+
+struct AttnArgs {
+  const float* q;   // [n_heads*128] (already rotated)
+  const uint16_t* k_cache;
+  const uint16_t* v_cache;
+  const int32_t* block_table;
+  const StepState* st;  // ctx = st->pos + 1
+  int n_heads, n_kv_heads;
+  float* out;           // [n_heads*128]
+  float* partial;       // scratch [n_kv][n_splits][group][130]
+  unsigned int* counters;  // scratch [n_kv], must be zero before the first launch; self-resetting
+  int n_splits;
+  int fixed_ctx;        // >0: use this context length instead of st->pos+1 (test hook)
+};
+cudaError_t launch_attn_decode(const AttnArgs& a, cudaStream_t s, bool pdl);
+size_t attn_partial_floats(int n_heads, int n_kv_heads, int n_splits);
+
+struct FinishArgs {
+  StepState* st;
+  const int32_t* prompt;     // device [max_ctx]
+  int32_t* out_tokens;       // device-visible (mapped pinned host) [max_out]
+  volatile int32_t* host_n_out;  // mapped pinned host counter
+  const uint8_t* embd;       // token_embd in GGUF layout
+  int embd_type;
+  int d_model;
+  float* x;                  // residual stream for the next step
+  int max_ctx;
+};
+cudaError_t launch_finish_step(const FinishArgs& a, cudaStream_t s, bool pdl);
+cudaError_t launch_embed(const uint8_t* embd, int embd_type, int d_model, const int32_t* token_dev, float* x,
+                         cudaStream_t s);
+
+// dequantisation of GGUF-layout blocks (bit-exact w.r.t. ggml / gguf-py)
+cudaError_t launch_dequant(int type, const void* blocks, int64_t n_blocks, float* out_f32, uint16_t* out_bf16,
+                           cudaStream_t s);
+cudaError_t launch_quant_q16(const float* x, int64_t n, int16_t* q, float* d, cudaStream_t s);
+// Q6_K rows: GGUF block order <-> device section order ([ql][qh][scales][d] per row)
+cudaError_t launch_q6k_repack(const uint8_t* src, uint8_t* dst, int64_t rows, int64_t blocks_per_row, int to_device,
+                              cudaStream_t s);
+// deterministic random-init tensors (see synth.cu for the recipe)
+cudaError_t launch_synth(int type, void* dst, int64_t rows, int64_t cols, uint64_t seed, uint32_t tensor_id,
+                         float sigma, cudaStream_t s);
+cudaError_t launch_f32_to_bf16(const float* x, uint16_t* y, int64_t n, cudaStream_t s);
+cudaError_t launch_l2_flush(void* buf, size_t bytes, cudaStream_t s);
+
+}  // namespace b200

@@ -1,0 +1,263 @@
+// misc.cu — small sm_100a kernels around the decode path: GGUF block dequantisation (bit-exact w.r.t.
+// ggml / gguf-py), activation quantisation, Q6_K re-layout, deterministic random-init tensors,
+// the step epilogue (token hand-over + embedding gather) and an L2 flush for benchmarking.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200 {
+namespace {
+
+// ---- GGUF dequantisation ----------------------------------------------------------------------------
+// ggml-quants.c dequantize_row_q4_K: w = (d*sc)*q - (dmin*m); every product rounded to fp32 on its own
+// (no FMA contraction), which is what gguf-py's numpy code and the CPU oracle do.
+DEVINL void q4k_scale_min(int j, const uint8_t* q, int* sc, int* mn) {
+  if (j < 4) {
+    *sc = q[j] & 63;
+    *mn = q[j + 4] & 63;
+  } else {
+    *sc = (q[j + 4] & 0xF) | ((q[j - 4] >> 6) << 4);
+    *mn = (q[j + 4] >> 4) | ((q[j] >> 6) << 4);
+  }
+}
+
+DEVINL float dequant_q4k_elem(const uint8_t* blk, int i) {  // i in [0,256)
+  const float d = fp16_bits_to_f32(*reinterpret_cast<const uint16_t*>(blk));
+  const float dmin = fp16_bits_to_f32(*reinterpret_cast<const uint16_t*>(blk + 2));
+  const int sb = i >> 5, l = i & 31;
+  int sc, mn;
+  q4k_scale_min(sb, blk + 4, &sc, &mn);
+  const uint8_t qb = blk[16 + (sb >> 1) * 32 + l];
+  const int q = (sb & 1) ? (qb >> 4) : (qb & 0xF);
+  return __fsub_rn(__fmul_rn(__fmul_rn(d, (float)sc), (float)q), __fmul_rn(dmin, (float)mn));
+}
+
+DEVINL float dequant_q6k_elem(const uint8_t* blk, int i) {
+  const int half = i >> 7, t = (i & 127) >> 5, l = i & 31;
+  const uint8_t* ql = blk + half * 64;
+  const uint8_t* qh = blk + 128 + half * 32;
+  const int8_t* sc = reinterpret_cast<const int8_t*>(blk + 192) + half * 8;
+  const float d = fp16_bits_to_f32((uint16_t)(blk[208] | (blk[209] << 8)));
+  const uint8_t lb = ql[(t & 1) * 32 + l];
+  const int lo = (t >> 1) ? (lb >> 4) : (lb & 0xF);
+  const int q = (lo | (((qh[l] >> (2 * t)) & 3) << 4)) - 32;
+  return __fmul_rn(__fmul_rn(d, (float)sc[2 * t + l / 16]), (float)q);
+}
+
+__global__ void dequant_kernel(int type, const uint8_t* blocks, int64_t n_blocks, float* out_f32, uint16_t* out_bf16) {
+  const int64_t b = blockIdx.x;
+  if (b >= n_blocks) return;
+  const int i = threadIdx.x;  // 256 threads
+  const float v = (type == T_Q4_K) ? dequant_q4k_elem(blocks + b * Q4K_BYTES, i) : dequant_q6k_elem(blocks + b * Q6K_BYTES, i);
+  if (out_f32) out_f32[b * QK_K + i] = v;
+  if (out_bf16) out_bf16[b * QK_K + i] = f32_to_bf16_bits(v);
+}
+
+__global__ void quant_q16_kernel(const float* x, int64_t n, int16_t* q, float* d) {
+  const int64_t b = (int64_t)blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (b >= n / 32) return;
+  const float v = x[b * 32 + lane];
+  const float amax = warp_max(fabsf(v));
+  const float dd = __fdiv_rn(amax, 32767.0f);
+  const float id = dd > 0.f ? __fdiv_rn(1.0f, dd) : 0.f;
+  float r = rintf(__fmul_rn(v, id));
+  r = fminf(32767.f, fmaxf(-32767.f, r));
+  q[b * 32 + lane] = (int16_t)(int)r;
+  if (lane == 0) d[b] = dd;
+}
+
+// GGUF Q6_K row (nb blocks of 210 B: ql[128] qh[64] sc[16] d[2]) <-> device row [ql*nb][qh*nb][sc*nb][d*nb]
+__global__ void q6k_repack_kernel(const uint8_t* src, uint8_t* dst, int64_t rows, int64_t nb, int to_device) {
+  const int64_t row = blockIdx.y;
+  const int64_t blk = blockIdx.x;
+  const int t = threadIdx.x;  // 210 threads, one byte each
+  if (row >= rows || blk >= nb || t >= Q6K_BYTES) return;
+  const size_t rb = (size_t)nb * Q6K_BYTES;
+  size_t dev_off;
+  if (t < 128) dev_off = (size_t)blk * 128 + t;
+  else if (t < 192) dev_off = (size_t)nb * 128 + (size_t)blk * 64 + (t - 128);
+  else if (t < 208) dev_off = (size_t)nb * 192 + (size_t)blk * 16 + (t - 192);
+  else dev_off = (size_t)nb * 208 + (size_t)blk * 2 + (t - 208);
+  const size_t gguf_off = (size_t)blk * Q6K_BYTES + t;
+  if (to_device) dst[row * rb + dev_off] = src[row * rb + gguf_off];
+  else dst[row * rb + gguf_off] = src[row * rb + dev_off];
+}
+
+// ---- deterministic random-init tensors -----------------------------------------------------------------
+// Counter-based: every value is a pure function of (seed, tensor_id, index); integer hashing plus one
+// fp32 multiply, so the bytes do not depend on grid shape.  The CPU oracle never re-derives them: it reads
+// the tensors back through b200_get_tensor.
+DEVINL uint64_t splitmix64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+DEVINL uint64_t hash3(uint64_t seed, uint32_t tid, uint64_t idx) {
+  return splitmix64(splitmix64(seed * 0x9E3779B97F4A7C15ull + tid) ^ (idx * 0xD1B54A32D192ED03ull));
+}
+DEVINL float unit_pm1(uint64_t r) {  // uniform in [-1, 1), 24-bit
+  return (float)((int)(r >> 40) - (1 << 23)) * (1.0f / 8388608.0f);
+}
+
+__global__ void synth_kernel(int type, uint8_t* dst, int64_t rows, int64_t cols, uint64_t seed, uint32_t tid, float sigma) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (type == T_F32) {  // norm weights: 1 + 0.1 u
+    float* o = reinterpret_cast<float*>(dst);
+    for (int64_t i = i0; i < rows * cols; i += stride) o[i] = 1.0f + 0.1f * unit_pm1(hash3(seed, tid, i));
+  } else if (type == T_BF16) {  // uniform with std sigma
+    uint16_t* o = reinterpret_cast<uint16_t*>(dst);
+    const float a = 1.7320508f * sigma;
+    for (int64_t i = i0; i < rows * cols; i += stride) o[i] = f32_to_bf16_bits(unit_pm1(hash3(seed, tid, i)) * a);
+  } else if (type == T_Q4_K) {
+    // random nibbles and 6-bit scales; d chosen so that std(w) ~ sigma, dmin = 7.5 d centres the weights
+    const int64_t nblk = rows * cols / QK_K;
+    for (int64_t b = i0; b < nblk; b += stride) {
+      uint32_t* w = reinterpret_cast<uint32_t*>(dst + b * Q4K_BYTES);
+      for (int k = 0; k < Q4K_BYTES / 4; ++k) w[k] = (uint32_t)(hash3(seed, tid, b * 64 + k) >> 16);
+      const float u = 0.75f + 0.25f * (unit_pm1(hash3(seed, tid, b * 64 + 63)) + 1.0f);
+      const float d = sigma * (1.0f / 258.3f) * u;
+      const __half dh = __float2half_rn(d), mh = __float2half_rn(7.5f * __half2float(dh));
+      w[0] = (uint32_t)__half_as_ushort(dh) | ((uint32_t)__half_as_ushort(mh) << 16);
+    }
+  } else if (type == T_Q6_K) {  // GGUF block order; scales in [32,95]
+    const int64_t nblk = rows * cols / QK_K;
+    for (int64_t b = i0; b < nblk; b += stride) {
+      uint8_t* p = dst + b * Q6K_BYTES;
+      for (int k = 0; k < 192; k += 2) {
+        const uint32_t r = (uint32_t)(hash3(seed, tid, b * 128 + k / 2) >> 24);
+        p[k] = (uint8_t)r;
+        p[k + 1] = (uint8_t)(r >> 8);
+      }
+      for (int k = 0; k < 16; ++k) p[192 + k] = (uint8_t)(32 + ((hash3(seed, tid, b * 128 + 100 + k) >> 30) & 63));
+      const float u = 0.75f + 0.25f * (unit_pm1(hash3(seed, tid, b * 128 + 127)) + 1.0f);
+      const unsigned short dh = __half_as_ushort(__float2half_rn(sigma * (1.0f / 1221.0f) * u));
+      p[208] = (uint8_t)dh;
+      p[209] = (uint8_t)(dh >> 8);
+    }
+  }
+}
+
+__global__ void f32_to_bf16_kernel(const float* x, uint16_t* y, int64_t n) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) y[i] = f32_to_bf16_bits(x[i]);
+}
+
+__global__ void l2_flush_kernel(uint4* buf, size_t n16) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) buf[i] = make_uint4(i, 0, 0, 0);
+}
+
+// ---- embedding gather / step epilogue ----------------------------------------------------------------------
+DEVINL void embed_row(const uint8_t* embd, int type, int d_model, int token, float* x) {
+  for (int i = threadIdx.x; i < d_model; i += blockDim.x) {
+    float v;
+    if (type == T_BF16) v = __uint_as_float((uint32_t)reinterpret_cast<const uint16_t*>(embd)[(size_t)token * d_model + i] << 16);
+    else if (type == T_F32) v = reinterpret_cast<const float*>(embd)[(size_t)token * d_model + i];
+    else if (type == T_Q4_K) v = dequant_q4k_elem(embd + ((size_t)token * (d_model / QK_K) + i / QK_K) * Q4K_BYTES, i % QK_K);
+    else v = dequant_q6k_elem(embd + ((size_t)token * (d_model / QK_K) + i / QK_K) * Q6K_BYTES, i % QK_K);
+    x[i] = v;
+  }
+}
+
+__global__ void embed_kernel(const uint8_t* embd, int type, int d_model, const int32_t* token, float* x) {
+  embed_row(embd, type, d_model, *token, x);
+}
+
+// Last kernel of a decode step: picks the next token (forced from the prompt while prefilling token by
+// token, else argmax / sampled), publishes generated tokens to mapped host memory, advances the position
+// and gathers the next token's embedding into the residual stream.
+__global__ void finish_step_kernel(FinishArgs a) {
+  pdl_wait();
+  __shared__ int s_tok;
+  if (threadIdx.x == 0) {
+    StepState* st = a.st;
+    const int pos = st->pos;
+    int tok;
+    if (pos + 1 < st->n_prompt) {
+      tok = a.prompt[pos + 1];
+    } else {
+      tok = st->greedy ? (int)argmax_key_index(st->argmax_key) : st->sampled;
+      if (!st->done) {
+        const int n = st->n_out;
+        a.out_tokens[n] = tok;
+        st->n_out = n + 1;
+        if (tok == st->eos) st->done = 1;
+        else if (n + 1 >= st->max_out) st->done = 2;
+        __threadfence_system();
+        *a.host_n_out = n + 1;
+      }
+    }
+    st->argmax_key = 0ull;
+    st->cur_token = tok;
+    if (pos + 1 < a.max_ctx) st->pos = pos + 1;
+    s_tok = tok;
+  }
+  __syncthreads();
+  pdl_launch_dependents();
+  embed_row(a.embd, a.embd_type, a.d_model, s_tok, a.x);
+}
+
+}  // namespace
+
+cudaError_t launch_dequant(int type, const void* blocks, int64_t n_blocks, float* out_f32, uint16_t* out_bf16, cudaStream_t s) {
+  if (type != T_Q4_K && type != T_Q6_K) return cudaErrorInvalidValue;
+  if (n_blocks == 0) return cudaSuccess;
+  dequant_kernel<<<(unsigned)n_blocks, 256, 0, s>>>(type, (const uint8_t*)blocks, n_blocks, out_f32, out_bf16);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_quant_q16(const float* x, int64_t n, int16_t* q, float* d, cudaStream_t s) {
+  if (n % 32) return cudaErrorInvalidValue;
+  if (n == 0) return cudaSuccess;
+  const int64_t nb = n / 32;
+  quant_q16_kernel<<<(unsigned)((nb + 7) / 8), 256, 0, s>>>(x, n, q, d);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_q6k_repack(const uint8_t* src, uint8_t* dst, int64_t rows, int64_t nb, int to_device, cudaStream_t s) {
+  if (rows == 0 || nb == 0) return cudaSuccess;
+  for (int64_t r0 = 0; r0 < rows; r0 += 32768) {  // gridDim.y limit
+    const int64_t nr = rows - r0 < 32768 ? rows - r0 : 32768;
+    dim3 grid((unsigned)nb, (unsigned)nr);
+    q6k_repack_kernel<<<grid, 224, 0, s>>>(src + r0 * nb * Q6K_BYTES, dst + r0 * nb * Q6K_BYTES, nr, nb, to_device);
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_synth(int type, void* dst, int64_t rows, int64_t cols, uint64_t seed, uint32_t tensor_id, float sigma, cudaStream_t s) {
+  synth_kernel<<<1184, 256, 0, s>>>(type, (uint8_t*)dst, rows, cols, seed, tensor_id, sigma);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_f32_to_bf16(const float* x, uint16_t* y, int64_t n, cudaStream_t s) {
+  if (n == 0) return cudaSuccess;
+  f32_to_bf16_kernel<<<592, 256, 0, s>>>(x, y, n);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_l2_flush(void* buf, size_t bytes, cudaStream_t s) {
+  l2_flush_kernel<<<592, 256, 0, s>>>((uint4*)buf, bytes / 16);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_embed(const uint8_t* embd, int embd_type, int d_model, const int32_t* token_dev, float* x, cudaStream_t s) {
+  embed_kernel<<<1, 256, 0, s>>>(embd, embd_type, d_model, token_dev, x);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_finish_step(const FinishArgs& a, cudaStream_t s, bool pdl) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(1);
+  cfg.blockDim = dim3(256);
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, finish_step_kernel, a);
+}
+
+}  // namespace b200

@@ -1,0 +1,132 @@
+"""GPU parity, kernel level: each sm_100a kernel through the C ABI vs the CPU oracle on the same inputs.
+Bit-exact for integer/byte work (dequantisation, activation quantisation); stated tolerance for fp32 sums."""
+import os
+
+import numpy as np
+import pytest
+
+import __graft_entry__ as ge
+from oracle import orc
+from tests.util import random_tensor
+
+pytestmark = pytest.mark.gpu
+
+# fp32 accumulation in another order than the oracle's double sums: |err| <= TOL * sum_k |w_k x_k|
+GEMV_RTOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    p = ge.load_package()
+    p.lib()
+    assert p.device_count() >= 1, "gpu tests need a CUDA device"
+    return p
+
+
+@pytest.mark.parametrize("name,wtype", [("q4k", orc.Q4_K), ("q6k", orc.Q6_K)])
+def test_dequant_bit_exact_golden(pkg, golden_dir, name, wtype):
+    z = np.load(os.path.join(golden_dir, f"dequant_{name}.npz"))
+    got = pkg.dequant(z["blocks"], wtype).reshape(z["out"].shape)
+    assert np.array_equal(got.view(np.uint32), z["out"].view(np.uint32))
+
+
+@pytest.mark.parametrize("wtype,bs", [(orc.Q4_K, 144), (orc.Q6_K, 210)])
+@pytest.mark.parametrize("nb", [1, 7, 4096])
+def test_dequant_bit_exact_vs_oracle(pkg, wtype, bs, nb):
+    rng = np.random.default_rng(nb + bs)
+    blk = random_tensor(rng, wtype, nb, 256, sigma=0.05)
+    assert blk.size == nb * bs
+    got, want = pkg.dequant(blk, wtype), orc.dequant(blk, wtype)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+
+
+def test_dequant_empty(pkg):
+    assert pkg.dequant(np.zeros(0, np.uint8), pkg.Q4_K).size == 0
+
+
+@pytest.mark.parametrize("n", [32, 4096, 14336])
+def test_quant_q16_bit_exact(pkg, n):
+    rng = np.random.default_rng(n)
+    x = (rng.standard_normal(n) * np.exp(rng.uniform(-8, 4, n))).astype(np.float32)
+    x[:32] = 0.0                      # an all-zero block (d = 0)
+    if n > 64:
+        x[40] = 3.0e38                # huge magnitude
+    q, d = pkg.quant_q16(x)
+    q0, d0 = orc.quant_q16(x)
+    assert np.array_equal(q, q0) and np.array_equal(d.view(np.uint32), d0.view(np.uint32))
+
+
+def _gemv_case(pkg, wtype, rows, cols, seed, norm=False):
+    rng = np.random.default_rng(seed)
+    W = random_tensor(rng, wtype, rows, cols)
+    x = rng.standard_normal(cols).astype(np.float32) * 1.5
+    if norm:
+        nw = (1 + 0.1 * rng.standard_normal(cols)).astype(np.float32)
+        got = pkg.gemv(wtype, W, rows, cols, x, norm_w=nw, eps=1e-5)
+        xin = orc.rmsnorm(x, nw, 1e-5)
+    else:
+        got = pkg.gemv(wtype, W, rows, cols, x)
+        xin = x
+    want = orc.matmul(wtype, W, rows, cols, xin, mode=0)[0]
+    # error budget from the magnitude of the terms, not of the (cancelling) result
+    wabs = np.abs(orc.dequant(W, wtype).reshape(rows, cols)) if wtype in (orc.Q4_K, orc.Q6_K) else np.abs(
+        orc.bf16_to_f32(W).reshape(rows, cols))
+    budget = wabs @ np.abs(xin).astype(np.float64)
+    err = np.abs(got.astype(np.float64) - want)
+    tol = (2 if norm else 1) * GEMV_RTOL * budget  # norm: the fp32 inverse rms differs in the last ulp
+    assert (err <= tol + 1e-30).all(), (float((err / (budget + 1e-30)).max()), wtype, rows, cols)
+    return got, want
+
+
+@pytest.mark.parametrize("rows,cols", [(4, 256), (64, 512), (1028, 4096), (4096, 14336), (6144, 4096)])
+def test_gemv_bf16(pkg, rows, cols):
+    _gemv_case(pkg, orc.BF16, rows, cols, seed=rows + cols)
+
+
+@pytest.mark.parametrize("rows,cols", [(4, 1024), (520, 4096), (4096, 14336)])
+def test_gemv_q4k(pkg, rows, cols):
+    _gemv_case(pkg, orc.Q4_K, rows, cols, seed=rows + cols)
+
+
+@pytest.mark.parametrize("rows,cols", [(2, 2048), (514, 4096), (4096, 14336)])
+def test_gemv_q6k(pkg, rows, cols):
+    _gemv_case(pkg, orc.Q6_K, rows, cols, seed=rows + cols)
+
+
+@pytest.mark.parametrize("wtype,rows,cols", [(orc.BF16, 512, 4096), (orc.Q4_K, 512, 4096), (orc.Q6_K, 512, 4096)])
+def test_gemv_fused_rmsnorm(pkg, wtype, rows, cols):
+    _gemv_case(pkg, wtype, rows, cols, seed=99, norm=True)
+
+
+def test_gemv_linearity_full_size(pkg):
+    """Size-independent property at the 8B lm_head shape: W.(a+b) == W.a + W.b (bf16 weights, fp32 x)."""
+    rows, cols = 128256, 4096
+    rng = np.random.default_rng(5)
+    W = rng.integers(0, 65536, (rows, cols), dtype=np.uint16)
+    W &= np.uint16(0xBFFF)  # clear the top exponent bit: no inf/nan, |w| < 2
+    a = rng.standard_normal(cols).astype(np.float32)
+    b = rng.standard_normal(cols).astype(np.float32)
+    ya, yb, yab = (pkg.gemv(orc.BF16, W, rows, cols, v) for v in (a, b, a + b))
+    scale = np.abs(ya) + np.abs(yb) + 1.0
+    assert (np.abs(yab - (ya + yb)) <= 3e-4 * scale).all()
+
+
+def test_gemv_rejects_bad_shapes(pkg):
+    with pytest.raises(pkg.B200Error):
+        pkg.gemv(orc.BF16, np.zeros((4, 100), np.uint16), 4, 100, np.zeros(100, np.float32))
+    with pytest.raises(pkg.B200Error):
+        pkg.gemv(orc.Q4_K, np.zeros(144 * 3, np.uint8), 3, 256, np.zeros(256, np.float32))
+
+
+@pytest.mark.parametrize("n_ctx,n_heads,n_kv", [(1, 4, 1), (17, 8, 2), (640, 32, 8), (1000, 8, 1), (33, 2, 2)])
+def test_attn_decode(pkg, n_ctx, n_heads, n_kv):
+    rng = np.random.default_rng(n_ctx)
+    q = rng.standard_normal(n_heads * 128).astype(np.float32)
+    K = orc.bf16_to_f32(orc.f32_to_bf16(rng.standard_normal((n_ctx, n_kv * 128)).astype(np.float32)))
+    V = orc.bf16_to_f32(orc.f32_to_bf16(rng.standard_normal((n_ctx, n_kv * 128)).astype(np.float32)))
+    got = pkg.attn_decode(q, K, V, n_heads, n_kv)
+    want = orc.attention(q, K, V, n_heads, n_kv, 128)
+    assert np.abs(got - want).max() <= 2e-5 * max(1.0, np.abs(want).max())
+    # run it again: the ticket counters must have reset themselves
+    got2 = pkg.attn_decode(q, K, V, n_heads, n_kv)
+    assert np.array_equal(got, got2)

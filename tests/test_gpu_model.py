@@ -1,0 +1,132 @@
+"""GPU parity, whole model: logits within tolerance and greedy token ids identical to the CPU oracle,
+through the C ABI (b200_set_tensor / b200_forward_logits / b200_generate_greedy / b200_submit+b200_next)."""
+import numpy as np
+import pytest
+
+import __graft_entry__ as ge
+from oracle import orc
+from tests.util import engine_and_oracle, oracle_from_engine
+
+pytestmark = pytest.mark.gpu
+
+# logits: max-abs error relative to the largest |logit| of the position (fp32 sums in a different order,
+# bf16 KV rounding flips); measured values are ~1e-5, see profiles/.
+LOGIT_TOL = 1e-3
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    p = ge.load_package()
+    p.lib()
+    assert p.device_count() >= 1
+    return p
+
+
+def _prompt(cfg, n, seed):
+    return np.random.default_rng(seed).integers(0, cfg.vocab, n).astype(np.int32)
+
+
+@pytest.mark.parametrize("fmt", [0, 1])
+@pytest.mark.parametrize("source", ["numpy", "synth"])
+def test_logits_teacher_forced(pkg, fmt, source):
+    eng, ora, cfg = engine_and_oracle(pkg, fmt, n_layers=2, seed=11, source=source)
+    with eng:
+        toks = _prompt(cfg, 40, 1)
+        for n in (1, 2, 17, 40):
+            got = eng.forward_logits(toks[:n], pkg.MODE_GEMV)
+            ora.reset()
+            for t in toks[:n]:
+                want = ora.forward([t], mode=0)
+            err = np.abs(got - want).max()
+            assert err <= LOGIT_TOL * max(1.0, np.abs(want).max()), (fmt, source, n, err)
+            assert int(np.argmax(got)) == orc.argmax(want)[0]
+
+
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_greedy_128_tokens_identical(pkg, fmt):
+    eng, ora, cfg = engine_and_oracle(pkg, fmt, n_layers=2, seed=21, source="synth", max_ctx=256)
+    with eng:
+        prompt = _prompt(cfg, 32, 2)
+        ids, ttft, dec = eng.generate_greedy(prompt, 128, pkg.MODE_GEMV)
+        want, margins = ora.generate_greedy(prompt, 128, prefill_mode=0)
+        assert ids.tolist() == want.tolist(), (np.nonzero(ids != want)[0][:4], margins.min())
+        assert ttft > 0 and dec > 0
+
+
+def test_get_tensor_round_trips_set_tensor(pkg):
+    eng, ora, cfg = engine_and_oracle(pkg, 1, n_layers=2, seed=5, source="numpy")
+    with eng:
+        for name in eng.tensor_names():
+            t, r, c, buf = eng.get_tensor(name)
+            assert np.array_equal(buf, np.ascontiguousarray(ora._keep[name]).view(np.uint8).reshape(-1)), name
+
+
+def test_submit_next_streams_the_same_tokens(pkg):
+    eng, ora, cfg = engine_and_oracle(pkg, 0, n_layers=2, seed=31, source="synth")
+    with eng:
+        prompt = _prompt(cfg, 9, 3)
+        sp = pkg.default_sampling()
+        sp.temperature, sp.num_predict, sp.prefill_mode = 0.0, 24, pkg.MODE_GEMV
+        req = eng.submit(prompt, sp)
+        got = list(req.tokens())
+        st = req.stats()
+        req.free()
+        want, _ = ora.generate_greedy(prompt, 24, prefill_mode=0)
+        assert got == want.tolist()
+        assert st.eval_count == 24 and st.prompt_eval_count == 9 and st.done_reason == 2
+        assert st.total_ns >= st.eval_ns > 0
+        # two requests queued back to back are served in order on the same engine
+        r1, r2 = eng.submit(prompt, sp), eng.submit(prompt[:4], sp)
+        a, b = list(r1.tokens()), list(r2.tokens())
+        r1.free(); r2.free()
+        assert a == want.tolist()
+        want2, _ = ora.generate_greedy(prompt[:4], 24, prefill_mode=0)
+        assert b == want2.tolist()
+
+
+def test_eos_stops_generation(pkg):
+    eng, ora, cfg = engine_and_oracle(pkg, 0, n_layers=2, seed=41, source="synth")
+    with eng:
+        prompt = _prompt(cfg, 5, 4)
+        want, _ = ora.generate_greedy(prompt, 12, prefill_mode=0)
+    cfg2 = eng.cfg
+    cfg2.eos_token = int(want[5])
+    first = int(np.nonzero(want == want[5])[0][0])
+    with pkg.Engine(cfg2) as eng2:
+        sp = pkg.default_sampling()
+        sp.temperature, sp.num_predict, sp.prefill_mode = 0.0, 12, pkg.MODE_GEMV
+        req = eng2.submit(prompt, sp)
+        got = list(req.tokens())
+        st = req.stats()
+        req.free()
+        assert got == want[:first + 1].tolist() and st.done_reason == 1
+
+
+def test_rejects_bad_requests(pkg):
+    eng, ora, cfg = engine_and_oracle(pkg, 0, n_layers=2, seed=1, source="synth", max_ctx=64)
+    with eng:
+        with pytest.raises(pkg.B200Error):
+            eng.forward_logits(np.array([cfg.vocab], np.int32))      # id out of range
+        with pytest.raises(pkg.B200Error):
+            eng.forward_logits(np.zeros(65, np.int32))               # longer than max_ctx
+        with pytest.raises(pkg.B200Error):
+            eng.generate_greedy(np.zeros(60, np.int32), 10)          # prompt + new > max_ctx
+
+
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_full_size_8b_few_tokens(pkg, fmt):
+    """BASELINE shape (Llama-3.1-8B, random-init): 3-token prompt + 3 greedy tokens vs the CPU oracle."""
+    cfg = pkg.llama31_8b()
+    cfg.weight_format, cfg.seed, cfg.max_ctx, cfg.eos_token = fmt, 0, 64, -1
+    with pkg.Engine(cfg) as eng:
+        ora = oracle_from_engine(eng)
+        prompt = np.array([128000, 9906, 1917], np.int32)
+        got = eng.forward_logits(prompt, pkg.MODE_GEMV)
+        ora.reset()
+        for t in prompt:
+            want = ora.forward([t], mode=0)
+        err = np.abs(got - want).max()
+        assert err <= LOGIT_TOL * max(1.0, np.abs(want).max()), err
+        ids, _, _ = eng.generate_greedy(prompt, 3, pkg.MODE_GEMV)
+        want_ids, margins = ora.generate_greedy(prompt, 3, prefill_mode=0)
+        assert ids.tolist() == want_ids.tolist(), (ids, want_ids, margins)
