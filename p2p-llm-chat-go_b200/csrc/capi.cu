@@ -241,7 +241,7 @@ int b200_next(b200_req* h, int32_t* id, int* done, int timeout_ms) {
   }
   *id = r->tokens.front();
   r->tokens.pop_front();
-  *done = (r->finished && r->tokens.empty()) ? 1 : 0;
+  *done = (r->complete && r->tokens.empty()) ? 1 : 0;
   if (*done) r->done_delivered = true;
   return 0;
 }
@@ -249,7 +249,9 @@ int b200_next(b200_req* h, int32_t* id, int* done, int timeout_ms) {
 int b200_stats_get(b200_req* h, b200_stats* out) {
   Request* r = reinterpret_cast<Request*>(h);
   if (!r || !out) { set_error("null argument"); return B200_EINVAL; }
-  std::lock_guard<std::mutex> lk(r->mu);
+  std::unique_lock<std::mutex> lk(r->mu);
+  // the counters are final once the worker has drained the stream; that is moments after the last token
+  if (r->complete || r->cancelled) r->cv.wait(lk, [&] { return r->finished; });
   *out = r->stats;
   return 0;
 }

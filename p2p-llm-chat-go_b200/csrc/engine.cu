@@ -178,6 +178,8 @@ int Engine::init(const b200_config& c) {
   for (auto& L : layers) {
     int rc;
     if ((rc = alloc((void**)&L.k_cache, layer_kv)) || (rc = alloc((void**)&L.v_cache, layer_kv))) return rc;
+    B200_CUDA(cudaMemsetAsync(L.k_cache, 0, layer_kv, stream));
+    B200_CUDA(cudaMemsetAsync(L.v_cache, 0, layer_kv, stream));
   }
   {
     int rc;
@@ -475,7 +477,11 @@ void Engine::worker_loop() {
         if (avail > delivered) {
           if (delivered == 0) t_first = clk::now();
           std::lock_guard<std::mutex> l2(r->mu);
-          for (; delivered < avail; ++delivered) r->tokens.push_back(out_tokens[delivered]);
+          for (; delivered < avail; ++delivered) {
+            r->tokens.push_back(out_tokens[delivered]);
+            // the consumer learns "this was the last token" together with the token itself
+            if (out_tokens[delivered] == cfg.eos_token || delivered + 1 >= max_out) r->complete = true;
+          }
           r->cv.notify_all();
         }
         if (cancelled) { reason = 3; break; }

@@ -117,6 +117,7 @@ struct Request {
   std::condition_variable cv;
   std::deque<int32_t> tokens;
   bool finished = false, cancelled = false, done_delivered = false;
+  bool complete = false;  // the final token (EOS / length) has been queued
   int error = 0;
   b200_stats stats{};
 };
