@@ -19,6 +19,7 @@ namespace {
 constexpr int kTile = 32;
 constexpr int kKStride = 65;  // words per K row in smem (64 data + 1 pad): lane=token reads are conflict-free
 constexpr int kPart = kHeadDim + 2;  // acc[128], m, l
+constexpr int kMaxSplits = 32;
 
 template <int G>
 __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnArgs a) {
@@ -117,21 +118,37 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnArgs a) {
   __syncthreads();
   if (!s_last) return;
   __threadfence();
+  // merge the splits: (m, l) of every (head, split) into shared memory with one parallel round of loads,
+  // softmax weights per split, then one pass over the partial accumulators with independent loads
   const float* base = a.partial + (size_t)kvh * S * G * kPart;
+  float* w_s = reinterpret_cast<float*>(Ks);  // [G][S] weights, reusing the K tile (G*S <= 8*32 floats)
+  float* l_s = w_s + G * kMaxSplits;
+  for (int i = tid; i < G * S; i += 128) {
+    const int h = i / S, sp = i % S;
+    const float* ps = base + ((size_t)sp * G + h) * kPart;
+    w_s[h * kMaxSplits + sp] = __ldcg(ps + kHeadDim);
+    l_s[h * kMaxSplits + sp] = __ldcg(ps + kHeadDim + 1);
+  }
+  __syncthreads();
+  if (tid < G) {
+    float M = -INFINITY;
+    for (int sp = 0; sp < S; ++sp) M = fmaxf(M, w_s[tid * kMaxSplits + sp]);
+    float den = 0.f;
+    for (int sp = 0; sp < S; ++sp) {
+      const float ms = w_s[tid * kMaxSplits + sp];
+      const float w = (ms == -INFINITY) ? 0.f : expf(ms - M);
+      den = fmaf(l_s[tid * kMaxSplits + sp], w, den);
+      w_s[tid * kMaxSplits + sp] = w;
+    }
+    corr_s[tid] = 1.0f / den;
+  }
+  __syncthreads();
 #pragma unroll
   for (int h = 0; h < G; ++h) {
-    float M = -INFINITY;
-    for (int s = 0; s < S; ++s) M = fmaxf(M, __ldcg(base + ((size_t)s * G + h) * kPart + kHeadDim));
-    float num = 0.f, den = 0.f;
-    for (int s = 0; s < S; ++s) {
-      const float* ps = base + ((size_t)s * G + h) * kPart;
-      const float ms = __ldcg(ps + kHeadDim);
-      if (ms == -INFINITY) continue;
-      const float w = expf(ms - M);
-      num = fmaf(__ldcg(ps + tid), w, num);
-      den = fmaf(__ldcg(ps + kHeadDim + 1), w, den);
-    }
-    a.out[((size_t)kvh * G + h) * kHeadDim + tid] = num / den;
+    float num = 0.f;
+#pragma unroll 4
+    for (int sp = 0; sp < S; ++sp) num = fmaf(__ldcg(base + ((size_t)sp * G + h) * kPart + tid), w_s[h * kMaxSplits + sp], num);
+    a.out[((size_t)kvh * G + h) * kHeadDim + tid] = num * corr_s[h];
   }
   if (tid == 0) a.counters[kvh] = 0u;
 }
@@ -143,7 +160,7 @@ size_t attn_partial_floats(int n_heads, int n_kv_heads, int n_splits) {
 }
 
 cudaError_t launch_attn_decode(const AttnArgs& a, cudaStream_t s, bool pdl) {
-  if (a.n_kv_heads <= 0 || a.n_heads % a.n_kv_heads || a.n_splits <= 0) return cudaErrorInvalidValue;
+  if (a.n_kv_heads <= 0 || a.n_heads % a.n_kv_heads || a.n_splits <= 0 || a.n_splits > kMaxSplits) return cudaErrorInvalidValue;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(a.n_kv_heads, a.n_splits);
   cfg.blockDim = dim3(128);

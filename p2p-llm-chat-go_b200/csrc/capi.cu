@@ -372,11 +372,30 @@ int b200_attn_decode(const float* q, const float* k, const float* v, int n_ctx, 
 }
 
 int b200_gemm(int type, const void* w, int64_t rows, int64_t cols, const float* x, int64_t n, float* y) {
-  (void)type; (void)w; (void)rows; (void)cols; (void)x; (void)n; (void)y;
   int rc = have_device();
   if (rc) return rc;
-  set_error("b200_gemm: tcgen05 GEMM not linked into this build");
-  return B200_ESTATE;
+  if (!w || !x || !y) { set_error("null argument"); return B200_EINVAL; }
+  if (type != T_BF16 && type != T_Q4_K && type != T_Q6_K) { set_error("b200_gemm: type must be BF16, Q4_K or Q6_K"); return B200_EINVAL; }
+  if (!gemm_shape_ok(rows, cols, n) || (type != T_BF16 && cols % QK_K)) {
+    set_error("gemm shape rows=%lld (need %%128) cols=%lld (need %%64; %%256 for k-quants) n=%lld unsupported", (long long)rows, (long long)cols, (long long)n);
+    return B200_EINVAL;
+  }
+  DevBuf dw, dw16, dxf, dx16, dy;
+  const size_t wbytes = (size_t)rows * gemv_row_bytes(type, cols);
+  if ((rc = dw.alloc(wbytes)) || (rc = dxf.alloc((size_t)n * cols * 4)) || (rc = dx16.alloc((size_t)n * cols * 2)) || (rc = dy.alloc((size_t)n * rows * 4))) return rc;
+  B200_CUDA(cudaMemcpy(dw.p, w, wbytes, cudaMemcpyHostToDevice));
+  const uint16_t* w16 = dw.as<uint16_t>();
+  if (type != T_BF16) {  // GEMM numerics: k-quant weights are dequantised and rounded to bf16
+    if ((rc = dw16.alloc((size_t)rows * cols * 2))) return rc;
+    B200_CUDA(launch_dequant(type, dw.p, rows * cols / QK_K, nullptr, dw16.as<uint16_t>(), 0));
+    w16 = dw16.as<uint16_t>();
+  }
+  B200_CUDA(cudaMemcpy(dxf.p, x, (size_t)n * cols * 4, cudaMemcpyHostToDevice));
+  B200_CUDA(launch_f32_to_bf16(dxf.as<float>(), dx16.as<uint16_t>(), n * cols, 0));
+  B200_CUDA(launch_gemm_bf16(w16, rows, cols, dx16.as<uint16_t>(), n, dy.as<float>(), rows, 0));
+  B200_CUDA(cudaDeviceSynchronize());
+  B200_CUDA(cudaMemcpy(y, dy.p, (size_t)n * rows * 4, cudaMemcpyDeviceToHost));
+  return 0;
 }
 
 int b200_sample(const float* logits, int vocab, const b200_sampling* s, const int32_t* history, int n_hist, uint64_t step, int32_t* id) {

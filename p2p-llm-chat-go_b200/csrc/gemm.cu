@@ -1,0 +1,232 @@
+// gemm.cu — bf16 GEMM on the 5th-generation tensor cores (tcgen05.mma, accumulators in TMEM, operands
+// staged by TMA with 128-byte swizzle) for the paths that really are dense contractions: prefill and
+// batched decode.  Y[t][r] = sum_k X[t][k] * W[r][k]   (X: tokens x K bf16, W: rows x K bf16, Y fp32).
+//
+// "Swap-AB" orientation: the weight tile is the M operand (128 rows = 128 TMEM lanes), the token tile is
+// the N operand (BN = 128 or 256 TMEM columns).  Both operands are K-major, which is how the weights
+// already sit in HBM for the GEMV path, so bf16 models share one copy between decode and prefill; small
+// token counts (batched decode) only shrink N.  The epilogue reads the accumulator with tcgen05.ld
+// (lane = weight row, column = token), so for each token 32 lanes store 32 consecutive floats.
+//
+// Warp roles (192 threads): warp 0 = TMA producer (one elected lane), warp 1 = TMEM allocator + MMA issuer
+// (one elected lane), warps 2..5 = epilogue (TMEM lane quadrant = warp % 4).  A ring of STAGES
+// {A 128x64, B BNx64} tiles is handed between them with full/empty mbarriers; tcgen05.commit releases
+// a stage when the MMAs that read it have retired.  Two CTAs fit per SM (smem <= 113 KB, TMEM 2 x <=256
+// columns), so one CTA's epilogue overlaps the other's main loop.
+//
+// Numerics (oracle mode 1): inputs bf16, products exact, fp32 accumulation in TMEM.
+#include <cuda.h>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200 {
+namespace {
+
+constexpr int BM = 128, BK = 64;  // BK * 2 B = 128 B = one swizzle row
+constexpr uint32_t A_BYTES = BM * BK * 2;
+
+DEVINL void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar)
+      : "memory");
+}
+DEVINL void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+DEVINL void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+DEVINL void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc]^T, kind::f16 (bf16 inputs, fp32 accumulate), issued by ONE thread
+DEVINL void tc_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor, sm_100 version 1):
+// start>>4 [0,14) | LBO>>4 [16,30) (unused for swizzled K-major) | SBO>>4 [32,46) = 1024 B between 8-row
+// groups | version=1 [46,48) | layout=SWIZZLE_128B(2) [61,64)
+DEVINL uint64_t smem_desc_sw128(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) |
+         ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+}
+// Instruction descriptor (cute::UMMA::InstrDescriptor): c=F32 [4,6)=1, a=BF16 [7,10)=1, b=BF16 [10,13)=1,
+// a/b K-major (bits 15,16 = 0), N>>3 [17,23), M>>4 [24,29)
+__host__ __device__ constexpr uint32_t instr_desc(int M, int N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int STAGES = (BN == 128) ? 3 : 2;
+  static constexpr uint32_t B_BYTES = BN * BK * 2;
+  static constexpr uint32_t STAGE = A_BYTES + B_BYTES;
+  static constexpr size_t SMEM = (size_t)STAGES * STAGE + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+struct GemmArgs {
+  float* y;
+  int ldy;       // floats between consecutive tokens of y
+  int n_tokens;  // valid tokens (TMA zero-fills the rest of a token tile)
+  int k_blocks;  // K / 64
+};
+
+template <int BN>
+__global__ void __launch_bounds__(192) gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                         const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
+  using C = GemmCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  // SWIZZLE_128B tiles must start on 1024-byte boundaries
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t tiles = (raw + 1023u) & ~1023u;
+  uint8_t* bar_mem = smem_raw + (tiles - raw) + C::STAGES * C::STAGE;
+  uint64_t* full = reinterpret_cast<uint64_t*>(bar_mem);
+  uint64_t* empty = full + C::STAGES;
+  uint64_t* tmem_full = empty + C::STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  const uint32_t full_s = smem_u32(full), empty_s = smem_u32(empty), tfull_s = smem_u32(tmem_full);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(full_s + 8 * s, 1);
+      mbar_init(empty_s + 8 * s, 1);
+    }
+    mbar_init(tfull_s, 1);
+    mbar_fence_init();
+  }
+  if (warp == 1) {  // whole warp: allocate BN TMEM columns (power of two >= 32), then give up the permit
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(BN) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {  // ===== TMA producer =====
+      int s = 0;
+      uint32_t ph = 0;
+      for (int kb = 0; kb < g.k_blocks; ++kb) {
+        mbar_wait(empty_s + 8 * s, ph ^ 1);
+        const uint32_t dst = tiles + s * C::STAGE;
+        mbar_expect_tx(full_s + 8 * s, C::STAGE);
+        tma_load_2d(dst, &tmA, kb * BK, m0, full_s + 8 * s);
+        tma_load_2d(dst + A_BYTES, &tmB, kb * BK, n0, full_s + 8 * s);
+        if (++s == C::STAGES) { s = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {  // ===== MMA issuer =====
+      constexpr uint32_t idesc = instr_desc(BM, BN);
+      int s = 0;
+      uint32_t ph = 0;
+      for (int kb = 0; kb < g.k_blocks; ++kb) {
+        mbar_wait(full_s + 8 * s, ph);
+        tc_fence_after();
+        const uint64_t ad = smem_desc_sw128(tiles + s * C::STAGE);
+        const uint64_t bd = smem_desc_sw128(tiles + s * C::STAGE + A_BYTES);
+#pragma unroll
+        for (int k = 0; k < BK / 16; ++k)  // UMMA_K = 16 bf16 = 32 B: advance the start address by 2 (x16 B)
+          tc_mma(tmem_base, ad + 2 * k, bd + 2 * k, idesc, (uint32_t)(kb | k));
+        tc_commit(empty_s + 8 * s);  // stage reusable once these MMAs have read it
+        if (++s == C::STAGES) { s = 0; ph ^= 1; }
+      }
+      tc_commit(tfull_s);  // accumulator complete
+    }
+  } else {  // ===== epilogue: TMEM -> registers -> global =====
+    mbar_wait(tfull_s, 0);
+    tc_fence_after();
+    const int quad = warp & 3;  // a warp may only touch TMEM lanes [32*(warp%4), +32)
+    const int row = m0 + quad * 32 + lane;
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      uint32_t v[32];
+      const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(c * 32);
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+          "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+          : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+            "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
+            "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+            "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+          : "r"(taddr));
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int tok = n0 + c * 32 + j;
+        if (tok < g.n_tokens) g.y[(size_t)tok * g.ldy + row] = __uint_as_float(v[j]);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(BN) : "memory");
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// bf16 [rows][K] row-major -> 2-D tensor map with a {64 (K), box_rows} box, 128-byte swizzle
+bool make_map(CUtensorMap* m, const void* base, uint64_t rows, uint64_t K, uint32_t box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return false;
+  const cuuint64_t dims[2] = {K, rows};
+  const cuuint64_t strides[1] = {K * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <int BN>
+cudaError_t launch_bn(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y, int64_t ldy,
+                      cudaStream_t s) {
+  CUtensorMap ma, mb;
+  if (!make_map(&ma, W, (uint64_t)rows, (uint64_t)K, BM) || !make_map(&mb, X, (uint64_t)n_tokens, (uint64_t)K, BN))
+    return cudaErrorInvalidValue;
+  auto kern = gemm_bf16_kernel<BN>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmCfg<BN>::SMEM);
+  if (e != cudaSuccess) return e;
+  GemmArgs g;
+  g.y = Y; g.ldy = (int)ldy; g.n_tokens = (int)n_tokens; g.k_blocks = (int)(K / BK);
+  dim3 grid((unsigned)(rows / BM), (unsigned)((n_tokens + BN - 1) / BN));
+  kern<<<grid, 192, GemmCfg<BN>::SMEM, s>>>(ma, mb, g);
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+bool gemm_shape_ok(int64_t rows, int64_t K, int64_t n_tokens) {
+  return rows > 0 && rows % BM == 0 && K > 0 && K % BK == 0 && n_tokens > 0 && n_tokens <= (1 << 20);
+}
+
+// Y[t*ldy + r] = sum_k X[t][k] W[r][k];  W, X bf16 (K-major, 16-byte aligned rows), Y fp32.
+cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
+                             int64_t ldy, cudaStream_t s) {
+  if (!gemm_shape_ok(rows, K, n_tokens)) return cudaErrorInvalidValue;
+  // token tile: 256 when that still yields >= 2 CTAs per SM of work, else 128 (more, smaller tiles)
+  const int64_t tiles256 = (rows / BM) * ((n_tokens + 255) / 256);
+  if (n_tokens > 128 && tiles256 >= 296) return launch_bn<256>(W, rows, K, X, n_tokens, Y, ldy, s);
+  return launch_bn<128>(W, rows, K, X, n_tokens, Y, ldy, s);
+}
+
+}  // namespace b200

@@ -25,7 +25,7 @@ namespace b200 {
 
 namespace {
 
-constexpr int kWarps = 8;  // consumer warps per CTA (each is its own TMA producer)
+constexpr int kWarps = 16;  // consumer warps per CTA (each is its own TMA producer); one CTA per SM
 
 // ------------------------------------------------------------------ block helpers
 DEVINL float block_sum(float v, float* red, int warp, int lane) {
@@ -57,7 +57,7 @@ DEVINL float rms_inv(const GemvArgs& a, float* red, int warp, int lane) {
 
 template <int KC>  // KC in {256, 512}
 struct FmtBF16 {
-  static constexpr int R = 4, CHUNK = KC, STAGES = 3;
+  static constexpr int R = 4, CHUNK = KC, STAGES = 2;
   static constexpr int ROW_STAGE_BYTES = KC * 2;
   static constexpr int STAGE_BYTES = R * ROW_STAGE_BYTES;
   static __host__ __device__ size_t x_bytes(int K) { return (size_t)K * 4; }
@@ -154,7 +154,7 @@ DEVINL void q16_prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, i
 }
 
 struct FmtQ4K {
-  static constexpr int R = 4, BLOCKS = 4, CHUNK = BLOCKS * QK_K, STAGES = 4;
+  static constexpr int R = 4, BLOCKS = 4, CHUNK = BLOCKS * QK_K, STAGES = 3;
   static constexpr int ROW_STAGE_BYTES = BLOCKS * Q4K_BYTES;  // 576
   static constexpr int STAGE_BYTES = R * ROW_STAGE_BYTES;
   static __host__ __device__ size_t x_bytes(int K) { return QActLayout::bytes(K); }
@@ -229,7 +229,7 @@ struct FmtQ4K {
 // Q6_K rows are stored on the device section-wise: [ql: nb*128][qh: nb*64][scales: nb*16][d: nb*2]
 // (same bytes as GGUF's 210-byte blocks, re-ordered so that every section is 16-byte aligned).
 struct FmtQ6K {
-  static constexpr int R = 2, BLOCKS = 8, CHUNK = BLOCKS * QK_K, STAGES = 3;
+  static constexpr int R = 2, BLOCKS = 8, CHUNK = BLOCKS * QK_K, STAGES = 2;
   static constexpr int QL = BLOCKS * 128, QH = BLOCKS * 64, SC = BLOCKS * 16, DD = BLOCKS * 2;
   static constexpr int ROW_STAGE_BYTES = QL + QH + SC + DD;  // 1680
   static constexpr int STAGE_BYTES = R * ROW_STAGE_BYTES;
@@ -369,16 +369,20 @@ DEVINL void epilogue(const GemvArgs& a, int unit, int lane, const float* acc, fl
 template <class F, int PRO, int EPI>
 __global__ void __launch_bounds__(kWarps * 32, 1) gemv_kernel(const GemvArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp index through a shuffle so the compiler knows it is warp-uniform: the TMA issue below then takes
+  // its addresses from uniform registers instead of a per-lane "waterfall" loop around every UBLKCP
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const size_t xb = (F::x_bytes(a.K) + 127) & ~(size_t)127;
   uint8_t* xs = smem;
   uint8_t* ring = smem + xb + (size_t)warp * F::STAGES * F::STAGE_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + xb + (size_t)kWarps * F::STAGES * F::STAGE_BYTES) + warp * F::STAGES;
   float* red = reinterpret_cast<float*>(smem + xb + (size_t)kWarps * F::STAGES * F::STAGE_BYTES + kWarps * F::STAGES * 8);
 
+  // unit u (R rows, full K) -> global warp u % twarps; consecutive units land on consecutive CTAs, so a
+  // matrix with fewer units than warps still spreads over every SM
   const int n_units = a.N / F::R;
   const int chunks = a.K / F::CHUNK;
-  const int gwarp = blockIdx.x * kWarps + warp, twarps = gridDim.x * kWarps;
+  const int gwarp = warp * (int)gridDim.x + (int)blockIdx.x, twarps = (int)gridDim.x * kWarps;
   const int my_units = gwarp < n_units ? (n_units - gwarp + twarps - 1) / twarps : 0;
   const int n_items = my_units * chunks;
   const uint32_t ring_s = smem_u32(ring), bars_s = smem_u32(bars);
@@ -395,12 +399,14 @@ __global__ void __launch_bounds__(kWarps * 32, 1) gemv_kernel(const GemvArgs a) 
   }
   __syncwarp();
 
-  // producer cursor (lane 0 only)
+  // producer cursor: kept by every lane (warp-uniform), only the elected lane touches the TMA unit
   int p_item = 0, p_unit = gwarp, p_chunk = 0, p_stage = 0;
   auto produce = [&]() {
-    const uint32_t bar = bars_s + 8 * p_stage;
-    mbar_expect_tx(bar, F::STAGE_BYTES);
-    F::issue(ring_s + p_stage * F::STAGE_BYTES, bar, a, p_unit, p_chunk, pol);
+    if (lane == 0) {
+      const uint32_t bar = bars_s + 8 * p_stage;
+      mbar_expect_tx(bar, F::STAGE_BYTES);
+      F::issue(ring_s + p_stage * F::STAGE_BYTES, bar, a, p_unit, p_chunk, pol);
+    }
     ++p_item;
     if (++p_chunk == chunks) {
       p_chunk = 0;
@@ -408,9 +414,9 @@ __global__ void __launch_bounds__(kWarps * 32, 1) gemv_kernel(const GemvArgs a) 
     }
     if (++p_stage == F::STAGES) p_stage = 0;
   };
-  if (lane == 0) {
-    for (int s = 0; s < F::STAGES && p_item < n_items; ++s) produce();
-  }
+#pragma unroll
+  for (int s = 0; s < F::STAGES; ++s)
+    if (p_item < n_items) produce();
   if (EPI != EPI_LOGITS) {
     pdl_launch_dependents();
     pdl_wait();
@@ -430,8 +436,8 @@ __global__ void __launch_bounds__(kWarps * 32, 1) gemv_kernel(const GemvArgs a) 
       mbar_wait(bars_s + 8 * c_stage, c_parity);
       F::consume(ring + (size_t)c_stage * F::STAGE_BYTES, xs, c, a, lane, acc);
       __syncwarp();
-      if (lane == 0 && p_item < n_items) {
-        fence_proxy_async();
+      if (p_item < n_items) {
+        if (lane == 0) fence_proxy_async();
         produce();
       }
       if (++c_stage == F::STAGES) {
@@ -463,8 +469,7 @@ cudaError_t launch_t(const GemvArgs& a, cudaStream_t s, bool pdl, int sm_count) 
     configured = smem;
   }
   const int n_units = a.N / F::R;
-  int grid = (n_units + kWarps - 1) / kWarps;
-  if (grid > sm_count) grid = sm_count;
+  int grid = n_units < sm_count ? n_units : sm_count;  // units are dealt CTA-first (see gemv_kernel)
   if (grid < 1) grid = 1;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);

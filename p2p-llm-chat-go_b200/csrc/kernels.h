@@ -105,4 +105,9 @@ cudaError_t launch_synth(int type, void* dst, int64_t rows, int64_t cols, uint64
 cudaError_t launch_f32_to_bf16(const float* x, uint16_t* y, int64_t n, cudaStream_t s);
 cudaError_t launch_l2_flush(void* buf, size_t bytes, cudaStream_t s);
 
+// tcgen05/TMEM bf16 GEMM (gemm.cu): Y[t*ldy + r] = sum_k X[t][k] W[r][k], fp32 out
+cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
+                             int64_t ldy, cudaStream_t s);
+bool gemm_shape_ok(int64_t rows, int64_t K, int64_t n_tokens);
+
 }  // namespace b200

@@ -130,3 +130,24 @@ def test_attn_decode(pkg, n_ctx, n_heads, n_kv):
     # run it again: the ticket counters must have reset themselves
     got2 = pkg.attn_decode(q, K, V, n_heads, n_kv)
     assert np.array_equal(got, got2)
+
+
+# tcgen05 GEMM (GEMM numerics, oracle mode 1): bf16 inputs, exact products, fp32 accumulation in TMEM
+@pytest.mark.parametrize("wtype,rows,cols,n", [
+    (orc.BF16, 128, 64, 1), (orc.BF16, 256, 512, 7), (orc.BF16, 1024, 4096, 128), (orc.BF16, 512, 2048, 129),
+    (orc.BF16, 6144, 4096, 512), (orc.BF16, 4096, 14336, 300), (orc.Q4_K, 256, 1024, 33), (orc.Q6_K, 256, 2048, 64)])
+def test_gemm_tcgen05(pkg, wtype, rows, cols, n):
+    rng = np.random.default_rng(rows + cols + n)
+    W = random_tensor(rng, wtype, rows, cols)
+    X = rng.standard_normal((n, cols)).astype(np.float32)
+    got = pkg.gemm(wtype, W, rows, cols, X)
+    want = orc.matmul(wtype, W, rows, cols, X, mode=1)
+    Wf = orc.dequant(W, wtype).reshape(rows, cols) if wtype in (orc.Q4_K, orc.Q6_K) else orc.bf16_to_f32(W).reshape(rows, cols)
+    budget = np.abs(X).astype(np.float64) @ np.abs(Wf).astype(np.float64).T
+    err = np.abs(got.astype(np.float64) - want)
+    assert (err <= 1e-5 * budget + 1e-30).all(), float((err / (budget + 1e-30)).max())
+
+
+def test_gemm_rejects_bad_shapes(pkg):
+    with pytest.raises(pkg.B200Error):
+        pkg.gemm(orc.BF16, np.zeros((100, 64), np.uint16), 100, 64, np.zeros((1, 64), np.float32))
