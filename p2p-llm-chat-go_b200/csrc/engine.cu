@@ -279,7 +279,12 @@ int Engine::synthesize() {
   int rc = 0;
   for (auto& kv : slots) {  // std::map: deterministic (name-sorted) tensor ids
     Slot& s = kv.second;
-    const float sigma = kv.first == "token_embd.weight" ? 1.0f : 1.0f / sqrtf((float)s.cols);
+    // std 1/sqrt(fan_in); the two projections that write into the residual stream are scaled by
+    // 1/sqrt(2*n_layers) (GPT-2 / Megatron random-init convention), which keeps a deep random network from
+    // amplifying rounding differences chaotically layer after layer
+    float sigma = kv.first == "token_embd.weight" ? 1.0f : 1.0f / sqrtf((float)s.cols);
+    if (kv.first.find("attn_output") != std::string::npos || kv.first.find("ffn_down") != std::string::npos)
+      sigma /= sqrtf(2.0f * (float)cfg.n_layers);
     cudaError_t e = launch_synth(s.type, tmp, s.rows, s.cols, (uint64_t)cfg.seed, tid++, sigma, stream);
     if (e != cudaSuccess) { rc = cuda_fail(e, "synth"); break; }
     if ((rc = place_tensor(s, tmp))) break;
