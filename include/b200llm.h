@@ -155,6 +155,28 @@ B200_API int b200_attn_decode(const float* q, const float* k, const float* v, in
 B200_API int b200_sample(const float* logits, int vocab, const b200_sampling* s, const int32_t* history,
                          int n_hist, uint64_t step, int32_t* id);
 
+/* ---- allocation-free entry point -------------------------------------------------------------------- */
+/* No counterpart in the reference (the reference has no GPU code at all).
+ * The same paged GQA decode-attention kernel as b200_attn_decode, for hosts that cannot let this library
+ * allocate device memory: a process that has already given all of HBM to its own pool (an llmd replica whose
+ * KV pool fills the GPU, a PyTorch caching allocator) would see an in-library cudaMalloc fail, and even a
+ * successful cudaMalloc stalls every stream of the device.  Here the caller passes DEVICE pointers for all
+ * inputs and the output, and the kernel's scratch lives in a fixed ~0.64 MB array inside the library image
+ * (held by every GPU that loads the library until the process exits).  The call allocates and frees nothing.
+ *   q_dev           [n_heads*128] fp32, already rotated
+ *   k/v_cache_dev   paged bf16 cache [page][n_kv_heads][16][128]
+ *   block_table_dev physical page of each logical 16-token page, int32[ceil(n_ctx/16)]
+ *   out_dev         [n_heads*128] fp32
+ *   stream          a cudaStream_t (NULL = default stream); the call is asynchronous on it
+ * Limit: n_heads <= B200_NOALLOC_MAX_HEADS, larger shapes are refused with B200_ERANGE.
+ * The first call on a device looks up the scratch address (with that device current) — make that first
+ * call before starting any stream capture.  All calls on one GPU share the scratch: issue them in stream
+ * order; calls that overlap on the GPU race. */
+#define B200_NOALLOC_MAX_HEADS 64
+B200_API int b200_attn_decode_noalloc(const float* q_dev, const uint16_t* k_cache_dev, const uint16_t* v_cache_dev,
+                                      const int32_t* block_table_dev, int n_ctx, int n_heads, int n_kv_heads,
+                                      float* out_dev, void* stream);
+
 /* ---- bench hooks: device-resident steps timed with CUDA events on the engine's stream --------------- */
 /* Runs `n_steps` decode steps (graph replays) starting from the current context; returns the mean step
  * time in milliseconds and the number of kernels launched per step. */

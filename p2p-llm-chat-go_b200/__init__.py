@@ -96,6 +96,7 @@ def lib():
         "b200_gemv_rmsnorm": (i32, [i32, vp, i64, i64, vp, vp, f32, vp]),
         "b200_gemm": (i32, [i32, vp, i64, i64, vp, i64, vp]),
         "b200_attn_decode": (i32, [vp, vp, vp, i32, i32, i32, vp]),
+        "b200_attn_decode_noalloc": (i32, [vp, vp, vp, vp, i32, i32, i32, vp, vp]),
         "b200_sample": (i32, [vp, i32, smpp, vp, i32, u64, C.POINTER(C.c_int32)]),
         "b200_bench_decode": (i32, [vp, i32, i32, C.POINTER(f32), C.POINTER(i32)]),
         "b200_bench_kernel": (i32, [vp, C.c_char_p, i32, C.POINTER(f32), C.POINTER(i64)]),
@@ -187,6 +188,12 @@ def attn_decode(q, K, V, n_heads, n_kv_heads):
     out = np.empty(n_heads * 128, np.float32)
     _check(lib().b200_attn_decode(_p(q), _p(K), _p(V), n_ctx, n_heads, n_kv_heads, _p(out)))
     return out
+
+
+def attn_decode_noalloc(q_ptr, k_cache_ptr, v_cache_ptr, block_table_ptr, n_ctx, n_heads, n_kv_heads, out_ptr, stream=0):
+    """Device pointers (ints) in, nothing allocated; asynchronous on `stream` (a cudaStream_t value)."""
+    _check(lib().b200_attn_decode_noalloc(q_ptr, k_cache_ptr, v_cache_ptr, block_table_ptr, n_ctx, n_heads, n_kv_heads,
+                                          out_ptr, stream))
 
 
 def sample(logits, sp, history, step):

@@ -371,6 +371,24 @@ int b200_attn_decode(const float* q, const float* k, const float* v, int n_ctx, 
   return 0;
 }
 
+int b200_attn_decode_noalloc(const float* q_dev, const uint16_t* k_cache_dev, const uint16_t* v_cache_dev, const int32_t* block_table_dev,
+                             int n_ctx, int n_heads, int n_kv_heads, float* out_dev, void* stream) {
+  if (!q_dev || !k_cache_dev || !v_cache_dev || !block_table_dev || !out_dev) { set_error("null argument"); return B200_EINVAL; }
+  if (n_heads > attn_noalloc_max_heads()) {
+    set_error("b200_attn_decode_noalloc: n_heads=%d exceeds the built-in scratch (B200_NOALLOC_MAX_HEADS=%d); use b200_attn_decode",
+              n_heads, attn_noalloc_max_heads());
+    return B200_ERANGE;
+  }
+  const int G = (n_kv_heads > 0 && n_heads % n_kv_heads == 0) ? n_heads / n_kv_heads : 0;
+  if (n_ctx < 1 || n_heads < 1 || (G != 1 && G != 2 && G != 4 && G != 8)) {
+    set_error("b200_attn_decode_noalloc: bad shape (n_ctx=%d n_heads=%d n_kv_heads=%d)", n_ctx, n_heads, n_kv_heads);
+    return B200_EINVAL;
+  }
+  B200_CUDA(launch_attn_decode_noalloc(q_dev, k_cache_dev, v_cache_dev, block_table_dev, n_ctx, n_heads, n_kv_heads, out_dev,
+                                       reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
 int b200_gemm(int type, const void* w, int64_t rows, int64_t cols, const float* x, int64_t n, float* y) {
   int rc = have_device();
   if (rc) return rc;

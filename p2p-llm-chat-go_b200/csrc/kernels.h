@@ -76,6 +76,11 @@ struct AttnArgs {
 };
 cudaError_t launch_attn_decode(const AttnArgs& a, cudaStream_t s, bool pdl);
 size_t attn_partial_floats(int n_heads, int n_kv_heads, int n_splits);
+// allocation-free variant: scratch in a static __device__ array inside attn.cu (see there)
+cudaError_t launch_attn_decode_noalloc(const float* q, const uint16_t* k_cache, const uint16_t* v_cache,
+                                       const int32_t* block_table, int n_ctx, int n_heads, int n_kv_heads, float* out,
+                                       cudaStream_t s);
+int attn_noalloc_max_heads();
 
 struct FinishArgs {
   StepState* st;
