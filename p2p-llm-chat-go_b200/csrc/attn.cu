@@ -36,10 +36,15 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnArgs a) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   pdl_wait();
   pdl_launch_dependents();
-  const int ctx = a.fixed_ctx > 0 ? a.fixed_ctx : a.st->pos + 1;
+  const int qi = blockIdx.z;  // query position within the launch (0 for decode)
+  const int ctx = a.fixed_ctx > 0 ? a.fixed_ctx + qi : a.st->pos + 1;
   const float scale = 1.0f / sqrtf((float)kHeadDim);
+  const float* q_in = a.q + (size_t)qi * a.q_stride;
+  float* out = a.out + (size_t)qi * a.q_stride;
+  float* partial = a.partial + (size_t)qi * gridDim.x * S * G * kPart;
+  unsigned int* counters = a.counters + (size_t)qi * gridDim.x;
 
-  for (int i = tid; i < G * kHeadDim; i += 128) qs[i] = a.q[(size_t)kvh * G * kHeadDim + i];
+  for (int i = tid; i < G * kHeadDim; i += 128) qs[i] = q_in[(size_t)kvh * G * kHeadDim + i];
   if (tid < G) {
     m_run[tid] = -INFINITY;
     l_run[tid] = 0.f;
@@ -107,7 +112,7 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnArgs a) {
     __syncthreads();
   }
 
-  float* part = a.partial + ((size_t)kvh * S + split) * G * kPart;
+  float* part = partial + ((size_t)kvh * S + split) * G * kPart;
 #pragma unroll
   for (int h = 0; h < G; ++h) part[h * kPart + tid] = acc[h];
   if (tid < G) {
@@ -116,13 +121,13 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnArgs a) {
   }
   __threadfence();
   __syncthreads();
-  if (tid == 0) s_last = (atomicAdd(a.counters + kvh, 1u) == (unsigned)(S - 1));
+  if (tid == 0) s_last = (atomicAdd(counters + kvh, 1u) == (unsigned)(S - 1));
   __syncthreads();
   if (!s_last) return;
   __threadfence();
   // merge the splits: (m, l) of every (head, split) into shared memory with one parallel round of loads,
   // softmax weights per split, then one pass over the partial accumulators with independent loads
-  const float* base = a.partial + (size_t)kvh * S * G * kPart;
+  const float* base = partial + (size_t)kvh * S * G * kPart;
   float* w_s = reinterpret_cast<float*>(Ks);  // [G][S] weights, reusing the K tile (G*S <= 8*32 floats)
   float* l_s = w_s + G * kMaxSplits;
   for (int i = tid; i < G * S; i += 128) {
@@ -150,9 +155,9 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnArgs a) {
     float num = 0.f;
 #pragma unroll 4
     for (int sp = 0; sp < S; ++sp) num = fmaf(__ldcg(base + ((size_t)sp * G + h) * kPart + tid), w_s[h * kMaxSplits + sp], num);
-    a.out[((size_t)kvh * G + h) * kHeadDim + tid] = num * corr_s[h];
+    out[((size_t)kvh * G + h) * kHeadDim + tid] = num * corr_s[h];
   }
-  if (tid == 0) a.counters[kvh] = 0u;
+  if (tid == 0) counters[kvh] = 0u;
 }
 
 }  // namespace
@@ -164,7 +169,7 @@ size_t attn_partial_floats(int n_heads, int n_kv_heads, int n_splits) {
 cudaError_t launch_attn_decode(const AttnArgs& a, cudaStream_t s, bool pdl) {
   if (a.n_kv_heads <= 0 || a.n_heads % a.n_kv_heads || a.n_splits <= 0 || a.n_splits > kMaxSplits) return cudaErrorInvalidValue;
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(a.n_kv_heads, a.n_splits);
+  cfg.gridDim = dim3(a.n_kv_heads, a.n_splits, a.n_queries > 1 ? a.n_queries : 1);
   cfg.blockDim = dim3(128);
   cfg.stream = s;
   cudaLaunchAttribute at[1];

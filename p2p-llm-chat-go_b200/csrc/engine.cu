@@ -396,16 +396,15 @@ int Engine::begin_sequence(const int32_t* prompt, int n_prompt, int max_out, int
 
 int Engine::generate_greedy(const int32_t* prompt, int n_prompt, int32_t* ids, int n_new, int prefill_mode, float* ttft_ms,
                             float* decode_ms) {
-  (void)prefill_mode;
   int rc = ensure_graph();
   if (rc) return rc;
-  if ((rc = begin_sequence(prompt, n_prompt, n_new, 1))) return rc;
+  if (prefill_mode == B200_MODE_GEMM && n_prompt > 1 && (rc = ensure_prefill())) return rc;
   cudaEvent_t e0, e1, e2;
   B200_CUDA(cudaEventCreate(&e0));
   B200_CUDA(cudaEventCreate(&e1));
   B200_CUDA(cudaEventCreate(&e2));
   B200_CUDA(cudaEventRecord(e0, stream));
-  rc = launch_steps(n_prompt);  // after these the first generated token exists
+  rc = run_prompt(prompt, n_prompt, n_new, 1, prefill_mode);  // after this the first generated token exists
   if (!rc) {
     cudaEventRecord(e1, stream);
     rc = launch_steps(n_new - 1);
@@ -427,10 +426,8 @@ int Engine::generate_greedy(const int32_t* prompt, int n_prompt, int32_t* ids, i
 }
 
 int Engine::forward_logits(const int32_t* ids, int n, int mode, float* logits_host) {
-  (void)mode;
-  int rc = begin_sequence(ids, n, 1, 1);
+  int rc = run_prompt(ids, n, 1, 1, mode);
   if (rc) return rc;
-  if ((rc = launch_steps(n))) return rc;
   B200_CUDA(cudaMemcpyAsync(logits_host, logits, (size_t)cfg.vocab * 4, cudaMemcpyDeviceToHost, stream));
   B200_CUDA(cudaStreamSynchronize(stream));
   return 0;
@@ -465,11 +462,12 @@ void Engine::worker_loop() {
       int max_out = r->sp.num_predict > 0 ? r->sp.num_predict : cfg.max_ctx;
       if (n_prompt + max_out - 1 > cfg.max_ctx) max_out = cfg.max_ctx - n_prompt + 1;
       const int greedy = 1;  // sampler hook: set from r->sp once sample_kernel is in the graph
-      rc = max_out < 1 ? B200_EINVAL : begin_sequence(r->prompt.data(), n_prompt, max_out, greedy);
-      if (rc == B200_EINVAL && max_out < 1) set_error("prompt fills the whole context");
+      if (max_out < 1) { rc = B200_EINVAL; set_error("prompt fills the whole context"); }
+      if (!rc && r->sp.prefill_mode == B200_MODE_GEMM && n_prompt > 1) rc = ensure_prefill();
+      if (!rc) rc = ensure_graph();
       const auto t_load = clk::now();
       auto t_first = t_load;
-      if (!rc) rc = launch_steps(n_prompt);
+      if (!rc) rc = run_prompt(r->prompt.data(), n_prompt, max_out, greedy, r->sp.prefill_mode);
       int launched = 1;  // decode steps launched that can produce tokens (the prefill's last step makes #1)
       const int window = 4;
       while (!rc) {
@@ -518,6 +516,118 @@ void Engine::worker_loop() {
       r->cv.notify_all();
     }
   }
+}
+
+}  // namespace b200
+
+// ------------------------------------------------------------------------------------------------------
+// Prefill on the tensor cores (GEMM numerics, oracle mode 1).
+namespace b200 {
+
+int Engine::ensure_prefill() {
+  if (pf_ready) return 0;
+  const b200_config& c = cfg;
+  const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn, T = c.max_ctx;
+  if (!gemm_shape_ok(qd + 2 * kvd, d, 1) || !gemm_shape_ok(d, qd, 1) || !gemm_shape_ok(2 * ff, d, 1) || !gemm_shape_ok(d, ff, 1)) {
+    set_error("model dims not supported by the tensor-core path (rows %%128, K %%64)");
+    return B200_EINVAL;
+  }
+  int rc;
+  const bool q4 = c.weight_format == B200_WEIGHTS_Q4_K_M;
+  if (q4) {
+    size_t maxb = 0;
+    for (auto& kv : slots) maxb = std::max(maxb, (size_t)kv.second.rows * tensor_row_bytes(kv.second.type, kv.second.cols));
+    uint8_t* tmp = nullptr;
+    uint16_t* tmp16 = nullptr;
+    if ((rc = alloc((void**)&tmp, maxb)) || (rc = alloc((void**)&tmp16, (size_t)2 * ff * std::max(d, qd) * 2 + (size_t)d * ff * 2))) return rc;
+    for (int l = 0; l < c.n_layers; ++l) {
+      Layer& L = layers[l];
+      if ((rc = alloc((void**)&L.qkv16, (size_t)(qd + 2 * kvd) * d * 2)) || (rc = alloc((void**)&L.o16, (size_t)d * qd * 2)) ||
+          (rc = alloc((void**)&L.gu16, (size_t)2 * ff * d * 2)) || (rc = alloc((void**)&L.down16, (size_t)d * ff * 2)))
+        return rc;
+      const std::string p = "blk." + std::to_string(l) + ".";
+      struct Dst { const char* name; uint16_t* base; int64_t row0, step; };
+      const Dst dsts[] = {{"attn_q", L.qkv16, 0, 1}, {"attn_k", L.qkv16, qd, 1}, {"attn_v", L.qkv16, qd + kvd, 1}, {"attn_output", L.o16, 0, 1},
+                          {"ffn_gate", L.gu16, 0, 2}, {"ffn_up", L.gu16, 1, 2}, {"ffn_down", L.down16, 0, 1}};
+      for (const Dst& t : dsts) {
+        const Slot& s = slots[p + t.name + ".weight"];
+        if ((rc = fetch_tensor(s, tmp))) return rc;  // GGUF block order
+        B200_CUDA(launch_dequant(s.type, tmp, s.rows * s.cols / QK_K, nullptr, tmp16, stream));
+        B200_CUDA(cudaMemcpy2DAsync(t.base + (size_t)t.row0 * s.cols, (size_t)t.step * s.cols * 2, tmp16, (size_t)s.cols * 2,
+                                    (size_t)s.cols * 2, (size_t)s.rows, cudaMemcpyDeviceToDevice, stream));
+      }
+    }
+    B200_CUDA(cudaStreamSynchronize(stream));
+  } else {
+    for (auto& L : layers) {
+      L.qkv16 = (uint16_t*)L.qkv; L.o16 = (uint16_t*)L.o; L.gu16 = (uint16_t*)L.gate_up; L.down16 = (uint16_t*)L.down;
+    }
+  }
+  const size_t wmax = (size_t)std::max(std::max(d, qd), ff);
+  if ((rc = alloc((void**)&pf_x, (size_t)T * d * 4)) || (rc = alloc((void**)&pf_xb, (size_t)T * wmax * 2)) ||
+      (rc = alloc((void**)&pf_qkv, (size_t)T * (qd + 2 * kvd) * 4)) || (rc = alloc((void**)&pf_q, (size_t)T * qd * 4)) ||
+      (rc = alloc((void**)&pf_att, (size_t)T * qd * 4)) || (rc = alloc((void**)&pf_proj, (size_t)T * d * 4)) ||
+      (rc = alloc((void**)&pf_gu, (size_t)T * 2 * ff * 4)) ||
+      (rc = alloc((void**)&pf_partial, (size_t)T * attn_partial_floats(c.n_heads, c.n_kv_heads, pf_splits) * 4)) ||
+      (rc = alloc((void**)&pf_counters, (size_t)T * c.n_kv_heads * 4)))
+    return rc;
+  B200_CUDA(cudaMemsetAsync(pf_counters, 0, (size_t)T * c.n_kv_heads * 4, stream));
+  pf_ready = true;
+  return 0;
+}
+
+int Engine::prefill_gemm(int n) {
+  const b200_config& c = cfg;
+  const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn;
+  cudaStream_t s = stream;
+  B200_CUDA(launch_embed_tokens(token_embd, embd_type, d, prompt_dev, n, pf_x, s));
+  for (int l = 0; l < c.n_layers; ++l) {
+    Layer& L = layers[l];
+    B200_CUDA(launch_add_rmsnorm_bf16(pf_x, l ? pf_proj : nullptr, L.attn_norm, pf_xb, n, d, c.rms_eps, s));
+    B200_CUDA(launch_gemm_bf16(L.qkv16, qd + 2 * kvd, d, pf_xb, n, pf_qkv, qd + 2 * kvd, s));
+    B200_CUDA(launch_rope_kv(pf_qkv, pf_q, L.k_cache, L.v_cache, block_table, rope, n, qd, kvd, c.n_kv_heads, 0, s));
+    AttnArgs t = {};
+    t.q = pf_q; t.k_cache = L.k_cache; t.v_cache = L.v_cache; t.block_table = block_table; t.st = nullptr;
+    t.n_heads = c.n_heads; t.n_kv_heads = c.n_kv_heads; t.out = pf_att; t.partial = pf_partial; t.counters = pf_counters;
+    t.n_splits = pf_splits; t.fixed_ctx = 1; t.n_queries = n; t.q_stride = qd;
+    B200_CUDA(launch_attn_decode(t, s, false));
+    B200_CUDA(launch_f32_to_bf16(pf_att, pf_xb, (int64_t)n * qd, s));
+    B200_CUDA(launch_gemm_bf16(L.o16, d, qd, pf_xb, n, pf_proj, d, s));
+    B200_CUDA(launch_add_rmsnorm_bf16(pf_x, pf_proj, L.ffn_norm, pf_xb, n, d, c.rms_eps, s));
+    B200_CUDA(launch_gemm_bf16(L.gu16, 2 * ff, d, pf_xb, n, pf_gu, 2 * ff, s));
+    B200_CUDA(launch_swiglu_bf16(pf_gu, pf_xb, (int64_t)n * ff, s));
+    B200_CUDA(launch_gemm_bf16(L.down16, d, ff, pf_xb, n, pf_proj, d, s));
+  }
+  // hand the last position over to the batch-1 path: residual stream, then lm_head (mode 0) + token pick
+  B200_CUDA(launch_take_row(pf_x, pf_proj, d, n - 1, x, s));
+  GemvArgs lm = {};
+  lm.W = output; lm.N = c.vocab; lm.K = d; lm.x = x; lm.norm_w = output_norm; lm.eps = c.rms_eps; lm.y = logits;
+  lm.st = st; lm.store_logits = 1; lm.argmax_key = &st->argmax_key;
+  B200_CUDA(launch_gemv(output_type, PRO_RMSNORM, EPI_LOGITS, lm, s, false, sm_count));
+  FinishArgs f = {};
+  f.st = st; f.prompt = prompt_dev; f.out_tokens = out_tokens_dev; f.host_n_out = host_n_out_dev; f.embd = token_embd;
+  f.embd_type = embd_type; f.d_model = d; f.x = x; f.max_ctx = c.max_ctx;
+  B200_CUDA(launch_finish_step(f, s, false));
+  return 0;
+}
+
+// Puts the prompt through the model and produces the first generated token.
+// mode GEMM: tensor-core prefill; mode GEMV (or a 1-token prompt): token by token through the decode graph.
+int Engine::run_prompt(const int32_t* prompt, int n_prompt, int max_out, int greedy, int mode) {
+  int rc;
+  if (mode == B200_MODE_GEMM && n_prompt > 1) {
+    if ((rc = ensure_prefill())) return rc;
+    if ((rc = begin_sequence(prompt, n_prompt, max_out, greedy))) return rc;
+    // the state kernels see "position n-1 is being processed": the token after it is the first generated one
+    StepState s0 = {};
+    s0.pos = n_prompt - 1; s0.cur_token = prompt[n_prompt - 1]; s0.n_prompt = n_prompt; s0.max_out = max_out; s0.eos = cfg.eos_token;
+    s0.greedy = greedy;
+    B200_CUDA(cudaMemcpyAsync(st, &s0, sizeof s0, cudaMemcpyHostToDevice, stream));
+    B200_CUDA(cudaStreamSynchronize(stream));
+    return prefill_gemm(n_prompt);
+  }
+  if ((rc = begin_sequence(prompt, n_prompt, max_out, greedy))) return rc;
+  return launch_steps(n_prompt);
 }
 
 }  // namespace b200

@@ -46,6 +46,9 @@ struct Layer {
   float* ffn_norm = nullptr;
   uint16_t* k_cache = nullptr;  // [n_pages][n_kv][16][128]
   uint16_t* v_cache = nullptr;
+  // bf16 K-major operands of the tensor-core path: the GEMV buffers themselves for bf16 models, dequantised
+  // shadow copies (same fused row order) for k-quant models
+  uint16_t *qkv16 = nullptr, *o16 = nullptr, *gu16 = nullptr, *down16 = nullptr;
 };
 
 struct Request;
@@ -78,6 +81,14 @@ struct Engine {
   volatile int32_t* host_n_out = nullptr;
   int32_t* host_n_out_dev = nullptr;
 
+  // prefill (GEMM path) work buffers, sized for max_ctx tokens, allocated on first use
+  bool pf_ready = false;
+  float *pf_x = nullptr, *pf_qkv = nullptr, *pf_q = nullptr, *pf_att = nullptr, *pf_proj = nullptr, *pf_gu = nullptr;
+  uint16_t* pf_xb = nullptr;
+  float* pf_partial = nullptr;
+  unsigned int* pf_counters = nullptr;
+  int pf_splits = 4;
+
   cudaGraphExec_t step_graph = nullptr;
   bool use_pdl = true, use_graph = true;
   int launches_per_step = 0;
@@ -106,6 +117,9 @@ struct Engine {
   int generate_greedy(const int32_t* prompt, int n_prompt, int32_t* ids, int n_new, int prefill_mode, float* ttft_ms,
                       float* decode_ms);
   int forward_logits(const int32_t* ids, int n, int mode, float* logits_host);
+  int ensure_prefill();                      // shadow weights + work buffers of the GEMM path
+  int prefill_gemm(int n_prompt);            // prompt_dev[0..n) -> KV cache, residual of the last position, first token
+  int run_prompt(const int32_t* prompt, int n_prompt, int max_out, int greedy, int mode);  // either prefill flavour
   void worker_loop();
 };
 

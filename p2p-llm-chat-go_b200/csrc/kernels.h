@@ -72,7 +72,11 @@ struct AttnArgs {
   float* partial;       // scratch [n_kv][n_splits][group][130]
   unsigned int* counters;  // scratch [n_kv], must be zero before the first launch; self-resetting
   int n_splits;
-  int fixed_ctx;        // >0: use this context length instead of st->pos+1 (test hook)
+  int fixed_ctx;        // >0: use this context length instead of st->pos+1 (test hook / prefill)
+  // several query positions in one launch (prefill): query z has ctx = fixed_ctx + z, q/out advance by
+  // q_stride floats, scratch by one query's worth.  n_queries <= 1: the single-query decode case.
+  int n_queries;
+  int q_stride;
 };
 cudaError_t launch_attn_decode(const AttnArgs& a, cudaStream_t s, bool pdl);
 size_t attn_partial_floats(int n_heads, int n_kv_heads, int n_splits);
@@ -114,5 +118,13 @@ cudaError_t launch_l2_flush(void* buf, size_t bytes, cudaStream_t s);
 cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
                              int64_t ldy, cudaStream_t s);
 bool gemm_shape_ok(int64_t rows, int64_t K, int64_t n_tokens);
+
+// element-wise kernels of the prefill / batched pass (prefill.cu)
+cudaError_t launch_embed_tokens(const uint8_t* embd, int embd_type, int d_model, const int32_t* tokens_dev, int n, float* x, cudaStream_t s);
+cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, const float* w, uint16_t* xb, int tokens, int d, float eps, cudaStream_t s);
+cudaError_t launch_rope_kv(const float* qkv, float* q, uint16_t* k_cache, uint16_t* v_cache, const int32_t* block_table, const float* rope,
+                           int tokens, int q_rows, int kv_rows, int n_kv_heads, int pos0, cudaStream_t s);
+cudaError_t launch_swiglu_bf16(const float* gu, uint16_t* h, int64_t n_pairs, cudaStream_t s);
+cudaError_t launch_take_row(const float* x, const float* add, int d, int row, float* out, cudaStream_t s);
 
 }  // namespace b200

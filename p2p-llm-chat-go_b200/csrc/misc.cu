@@ -165,6 +165,10 @@ __global__ void embed_kernel(const uint8_t* embd, int type, int d_model, const i
   embed_row(embd, type, d_model, *token, x);
 }
 
+__global__ void embed_tokens_kernel(const uint8_t* embd, int type, int d_model, const int32_t* tokens, float* x) {
+  embed_row(embd, type, d_model, tokens[blockIdx.x], x + (size_t)blockIdx.x * d_model);
+}
+
 // Last kernel of a decode step: picks the next token (forced from the prompt while prefilling token by
 // token, else argmax / sampled), publishes generated tokens to mapped host memory, advances the position
 // and gathers the next token's embedding into the residual stream.
@@ -244,6 +248,11 @@ cudaError_t launch_l2_flush(void* buf, size_t bytes, cudaStream_t s) {
 
 cudaError_t launch_embed(const uint8_t* embd, int embd_type, int d_model, const int32_t* token_dev, float* x, cudaStream_t s) {
   embed_kernel<<<1, 256, 0, s>>>(embd, embd_type, d_model, token_dev, x);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_embed_tokens(const uint8_t* embd, int embd_type, int d_model, const int32_t* tokens_dev, int n, float* x, cudaStream_t s) {
+  embed_tokens_kernel<<<n, 256, 0, s>>>(embd, embd_type, d_model, tokens_dev, x);
   return cudaGetLastError();
 }
 

@@ -1,0 +1,118 @@
+// prefill.cu — the element-wise kernels between the tensor-core GEMMs of a prefill / batched pass
+// (GEMM numerics, oracle mode 1): token embedding gather, (residual add +) RMSNorm -> bf16, RoPE + KV-cache
+// append, SwiGLU -> bf16, and the hand-over of the last position's residual to the decode path.
+// All are HBM/L2-bound streaming kernels over [tokens x width] fp32; the bf16 rounding of GEMM inputs
+// happens exactly once, here, with the same RNE recipe as the oracle.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200 {
+namespace {
+
+DEVINL float block_sum256(float v, float* red) {
+  v = warp_sum(v);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float t = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) t += red[i];
+  __syncthreads();
+  return t;
+}
+
+// x[t][:] (+= add[t][:]) ; xb[t][:] = bf16( (x * inv_rms) * w )        grid = tokens, block = 256
+__global__ void add_rmsnorm_bf16_kernel(float* x, const float* add, const float* w, uint16_t* xb, int d, float eps) {
+  __shared__ float red[8];
+  float* xr = x + (size_t)blockIdx.x * d;
+  const float* ar = add ? add + (size_t)blockIdx.x * d : nullptr;
+  float ss = 0.f;
+  for (int k = threadIdx.x * 4; k < d; k += 1024) {
+    float4 v = *reinterpret_cast<const float4*>(xr + k);
+    if (ar) {
+      const float4 a = *reinterpret_cast<const float4*>(ar + k);
+      v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+      *reinterpret_cast<float4*>(xr + k) = v;
+    }
+    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+  }
+  ss = block_sum256(ss, red);
+  const float inv = 1.0f / sqrtf(ss / (float)d + eps);
+  uint16_t* o = xb + (size_t)blockIdx.x * d;
+  for (int k = threadIdx.x * 4; k < d; k += 1024) {
+    const float4 v = *reinterpret_cast<const float4*>(xr + k);
+    const float4 g = *reinterpret_cast<const float4*>(w + k);
+    uint2 p;
+    p.x = (uint32_t)f32_to_bf16_bits(__fmul_rn(__fmul_rn(v.x, inv), g.x)) | ((uint32_t)f32_to_bf16_bits(__fmul_rn(__fmul_rn(v.y, inv), g.y)) << 16);
+    p.y = (uint32_t)f32_to_bf16_bits(__fmul_rn(__fmul_rn(v.z, inv), g.z)) | ((uint32_t)f32_to_bf16_bits(__fmul_rn(__fmul_rn(v.w, inv), g.w)) << 16);
+    *reinterpret_cast<uint2*>(o + k) = p;
+  }
+}
+
+// qkv[t][q_rows + 2 kv_rows] fp32 -> q[t][q_rows] (rotated), K/V appended to the paged bf16 cache at pos0+t
+__global__ void rope_kv_kernel(const float* qkv, float* q, uint16_t* k_cache, uint16_t* v_cache, const int32_t* block_table,
+                               const float* rope, int q_rows, int kv_rows, int n_kv_heads, int pos0) {
+  const int t = blockIdx.x, pos = pos0 + t;
+  const int width = q_rows + 2 * kv_rows;
+  const float* in = qkv + (size_t)t * width;
+  const int page = block_table[pos / kPageTokens];
+  for (int p = threadIdx.x; p < width / 2; p += blockDim.x) {
+    const int row = 2 * p;
+    float x0 = in[row], x1 = in[row + 1];
+    if (row < q_rows + kv_rows) {
+      const int i = (row & (kHeadDim - 1)) >> 1;
+      const float2 cs = *reinterpret_cast<const float2*>(rope + ((size_t)pos * (kHeadDim / 2) + i) * 2);
+      const float r0 = __fsub_rn(__fmul_rn(x0, cs.x), __fmul_rn(x1, cs.y));
+      const float r1 = __fadd_rn(__fmul_rn(x0, cs.y), __fmul_rn(x1, cs.x));
+      x0 = r0;
+      x1 = r1;
+    }
+    if (row < q_rows) {
+      *reinterpret_cast<float2*>(q + (size_t)t * q_rows + row) = make_float2(x0, x1);
+    } else {
+      const bool isk = row < q_rows + kv_rows;
+      const int kr = row - q_rows - (isk ? 0 : kv_rows);
+      const int kvh = kr >> 7, dim = kr & (kHeadDim - 1);
+      const size_t idx = (((size_t)page * n_kv_heads + kvh) * kPageTokens + (pos % kPageTokens)) * kHeadDim + dim;
+      *reinterpret_cast<uint32_t*>((isk ? k_cache : v_cache) + idx) = (uint32_t)f32_to_bf16_bits(x0) | ((uint32_t)f32_to_bf16_bits(x1) << 16);
+    }
+  }
+}
+
+// gu[t][2 ff] (rows interleaved gate_i, up_i) -> h[t][ff] = bf16( silu(g) * u )
+__global__ void swiglu_bf16_kernel(const float* gu, uint16_t* h, int64_t n_pairs) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_pairs; i += stride) {
+    const float2 v = *reinterpret_cast<const float2*>(gu + 2 * i);
+    h[i] = f32_to_bf16_bits((v.x / (1.0f + expf(-v.x))) * v.y);
+  }
+}
+
+// out[:] = x[row][:] + add[row][:]   (residual of the last prompt position -> the decode path's stream)
+__global__ void take_row_kernel(const float* x, const float* add, int d, int row, float* out) {
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < d; k += gridDim.x * blockDim.x)
+    out[k] = x[(size_t)row * d + k] + add[(size_t)row * d + k];
+}
+
+}  // namespace
+
+cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, const float* w, uint16_t* xb, int tokens, int d, float eps, cudaStream_t s) {
+  if (d % 4) return cudaErrorInvalidValue;
+  add_rmsnorm_bf16_kernel<<<tokens, 256, 0, s>>>(x, add, w, xb, d, eps);
+  return cudaGetLastError();
+}
+cudaError_t launch_rope_kv(const float* qkv, float* q, uint16_t* k_cache, uint16_t* v_cache, const int32_t* block_table, const float* rope,
+                           int tokens, int q_rows, int kv_rows, int n_kv_heads, int pos0, cudaStream_t s) {
+  rope_kv_kernel<<<tokens, 256, 0, s>>>(qkv, q, k_cache, v_cache, block_table, rope, q_rows, kv_rows, n_kv_heads, pos0);
+  return cudaGetLastError();
+}
+cudaError_t launch_swiglu_bf16(const float* gu, uint16_t* h, int64_t n_pairs, cudaStream_t s) {
+  swiglu_bf16_kernel<<<1184, 256, 0, s>>>(gu, h, n_pairs);
+  return cudaGetLastError();
+}
+cudaError_t launch_take_row(const float* x, const float* add, int d, int row, float* out, cudaStream_t s) {
+  take_row_kernel<<<8, 256, 0, s>>>(x, add, d, row, out);
+  return cudaGetLastError();
+}
+
+}  // namespace b200

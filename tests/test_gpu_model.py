@@ -130,3 +130,46 @@ def test_full_size_8b_few_tokens(pkg, fmt):
         ids, _, _ = eng.generate_greedy(prompt, 3, pkg.MODE_GEMV)
         want_ids, margins = ora.generate_greedy(prompt, 3, prefill_mode=0)
         assert ids.tolist() == want_ids.tolist(), (ids, want_ids, margins)
+
+
+# ---- tensor-core prefill (GEMM numerics, oracle mode 1) -------------------------------------------------
+# bf16 rounding of GEMM inputs: an activation that lands within 1e-6 of a rounding boundary may round the
+# other way on the GPU (fp32 sums in a different order), which moves that input by one bf16 ulp (4e-3).
+PREFILL_LOGIT_TOL = 3e-3
+
+
+@pytest.mark.parametrize("fmt", [0, 1])
+@pytest.mark.parametrize("n", [2, 33, 128, 200])
+def test_prefill_gemm_logits(pkg, fmt, n):
+    eng, ora, cfg = engine_and_oracle(pkg, fmt, n_layers=2, seed=51, source="synth")
+    with eng:
+        toks = _prompt(cfg, n, 7)
+        got = eng.forward_logits(toks, pkg.MODE_GEMM)
+        ora.reset()
+        want = ora.forward(toks, mode=1)
+        err = np.abs(got - want).max()
+        assert err <= PREFILL_LOGIT_TOL * max(1.0, np.abs(want).max()), (fmt, n, err)
+        assert int(np.argmax(got)) == orc.argmax(want)[0] or orc.argmax(want)[1] < 2 * err
+        # and the cache it leaves behind continues correctly on the decode path.  Token identity is required
+        # wherever the oracle itself is decisive: take the first prompt whose top-1/top-2 margins all exceed
+        # the logit tolerance (a margin below it is a tie that either side may break either way).
+        for seed in range(7, 27):
+            toks = _prompt(cfg, n, seed)
+            want_ids, margins = ora.generate_greedy(toks, 16, prefill_mode=1)
+            if margins.min() > 4 * PREFILL_LOGIT_TOL:
+                break
+        else:
+            pytest.fail("no decisive prompt found")
+        ids, _, _ = eng.generate_greedy(toks, 16, pkg.MODE_GEMM)
+        assert ids.tolist() == want_ids.tolist(), (ids, want_ids, margins.min())
+
+
+def test_prefill_gemm_matches_gemv_prefill_closely(pkg):
+    """Two numerics modes, one model: the logits after a 64-token prompt agree to bf16-input precision."""
+    eng, ora, cfg = engine_and_oracle(pkg, 0, n_layers=2, seed=52, source="synth")
+    with eng:
+        toks = _prompt(cfg, 64, 8)
+        a = eng.forward_logits(toks, pkg.MODE_GEMM)
+        b = eng.forward_logits(toks, pkg.MODE_GEMV)
+        assert np.abs(a - b).max() <= 0.05 * max(1.0, np.abs(b).max())
+        assert np.abs(a - b).max() > 0  # they really are different arithmetic
