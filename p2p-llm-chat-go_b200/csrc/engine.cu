@@ -103,7 +103,7 @@ int Engine::init(const b200_config& c) {
 
   auto need = [&](int type, int64_t N, int64_t K, const char* what) -> int {
     if (!gemv_shape_ok(type, N, K, 0)) {
-      set_error("shape %lldx%lld of %s not supported for tensor type %d (bf16: K%%256, Q4_K: K%%1024, Q6_K: K%%2048, N%%4)",
+      set_error("shape %lldx%lld of %s not supported for tensor type %d (bf16: K%%256, Q4_K/Q6_K: K%%2048, N%%4)",
                 (long long)N, (long long)K, what, type);
       return B200_EINVAL;
     }

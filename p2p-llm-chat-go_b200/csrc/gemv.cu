@@ -17,7 +17,7 @@
 //
 // Numerics (DESIGN.md "Numerics contract", mirrored by oracle/oracle.cpp mode 0): fp32 activations and
 // accumulation; bf16 weights used exactly; Q4_K/Q6_K weights multiply activations quantised to int16 per
-// 32-element block (hi/lo byte planes, dp4a) with exact integer sub-block sums.
+// 32-element block (dp2a: int16 x int8) with exact integer sub-block sums.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -114,22 +114,46 @@ struct FmtBF16 {
   }
 };
 
-// Shared by Q4_K / Q6_K: x -> int16 per 32-block (Q16_32), stored as a signed hi-byte plane and an
-// unsigned lo-byte plane (X = 256*hi + lo) so that dp4a does the integer dot products exactly.
-// smem: Xhi[K] | Xlo[K] | dx[K/32] | dxs[K/32]  (dxs = dx * sum(X), used by Q4_K's "min" term)
+// Shared by Q4_K / Q6_K: x -> int16 per 32-block ("Q16_32": d = amax/32767, X = rint(x/d)), kept in shared
+// memory as int16 in a *lane-major* order chosen per weight format, so that every lane fetches the 64
+// activations its 64 weights need with eight conflict-free 16-byte loads:
+//     element k of a 2048-wide chunk  ->  ((i*32 + lane)*8 + r)   where (lane, i, r) = Fmt::xpos(k)
+// The integer dot products use dp2a (two int16 x two int8 per instruction) and are exact.
+// smem: X[K] int16 | dx[K/32] | dxs[K/32]  (dxs = dx * sum(X), used by Q4_K's "min" term)
 struct QActLayout {
   static __host__ __device__ size_t bytes(int K) { return (size_t)K * 2 + (size_t)(K / 32) * 8; }
-  static DEVINL const int8_t* hi(const uint8_t* xs) { return reinterpret_cast<const int8_t*>(xs); }
-  static DEVINL const uint8_t* lo(const uint8_t* xs, int K) { return xs + K; }
+  static DEVINL const uint4* x(const uint8_t* xs) { return reinterpret_cast<const uint4*>(xs); }
   static DEVINL const float* dx(const uint8_t* xs, int K) { return reinterpret_cast<const float*>(xs + 2 * (size_t)K); }
   static DEVINL const float* dxs(const uint8_t* xs, int K) { return dx(xs, K) + K / 32; }
 };
 
-template <int PRO>
+DEVINL int dp2a_lo_su(uint32_t x2, uint32_t q4, int c) {  // x2 = 2 x s16, q4 bytes 0,1 unsigned
+  int d;
+  asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(x2), "r"(q4), "r"(c));
+  return d;
+}
+DEVINL int dp2a_hi_su(uint32_t x2, uint32_t q4, int c) {  // q4 bytes 2,3 unsigned
+  int d;
+  asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(x2), "r"(q4), "r"(c));
+  return d;
+}
+DEVINL int dp2a_lo_ss(uint32_t x2, uint32_t q4, int c) {  // q4 bytes 0,1 signed
+  int d;
+  asm("dp2a.lo.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(x2), "r"(q4), "r"(c));
+  return d;
+}
+DEVINL int dp2a_hi_ss(uint32_t x2, uint32_t q4, int c) {
+  int d;
+  asm("dp2a.hi.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(x2), "r"(q4), "r"(c));
+  return d;
+}
+// small non-negative integer (< 2^23) -> float without the conversion pipe
+DEVINL float small_u2f(uint32_t v) { return __uint_as_float(0x4B000000u | v) - 8388608.0f; }
+
+template <class F, int PRO>
 DEVINL void q16_prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane) {
   const float inv = rms_inv<PRO>(a, red, warp, lane);
-  int8_t* xh = reinterpret_cast<int8_t*>(xs);
-  uint8_t* xl = xs + a.K;
+  int16_t* xq = reinterpret_cast<int16_t*>(xs);
   float* dx = reinterpret_cast<float*>(xs + 2 * (size_t)a.K);
   float* dxs = dx + a.K / 32;
   for (int b = warp; b < a.K / 32; b += kWarps) {
@@ -142,8 +166,7 @@ DEVINL void q16_prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, i
     float r = rintf(__fmul_rn(v, id));
     r = fminf(32767.f, fmaxf(-32767.f, r));
     const int X = (int)r;
-    xh[k] = (int8_t)(X >> 8);
-    xl[k] = (uint8_t)(X & 255);
+    xq[(k & ~2047) + F::xpos(k & 2047)] = (int16_t)X;
     const int xsum = __reduce_add_sync(0xffffffffu, X);
     if (lane == 0) {
       dx[b] = d;
@@ -153,12 +176,17 @@ DEVINL void q16_prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, i
   __syncthreads();
 }
 
+// Q4_K: a stage is R rows x 8 super-blocks (GGUF byte order, 144 B each).  lane = (block, j): the 32 qs bytes
+// of sub-block pair (2j, 2j+1) = 64 weights [64j, 64j+64) of that block; both sub-block sums are complete in
+// one lane, so (d*sc)*(dx*isum) is formed exactly as in the oracle.
 struct FmtQ4K {
-  static constexpr int R = 4, BLOCKS = 4, CHUNK = BLOCKS * QK_K, STAGES = 3;
-  static constexpr int ROW_STAGE_BYTES = BLOCKS * Q4K_BYTES;  // 576
+  static constexpr int R = 4, BLOCKS = 8, CHUNK = BLOCKS * QK_K, STAGES = 2;
+  static constexpr int ROW_STAGE_BYTES = BLOCKS * Q4K_BYTES;  // 1152
   static constexpr int STAGE_BYTES = R * ROW_STAGE_BYTES;
   static __host__ __device__ size_t x_bytes(int K) { return QActLayout::bytes(K); }
   static __host__ __device__ size_t row_bytes(int K) { return (size_t)(K / QK_K) * Q4K_BYTES; }
+  // k in [0,2048): block = k>>8, j = (k>>6)&3, i = (k>>3)&7, r = k&7 ; lane = block*4 + j
+  static DEVINL int xpos(int k) { return ((((k >> 3) & 7) * 32 + ((k >> 8) * 4 + ((k >> 6) & 3))) << 3) + (k & 7); }
 
   static DEVINL void issue(uint32_t dst, uint32_t bar, const GemvArgs& a, int unit, int c, uint64_t pol) {
     const size_t rb = row_bytes(a.K);
@@ -168,117 +196,118 @@ struct FmtQ4K {
   }
   template <int PRO>
   static DEVINL void prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane) {
-    q16_prologue<PRO>(xs, a, red, warp, lane);
+    q16_prologue<FmtQ4K, PRO>(xs, a, red, warp, lane);
   }
 
-  // lane -> (block = lane/8, s = lane%8): 16 bytes of qs = low nibbles of sub-block 2j (16 weights at
-  // 64j+16h) and high nibbles of sub-block 2j+1 (16 weights at 64j+32+16h), j = s/2, h = s%2.
   static DEVINL void consume(const uint8_t* st, const uint8_t* xs, int c, const GemvArgs& a, int lane, float* acc) {
-    const int blk = lane >> 3, s = lane & 7, j = s >> 1, h = s & 1;
-    const int e0 = c * CHUNK + blk * QK_K + 64 * j + 16 * h;
-    const uint4 xh0 = *reinterpret_cast<const uint4*>(QActLayout::hi(xs) + e0);
-    const uint4 xl0 = *reinterpret_cast<const uint4*>(QActLayout::lo(xs, a.K) + e0);
-    const uint4 xh1 = *reinterpret_cast<const uint4*>(QActLayout::hi(xs) + e0 + 32);
-    const uint4 xl1 = *reinterpret_cast<const uint4*>(QActLayout::lo(xs, a.K) + e0 + 32);
-    const int xb = (c * CHUNK + blk * QK_K) / 32;
-    const float dxA = QActLayout::dx(xs, a.K)[xb + 2 * j];
-    const float dxB = QActLayout::dx(xs, a.K)[xb + 2 * j + 1];
-    const float dxsS = QActLayout::dxs(xs, a.K)[xb + s];
-    const int sh = (j & 1) * 16;
+    const int blk = lane >> 2, j = lane & 3;
+    uint32_t xr[32];  // 64 int16: [0,16) low-nibble sub-block 2j, [16,32) high-nibble sub-block 2j+1
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
+    for (int i = 0; i < 8; ++i) {
+      const uint4 v = QActLayout::x(xs)[(size_t)c * (CHUNK / 8) + i * 32 + lane];
+      xr[4 * i] = v.x; xr[4 * i + 1] = v.y; xr[4 * i + 2] = v.z; xr[4 * i + 3] = v.w;
+    }
+    const int xb = (c * CHUNK + blk * QK_K) / 32 + 2 * j;
+    const float dxA = QActLayout::dx(xs, a.K)[xb], dxB = QActLayout::dx(xs, a.K)[xb + 1];
+    const float dxsA = QActLayout::dxs(xs, a.K)[xb], dxsB = QActLayout::dxs(xs, a.K)[xb + 1];
+    const int sh = (j & 1) * 16;
+    const bool upper = j >= 2;
+    int iA[R], iB[R];
+    uint32_t scp[R], mnp[R], dd[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {  // phase 1: integer work of every row (independent chains)
       const uint8_t* b = st + r * ROW_STAGE_BYTES + blk * Q4K_BYTES;
       const uint4 hdr = *reinterpret_cast<const uint4*>(b);
-      const uint4 q = *reinterpret_cast<const uint4*>(b + 16 + 16 * s);
-      const float d = __half2float(__ushort_as_half((unsigned short)(hdr.x & 0xffffu)));
-      const float dmin = __half2float(__ushort_as_half((unsigned short)(hdr.x >> 16)));
-      // six-bit (scale, min) pairs of sub-blocks 2j, 2j+1 (ggml get_scale_min_k4), two at a time
-      uint32_t scp, mnp;
-      if (j < 2) {
-        scp = (hdr.y >> sh) & 0x3F3Fu;
-        mnp = (hdr.z >> sh) & 0x3F3Fu;
-      } else {
-        const uint32_t t = (hdr.w >> sh) & 0xFFFFu, u = (hdr.y >> sh) & 0xFFFFu, v = (hdr.z >> sh) & 0xFFFFu;
-        scp = (t & 0x0F0Fu) | ((u >> 2) & 0x3030u);
-        mnp = ((t >> 4) & 0x0F0Fu) | ((v >> 2) & 0x3030u);
-      }
-      const float scA = (float)(scp & 0xFFu), scB = (float)(scp >> 8);
-      const float mS = (float)(h ? (mnp >> 8) : (mnp & 0xFFu));
-      int iAh = 0, iAl = 0, iBh = 0, iBl = 0;
-      const uint32_t qw[4] = {q.x, q.y, q.z, q.w};
-      const uint32_t h0[4] = {xh0.x, xh0.y, xh0.z, xh0.w}, l0[4] = {xl0.x, xl0.y, xl0.z, xl0.w};
-      const uint32_t h1[4] = {xh1.x, xh1.y, xh1.z, xh1.w}, l1[4] = {xl1.x, xl1.y, xl1.z, xl1.w};
+      const uint4 q0 = *reinterpret_cast<const uint4*>(b + 16 + 32 * j);
+      const uint4 q1 = *reinterpret_cast<const uint4*>(b + 32 + 32 * j);
+      dd[r] = hdr.x;
+      // six-bit (scale, min) of sub-blocks 2j, 2j+1 (ggml get_scale_min_k4), both variants then select
+      const uint32_t u = hdr.y >> sh, v = hdr.z >> sh, t = hdr.w >> sh;
+      const uint32_t sc_lo = u & 0x3F3Fu, mn_lo = v & 0x3F3Fu;
+      const uint32_t sc_hi = (t & 0x0F0Fu) | ((u >> 2) & 0x3030u), mn_hi = ((t >> 4) & 0x0F0Fu) | ((v >> 2) & 0x3030u);
+      scp[r] = upper ? sc_hi : sc_lo;
+      mnp[r] = upper ? mn_hi : mn_lo;
+      const uint32_t qw[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+      int sa = 0, sb = 0;
 #pragma unroll
-      for (int w = 0; w < 4; ++w) {
-        const int lo = (int)(qw[w] & 0x0F0F0F0Fu), hi = (int)((qw[w] >> 4) & 0x0F0F0F0Fu);
-        iAh = dp4a_ss(lo, (int)h0[w], iAh);
-        iAl = dp4a_su(lo, l0[w], iAl);
-        iBh = dp4a_ss(hi, (int)h1[w], iBh);
-        iBl = dp4a_su(hi, l1[w], iBl);
+      for (int w = 0; w < 8; ++w) {
+        const uint32_t lo = qw[w] & 0x0F0F0F0Fu, hi = (qw[w] >> 4) & 0x0F0F0F0Fu;
+        sa = dp2a_lo_su(xr[2 * w], lo, sa);
+        sa = dp2a_hi_su(xr[2 * w + 1], lo, sa);
+        sb = dp2a_lo_su(xr[16 + 2 * w], hi, sb);
+        sb = dp2a_hi_su(xr[17 + 2 * w], hi, sb);
       }
-      const float fa = (float)(iAh * 256 + iAl), fb = (float)(iBh * 256 + iBl);
+      iA[r] = sa;
+      iB[r] = sb;
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {  // phase 2: scales in fp32
+      const float d = __half2float(__ushort_as_half((unsigned short)(dd[r] & 0xffffu)));
+      const float dmin = __half2float(__ushort_as_half((unsigned short)(dd[r] >> 16)));
+      const float scA = small_u2f(scp[r] & 0xFFu), scB = small_u2f(scp[r] >> 8);
+      const float mA = small_u2f(mnp[r] & 0xFFu), mB = small_u2f(mnp[r] >> 8);
       float t = acc[r];
-      t = fmaf(__fmul_rn(d, scA), __fmul_rn(dxA, fa), t);
-      t = fmaf(__fmul_rn(d, scB), __fmul_rn(dxB, fb), t);
-      t = fmaf(-__fmul_rn(dmin, mS), dxsS, t);
+      t = fmaf(__fmul_rn(d, scA), __fmul_rn(dxA, (float)iA[r]), t);
+      t = fmaf(__fmul_rn(d, scB), __fmul_rn(dxB, (float)iB[r]), t);
+      t = fmaf(-__fmul_rn(dmin, mA), dxsA, t);
+      t = fmaf(-__fmul_rn(dmin, mB), dxsB, t);
       acc[r] = t;
     }
   }
 };
 
-// Q6_K rows are stored on the device section-wise: [ql: nb*128][qh: nb*64][scales: nb*16][d: nb*2]
-// (same bytes as GGUF's 210-byte blocks, re-ordered so that every section is 16-byte aligned).
+// Q6_K rows are stored on the device chunk-wise (8 super-blocks = 1680 B, the same bytes as GGUF's eight
+// 210-byte blocks, re-ordered lane-major): [qlA 32x16][qlB 32x16][qh 32x16][scales 32x4][d 8x2].
+// lane = (block, half, lh): l in [16lh,16lh+16) of the four 32-wide runs t=0..3 of that half; every run is
+// exactly one 16-weight scale group.  qlA = ql[half*64 + 16lh..], qlB = ql[half*64 + 32 + 16lh..].
 struct FmtQ6K {
   static constexpr int R = 2, BLOCKS = 8, CHUNK = BLOCKS * QK_K, STAGES = 2;
-  static constexpr int QL = BLOCKS * 128, QH = BLOCKS * 64, SC = BLOCKS * 16, DD = BLOCKS * 2;
-  static constexpr int ROW_STAGE_BYTES = QL + QH + SC + DD;  // 1680
+  static constexpr int ROW_STAGE_BYTES = BLOCKS * Q6K_BYTES;  // 1680
   static constexpr int STAGE_BYTES = R * ROW_STAGE_BYTES;
   static __host__ __device__ size_t x_bytes(int K) { return QActLayout::bytes(K); }
   static __host__ __device__ size_t row_bytes(int K) { return (size_t)(K / QK_K) * Q6K_BYTES; }
+  // k in [0,2048): block = k>>8, half = (k>>7)&1, t = (k>>5)&3, lh = (k>>4)&1, u = (k>>3)&1, r = k&7
+  static DEVINL int xpos(int k) {
+    const int lane = (k >> 8) * 4 + ((k >> 7) & 1) * 2 + ((k >> 4) & 1), i = ((k >> 5) & 3) * 2 + ((k >> 3) & 1);
+    return ((i * 32 + lane) << 3) + (k & 7);
+  }
 
   static DEVINL void issue(uint32_t dst, uint32_t bar, const GemvArgs& a, int unit, int c, uint64_t pol) {
-    const int nb = a.K / QK_K;
     const size_t rb = row_bytes(a.K);
+    const uint8_t* src = a.W + (size_t)unit * R * rb + (size_t)c * ROW_STAGE_BYTES;
 #pragma unroll
-    for (int r = 0; r < R; ++r) {
-      const uint8_t* row = a.W + ((size_t)unit * R + r) * rb;
-      const uint32_t d = dst + r * ROW_STAGE_BYTES;
-      bulk_g2s(d, row + (size_t)c * QL, QL, bar, pol);
-      bulk_g2s(d + QL, row + (size_t)nb * 128 + (size_t)c * QH, QH, bar, pol);
-      bulk_g2s(d + QL + QH, row + (size_t)nb * 192 + (size_t)c * SC, SC, bar, pol);
-      bulk_g2s(d + QL + QH + SC, row + (size_t)nb * 208 + (size_t)c * DD, DD, bar, pol);
-    }
+    for (int r = 0; r < R; ++r) bulk_g2s(dst + r * ROW_STAGE_BYTES, src + (size_t)r * rb, ROW_STAGE_BYTES, bar, pol);
   }
   template <int PRO>
   static DEVINL void prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane) {
-    q16_prologue<PRO>(xs, a, red, warp, lane);
+    q16_prologue<FmtQ6K, PRO>(xs, a, red, warp, lane);
   }
 
-  // lane -> (block = lane/4, half = (lane%4)/2, lh = lane%2): 16 values of l in [16lh,16lh+16) for the four
-  // 32-wide runs t=0..3 of that half; each run is exactly one 16-weight scale group.
   static DEVINL void consume(const uint8_t* st, const uint8_t* xs, int c, const GemvArgs& a, int lane, float* acc) {
     const int blk = lane >> 2, half = (lane >> 1) & 1, lh = lane & 1;
-    const int e = c * CHUNK + blk * QK_K + half * 128 + 16 * lh;  // + 32 t
-    uint32_t xh[4][4], xl[4][4];
+    uint32_t xr[32];  // run t: xr[8t .. 8t+8) = 16 int16
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const uint4 v = QActLayout::x(xs)[(size_t)c * (CHUNK / 8) + i * 32 + lane];
+      xr[4 * i] = v.x; xr[4 * i + 1] = v.y; xr[4 * i + 2] = v.z; xr[4 * i + 3] = v.w;
+    }
     float dxt[4];
 #pragma unroll
-    for (int t = 0; t < 4; ++t) {
-      const uint4 vh = *reinterpret_cast<const uint4*>(QActLayout::hi(xs) + e + 32 * t);
-      const uint4 vl = *reinterpret_cast<const uint4*>(QActLayout::lo(xs, a.K) + e + 32 * t);
-      xh[t][0] = vh.x; xh[t][1] = vh.y; xh[t][2] = vh.z; xh[t][3] = vh.w;
-      xl[t][0] = vl.x; xl[t][1] = vl.y; xl[t][2] = vl.z; xl[t][3] = vl.w;
-      dxt[t] = QActLayout::dx(xs, a.K)[(e + 32 * t) / 32];
-    }
+    for (int t = 0; t < 4; ++t) dxt[t] = QActLayout::dx(xs, a.K)[(c * CHUNK + blk * QK_K + half * 128) / 32 + t];
+    (void)lh;
+    int is[R][4];
+    uint32_t scw[R];
+    float dv[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) {
       const uint8_t* b = st + r * ROW_STAGE_BYTES;
-      const uint4 q0 = *reinterpret_cast<const uint4*>(b + blk * 128 + half * 64 + 16 * lh);
-      const uint4 q1 = *reinterpret_cast<const uint4*>(b + blk * 128 + half * 64 + 32 + 16 * lh);
-      const uint4 qh = *reinterpret_cast<const uint4*>(b + QL + blk * 64 + half * 32 + 16 * lh);
-      const int8_t* sc = reinterpret_cast<const int8_t*>(b + QL + QH + blk * 16 + half * 8 + lh);
-      const float d = __half2float(__ushort_as_half(*reinterpret_cast<const unsigned short*>(b + QL + QH + SC + blk * 2)));
+      const uint4 q0 = *reinterpret_cast<const uint4*>(b + lane * 16);
+      const uint4 q1 = *reinterpret_cast<const uint4*>(b + 512 + lane * 16);
+      const uint4 qh = *reinterpret_cast<const uint4*>(b + 1024 + lane * 16);
+      scw[r] = *reinterpret_cast<const uint32_t*>(b + 1536 + lane * 4);
+      dv[r] = __half2float(__ushort_as_half(*reinterpret_cast<const unsigned short*>(b + 1664 + blk * 2)));
       const uint32_t a0[4] = {q0.x, q0.y, q0.z, q0.w}, a1[4] = {q1.x, q1.y, q1.z, q1.w}, ah[4] = {qh.x, qh.y, qh.z, qh.w};
-      int ih[4] = {0, 0, 0, 0}, il[4] = {0, 0, 0, 0};
+      int s[4] = {0, 0, 0, 0};
 #pragma unroll
       for (int w = 0; w < 4; ++w) {
         uint32_t qt[4];
@@ -288,16 +317,21 @@ struct FmtQ6K {
         qt[3] = ((a1[w] >> 4) & 0x0F0F0F0Fu) | ((ah[w] >> 2) & 0x30303030u);
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
-          const int qs = (int)__vsub4(qt[t], 0x20202020u);  // bytes q-32 in [-32,31]
-          ih[t] = dp4a_ss(qs, (int)xh[t][w], ih[t]);
-          il[t] = dp4a_su(qs, xl[t][w], il[t]);
+          const uint32_t qs = __vsub4(qt[t], 0x20202020u);  // bytes q-32 in [-32,31]
+          s[t] = dp2a_lo_ss(xr[8 * t + 2 * w], qs, s[t]);
+          s[t] = dp2a_hi_ss(xr[8 * t + 2 * w + 1], qs, s[t]);
         }
       }
+#pragma unroll
+      for (int t = 0; t < 4; ++t) is[r][t] = s[t];
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
       float tacc = acc[r];
 #pragma unroll
       for (int t = 0; t < 4; ++t) {
-        const float f = (float)(ih[t] * 256 + il[t]);
-        tacc = fmaf(__fmul_rn(d, (float)sc[2 * t]), __fmul_rn(dxt[t], f), tacc);
+        const float sc = (float)(int)(signed char)((scw[r] >> (8 * t)) & 0xFFu);
+        tacc = fmaf(__fmul_rn(dv[r], sc), __fmul_rn(dxt[t], (float)is[r][t]), tacc);
       }
       acc[r] = tacc;
     }

@@ -66,18 +66,29 @@ __global__ void quant_q16_kernel(const float* x, int64_t n, int16_t* q, float* d
   if (lane == 0) d[b] = dd;
 }
 
-// GGUF Q6_K row (nb blocks of 210 B: ql[128] qh[64] sc[16] d[2]) <-> device row [ql*nb][qh*nb][sc*nb][d*nb]
+// GGUF Q6_K row (nb blocks of 210 B: ql[128] qh[64] sc[16] d[2]) <-> device row, chunked by 8 blocks (1680 B):
+// [qlA 32x16][qlB 32x16][qh 32x16][scales 32x4][d 8x2] with lane = block*4 + half*2 + lh (see gemv.cu FmtQ6K)
 __global__ void q6k_repack_kernel(const uint8_t* src, uint8_t* dst, int64_t rows, int64_t nb, int to_device) {
   const int64_t row = blockIdx.y;
   const int64_t blk = blockIdx.x;
   const int t = threadIdx.x;  // 210 threads, one byte each
   if (row >= rows || blk >= nb || t >= Q6K_BYTES) return;
   const size_t rb = (size_t)nb * Q6K_BYTES;
-  size_t dev_off;
-  if (t < 128) dev_off = (size_t)blk * 128 + t;
-  else if (t < 192) dev_off = (size_t)nb * 128 + (size_t)blk * 64 + (t - 128);
-  else if (t < 208) dev_off = (size_t)nb * 192 + (size_t)blk * 16 + (t - 192);
-  else dev_off = (size_t)nb * 208 + (size_t)blk * 2 + (t - 208);
+  const int bic = (int)(blk & 7);  // block in chunk
+  int off;
+  if (t < 128) {
+    const int half = t >> 6, o = t & 63, second = (o >> 5) & 1, lh = (o >> 4) & 1, r = o & 15;
+    off = second * 512 + (bic * 4 + half * 2 + lh) * 16 + r;
+  } else if (t < 192) {
+    const int b = t - 128, half = b >> 5, lh = (b >> 4) & 1, r = b & 15;
+    off = 1024 + (bic * 4 + half * 2 + lh) * 16 + r;
+  } else if (t < 208) {
+    const int s8 = t - 192, half = s8 >> 3, run = (s8 & 7) >> 1, lh = s8 & 1;
+    off = 1536 + (bic * 4 + half * 2 + lh) * 4 + run;
+  } else {
+    off = 1664 + bic * 2 + (t - 208);
+  }
+  const size_t dev_off = (size_t)(blk >> 3) * (8 * Q6K_BYTES) + off;
   const size_t gguf_off = (size_t)blk * Q6K_BYTES + t;
   if (to_device) dst[row * rb + dev_off] = src[row * rb + gguf_off];
   else dst[row * rb + gguf_off] = src[row * rb + dev_off];

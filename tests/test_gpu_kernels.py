@@ -83,7 +83,7 @@ def test_gemv_bf16(pkg, rows, cols):
     _gemv_case(pkg, orc.BF16, rows, cols, seed=rows + cols)
 
 
-@pytest.mark.parametrize("rows,cols", [(4, 1024), (520, 4096), (4096, 14336)])
+@pytest.mark.parametrize("rows,cols", [(4, 2048), (520, 4096), (4096, 14336)])
 def test_gemv_q4k(pkg, rows, cols):
     _gemv_case(pkg, orc.Q4_K, rows, cols, seed=rows + cols)
 
@@ -115,7 +115,7 @@ def test_gemv_rejects_bad_shapes(pkg):
     with pytest.raises(pkg.B200Error):
         pkg.gemv(orc.BF16, np.zeros((4, 100), np.uint16), 4, 100, np.zeros(100, np.float32))
     with pytest.raises(pkg.B200Error):
-        pkg.gemv(orc.Q4_K, np.zeros(144 * 3, np.uint8), 3, 256, np.zeros(256, np.float32))
+        pkg.gemv(orc.Q4_K, np.zeros(144 * 4 * 4, np.uint8), 4, 1024, np.zeros(1024, np.float32))
 
 
 @pytest.mark.parametrize("n_ctx,n_heads,n_kv", [(1, 4, 1), (17, 8, 2), (640, 32, 8), (1000, 8, 1), (33, 2, 2)])
@@ -135,7 +135,7 @@ def test_attn_decode(pkg, n_ctx, n_heads, n_kv):
 # tcgen05 GEMM (GEMM numerics, oracle mode 1): bf16 inputs, exact products, fp32 accumulation in TMEM
 @pytest.mark.parametrize("wtype,rows,cols,n", [
     (orc.BF16, 128, 64, 1), (orc.BF16, 256, 512, 7), (orc.BF16, 1024, 4096, 128), (orc.BF16, 512, 2048, 129),
-    (orc.BF16, 6144, 4096, 512), (orc.BF16, 4096, 14336, 300), (orc.Q4_K, 256, 1024, 33), (orc.Q6_K, 256, 2048, 64)])
+    (orc.BF16, 6144, 4096, 512), (orc.BF16, 4096, 14336, 300), (orc.Q4_K, 256, 2048, 33), (orc.Q6_K, 256, 2048, 64)])
 def test_gemm_tcgen05(pkg, wtype, rows, cols, n):
     rng = np.random.default_rng(rows + cols + n)
     W = random_tensor(rng, wtype, rows, cols)

@@ -81,7 +81,7 @@ def random_tensor(rng, wtype, rows, cols, sigma=None):
     raise ValueError(wtype)
 
 
-def tiny_cfg(pkg, fmt, n_layers=2, d_model=2048, n_heads=8, n_kv_heads=2, d_ffn=2048, vocab=1024, max_ctx=256,
+def tiny_cfg(pkg, fmt, n_layers=2, d_model=2048, n_heads=16, n_kv_heads=4, d_ffn=2048, vocab=1024, max_ctx=256,
              seed=-1, eos=-1):
     c = pkg.Config()
     c.n_layers, c.d_model, c.n_heads, c.n_kv_heads, c.head_dim = n_layers, d_model, n_heads, n_kv_heads, 128
