@@ -156,21 +156,37 @@ DEVINL void q16_prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, i
   int16_t* xq = reinterpret_cast<int16_t*>(xs);
   float* dx = reinterpret_cast<float*>(xs + 2 * (size_t)a.K);
   float* dxs = dx + a.K / 32;
-  for (int b = warp; b < a.K / 32; b += kWarps) {
-    const int k = b * 32 + lane;
-    float v = a.x[k];
-    if (PRO == PRO_RMSNORM) v = __fmul_rn(__fmul_rn(v, inv), a.norm_w[k]);
-    const float amax = warp_max(fabsf(v));
-    const float d = __fdiv_rn(amax, 32767.0f);
-    const float id = d > 0.f ? __fdiv_rn(1.0f, d) : 0.f;
-    float r = rintf(__fmul_rn(v, id));
-    r = fminf(32767.f, fmaxf(-32767.f, r));
-    const int X = (int)r;
-    xq[(k & ~2047) + F::xpos(k & 2047)] = (int16_t)X;
-    const int xsum = __reduce_add_sync(0xffffffffu, X);
-    if (lane == 0) {
-      dx[b] = d;
-      dxs[b] = __fmul_rn(d, (float)xsum);
+  // U blocks per round: all of a round's global loads are issued before the first dependent shuffle, so the
+  // prologue costs ceil(K/32/16/U) L2 round trips instead of one per block
+  constexpr int U = 8;
+  const int nblk = a.K / 32;
+  for (int b0 = warp; b0 < nblk; b0 += kWarps * U) {
+    float v[U], g[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int b = b0 + u * kWarps;
+      v[u] = b < nblk ? a.x[b * 32 + lane] : 0.f;
+      g[u] = (PRO == PRO_RMSNORM && b < nblk) ? a.norm_w[b * 32 + lane] : 1.f;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int b = b0 + u * kWarps;
+      if (b >= nblk) break;
+      const int k = b * 32 + lane;
+      float val = v[u];
+      if (PRO == PRO_RMSNORM) val = __fmul_rn(__fmul_rn(val, inv), g[u]);
+      const float amax = warp_max(fabsf(val));
+      const float d = __fdiv_rn(amax, 32767.0f);
+      const float id = d > 0.f ? __fdiv_rn(1.0f, d) : 0.f;
+      float r = rintf(__fmul_rn(val, id));
+      r = fminf(32767.f, fmaxf(-32767.f, r));
+      const int X = (int)r;
+      xq[(k & ~2047) + F::xpos(k & 2047)] = (int16_t)X;
+      const int xsum = __reduce_add_sync(0xffffffffu, X);
+      if (lane == 0) {
+        dx[b] = d;
+        dxs[b] = __fmul_rn(d, (float)xsum);
+      }
     }
   }
   __syncthreads();
