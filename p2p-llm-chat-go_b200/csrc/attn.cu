@@ -77,14 +77,17 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnArgs a) {
     for (int h = warp; h < G; h += 4) {
       const uint32_t* kr = Ks + lane * kKStride;
       const float* qh = qs + h * kHeadDim;
-      float s = 0.f;
-#pragma unroll 16
-      for (int w = 0; w < kHeadDim / 2; ++w) {
-        const uint32_t kw = kr[w];
-        const float2 q2 = *reinterpret_cast<const float2*>(qh + 2 * w);
-        s = fmaf(q2.x, bf16lo(kw), s);
-        s = fmaf(q2.y, bf16hi(kw), s);
+      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;  // four chains: the dot product is latency-, not issue-bound
+#pragma unroll 8
+      for (int w = 0; w < kHeadDim / 2; w += 2) {
+        const uint32_t ka = kr[w], kb = kr[w + 1];
+        const float4 q4 = *reinterpret_cast<const float4*>(qh + 2 * w);
+        s0 = fmaf(q4.x, bf16lo(ka), s0);
+        s1 = fmaf(q4.y, bf16hi(ka), s1);
+        s2 = fmaf(q4.z, bf16lo(kb), s2);
+        s3 = fmaf(q4.w, bf16hi(kb), s3);
       }
+      float s = (s0 + s1) + (s2 + s3);
       const bool valid = (t0 + lane) < ctx;
       s = valid ? s * scale : -INFINITY;
       const float m_old = m_run[h];
@@ -128,35 +131,35 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnArgs a) {
   // merge the splits: (m, l) of every (head, split) into shared memory with one parallel round of loads,
   // softmax weights per split, then one pass over the partial accumulators with independent loads
   const float* base = partial + (size_t)kvh * S * G * kPart;
-  float* w_s = reinterpret_cast<float*>(Ks);  // [G][S] weights, reusing the K tile (G*S <= 8*32 floats)
-  float* l_s = w_s + G * kMaxSplits;
-  for (int i = tid; i < G * S; i += 128) {
-    const int h = i / S, sp = i % S;
-    const float* ps = base + ((size_t)sp * G + h) * kPart;
-    w_s[h * kMaxSplits + sp] = __ldcg(ps + kHeadDim);
-    l_s[h * kMaxSplits + sp] = __ldcg(ps + kHeadDim + 1);
+  float* w_s = reinterpret_cast<float*>(Ks);  // [G][kMaxSplits] softmax weight of every split (reuses the K tile)
+  for (int h = warp; h < G; h += 4) {       // one head per warp, lane = split: a single round of loads
+    const bool on = lane < S;
+    const float* ps = base + ((size_t)(on ? lane : 0) * G + h) * kPart;
+    const float ms = on ? __ldcg(ps + kHeadDim) : -INFINITY;
+    const float ls = on ? __ldcg(ps + kHeadDim + 1) : 0.f;
+    const float M = warp_max(ms);
+    const float w = (ms == -INFINITY) ? 0.f : expf(ms - M);
+    const float den = warp_sum(ls * w);
+    w_s[h * kMaxSplits + lane] = w;
+    if (lane == 0) corr_s[h] = 1.0f / den;
   }
   __syncthreads();
-  if (tid < G) {
-    float M = -INFINITY;
-    for (int sp = 0; sp < S; ++sp) M = fmaxf(M, w_s[tid * kMaxSplits + sp]);
-    float den = 0.f;
-    for (int sp = 0; sp < S; ++sp) {
-      const float ms = w_s[tid * kMaxSplits + sp];
-      const float w = (ms == -INFINITY) ? 0.f : expf(ms - M);
-      den = fmaf(l_s[tid * kMaxSplits + sp], w, den);
-      w_s[tid * kMaxSplits + sp] = w;
-    }
-    corr_s[tid] = 1.0f / den;
-  }
-  __syncthreads();
+  float num[G];
 #pragma unroll
-  for (int h = 0; h < G; ++h) {
-    float num = 0.f;
-#pragma unroll 4
-    for (int sp = 0; sp < S; ++sp) num = fmaf(__ldcg(base + ((size_t)sp * G + h) * kPart + tid), w_s[h * kMaxSplits + sp], num);
-    out[((size_t)kvh * G + h) * kHeadDim + tid] = num * corr_s[h];
+  for (int h = 0; h < G; ++h) num[h] = 0.f;
+  for (int sp = 0; sp < S; sp += 4) {  // 4 x G independent loads in flight per thread
+    float p[4][G];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int h = 0; h < G; ++h) p[u][h] = (sp + u < S) ? __ldcg(base + ((size_t)(sp + u) * G + h) * kPart + tid) : 0.f;
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int h = 0; h < G; ++h) num[h] = fmaf(p[u][h], (sp + u < S) ? w_s[h * kMaxSplits + sp + u] : 0.f, num[h]);
   }
+#pragma unroll
+  for (int h = 0; h < G; ++h) out[((size_t)kvh * G + h) * kHeadDim + tid] = num[h] * corr_s[h];
   if (tid == 0) counters[kvh] = 0u;
 }
 

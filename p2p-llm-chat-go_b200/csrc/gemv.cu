@@ -55,9 +55,9 @@ DEVINL float rms_inv(const GemvArgs& a, float* red, int warp, int lane) {
 // Each policy states: R rows per unit, CHUNK columns per stage, the stage layout, how lane 0 issues the
 // bulk copies of a stage, how the block prepares x in shared memory, and how a warp consumes a stage.
 
-template <int KC>  // KC in {256, 512}
+template <int KC, int R_>  // KC in {256, 512}; R_ rows per work unit (4, or 2 for matrices with few rows)
 struct FmtBF16 {
-  static constexpr int R = 4, CHUNK = KC, STAGES = 2;
+  static constexpr int R = R_, CHUNK = KC, STAGES = (R_ == 4) ? 2 : 3;
   static constexpr int ROW_STAGE_BYTES = KC * 2;
   static constexpr int STAGE_BYTES = R * ROW_STAGE_BYTES;
   static __host__ __device__ size_t x_bytes(int K) { return (size_t)K * 4; }
@@ -195,8 +195,9 @@ DEVINL void q16_prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, i
 // Q4_K: a stage is R rows x 8 super-blocks (GGUF byte order, 144 B each).  lane = (block, j): the 32 qs bytes
 // of sub-block pair (2j, 2j+1) = 64 weights [64j, 64j+64) of that block; both sub-block sums are complete in
 // one lane, so (d*sc)*(dx*isum) is formed exactly as in the oracle.
+template <int R_>
 struct FmtQ4K {
-  static constexpr int R = 4, BLOCKS = 8, CHUNK = BLOCKS * QK_K, STAGES = 2;
+  static constexpr int R = R_, BLOCKS = 8, CHUNK = BLOCKS * QK_K, STAGES = (R_ == 4) ? 2 : 3;
   static constexpr int ROW_STAGE_BYTES = BLOCKS * Q4K_BYTES;  // 1152
   static constexpr int STAGE_BYTES = R * ROW_STAGE_BYTES;
   static __host__ __device__ size_t x_bytes(int K) { return QActLayout::bytes(K); }
@@ -212,7 +213,7 @@ struct FmtQ4K {
   }
   template <int PRO>
   static DEVINL void prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane) {
-    q16_prologue<FmtQ4K, PRO>(xs, a, red, warp, lane);
+    q16_prologue<FmtQ4K<R_>, PRO>(xs, a, red, warp, lane);
   }
 
   static DEVINL void consume(const uint8_t* st, const uint8_t* xs, int c, const GemvArgs& a, int lane, float* acc) {
@@ -563,7 +564,7 @@ bool gemv_shape_ok(int wtype, int64_t N, int64_t K, int epi) {
   if (N <= 0 || K <= 0 || K > 32768) return false;
   switch (wtype) {
     case T_BF16: return K % 256 == 0 && N % 4 == 0;
-    case T_Q4_K: return K % FmtQ4K::CHUNK == 0 && N % FmtQ4K::R == 0;
+    case T_Q4_K: return K % FmtQ4K<4>::CHUNK == 0 && N % 4 == 0;
     case T_Q6_K: return K % FmtQ6K::CHUNK == 0 && N % FmtQ6K::R == 0;
   }
   (void)epi;
@@ -572,11 +573,15 @@ bool gemv_shape_ok(int wtype, int64_t N, int64_t K, int epi) {
 
 cudaError_t launch_gemv(int wtype, int pro, int epi, const GemvArgs& a, cudaStream_t s, bool pdl, int sm_count) {
   if (!gemv_shape_ok(wtype, a.N, a.K, epi)) return cudaErrorInvalidValue;
+  // 4 rows per unit amortise the activation loads best; matrices with fewer than one such unit per warp
+  // (o / down / qkv: 4096-6144 rows) use 2-row units so that every warp of every SM streams something
+  const bool wide = (a.N / 4) >= sm_count * kWarps;
   switch (wtype) {
     case T_BF16:
-      return (a.K % 512 == 0) ? launch_f<FmtBF16<512>>(pro, epi, a, s, pdl, sm_count)
-                              : launch_f<FmtBF16<256>>(pro, epi, a, s, pdl, sm_count);
-    case T_Q4_K: return launch_f<FmtQ4K>(pro, epi, a, s, pdl, sm_count);
+      if (a.K % 512 == 0)
+        return wide ? launch_f<FmtBF16<512, 4>>(pro, epi, a, s, pdl, sm_count) : launch_f<FmtBF16<512, 2>>(pro, epi, a, s, pdl, sm_count);
+      return wide ? launch_f<FmtBF16<256, 4>>(pro, epi, a, s, pdl, sm_count) : launch_f<FmtBF16<256, 2>>(pro, epi, a, s, pdl, sm_count);
+    case T_Q4_K: return wide ? launch_f<FmtQ4K<4>>(pro, epi, a, s, pdl, sm_count) : launch_f<FmtQ4K<2>>(pro, epi, a, s, pdl, sm_count);
     case T_Q6_K: return launch_f<FmtQ6K>(pro, epi, a, s, pdl, sm_count);
   }
   return cudaErrorInvalidValue;
