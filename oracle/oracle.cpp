@@ -19,7 +19,7 @@
 //
 // Numerics contract shared with the CUDA engine (DESIGN.md §"Numerics"):
 //   mode 0 ("gemv", batch-1 decode): activations fp32; bf16 weights used exactly; Q4_K/Q6_K weights are
-//       multiplied against activations quantised to int16 per 32-element block (d = amax/32767,
+//       multiplied against activations quantised to int16 per 32-element block (d = amax*(1/32767),
 //       X = rint(x/d)) with exact integer sub-block dot products and fp32 scale arithmetic.
 //   mode 1 ("gemm", prefill / batched decode on tensor cores): GEMM inputs rounded to bf16 (activations,
 //       and dequantised Q4_K/Q6_K weights), fp32 accumulate.
@@ -157,12 +157,12 @@ void dequant_q6k_block(const uint8_t* blk, float* y) {
   }
 }
 
-// Activation quantisation "Q16_32": per 32 elements, d = amax/32767, X = rint(x * (1/d)).
+// Activation quantisation "Q16_32": per 32 elements, d = amax * (1/32767), X = rint(x * (1/d)).
 void quant_q16(const float* x, int64_t n, int16_t* q, float* d) {
   for (int64_t b = 0; b < n / 32; ++b) {
     float amax = 0.f;
     for (int i = 0; i < 32; ++i) amax = std::max(amax, std::fabs(x[b * 32 + i]));
-    const float dd = amax / 32767.0f;
+    const float dd = amax * (1.0f / 32767.0f);
     const float id = dd > 0.f ? 1.0f / dd : 0.f;
     d[b] = dd;
     for (int i = 0; i < 32; ++i) {

@@ -58,8 +58,8 @@ __global__ void quant_q16_kernel(const float* x, int64_t n, int16_t* q, float* d
   if (b >= n / 32) return;
   const float v = x[b * 32 + lane];
   const float amax = warp_max(fabsf(v));
-  const float dd = __fdiv_rn(amax, 32767.0f);
-  const float id = dd > 0.f ? __fdiv_rn(1.0f, dd) : 0.f;
+  const float dd = __fmul_rn(amax, 1.0f / 32767.0f);
+  const float id = dd > 0.f ? __frcp_rn(dd) : 0.f;
   float r = rintf(__fmul_rn(v, id));
   r = fminf(32767.f, fmaxf(-32767.f, r));
   q[b * 32 + lane] = (int16_t)(int)r;
