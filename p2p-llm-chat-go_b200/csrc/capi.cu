@@ -416,12 +416,25 @@ int b200_gemm(int type, const void* w, int64_t rows, int64_t cols, const float* 
   return 0;
 }
 
-int b200_sample(const float* logits, int vocab, const b200_sampling* s, const int32_t* history, int n_hist, uint64_t step, int32_t* id) {
-  (void)logits; (void)vocab; (void)s; (void)history; (void)n_hist; (void)step; (void)id;
+int b200_sample(const float* logits, int vocab, const b200_sampling* sp, const int32_t* history, int n_hist, uint64_t step, int32_t* id) {
   int rc = have_device();
   if (rc) return rc;
-  set_error("b200_sample: sampler kernel not linked into this build");
-  return B200_ESTATE;
+  if (!logits || !sp || !id || vocab < 1 || vocab > (1 << 18) || n_hist < 0 || (n_hist && !history)) { set_error("bad argument"); return B200_EINVAL; }
+  DevBuf dl, dp, dh, dout;
+  SampleParams p0 = {};
+  p0.temperature = sp->temperature; p0.top_p = sp->top_p; p0.repeat_penalty = sp->repeat_penalty; p0.top_k = sp->top_k;
+  p0.repeat_last_n = sp->repeat_last_n; p0.seed = sp->seed;
+  if ((rc = dl.alloc((size_t)vocab * 4)) || (rc = dp.alloc(sizeof p0)) || (rc = dh.alloc((size_t)n_hist * 4)) || (rc = dout.alloc(4))) return rc;
+  B200_CUDA(cudaMemcpy(dl.p, logits, (size_t)vocab * 4, cudaMemcpyHostToDevice));
+  B200_CUDA(cudaMemcpy(dp.p, &p0, sizeof p0, cudaMemcpyHostToDevice));
+  if (n_hist) B200_CUDA(cudaMemcpy(dh.p, history, (size_t)n_hist * 4, cudaMemcpyHostToDevice));
+  SampleArgs a = {};
+  a.logits = dl.as<float>(); a.vocab = vocab; a.params = dp.as<SampleParams>(); a.history = dh.as<int32_t>(); a.st = nullptr;
+  a.out = dout.as<int32_t>(); a.n_hist = n_hist; a.step = step;
+  B200_CUDA(launch_sample(a, 0, false));
+  B200_CUDA(cudaDeviceSynchronize());
+  B200_CUDA(cudaMemcpy(id, dout.p, 4, cudaMemcpyDeviceToHost));
+  return 0;
 }
 
 int b200_bench_decode(b200_engine* h, int ctx, int n_steps, float* ms_per_step, int* launches_per_step) {

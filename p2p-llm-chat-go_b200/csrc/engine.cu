@@ -197,6 +197,7 @@ int Engine::init(const b200_config& c) {
         (rc = alloc((void**)&rope, (size_t)c.max_ctx * (kHeadDim / 2) * 2 * 4)) ||
         (rc = alloc((void**)&attn_partial, attn_partial_floats(c.n_heads, c.n_kv_heads, n_splits) * 4)) ||
         (rc = alloc((void**)&attn_counters, (size_t)c.n_kv_heads * 4)) || (rc = alloc((void**)&st, sizeof(StepState))) ||
+        (rc = alloc((void**)&sp_dev, sizeof(SampleParams))) ||
         (rc = alloc((void**)&prompt_dev, (size_t)c.max_ctx * 4)))
       return rc;
     B200_CUDA(cudaMemset(attn_counters, 0, (size_t)c.n_kv_heads * 4));
@@ -296,6 +297,23 @@ int Engine::synthesize() {
   return rc;
 }
 
+// lm_head GEMV (logits + argmax), sampler (no-op for greedy requests), finish_step (token hand-over)
+int Engine::enqueue_tail(cudaStream_t s, bool pdl, int* n) {
+  const b200_config& c = cfg;
+  GemvArgs lm = {};
+  lm.W = output; lm.N = c.vocab; lm.K = c.d_model; lm.x = x; lm.norm_w = output_norm; lm.eps = c.rms_eps; lm.y = logits;
+  lm.st = st; lm.store_logits = 1; lm.argmax_key = &st->argmax_key;
+  B200_CUDA(launch_gemv(output_type, PRO_RMSNORM, EPI_LOGITS, lm, s, pdl, sm_count)); ++*n;
+  SampleArgs sa = {};
+  sa.logits = logits; sa.vocab = c.vocab; sa.params = sp_dev; sa.history = prompt_dev; sa.st = st; sa.out = &st->sampled; sa.n_hist = -1;
+  B200_CUDA(launch_sample(sa, s, pdl)); ++*n;
+  FinishArgs f = {};
+  f.st = st; f.prompt = prompt_dev; f.out_tokens = out_tokens_dev; f.host_n_out = host_n_out_dev; f.embd = token_embd;
+  f.embd_type = embd_type; f.d_model = c.d_model; f.x = x; f.max_ctx = c.max_ctx;
+  B200_CUDA(launch_finish_step(f, s, pdl)); ++*n;
+  return 0;
+}
+
 int Engine::enqueue_step(cudaStream_t s) {
   const b200_config& c = cfg;
   const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn;
@@ -326,14 +344,10 @@ int Engine::enqueue_step(cudaStream_t s) {
     dn.W = L.down; dn.N = d; dn.K = ff; dn.x = h; dn.y = x;
     B200_CUDA(launch_gemv(L.down_type, PRO_COPY, EPI_RESID, dn, s, use_pdl, sm_count)); ++n;
   }
-  GemvArgs lm = {};
-  lm.W = output; lm.N = c.vocab; lm.K = d; lm.x = x; lm.norm_w = output_norm; lm.eps = c.rms_eps; lm.y = logits;
-  lm.st = st; lm.store_logits = 1; lm.argmax_key = &st->argmax_key;
-  B200_CUDA(launch_gemv(output_type, PRO_RMSNORM, EPI_LOGITS, lm, s, use_pdl, sm_count)); ++n;
-  FinishArgs f = {};
-  f.st = st; f.prompt = prompt_dev; f.out_tokens = out_tokens_dev; f.host_n_out = host_n_out_dev; f.embd = token_embd;
-  f.embd_type = embd_type; f.d_model = d; f.x = x; f.max_ctx = c.max_ctx;
-  B200_CUDA(launch_finish_step(f, s, use_pdl)); ++n;
+  {
+    int rc = enqueue_tail(s, use_pdl, &n);
+    if (rc) return rc;
+  }
   launches_per_step = n;
   return 0;
 }
@@ -376,7 +390,7 @@ int Engine::launch_steps(int n) {
   return 0;
 }
 
-int Engine::begin_sequence(const int32_t* prompt, int n_prompt, int max_out, int greedy) {
+int Engine::begin_sequence(const int32_t* prompt, int n_prompt, int max_out, int greedy, const b200_sampling* sp) {
   if (n_prompt < 1 || n_prompt > cfg.max_ctx || max_out < 1 || n_prompt + max_out - 1 > cfg.max_ctx) {
     set_error("prompt of %d tokens + %d new tokens does not fit max_ctx %d", n_prompt, max_out, cfg.max_ctx);
     return B200_EINVAL;
@@ -388,7 +402,13 @@ int Engine::begin_sequence(const int32_t* prompt, int n_prompt, int max_out, int
   s0.pos = 0; s0.cur_token = prompt[0]; s0.n_prompt = n_prompt; s0.n_out = 0; s0.max_out = max_out; s0.eos = cfg.eos_token;
   s0.done = 0; s0.greedy = greedy; s0.argmax_key = 0ull;
   B200_CUDA(cudaMemcpyAsync(st, &s0, sizeof s0, cudaMemcpyHostToDevice, stream));
-  B200_CUDA(cudaStreamSynchronize(stream));  // s0 / prompt are stack / caller memory
+  SampleParams sp0 = {};
+  if (sp) {
+    sp0.temperature = sp->temperature; sp0.top_p = sp->top_p; sp0.repeat_penalty = sp->repeat_penalty;
+    sp0.top_k = sp->top_k; sp0.repeat_last_n = sp->repeat_last_n; sp0.seed = sp->seed;
+  }
+  B200_CUDA(cudaMemcpyAsync(sp_dev, &sp0, sizeof sp0, cudaMemcpyHostToDevice, stream));
+  B200_CUDA(cudaStreamSynchronize(stream));  // s0 / sp0 / prompt are stack / caller memory
   *host_n_out = 0;
   B200_CUDA(launch_embed(token_embd, embd_type, cfg.d_model, &st->cur_token, x, stream));
   return 0;
@@ -461,13 +481,13 @@ void Engine::worker_loop() {
       const int n_prompt = (int)r->prompt.size();
       int max_out = r->sp.num_predict > 0 ? r->sp.num_predict : cfg.max_ctx;
       if (n_prompt + max_out - 1 > cfg.max_ctx) max_out = cfg.max_ctx - n_prompt + 1;
-      const int greedy = 1;  // sampler hook: set from r->sp once sample_kernel is in the graph
+      const int greedy = r->sp.temperature <= 0.f ? 1 : 0;
       if (max_out < 1) { rc = B200_EINVAL; set_error("prompt fills the whole context"); }
       if (!rc && r->sp.prefill_mode == B200_MODE_GEMM && n_prompt > 1) rc = ensure_prefill();
       if (!rc) rc = ensure_graph();
       const auto t_load = clk::now();
       auto t_first = t_load;
-      if (!rc) rc = run_prompt(r->prompt.data(), n_prompt, max_out, greedy, r->sp.prefill_mode);
+      if (!rc) rc = run_prompt(r->prompt.data(), n_prompt, max_out, greedy, r->sp.prefill_mode, &r->sp);
       int launched = 1;  // decode steps launched that can produce tokens (the prefill's last step makes #1)
       const int window = 4;
       while (!rc) {
@@ -600,24 +620,19 @@ int Engine::prefill_gemm(int n) {
   }
   // hand the last position over to the batch-1 path: residual stream, then lm_head (mode 0) + token pick
   B200_CUDA(launch_take_row(pf_x, pf_proj, d, n - 1, x, s));
-  GemvArgs lm = {};
-  lm.W = output; lm.N = c.vocab; lm.K = d; lm.x = x; lm.norm_w = output_norm; lm.eps = c.rms_eps; lm.y = logits;
-  lm.st = st; lm.store_logits = 1; lm.argmax_key = &st->argmax_key;
-  B200_CUDA(launch_gemv(output_type, PRO_RMSNORM, EPI_LOGITS, lm, s, false, sm_count));
-  FinishArgs f = {};
-  f.st = st; f.prompt = prompt_dev; f.out_tokens = out_tokens_dev; f.host_n_out = host_n_out_dev; f.embd = token_embd;
-  f.embd_type = embd_type; f.d_model = d; f.x = x; f.max_ctx = c.max_ctx;
-  B200_CUDA(launch_finish_step(f, s, false));
+  int n_tail = 0;
+  int rc = enqueue_tail(s, false, &n_tail);
+  if (rc) return rc;
   return 0;
 }
 
 // Puts the prompt through the model and produces the first generated token.
 // mode GEMM: tensor-core prefill; mode GEMV (or a 1-token prompt): token by token through the decode graph.
-int Engine::run_prompt(const int32_t* prompt, int n_prompt, int max_out, int greedy, int mode) {
+int Engine::run_prompt(const int32_t* prompt, int n_prompt, int max_out, int greedy, int mode, const b200_sampling* sp) {
   int rc;
   if (mode == B200_MODE_GEMM && n_prompt > 1) {
     if ((rc = ensure_prefill())) return rc;
-    if ((rc = begin_sequence(prompt, n_prompt, max_out, greedy))) return rc;
+    if ((rc = begin_sequence(prompt, n_prompt, max_out, greedy, sp))) return rc;
     // the state kernels see "position n-1 is being processed": the token after it is the first generated one
     StepState s0 = {};
     s0.pos = n_prompt - 1; s0.cur_token = prompt[n_prompt - 1]; s0.n_prompt = n_prompt; s0.max_out = max_out; s0.eos = cfg.eos_token;
@@ -626,7 +641,7 @@ int Engine::run_prompt(const int32_t* prompt, int n_prompt, int max_out, int gre
     B200_CUDA(cudaStreamSynchronize(stream));
     return prefill_gemm(n_prompt);
   }
-  if ((rc = begin_sequence(prompt, n_prompt, max_out, greedy))) return rc;
+  if ((rc = begin_sequence(prompt, n_prompt, max_out, greedy, sp))) return rc;
   return launch_steps(n_prompt);
 }
 

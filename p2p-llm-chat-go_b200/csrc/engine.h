@@ -73,6 +73,7 @@ struct Engine {
   unsigned int* attn_counters = nullptr;
   int n_splits = 20;
   StepState* st = nullptr;
+  SampleParams* sp_dev = nullptr;
   int32_t* prompt_dev = nullptr;
   int32_t* block_table = nullptr;  // [max_seqs][pages_per_seq]
   int pages_per_seq = 0;
@@ -110,16 +111,17 @@ struct Engine {
   int synthesize();
   bool all_set() const;
 
+  int enqueue_tail(cudaStream_t s, bool pdl, int* n);  // lm_head + sampler + finish_step
   int enqueue_step(cudaStream_t s);          // launches the kernels of one decode step (capturable)
   int ensure_graph();
   int launch_steps(int n);                   // n graph replays (or direct launches)
-  int begin_sequence(const int32_t* prompt, int n_prompt, int max_out, int greedy);
+  int begin_sequence(const int32_t* prompt, int n_prompt, int max_out, int greedy, const b200_sampling* sp = nullptr);
   int generate_greedy(const int32_t* prompt, int n_prompt, int32_t* ids, int n_new, int prefill_mode, float* ttft_ms,
                       float* decode_ms);
   int forward_logits(const int32_t* ids, int n, int mode, float* logits_host);
   int ensure_prefill();                      // shadow weights + work buffers of the GEMM path
   int prefill_gemm(int n_prompt);            // prompt_dev[0..n) -> KV cache, residual of the last position, first token
-  int run_prompt(const int32_t* prompt, int n_prompt, int max_out, int greedy, int mode);  // either prefill flavour
+  int run_prompt(const int32_t* prompt, int n_prompt, int max_out, int greedy, int mode, const b200_sampling* sp = nullptr);  // either prefill flavour
   void worker_loop();
 };
 

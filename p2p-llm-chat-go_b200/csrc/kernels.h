@@ -86,9 +86,26 @@ cudaError_t launch_attn_decode_noalloc(const float* q, const uint16_t* k_cache, 
                                        cudaStream_t s);
 int attn_noalloc_max_heads();
 
+struct SampleParams {  // device copy of the request's sampling options
+  float temperature, top_p, repeat_penalty;
+  int32_t top_k, repeat_last_n;
+  unsigned long long seed;
+};
+struct SampleArgs {
+  const float* logits;
+  int vocab;
+  const SampleParams* params;
+  const int32_t* history;  // every token of the sequence so far (prompt, then generated)
+  const StepState* st;     // engine mode: n_hist = st->pos+1, step = st->n_out, no-op when st->greedy
+  int32_t* out;
+  int n_hist;              // >= 0: stand-alone mode (test hook) with explicit history length and step
+  unsigned long long step;
+};
+cudaError_t launch_sample(const SampleArgs& a, cudaStream_t s, bool pdl);
+
 struct FinishArgs {
   StepState* st;
-  const int32_t* prompt;     // device [max_ctx]
+  int32_t* prompt;           // device [max_ctx]: the prompt, extended with every generated token (history)
   int32_t* out_tokens;       // device-visible (mapped pinned host) [max_out]
   volatile int32_t* host_n_out;  // mapped pinned host counter
   const uint8_t* embd;       // token_embd in GGUF layout

@@ -194,6 +194,7 @@ __global__ void finish_step_kernel(FinishArgs a) {
       tok = a.prompt[pos + 1];
     } else {
       tok = st->greedy ? (int)argmax_key_index(st->argmax_key) : st->sampled;
+      if (pos + 1 < a.max_ctx) a.prompt[pos + 1] = tok;  // history for the repeat penalty
       if (!st->done) {
         const int n = st->n_out;
         a.out_tokens[n] = tok;
