@@ -30,6 +30,8 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# torchrun exports OMP_NUM_THREADS=1; the CPU legs (oracle) are meant to use every host thread
+os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
 
 N_PROMPT, N_NEW = 512, 128
 METRIC, UNIT = "decode_tok_per_s_llama3.1_8b_bs1", "tok/s"
@@ -269,9 +271,11 @@ def run_ours(args):
         extra["step_roofline"] = {"bound": "hbm", "bytes_per_token": wbytes + kv_bytes, "ms_per_token": step_ms,
                                   "achieved": sach, "peak": hbm, "unit": "GB/s", "frac": sach / hbm,
                                   "ceiling_tok_per_s": hbm * 1e9 / (wbytes + kv_bytes), "launches_per_token": launches}
-        # BASELINE configs[2]: the same model in Ollama's default Q4_K_M mix
+        # BASELINE configs[2]: the same model in Ollama's default Q4_K_M mix (N=1 only, like the CPU baseline)
         eng.close()
         try:
+            if world > 1:
+                raise RuntimeError("measured at N=1 only")
             cfg.weight_format = pkg.WEIGHTS_Q4_K_M
             q = pkg.Engine(cfg)
             for _ in range(2):
@@ -286,6 +290,8 @@ def run_ours(args):
             extra["q4_k_m"] = {"error": str(ex)}
         # CPU baseline: the oracle on this box's host cores, bounded sample of the same workload
         try:
+            if world > 1:
+                raise RuntimeError("measured at N=1 only")
             from oracle import orc
             cores = os.cpu_count() or 1
             m = cpu_weights_8b(orc, cfg)
