@@ -68,7 +68,8 @@ typedef struct b200_config {
   int64_t seed;          /* >=0: synthesise deterministic random-init weights on the device;      */
                          /* <0 : tensors arrive through b200_set_tensor                           */
   int32_t eos_token;     /* generation stops on this id (<0: never)                               */
-  int32_t reserved;
+  int32_t reserved;      /* bit 0: decode every step on the batched tensor-core path, even for a single active   */
+                         /* sequence (makes the numerics of concurrent requests independent of arrival timing)    */
 } b200_config;
 
 /* Sampling options = Ollama's `options` object (the reference sends none, web/streamlit_app.py:91-95, so

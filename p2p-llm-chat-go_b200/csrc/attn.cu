@@ -37,7 +37,8 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnArgs a) {
   pdl_wait();
   pdl_launch_dependents();
   const int qi = blockIdx.z;  // query position within the launch (0 for decode)
-  const int ctx = a.fixed_ctx > 0 ? a.fixed_ctx + qi : a.st->pos + 1;
+  const int ctx = a.q_ctx ? a.q_ctx[qi] : (a.fixed_ctx > 0 ? a.fixed_ctx + qi : a.st->pos + 1);
+  const int32_t* bt = a.q_slot ? a.block_table + (size_t)a.q_slot[qi] * a.pages_per_seq : a.block_table;
   const float scale = 1.0f / sqrtf((float)kHeadDim);
   const float* q_in = a.q + (size_t)qi * a.q_stride;
   float* out = a.out + (size_t)qi * a.q_stride;
@@ -63,7 +64,7 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnArgs a) {
       const int tok = t0 + t;
       uint4 kv = make_uint4(0, 0, 0, 0), vv = make_uint4(0, 0, 0, 0);
       if (tok < ctx) {
-        const int page = a.block_table[tok / kPageTokens];
+        const int page = bt[tok / kPageTokens];
         const size_t row = (((size_t)page * a.n_kv_heads + kvh) * kPageTokens + (tok % kPageTokens)) * kHeadDim;
         kv = *reinterpret_cast<const uint4*>(a.k_cache + row + seg * 8);
         vv = *reinterpret_cast<const uint4*>(a.v_cache + row + seg * 8);

@@ -442,8 +442,12 @@ int b200_bench_decode(b200_engine* h, int ctx, int n_steps, float* ms_per_step, 
   if (!e || ctx < 1 || n_steps < 1 || ctx + n_steps > e->cfg.max_ctx) { set_error("bad argument (ctx + n_steps must fit max_ctx)"); return B200_EINVAL; }
   std::lock_guard<std::mutex> lk(e->mu);
   B200_CUDA(cudaSetDevice(e->cfg.device));
-  int rc = e->ensure_graph();
+  for (auto& q : e->seqs)
+    if (q.r) { set_error("engine is serving requests"); return B200_ESTATE; }
+  e->bs1_owner = -1;
+  int rc = e->set_active_slot(0);
   if (rc) return rc;
+  if ((rc = e->ensure_graph())) return rc;
   // Start from a context of `ctx` tokens already "in" the cache (its contents do not change the bytes moved).
   std::vector<int32_t> p(1, 1);
   if ((rc = e->begin_sequence(p.data(), 1, n_steps + 3, 1))) return rc;

@@ -187,6 +187,9 @@ int Engine::init(const b200_config& c) {
     std::vector<int32_t> bt(n_pages);
     for (size_t i = 0; i < n_pages; ++i) bt[i] = (int32_t)i;
     B200_CUDA(cudaMemcpy(block_table, bt.data(), n_pages * 4, cudaMemcpyHostToDevice));
+    if ((rc = alloc((void**)&active_table, (size_t)pages_per_seq * 4))) return rc;
+    B200_CUDA(cudaMemcpy(active_table, block_table, (size_t)pages_per_seq * 4, cudaMemcpyDeviceToDevice));
+    seqs.resize(c.max_seqs);
   }
   // activations + sequence state
   n_splits = 20;
@@ -323,14 +326,14 @@ int Engine::enqueue_step(cudaStream_t s) {
     GemvArgs a = {};
     a.W = L.qkv; a.N = L.v ? qd + kvd : qd + 2 * kvd; a.K = d; a.x = x; a.norm_w = L.attn_norm; a.eps = c.rms_eps; a.y = q;
     a.row_base = 0; a.q_rows = qd; a.kv_rows = kvd; a.n_kv_heads = c.n_kv_heads; a.rope = rope;
-    a.k_cache = L.k_cache; a.v_cache = L.v_cache; a.block_table = block_table; a.st = st;
+    a.k_cache = L.k_cache; a.v_cache = L.v_cache; a.block_table = active_table; a.st = st;
     B200_CUDA(launch_gemv(L.qkv_type, PRO_RMSNORM, EPI_QKV, a, s, use_pdl, sm_count)); ++n;
     if (L.v) {
       a.W = L.v; a.N = kvd; a.row_base = qd + kvd;
       B200_CUDA(launch_gemv(L.v_type, PRO_RMSNORM, EPI_QKV, a, s, use_pdl, sm_count)); ++n;
     }
     AttnArgs t = {};
-    t.q = q; t.k_cache = L.k_cache; t.v_cache = L.v_cache; t.block_table = block_table; t.st = st;
+    t.q = q; t.k_cache = L.k_cache; t.v_cache = L.v_cache; t.block_table = active_table; t.st = st;
     t.n_heads = c.n_heads; t.n_kv_heads = c.n_kv_heads; t.out = att; t.partial = attn_partial; t.counters = attn_counters;
     t.n_splits = n_splits; t.fixed_ctx = 0;
     B200_CUDA(launch_attn_decode(t, s, use_pdl)); ++n;
@@ -414,10 +417,19 @@ int Engine::begin_sequence(const int32_t* prompt, int n_prompt, int max_out, int
   return 0;
 }
 
+// The synchronous hooks borrow slot 0 and the single-sequence state; they refuse to run under live requests.
+static int claim_slot0(Engine* e) {
+  for (auto& q : e->seqs)
+    if (q.r) { set_error("engine is serving requests; synchronous hooks need an idle engine"); return B200_ESTATE; }
+  e->bs1_owner = -1;
+  return e->set_active_slot(0);
+}
+
 int Engine::generate_greedy(const int32_t* prompt, int n_prompt, int32_t* ids, int n_new, int prefill_mode, float* ttft_ms,
                             float* decode_ms) {
-  int rc = ensure_graph();
+  int rc = claim_slot0(this);
   if (rc) return rc;
+  if ((rc = ensure_graph())) return rc;
   if (prefill_mode == B200_MODE_GEMM && n_prompt > 1 && (rc = ensure_prefill())) return rc;
   cudaEvent_t e0, e1, e2;
   B200_CUDA(cudaEventCreate(&e0));
@@ -446,96 +458,12 @@ int Engine::generate_greedy(const int32_t* prompt, int n_prompt, int32_t* ids, i
 }
 
 int Engine::forward_logits(const int32_t* ids, int n, int mode, float* logits_host) {
-  int rc = run_prompt(ids, n, 1, 1, mode);
+  int rc = claim_slot0(this);
   if (rc) return rc;
+  if ((rc = run_prompt(ids, n, 1, 1, mode))) return rc;
   B200_CUDA(cudaMemcpyAsync(logits_host, logits, (size_t)cfg.vocab * 4, cudaMemcpyDeviceToHost, stream));
   B200_CUDA(cudaStreamSynchronize(stream));
   return 0;
-}
-
-// One request at a time (batch-1 path): prefill, then decode in small launch windows while the host polls
-// the mapped token counter, so the GPU never waits on the host and EOS wastes at most `window` steps.
-void Engine::worker_loop() {
-  cudaSetDevice(cfg.device);
-  for (;;) {
-    Request* r;
-    {
-      std::unique_lock<std::mutex> lk(qmu);
-      qcv.wait(lk, [&] { return stopping || !queue.empty(); });
-      if (stopping) {
-        for (Request* p : queue) {
-          std::lock_guard<std::mutex> l2(p->mu);
-          p->finished = true; p->error = B200_ESTATE; p->cv.notify_all();
-        }
-        queue.clear();
-        return;
-      }
-      r = queue.front();
-      queue.pop_front();
-    }
-    using clk = std::chrono::steady_clock;
-    const auto t0 = clk::now();
-    int rc = 0, delivered = 0, reason = 0;
-    {
-      std::lock_guard<std::mutex> lk(mu);
-      const int n_prompt = (int)r->prompt.size();
-      int max_out = r->sp.num_predict > 0 ? r->sp.num_predict : cfg.max_ctx;
-      if (n_prompt + max_out - 1 > cfg.max_ctx) max_out = cfg.max_ctx - n_prompt + 1;
-      const int greedy = r->sp.temperature <= 0.f ? 1 : 0;
-      if (max_out < 1) { rc = B200_EINVAL; set_error("prompt fills the whole context"); }
-      if (!rc && r->sp.prefill_mode == B200_MODE_GEMM && n_prompt > 1) rc = ensure_prefill();
-      if (!rc) rc = ensure_graph();
-      const auto t_load = clk::now();
-      auto t_first = t_load;
-      if (!rc) rc = run_prompt(r->prompt.data(), n_prompt, max_out, greedy, r->sp.prefill_mode, &r->sp);
-      int launched = 1;  // decode steps launched that can produce tokens (the prefill's last step makes #1)
-      const int window = 4;
-      while (!rc) {
-        bool cancelled;
-        {
-          std::lock_guard<std::mutex> l2(r->mu);
-          cancelled = r->cancelled;
-        }
-        const int avail = *host_n_out;
-        if (avail > delivered) {
-          if (delivered == 0) t_first = clk::now();
-          std::lock_guard<std::mutex> l2(r->mu);
-          for (; delivered < avail; ++delivered) {
-            r->tokens.push_back(out_tokens[delivered]);
-            // the consumer learns "this was the last token" together with the token itself
-            if (out_tokens[delivered] == cfg.eos_token || delivered + 1 >= max_out) r->complete = true;
-          }
-          r->cv.notify_all();
-        }
-        if (cancelled) { reason = 3; break; }
-        if (delivered > 0 && (out_tokens[delivered - 1] == cfg.eos_token)) { reason = 1; break; }
-        if (delivered >= max_out) { reason = 2; break; }
-        if (launched < max_out && launched - delivered < window) {
-          rc = launch_steps(1);
-          ++launched;
-        } else {
-          std::this_thread::sleep_for(std::chrono::microseconds(20));
-        }
-      }
-      cudaStreamSynchronize(stream);
-      const auto t_end = clk::now();
-      auto ns = [](clk::time_point a, clk::time_point b) { return (int64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(b - a).count(); };
-      std::lock_guard<std::mutex> l2(r->mu);
-      r->stats.load_ns = ns(t0, t_load);
-      r->stats.prompt_eval_ns = ns(t_load, t_first);
-      r->stats.eval_ns = ns(t_first, t_end);
-      r->stats.total_ns = ns(t0, t_end);
-      r->stats.prompt_eval_count = n_prompt;
-      r->stats.eval_count = delivered;
-      r->stats.done_reason = rc ? 3 : reason;
-    }
-    {
-      std::lock_guard<std::mutex> l2(r->mu);
-      r->error = rc;
-      r->finished = true;
-      r->cv.notify_all();
-    }
-  }
 }
 
 }  // namespace b200
@@ -547,7 +475,7 @@ namespace b200 {
 int Engine::ensure_prefill() {
   if (pf_ready) return 0;
   const b200_config& c = cfg;
-  const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn, T = c.max_ctx;
+  const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn, T = std::max(c.max_ctx, c.max_seqs);
   if (!gemm_shape_ok(qd + 2 * kvd, d, 1) || !gemm_shape_ok(d, qd, 1) || !gemm_shape_ok(2 * ff, d, 1) || !gemm_shape_ok(d, ff, 1)) {
     set_error("model dims not supported by the tensor-core path (rows %%128, K %%64)");
     return B200_EINVAL;
@@ -596,20 +524,26 @@ int Engine::ensure_prefill() {
   return 0;
 }
 
-int Engine::prefill_gemm(int n) {
+// The layer stack on the tensor cores over n rows.  pos_arr == nullptr: rows are positions 0..n-1 of the
+// sequence whose block table is `active_table` (prefill).  Otherwise row t is position pos_arr[t] of the
+// sequence in slot slot_arr[t], which then sees ctx_arr[t] tokens (batched decode).
+// Leaves the residual stream of every row in pf_x (+ pf_proj still to be added).
+int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_arr, const int32_t* ctx_arr, const int32_t* slot_arr) {
   const b200_config& c = cfg;
   const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn;
   cudaStream_t s = stream;
-  B200_CUDA(launch_embed_tokens(token_embd, embd_type, d, prompt_dev, n, pf_x, s));
+  const int32_t* table = pos_arr ? block_table : active_table;
+  B200_CUDA(launch_embed_tokens(token_embd, embd_type, d, tokens_dev, n, pf_x, s));
   for (int l = 0; l < c.n_layers; ++l) {
     Layer& L = layers[l];
     B200_CUDA(launch_add_rmsnorm_bf16(pf_x, l ? pf_proj : nullptr, L.attn_norm, pf_xb, n, d, c.rms_eps, s));
     B200_CUDA(launch_gemm_bf16(L.qkv16, qd + 2 * kvd, d, pf_xb, n, pf_qkv, qd + 2 * kvd, s));
-    B200_CUDA(launch_rope_kv(pf_qkv, pf_q, L.k_cache, L.v_cache, block_table, rope, n, qd, kvd, c.n_kv_heads, 0, s));
+    B200_CUDA(launch_rope_kv(pf_qkv, pf_q, L.k_cache, L.v_cache, table, rope, n, qd, kvd, c.n_kv_heads, 0, pos_arr, slot_arr, pages_per_seq, s));
     AttnArgs t = {};
-    t.q = pf_q; t.k_cache = L.k_cache; t.v_cache = L.v_cache; t.block_table = block_table; t.st = nullptr;
+    t.q = pf_q; t.k_cache = L.k_cache; t.v_cache = L.v_cache; t.block_table = table; t.st = nullptr;
     t.n_heads = c.n_heads; t.n_kv_heads = c.n_kv_heads; t.out = pf_att; t.partial = pf_partial; t.counters = pf_counters;
     t.n_splits = pf_splits; t.fixed_ctx = 1; t.n_queries = n; t.q_stride = qd;
+    t.q_ctx = ctx_arr; t.q_slot = slot_arr; t.pages_per_seq = pages_per_seq;
     B200_CUDA(launch_attn_decode(t, s, false));
     B200_CUDA(launch_f32_to_bf16(pf_att, pf_xb, (int64_t)n * qd, s));
     B200_CUDA(launch_gemm_bf16(L.o16, d, qd, pf_xb, n, pf_proj, d, s));
@@ -618,6 +552,15 @@ int Engine::prefill_gemm(int n) {
     B200_CUDA(launch_swiglu_bf16(pf_gu, pf_xb, (int64_t)n * ff, s));
     B200_CUDA(launch_gemm_bf16(L.down16, d, ff, pf_xb, n, pf_proj, d, s));
   }
+  return 0;
+}
+
+int Engine::prefill_gemm(int n) {
+  const b200_config& c = cfg;
+  const int d = c.d_model;
+  cudaStream_t s = stream;
+  int rc0 = forward_gemm(n, prompt_dev, nullptr, nullptr, nullptr);
+  if (rc0) return rc0;
   // hand the last position over to the batch-1 path: residual stream, then lm_head (mode 0) + token pick
   B200_CUDA(launch_take_row(pf_x, pf_proj, d, n - 1, x, s));
   int n_tail = 0;

@@ -3,6 +3,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <chrono>
 #include <condition_variable>
 #include <deque>
 #include <map>
@@ -90,6 +91,26 @@ struct Engine {
   unsigned int* pf_counters = nullptr;
   int pf_splits = 4;
 
+  // sequence slots (continuous batching): slot s statically owns block-table row s
+  struct Seq {
+    Request* r = nullptr;
+    int n_prompt = 0, pos = 0, delivered = 0, max_out = 0;  // pos = position of `token` (not yet in the cache)
+    int32_t token = 0;
+    bool greedy = true;
+    std::chrono::steady_clock::time_point t0, t_load, t_first;
+  };
+  std::vector<Seq> seqs;
+  int32_t* active_table = nullptr;  // block-table row used by the batch-1 graph and single-sequence prefill
+  int bs1_owner = -1;               // slot whose state currently lives in StepState / prompt_dev
+  bool force_batched = false;       // cfg.reserved bit 0: never use the batch-1 path for decode (tests)
+  bool batched_ready = false;
+  int32_t *b_tok = nullptr, *b_pos = nullptr, *b_ctx = nullptr, *b_slot = nullptr, *b_next = nullptr;  // device [max_seqs]
+  int32_t* b_next_host = nullptr;   // pinned
+  int32_t* hist_dev = nullptr;      // [max_seqs][max_ctx] token history per slot
+  SampleParams* sp_arr = nullptr;   // [max_seqs]
+  float* b_logits = nullptr;        // [max_seqs][vocab]
+  uint16_t* output16 = nullptr;     // bf16 lm_head operand of the tensor-core path
+
   cudaGraphExec_t step_graph = nullptr;
   bool use_pdl = true, use_graph = true;
   int launches_per_step = 0;
@@ -121,6 +142,15 @@ struct Engine {
   int forward_logits(const int32_t* ids, int n, int mode, float* logits_host);
   int ensure_prefill();                      // shadow weights + work buffers of the GEMM path
   int prefill_gemm(int n_prompt);            // prompt_dev[0..n) -> KV cache, residual of the last position, first token
+  // the tensor-core layer stack over n rows: one sequence at positions 0..n-1 (arrays null) or one row per sequence
+  int forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_arr, const int32_t* ctx_arr, const int32_t* slot_arr);
+  int set_active_slot(int slot);
+  int ensure_batched();
+  int batched_step(const std::vector<int>& slots, std::vector<int32_t>* next);
+  int admit(Request* r, int slot);           // prefill a new request into a slot, deliver its first token
+  int decode_bs1_window(int slot);           // batch-1 graph steps for the only active sequence
+  void finish_request(int slot, int rc, int reason);
+  void deliver(int slot, const int32_t* toks, int n);
   int run_prompt(const int32_t* prompt, int n_prompt, int max_out, int greedy, int mode, const b200_sampling* sp = nullptr);  // either prefill flavour
   void worker_loop();
 };

@@ -77,6 +77,10 @@ struct AttnArgs {
   // q_stride floats, scratch by one query's worth.  n_queries <= 1: the single-query decode case.
   int n_queries;
   int q_stride;
+  // batched decode: query z belongs to the sequence in slot q_slot[z] (block-table row) and sees q_ctx[z] tokens
+  const int32_t* q_ctx;
+  const int32_t* q_slot;
+  int pages_per_seq;
 };
 cudaError_t launch_attn_decode(const AttnArgs& a, cudaStream_t s, bool pdl);
 size_t attn_partial_floats(int n_heads, int n_kv_heads, int n_splits);
@@ -140,7 +144,11 @@ bool gemm_shape_ok(int64_t rows, int64_t K, int64_t n_tokens);
 cudaError_t launch_embed_tokens(const uint8_t* embd, int embd_type, int d_model, const int32_t* tokens_dev, int n, float* x, cudaStream_t s);
 cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, const float* w, uint16_t* xb, int tokens, int d, float eps, cudaStream_t s);
 cudaError_t launch_rope_kv(const float* qkv, float* q, uint16_t* k_cache, uint16_t* v_cache, const int32_t* block_table, const float* rope,
-                           int tokens, int q_rows, int kv_rows, int n_kv_heads, int pos0, cudaStream_t s);
+                           int tokens, int q_rows, int kv_rows, int n_kv_heads, int pos0, const int32_t* pos_arr, const int32_t* slot_arr,
+                           int pages_per_seq, cudaStream_t s);
+cudaError_t launch_argmax_rows(const float* logits, int rows, int vocab, int32_t* next, cudaStream_t s);
+cudaError_t launch_append_history(const int32_t* next, const int32_t* slot_arr, const int32_t* pos_arr, int32_t* history, int max_ctx, int rows,
+                                  cudaStream_t s);
 cudaError_t launch_swiglu_bf16(const float* gu, uint16_t* h, int64_t n_pairs, cudaStream_t s);
 cudaError_t launch_take_row(const float* x, const float* add, int d, int row, float* out, cudaStream_t s);
 

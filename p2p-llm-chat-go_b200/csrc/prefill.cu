@@ -50,12 +50,16 @@ __global__ void add_rmsnorm_bf16_kernel(float* x, const float* add, const float*
 }
 
 // qkv[t][q_rows + 2 kv_rows] fp32 -> q[t][q_rows] (rotated), K/V appended to the paged bf16 cache at pos0+t
+// Row t is position pos0+t of one sequence (prefill), or — batched decode — position pos_arr[t] of the
+// sequence in slot slot_arr[t], whose block table is row slot_arr[t] of `block_table` (pages_per_seq wide).
 __global__ void rope_kv_kernel(const float* qkv, float* q, uint16_t* k_cache, uint16_t* v_cache, const int32_t* block_table,
-                               const float* rope, int q_rows, int kv_rows, int n_kv_heads, int pos0) {
-  const int t = blockIdx.x, pos = pos0 + t;
+                               const float* rope, int q_rows, int kv_rows, int n_kv_heads, int pos0, const int32_t* pos_arr,
+                               const int32_t* slot_arr, int pages_per_seq) {
+  const int t = blockIdx.x, pos = pos_arr ? pos_arr[t] : pos0 + t;
   const int width = q_rows + 2 * kv_rows;
   const float* in = qkv + (size_t)t * width;
-  const int page = block_table[pos / kPageTokens];
+  const int32_t* bt = slot_arr ? block_table + (size_t)slot_arr[t] * pages_per_seq : block_table;
+  const int page = bt[pos / kPageTokens];
   for (int p = threadIdx.x; p < width / 2; p += blockDim.x) {
     const int row = 2 * p;
     float x0 = in[row], x1 = in[row + 1];
@@ -94,7 +98,44 @@ __global__ void take_row_kernel(const float* x, const float* add, int d, int row
     out[k] = x[(size_t)row * d + k] + add[(size_t)row * d + k];
 }
 
+// next[row] = argmax of logits[row][:] (lowest id on ties); one CTA per row
+__global__ void argmax_rows_kernel(const float* logits, int vocab, int32_t* next) {
+  __shared__ unsigned long long red[32];
+  const float* lg = logits + (size_t)blockIdx.x * vocab;
+  unsigned long long best = 0;
+  for (int i = threadIdx.x; i < vocab; i += blockDim.x) {
+    const unsigned long long k = argmax_key(lg[i], (uint32_t)i);
+    best = k > best ? k : best;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+    best = other > best ? other : best;
+  }
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = best;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < (int)(blockDim.x >> 5); ++w) best = red[w] > best ? red[w] : best;
+    next[blockIdx.x] = (int32_t)argmax_key_index(best);
+  }
+}
+
+// history[slot][pos+1] = next token of every row (the repeat penalty of sampled requests reads it)
+__global__ void append_history_kernel(const int32_t* next, const int32_t* slot_arr, const int32_t* pos_arr, int32_t* history, int max_ctx, int rows) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < rows && pos_arr[r] + 1 < max_ctx) history[(size_t)slot_arr[r] * max_ctx + pos_arr[r] + 1] = next[r];
+}
+
 }  // namespace
+
+cudaError_t launch_argmax_rows(const float* logits, int rows, int vocab, int32_t* next, cudaStream_t s) {
+  argmax_rows_kernel<<<rows, 1024, 0, s>>>(logits, vocab, next);
+  return cudaGetLastError();
+}
+cudaError_t launch_append_history(const int32_t* next, const int32_t* slot_arr, const int32_t* pos_arr, int32_t* history, int max_ctx, int rows,
+                                  cudaStream_t s) {
+  append_history_kernel<<<(rows + 255) / 256, 256, 0, s>>>(next, slot_arr, pos_arr, history, max_ctx, rows);
+  return cudaGetLastError();
+}
 
 cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, const float* w, uint16_t* xb, int tokens, int d, float eps, cudaStream_t s) {
   if (d % 4) return cudaErrorInvalidValue;
@@ -102,8 +143,10 @@ cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, const float* w, 
   return cudaGetLastError();
 }
 cudaError_t launch_rope_kv(const float* qkv, float* q, uint16_t* k_cache, uint16_t* v_cache, const int32_t* block_table, const float* rope,
-                           int tokens, int q_rows, int kv_rows, int n_kv_heads, int pos0, cudaStream_t s) {
-  rope_kv_kernel<<<tokens, 256, 0, s>>>(qkv, q, k_cache, v_cache, block_table, rope, q_rows, kv_rows, n_kv_heads, pos0);
+                           int tokens, int q_rows, int kv_rows, int n_kv_heads, int pos0, const int32_t* pos_arr, const int32_t* slot_arr,
+                           int pages_per_seq, cudaStream_t s) {
+  rope_kv_kernel<<<tokens, 256, 0, s>>>(qkv, q, k_cache, v_cache, block_table, rope, q_rows, kv_rows, n_kv_heads, pos0, pos_arr, slot_arr,
+                                        pages_per_seq);
   return cudaGetLastError();
 }
 cudaError_t launch_swiglu_bf16(const float* gu, uint16_t* h, int64_t n_pairs, cudaStream_t s) {

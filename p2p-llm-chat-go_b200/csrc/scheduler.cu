@@ -1,0 +1,321 @@
+// scheduler.cu — the request worker: continuous batching over sequence slots.
+//
+// Every peer's suggestion is an independent request (web/streamlit_app.py:163-165), so the unit of
+// scheduling is a sequence slot (its own run of KV pages).  One worker thread per engine owns the stream:
+//   admit    : a waiting request gets a free slot, its prompt goes through the tensor-core prefill (or the
+//              token-by-token GEMV path if it asked for it) and its first token is delivered;
+//   decode   : exactly one active sequence and nobody waiting -> the batch-1 CUDA-graph path (GEMV kernels,
+//              numerics mode 0); otherwise ONE batched step for all active sequences on the tensor cores
+//              (weights stream once per step for the whole batch; numerics mode 1), then new arrivals are
+//              admitted before the next step (iteration-level scheduling);
+//   finish   : EOS / length / cancel frees the slot at once.
+// A sequence moves between the two decode paths without copying anything: both use the same paged KV cache;
+// only the small per-sequence state (position, last token, history) is handed over.
+#include <algorithm>
+#include <cstring>
+
+#include "engine.h"
+
+namespace b200 {
+
+static int64_t ns_between(std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+  return (int64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(b - a).count();
+}
+
+int Engine::set_active_slot(int slot) {
+  B200_CUDA(cudaMemcpyAsync(active_table, block_table + (size_t)slot * pages_per_seq, (size_t)pages_per_seq * 4, cudaMemcpyDeviceToDevice, stream));
+  return 0;
+}
+
+int Engine::ensure_batched() {
+  if (batched_ready) return 0;
+  int rc = ensure_prefill();
+  if (rc) return rc;
+  const b200_config& c = cfg;
+  const size_t S = (size_t)c.max_seqs;
+  if (!gemm_shape_ok(c.vocab, c.d_model, 1)) { set_error("vocab must be a multiple of 128 for the batched lm_head"); return B200_EINVAL; }
+  if ((rc = alloc((void**)&b_tok, S * 4)) || (rc = alloc((void**)&b_pos, S * 4)) || (rc = alloc((void**)&b_ctx, S * 4)) ||
+      (rc = alloc((void**)&b_slot, S * 4)) || (rc = alloc((void**)&b_next, S * 4)) || (rc = alloc((void**)&hist_dev, S * c.max_ctx * 4)) ||
+      (rc = alloc((void**)&sp_arr, S * sizeof(SampleParams))) || (rc = alloc((void**)&b_logits, S * (size_t)c.vocab * 4)))
+    return rc;
+  B200_CUDA(cudaHostAlloc((void**)&b_next_host, S * 4, cudaHostAllocDefault));
+  if (c.weight_format == B200_WEIGHTS_Q4_K_M) {  // bf16 shadow of the Q6_K lm_head
+    const Slot& s = slots["output.weight"];
+    const size_t bytes = (size_t)s.rows * gemv_row_bytes(s.type, s.cols);
+    uint8_t* tmp = nullptr;
+    B200_CUDA(cudaMalloc((void**)&tmp, bytes));
+    if ((rc = alloc((void**)&output16, (size_t)s.rows * s.cols * 2)) || (rc = fetch_tensor(s, tmp))) { cudaFree(tmp); return rc; }
+    cudaError_t e = launch_dequant(s.type, tmp, s.rows * s.cols / QK_K, nullptr, output16, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    cudaFree(tmp);
+    if (e != cudaSuccess) return cuda_fail(e, "lm_head shadow");
+  } else {
+    output16 = (uint16_t*)output;
+  }
+  batched_ready = true;
+  return 0;
+}
+
+// One decode step for the sequences in `slots` (one row each): token seqs[s].token at position seqs[s].pos.
+int Engine::batched_step(const std::vector<int>& sl, std::vector<int32_t>* next) {
+  const b200_config& c = cfg;
+  const int B = (int)sl.size();
+  std::vector<int32_t> tok(B), pos(B), ctx(B), slot(B);
+  for (int i = 0; i < B; ++i) {
+    const Seq& q = seqs[sl[i]];
+    tok[i] = q.token; pos[i] = q.pos; ctx[i] = q.pos + 1; slot[i] = sl[i];
+  }
+  B200_CUDA(cudaMemcpyAsync(b_tok, tok.data(), (size_t)B * 4, cudaMemcpyHostToDevice, stream));
+  B200_CUDA(cudaMemcpyAsync(b_pos, pos.data(), (size_t)B * 4, cudaMemcpyHostToDevice, stream));
+  B200_CUDA(cudaMemcpyAsync(b_ctx, ctx.data(), (size_t)B * 4, cudaMemcpyHostToDevice, stream));
+  B200_CUDA(cudaMemcpyAsync(b_slot, slot.data(), (size_t)B * 4, cudaMemcpyHostToDevice, stream));
+  int rc = forward_gemm(B, b_tok, b_pos, b_ctx, b_slot);
+  if (rc) return rc;
+  B200_CUDA(launch_add_rmsnorm_bf16(pf_x, pf_proj, output_norm, pf_xb, B, c.d_model, c.rms_eps, stream));
+  B200_CUDA(launch_gemm_bf16(output16, c.vocab, c.d_model, pf_xb, B, b_logits, c.vocab, stream));
+  B200_CUDA(launch_argmax_rows(b_logits, B, c.vocab, b_next, stream));
+  for (int i = 0; i < B; ++i) {  // sampled requests: the sampler kernel on that row, writing over the argmax
+    const Seq& q = seqs[sl[i]];
+    if (q.greedy) continue;
+    SampleArgs sa = {};
+    sa.logits = b_logits + (size_t)i * c.vocab; sa.vocab = c.vocab; sa.params = sp_arr + sl[i];
+    sa.history = hist_dev + (size_t)sl[i] * c.max_ctx; sa.st = nullptr; sa.out = b_next + i; sa.n_hist = q.pos + 1;
+    sa.step = (unsigned long long)q.delivered;
+    B200_CUDA(launch_sample(sa, stream, false));
+  }
+  B200_CUDA(launch_append_history(b_next, b_slot, b_pos, hist_dev, c.max_ctx, B, stream));
+  B200_CUDA(cudaMemcpyAsync(b_next_host, b_next, (size_t)B * 4, cudaMemcpyDeviceToHost, stream));
+  B200_CUDA(cudaStreamSynchronize(stream));
+  next->assign(b_next_host, b_next_host + B);
+  return 0;
+}
+
+void Engine::deliver(int slot, const int32_t* toks, int n) {
+  Seq& q = seqs[slot];
+  Request* r = q.r;
+  if (q.delivered == 0 && n > 0) q.t_first = std::chrono::steady_clock::now();
+  std::lock_guard<std::mutex> lk(r->mu);
+  for (int i = 0; i < n; ++i) {
+    r->tokens.push_back(toks[i]);
+    ++q.delivered;
+    if (toks[i] == cfg.eos_token || q.delivered >= q.max_out) r->complete = true;
+  }
+  r->cv.notify_all();
+}
+
+void Engine::finish_request(int slot, int rc, int reason) {
+  Seq& q = seqs[slot];
+  Request* r = q.r;
+  const auto t_end = std::chrono::steady_clock::now();
+  {
+    std::lock_guard<std::mutex> lk(r->mu);
+    r->stats.load_ns = ns_between(q.t0, q.t_load);
+    r->stats.prompt_eval_ns = ns_between(q.t_load, q.delivered ? q.t_first : t_end);
+    r->stats.eval_ns = q.delivered ? ns_between(q.t_first, t_end) : 0;
+    r->stats.total_ns = ns_between(q.t0, t_end);
+    r->stats.prompt_eval_count = q.n_prompt;
+    r->stats.eval_count = q.delivered;
+    r->stats.done_reason = rc ? 3 : reason;
+    r->error = rc;
+    r->finished = true;
+    r->cv.notify_all();
+  }
+  q.r = nullptr;
+  if (bs1_owner == slot) bs1_owner = -1;
+}
+
+// Prefill a new request into `slot` and deliver its first token.  Uses the single-sequence state
+// (StepState / prompt_dev / active_table), which afterwards describes this sequence (bs1_owner = slot).
+int Engine::admit(Request* r, int slot) {
+  Seq& q = seqs[slot];
+  q = Seq();
+  q.r = r;
+  q.t0 = std::chrono::steady_clock::now();
+  q.n_prompt = (int)r->prompt.size();
+  int max_out = r->sp.num_predict > 0 ? r->sp.num_predict : cfg.max_ctx;
+  if (q.n_prompt + max_out - 1 > cfg.max_ctx) max_out = cfg.max_ctx - q.n_prompt + 1;
+  q.max_out = max_out;
+  q.greedy = r->sp.temperature <= 0.f;
+  if (max_out < 1) { set_error("prompt fills the whole context"); return B200_EINVAL; }
+  int rc;
+  const bool gemm = r->sp.prefill_mode == B200_MODE_GEMM && q.n_prompt > 1;
+  if (gemm && (rc = ensure_prefill())) return rc;
+  if ((rc = ensure_graph())) return rc;
+  if (cfg.max_seqs > 1 && (rc = ensure_batched())) return rc;
+  if ((rc = set_active_slot(slot))) return rc;
+  q.t_load = std::chrono::steady_clock::now();
+  if ((rc = run_prompt(r->prompt.data(), q.n_prompt, max_out, q.greedy ? 1 : 0, r->sp.prefill_mode, &r->sp))) return rc;
+  bs1_owner = slot;
+  if (batched_ready) {  // per-slot history and sampling options for the batched path
+    SampleParams sp0 = {};
+    sp0.temperature = r->sp.temperature; sp0.top_p = r->sp.top_p; sp0.repeat_penalty = r->sp.repeat_penalty;
+    sp0.top_k = r->sp.top_k; sp0.repeat_last_n = r->sp.repeat_last_n; sp0.seed = r->sp.seed;
+    B200_CUDA(cudaMemcpyAsync(sp_arr + slot, &sp0, sizeof sp0, cudaMemcpyHostToDevice, stream));
+  }
+  B200_CUDA(cudaStreamSynchronize(stream));
+  if (*host_n_out < 1) { set_error("prefill produced no token"); return B200_ECUDA; }
+  const int32_t first = out_tokens[0];
+  if (batched_ready)  // prompt + first token -> this slot's history row (prompt_dev holds exactly that now)
+    B200_CUDA(cudaMemcpyAsync(hist_dev + (size_t)slot * cfg.max_ctx, prompt_dev, (size_t)std::min(q.n_prompt + 1, cfg.max_ctx) * 4,
+                              cudaMemcpyDeviceToDevice, stream));
+  q.token = first;
+  q.pos = q.n_prompt;
+  deliver(slot, &first, 1);
+  return 0;
+}
+
+// The only active sequence decodes on the batch-1 graph.  Returns when it finishes, is cancelled, or another
+// request shows up (the caller then carries on with batched steps).
+int Engine::decode_bs1_window(int slot) {
+  Seq& q = seqs[slot];
+  int rc = 0;
+  if (bs1_owner != slot) {  // hand the sequence over to the single-sequence state
+    if ((rc = set_active_slot(slot))) return rc;
+    StepState s0 = {};
+    s0.pos = q.pos; s0.cur_token = q.token; s0.n_prompt = std::min(q.n_prompt, q.pos); s0.n_out = q.delivered; s0.max_out = q.max_out;
+    s0.eos = cfg.eos_token; s0.greedy = q.greedy ? 1 : 0;
+    B200_CUDA(cudaMemcpyAsync(st, &s0, sizeof s0, cudaMemcpyHostToDevice, stream));
+    B200_CUDA(cudaMemcpyAsync(prompt_dev, hist_dev + (size_t)slot * cfg.max_ctx, (size_t)cfg.max_ctx * 4, cudaMemcpyDeviceToDevice, stream));
+    SampleParams sp0 = {};
+    sp0.temperature = q.r->sp.temperature; sp0.top_p = q.r->sp.top_p; sp0.repeat_penalty = q.r->sp.repeat_penalty;
+    sp0.top_k = q.r->sp.top_k; sp0.repeat_last_n = q.r->sp.repeat_last_n; sp0.seed = q.r->sp.seed;
+    B200_CUDA(cudaMemcpyAsync(sp_dev, &sp0, sizeof sp0, cudaMemcpyHostToDevice, stream));
+    B200_CUDA(cudaStreamSynchronize(stream));
+    *host_n_out = q.delivered;
+    B200_CUDA(launch_embed(token_embd, embd_type, cfg.d_model, &st->cur_token, x, stream));
+    bs1_owner = slot;
+  }
+  int launched = q.delivered;  // token-producing steps issued so far (== tokens that will exist)
+  const int window = 4;
+  bool interrupted = false;
+  for (;;) {
+    bool cancelled;
+    {
+      std::lock_guard<std::mutex> lk(q.r->mu);
+      cancelled = q.r->cancelled;
+    }
+    const int avail = *host_n_out;
+    if (avail > q.delivered) {
+      const int n = avail - q.delivered, from = q.delivered;
+      deliver(slot, out_tokens + from, n);
+      q.token = out_tokens[avail - 1];
+      q.pos = q.n_prompt + avail - 1;
+    }
+    int reason = 0;
+    if (cancelled) reason = 3;
+    else if (q.delivered > 0 && q.token == cfg.eos_token) reason = 1;
+    else if (q.delivered >= q.max_out) reason = 2;
+    if (reason) {
+      cudaStreamSynchronize(stream);
+      finish_request(slot, 0, reason);
+      return 0;
+    }
+    if (!interrupted) {
+      std::lock_guard<std::mutex> lk(qmu);
+      interrupted = !queue.empty() || stopping;
+    }
+    if (interrupted) {  // drain what is in flight, then let the scheduler batch
+      if (launched == q.delivered) {
+        // history of this slot for the batched path = what the finish kernel kept in prompt_dev
+        if (batched_ready)
+          B200_CUDA(cudaMemcpyAsync(hist_dev + (size_t)slot * cfg.max_ctx, prompt_dev, (size_t)cfg.max_ctx * 4, cudaMemcpyDeviceToDevice, stream));
+        B200_CUDA(cudaStreamSynchronize(stream));
+        return 0;
+      }
+      std::this_thread::sleep_for(std::chrono::microseconds(20));
+      continue;
+    }
+    if (launched < q.max_out && launched - q.delivered < window) {
+      if ((rc = launch_steps(1))) return rc;
+      ++launched;
+    } else {
+      std::this_thread::sleep_for(std::chrono::microseconds(20));
+    }
+  }
+}
+
+void Engine::worker_loop() {
+  cudaSetDevice(cfg.device);
+  force_batched = (cfg.reserved & 1) != 0;
+  for (;;) {
+    // ---- wait for work
+    std::vector<int> active;
+    for (int s = 0; s < (int)seqs.size(); ++s)
+      if (seqs[s].r) active.push_back(s);
+    {
+      std::unique_lock<std::mutex> lk(qmu);
+      if (active.empty()) qcv.wait(lk, [&] { return stopping || !queue.empty(); });
+      if (stopping) {
+        for (Request* p : queue) {
+          std::lock_guard<std::mutex> l2(p->mu);
+          p->finished = true; p->error = B200_ESTATE; p->cv.notify_all();
+        }
+        queue.clear();
+        lk.unlock();
+        for (int s : active) finish_request(s, B200_ESTATE, 3);
+        return;
+      }
+    }
+    std::lock_guard<std::mutex> dev(mu);
+    // ---- admit waiting requests into free slots
+    for (int s = 0; s < (int)seqs.size(); ++s) {
+      if (seqs[s].r) continue;
+      Request* r = nullptr;
+      {
+        std::lock_guard<std::mutex> lk(qmu);
+        if (queue.empty()) break;
+        r = queue.front();
+        queue.pop_front();
+      }
+      const int rc = admit(r, s);
+      if (rc) { if (!seqs[s].r) seqs[s].r = r; finish_request(s, rc, 3); continue; }
+      Seq& q = seqs[s];
+      if (q.token == cfg.eos_token) finish_request(s, 0, 1);
+      else if (q.delivered >= q.max_out) finish_request(s, 0, 2);
+    }
+    active.clear();
+    for (int s = 0; s < (int)seqs.size(); ++s)
+      if (seqs[s].r) active.push_back(s);
+    if (active.empty()) continue;
+    // ---- decode
+    bool waiting;
+    {
+      std::lock_guard<std::mutex> lk(qmu);
+      waiting = !queue.empty();
+    }
+    if (active.size() == 1 && !waiting && !force_batched) {
+      const int rc = decode_bs1_window(active[0]);
+      if (rc && seqs[active[0]].r) finish_request(active[0], rc, 3);
+      continue;
+    }
+    // cancelled sequences leave before the step
+    for (size_t i = 0; i < active.size();) {
+      bool c;
+      {
+        std::lock_guard<std::mutex> lk(seqs[active[i]].r->mu);
+        c = seqs[active[i]].r->cancelled;
+      }
+      if (c) { finish_request(active[i], 0, 3); active.erase(active.begin() + i); }
+      else ++i;
+    }
+    if (active.empty()) continue;
+    std::vector<int32_t> next;
+    int rc = ensure_batched();
+    if (!rc) {
+      if (bs1_owner >= 0) bs1_owner = -1;  // the single-sequence state goes stale once a batched step runs
+      rc = batched_step(active, &next);
+    }
+    for (size_t i = 0; i < active.size(); ++i) {
+      const int s = active[i];
+      if (rc) { finish_request(s, rc, 3); continue; }
+      Seq& q = seqs[s];
+      q.pos += 1;
+      q.token = next[i];
+      deliver(s, &next[i], 1);
+      if (q.token == cfg.eos_token) finish_request(s, 0, 1);
+      else if (q.delivered >= q.max_out) finish_request(s, 0, 2);
+    }
+  }
+}
+
+}  // namespace b200

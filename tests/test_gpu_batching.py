@@ -1,0 +1,115 @@
+"""Continuous batching: several peers' requests decode together on the tensor-core path (numerics mode 1);
+token ids must equal the CPU oracle's for every sequence, whatever the others in the batch are doing."""
+import threading
+
+import numpy as np
+import pytest
+
+import __graft_entry__ as ge
+from oracle import orc
+from tests.util import engine_and_oracle
+
+pytestmark = pytest.mark.gpu
+TOL = 3e-3  # same logit tolerance as the prefill tests (bf16 GEMM inputs)
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    p = ge.load_package()
+    p.lib()
+    assert p.device_count() >= 1
+    return p
+
+
+def oracle_batched_greedy(ora, prompt, n_new):
+    """Prefill in GEMM numerics (first token from the mode-0 lm_head), then every decode step in GEMM numerics."""
+    ora.reset()
+    lg = ora.forward(prompt, mode=1)
+    out, margins = [], []
+    for _ in range(n_new):
+        tok, m = orc.argmax(lg)
+        out.append(tok)
+        margins.append(m)
+        lg = ora.forward([tok], mode=1, all_logits=True)[0]
+    return out, min(margins)
+
+
+def decisive_prompts(ora, cfg, lengths, n_new):
+    prompts, wants = [], []
+    seed = 100
+    for n in lengths:
+        while True:
+            seed += 1
+            p = np.random.default_rng(seed).integers(0, cfg.vocab, n).astype(np.int32)
+            w, m = oracle_batched_greedy(ora, p, n_new)
+            if m > 4 * TOL:
+                break
+        prompts.append(p)
+        wants.append(w)
+    return prompts, wants
+
+
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_batched_decode_matches_oracle(pkg, fmt):
+    eng, ora, cfg = engine_and_oracle(pkg, fmt, n_layers=2, seed=71, source="synth", max_ctx=128)
+    eng.close()
+    cfg.max_seqs, cfg.reserved, cfg.seed = 8, 1, 71          # reserved bit 0: always decode on the batched path
+    n_new = 12
+    prompts, wants = decisive_prompts(ora, cfg, [3, 17, 40, 9, 64, 5, 23, 31, 12, 2], n_new)
+    with pkg.Engine(cfg) as eng:
+        sp = pkg.default_sampling()
+        sp.temperature, sp.num_predict, sp.prefill_mode = 0.0, n_new, pkg.MODE_GEMM
+        reqs = [eng.submit(p, sp) for p in prompts]       # 10 requests on 8 slots: two wait for a free slot
+        got = [list(r.tokens()) for r in reqs]
+        stats = [r.stats() for r in reqs]
+        [r.free() for r in reqs]
+        for i, (g, w) in enumerate(zip(got, wants)):
+            assert g == w, (i, g, w)
+        assert all(s.eval_count == n_new and s.done_reason == 2 and s.prompt_eval_count == len(p) for s, p in zip(stats, prompts))
+
+
+def test_mixed_traffic_completes_and_single_request_uses_fast_path(pkg):
+    eng, ora, cfg = engine_and_oracle(pkg, 0, n_layers=2, seed=72, source="synth", max_ctx=128)
+    eng.close()
+    cfg.max_seqs, cfg.seed = 4, 72
+    with pkg.Engine(cfg) as eng:
+        sp = pkg.default_sampling()
+        sp.temperature, sp.num_predict, sp.prefill_mode = 0.0, 20, pkg.MODE_GEMV
+        # a lone request decodes on the batch-1 path: exact mode-0 parity
+        p0 = np.random.default_rng(1).integers(0, cfg.vocab, 11).astype(np.int32)
+        r = eng.submit(p0, sp)
+        got = list(r.tokens())
+        r.free()
+        want, _ = ora.generate_greedy(p0, 20, prefill_mode=0)
+        assert got == want.tolist()
+        # bursts from several threads, some cancelled, some sampled: everything terminates with the right counts
+        results = {}
+
+        def peer(i):
+            s = pkg.default_sampling()
+            s.num_predict, s.seed, s.prefill_mode = 5 + i, i, pkg.MODE_GEMM
+            s.temperature = 0.0 if i % 2 else 0.8
+            rq = eng.submit(np.random.default_rng(i).integers(0, cfg.vocab, 4 + 3 * i).astype(np.int32), s)
+            if i == 3:
+                rq.cancel()
+            toks = []
+            try:
+                for t in rq.tokens():
+                    toks.append(t)
+            except pkg.B200Error:
+                pass
+            results[i] = (toks, rq.stats().done_reason)
+            rq.free()
+        ts = [threading.Thread(target=peer, args=(i,)) for i in range(9)]
+        [t.start() for t in ts]
+        [t.join(timeout=120) for t in ts]
+        assert len(results) == 9
+        for i, (toks, reason) in results.items():
+            if i == 3:
+                assert reason in (2, 3)
+            else:
+                assert len(toks) == 5 + i and reason == 2, (i, toks, reason)
+        # and afterwards the engine still serves a lone request exactly
+        r = eng.submit(p0, sp)
+        assert list(r.tokens()) == want.tolist()
+        r.free()
