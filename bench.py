@@ -210,6 +210,26 @@ def aggregate_tok_per_s(world, steps, n_new, max_decode_ms):
     return world * steps * (n_new - 1) / (max_decode_ms / 1e3)
 
 
+def run_peers(eng, pkg, cfg, n_peers, n_prompt, n_new):
+    """BASELINE configs[3]: n_peers UI sessions click 'Suggest a reply' at once (closed loop, one request each);
+    continuous batching inside one engine.  Returns aggregate tok/s and server-side TTFT percentiles."""
+    sp = pkg.default_sampling()
+    sp.temperature, sp.num_predict, sp.prefill_mode = 0.0, n_new, pkg.MODE_GEMM
+    prompts = [synthetic_prompt(cfg.vocab, n_prompt, seed=100 + i) for i in range(n_peers)]
+    t0 = time.perf_counter()
+    reqs = [eng.submit(p, sp) for p in prompts]
+    n_tok = 0
+    for r in reqs:
+        n_tok += sum(1 for _ in r.tokens())
+    wall = time.perf_counter() - t0
+    ttft = sorted((r.stats().load_ns + r.stats().prompt_eval_ns) / 1e6 for r in reqs)
+    totals = sorted(r.stats().total_ns / 1e6 for r in reqs)
+    [r.free() for r in reqs]
+    return {"peers": n_peers, "n_prompt": n_prompt, "n_new": n_new, "aggregate_tok_per_s": n_tok / wall, "wall_s": wall,
+            "ttft_ms_p50_in_engine": ttft[len(ttft) // 2], "ttft_ms_p99_in_engine": ttft[min(len(ttft) - 1, int(0.99 * len(ttft)))],
+            "request_ms_p50": totals[len(totals) // 2], "note": "TTFT counted from admission into a slot; queueing before it is in request_ms"}
+
+
 def run_ours(args):
     import torch
     import __graft_entry__ as ge
@@ -288,6 +308,17 @@ def run_ours(args):
             q.close()
         except Exception as ex:  # reported, never silently dropped
             extra["q4_k_m"] = {"error": str(ex)}
+        # BASELINE configs[3]: 256 concurrent peers, continuous batching, one engine (N=1 only)
+        try:
+            if world > 1 or os.environ.get("B200_BENCH_FAST"):
+                raise RuntimeError("measured at N=1 only")
+            cfg.weight_format, cfg.max_seqs, cfg.max_ctx = pkg.WEIGHTS_BF16, 256, N_PROMPT + N_NEW
+            with pkg.Engine(cfg) as pe:
+                run_peers(pe, pkg, cfg, 8, N_PROMPT, 8)   # warm-up: graph capture, shadow buffers
+                extra["peers256"] = run_peers(pe, pkg, cfg, 256, N_PROMPT, N_NEW)
+            cfg.max_seqs, cfg.max_ctx = 1, 1024
+        except Exception as ex:
+            extra["peers256"] = {"error": str(ex)}
         # CPU baseline: the oracle on this box's host cores, bounded sample of the same workload
         try:
             if world > 1:

@@ -257,9 +257,12 @@ void Engine::worker_loop() {
       }
     }
     std::lock_guard<std::mutex> dev(mu);
-    // ---- admit waiting requests into free slots
-    for (int s = 0; s < (int)seqs.size(); ++s) {
+    // ---- admit waiting requests into free slots; while sequences are decoding, at most a few prefills per
+    // iteration so that running requests keep producing tokens (bounded inter-token stall)
+    int budget = active.empty() ? (int)seqs.size() : 4;
+    for (int s = 0; s < (int)seqs.size() && budget > 0; ++s) {
       if (seqs[s].r) continue;
+      --budget;
       Request* r = nullptr;
       {
         std::lock_guard<std::mutex> lk(qmu);
