@@ -104,6 +104,14 @@ B200_API void b200_llama31_70b(b200_config* cfg);               /* shapes of Lla
 
 /* ---- engine life cycle (replaces: Ollama model load, README.md:62-70) ------------------------------- */
 B200_API int b200_init(const b200_config* cfg, b200_engine** out);
+/* Tensor parallelism (BASELINE config 5: Llama-3.1-70B over 8xB200).  One process/thread per GPU calls
+ * b200_init_tp with the same full-model cfg, its rank, the degree, and the 128-byte NCCL id that rank 0 got
+ * from b200_tp_unique_id (the host distributes it: torch.distributed, a file, ...).  Weights are sharded
+ * column-/row-/vocab-parallel; o and down end in an NCCL all-reduce over NVLink.  Every rank must then issue
+ * the same calls in the same order (SPMD): b200_set_tensor (full tensors; each rank keeps its window),
+ * b200_forward_logits, b200_generate_greedy, b200_bench_decode.  bf16 weights, greedy decoding, max_seqs 1. */
+B200_API int b200_tp_unique_id(void* id128);
+B200_API int b200_init_tp(const b200_config* cfg, int tp_rank, int tp_size, const void* id128, b200_engine** out);
 B200_API void b200_shutdown(b200_engine* e);
 B200_API int b200_get_config(const b200_engine* e, b200_config* out);
 

@@ -75,6 +75,8 @@ def lib():
         "b200_llama31_8b": (None, [cfgp]),
         "b200_llama31_70b": (None, [cfgp]),
         "b200_init": (i32, [cfgp, C.POINTER(vp)]),
+        "b200_tp_unique_id": (i32, [vp]),
+        "b200_init_tp": (i32, [cfgp, i32, i32, vp, C.POINTER(vp)]),
         "b200_shutdown": (None, [vp]),
         "b200_get_config": (i32, [vp, cfgp]),
         "b200_set_tensor": (i32, [vp, C.c_char_p, i32, vp, i64, i64]),
@@ -240,10 +242,21 @@ class Request:
             pass
 
 
+def tp_unique_id():
+    """128-byte NCCL id (rank 0 creates it; the host hands it to every rank)."""
+    buf = C.create_string_buffer(128)
+    _check(lib().b200_tp_unique_id(buf))
+    return buf.raw
+
+
 class Engine:
-    def __init__(self, cfg):
+    def __init__(self, cfg, tp_rank=0, tp_size=1, nccl_id=None):
         h = C.c_void_p()
-        _check(lib().b200_init(C.byref(cfg), C.byref(h)))
+        if tp_size > 1:
+            idbuf = C.create_string_buffer(nccl_id, 128)
+            _check(lib().b200_init_tp(C.byref(cfg), tp_rank, tp_size, idbuf, C.byref(h)))
+        else:
+            _check(lib().b200_init(C.byref(cfg), C.byref(h)))
         self.h, self.cfg = h, cfg
 
     def close(self):

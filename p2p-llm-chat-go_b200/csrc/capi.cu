@@ -6,6 +6,7 @@
 #include "engine.h"
 
 namespace b200 {
+int tp_unique_id(void* out128);
 const char* last_error();
 int tokenizer_encode(const b200_config& cfg, const char* utf8, size_t n, int add_bos, int32_t* ids, size_t cap, size_t* n_out);
 int tokenizer_decode(const b200_config& cfg, const int32_t* ids, size_t n, char* buf, size_t cap, size_t* n_out);
@@ -124,6 +125,24 @@ int b200_init(const b200_config* cfg, b200_engine** out) {
   return 0;
 }
 
+int b200_tp_unique_id(void* id128) {
+  if (!id128) { set_error("null argument"); return B200_EINVAL; }
+  return tp_unique_id(id128);
+}
+
+int b200_init_tp(const b200_config* cfg, int tp_rank, int tp_size, const void* id128, b200_engine** out) {
+  if (!cfg || !out) { set_error("null argument"); return B200_EINVAL; }
+  *out = nullptr;
+  Engine* e = new (std::nothrow) Engine();
+  if (!e) return B200_ENOMEM;
+  e->tp_rank = tp_rank;
+  e->tp_size = tp_size;
+  int rc = e->init(*cfg, id128);
+  if (rc) { delete e; return rc; }
+  *out = reinterpret_cast<b200_engine*>(e);
+  return 0;
+}
+
 void b200_shutdown(b200_engine* h) { delete reinterpret_cast<Engine*>(h); }
 
 int b200_get_config(const b200_engine* h, b200_config* out) {
@@ -139,13 +158,14 @@ int b200_set_tensor(b200_engine* h, const char* name, int type, const void* data
   auto it = e->slots.find(name);
   if (it == e->slots.end()) { set_error("unknown tensor '%s'", name); return B200_EINVAL; }
   Slot& s = it->second;
-  if (s.type != type || s.rows * s.cols != rows * cols || (s.rows != 1 && (s.rows != rows || s.cols != cols))) {
-    set_error("tensor '%s' expects type %d shape %lldx%lld, got type %d shape %lldx%lld", name, s.type, (long long)s.rows,
-              (long long)s.cols, type, (long long)rows, (long long)cols);
+  if (s.type != type || s.full_rows * s.full_cols != rows * cols || (s.full_rows != 1 && (s.full_rows != rows || s.full_cols != cols))) {
+    set_error("tensor '%s' expects type %d shape %lldx%lld, got type %d shape %lldx%lld", name, s.type, (long long)s.full_rows,
+              (long long)s.full_cols, type, (long long)rows, (long long)cols);
     return B200_EINVAL;
   }
   B200_CUDA(cudaSetDevice(e->cfg.device));
-  const size_t bytes = (size_t)s.rows * (s.type == T_F32 ? (size_t)s.cols * 4 : gemv_row_bytes(s.type, s.cols));
+  // the caller always passes the FULL tensor; a tensor-parallel rank keeps its window of it
+  const size_t bytes = (size_t)s.full_rows * (s.type == T_F32 ? (size_t)s.full_cols * 4 : gemv_row_bytes(s.type, s.full_cols));
   DevBuf tmp;
   int rc = tmp.alloc(bytes);
   if (rc) return rc;
@@ -163,9 +183,9 @@ int b200_tensor_info(const b200_engine* h, const char* name, int* type, int64_t*
   if (it == e->slots.end()) { set_error("unknown tensor '%s'", name); return B200_EINVAL; }
   const Slot& s = it->second;
   if (type) *type = s.type;
-  if (rows) *rows = s.rows;
-  if (cols) *cols = s.cols;
-  if (nbytes) *nbytes = (int64_t)s.rows * (int64_t)(s.type == T_F32 ? (size_t)s.cols * 4 : gemv_row_bytes(s.type, s.cols));
+  if (rows) *rows = s.full_rows;
+  if (cols) *cols = s.full_cols;
+  if (nbytes) *nbytes = (int64_t)s.full_rows * (int64_t)(s.type == T_F32 ? (size_t)s.full_cols * 4 : gemv_row_bytes(s.type, s.full_cols));
   return 0;
 }
 
@@ -177,6 +197,7 @@ int b200_get_tensor(b200_engine* h, const char* name, void* buf, int64_t cap) {
   if (it == e->slots.end()) { set_error("unknown tensor '%s'", name); return B200_EINVAL; }
   const Slot& s = it->second;
   if (!s.set) { set_error("tensor '%s' has not been set", name); return B200_ESTATE; }
+  if (s.full_rows != s.rows || s.full_cols != s.cols) { set_error("b200_get_tensor: '%s' is sharded across tensor-parallel ranks", name); return B200_ESTATE; }
   const size_t bytes = (size_t)s.rows * (s.type == T_F32 ? (size_t)s.cols * 4 : gemv_row_bytes(s.type, s.cols));
   if ((int64_t)bytes > cap) { set_error("buffer too small: need %zu bytes", bytes); return B200_ERANGE; }
   B200_CUDA(cudaSetDevice(e->cfg.device));
@@ -477,7 +498,7 @@ int b200_bench_kernel(b200_engine* h, const char* which, int iters, float* ms, i
   if (!e || !which || iters < 1) { set_error("bad argument"); return B200_EINVAL; }
   std::lock_guard<std::mutex> lk(e->mu);
   B200_CUDA(cudaSetDevice(e->cfg.device));
-  const b200_config& c = e->cfg;
+  const b200_config& c = e->lc;
   const int d = c.d_model, qd = c.n_heads * kHeadDim, ff = c.d_ffn;
   Layer& L = e->layers[0];
   GemvArgs a = {};

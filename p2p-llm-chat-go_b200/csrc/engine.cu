@@ -12,6 +12,8 @@
 
 namespace b200 {
 
+void tp_destroy(void* comm);
+
 static thread_local char g_err[512] = "";
 void set_error(const char* fmt, ...) {
   va_list ap;
@@ -44,6 +46,7 @@ Engine::~Engine() {
   if (worker.joinable()) worker.join();
   if (stream) cudaStreamSynchronize(stream);
   if (step_graph) cudaGraphExecDestroy(step_graph);
+  tp_destroy(nccl_comm);
   for (void* p : allocs) cudaFree(p);
   if (out_tokens) cudaFreeHost(out_tokens);
   if (host_n_out) cudaFreeHost((void*)host_n_out);
@@ -58,7 +61,7 @@ int Engine::alloc(void** p, size_t bytes) {
   return 0;
 }
 
-int Engine::init(const b200_config& c) {
+int Engine::init(const b200_config& c, const void* nccl_id) {
   cfg = c;
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -82,7 +85,17 @@ int Engine::init(const b200_config& c) {
   use_pdl = getenv("B200_NO_PDL") == nullptr;
   use_graph = getenv("B200_NO_GRAPH") == nullptr;
 
-  const int d = c.d_model, qd = c.n_heads * c.head_dim, kvd = c.n_kv_heads * c.head_dim, ff = c.d_ffn;
+  const int tp = tp_size, R = tp_rank;
+  if (tp < 1 || R < 0 || R >= tp || c.n_heads % tp || c.n_kv_heads % tp || c.d_ffn % tp || c.vocab % tp ||
+      (tp > 1 && (c.weight_format != B200_WEIGHTS_BF16 || c.max_seqs != 1))) {
+    set_error("tensor parallel degree %d unsupported for this config (heads, kv heads, d_ffn, vocab must divide; bf16, max_seqs 1)", tp);
+    return B200_EINVAL;
+  }
+  lc = c;
+  lc.n_heads /= tp; lc.n_kv_heads /= tp; lc.d_ffn /= tp; lc.vocab /= tp;
+  // local (per-rank) sizes; upper-case = the full model
+  const int d = c.d_model, qd = lc.n_heads * c.head_dim, kvd = lc.n_kv_heads * c.head_dim, ff = lc.d_ffn, voc = lc.vocab;
+  const int QD = c.n_heads * c.head_dim, KVD = c.n_kv_heads * c.head_dim, FF = c.d_ffn, VOC = c.vocab;
   if (c.head_dim != kHeadDim || c.n_layers <= 0 || c.n_kv_heads <= 0 || c.n_heads % c.n_kv_heads ||
       c.max_ctx <= 0 || c.vocab <= 0 || c.max_seqs < 1) {
     set_error("unsupported config (head_dim must be 128, n_heads %% n_kv_heads == 0, sizes > 0)");
@@ -100,6 +113,11 @@ int Engine::init(const b200_config& c) {
   }
   const int tmat = q4 ? T_Q4_K : T_BF16, tbig = q4 ? T_Q6_K : T_BF16;
   B200_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  if (tp_size > 1) {
+    if (!nccl_id) { set_error("tensor parallelism needs the NCCL unique id of rank 0"); return B200_EINVAL; }
+    int rc = tp_init(nccl_id);
+    if (rc) return rc;
+  }
 
   auto need = [&](int type, int64_t N, int64_t K, const char* what) -> int {
     if (!gemv_shape_ok(type, N, K, 0)) {
@@ -110,9 +128,11 @@ int Engine::init(const b200_config& c) {
     return 0;
   };
   auto add_slot = [&](const std::string& name, int type, int64_t rows, int64_t cols, uint8_t* base, int64_t row0,
-                      int64_t step) {
+                      int64_t step, int64_t full_rows = -1, int64_t full_cols = -1, int64_t src_row0 = 0, int64_t src_col0 = 0) {
     Slot s;
     s.type = type; s.rows = rows; s.cols = cols; s.base = base; s.row0 = row0; s.row_step = step;
+    s.full_rows = full_rows < 0 ? rows : full_rows; s.full_cols = full_cols < 0 ? cols : full_cols;
+    s.src_row0 = src_row0; s.src_col0 = src_col0;
     slots[name] = s;
   };
 
@@ -131,25 +151,25 @@ int Engine::init(const b200_config& c) {
     const size_t rb = gemv_row_bytes(tmat, d);
     if (tv == tmat) {
       if ((rc = alloc((void**)&L.qkv, (size_t)(qd + 2 * kvd) * rb))) return rc;
-      add_slot(p + "attn_v.weight", tv, kvd, d, L.qkv, qd + kvd, 1);
+      add_slot(p + "attn_v.weight", tv, kvd, d, L.qkv, qd + kvd, 1, KVD, d, (int64_t)R * kvd, 0);
     } else {
       if ((rc = alloc((void**)&L.qkv, (size_t)(qd + kvd) * rb))) return rc;
       if ((rc = alloc((void**)&L.v, (size_t)kvd * gemv_row_bytes(tv, d)))) return rc;
       L.v_type = tv;
-      add_slot(p + "attn_v.weight", tv, kvd, d, L.v, 0, 1);
+      add_slot(p + "attn_v.weight", tv, kvd, d, L.v, 0, 1, KVD, d, (int64_t)R * kvd, 0);
     }
-    add_slot(p + "attn_q.weight", tmat, qd, d, L.qkv, 0, 1);
-    add_slot(p + "attn_k.weight", tmat, kvd, d, L.qkv, qd, 1);
+    add_slot(p + "attn_q.weight", tmat, qd, d, L.qkv, 0, 1, QD, d, (int64_t)R * qd, 0);
+    add_slot(p + "attn_k.weight", tmat, kvd, d, L.qkv, qd, 1, KVD, d, (int64_t)R * kvd, 0);
     L.o_type = tmat;
     if ((rc = alloc((void**)&L.o, (size_t)d * gemv_row_bytes(tmat, qd)))) return rc;
-    add_slot(p + "attn_output.weight", tmat, d, qd, L.o, 0, 1);
+    add_slot(p + "attn_output.weight", tmat, d, qd, L.o, 0, 1, d, QD, 0, (int64_t)R * qd);
     L.gu_type = tmat;
     if ((rc = alloc((void**)&L.gate_up, (size_t)2 * ff * rb))) return rc;
-    add_slot(p + "ffn_gate.weight", tmat, ff, d, L.gate_up, 0, 2);
-    add_slot(p + "ffn_up.weight", tmat, ff, d, L.gate_up, 1, 2);
+    add_slot(p + "ffn_gate.weight", tmat, ff, d, L.gate_up, 0, 2, FF, d, (int64_t)R * ff, 0);
+    add_slot(p + "ffn_up.weight", tmat, ff, d, L.gate_up, 1, 2, FF, d, (int64_t)R * ff, 0);
     L.down_type = tdown;
     if ((rc = alloc((void**)&L.down, (size_t)d * gemv_row_bytes(tdown, ff)))) return rc;
-    add_slot(p + "ffn_down.weight", tdown, d, ff, L.down, 0, 1);
+    add_slot(p + "ffn_down.weight", tdown, d, ff, L.down, 0, 1, d, FF, 0, (int64_t)R * ff);
     if ((rc = alloc((void**)&L.attn_norm, (size_t)d * 4)) || (rc = alloc((void**)&L.ffn_norm, (size_t)d * 4))) return rc;
     add_slot(p + "attn_norm.weight", T_F32, 1, d, (uint8_t*)L.attn_norm, 0, 1);
     add_slot(p + "ffn_norm.weight", T_F32, 1, d, (uint8_t*)L.ffn_norm, 0, 1);
@@ -160,21 +180,21 @@ int Engine::init(const b200_config& c) {
     int rc;
     embd_type = tmat;
     if (tmat == T_Q4_K && d % QK_K) { set_error("d_model must be a multiple of 256 for Q4_K embeddings"); return B200_EINVAL; }
-    if ((rc = need(tbig, c.vocab, d, "output"))) return rc;
+    if ((rc = need(tbig, voc, d, "output"))) return rc;
     if ((rc = alloc((void**)&token_embd, (size_t)c.vocab * tensor_row_bytes(tmat, d)))) return rc;
     add_slot("token_embd.weight", tmat, c.vocab, d, token_embd, 0, 1);
     output_type = tbig;
-    if ((rc = alloc((void**)&output, (size_t)c.vocab * gemv_row_bytes(tbig, d)))) return rc;
-    add_slot("output.weight", tbig, c.vocab, d, output, 0, 1);
+    if ((rc = alloc((void**)&output, (size_t)voc * gemv_row_bytes(tbig, d)))) return rc;
+    add_slot("output.weight", tbig, voc, d, output, 0, 1, VOC, d, (int64_t)R * voc, 0);
     if ((rc = alloc((void**)&output_norm, (size_t)d * 4))) return rc;
     add_slot("output_norm.weight", T_F32, 1, d, (uint8_t*)output_norm, 0, 1);
-    weight_bytes += (int64_t)c.vocab * gemv_row_bytes(tbig, d) + (int64_t)d * 4;
+    weight_bytes += (int64_t)voc * gemv_row_bytes(tbig, d) + (int64_t)d * 4;
   }
 
   // paged KV pool: page = 16 tokens of one kv head; static ownership (sequence slot s owns a page run)
   pages_per_seq = (c.max_ctx + kPageTokens - 1) / kPageTokens;
   const size_t n_pages = (size_t)pages_per_seq * c.max_seqs;
-  const size_t layer_kv = n_pages * c.n_kv_heads * kPageTokens * kHeadDim * 2;
+  const size_t layer_kv = n_pages * lc.n_kv_heads * kPageTokens * kHeadDim * 2;
   for (auto& L : layers) {
     int rc;
     if ((rc = alloc((void**)&L.k_cache, layer_kv)) || (rc = alloc((void**)&L.v_cache, layer_kv))) return rc;
@@ -198,12 +218,13 @@ int Engine::init(const b200_config& c) {
     if ((rc = alloc((void**)&x, (size_t)d * 4)) || (rc = alloc((void**)&q, (size_t)qd * 4)) || (rc = alloc((void**)&att, (size_t)qd * 4)) ||
         (rc = alloc((void**)&h, (size_t)ff * 4)) || (rc = alloc((void**)&logits, (size_t)c.vocab * 4)) ||
         (rc = alloc((void**)&rope, (size_t)c.max_ctx * (kHeadDim / 2) * 2 * 4)) ||
-        (rc = alloc((void**)&attn_partial, attn_partial_floats(c.n_heads, c.n_kv_heads, n_splits) * 4)) ||
-        (rc = alloc((void**)&attn_counters, (size_t)c.n_kv_heads * 4)) || (rc = alloc((void**)&st, sizeof(StepState))) ||
+        (rc = alloc((void**)&attn_partial, attn_partial_floats(lc.n_heads, lc.n_kv_heads, n_splits) * 4)) ||
+        (rc = alloc((void**)&tp_partial, (size_t)d * 4)) ||
+        (rc = alloc((void**)&attn_counters, (size_t)lc.n_kv_heads * 4)) || (rc = alloc((void**)&st, sizeof(StepState))) ||
         (rc = alloc((void**)&sp_dev, sizeof(SampleParams))) ||
         (rc = alloc((void**)&prompt_dev, (size_t)c.max_ctx * 4)))
       return rc;
-    B200_CUDA(cudaMemset(attn_counters, 0, (size_t)c.n_kv_heads * 4));
+    B200_CUDA(cudaMemset(attn_counters, 0, (size_t)lc.n_kv_heads * 4));
     B200_CUDA(cudaMemset(st, 0, sizeof(StepState)));
   }
   B200_CUDA(cudaHostAlloc((void**)&out_tokens, (size_t)c.max_ctx * 4, cudaHostAllocMapped));
@@ -246,17 +267,22 @@ int Engine::init(const b200_config& c) {
   return 0;
 }
 
+// `src` holds the FULL tensor in GGUF layout; the slot takes its window of it (the whole tensor unless TP).
 int Engine::place_tensor(const Slot& s, const uint8_t* src) {
-  const size_t rb = tensor_row_bytes(s.type, s.cols);
+  const size_t rb = tensor_row_bytes(s.type, s.cols), full_rb = tensor_row_bytes(s.type, s.full_cols);
   uint8_t* dst = s.base + (size_t)s.row0 * rb;
+  const bool window = s.full_rows != s.rows || s.full_cols != s.cols;
+  if (window && s.type != T_BF16 && s.type != T_F32) { set_error("tensor-parallel windows need bf16 / f32 tensors"); return B200_EINVAL; }
+  const uint8_t* from = src + (size_t)s.src_row0 * full_rb + tensor_row_bytes(s.type, s.src_col0);
   if (s.type == T_Q6_K && s.base != token_embd) {
-    B200_CUDA(launch_q6k_repack(src, dst, s.rows, s.cols / QK_K, 1, stream));
+    B200_CUDA(launch_q6k_repack(from, dst, s.rows, s.cols / QK_K, 1, stream));
   } else {
-    B200_CUDA(cudaMemcpy2DAsync(dst, (size_t)s.row_step * rb, src, rb, rb, (size_t)s.rows, cudaMemcpyDeviceToDevice, stream));
+    B200_CUDA(cudaMemcpy2DAsync(dst, (size_t)s.row_step * rb, from, full_rb, rb, (size_t)s.rows, cudaMemcpyDeviceToDevice, stream));
   }
   return 0;
 }
 
+// The slot's (local) tensor back in GGUF layout, rows x cols.
 int Engine::fetch_tensor(const Slot& s, uint8_t* dst) {
   const size_t rb = tensor_row_bytes(s.type, s.cols);
   const uint8_t* src = s.base + (size_t)s.row0 * rb;
@@ -276,7 +302,7 @@ bool Engine::all_set() const {
 
 int Engine::synthesize() {
   size_t maxb = 0;
-  for (auto& kv : slots) maxb = std::max(maxb, (size_t)kv.second.rows * tensor_row_bytes(kv.second.type, kv.second.cols));
+  for (auto& kv : slots) maxb = std::max(maxb, (size_t)kv.second.full_rows * tensor_row_bytes(kv.second.type, kv.second.full_cols));
   uint8_t* tmp = nullptr;
   B200_CUDA(cudaMalloc((void**)&tmp, maxb));
   uint32_t tid = 0;
@@ -286,10 +312,10 @@ int Engine::synthesize() {
     // std 1/sqrt(fan_in); the two projections that write into the residual stream are scaled by
     // 1/sqrt(2*n_layers) (GPT-2 / Megatron random-init convention), which keeps a deep random network from
     // amplifying rounding differences chaotically layer after layer
-    float sigma = kv.first == "token_embd.weight" ? 1.0f : 1.0f / sqrtf((float)s.cols);
+    float sigma = kv.first == "token_embd.weight" ? 1.0f : 1.0f / sqrtf((float)s.full_cols);
     if (kv.first.find("attn_output") != std::string::npos || kv.first.find("ffn_down") != std::string::npos)
       sigma /= sqrtf(2.0f * (float)cfg.n_layers);
-    cudaError_t e = launch_synth(s.type, tmp, s.rows, s.cols, (uint64_t)cfg.seed, tid++, sigma, stream);
+    cudaError_t e = launch_synth(s.type, tmp, s.full_rows, s.full_cols, (uint64_t)cfg.seed, tid++, sigma, stream);
     if (e != cudaSuccess) { rc = cuda_fail(e, "synth"); break; }
     if ((rc = place_tensor(s, tmp))) break;
     s.set = true;
@@ -302,14 +328,21 @@ int Engine::synthesize() {
 
 // lm_head GEMV (logits + argmax), sampler (no-op for greedy requests), finish_step (token hand-over)
 int Engine::enqueue_tail(cudaStream_t s, bool pdl, int* n) {
-  const b200_config& c = cfg;
+  const b200_config& c = lc;
   GemvArgs lm = {};
-  lm.W = output; lm.N = c.vocab; lm.K = c.d_model; lm.x = x; lm.norm_w = output_norm; lm.eps = c.rms_eps; lm.y = logits;
+  lm.W = output; lm.N = c.vocab; lm.K = c.d_model; lm.x = x; lm.norm_w = output_norm; lm.eps = c.rms_eps;
+  lm.y = logits + (size_t)tp_rank * c.vocab;  // vocab-parallel: this rank's slice of the logits
+  lm.row_base = tp_rank * c.vocab;             // global token id of row 0 (argmax key)
   lm.st = st; lm.store_logits = 1; lm.argmax_key = &st->argmax_key;
   B200_CUDA(launch_gemv(output_type, PRO_RMSNORM, EPI_LOGITS, lm, s, pdl, sm_count)); ++*n;
+  if (tp_size > 1) {  // global argmax = max over ranks of the packed (logit, ~id) keys
+    int rc = tp_allreduce_max_u64(&st->argmax_key, s);
+    if (rc) return rc;
+    ++*n;
+  }
   SampleArgs sa = {};
-  sa.logits = logits; sa.vocab = c.vocab; sa.params = sp_dev; sa.history = prompt_dev; sa.st = st; sa.out = &st->sampled; sa.n_hist = -1;
-  B200_CUDA(launch_sample(sa, s, pdl)); ++*n;
+  sa.logits = logits; sa.vocab = cfg.vocab; sa.params = sp_dev; sa.history = prompt_dev; sa.st = st; sa.out = &st->sampled; sa.n_hist = -1;
+  B200_CUDA(launch_sample(sa, s, pdl && tp_size == 1)); ++*n;
   FinishArgs f = {};
   f.st = st; f.prompt = prompt_dev; f.out_tokens = out_tokens_dev; f.host_n_out = host_n_out_dev; f.embd = token_embd;
   f.embd_type = embd_type; f.d_model = c.d_model; f.x = x; f.max_ctx = c.max_ctx;
@@ -318,8 +351,9 @@ int Engine::enqueue_tail(cudaStream_t s, bool pdl, int* n) {
 }
 
 int Engine::enqueue_step(cudaStream_t s) {
-  const b200_config& c = cfg;
+  const b200_config& c = lc;  // per-rank shapes (== cfg without tensor parallelism)
   const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn;
+  const bool tp = tp_size > 1;
   int n = 0;
   for (int l = 0; l < c.n_layers; ++l) {
     Layer& L = layers[l];
@@ -337,15 +371,27 @@ int Engine::enqueue_step(cudaStream_t s) {
     t.n_heads = c.n_heads; t.n_kv_heads = c.n_kv_heads; t.out = att; t.partial = attn_partial; t.counters = attn_counters;
     t.n_splits = n_splits; t.fixed_ctx = 0;
     B200_CUDA(launch_attn_decode(t, s, use_pdl)); ++n;
+    // row-parallel projections: without TP the residual add is the GEMV epilogue; with TP every rank holds a
+    // K-slice, so the partial products are summed over NVLink (NCCL all-reduce) before they join the stream
     GemvArgs o = {};
-    o.W = L.o; o.N = d; o.K = qd; o.x = att; o.y = x;
-    B200_CUDA(launch_gemv(L.o_type, PRO_COPY, EPI_RESID, o, s, use_pdl, sm_count)); ++n;
+    o.W = L.o; o.N = d; o.K = qd; o.x = att; o.y = tp ? tp_partial : x;
+    B200_CUDA(launch_gemv(L.o_type, PRO_COPY, tp ? EPI_STORE : EPI_RESID, o, s, use_pdl, sm_count)); ++n;
+    if (tp) {
+      int rc = tp_allreduce_sum(tp_partial, (size_t)d, s);
+      if (rc) return rc;
+      B200_CUDA(launch_add_inplace(x, tp_partial, d, s)); n += 2;
+    }
     GemvArgs g = {};
     g.W = L.gate_up; g.N = 2 * ff; g.K = d; g.x = x; g.norm_w = L.ffn_norm; g.eps = c.rms_eps; g.y = h;
-    B200_CUDA(launch_gemv(L.gu_type, PRO_RMSNORM, EPI_SWIGLU, g, s, use_pdl, sm_count)); ++n;
+    B200_CUDA(launch_gemv(L.gu_type, PRO_RMSNORM, EPI_SWIGLU, g, s, use_pdl && !tp, sm_count)); ++n;
     GemvArgs dn = {};
-    dn.W = L.down; dn.N = d; dn.K = ff; dn.x = h; dn.y = x;
-    B200_CUDA(launch_gemv(L.down_type, PRO_COPY, EPI_RESID, dn, s, use_pdl, sm_count)); ++n;
+    dn.W = L.down; dn.N = d; dn.K = ff; dn.x = h; dn.y = tp ? tp_partial : x;
+    B200_CUDA(launch_gemv(L.down_type, PRO_COPY, tp ? EPI_STORE : EPI_RESID, dn, s, use_pdl, sm_count)); ++n;
+    if (tp) {
+      int rc = tp_allreduce_sum(tp_partial, (size_t)d, s);
+      if (rc) return rc;
+      B200_CUDA(launch_add_inplace(x, tp_partial, d, s)); n += 2;
+    }
   }
   {
     int rc = enqueue_tail(s, use_pdl, &n);
@@ -461,6 +507,10 @@ int Engine::forward_logits(const int32_t* ids, int n, int mode, float* logits_ho
   int rc = claim_slot0(this);
   if (rc) return rc;
   if ((rc = run_prompt(ids, n, 1, 1, mode))) return rc;
+  if (tp_size > 1) {  // every rank holds its vocab slice in place; exchange the slices
+    int rc2 = tp_allgather(logits + (size_t)tp_rank * lc.vocab, logits, (size_t)lc.vocab, stream);
+    if (rc2) return rc2;
+  }
   B200_CUDA(cudaMemcpyAsync(logits_host, logits, (size_t)cfg.vocab * 4, cudaMemcpyDeviceToHost, stream));
   B200_CUDA(cudaStreamSynchronize(stream));
   return 0;
@@ -474,7 +524,7 @@ namespace b200 {
 
 int Engine::ensure_prefill() {
   if (pf_ready) return 0;
-  const b200_config& c = cfg;
+  const b200_config& c = lc;
   const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn, T = std::max(c.max_ctx, c.max_seqs);
   if (!gemm_shape_ok(qd + 2 * kvd, d, 1) || !gemm_shape_ok(d, qd, 1) || !gemm_shape_ok(2 * ff, d, 1) || !gemm_shape_ok(d, ff, 1)) {
     set_error("model dims not supported by the tensor-core path (rows %%128, K %%64)");
@@ -529,7 +579,7 @@ int Engine::ensure_prefill() {
 // sequence in slot slot_arr[t], which then sees ctx_arr[t] tokens (batched decode).
 // Leaves the residual stream of every row in pf_x (+ pf_proj still to be added).
 int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_arr, const int32_t* ctx_arr, const int32_t* slot_arr) {
-  const b200_config& c = cfg;
+  const b200_config& c = lc;
   const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn;
   cudaStream_t s = stream;
   const int32_t* table = pos_arr ? block_table : active_table;
@@ -547,10 +597,12 @@ int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_ar
     B200_CUDA(launch_attn_decode(t, s, false));
     B200_CUDA(launch_f32_to_bf16(pf_att, pf_xb, (int64_t)n * qd, s));
     B200_CUDA(launch_gemm_bf16(L.o16, d, qd, pf_xb, n, pf_proj, d, s));
+    if (tp_size > 1) { int rc = tp_allreduce_sum(pf_proj, (size_t)n * d, s); if (rc) return rc; }
     B200_CUDA(launch_add_rmsnorm_bf16(pf_x, pf_proj, L.ffn_norm, pf_xb, n, d, c.rms_eps, s));
     B200_CUDA(launch_gemm_bf16(L.gu16, 2 * ff, d, pf_xb, n, pf_gu, 2 * ff, s));
     B200_CUDA(launch_swiglu_bf16(pf_gu, pf_xb, (int64_t)n * ff, s));
     B200_CUDA(launch_gemm_bf16(L.down16, d, ff, pf_xb, n, pf_proj, d, s));
+    if (tp_size > 1) { int rc = tp_allreduce_sum(pf_proj, (size_t)n * d, s); if (rc) return rc; }
   }
   return 0;
 }

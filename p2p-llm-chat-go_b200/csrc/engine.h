@@ -33,6 +33,8 @@ struct Slot {
   uint8_t* base = nullptr;  // device buffer holding this tensor's rows
   int64_t row0 = 0;         // first row inside the buffer
   int64_t row_step = 1;     // 2 for the interleaved gate/up buffer
+  // tensor parallelism: this slot holds the window [src_row0, +rows) x [src_col0, +cols) of the full tensor
+  int64_t full_rows = 0, full_cols = 0, src_row0 = 0, src_col0 = 0;
   bool set = false;
 };
 
@@ -54,8 +56,18 @@ struct Layer {
 
 struct Request;
 
+struct NcclApi;  // dlopen'ed libnccl entry points (tp.cu)
+
 struct Engine {
-  b200_config cfg{};
+  b200_config cfg{};   // the full model
+  b200_config lc{};    // this rank's shard of it (n_heads, n_kv_heads, d_ffn, vocab divided by tp_size)
+  int tp_rank = 0, tp_size = 1;
+  void* nccl_comm = nullptr;
+  float* tp_partial = nullptr;  // [d_model] partial sums of the row-parallel projections (batch-1 path)
+  int tp_init(const void* unique_id);
+  int tp_allreduce_sum(float* buf, size_t n, cudaStream_t s);
+  int tp_allreduce_max_u64(unsigned long long* buf, cudaStream_t s);
+  int tp_allgather(const float* send, float* recv, size_t n_per_rank, cudaStream_t s);
   int sm_count = 148;
   cudaStream_t stream = nullptr;
   std::mutex mu;  // serialises every device-touching entry point
@@ -125,7 +137,7 @@ struct Engine {
   bool stopping = false;
 
   ~Engine();
-  int init(const b200_config& c);
+  int init(const b200_config& c, const void* nccl_id = nullptr);
   int alloc(void** p, size_t bytes);
   int place_tensor(const Slot& s, const uint8_t* dev_src);      // GGUF-layout rows on device -> slot
   int fetch_tensor(const Slot& s, uint8_t* dev_dst);            // slot -> GGUF-layout rows on device

@@ -388,7 +388,7 @@ DEVINL void epilogue(const GemvArgs& a, int unit, int lane, const float* acc, fl
         for (int r = 0; r < R; ++r)
           if (acc[r] > bestv) {
             bestv = acc[r];
-            besti = (uint32_t)(row0 + r);
+            besti = (uint32_t)(a.row_base + row0 + r);  // row_base: global id of row 0 (vocab-parallel lm_head)
           }
       }
     }

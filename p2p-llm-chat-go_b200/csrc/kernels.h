@@ -134,6 +134,7 @@ cudaError_t launch_synth(int type, void* dst, int64_t rows, int64_t cols, uint64
                          float sigma, cudaStream_t s);
 cudaError_t launch_f32_to_bf16(const float* x, uint16_t* y, int64_t n, cudaStream_t s);
 cudaError_t launch_l2_flush(void* buf, size_t bytes, cudaStream_t s);
+cudaError_t launch_add_inplace(float* x, const float* y, int n, cudaStream_t s);
 
 // tcgen05/TMEM bf16 GEMM (gemm.cu): Y[t*ldy + r] = sum_k X[t][k] W[r][k], fp32 out
 cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,

@@ -155,6 +155,10 @@ __global__ void f32_to_bf16_kernel(const float* x, uint16_t* y, int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) y[i] = f32_to_bf16_bits(x[i]);
 }
 
+__global__ void add_inplace_kernel(float* x, const float* y, int n) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) x[i] += y[i];
+}
+
 __global__ void l2_flush_kernel(uint4* buf, size_t n16) {
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) buf[i] = make_uint4(i, 0, 0, 0);
@@ -250,6 +254,11 @@ cudaError_t launch_synth(int type, void* dst, int64_t rows, int64_t cols, uint64
 cudaError_t launch_f32_to_bf16(const float* x, uint16_t* y, int64_t n, cudaStream_t s) {
   if (n == 0) return cudaSuccess;
   f32_to_bf16_kernel<<<592, 256, 0, s>>>(x, y, n);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_add_inplace(float* x, const float* y, int n, cudaStream_t s) {
+  add_inplace_kernel<<<(n + 1023) / 1024, 256, 0, s>>>(x, y, n);
   return cudaGetLastError();
 }
 
