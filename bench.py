@@ -230,6 +230,56 @@ def run_peers(eng, pkg, cfg, n_peers, n_prompt, n_new):
             "request_ms_p50": totals[len(totals) // 2], "note": "TTFT counted from admission into a slot; queueing before it is in request_ms"}
 
 
+def run_tp(args):
+    """BASELINE configs[4]: one model tensor-parallel over all ranks (torchrun), NCCL all-reduce over NVLink.
+    Every rank drives its shard with the same calls (SPMD); timing is the max over ranks."""
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as ge
+    rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pkg = ge.load_package()
+    box = [pkg.tp_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    cfg = pkg.llama31_70b() if args.model == "70b" else pkg.llama31_8b()
+    cfg.device, cfg.max_ctx, cfg.seed, cfg.eos_token = local, 1024, 0, -1
+    eng = pkg.Engine(cfg, tp_rank=rank, tp_size=world, nccl_id=box[0])
+    prompt = synthetic_prompt(cfg.vocab, N_PROMPT)
+    for _ in range(max(args.warmup, 3)):
+        eng.generate_greedy(prompt, 16)
+    torch.cuda.synchronize(local); dist.barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ttfts, dec_ms, t0 = [], 0.0, time.perf_counter()
+    for _ in range(args.steps):
+        _, ttft, dec = eng.generate_greedy(prompt, N_NEW)
+        ttfts.append(ttft); dec_ms += dec
+    torch.cuda.synchronize(local); dist.barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop()
+    step_ms, launches = eng.bench_decode(N_PROMPT + N_NEW // 2, 32)
+    dec_ms, wall, ttft_p50, step_ms = max_over_ranks(dist, [dec_ms, wall, statistics.median(ttfts), step_ms], f"cuda:{local}")
+    if rank == 0:
+        peaks, peak_src = measured_peaks()
+        hbm = float(peaks["hbm_gbs"])
+        wb = eng.weight_bytes()  # per rank
+        kv = 2 * cfg.n_layers * (cfg.n_kv_heads // world) * cfg.head_dim * 2 * (N_PROMPT + N_NEW // 2)
+        print(json.dumps({
+            "metric": f"decode_tok_per_s_llama3.1_{args.model}_tp{world}_bs1", "value": args.steps * (N_NEW - 1) / (dec_ms / 1e3), "unit": UNIT,
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * wall / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "ttft_ms": ttft_p50,
+            "config": {"workload": f"llama3.1-{args.model} bf16 bs1: 512-token synthetic prompt, 128 greedy tokens",
+                       "parallelism": f"tp{world} (NCCL all-reduce after o and down, vocab-parallel lm_head)"},
+            "step_roofline": {"bound": "hbm", "bytes_per_token_per_gpu": wb + kv, "ms_per_token": step_ms,
+                              "achieved": (wb + kv) / (step_ms * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s per GPU",
+                              "frac": (wb + kv) / (step_ms * 1e-3) / 1e9 / hbm, "launches_per_token": launches, "peak_source": peak_src},
+            "gpu_launches": args.steps * (N_NEW - 1) * launches, "clocks": clocks}))
+    eng.close()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
 def run_ours(args):
     import torch
     import __graft_entry__ as ge
@@ -361,9 +411,14 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="suggest", choices=["suggest", "tp"],
+                    help="suggest: BASELINE configs[1] on independent replicas (default); tp: one model tensor-parallel over all ranks")
+    ap.add_argument("--model", default="70b", choices=["8b", "70b"], help="--workload tp only")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "tp":
+        run_tp(args)
     else:
         run_ours(args)
 
