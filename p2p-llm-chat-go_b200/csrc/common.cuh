@@ -57,6 +57,10 @@ DEVINL void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar
       ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(policy)
       : "memory");
 }
+// asks L2 to fetch [p, p+bytes) from HBM (bytes % 16 == 0); a hint, nothing waits on it
+DEVINL void l2_prefetch(const void* p, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
 DEVINL void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // Programmatic dependent launch: everything before pdl_wait() overlaps the previous kernel's tail.

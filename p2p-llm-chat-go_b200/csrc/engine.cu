@@ -84,6 +84,9 @@ int Engine::init(const b200_config& c, const void* nccl_id) {
   sm_count = prop.multiProcessorCount;
   use_pdl = getenv("B200_NO_PDL") == nullptr;
   use_graph = getenv("B200_NO_GRAPH") == nullptr;
+  // measured on B200 (round 1): chaining L2 prefetches of the next kernel's weights made the step SLOWER
+  // (bf16 3.18 vs 3.05 ms, Q4_K_M 1.84 vs 1.78 ms), so it is opt-in for experiments only
+  use_l2_chain = getenv("B200_L2_CHAIN") != nullptr;
 
   const int tp = tp_size, R = tp_rank;
   if (tp < 1 || R < 0 || R >= tp || c.n_heads % tp || c.n_kv_heads % tp || c.d_ffn % tp || c.vocab % tp ||
@@ -361,8 +364,16 @@ int Engine::enqueue_step(cudaStream_t s) {
     a.W = L.qkv; a.N = L.v ? qd + kvd : qd + 2 * kvd; a.K = d; a.x = x; a.norm_w = L.attn_norm; a.eps = c.rms_eps; a.y = q;
     a.row_base = 0; a.q_rows = qd; a.kv_rows = kvd; a.n_kv_heads = c.n_kv_heads; a.rope = rope;
     a.k_cache = L.k_cache; a.v_cache = L.v_cache; a.block_table = active_table; a.st = st;
+    // L2 prefetch chain: qkv -> o (waits in L2 while attention runs), o -> gate/up, gate/up -> down, down -> next qkv
+    const unsigned long long pf_cap = use_l2_chain ? (40ull << 20) : 0ull;
+    auto chain = [&](GemvArgs& g, const uint8_t* w, int type, int64_t rows, int64_t k) {
+      g.next_W = w;
+      g.next_bytes = std::min<unsigned long long>(pf_cap, (unsigned long long)rows * gemv_row_bytes(type, k)) & ~127ull;
+    };
+    chain(a, L.o, L.o_type, d, qd);
     B200_CUDA(launch_gemv(L.qkv_type, PRO_RMSNORM, EPI_QKV, a, s, use_pdl, sm_count)); ++n;
     if (L.v) {
+      a.next_bytes = 0;
       a.W = L.v; a.N = kvd; a.row_base = qd + kvd;
       B200_CUDA(launch_gemv(L.v_type, PRO_RMSNORM, EPI_QKV, a, s, use_pdl, sm_count)); ++n;
     }
@@ -375,6 +386,7 @@ int Engine::enqueue_step(cudaStream_t s) {
     // K-slice, so the partial products are summed over NVLink (NCCL all-reduce) before they join the stream
     GemvArgs o = {};
     o.W = L.o; o.N = d; o.K = qd; o.x = att; o.y = tp ? tp_partial : x;
+    chain(o, L.gate_up, L.gu_type, 2 * ff, d);
     B200_CUDA(launch_gemv(L.o_type, PRO_COPY, tp ? EPI_STORE : EPI_RESID, o, s, use_pdl, sm_count)); ++n;
     if (tp) {
       int rc = tp_allreduce_sum(tp_partial, (size_t)d, s);
@@ -383,9 +395,12 @@ int Engine::enqueue_step(cudaStream_t s) {
     }
     GemvArgs g = {};
     g.W = L.gate_up; g.N = 2 * ff; g.K = d; g.x = x; g.norm_w = L.ffn_norm; g.eps = c.rms_eps; g.y = h;
+    chain(g, L.down, L.down_type, d, ff);
     B200_CUDA(launch_gemv(L.gu_type, PRO_RMSNORM, EPI_SWIGLU, g, s, use_pdl && !tp, sm_count)); ++n;
     GemvArgs dn = {};
     dn.W = L.down; dn.N = d; dn.K = ff; dn.x = h; dn.y = tp ? tp_partial : x;
+    if (l + 1 < c.n_layers) chain(dn, layers[l + 1].qkv, layers[l + 1].qkv_type, layers[l + 1].v ? qd + kvd : qd + 2 * kvd, d);
+    else chain(dn, output, output_type, c.vocab, d);
     B200_CUDA(launch_gemv(L.down_type, PRO_COPY, tp ? EPI_STORE : EPI_RESID, dn, s, use_pdl, sm_count)); ++n;
     if (tp) {
       int rc = tp_allreduce_sum(tp_partial, (size_t)d, s);

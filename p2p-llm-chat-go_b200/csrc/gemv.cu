@@ -519,6 +519,12 @@ __global__ void __launch_bounds__(kWarps * 32, 1) gemv_kernel(const GemvArgs a) 
     epilogue<EPI, F::R>(a, gwarp + u * twarps, lane, acc, bestv, besti);
   }
   if (EPI == EPI_LOGITS && lane == 0 && my_units > 0) atomicMax(a.argmax_key, argmax_key(bestv, besti));
+  if (a.next_bytes != 0 && lane == 0) {  // this warp's slice of the next kernel's weights -> L2
+    const unsigned long long per = ((a.next_bytes / (unsigned long long)twarps) + 127ull) & ~127ull;
+    unsigned long long off = per * (unsigned long long)gwarp;
+    const unsigned long long end = off + per < a.next_bytes ? off + per : a.next_bytes;
+    for (; off < end; off += 8192ull) l2_prefetch(a.next_W + off, (uint32_t)((end - off < 8192ull ? end - off : 8192ull) & ~15ull));
+  }
 }
 
 template <class F>

@@ -49,6 +49,10 @@ struct GemvArgs {
   // EPI_LOGITS
   int store_logits;
   unsigned long long* argmax_key;
+  // L2 prefetch chaining: when a warp has streamed its last unit it asks L2 for a slice of the weights the
+  // NEXT kernel of the step will stream, so that kernel starts on L2 hits while HBM would otherwise idle
+  const uint8_t* next_W;
+  unsigned long long next_bytes;
 };
 
 struct GemvPlan {  // launch geometry chosen on the host
