@@ -46,6 +46,7 @@ Engine::~Engine() {
   if (worker.joinable()) worker.join();
   if (stream) cudaStreamSynchronize(stream);
   if (step_graph) cudaGraphExecDestroy(step_graph);
+  for (void* p : tp_ipc_opened) cudaIpcCloseMemHandle(p);
   tp_destroy(nccl_comm);
   for (void* p : allocs) cudaFree(p);
   if (out_tokens) cudaFreeHost(out_tokens);
@@ -261,6 +262,10 @@ int Engine::init(const b200_config& c, const void* nccl_id) {
       }
     B200_CUDA(cudaMemcpy(rope, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice));
   }
+  if (tp_size > 1 && getenv("B200_TP_NCCL") == nullptr) {
+    int rc = tp_setup_link();
+    if (rc) return rc;
+  }
   if (c.seed >= 0) {
     int rc = synthesize();
     if (rc) return rc;
@@ -330,14 +335,19 @@ int Engine::synthesize() {
 }
 
 // lm_head GEMV (logits + argmax), sampler (no-op for greedy requests), finish_step (token hand-over)
-int Engine::enqueue_tail(cudaStream_t s, bool pdl, int* n) {
+int Engine::enqueue_tail(cudaStream_t s, bool pdl, int* n, bool consume_tp) {
   const b200_config& c = lc;
   GemvArgs lm = {};
   lm.W = output; lm.N = c.vocab; lm.K = c.d_model; lm.x = x; lm.norm_w = output_norm; lm.eps = c.rms_eps;
+  int pro = PRO_RMSNORM;
+  if (consume_tp) {  // the last down projection of the step is still sitting in the receive buffers
+    pro = PRO_TP_RMSNORM;
+    lm.tp = tp_link; lm.tp_index = 2 * c.n_layers - 1; lm.x = x_alt; lm.x_out = x;  // index odd -> reads buffer 1
+  }
   lm.y = logits + (size_t)tp_rank * c.vocab;  // vocab-parallel: this rank's slice of the logits
   lm.row_base = tp_rank * c.vocab;             // global token id of row 0 (argmax key)
   lm.st = st; lm.store_logits = 1; lm.argmax_key = &st->argmax_key;
-  B200_CUDA(launch_gemv(output_type, PRO_RMSNORM, EPI_LOGITS, lm, s, pdl, sm_count)); ++*n;
+  B200_CUDA(launch_gemv(output_type, pro, EPI_LOGITS, lm, s, pdl, sm_count)); ++*n;
   if (tp_size > 1) {  // global argmax = max over ranks of the packed (logit, ~id) keys
     int rc = tp_allreduce_max_u64(&st->argmax_key, s);
     if (rc) return rc;
@@ -349,6 +359,7 @@ int Engine::enqueue_tail(cudaStream_t s, bool pdl, int* n) {
   FinishArgs f = {};
   f.st = st; f.prompt = prompt_dev; f.out_tokens = out_tokens_dev; f.host_n_out = host_n_out_dev; f.embd = token_embd;
   f.embd_type = embd_type; f.d_model = c.d_model; f.x = x; f.max_ctx = c.max_ctx;
+  f.tp_epoch = tp_fused ? tp_link_host.epoch : nullptr;
   B200_CUDA(launch_finish_step(f, s, pdl)); ++*n;
   return 0;
 }
@@ -360,8 +371,16 @@ int Engine::enqueue_step(cudaStream_t s) {
   int n = 0;
   for (int l = 0; l < c.n_layers; ++l) {
     Layer& L = layers[l];
+    // fused all-reduce: residual buffers alternate, all-reduce i is consumed from xbuf[i&1] into xbuf[(i+1)&1]
+    float* xbuf[2] = {x, x_alt};
+    const bool fused = tp && tp_fused;
     GemvArgs a = {};
     a.W = L.qkv; a.N = L.v ? qd + kvd : qd + 2 * kvd; a.K = d; a.x = x; a.norm_w = L.attn_norm; a.eps = c.rms_eps; a.y = q;
+    int qkv_pro = PRO_RMSNORM;
+    if (fused && l > 0) {  // consumes the previous layer's down projection (all-reduce 2l-1)
+      qkv_pro = PRO_TP_RMSNORM;
+      a.tp = tp_link; a.tp_index = 2 * l - 1; a.x = xbuf[(2 * l - 1) & 1]; a.x_out = xbuf[(2 * l) & 1];
+    }
     a.row_base = 0; a.q_rows = qd; a.kv_rows = kvd; a.n_kv_heads = c.n_kv_heads; a.rope = rope;
     a.k_cache = L.k_cache; a.v_cache = L.v_cache; a.block_table = active_table; a.st = st;
     // L2 prefetch chain: qkv -> o (waits in L2 while attention runs), o -> gate/up, gate/up -> down, down -> next qkv
@@ -371,7 +390,7 @@ int Engine::enqueue_step(cudaStream_t s) {
       g.next_bytes = std::min<unsigned long long>(pf_cap, (unsigned long long)rows * gemv_row_bytes(type, k)) & ~127ull;
     };
     chain(a, L.o, L.o_type, d, qd);
-    B200_CUDA(launch_gemv(L.qkv_type, PRO_RMSNORM, EPI_QKV, a, s, use_pdl, sm_count)); ++n;
+    B200_CUDA(launch_gemv(L.qkv_type, qkv_pro, EPI_QKV, a, s, use_pdl, sm_count)); ++n;
     if (L.v) {
       a.next_bytes = 0;
       a.W = L.v; a.N = kvd; a.row_base = qd + kvd;
@@ -387,8 +406,9 @@ int Engine::enqueue_step(cudaStream_t s) {
     GemvArgs o = {};
     o.W = L.o; o.N = d; o.K = qd; o.x = att; o.y = tp ? tp_partial : x;
     chain(o, L.gate_up, L.gu_type, 2 * ff, d);
-    B200_CUDA(launch_gemv(L.o_type, PRO_COPY, tp ? EPI_STORE : EPI_RESID, o, s, use_pdl, sm_count)); ++n;
-    if (tp) {
+    if (fused) { o.tp = tp_link; o.tp_index = 2 * l; o.y = nullptr; }
+    B200_CUDA(launch_gemv(L.o_type, PRO_COPY, fused ? EPI_TP_PUSH : (tp ? EPI_STORE : EPI_RESID), o, s, use_pdl, sm_count)); ++n;
+    if (tp && !fused) {
       int rc = tp_allreduce_sum(tp_partial, (size_t)d, s);
       if (rc) return rc;
       B200_CUDA(launch_add_inplace(x, tp_partial, d, s)); n += 2;
@@ -396,20 +416,26 @@ int Engine::enqueue_step(cudaStream_t s) {
     GemvArgs g = {};
     g.W = L.gate_up; g.N = 2 * ff; g.K = d; g.x = x; g.norm_w = L.ffn_norm; g.eps = c.rms_eps; g.y = h;
     chain(g, L.down, L.down_type, d, ff);
-    B200_CUDA(launch_gemv(L.gu_type, PRO_RMSNORM, EPI_SWIGLU, g, s, use_pdl && !tp, sm_count)); ++n;
+    int gu_pro = PRO_RMSNORM;
+    if (fused) {  // consumes this layer's o projection (all-reduce 2l): reads xbuf[0], publishes xbuf[1]
+      gu_pro = PRO_TP_RMSNORM;
+      g.tp = tp_link; g.tp_index = 2 * l; g.x = xbuf[(2 * l) & 1]; g.x_out = xbuf[(2 * l + 1) & 1];
+    }
+    B200_CUDA(launch_gemv(L.gu_type, gu_pro, EPI_SWIGLU, g, s, use_pdl && (!tp || fused), sm_count)); ++n;
     GemvArgs dn = {};
     dn.W = L.down; dn.N = d; dn.K = ff; dn.x = h; dn.y = tp ? tp_partial : x;
     if (l + 1 < c.n_layers) chain(dn, layers[l + 1].qkv, layers[l + 1].qkv_type, layers[l + 1].v ? qd + kvd : qd + 2 * kvd, d);
     else chain(dn, output, output_type, c.vocab, d);
-    B200_CUDA(launch_gemv(L.down_type, PRO_COPY, tp ? EPI_STORE : EPI_RESID, dn, s, use_pdl, sm_count)); ++n;
-    if (tp) {
+    if (fused) { dn.tp = tp_link; dn.tp_index = 2 * l + 1; dn.y = nullptr; }
+    B200_CUDA(launch_gemv(L.down_type, PRO_COPY, fused ? EPI_TP_PUSH : (tp ? EPI_STORE : EPI_RESID), dn, s, use_pdl, sm_count)); ++n;
+    if (tp && !fused) {
       int rc = tp_allreduce_sum(tp_partial, (size_t)d, s);
       if (rc) return rc;
       B200_CUDA(launch_add_inplace(x, tp_partial, d, s)); n += 2;
     }
   }
   {
-    int rc = enqueue_tail(s, use_pdl, &n);
+    int rc = enqueue_tail(s, use_pdl, &n, tp && tp_fused);
     if (rc) return rc;
   }
   launches_per_step = n;
@@ -505,6 +531,7 @@ int Engine::generate_greedy(const int32_t* prompt, int n_prompt, int32_t* ids, i
   }
   cudaError_t e = cudaStreamSynchronize(stream);
   if (!rc && e != cudaSuccess) rc = cuda_fail(e, "generate sync");
+  if (!rc) rc = tp_check_error();
   if (!rc) {
     float a = 0, b = 0;
     cudaEventElapsedTime(&a, e0, e1);

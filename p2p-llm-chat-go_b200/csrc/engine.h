@@ -63,7 +63,15 @@ struct Engine {
   b200_config lc{};    // this rank's shard of it (n_heads, n_kv_heads, d_ffn, vocab divided by tp_size)
   int tp_rank = 0, tp_size = 1;
   void* nccl_comm = nullptr;
-  float* tp_partial = nullptr;  // [d_model] partial sums of the row-parallel projections (batch-1 path)
+  float* tp_partial = nullptr;  // [d_model] partial sums of the row-parallel projections (NCCL fallback path)
+  // fused all-reduce over peer memory (batch-1 decode): see TpLink in kernels.h
+  bool tp_fused = false;
+  TpLink* tp_link = nullptr;      // device copy
+  TpLink tp_link_host{};
+  float* x_alt = nullptr;         // second residual buffer (consumers read one, publish into the other)
+  std::vector<void*> tp_ipc_opened;
+  int tp_setup_link();
+  int tp_check_error();
   int tp_init(const void* unique_id);
   int tp_allreduce_sum(float* buf, size_t n, cudaStream_t s);
   int tp_allreduce_max_u64(unsigned long long* buf, cudaStream_t s);
@@ -144,7 +152,7 @@ struct Engine {
   int synthesize();
   bool all_set() const;
 
-  int enqueue_tail(cudaStream_t s, bool pdl, int* n);  // lm_head + sampler + finish_step
+  int enqueue_tail(cudaStream_t s, bool pdl, int* n, bool consume_tp = false);  // lm_head + sampler + finish_step
   int enqueue_step(cudaStream_t s);          // launches the kernels of one decode step (capturable)
   int ensure_graph();
   int launch_steps(int n);                   // n graph replays (or direct launches)

@@ -41,7 +41,7 @@ DEVINL float block_sum(float v, float* red, int warp, int lane) {
 
 template <int PRO>
 DEVINL float rms_inv(const GemvArgs& a, float* red, int warp, int lane) {
-  if (PRO != PRO_RMSNORM) return 1.f;
+  if (PRO != PRO_RMSNORM) return 1.f;  // (PRO_TP_RMSNORM is bf16-only and has its own prologue)
   float ss = 0.f;
   for (int k = threadIdx.x * 4; k < a.K; k += kWarps * 32 * 4) {
     const float4 v = *reinterpret_cast<const float4*>(a.x + k);
@@ -54,6 +54,62 @@ DEVINL float rms_inv(const GemvArgs& a, float* red, int warp, int lane) {
 // ------------------------------------------------------------------ format policies
 // Each policy states: R rows per unit, CHUNK columns per stage, the stage layout, how lane 0 issues the
 // bulk copies of a stage, how the block prepares x in shared memory, and how a warp consumes a stage.
+
+DEVINL unsigned int ld_acquire_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+DEVINL void st_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Consumer half of the fused all-reduce (see TpLink): wait until every rank's partial of all-reduce
+// `tp_index` has landed in this GPU's receive buffer, x_new = x + sum over ranks (fixed order, so every rank
+// computes the same bits), CTA 0 publishes x_new, and the RMS-normalised x_new goes to shared memory in the
+// GEMV's permuted layout.  A wait that exceeds ~2 s sets the error flag and carries on (no hang).
+DEVINL void tp_prologue(float* xs, const GemvArgs& a, float* red, int warp, int lane) {
+  const TpLink* t = a.tp;
+  const int buf = a.tp_index & 1, size = t->size, d = a.K;
+  const unsigned int seq = *t->epoch * (unsigned int)t->per_step + (unsigned int)a.tp_index + 1u;
+  if (warp == 0 && lane < size) {
+    const unsigned int* f = t->flags + buf * kMaxTp + lane;
+    const long long t0 = clock64();
+    while ((int)(ld_acquire_sys(f) - seq) < 0) {
+      if (clock64() - t0 > 4000000000ll) {
+        *t->error = 1;
+        break;
+      }
+    }
+  }
+  __syncthreads();
+  const float* rv = t->recv[buf];
+  float ss = 0.f;
+  for (int k = threadIdx.x * 4; k < d; k += kWarps * 32 * 4) {
+    float4 v = *reinterpret_cast<const float4*>(a.x + k);
+    for (int s = 0; s < size; ++s) {
+      const float4 p = __ldcg(reinterpret_cast<const float4*>(rv + (size_t)s * d + k));
+      v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
+    }
+    if (blockIdx.x == 0) *reinterpret_cast<float4*>(a.x_out + k) = v;
+    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    const int idx = (k & ~255) + ((k >> 2) & 1) * 128 + ((k & 255) >> 3) * 4;
+    *reinterpret_cast<float4*>(xs + idx) = v;
+  }
+  ss = block_sum(ss, red, warp, lane);
+  const float inv = 1.0f / sqrtf(ss / (float)d + a.eps);
+  for (int k = threadIdx.x * 4; k < d; k += kWarps * 32 * 4) {
+    const int idx = (k & ~255) + ((k >> 2) & 1) * 128 + ((k & 255) >> 3) * 4;
+    float4 v = *reinterpret_cast<float4*>(xs + idx);
+    const float4 w = *reinterpret_cast<const float4*>(a.norm_w + k);
+    v.x = __fmul_rn(__fmul_rn(v.x, inv), w.x);
+    v.y = __fmul_rn(__fmul_rn(v.y, inv), w.y);
+    v.z = __fmul_rn(__fmul_rn(v.z, inv), w.z);
+    v.w = __fmul_rn(__fmul_rn(v.w, inv), w.w);
+    *reinterpret_cast<float4*>(xs + idx) = v;
+  }
+  __syncthreads();
+}
 
 template <int KC, int R_>  // KC in {256, 512}; R_ rows per work unit (4, or 2 for matrices with few rows)
 struct FmtBF16 {
@@ -74,6 +130,10 @@ struct FmtBF16 {
   template <int PRO>
   static DEVINL void prologue(uint8_t* xs_, const GemvArgs& a, float* red, int warp, int lane) {
     float* xs = reinterpret_cast<float*>(xs_);
+    if (PRO == PRO_TP_RMSNORM) {
+      tp_prologue(xs, a, red, warp, lane);
+      return;
+    }
     const float inv = rms_inv<PRO>(a, red, warp, lane);
     for (int k = threadIdx.x * 4; k < a.K; k += kWarps * 32 * 4) {
       float4 v = *reinterpret_cast<const float4*>(a.x + k);
@@ -392,6 +452,13 @@ DEVINL void epilogue(const GemvArgs& a, int unit, int lane, const float* acc, fl
           }
       }
     }
+  } else if (EPI == EPI_TP_PUSH) {  // lane p sends this unit's partial sums to peer p over NVLink
+    const TpLink* t = a.tp;
+    if (lane < t->size) {
+      float* dst = t->peer_recv[a.tp_index & 1][lane] + (size_t)t->rank * t->d + row0;
+#pragma unroll
+      for (int r = 0; r < R; ++r) dst[r] = acc[r];
+    }
   } else if (EPI == EPI_RESID) {
     if (lane == 0) {
 #pragma unroll
@@ -519,6 +586,19 @@ __global__ void __launch_bounds__(kWarps * 32, 1) gemv_kernel(const GemvArgs a) 
     epilogue<EPI, F::R>(a, gwarp + u * twarps, lane, acc, bestv, besti);
   }
   if (EPI == EPI_LOGITS && lane == 0 && my_units > 0) atomicMax(a.argmax_key, argmax_key(bestv, besti));
+  if (EPI == EPI_TP_PUSH) {  // when the last CTA of the grid has pushed, raise this rank's flag on every peer
+    const TpLink* t = a.tp;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      if (atomicAdd(t->ticket, 1u) == gridDim.x - 1) {
+        *t->ticket = 0u;
+        __threadfence_system();
+        const unsigned int seq = *t->epoch * (unsigned int)t->per_step + (unsigned int)a.tp_index + 1u;
+        for (int p = 0; p < t->size; ++p) st_release_sys(t->peer_flags[p] + (a.tp_index & 1) * kMaxTp + t->rank, seq);
+      }
+    }
+  }
   if (a.next_bytes != 0 && lane == 0) {  // this warp's slice of the next kernel's weights -> L2
     const unsigned long long per = ((a.next_bytes / (unsigned long long)twarps) + 127ull) & ~127ull;
     unsigned long long off = per * (unsigned long long)gwarp;
@@ -569,6 +649,10 @@ cudaError_t launch_f(int pro, int epi, const GemvArgs& a, cudaStream_t s, bool p
   CASE(PRO_RMSNORM, EPI_SWIGLU)
   CASE(PRO_RMSNORM, EPI_QKV)
   CASE(PRO_RMSNORM, EPI_LOGITS)
+  CASE(PRO_COPY, EPI_TP_PUSH)
+  CASE(PRO_TP_RMSNORM, EPI_SWIGLU)
+  CASE(PRO_TP_RMSNORM, EPI_QKV)
+  CASE(PRO_TP_RMSNORM, EPI_LOGITS)
 #undef CASE
   return cudaErrorInvalidValue;
 }

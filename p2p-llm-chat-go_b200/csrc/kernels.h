@@ -12,8 +12,24 @@ constexpr int QK_K = 256, Q4K_BYTES = 144, Q6K_BYTES = 210;  // GGUF k-quant sup
 // ggml type ids (== B200_TYPE_*)
 enum { T_F32 = 0, T_Q4_K = 12, T_Q6_K = 14, T_BF16 = 30 };
 
-enum { PRO_COPY = 0, PRO_RMSNORM = 1 };
-enum { EPI_STORE = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_QKV = 3, EPI_LOGITS = 4 };
+enum { PRO_COPY = 0, PRO_RMSNORM = 1, PRO_TP_RMSNORM = 2 };
+enum { EPI_STORE = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_QKV = 3, EPI_LOGITS = 4, EPI_TP_PUSH = 5 };
+
+// Tensor-parallel link of one rank (device-resident): peers' receive buffers and flags, mapped over NVLink.
+// The row-parallel GEMVs (o, down) push their partial sums straight into every peer's buffer from their
+// epilogue (EPI_TP_PUSH); the next GEMV's prologue (PRO_TP_RMSNORM) waits for the flags, adds the partials in
+// rank order to the residual stream and normalises — the all-reduce costs no launch of its own.
+constexpr int kMaxTp = 8;
+struct TpLink {
+  float* peer_recv[2][kMaxTp];      // [buffer][peer] -> that peer's recv buffer ([size][d] floats, slot = source rank)
+  unsigned int* peer_flags[kMaxTp]; // -> that peer's flags [2][kMaxTp] (sequence number per source rank)
+  float* recv[2];                   // this rank's own buffers
+  unsigned int* flags;              // this rank's own flags
+  unsigned int* epoch;              // decode steps completed (advanced by finish_step)
+  unsigned int* ticket;             // CTA ticket of the pushing kernel (self-resetting)
+  int* error;                       // set if a wait timed out
+  int rank, size, d, per_step;      // per_step = all-reduces per decode step (2 * n_layers)
+};
 
 // Device-resident state of the sequence being decoded; every kernel of a step reads it, the last kernel
 // of the step (finish_step) advances it, so one captured CUDA graph serves every position.
@@ -53,6 +69,10 @@ struct GemvArgs {
   // NEXT kernel of the step will stream, so that kernel starts on L2 hits while HBM would otherwise idle
   const uint8_t* next_W;
   unsigned long long next_bytes;
+  // tensor parallelism over peer memory (null without it)
+  const TpLink* tp;
+  int tp_index;        // which all-reduce of the step this kernel produces (EPI_TP_PUSH) / consumes (PRO_TP_RMSNORM)
+  float* x_out;        // PRO_TP_RMSNORM: where CTA 0 leaves the updated residual stream (x + sum of partials)
 };
 
 struct GemvPlan {  // launch geometry chosen on the host
@@ -121,6 +141,7 @@ struct FinishArgs {
   int d_model;
   float* x;                  // residual stream for the next step
   int max_ctx;
+  unsigned int* tp_epoch;    // tensor parallelism over peer memory: step counter to advance (or null)
 };
 cudaError_t launch_finish_step(const FinishArgs& a, cudaStream_t s, bool pdl);
 cudaError_t launch_embed(const uint8_t* embd, int embd_type, int d_model, const int32_t* token_dev, float* x,

@@ -210,6 +210,7 @@ __global__ void finish_step_kernel(FinishArgs a) {
       }
     }
     st->argmax_key = 0ull;
+    if (a.tp_epoch) *a.tp_epoch += 1u;
     st->cur_token = tok;
     if (pos + 1 < a.max_ctx) st->pos = pos + 1;
     s_tok = tok;

@@ -8,6 +8,10 @@
 // libnccl.so.2 the process already has (e.g. PyTorch's) is the one that gets used.
 #include <dlfcn.h>
 #include <nccl.h>
+#include <unistd.h>
+
+#include <cstring>
+#include <vector>
 
 #include "engine.h"
 
@@ -88,6 +92,90 @@ int Engine::tp_allreduce_max_u64(unsigned long long* buf, cudaStream_t s) {
 int Engine::tp_allgather(const float* send, float* recv, size_t n_per_rank, cudaStream_t s) {
   ncclResult_t r = nccl()->AllGather(send, recv, n_per_rank, ncclFloat32, (ncclComm_t)nccl_comm, s);
   return r == ncclSuccess ? 0 : nccl_fail(r, "ncclAllGather");
+}
+
+}  // namespace b200
+
+// ---- fused all-reduce over peer memory -------------------------------------------------------------------
+// Every rank owns two receive buffers ([tp][d_model] fp32, alternating between consecutive all-reduces) and a
+// flag word per (buffer, source rank).  Their addresses are exchanged once with an NCCL all-gather: ranks that
+// live in the same process use the raw pointers after cudaDeviceEnablePeerAccess, ranks in other processes
+// (torchrun) open CUDA IPC handles.  From then on the decode step needs NCCL only for the 8-byte argmax.
+namespace b200 {
+
+struct TpXchg {
+  long long pid;
+  int device, pad;
+  void *recv0, *recv1, *flags;
+  cudaIpcMemHandle_t h0, h1, hf;
+};
+
+int Engine::tp_setup_link() {
+  const int d = cfg.d_model, n = tp_size;
+  if (n > kMaxTp) { set_error("tensor parallel degree %d > %d", n, kMaxTp); return B200_EINVAL; }
+  TpLink& L = tp_link_host;
+  memset(&L, 0, sizeof L);
+  L.rank = tp_rank; L.size = n; L.d = d; L.per_step = 2 * cfg.n_layers;
+  unsigned int* small = nullptr;  // flags[2][kMaxTp] | epoch | ticket | error
+  B200_CUDA(cudaMalloc((void**)&L.recv[0], (size_t)n * d * 4));
+  B200_CUDA(cudaMalloc((void**)&L.recv[1], (size_t)n * d * 4));
+  B200_CUDA(cudaMalloc((void**)&small, 256));
+  allocs.push_back(L.recv[0]); allocs.push_back(L.recv[1]); allocs.push_back(small);
+  B200_CUDA(cudaMemset(L.recv[0], 0, (size_t)n * d * 4));
+  B200_CUDA(cudaMemset(L.recv[1], 0, (size_t)n * d * 4));
+  B200_CUDA(cudaMemset(small, 0, 256));
+  L.flags = small; L.epoch = small + 2 * kMaxTp; L.ticket = small + 2 * kMaxTp + 1; L.error = (int*)(small + 2 * kMaxTp + 2);
+  int rc;
+  if ((rc = alloc((void**)&x_alt, (size_t)d * 4)) || (rc = alloc((void**)&tp_link, sizeof(TpLink)))) return rc;
+
+  TpXchg mine = {};
+  mine.pid = (long long)getpid(); mine.device = cfg.device;
+  mine.recv0 = L.recv[0]; mine.recv1 = L.recv[1]; mine.flags = L.flags;
+  B200_CUDA(cudaIpcGetMemHandle(&mine.h0, L.recv[0]));
+  B200_CUDA(cudaIpcGetMemHandle(&mine.h1, L.recv[1]));
+  B200_CUDA(cudaIpcGetMemHandle(&mine.hf, small));
+  TpXchg* dev_all = nullptr;
+  B200_CUDA(cudaMalloc((void**)&dev_all, sizeof(TpXchg) * n));
+  B200_CUDA(cudaMemcpy(dev_all + tp_rank, &mine, sizeof mine, cudaMemcpyHostToDevice));
+  ncclResult_t r = nccl()->AllGather(dev_all + tp_rank, dev_all, sizeof(TpXchg), ncclChar, (ncclComm_t)nccl_comm, stream);
+  if (r != ncclSuccess) { cudaFree(dev_all); return nccl_fail(r, "ncclAllGather(link)"); }
+  std::vector<TpXchg> all(n);
+  cudaError_t e = cudaMemcpyAsync(all.data(), dev_all, sizeof(TpXchg) * n, cudaMemcpyDeviceToHost, stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+  cudaFree(dev_all);
+  if (e != cudaSuccess) return cuda_fail(e, "link exchange");
+  for (int p = 0; p < n; ++p) {
+    if (p == tp_rank) {
+      L.peer_recv[0][p] = L.recv[0]; L.peer_recv[1][p] = L.recv[1]; L.peer_flags[p] = L.flags;
+    } else if (all[p].pid == mine.pid) {  // a thread of this process drives that GPU: map it directly
+      e = cudaDeviceEnablePeerAccess(all[p].device, 0);
+      if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return cuda_fail(e, "cudaDeviceEnablePeerAccess");
+      (void)cudaGetLastError();
+      L.peer_recv[0][p] = (float*)all[p].recv0; L.peer_recv[1][p] = (float*)all[p].recv1; L.peer_flags[p] = (unsigned int*)all[p].flags;
+    } else {
+      void *a = nullptr, *b = nullptr, *f = nullptr;
+      B200_CUDA(cudaIpcOpenMemHandle(&a, all[p].h0, cudaIpcMemLazyEnablePeerAccess));
+      B200_CUDA(cudaIpcOpenMemHandle(&b, all[p].h1, cudaIpcMemLazyEnablePeerAccess));
+      B200_CUDA(cudaIpcOpenMemHandle(&f, all[p].hf, cudaIpcMemLazyEnablePeerAccess));
+      tp_ipc_opened.push_back(a); tp_ipc_opened.push_back(b); tp_ipc_opened.push_back(f);
+      L.peer_recv[0][p] = (float*)a; L.peer_recv[1][p] = (float*)b; L.peer_flags[p] = (unsigned int*)f;
+    }
+  }
+  B200_CUDA(cudaMemcpy(tp_link, &L, sizeof L, cudaMemcpyHostToDevice));
+  // nobody may push before every rank has mapped everything: one more collective as a barrier
+  float* one = tp_partial;
+  if ((rc = tp_allreduce_sum(one, 1, stream))) return rc;
+  B200_CUDA(cudaStreamSynchronize(stream));
+  tp_fused = true;
+  return 0;
+}
+
+int Engine::tp_check_error() {
+  if (!tp_fused) return 0;
+  int err = 0;
+  B200_CUDA(cudaMemcpy(&err, tp_link_host.error, 4, cudaMemcpyDeviceToHost));
+  if (err) { set_error("tensor-parallel peer did not deliver its partial sums in time"); return B200_ETIMEOUT; }
+  return 0;
 }
 
 }  // namespace b200
