@@ -270,7 +270,7 @@ def run_tp(args):
             "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * wall / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "ttft_ms": ttft_p50,
             "config": {"workload": f"llama3.1-{args.model} bf16 bs1: 512-token synthetic prompt, 128 greedy tokens",
-                       "parallelism": f"tp{world} (NCCL all-reduce after o and down, vocab-parallel lm_head)"},
+                       "parallelism": f"tp{world} (o/down all-reduce fused into the GEMVs over NVLink peer memory; NCCL for prefill and the argmax key)" if not os.environ.get("B200_TP_NCCL") else f"tp{world} (NCCL all-reduce after o and down)"},
             "step_roofline": {"bound": "hbm", "bytes_per_token_per_gpu": wb + kv, "ms_per_token": step_ms,
                               "achieved": (wb + kv) / (step_ms * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s per GPU",
                               "frac": (wb + kv) / (step_ms * 1e-3) / 1e9 / hbm, "launches_per_token": launches, "peak_source": peak_src},
