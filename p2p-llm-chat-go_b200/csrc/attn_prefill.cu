@@ -1,0 +1,186 @@
+// attn_prefill.cu — causal GQA attention over a whole prompt (one sequence, positions pos0..pos0+T-1), sm_100a.
+//
+// grid = (n_kv_heads, ceil(T/16)); one warp per query head of the KV head's group, 16 query rows per warp, so
+// a CTA re-uses every K/V tile it stages for all G heads.  K/V tiles of 64 tokens are gathered through the
+// block table into XOR-swizzled shared memory (bf16, exactly the cache contents); S = Q.K^T and O += P.V run on
+// the tensor cores with mma.sync m16n8k16 (ldmatrix / ldmatrix.trans operands), online softmax in fp32
+// registers.  Prefill attention is 1 % of the prefill FLOPs, so it does not need tcgen05; it needs to stop
+// re-reading K/V per query, which the per-query decode kernel did (6.6 ms of a 16.8 ms TTFT).
+//
+// Numerics: Q (fp32) and P (fp32) are each fed as a bf16 "hi" plus a bf16 "lo" part (x = hi + lo to ~2^-17),
+// two MMAs each, so the result matches fp32 attention over the bf16 cache to ~1e-5 and the CPU oracle needs
+// no separate rounding rule for this kernel.  Output is bf16: it is the A operand of the o-projection GEMM.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200 {
+namespace {
+
+constexpr int kQRows = 16, kKvTile = 64;
+
+DEVINL void mma_bf16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+DEVINL void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+DEVINL void ldsm_x4_trans(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+// (x0, x1) -> packed bf16 hi parts and packed bf16 lo parts (x = hi + lo up to 2^-17 relative)
+DEVINL void split2(float x0, float x1, uint32_t& hi, uint32_t& lo) {
+  const uint16_t h0 = f32_to_bf16_bits(x0), h1 = f32_to_bf16_bits(x1);
+  const float r0 = x0 - __uint_as_float((uint32_t)h0 << 16), r1 = x1 - __uint_as_float((uint32_t)h1 << 16);
+  hi = (uint32_t)h0 | ((uint32_t)h1 << 16);
+  lo = (uint32_t)f32_to_bf16_bits(r0) | ((uint32_t)f32_to_bf16_bits(r1) << 16);
+}
+// byte offset of 16-byte chunk c (0..15) of token row r in a [64][128] bf16 tile, XOR-swizzled per 8 rows
+DEVINL uint32_t tile_off(int r, int c) { return (uint32_t)((r * 16 + (c ^ (r & 7))) * 16); }
+
+template <int G>
+__global__ void __launch_bounds__(G * 32) attn_prefill_kernel(const float* __restrict__ q, const uint16_t* __restrict__ k_cache,
+                                                             const uint16_t* __restrict__ v_cache, const int32_t* __restrict__ block_table,
+                                                             uint16_t* __restrict__ out, int T, int pos0, int n_heads, int n_kv_heads) {
+  __shared__ __align__(128) uint8_t Ks[kKvTile * 256];
+  __shared__ __align__(128) uint8_t Vs[kKvTile * 256];
+  const int kvh = blockIdx.x, q0 = blockIdx.y * kQRows;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int head = kvh * G + warp, qd = n_heads * kHeadDim;
+  const float scale = 1.0f / sqrtf((float)kHeadDim);
+  const int rowA = min(q0 + g, T - 1), rowB = min(q0 + g + 8, T - 1);  // clamp: rows past T compute, never store
+  const int posA = pos0 + rowA, posB = pos0 + rowB;
+
+  // Q fragments (A operand), hi and lo parts: 8 k-steps of 16 dims
+  uint32_t qh[8][4], ql[8][4];
+  {
+    const float* qa = q + (size_t)rowA * qd + (size_t)head * kHeadDim;
+    const float* qb = q + (size_t)rowB * qd + (size_t)head * kHeadDim;
+#pragma unroll
+    for (int kk = 0; kk < 8; ++kk) {
+      const float2 a0 = *reinterpret_cast<const float2*>(qa + 16 * kk + 2 * t), a1 = *reinterpret_cast<const float2*>(qb + 16 * kk + 2 * t);
+      const float2 a2 = *reinterpret_cast<const float2*>(qa + 16 * kk + 8 + 2 * t), a3 = *reinterpret_cast<const float2*>(qb + 16 * kk + 8 + 2 * t);
+      split2(a0.x * scale, a0.y * scale, qh[kk][0], ql[kk][0]);
+      split2(a1.x * scale, a1.y * scale, qh[kk][1], ql[kk][1]);
+      split2(a2.x * scale, a2.y * scale, qh[kk][2], ql[kk][2]);
+      split2(a3.x * scale, a3.y * scale, qh[kk][3], ql[kk][3]);
+    }
+  }
+  float o[16][4];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
+  float mA = -INFINITY, mB = -INFINITY, lA = 0.f, lB = 0.f;
+
+  const int kv_len = pos0 + min(q0 + kQRows, T);  // causal: the last row of this block sees this many tokens
+  const uint32_t ks = smem_u32(Ks), vs = smem_u32(Vs);
+  for (int t0 = 0; t0 < kv_len; t0 += kKvTile) {
+    __syncthreads();  // previous tile fully consumed
+    for (int item = threadIdx.x; item < kKvTile * 16; item += G * 32) {
+      const int r = item >> 4, c = item & 15, tok = t0 + r;
+      uint4 kv = make_uint4(0, 0, 0, 0), vv = make_uint4(0, 0, 0, 0);
+      if (tok < kv_len) {
+        const int page = block_table[tok / kPageTokens];
+        const size_t row = (((size_t)page * n_kv_heads + kvh) * kPageTokens + (tok % kPageTokens)) * kHeadDim;
+        kv = *reinterpret_cast<const uint4*>(k_cache + row + c * 8);
+        vv = *reinterpret_cast<const uint4*>(v_cache + row + c * 8);
+      }
+      *reinterpret_cast<uint4*>(Ks + tile_off(r, c)) = kv;
+      *reinterpret_cast<uint4*>(Vs + tile_off(r, c)) = vv;
+    }
+    __syncthreads();
+
+    // ---- S = (Q*scale) . K^T : 8 n-tiles of 8 tokens
+    float s[8][4];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+#pragma unroll
+      for (int kk = 0; kk < 8; kk += 2) {
+        // four 8x8 matrices: tokens 8j..8j+7 x dim chunks 2kk, 2kk+1, 2kk+2, 2kk+3
+        uint32_t b[4];
+        ldsm_x4(b, ks + tile_off(8 * j + (lane & 7), 2 * kk + (lane >> 3)));
+        mma_bf16(s[j], qh[kk], b[0], b[1]);
+        mma_bf16(s[j], ql[kk], b[0], b[1]);
+        mma_bf16(s[j], qh[kk + 1], b[2], b[3]);
+        mma_bf16(s[j], ql[kk + 1], b[2], b[3]);
+      }
+    }
+    // ---- causal mask + online softmax (rows g and g+8 of this warp's 16)
+    float mxA = -INFINITY, mxB = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int tk = t0 + 8 * j + 2 * t;
+      if (tk > posA) s[j][0] = -INFINITY;
+      if (tk + 1 > posA) s[j][1] = -INFINITY;
+      if (tk > posB) s[j][2] = -INFINITY;
+      if (tk + 1 > posB) s[j][3] = -INFINITY;
+      mxA = fmaxf(mxA, fmaxf(s[j][0], s[j][1]));
+      mxB = fmaxf(mxB, fmaxf(s[j][2], s[j][3]));
+    }
+    mxA = fmaxf(mxA, __shfl_xor_sync(0xffffffffu, mxA, 1)); mxA = fmaxf(mxA, __shfl_xor_sync(0xffffffffu, mxA, 2));
+    mxB = fmaxf(mxB, __shfl_xor_sync(0xffffffffu, mxB, 1)); mxB = fmaxf(mxB, __shfl_xor_sync(0xffffffffu, mxB, 2));
+    const float nA = fmaxf(mA, mxA), nB = fmaxf(mB, mxB);  // finite from the first tile on (token 0 is always visible)
+    const float cA = expf(mA - nA), cB = expf(mB - nB);   // exp(-inf) = 0 on the first tile
+    mA = nA; mB = nB;
+    lA *= cA; lB *= cB;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { o[j][0] *= cA; o[j][1] *= cA; o[j][2] *= cB; o[j][3] *= cB; }
+    uint32_t ph[4][4], pl[4][4];  // P as A fragments: k-step kk2 covers tokens 16kk2..16kk2+15 = n-tiles 2kk2, 2kk2+1
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float p0 = expf(s[j][0] - mA), p1 = expf(s[j][1] - mA), p2 = expf(s[j][2] - mB), p3 = expf(s[j][3] - mB);
+      lA += p0 + p1;
+      lB += p2 + p3;
+      split2(p0, p1, ph[j >> 1][(j & 1) * 2], pl[j >> 1][(j & 1) * 2]);
+      split2(p2, p3, ph[j >> 1][(j & 1) * 2 + 1], pl[j >> 1][(j & 1) * 2 + 1]);
+    }
+    // ---- O += P . V : 16 n-tiles of 8 dims, 4 k-steps of 16 tokens
+#pragma unroll
+    for (int kk2 = 0; kk2 < 4; ++kk2) {
+#pragma unroll
+      for (int jd = 0; jd < 16; jd += 2) {
+        // transposed 8x8 loads: tokens 16kk2+0..7 / +8..15 at dim chunk jd, then the same at chunk jd+1
+        uint32_t b[4];
+        ldsm_x4_trans(b, vs + tile_off(16 * kk2 + (lane & 7) + ((lane >> 3) & 1) * 8, jd + (lane >> 4)));
+        mma_bf16(o[jd], ph[kk2], b[0], b[1]);
+        mma_bf16(o[jd], pl[kk2], b[0], b[1]);
+        mma_bf16(o[jd + 1], ph[kk2], b[2], b[3]);
+        mma_bf16(o[jd + 1], pl[kk2], b[2], b[3]);
+      }
+    }
+  }
+  lA += __shfl_xor_sync(0xffffffffu, lA, 1); lA += __shfl_xor_sync(0xffffffffu, lA, 2);
+  lB += __shfl_xor_sync(0xffffffffu, lB, 1); lB += __shfl_xor_sync(0xffffffffu, lB, 2);
+  const float iA = 1.0f / lA, iB = 1.0f / lB;
+  uint16_t* oa = out + (size_t)(q0 + g) * qd + (size_t)head * kHeadDim;
+  uint16_t* ob = out + (size_t)(q0 + g + 8) * qd + (size_t)head * kHeadDim;
+#pragma unroll
+  for (int jd = 0; jd < 16; ++jd) {
+    if (q0 + g < T)
+      *reinterpret_cast<uint32_t*>(oa + 8 * jd + 2 * t) = (uint32_t)f32_to_bf16_bits(o[jd][0] * iA) | ((uint32_t)f32_to_bf16_bits(o[jd][1] * iA) << 16);
+    if (q0 + g + 8 < T)
+      *reinterpret_cast<uint32_t*>(ob + 8 * jd + 2 * t) = (uint32_t)f32_to_bf16_bits(o[jd][2] * iB) | ((uint32_t)f32_to_bf16_bits(o[jd][3] * iB) << 16);
+  }
+}
+
+}  // namespace
+
+// q: [T][n_heads*128] fp32 (rotated); out: [T][n_heads*128] bf16.  K/V of positions [0, pos0+T) must be in the cache.
+cudaError_t launch_attn_prefill(const float* q, const uint16_t* k_cache, const uint16_t* v_cache, const int32_t* block_table, uint16_t* out,
+                                int T, int pos0, int n_heads, int n_kv_heads, cudaStream_t s) {
+  if (T < 1 || n_kv_heads < 1 || n_heads % n_kv_heads) return cudaErrorInvalidValue;
+  dim3 grid(n_kv_heads, (T + kQRows - 1) / kQRows);
+  switch (n_heads / n_kv_heads) {
+    case 1: attn_prefill_kernel<1><<<grid, 32, 0, s>>>(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); break;
+    case 2: attn_prefill_kernel<2><<<grid, 64, 0, s>>>(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); break;
+    case 4: attn_prefill_kernel<4><<<grid, 128, 0, s>>>(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); break;
+    case 8: attn_prefill_kernel<8><<<grid, 256, 0, s>>>(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); break;
+    default: return cudaErrorInvalidValue;
+  }
+  return cudaGetLastError();
+}
+
+}  // namespace b200

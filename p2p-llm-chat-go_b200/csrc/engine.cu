@@ -85,6 +85,7 @@ int Engine::init(const b200_config& c, const void* nccl_id) {
   sm_count = prop.multiProcessorCount;
   use_pdl = getenv("B200_NO_PDL") == nullptr;
   use_graph = getenv("B200_NO_GRAPH") == nullptr;
+  use_fa_prefill = getenv("B200_NO_FA_PREFILL") == nullptr;
   // measured on B200 (round 1): chaining L2 prefetches of the next kernel's weights made the step SLOWER
   // (bf16 3.18 vs 3.05 ms, Q4_K_M 1.84 vs 1.78 ms), so it is opt-in for experiments only
   use_l2_chain = getenv("B200_L2_CHAIN") != nullptr;
@@ -631,13 +632,17 @@ int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_ar
     B200_CUDA(launch_add_rmsnorm_bf16(pf_x, l ? pf_proj : nullptr, L.attn_norm, pf_xb, n, d, c.rms_eps, s));
     B200_CUDA(launch_gemm_bf16(L.qkv16, qd + 2 * kvd, d, pf_xb, n, pf_qkv, qd + 2 * kvd, s));
     B200_CUDA(launch_rope_kv(pf_qkv, pf_q, L.k_cache, L.v_cache, table, rope, n, qd, kvd, c.n_kv_heads, 0, pos_arr, slot_arr, pages_per_seq, s));
-    AttnArgs t = {};
-    t.q = pf_q; t.k_cache = L.k_cache; t.v_cache = L.v_cache; t.block_table = table; t.st = nullptr;
-    t.n_heads = c.n_heads; t.n_kv_heads = c.n_kv_heads; t.out = pf_att; t.partial = pf_partial; t.counters = pf_counters;
-    t.n_splits = pf_splits; t.fixed_ctx = 1; t.n_queries = n; t.q_stride = qd;
-    t.q_ctx = ctx_arr; t.q_slot = slot_arr; t.pages_per_seq = pages_per_seq;
-    B200_CUDA(launch_attn_decode(t, s, false));
-    B200_CUDA(launch_f32_to_bf16(pf_att, pf_xb, (int64_t)n * qd, s));
+    if (!pos_arr && use_fa_prefill) {  // one sequence, causal: tensor-core attention, bf16 straight into the GEMM operand
+      B200_CUDA(launch_attn_prefill(pf_q, L.k_cache, L.v_cache, table, pf_xb, n, 0, c.n_heads, c.n_kv_heads, s));
+    } else {                            // one row per sequence (batched decode): the split-KV decode kernel, a query per z
+      AttnArgs t = {};
+      t.q = pf_q; t.k_cache = L.k_cache; t.v_cache = L.v_cache; t.block_table = table; t.st = nullptr;
+      t.n_heads = c.n_heads; t.n_kv_heads = c.n_kv_heads; t.out = pf_att; t.partial = pf_partial; t.counters = pf_counters;
+      t.n_splits = pf_splits; t.fixed_ctx = 1; t.n_queries = n; t.q_stride = qd;
+      t.q_ctx = ctx_arr; t.q_slot = slot_arr; t.pages_per_seq = pages_per_seq;
+      B200_CUDA(launch_attn_decode(t, s, false));
+      B200_CUDA(launch_f32_to_bf16(pf_att, pf_xb, (int64_t)n * qd, s));
+    }
     B200_CUDA(launch_gemm_bf16(L.o16, d, qd, pf_xb, n, pf_proj, d, s));
     if (tp_size > 1) { int rc = tp_allreduce_sum(pf_proj, (size_t)n * d, s); if (rc) return rc; }
     B200_CUDA(launch_add_rmsnorm_bf16(pf_x, pf_proj, L.ffn_norm, pf_xb, n, d, c.rms_eps, s));

@@ -166,6 +166,10 @@ cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const u
                              int64_t ldy, cudaStream_t s);
 bool gemm_shape_ok(int64_t rows, int64_t K, int64_t n_tokens);
 
+// causal attention over a whole prompt on the tensor cores (attn_prefill.cu); out is bf16 [T][n_heads*128]
+cudaError_t launch_attn_prefill(const float* q, const uint16_t* k_cache, const uint16_t* v_cache, const int32_t* block_table, uint16_t* out,
+                                int T, int pos0, int n_heads, int n_kv_heads, cudaStream_t s);
+
 // element-wise kernels of the prefill / batched pass (prefill.cu)
 cudaError_t launch_embed_tokens(const uint8_t* embd, int embd_type, int d_model, const int32_t* tokens_dev, int n, float* x, cudaStream_t s);
 cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, const float* w, uint16_t* xb, int tokens, int d, float eps, cudaStream_t s);
