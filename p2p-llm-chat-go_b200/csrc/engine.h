@@ -110,6 +110,9 @@ struct Engine {
   float* pf_partial = nullptr;
   unsigned int* pf_counters = nullptr;
   int pf_splits = 4;
+  int pf_rows = 0;             // rows the work buffers were sized for
+  int pf_proj_splits = 1;      // split-K partials currently sitting in pf_proj (consumers add them)
+  const float* proj2() const { return pf_proj_splits == 2 ? pf_proj + (size_t)pf_rows * cfg.d_model : nullptr; }
 
   // sequence slots (continuous batching): slot s statically owns block-table row s
   struct Seq {

@@ -71,7 +71,8 @@ struct GemmArgs {
   float* y;
   int ldy;       // floats between consecutive tokens of y
   int n_tokens;  // valid tokens (TMA zero-fills the rest of a token tile)
-  int k_blocks;  // K / 64
+  int k_blocks;  // K / 64 blocks handled by ONE CTA (split-K: blockIdx.z picks which run of them)
+  long long split_stride;  // floats between the partial outputs of consecutive K splits
 };
 
 template <int BN>
@@ -91,6 +92,7 @@ __global__ void __launch_bounds__(192) gemm_bf16_kernel(const __grid_constant__ 
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+  const int kb0 = blockIdx.z * g.k_blocks;  // split-K: this CTA's first K block
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < C::STAGES; ++s) {
@@ -117,8 +119,8 @@ __global__ void __launch_bounds__(192) gemm_bf16_kernel(const __grid_constant__ 
         mbar_wait(empty_s + 8 * s, ph ^ 1);
         const uint32_t dst = tiles + s * C::STAGE;
         mbar_expect_tx(full_s + 8 * s, C::STAGE);
-        tma_load_2d(dst, &tmA, kb * BK, m0, full_s + 8 * s);
-        tma_load_2d(dst + A_BYTES, &tmB, kb * BK, n0, full_s + 8 * s);
+        tma_load_2d(dst, &tmA, (kb0 + kb) * BK, m0, full_s + 8 * s);
+        tma_load_2d(dst + A_BYTES, &tmB, (kb0 + kb) * BK, n0, full_s + 8 * s);
         if (++s == C::STAGES) { s = 0; ph ^= 1; }
       }
     }
@@ -161,7 +163,7 @@ __global__ void __launch_bounds__(192) gemm_bf16_kernel(const __grid_constant__ 
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
         const int tok = n0 + c * 32 + j;
-        if (tok < g.n_tokens) g.y[(size_t)tok * g.ldy + row] = __uint_as_float(v[j]);
+        if (tok < g.n_tokens) g.y[(size_t)blockIdx.z * g.split_stride + (size_t)tok * g.ldy + row] = __uint_as_float(v[j]);
       }
     }
   }
@@ -199,7 +201,7 @@ bool make_map(CUtensorMap* m, const void* base, uint64_t rows, uint64_t K, uint3
 
 template <int BN>
 cudaError_t launch_bn(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y, int64_t ldy,
-                      cudaStream_t s) {
+                      int splits, int64_t split_stride, cudaStream_t s) {
   CUtensorMap ma, mb;
   if (!make_map(&ma, W, (uint64_t)rows, (uint64_t)K, BM) || !make_map(&mb, X, (uint64_t)n_tokens, (uint64_t)K, BN))
     return cudaErrorInvalidValue;
@@ -207,8 +209,8 @@ cudaError_t launch_bn(const uint16_t* W, int64_t rows, int64_t K, const uint16_t
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmCfg<BN>::SMEM);
   if (e != cudaSuccess) return e;
   GemmArgs g;
-  g.y = Y; g.ldy = (int)ldy; g.n_tokens = (int)n_tokens; g.k_blocks = (int)(K / BK);
-  dim3 grid((unsigned)(rows / BM), (unsigned)((n_tokens + BN - 1) / BN));
+  g.y = Y; g.ldy = (int)ldy; g.n_tokens = (int)n_tokens; g.k_blocks = (int)(K / BK) / splits; g.split_stride = split_stride;
+  dim3 grid((unsigned)(rows / BM), (unsigned)((n_tokens + BN - 1) / BN), (unsigned)splits);
   kern<<<grid, 192, GemmCfg<BN>::SMEM, s>>>(ma, mb, g);
   return cudaGetLastError();
 }
@@ -222,11 +224,24 @@ bool gemm_shape_ok(int64_t rows, int64_t K, int64_t n_tokens) {
 // Y[t*ldy + r] = sum_k X[t][k] W[r][k];  W, X bf16 (K-major, 16-byte aligned rows), Y fp32.
 cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
                              int64_t ldy, cudaStream_t s) {
+  int splits = 1;
+  return launch_gemm_bf16_splitk(W, rows, K, X, n_tokens, Y, ldy, 0, &splits, s);
+}
+
+// Same, but a GEMM with too few output tiles to fill the GPU may split K in two: partial p is written to
+// Y + p*split_stride and the caller adds the partials (deterministically) where it consumes Y.
+// *splits: in = maximum allowed (1 or 2), out = what was used.
+cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
+                                    int64_t ldy, int64_t split_stride, int* splits, cudaStream_t s) {
   if (!gemm_shape_ok(rows, K, n_tokens)) return cudaErrorInvalidValue;
   // token tile: 256 when that still yields >= 2 CTAs per SM of work, else 128 (more, smaller tiles)
   const int64_t tiles256 = (rows / BM) * ((n_tokens + 255) / 256);
-  if (n_tokens > 128 && tiles256 >= 296) return launch_bn<256>(W, rows, K, X, n_tokens, Y, ldy, s);
-  return launch_bn<128>(W, rows, K, X, n_tokens, Y, ldy, s);
+  const int64_t tiles128 = (rows / BM) * ((n_tokens + 127) / 128);
+  int use = 1;
+  if (*splits >= 2 && tiles128 < 296 && tiles128 >= 32 && (K / BK) % 2 == 0 && K >= 2048) use = 2;
+  *splits = use;
+  if (n_tokens > 128 && tiles256 >= 296) return launch_bn<256>(W, rows, K, X, n_tokens, Y, ldy, 1, 0, s);
+  return launch_bn<128>(W, rows, K, X, n_tokens, Y, ldy, use, split_stride, s);
 }
 
 }  // namespace b200

@@ -164,6 +164,8 @@ cudaError_t launch_add_inplace(float* x, const float* y, int n, cudaStream_t s);
 // tcgen05/TMEM bf16 GEMM (gemm.cu): Y[t*ldy + r] = sum_k X[t][k] W[r][k], fp32 out
 cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
                              int64_t ldy, cudaStream_t s);
+cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
+                                    int64_t ldy, int64_t split_stride, int* splits, cudaStream_t s);
 bool gemm_shape_ok(int64_t rows, int64_t K, int64_t n_tokens);
 
 // causal attention over a whole prompt on the tensor cores (attn_prefill.cu); out is bf16 [T][n_heads*128]
@@ -172,7 +174,8 @@ cudaError_t launch_attn_prefill(const float* q, const uint16_t* k_cache, const u
 
 // element-wise kernels of the prefill / batched pass (prefill.cu)
 cudaError_t launch_embed_tokens(const uint8_t* embd, int embd_type, int d_model, const int32_t* tokens_dev, int n, float* x, cudaStream_t s);
-cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, const float* w, uint16_t* xb, int tokens, int d, float eps, cudaStream_t s);
+cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, const float* add2, const float* w, uint16_t* xb, int tokens, int d, float eps,
+                                    cudaStream_t s);
 cudaError_t launch_rope_kv(const float* qkv, float* q, uint16_t* k_cache, uint16_t* v_cache, const int32_t* block_table, const float* rope,
                            int tokens, int q_rows, int kv_rows, int n_kv_heads, int pos0, const int32_t* pos_arr, const int32_t* slot_arr,
                            int pages_per_seq, cudaStream_t s);
@@ -180,6 +183,6 @@ cudaError_t launch_argmax_rows(const float* logits, int rows, int vocab, int32_t
 cudaError_t launch_append_history(const int32_t* next, const int32_t* slot_arr, const int32_t* pos_arr, int32_t* history, int max_ctx, int rows,
                                   cudaStream_t s);
 cudaError_t launch_swiglu_bf16(const float* gu, uint16_t* h, int64_t n_pairs, cudaStream_t s);
-cudaError_t launch_take_row(const float* x, const float* add, int d, int row, float* out, cudaStream_t s);
+cudaError_t launch_take_row(const float* x, const float* add, const float* add2, int d, int row, float* out, cudaStream_t s);
 
 }  // namespace b200
