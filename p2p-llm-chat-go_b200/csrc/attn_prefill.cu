@@ -44,14 +44,32 @@ template <int G>
 __global__ void __launch_bounds__(G * 32) attn_prefill_kernel(const float* __restrict__ q, const uint16_t* __restrict__ k_cache,
                                                              const uint16_t* __restrict__ v_cache, const int32_t* __restrict__ block_table,
                                                              uint16_t* __restrict__ out, int T, int pos0, int n_heads, int n_kv_heads) {
-  __shared__ __align__(128) uint8_t Ks[kKvTile * 256];
-  __shared__ __align__(128) uint8_t Vs[kKvTile * 256];
-  const int kvh = blockIdx.x, q0 = blockIdx.y * kQRows;
+  extern __shared__ __align__(128) uint8_t tiles[];  // 2 stages x {K tile 16 KB, V tile 16 KB}
+  // heavy blocks first: under the causal mask the last query block does ~T/64 tiles, the first only one
+  const int kvh = blockIdx.x, q0 = (gridDim.y - 1 - blockIdx.y) * kQRows;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const int head = kvh * G + warp, qd = n_heads * kHeadDim;
   const float scale = 1.0f / sqrtf((float)kHeadDim);
   const int rowA = min(q0 + g, T - 1), rowB = min(q0 + g + 8, T - 1);  // clamp: rows past T compute, never store
   const int posA = pos0 + rowA, posB = pos0 + rowB;
+  const int kv_len = pos0 + min(q0 + kQRows, T);  // causal: the last row of this block sees this many tokens
+  const uint32_t tiles_s = smem_u32(tiles);
+
+  // stage `st` <- K/V rows [t0, t0+64) gathered through the block table with 16-byte cp.async (zero-fill past kv_len)
+  auto load_tile = [&](int st, int t0) {
+    const uint32_t kb = tiles_s + st * (2 * kKvTile * 256), vb = kb + kKvTile * 256;
+    for (int item = threadIdx.x; item < kKvTile * 16; item += G * 32) {
+      const int r = item >> 4, c = item & 15, tok = t0 + r;
+      const bool ok = tok < kv_len;
+      const int page = ok ? block_table[tok / kPageTokens] : 0;
+      const size_t row = (((size_t)page * n_kv_heads + kvh) * kPageTokens + (ok ? tok % kPageTokens : 0)) * kHeadDim;
+      const uint32_t n = ok ? 16u : 0u;  // src-size 0: the 16 destination bytes are zero-filled
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(kb + tile_off(r, c)), "l"(k_cache + row + c * 8), "r"(n) : "memory");
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(vb + tile_off(r, c)), "l"(v_cache + row + c * 8), "r"(n) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  load_tile(0, 0);
 
   // Q fragments (A operand), hi and lo parts: 8 k-steps of 16 dims
   uint32_t qh[8][4], ql[8][4];
@@ -73,23 +91,16 @@ __global__ void __launch_bounds__(G * 32) attn_prefill_kernel(const float* __res
   for (int j = 0; j < 16; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
   float mA = -INFINITY, mB = -INFINITY, lA = 0.f, lB = 0.f;
 
-  const int kv_len = pos0 + min(q0 + kQRows, T);  // causal: the last row of this block sees this many tokens
-  const uint32_t ks = smem_u32(Ks), vs = smem_u32(Vs);
-  for (int t0 = 0; t0 < kv_len; t0 += kKvTile) {
-    __syncthreads();  // previous tile fully consumed
-    for (int item = threadIdx.x; item < kKvTile * 16; item += G * 32) {
-      const int r = item >> 4, c = item & 15, tok = t0 + r;
-      uint4 kv = make_uint4(0, 0, 0, 0), vv = make_uint4(0, 0, 0, 0);
-      if (tok < kv_len) {
-        const int page = block_table[tok / kPageTokens];
-        const size_t row = (((size_t)page * n_kv_heads + kvh) * kPageTokens + (tok % kPageTokens)) * kHeadDim;
-        kv = *reinterpret_cast<const uint4*>(k_cache + row + c * 8);
-        vv = *reinterpret_cast<const uint4*>(v_cache + row + c * 8);
-      }
-      *reinterpret_cast<uint4*>(Ks + tile_off(r, c)) = kv;
-      *reinterpret_cast<uint4*>(Vs + tile_off(r, c)) = vv;
+  int stage = 0;
+  for (int t0 = 0; t0 < kv_len; t0 += kKvTile, stage ^= 1) {
+    if (t0 + kKvTile < kv_len) {  // prefetch the next tile into the other stage, then wait for this one
+      load_tile(stage ^ 1, t0 + kKvTile);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
     }
     __syncthreads();
+    const uint32_t ks = tiles_s + stage * (2 * kKvTile * 256), vs = ks + kKvTile * 256;
 
     // ---- S = (Q*scale) . K^T : 8 n-tiles of 8 tokens
     float s[8][4];
@@ -151,6 +162,7 @@ __global__ void __launch_bounds__(G * 32) attn_prefill_kernel(const float* __res
         mma_bf16(o[jd + 1], pl[kk2], b[2], b[3]);
       }
     }
+    __syncthreads();  // every warp is done with this stage before the next iteration's prefetch overwrites it
   }
   lA += __shfl_xor_sync(0xffffffffu, lA, 1); lA += __shfl_xor_sync(0xffffffffu, lA, 2);
   lB += __shfl_xor_sync(0xffffffffu, lB, 1); lB += __shfl_xor_sync(0xffffffffu, lB, 2);
@@ -173,13 +185,20 @@ cudaError_t launch_attn_prefill(const float* q, const uint16_t* k_cache, const u
                                 int T, int pos0, int n_heads, int n_kv_heads, cudaStream_t s) {
   if (T < 1 || n_kv_heads < 1 || n_heads % n_kv_heads) return cudaErrorInvalidValue;
   dim3 grid(n_kv_heads, (T + kQRows - 1) / kQRows);
+  constexpr int kSmem = 2 * 2 * kKvTile * 256;  // 64 KB
+#define LAUNCH(G_)                                                                                                   \
+  {                                                                                                                  \
+    cudaError_t e_ = cudaFuncSetAttribute(attn_prefill_kernel<G_>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem); \
+    if (e_ != cudaSuccess) return e_;                                                                                \
+    attn_prefill_kernel<G_><<<grid, G_ * 32, kSmem, s>>>
   switch (n_heads / n_kv_heads) {
-    case 1: attn_prefill_kernel<1><<<grid, 32, 0, s>>>(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); break;
-    case 2: attn_prefill_kernel<2><<<grid, 64, 0, s>>>(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); break;
-    case 4: attn_prefill_kernel<4><<<grid, 128, 0, s>>>(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); break;
-    case 8: attn_prefill_kernel<8><<<grid, 256, 0, s>>>(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); break;
+    case 1: LAUNCH(1)(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); } break;
+    case 2: LAUNCH(2)(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); } break;
+    case 4: LAUNCH(4)(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); } break;
+    case 8: LAUNCH(8)(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); } break;
     default: return cudaErrorInvalidValue;
   }
+#undef LAUNCH
   return cudaGetLastError();
 }
 
