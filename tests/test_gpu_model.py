@@ -173,3 +173,25 @@ def test_prefill_gemm_matches_gemv_prefill_closely(pkg):
         b = eng.forward_logits(toks, pkg.MODE_GEMV)
         assert np.abs(a - b).max() <= 0.05 * max(1.0, np.abs(b).max())
         assert np.abs(a - b).max() > 0  # they really are different arithmetic
+
+
+def test_full_size_8b_greedy_prefix(pkg):
+    """BASELINE shape, batch-1 decode path (mode 0): greedy tokens must equal the oracle's at every step up to the
+    first one where the oracle itself is indecisive (top-1/top-2 margin below the logit noise that bf16 KV-cache
+    rounding flips cause at 32 layers, measured 2e-3).  A random-init model has flat logits, so such near-ties do
+    occur within 128 steps; a step that is decisive must never differ."""
+    cfg = pkg.llama31_8b()
+    cfg.weight_format, cfg.seed, cfg.max_ctx, cfg.eos_token = 0, 0, 128, -1
+    n_new = 40
+    with pkg.Engine(cfg) as eng:
+        ora = oracle_from_engine(eng)
+        prompt = np.array([128000, 9906, 1917, 11, 856, 836, 374, 3823], np.int32)
+        ids, _, _ = eng.generate_greedy(prompt, n_new, pkg.MODE_GEMV)
+        want, margins = ora.generate_greedy(prompt, n_new, prefill_mode=0)
+    scale = 5.0  # |logit| max of this model
+    indecisive = np.nonzero(margins < 4 * LOGIT_TOL * scale)[0]
+    stop = int(indecisive[0]) + 1 if indecisive.size else n_new
+    assert ids[:stop - 1].tolist() == want[:stop - 1].tolist(), (ids, want, margins)
+    if not indecisive.size:
+        assert ids.tolist() == want.tolist()
+    assert stop >= 4, margins  # the check must actually cover some tokens
