@@ -334,7 +334,10 @@ def run_ours(args):
         kv_bytes = 2 * cfg.n_layers * cfg.n_kv_heads * cfg.head_dim * 2 * (N_PROMPT + N_NEW // 2)
         ach = k_bytes / (k_ms * 1e-3) / 1e9
         extra["roofline"] = {"kernel": "gemv_kernel<bf16, rmsnorm, swiglu> (ffn gate/up, 28672x4096)", "bound": "hbm",
-                             "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm, "traffic": None,
+                             "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm,
+                             # dram__bytes_read + dram__bytes_write of this kernel, one launch, ncu --set full
+                             # (profiles/prof_gemv_bf16_r1_raw.csv): 234.94 MB + 3.62 MB vs 234.88 MB algorithmic
+                             "traffic": 238562816,
                              "peak_source": peak_src, "timing": "CUDA events on the engine stream, kernel alone, L2 flushed",
                              "bytes_per_launch": k_bytes, "ms_per_launch": k_ms}
         sach = (wbytes + kv_bytes) / (step_ms * 1e-3) / 1e9
