@@ -346,8 +346,19 @@ func main() {
 	ctx, _ := strconv.Atoi(getenv("LLMD_MAX_CTX", "2048"))
 	seed, _ := strconv.ParseInt(getenv("LLMD_SEED", "0"), 10, 64)
 	cfg.device, cfg.max_ctx, cfg.seed = C.int32_t(gpu), C.int32_t(ctx), C.int64_t(seed)
-	if C.b200_init(&cfg, &engine) != 0 {
-		log.Fatalf("llmd: engine init failed: %v", lastError())
+	seqs, _ := strconv.Atoi(getenv("LLMD_MAX_SEQS", "8"))
+	if path := os.Getenv("LLMD_GGUF"); path != "" { // a real model file, e.g. the blob `ollama pull llama3.1` stored
+		cpath := C.CString(path)
+		defer C.free(unsafe.Pointer(cpath))
+		if C.b200_load_gguf(cpath, cfg.device, cfg.max_ctx, C.int(seqs), &engine) != 0 {
+			log.Fatalf("llmd: loading %s failed: %v", path, lastError())
+		}
+		C.b200_get_config(engine, &cfg)
+	} else {
+		cfg.max_seqs = C.int32_t(seqs)
+		if C.b200_init(&cfg, &engine) != 0 {
+			log.Fatalf("llmd: engine init failed: %v", lastError())
+		}
 	}
 	defer C.b200_shutdown(engine)
 

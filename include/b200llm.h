@@ -131,6 +131,18 @@ B200_API int b200_tokenize(b200_engine* e, const char* utf8, size_t n, int add_b
                            size_t* n_out);
 B200_API int b200_detokenize(b200_engine* e, const int32_t* ids, size_t n, char* buf, size_t cap, size_t* n_out);
 
+/* ---- GGUF model files (what `ollama pull llama3.1` leaves on disk, README.md:70) ---------------------- */
+/* Reads shapes, storage types and the tokenizer vocabulary from a GGUF v2/v3 file of architecture "llama"
+ * and uploads every tensor (BF16, Q4_K, Q6_K matrices; F32 norms; the file dictates each tensor's type).
+ * b200_gguf_info needs no GPU.  A stand-alone tokenizer handle is offered for hosts that tokenise elsewhere. */
+typedef struct b200_tok b200_tok;
+B200_API int b200_gguf_info(const char* path, b200_config* cfg, int64_t* n_tensors, int64_t* n_vocab_tokens, int64_t* n_merges);
+B200_API int b200_load_gguf(const char* path, int device, int max_ctx, int max_seqs, b200_engine** out);
+B200_API int b200_tok_load_gguf(const char* path, b200_tok** out);
+B200_API void b200_tok_free(b200_tok* t);
+B200_API int b200_tok_encode(const b200_tok* t, const char* utf8, size_t n, int add_bos, int32_t* ids, size_t cap, size_t* n_out);
+B200_API int b200_tok_decode(const b200_tok* t, const int32_t* ids, size_t n, char* buf, size_t cap, size_t* n_out);
+
 /* ---- generation (replaces: the body of Ollama's /api/generate that web/streamlit_app.py:91 waits on) - */
 B200_API int b200_submit(b200_engine* e, const int32_t* prompt_ids, size_t n, const b200_sampling* s,
                          b200_req** out);

@@ -85,6 +85,12 @@ def lib():
         "b200_weight_bytes": (i64, [vp]),
         "b200_tokenize": (i32, [vp, C.c_char_p, sz, i32, vp, sz, C.POINTER(sz)]),
         "b200_detokenize": (i32, [vp, vp, sz, vp, sz, C.POINTER(sz)]),
+        "b200_gguf_info": (i32, [C.c_char_p, cfgp, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64)]),
+        "b200_load_gguf": (i32, [C.c_char_p, i32, i32, i32, C.POINTER(vp)]),
+        "b200_tok_load_gguf": (i32, [C.c_char_p, C.POINTER(vp)]),
+        "b200_tok_free": (None, [vp]),
+        "b200_tok_encode": (i32, [vp, C.c_char_p, sz, i32, vp, sz, C.POINTER(sz)]),
+        "b200_tok_decode": (i32, [vp, vp, sz, vp, sz, C.POINTER(sz)]),
         "b200_submit": (i32, [vp, vp, sz, smpp, C.POINTER(vp)]),
         "b200_next": (i32, [vp, C.POINTER(C.c_int32), C.POINTER(i32), i32]),
         "b200_stats_get": (i32, [vp, C.POINTER(Stats)]),
@@ -242,6 +248,41 @@ class Request:
             pass
 
 
+def gguf_info(path):
+    """(config, n_tensors, n_vocab_tokens, n_merges) of a GGUF file; needs no GPU."""
+    cfg, a, b, c = Config(), C.c_int64(), C.c_int64(), C.c_int64()
+    _check(lib().b200_gguf_info(path.encode(), C.byref(cfg), C.byref(a), C.byref(b), C.byref(c)))
+    return cfg, a.value, b.value, c.value
+
+
+class Tok:
+    """Stand-alone tokenizer handle over a GGUF vocabulary."""
+
+    def __init__(self, path):
+        self.h = C.c_void_p()
+        _check(lib().b200_tok_load_gguf(path.encode(), C.byref(self.h)))
+
+    def encode(self, text, add_bos=False):
+        b = text.encode()
+        ids = np.empty(len(b) + 8, np.int32)
+        n = C.c_size_t()
+        _check(lib().b200_tok_encode(self.h, b, len(b), int(add_bos), _p(ids), ids.size, C.byref(n)))
+        return ids[:n.value].tolist()
+
+    def decode(self, ids):
+        ids = _c(ids, np.int32)
+        buf = C.create_string_buffer(max(16, ids.size * 64))
+        n = C.c_size_t()
+        _check(lib().b200_tok_decode(self.h, _p(ids), ids.size, buf, len(buf), C.byref(n)))
+        return buf.raw[:n.value].decode(errors="replace")
+
+    def __del__(self):
+        try:
+            lib().b200_tok_free(self.h)
+        except Exception:
+            pass
+
+
 def tp_unique_id():
     """128-byte NCCL id (rank 0 creates it; the host hands it to every rank)."""
     buf = C.create_string_buffer(128)
@@ -258,6 +299,15 @@ class Engine:
         else:
             _check(lib().b200_init(C.byref(cfg), C.byref(h)))
         self.h, self.cfg = h, cfg
+
+    @classmethod
+    def from_gguf(cls, path, device=0, max_ctx=2048, max_seqs=1):
+        self = cls.__new__(cls)
+        h = C.c_void_p()
+        _check(lib().b200_load_gguf(path.encode(), device, max_ctx, max_seqs, C.byref(h)))
+        self.h, self.cfg = h, Config()
+        _check(lib().b200_get_config(h, C.byref(self.cfg)))
+        return self
 
     def close(self):
         if self.h:

@@ -4,12 +4,11 @@
 #include <cstring>
 
 #include "engine.h"
+#include "gguf.h"
 
 namespace b200 {
 int tp_unique_id(void* out128);
 const char* last_error();
-int tokenizer_encode(const b200_config& cfg, const char* utf8, size_t n, int add_bos, int32_t* ids, size_t cap, size_t* n_out);
-int tokenizer_decode(const b200_config& cfg, const int32_t* ids, size_t n, char* buf, size_t cap, size_t* n_out);
 }  // namespace b200
 
 using namespace b200;
@@ -212,15 +211,147 @@ int b200_get_tensor(b200_engine* h, const char* name, void* buf, int64_t cap) {
 
 int64_t b200_weight_bytes(const b200_engine* h) { return h ? reinterpret_cast<const Engine*>(h)->weight_bytes : 0; }
 
+static int tok_encode(const Tokenizer& tk, int32_t vocab, const char* utf8, size_t n, int add_bos, int32_t* ids, size_t cap, size_t* n_out) {
+  std::vector<int32_t> v;
+  tk.encode(utf8, n, add_bos != 0, vocab, &v);
+  *n_out = v.size();
+  if (v.size() > cap || (v.size() && !ids)) { set_error("tokenize: need room for %zu ids", v.size()); return B200_ERANGE; }
+  if (!v.empty()) memcpy(ids, v.data(), v.size() * 4);
+  return 0;
+}
+static int tok_decode(const Tokenizer& tk, const int32_t* ids, size_t n, char* buf, size_t cap, size_t* n_out) {
+  std::string s;
+  tk.decode(ids, n, &s);
+  *n_out = s.size();
+  if (s.size() > cap || (s.size() && !buf)) { set_error("detokenize: need room for %zu bytes", s.size()); return B200_ERANGE; }
+  if (!s.empty()) memcpy(buf, s.data(), s.size());
+  return 0;
+}
+
 int b200_tokenize(b200_engine* h, const char* utf8, size_t n, int add_bos, int32_t* ids, size_t cap, size_t* n_out) {
   Engine* e = reinterpret_cast<Engine*>(h);
   if (!e || (!utf8 && n) || !n_out) { set_error("null argument"); return B200_EINVAL; }
-  return tokenizer_encode(e->cfg, utf8, n, add_bos, ids, cap, n_out);
+  return tok_encode(e->tok, e->cfg.vocab, utf8, n, add_bos, ids, cap, n_out);
 }
 int b200_detokenize(b200_engine* h, const int32_t* ids, size_t n, char* buf, size_t cap, size_t* n_out) {
   Engine* e = reinterpret_cast<Engine*>(h);
   if (!e || (!ids && n) || !n_out) { set_error("null argument"); return B200_EINVAL; }
-  return tokenizer_decode(e->cfg, ids, n, buf, cap, n_out);
+  return tok_decode(e->tok, ids, n, buf, cap, n_out);
+}
+
+// ---- GGUF ----------------------------------------------------------------------------------------------
+struct TokHandle { Tokenizer tok; int32_t vocab = 1 << 30; };
+
+static int gguf_config(const GgufFile& f, b200_config* cfg, int64_t* n_tensors) {
+  const std::string arch = f.get_s("general.architecture", "");
+  if (arch != "llama") { set_error("GGUF architecture '%s' is not supported (llama only)", arch.c_str()); return B200_EINVAL; }
+  b200_llama31_8b(cfg);
+  cfg->n_layers = (int32_t)f.get_u("llama.block_count", 0);
+  cfg->d_model = (int32_t)f.get_u("llama.embedding_length", 0);
+  cfg->n_heads = (int32_t)f.get_u("llama.attention.head_count", 0);
+  cfg->n_kv_heads = (int32_t)f.get_u("llama.attention.head_count_kv", (uint64_t)cfg->n_heads);
+  cfg->d_ffn = (int32_t)f.get_u("llama.feed_forward_length", 0);
+  cfg->head_dim = (int32_t)f.get_u("llama.attention.key_length", cfg->n_heads ? (uint64_t)(cfg->d_model / cfg->n_heads) : 0);
+  cfg->rms_eps = (float)f.get_f("llama.attention.layer_norm_rms_epsilon", 1e-5);
+  cfg->rope_theta = (float)f.get_f("llama.rope.freq_base", 10000.0);
+  const GgufTensor* emb = f.tensor("token_embd.weight");
+  const GgufValue* toks = f.kv("tokenizer.ggml.tokens");
+  cfg->vocab = (int32_t)f.get_u("llama.vocab_size", toks ? toks->strs.size() : (emb && emb->ne.size() == 2 ? (uint64_t)emb->ne[1] : 0));
+  // Llama-3.1 files carry the "llama3" RoPE scaling as a rope_freqs tensor; its parameters are the published ones
+  if (f.tensor("rope_freqs.weight")) { cfg->rope_factor = 8.0f; cfg->rope_low_freq_factor = 1.0f; cfg->rope_high_freq_factor = 4.0f; cfg->rope_orig_ctx = 8192; }
+  else cfg->rope_factor = 1.0f;
+  cfg->eos_token = (int32_t)f.get_u("tokenizer.ggml.eos_token_id", 128009);
+  cfg->seed = -1;
+  const GgufTensor* q = f.tensor("blk.0.attn_q.weight");
+  if (!q) { set_error("GGUF file has no blk.0.attn_q.weight"); return B200_EINVAL; }
+  cfg->weight_format = q->type == T_BF16 ? B200_WEIGHTS_BF16 : B200_WEIGHTS_Q4_K_M;
+  if (n_tensors) *n_tensors = (int64_t)f.tensors().size();
+  return 0;
+}
+
+int b200_gguf_info(const char* path, b200_config* cfg, int64_t* n_tensors, int64_t* n_vocab_tokens, int64_t* n_merges) {
+  if (!path || !cfg) { set_error("null argument"); return B200_EINVAL; }
+  GgufFile f;
+  const std::string err = f.open(path);
+  if (!err.empty()) { set_error("%s", err.c_str()); return B200_EINVAL; }
+  const GgufValue* toks = f.kv("tokenizer.ggml.tokens");
+  const GgufValue* mg = f.kv("tokenizer.ggml.merges");
+  if (n_vocab_tokens) *n_vocab_tokens = toks ? (int64_t)toks->strs.size() : 0;
+  if (n_merges) *n_merges = mg ? (int64_t)mg->strs.size() : 0;
+  return gguf_config(f, cfg, n_tensors);
+}
+
+int b200_load_gguf(const char* path, int device, int max_ctx, int max_seqs, b200_engine** out) {
+  if (!path || !out) { set_error("null argument"); return B200_EINVAL; }
+  *out = nullptr;
+  GgufFile f;
+  const std::string err = f.open(path);
+  if (!err.empty()) { set_error("%s", err.c_str()); return B200_EINVAL; }
+  b200_config cfg;
+  int rc = gguf_config(f, &cfg, nullptr);
+  if (rc) return rc;
+  cfg.device = device; cfg.max_ctx = max_ctx > 0 ? max_ctx : 2048; cfg.max_seqs = max_seqs > 0 ? max_seqs : 1;
+  Engine* e = new (std::nothrow) Engine();
+  if (!e) return B200_ENOMEM;
+  for (const GgufTensor& t : f.tensors())
+    if (t.ne.size() == 2) e->type_override[t.name] = (int)t.type;  // the file dictates every matrix's storage type
+  if (f.kv("tokenizer.ggml.tokens")) {
+    const std::string terr = e->tok.load(f);
+    if (!terr.empty()) { set_error("%s", terr.c_str()); delete e; return B200_EINVAL; }
+  }
+  if ((rc = e->init(cfg))) { delete e; return rc; }
+  {
+    std::lock_guard<std::mutex> lk(e->mu);
+    size_t maxb = 0;
+    for (auto& kv : e->slots) maxb = std::max(maxb, (size_t)kv.second.full_rows * (kv.second.type == T_F32 ? (size_t)kv.second.full_cols * 4 : gemv_row_bytes(kv.second.type, kv.second.full_cols)));
+    DevBuf tmp;
+    if ((rc = tmp.alloc(maxb))) { delete e; return rc; }
+    for (auto& kv : e->slots) {
+      Slot& s = kv.second;
+      const GgufTensor* t = f.tensor(kv.first);
+      if (!t) { set_error("GGUF file lacks tensor '%s'", kv.first.c_str()); delete e; return B200_EINVAL; }
+      const int64_t cols = t->ne.empty() ? 0 : t->ne[0], rows = t->ne.size() > 1 ? t->ne[1] : 1;
+      if ((int)t->type != s.type || rows * cols != s.full_rows * s.full_cols || (s.full_rows != 1 && cols != s.full_cols)) {
+        set_error("GGUF tensor '%s': type %u shape %lldx%lld, engine expects type %d shape %lldx%lld", kv.first.c_str(), t->type,
+                  (long long)rows, (long long)cols, s.type, (long long)s.full_rows, (long long)s.full_cols);
+        delete e;
+        return B200_EINVAL;
+      }
+      cudaError_t ce = cudaMemcpyAsync(tmp.p, f.data(*t), t->nbytes, cudaMemcpyHostToDevice, e->stream);
+      if (ce != cudaSuccess) { rc = cuda_fail(ce, "gguf upload"); delete e; return rc; }
+      if ((rc = e->place_tensor(s, tmp.as<uint8_t>()))) { delete e; return rc; }
+      ce = cudaStreamSynchronize(e->stream);
+      if (ce != cudaSuccess) { rc = cuda_fail(ce, "gguf place"); delete e; return rc; }
+      s.set = true;
+    }
+  }
+  *out = reinterpret_cast<b200_engine*>(e);
+  return 0;
+}
+
+int b200_tok_load_gguf(const char* path, b200_tok** out) {
+  if (!path || !out) { set_error("null argument"); return B200_EINVAL; }
+  GgufFile f;
+  const std::string err = f.open(path);
+  if (!err.empty()) { set_error("%s", err.c_str()); return B200_EINVAL; }
+  TokHandle* h = new (std::nothrow) TokHandle();
+  if (!h) return B200_ENOMEM;
+  const std::string terr = h->tok.load(f);
+  if (!terr.empty()) { set_error("%s", terr.c_str()); delete h; return B200_EINVAL; }
+  h->vocab = (int32_t)h->tok.vocab_size();
+  *out = reinterpret_cast<b200_tok*>(h);
+  return 0;
+}
+void b200_tok_free(b200_tok* t) { delete reinterpret_cast<TokHandle*>(t); }
+int b200_tok_encode(const b200_tok* t, const char* utf8, size_t n, int add_bos, int32_t* ids, size_t cap, size_t* n_out) {
+  const TokHandle* h = reinterpret_cast<const TokHandle*>(t);
+  if (!h || (!utf8 && n) || !n_out) { set_error("null argument"); return B200_EINVAL; }
+  return tok_encode(h->tok, h->vocab, utf8, n, add_bos, ids, cap, n_out);
+}
+int b200_tok_decode(const b200_tok* t, const int32_t* ids, size_t n, char* buf, size_t cap, size_t* n_out) {
+  const TokHandle* h = reinterpret_cast<const TokHandle*>(t);
+  if (!h || (!ids && n) || !n_out) { set_error("null argument"); return B200_EINVAL; }
+  return tok_decode(h->tok, ids, n, buf, cap, n_out);
 }
 
 int b200_submit(b200_engine* h, const int32_t* prompt_ids, size_t n, const b200_sampling* s, b200_req** out) {

@@ -141,20 +141,28 @@ int Engine::init(const b200_config& c, const void* nccl_id) {
     slots[name] = s;
   };
 
+  // storage type of a tensor: what a GGUF file says (type_override, filled by the loader) or the recipe
+  auto ty = [&](const std::string& name, int recipe) {
+    auto it = type_override.find(name);
+    return it == type_override.end() ? recipe : it->second;
+  };
   layers.resize(c.n_layers);
   weight_bytes = 0;
   for (int l = 0; l < c.n_layers; ++l) {
     Layer& L = layers[l];
-    const int tv = (q4 && more_bits(l, c.n_layers)) ? T_Q6_K : tmat;
-    const int tdown = tv;
-    int rc;
-    if ((rc = need(tmat, qd + kvd, d, "attn_q/k")) || (rc = need(tv, kvd, d, "attn_v")) || (rc = need(tmat, d, qd, "attn_output")) ||
-        (rc = need(tmat, 2 * ff, d, "ffn_gate/up")) || (rc = need(tdown, d, ff, "ffn_down")))
-      return rc;
     const std::string p = "blk." + std::to_string(l) + ".";
-    L.qkv_type = tmat;
-    const size_t rb = gemv_row_bytes(tmat, d);
-    if (tv == tmat) {
+    const int t_more = (q4 && more_bits(l, c.n_layers)) ? T_Q6_K : tmat;
+    const int tq = ty(p + "attn_q.weight", tmat), tk = ty(p + "attn_k.weight", tmat), tv = ty(p + "attn_v.weight", t_more);
+    const int to = ty(p + "attn_output.weight", tmat), tg = ty(p + "ffn_gate.weight", tmat), tu = ty(p + "ffn_up.weight", tmat);
+    const int tdown = ty(p + "ffn_down.weight", t_more);
+    if (tq != tk || tg != tu) { set_error("layer %d: attn_q/attn_k (and ffn_gate/ffn_up) must share a storage type", l); return B200_EINVAL; }
+    int rc;
+    if ((rc = need(tq, qd + kvd, d, "attn_q/k")) || (rc = need(tv, kvd, d, "attn_v")) || (rc = need(to, d, qd, "attn_output")) ||
+        (rc = need(tg, 2 * ff, d, "ffn_gate/up")) || (rc = need(tdown, d, ff, "ffn_down")))
+      return rc;
+    L.qkv_type = tq;
+    const size_t rb = gemv_row_bytes(tq, d);
+    if (tv == tq) {
       if ((rc = alloc((void**)&L.qkv, (size_t)(qd + 2 * kvd) * rb))) return rc;
       add_slot(p + "attn_v.weight", tv, kvd, d, L.qkv, qd + kvd, 1, KVD, d, (int64_t)R * kvd, 0);
     } else {
@@ -163,37 +171,39 @@ int Engine::init(const b200_config& c, const void* nccl_id) {
       L.v_type = tv;
       add_slot(p + "attn_v.weight", tv, kvd, d, L.v, 0, 1, KVD, d, (int64_t)R * kvd, 0);
     }
-    add_slot(p + "attn_q.weight", tmat, qd, d, L.qkv, 0, 1, QD, d, (int64_t)R * qd, 0);
-    add_slot(p + "attn_k.weight", tmat, kvd, d, L.qkv, qd, 1, KVD, d, (int64_t)R * kvd, 0);
-    L.o_type = tmat;
-    if ((rc = alloc((void**)&L.o, (size_t)d * gemv_row_bytes(tmat, qd)))) return rc;
-    add_slot(p + "attn_output.weight", tmat, d, qd, L.o, 0, 1, d, QD, 0, (int64_t)R * qd);
-    L.gu_type = tmat;
-    if ((rc = alloc((void**)&L.gate_up, (size_t)2 * ff * rb))) return rc;
-    add_slot(p + "ffn_gate.weight", tmat, ff, d, L.gate_up, 0, 2, FF, d, (int64_t)R * ff, 0);
-    add_slot(p + "ffn_up.weight", tmat, ff, d, L.gate_up, 1, 2, FF, d, (int64_t)R * ff, 0);
+    add_slot(p + "attn_q.weight", tq, qd, d, L.qkv, 0, 1, QD, d, (int64_t)R * qd, 0);
+    add_slot(p + "attn_k.weight", tq, kvd, d, L.qkv, qd, 1, KVD, d, (int64_t)R * kvd, 0);
+    L.o_type = to;
+    if ((rc = alloc((void**)&L.o, (size_t)d * gemv_row_bytes(to, qd)))) return rc;
+    add_slot(p + "attn_output.weight", to, d, qd, L.o, 0, 1, d, QD, 0, (int64_t)R * qd);
+    L.gu_type = tg;
+    const size_t rbg = gemv_row_bytes(tg, d);
+    if ((rc = alloc((void**)&L.gate_up, (size_t)2 * ff * rbg))) return rc;
+    add_slot(p + "ffn_gate.weight", tg, ff, d, L.gate_up, 0, 2, FF, d, (int64_t)R * ff, 0);
+    add_slot(p + "ffn_up.weight", tg, ff, d, L.gate_up, 1, 2, FF, d, (int64_t)R * ff, 0);
     L.down_type = tdown;
     if ((rc = alloc((void**)&L.down, (size_t)d * gemv_row_bytes(tdown, ff)))) return rc;
     add_slot(p + "ffn_down.weight", tdown, d, ff, L.down, 0, 1, d, FF, 0, (int64_t)R * ff);
     if ((rc = alloc((void**)&L.attn_norm, (size_t)d * 4)) || (rc = alloc((void**)&L.ffn_norm, (size_t)d * 4))) return rc;
     add_slot(p + "attn_norm.weight", T_F32, 1, d, (uint8_t*)L.attn_norm, 0, 1);
     add_slot(p + "ffn_norm.weight", T_F32, 1, d, (uint8_t*)L.ffn_norm, 0, 1);
-    weight_bytes += (int64_t)(qd + kvd) * rb + (int64_t)kvd * gemv_row_bytes(tv, d) + (int64_t)d * gemv_row_bytes(tmat, qd) +
-                    (int64_t)2 * ff * rb + (int64_t)d * gemv_row_bytes(tdown, ff) + 2 * (int64_t)d * 4;
+    weight_bytes += (int64_t)(qd + kvd) * rb + (int64_t)kvd * gemv_row_bytes(tv, d) + (int64_t)d * gemv_row_bytes(to, qd) +
+                    (int64_t)2 * ff * rbg + (int64_t)d * gemv_row_bytes(tdown, ff) + 2 * (int64_t)d * 4;
   }
   {
     int rc;
-    embd_type = tmat;
-    if (tmat == T_Q4_K && d % QK_K) { set_error("d_model must be a multiple of 256 for Q4_K embeddings"); return B200_EINVAL; }
-    if ((rc = need(tbig, voc, d, "output"))) return rc;
-    if ((rc = alloc((void**)&token_embd, (size_t)c.vocab * tensor_row_bytes(tmat, d)))) return rc;
-    add_slot("token_embd.weight", tmat, c.vocab, d, token_embd, 0, 1);
-    output_type = tbig;
-    if ((rc = alloc((void**)&output, (size_t)voc * gemv_row_bytes(tbig, d)))) return rc;
-    add_slot("output.weight", tbig, voc, d, output, 0, 1, VOC, d, (int64_t)R * voc, 0);
+    embd_type = ty("token_embd.weight", tmat);
+    const int tout = ty("output.weight", tbig);
+    if (embd_type != T_BF16 && d % QK_K) { set_error("d_model must be a multiple of 256 for k-quant embeddings"); return B200_EINVAL; }
+    if ((rc = need(tout, voc, d, "output"))) return rc;
+    if ((rc = alloc((void**)&token_embd, (size_t)c.vocab * tensor_row_bytes(embd_type, d)))) return rc;
+    add_slot("token_embd.weight", embd_type, c.vocab, d, token_embd, 0, 1);
+    output_type = tout;
+    if ((rc = alloc((void**)&output, (size_t)voc * gemv_row_bytes(tout, d)))) return rc;
+    add_slot("output.weight", tout, voc, d, output, 0, 1, VOC, d, (int64_t)R * voc, 0);
     if ((rc = alloc((void**)&output_norm, (size_t)d * 4))) return rc;
     add_slot("output_norm.weight", T_F32, 1, d, (uint8_t*)output_norm, 0, 1);
-    weight_bytes += (int64_t)voc * gemv_row_bytes(tbig, d) + (int64_t)d * 4;
+    weight_bytes += (int64_t)voc * gemv_row_bytes(tout, d) + (int64_t)d * 4;
   }
 
   // paged KV pool: page = 16 tokens of one kv head; static ownership (sequence slot s owns a page run)
@@ -574,7 +584,8 @@ int Engine::ensure_prefill() {
     return B200_EINVAL;
   }
   int rc;
-  const bool q4 = c.weight_format == B200_WEIGHTS_Q4_K_M;
+  bool q4 = false;  // any k-quant matrix -> bf16 shadow copies (same fused row order) for the tensor-core path
+  for (auto& L : layers) q4 = q4 || L.qkv_type != T_BF16 || (L.v && L.v_type != T_BF16) || L.o_type != T_BF16 || L.gu_type != T_BF16 || L.down_type != T_BF16;
   if (q4) {
     size_t maxb = 0;
     for (auto& kv : slots) maxb = std::max(maxb, (size_t)kv.second.rows * tensor_row_bytes(kv.second.type, kv.second.cols));
@@ -593,8 +604,12 @@ int Engine::ensure_prefill() {
       for (const Dst& t : dsts) {
         const Slot& s = slots[p + t.name + ".weight"];
         if ((rc = fetch_tensor(s, tmp))) return rc;  // GGUF block order
-        B200_CUDA(launch_dequant(s.type, tmp, s.rows * s.cols / QK_K, nullptr, tmp16, stream));
-        B200_CUDA(cudaMemcpy2DAsync(t.base + (size_t)t.row0 * s.cols, (size_t)t.step * s.cols * 2, tmp16, (size_t)s.cols * 2,
+        const uint16_t* src16 = (const uint16_t*)tmp;  // bf16 tensors are copied as they are
+        if (s.type != T_BF16) {
+          B200_CUDA(launch_dequant(s.type, tmp, s.rows * s.cols / QK_K, nullptr, tmp16, stream));
+          src16 = tmp16;
+        }
+        B200_CUDA(cudaMemcpy2DAsync(t.base + (size_t)t.row0 * s.cols, (size_t)t.step * s.cols * 2, src16, (size_t)s.cols * 2,
                                     (size_t)s.cols * 2, (size_t)s.rows, cudaMemcpyDeviceToDevice, stream));
       }
     }

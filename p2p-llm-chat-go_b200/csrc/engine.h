@@ -14,6 +14,7 @@
 
 #include "../../include/b200llm.h"
 #include "kernels.h"
+#include "tokenizer.h"
 
 namespace b200 {
 
@@ -80,6 +81,8 @@ struct Engine {
   cudaStream_t stream = nullptr;
   std::mutex mu;  // serialises every device-touching entry point
 
+  std::map<std::string, int> type_override;  // per-tensor storage types dictated by a GGUF file (else: the recipe)
+  Tokenizer tok;                              // vocabulary of the GGUF file, or the byte-level fallback
   std::map<std::string, Slot> slots;
   std::vector<Layer> layers;
   uint8_t* token_embd = nullptr; int embd_type = -1;

@@ -12,8 +12,9 @@
 // Errors are a non-200 status with {"error": "..."} — the reference shows "(LLM error)" for any of them
 // (web/streamlit_app.py:99).  Configuration is by environment, like the reference's own services
 // (go/cmd/node/main.go:131-134): LLMD_ADDR (default 127.0.0.1:11434, Ollama's port, web/streamlit_app.py:27),
-// LLMD_MODEL (llama3.1), LLMD_WEIGHTS (bf16|q4_k_m), LLMD_GPU, LLMD_MAX_CTX, LLMD_SEED; LLMD_TINY=layers for
-// a small random-init model in tests.
+// LLMD_MODEL (llama3.1), LLMD_GGUF (path of a real model file; else random-init weights: LLMD_WEIGHTS
+// bf16|q4_k_m, LLMD_SEED), LLMD_GPU, LLMD_MAX_CTX, LLMD_MAX_SEQS (concurrent sequences, continuous batching);
+// LLMD_TINY=layers for a small random-init model in tests.
 #include <arpa/inet.h>
 #include <netinet/in.h>
 #include <netinet/tcp.h>
@@ -344,7 +345,17 @@ int main() {
   g_cfg.device = atoi(env("LLMD_GPU", "0").c_str());
   g_cfg.max_ctx = atoi(env("LLMD_MAX_CTX", "2048").c_str());
   g_cfg.seed = atoll(env("LLMD_SEED", "0").c_str());
-  if (b200_init(&g_cfg, &g_engine) != 0) {
+  const std::string gguf = env("LLMD_GGUF", "");
+  const int max_seqs = atoi(env("LLMD_MAX_SEQS", "8").c_str());
+  int rc;
+  if (!gguf.empty()) {  // a real model file, e.g. the blob `ollama pull llama3.1` stored (README.md:70)
+    rc = b200_load_gguf(gguf.c_str(), g_cfg.device, g_cfg.max_ctx, max_seqs, &g_engine);
+    if (rc == 0) b200_get_config(g_engine, &g_cfg);
+  } else {
+    g_cfg.max_seqs = max_seqs;
+    rc = b200_init(&g_cfg, &g_engine);
+  }
+  if (rc != 0) {
     fprintf(stderr, "llmd: engine init failed: %s\n", b200_last_error());
     return 1;
   }

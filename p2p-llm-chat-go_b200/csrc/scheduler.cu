@@ -39,7 +39,7 @@ int Engine::ensure_batched() {
       (rc = alloc((void**)&sp_arr, S * sizeof(SampleParams))) || (rc = alloc((void**)&b_logits, S * (size_t)c.vocab * 4)))
     return rc;
   B200_CUDA(cudaHostAlloc((void**)&b_next_host, S * 4, cudaHostAllocDefault));
-  if (c.weight_format == B200_WEIGHTS_Q4_K_M) {  // bf16 shadow of the Q6_K lm_head
+  if (output_type != T_BF16) {  // bf16 shadow of a k-quant lm_head
     const Slot& s = slots["output.weight"];
     const size_t bytes = (size_t)s.rows * gemv_row_bytes(s.type, s.cols);
     uint8_t* tmp = nullptr;

@@ -1,60 +1,208 @@
-// tokenizer.cpp — text <-> ids for the HTTP front end.
+// tokenizer.cpp — text <-> ids for the HTTP front end (see tokenizer.h).
 //
-// The reference sends text (web/streamlit_app.py:93) and Ollama tokenises it with the model's own
-// byte-level BPE vocabulary, which ships inside the GGUF file.  No tokenizer asset exists offline, so the
-// synthetic-weight engine uses the byte-level base alphabet of that scheme directly: ids 0..255 are the
-// raw UTF-8 bytes (lossless round trip for any string), Llama-3 special ids keep their published values
-// (128000 <|begin_of_text|>, 128009 <|eot_id|>).  Merges from a real GGUF plug in above this alphabet.
+// The reference sends text (web/streamlit_app.py:93) and Ollama tokenises it with the byte-level BPE
+// vocabulary stored in the model's GGUF file.  When the engine was created from a GGUF file that vocabulary
+// (tokens + merge ranks) is used; a synthetic random-init engine has no merge table and uses the base alphabet
+// of the same scheme directly: ids 0..255 are the raw UTF-8 bytes (lossless round trip for any string).
+#include "tokenizer.h"
+
 #include <cstdio>
 #include <cstring>
 
 #include "../../include/b200llm.h"
+#include "gguf.h"
 
 namespace b200 {
 void set_error(const char* fmt, ...);
 
-int tokenizer_encode(const b200_config& cfg, const char* utf8, size_t n, int add_bos, int32_t* ids, size_t cap, size_t* n_out) {
-  const bool bos = add_bos && cfg.vocab > 128000;
-  const size_t need = n + (bos ? 1 : 0);
-  *n_out = need;
-  if (need > cap || (need && !ids)) {
-    set_error("tokenize: need room for %zu ids", need);
-    return B200_ERANGE;
+namespace {
+
+// GPT-2 bytes_to_unicode: printable bytes map to themselves, the rest to U+0100.. in order.
+struct ByteMap {
+  int cp_of_byte[256];
+  std::unordered_map<int, int> byte_of_cp;
+  ByteMap() {
+    int n = 0;
+    for (int b = 0; b < 256; ++b) {
+      const bool keep = (b >= 33 && b <= 126) || (b >= 161 && b <= 172) || (b >= 174 && b <= 255);
+      cp_of_byte[b] = keep ? b : 256 + n++;
+      byte_of_cp[cp_of_byte[b]] = b;
+    }
   }
-  size_t o = 0;
-  if (bos) ids[o++] = 128000;
-  for (size_t i = 0; i < n; ++i) ids[o++] = (int32_t)(unsigned char)utf8[i] % cfg.vocab;
-  return 0;
+};
+const ByteMap& bytemap() {
+  static ByteMap m;
+  return m;
 }
 
-// Renders ids as text.  Byte tokens give their byte; special ids give nothing; any other id of the synthetic
-// vocabulary (no merge table is loaded) is shown as " t<id>" so that a random-init model still answers with
-// visible, valid UTF-8 text.
-int tokenizer_decode(const b200_config& cfg, const int32_t* ids, size_t n, char* buf, size_t cap, size_t* n_out) {
-  (void)cfg;
-  size_t o = 0;
-  char tmp[24];
-  for (int pass = 0; pass < 2; ++pass) {
-    o = 0;
-    for (size_t i = 0; i < n; ++i) {
-      const int32_t id = ids[i];
-      if (id >= 0 && id < 256) {
-        if (pass) buf[o] = (char)id;
-        ++o;
-      } else if (id >= 256 && id < 128000) {
-        const int m = snprintf(tmp, sizeof tmp, " t%d", id);
-        if (pass) memcpy(buf + o, tmp, (size_t)m);
-        o += (size_t)m;
+// token string in the byte-level unicode alphabet -> raw bytes; false if it uses other code points
+bool unicode_token_to_bytes(const std::string& s, std::string* out) {
+  const ByteMap& m = bytemap();
+  size_t i = 0;
+  while (i < s.size()) {
+    const unsigned char c = (unsigned char)s[i];
+    int cp, len;
+    if (c < 0x80) { cp = c; len = 1; }
+    else if ((c >> 5) == 6 && i + 1 < s.size()) { cp = ((c & 0x1F) << 6) | (s[i + 1] & 0x3F); len = 2; }
+    else if ((c >> 4) == 14 && i + 2 < s.size()) { cp = ((c & 0x0F) << 12) | ((s[i + 1] & 0x3F) << 6) | (s[i + 2] & 0x3F); len = 3; }
+    else return false;
+    auto it = m.byte_of_cp.find(cp);
+    if (it == m.byte_of_cp.end()) return false;
+    out->push_back((char)it->second);
+    i += len;
+  }
+  return true;
+}
+
+inline bool is_letter(unsigned char c) { return (c >= 'a' && c <= 'z') || (c >= 'A' && c <= 'Z') || c >= 0x80; }
+inline bool is_digit(unsigned char c) { return c >= '0' && c <= '9'; }
+inline bool is_space(unsigned char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\r' || c == '\v' || c == '\f'; }
+inline bool is_nl(unsigned char c) { return c == '\n' || c == '\r'; }
+
+std::string merge_key(const std::string& a, const std::string& b) {
+  std::string k;
+  k.reserve(a.size() + b.size() + 5);
+  const uint32_t n = (uint32_t)a.size();
+  k.append((const char*)&n, 4);
+  k += a;
+  k += b;
+  return k;
+}
+
+}  // namespace
+
+// (?i:'s|'t|'re|'ve|'m|'ll|'d) | [^\r\n\p{L}\p{N}]?\p{L}+ | \p{N}{1,3} | ?[^\s\p{L}\p{N}]+[\r\n]* | \s*[\r\n]+ | \s+(?!\S) | \s+
+void pretokenize(const char* t, size_t n, std::vector<std::string>* words) {
+  size_t i = 0;
+  auto U = [&](size_t k) { return (unsigned char)t[k]; };
+  while (i < n) {
+    size_t j = i;
+    // contractions
+    if (U(i) == '\'' && i + 1 < n) {
+      const unsigned char a = U(i + 1) | 0x20, b = i + 2 < n ? (U(i + 2) | 0x20) : 0;
+      size_t len = 0;
+      if (a == 's' || a == 't' || a == 'm' || a == 'd') len = 2;
+      if ((a == 'r' && b == 'e') || (a == 'v' && b == 'e') || (a == 'l' && b == 'l')) len = 3;
+      if (len) { words->emplace_back(t + i, len); i += len; continue; }
+    }
+    // optional single non-letter/digit/newline char, then letters
+    {
+      size_t k = i;
+      if (!is_letter(U(k)) && !is_digit(U(k)) && !is_nl(U(k)) && k + 1 < n && is_letter(U(k + 1))) ++k;
+      if (is_letter(U(k))) {
+        j = k;
+        while (j < n && is_letter(U(j))) ++j;
+        words->emplace_back(t + i, j - i); i = j; continue;
       }
     }
-    if (!pass) {
-      *n_out = o;
-      if (o > cap || (o && !buf)) {
-        set_error("detokenize: need room for %zu bytes", o);
-        return B200_ERANGE;
+    if (is_digit(U(i))) {
+      while (j < n && j - i < 3 && is_digit(U(j))) ++j;
+      words->emplace_back(t + i, j - i); i = j; continue;
+    }
+    {  // optional space, punctuation run, trailing newlines
+      size_t k = i;
+      if (U(k) == ' ' && k + 1 < n && !is_space(U(k + 1)) && !is_letter(U(k + 1)) && !is_digit(U(k + 1))) ++k;
+      if (!is_space(U(k)) && !is_letter(U(k)) && !is_digit(U(k))) {
+        j = k;
+        while (j < n && !is_space(U(j)) && !is_letter(U(j)) && !is_digit(U(j))) ++j;
+        while (j < n && is_nl(U(j))) ++j;
+        words->emplace_back(t + i, j - i); i = j; continue;
       }
+    }
+    // whitespace
+    while (j < n && is_space(U(j))) ++j;
+    size_t last_nl = 0;
+    bool has_nl = false;
+    for (size_t k = i; k < j; ++k)
+      if (is_nl(U(k))) { has_nl = true; last_nl = k; }
+    if (has_nl) { words->emplace_back(t + i, last_nl + 1 - i); i = last_nl + 1; continue; }  // \s*[\r\n]+
+    if (j < n && j - i > 1) --j;  // \s+(?!\S): leave the last space to the following word
+    words->emplace_back(t + i, j - i);
+    i = j;
+  }
+}
+
+std::string Tokenizer::load(const GgufFile& f) {
+  const GgufValue* toks = f.kv("tokenizer.ggml.tokens");
+  if (!toks || toks->strs.empty()) return "no tokenizer.ggml.tokens in the GGUF file";
+  const std::string model = f.get_s("tokenizer.ggml.model", "gpt2");
+  if (model != "gpt2") return "tokenizer model '" + model + "' is not a byte-level BPE (gpt2) vocabulary";
+  const GgufValue* types = f.kv("tokenizer.ggml.token_type");
+  const size_t V = toks->strs.size();
+  id_to_bytes_.assign(V, "");
+  is_special_.assign(V, 0);
+  for (size_t i = 0; i < V; ++i) {
+    const int tt = types && i < types->ints.size() ? (int)types->ints[i] : 1;
+    std::string raw;
+    if (tt == 1 && unicode_token_to_bytes(toks->strs[i], &raw)) {  // normal token
+      id_to_bytes_[i] = raw;
+      bytes_to_id_.emplace(raw, (int32_t)i);
+    } else {
+      is_special_[i] = 1;  // control / user-defined / unused: never produced by encode, rendered as nothing
     }
   }
-  return 0;
+  if (const GgufValue* merges = f.kv("tokenizer.ggml.merges")) {
+    for (size_t r = 0; r < merges->strs.size(); ++r) {
+      const std::string& m = merges->strs[r];
+      const size_t sp = m.find(' ', 1);
+      if (sp == std::string::npos) continue;
+      std::string a, b;
+      if (unicode_token_to_bytes(m.substr(0, sp), &a) && unicode_token_to_bytes(m.substr(sp + 1), &b))
+        merge_rank_.emplace(merge_key(a, b), (int32_t)r);
+    }
+  }
+  bos_id = (int32_t)f.get_u("tokenizer.ggml.bos_token_id", 128000);
+  eos_id = (int32_t)f.get_u("tokenizer.ggml.eos_token_id", 128009);
+  return "";
 }
+
+void Tokenizer::bpe_word(const std::string& w, std::vector<int32_t>* out) const {
+  std::vector<std::string> sym;
+  for (char c : w) sym.emplace_back(1, c);
+  while (sym.size() > 1) {
+    int best = -1, best_rank = 0x7fffffff;
+    for (size_t i = 0; i + 1 < sym.size(); ++i) {
+      auto it = merge_rank_.find(merge_key(sym[i], sym[i + 1]));
+      if (it != merge_rank_.end() && it->second < best_rank) { best_rank = it->second; best = (int)i; }
+    }
+    if (best < 0) break;
+    sym[best] += sym[best + 1];
+    sym.erase(sym.begin() + best + 1);
+  }
+  for (const std::string& s : sym) {
+    auto it = bytes_to_id_.find(s);
+    if (it != bytes_to_id_.end()) { out->push_back(it->second); continue; }
+    for (char c : s) {  // a merge produced a string that is not a token: fall back to its bytes
+      auto b = bytes_to_id_.find(std::string(1, c));
+      if (b != bytes_to_id_.end()) out->push_back(b->second);
+    }
+  }
+}
+
+void Tokenizer::encode(const char* text, size_t n, bool add_bos, int32_t vocab_limit, std::vector<int32_t>* out) const {
+  if (add_bos && bos_id >= 0 && bos_id < vocab_limit) out->push_back(bos_id);
+  if (!has_vocab()) {
+    for (size_t i = 0; i < n; ++i) out->push_back((int32_t)((unsigned char)text[i] % vocab_limit));
+    return;
+  }
+  std::vector<std::string> words;
+  pretokenize(text, n, &words);
+  for (const std::string& w : words) bpe_word(w, out);
+}
+
+void Tokenizer::decode(const int32_t* ids, size_t n, std::string* out) const {
+  char tmp[24];
+  for (size_t i = 0; i < n; ++i) {
+    const int32_t id = ids[i];
+    if (has_vocab()) {
+      if (id >= 0 && (size_t)id < id_to_bytes_.size() && !is_special_[id]) *out += id_to_bytes_[id];
+    } else if (id >= 0 && id < 256) {
+      out->push_back((char)id);
+    } else if (id >= 256 && id < 128000) {  // synthetic vocabulary: visible placeholder, valid UTF-8
+      snprintf(tmp, sizeof tmp, " t%d", id);
+      *out += tmp;
+    }
+  }
+}
+
 }  // namespace b200

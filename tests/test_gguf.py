@@ -1,0 +1,151 @@
+"""GGUF model files (the on-disk format either side of the path): the reader, the
+byte-level BPE tokenizer it feeds (CPU tests), and loading a whole model onto the GPU (gpu test).
+Files are written with gguf-py's own GGUFWriter, i.e. by the format's reference implementation."""
+import os
+
+import numpy as np
+import pytest
+
+import __graft_entry__ as ge
+from oracle import orc
+from tests.util import random_tensor
+
+gguf = pytest.importorskip("gguf")
+
+
+def bytes_to_unicode():
+    bs = list(range(33, 127)) + list(range(161, 173)) + list(range(174, 256))
+    cs, n = bs[:], 0
+    for b in range(256):
+        if b not in bs:
+            bs.append(b); cs.append(256 + n); n += 1
+    return {b: chr(c) for b, c in zip(bs, cs)}
+
+
+B2U = bytes_to_unicode()
+U = lambda raw: "".join(B2U[b] for b in raw)
+MERGES = [(b"h", b"e"), (b"l", b"l"), (b"he", b"ll"), (b"hell", b"o"), (b" ", b"w"), (b" w", b"o"), (b"r", b"l"), (b" wo", b"rl"),
+          (b" worl", b"d"), (b"1", b"2"), (b"12", b"3"), (b"\xc3", b"\xa9"), (b" ", b"t"), (b" t", b"h"), (b" th", b"e")]
+
+
+def vocab():
+    toks = [U(bytes([b])) for b in range(256)]
+    for a, b in MERGES:
+        toks.append(U(a + b))
+    toks += ["<|begin_of_text|>", "<|eot_id|>"]
+    types = [1] * (len(toks) - 2) + [3, 3]
+    return toks, types, [f"{U(a)} {U(b)}" for a, b in MERGES]
+
+
+def py_bpe(word, ranks, tok_id):
+    sym = [bytes([b]) for b in word]
+    while len(sym) > 1:
+        best = min(((ranks.get((sym[i], sym[i + 1]), 1 << 30), i) for i in range(len(sym) - 1)))
+        if best[0] == 1 << 30:
+            break
+        i = best[1]
+        sym[i:i + 2] = [sym[i] + sym[i + 1]]
+    return [tok_id[s] for s in sym]
+
+
+def write_model(path, fmt, seed=5):
+    """Tiny llama-architecture GGUF: 2 layers, d=2048, 16/4 heads, ffn 2048, vocab = len(tokens) padded to 512."""
+    toks, types, merges = vocab()
+    V, d, ff, nh, nkv, L = 512, 2048, 2048, 16, 4, 2
+    toks += [f"<|reserved_{i}|>" for i in range(V - len(toks))]
+    types += [3] * (V - len(types))
+    w = gguf.GGUFWriter(path, "llama")
+    w.add_block_count(L); w.add_embedding_length(d); w.add_feed_forward_length(ff); w.add_head_count(nh); w.add_head_count_kv(nkv)
+    w.add_layer_norm_rms_eps(1e-5); w.add_rope_freq_base(500000.0); w.add_context_length(8192); w.add_vocab_size(V)
+    w.add_tokenizer_model("gpt2"); w.add_tokenizer_pre("llama-bpe"); w.add_token_list(toks); w.add_token_types(types); w.add_token_merges(merges)
+    w.add_bos_token_id(V - 2 if False else toks.index("<|begin_of_text|>")); w.add_eos_token_id(toks.index("<|eot_id|>"))
+    rng = np.random.default_rng(seed)
+    Q = gguf.GGMLQuantizationType
+    tmat = orc.BF16 if fmt == 0 else orc.Q4_K
+    tensors = {}
+
+    def add(name, t, rows, cols):
+        arr = random_tensor(rng, t, rows, cols, sigma=1.0 if name.startswith("token_embd") else None)
+        tensors[name] = (t, arr, rows, cols)
+        if t == orc.F32:
+            w.add_tensor(name, arr.reshape(cols))
+        elif t == orc.BF16:
+            w.add_tensor(name, arr.view(np.uint8).reshape(rows, cols * 2), raw_dtype=Q.BF16)
+        else:
+            w.add_tensor(name, arr.reshape(rows, -1), raw_dtype=Q.Q4_K if t == orc.Q4_K else Q.Q6_K)
+    add("token_embd.weight", tmat, V, d)
+    add("output_norm.weight", orc.F32, 1, d)
+    add("output.weight", orc.BF16 if fmt == 0 else orc.Q6_K, V, d)
+    w.add_tensor("rope_freqs.weight", np.ones(64, np.float32))
+    for l in range(L):
+        tv = tmat if fmt == 0 else (orc.Q6_K if l == 1 else orc.Q4_K)   # a per-tensor mix, dictated by the file
+        for n, t, r, c in (("attn_q", tmat, nh * 128, d), ("attn_k", tmat, nkv * 128, d), ("attn_v", tv, nkv * 128, d),
+                           ("attn_output", tmat, d, nh * 128), ("ffn_gate", tmat, ff, d), ("ffn_up", tmat, ff, d), ("ffn_down", tv, d, ff)):
+            add(f"blk.{l}.{n}.weight", t, r, c)
+        add(f"blk.{l}.attn_norm.weight", orc.F32, 1, d)
+        add(f"blk.{l}.ffn_norm.weight", orc.F32, 1, d)
+    w.write_header_to_file(); w.write_kv_data_to_file(); w.write_tensors_to_file(); w.close()
+    return tensors, (V, d, ff, nh, nkv, L)
+
+
+@pytest.fixture(scope="module")
+def pkg():
+    return ge.build()
+
+
+@pytest.fixture(scope="module")
+def model_file(tmp_path_factory):
+    p = str(tmp_path_factory.mktemp("gguf") / "tiny-q4.gguf")
+    tensors, dims = write_model(p, fmt=1)
+    return p, tensors, dims
+
+
+def test_gguf_info(pkg, model_file):
+    path, tensors, (V, d, ff, nh, nkv, L) = model_file
+    cfg, n_tensors, n_tok, n_merges = pkg.gguf_info(path)
+    assert (cfg.n_layers, cfg.d_model, cfg.d_ffn, cfg.n_heads, cfg.n_kv_heads, cfg.head_dim, cfg.vocab) == (L, d, ff, nh, nkv, 128, V)
+    assert abs(cfg.rope_theta - 500000.0) < 1 and abs(cfg.rms_eps - 1e-5) < 1e-9 and cfg.rope_factor == 8.0
+    assert cfg.weight_format == pkg.WEIGHTS_Q4_K_M and n_tensors == len(tensors) + 1 and n_tok == V and n_merges == len(MERGES)
+    with pytest.raises(pkg.B200Error):
+        pkg.gguf_info(__file__)            # not a GGUF file
+
+
+def test_bpe_tokenizer_matches_reference_bpe(pkg, model_file):
+    tok = pkg.Tok(model_file[0])
+    toks, _, _ = vocab()
+    tok_id = {bytes([b]): b for b in range(256)}
+    for i, (a, b) in enumerate(MERGES):
+        tok_id[a + b] = 256 + i
+    ranks = {m: i for i, m in enumerate(MERGES)}
+    assert tok.encode("hello world") == [tok_id[b"hello"], tok_id[b" world"]]
+    assert tok.encode("hello") == py_bpe(b"hello", ranks, tok_id)
+    assert tok.encode("123456") == [tok_id[b"123"]] + py_bpe(b"456", ranks, tok_id)      # digits split in threes
+    assert tok.encode("the the") == py_bpe(b"the", ranks, tok_id) + py_bpe(b" the", ranks, tok_id)  # lowest rank first: (h,e) wins
+    for text in ["hello world", "café 中文!", "it's  1234\n\nnew  line ", "", "a\tb"]:
+        assert tok.decode(tok.encode(text)) == text                                        # lossless round trip
+    assert tok.encode("x", add_bos=True)[0] == toks.index("<|begin_of_text|>")
+    assert tok.decode([toks.index("<|eot_id|>"), ord("A")]) == "A"                          # specials render as nothing
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_load_gguf_and_match_oracle(pkg, tmp_path, fmt):
+    assert pkg.device_count() >= 1
+    path = str(tmp_path / f"tiny-{fmt}.gguf")
+    tensors, (V, d, ff, nh, nkv, L) = write_model(path, fmt, seed=9)
+    eng = pkg.Engine.from_gguf(path, max_ctx=128)
+    with eng:
+        from tests.util import oracle_cfg_from
+        ora = orc.Model(oracle_cfg_from(eng.cfg))
+        for name, (t, arr, r, c) in tensors.items():
+            ora.set_tensor(name, t, arr, r, c)
+        ids = np.array(eng.tokenize("hello world 123", add_bos=False), np.int32)
+        assert eng.detokenize(ids) == "hello world 123" and len(ids) < 8                   # merges were applied
+        got = eng.forward_logits(ids, pkg.MODE_GEMV)
+        ora.reset()
+        for t in ids:
+            want = ora.forward([t], mode=0)
+        assert np.abs(got - want).max() <= 1e-3 * max(1.0, np.abs(want).max())
+        out, _, _ = eng.generate_greedy(ids, 8, pkg.MODE_GEMV)
+        want_ids, _ = ora.generate_greedy(ids, 8, prefill_mode=0)
+        assert out.tolist() == want_ids.tolist()
