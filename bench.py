@@ -338,7 +338,8 @@ def run_ours(args):
                              # dram__bytes_read + dram__bytes_write of this kernel, one launch, ncu --set full
                              # (profiles/prof_gemv_bf16_r1_raw.csv): 234.94 MB + 3.62 MB vs 234.88 MB algorithmic
                              "traffic": 238562816,
-                             "peak_source": peak_src, "timing": "CUDA events on the engine stream, kernel alone, L2 flushed",
+                             "peak_source": peak_src,
+                             "timing": "CUDA events on the engine stream, 20 launches back to back; the 235 MB matrix exceeds the 126 MB L2",
                              "bytes_per_launch": k_bytes, "ms_per_launch": k_ms}
         sach = (wbytes + kv_bytes) / (step_ms * 1e-3) / 1e9
         extra["step_roofline"] = {"bound": "hbm", "bytes_per_token": wbytes + kv_bytes, "ms_per_token": step_ms,

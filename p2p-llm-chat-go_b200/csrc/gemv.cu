@@ -617,12 +617,9 @@ template <class F, int PRO, int EPI>
 cudaError_t launch_t(const GemvArgs& a, cudaStream_t s, bool pdl, int sm_count) {
   auto kern = gemv_kernel<F, PRO, EPI>;
   const size_t smem = smem_bytes<F>(a.K);
-  static thread_local size_t configured = 0;  // per instantiation
-  if (smem > configured) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    configured = smem;
-  }
+  // per-device attribute, cheap to set: no caching, so one host thread may drive several GPUs
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
   const int n_units = a.N / F::R;
   int grid = n_units < sm_count ? n_units : sm_count;  // units are dealt CTA-first (see gemv_kernel)
   if (grid < 1) grid = 1;
