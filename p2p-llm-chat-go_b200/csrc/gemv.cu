@@ -39,6 +39,8 @@ DEVINL float block_sum(float v, float* red, int warp, int lane) {
   return t;
 }
 
+constexpr int kProU = 4;  // float4 per thread kept in registers by the single-fetch prologues (K <= 8192)
+
 template <int PRO>
 DEVINL float rms_inv(const GemvArgs& a, float* red, int warp, int lane) {
   if (PRO != PRO_RMSNORM) return 1.f;  // (PRO_TP_RMSNORM is bf16-only and has its own prologue)
@@ -134,6 +136,39 @@ struct FmtBF16 {
       tp_prologue(xs, a, red, warp, lane);
       return;
     }
+    if (PRO == PRO_RMSNORM && a.K <= kWarps * 32 * 4 * kProU) {
+      // x and the norm weights are fetched once and stay in registers between the sum of squares and the
+      // scaling (same element -> thread mapping and summation order as rms_inv, so the same bits)
+      float4 v[kProU], w[kProU];
+#pragma unroll
+      for (int i = 0; i < kProU; ++i) {
+        const int k = threadIdx.x * 4 + i * kWarps * 32 * 4;
+        const bool on = k < a.K;
+        v[i] = on ? *reinterpret_cast<const float4*>(a.x + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+        w[i] = on ? *reinterpret_cast<const float4*>(a.norm_w + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      float ss = 0.f;
+#pragma unroll
+      for (int i = 0; i < kProU; ++i)
+        if (threadIdx.x * 4 + i * kWarps * 32 * 4 < a.K) ss += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
+      ss = block_sum(ss, red, warp, lane);
+      const float inv = 1.0f / sqrtf(ss / (float)a.K + a.eps);
+#pragma unroll
+      for (int i = 0; i < kProU; ++i) {
+        const int k = threadIdx.x * 4 + i * kWarps * 32 * 4;
+        if (k < a.K) {
+          float4 o;
+          o.x = __fmul_rn(__fmul_rn(v[i].x, inv), w[i].x);
+          o.y = __fmul_rn(__fmul_rn(v[i].y, inv), w[i].y);
+          o.z = __fmul_rn(__fmul_rn(v[i].z, inv), w[i].z);
+          o.w = __fmul_rn(__fmul_rn(v[i].w, inv), w[i].w);
+          const int idx = (k & ~255) + ((k >> 2) & 1) * 128 + ((k & 255) >> 3) * 4;
+          *reinterpret_cast<float4*>(xs + idx) = o;
+        }
+      }
+      __syncthreads();
+      return;
+    }
     const float inv = rms_inv<PRO>(a, red, warp, lane);
     for (int k = threadIdx.x * 4; k < a.K; k += kWarps * 32 * 4) {
       float4 v = *reinterpret_cast<const float4*>(a.x + k);
@@ -212,22 +247,43 @@ DEVINL float small_u2f(uint32_t v) { return __uint_as_float(0x4B000000u | v) - 8
 
 template <class F, int PRO>
 DEVINL void q16_prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane) {
-  const float inv = rms_inv<PRO>(a, red, warp, lane);
   int16_t* xq = reinterpret_cast<int16_t*>(xs);
   float* dx = reinterpret_cast<float*>(xs + 2 * (size_t)a.K);
   float* dxs = dx + a.K / 32;
   // lane = 4 consecutive elements (one float4), 8 lanes = one 32-element block, a warp = 4 blocks per round;
   // U rounds of loads are issued before the first dependent shuffle.  ~15 instructions per block instead of
   // ~120 with one element per lane, which matters because every CTA repeats this for the whole vector.
-  constexpr int U = 4;
+  constexpr int U = kProU;
   const int n4 = a.K / 4;
-  for (int g0 = warp * 32; g0 < n4; g0 += kWarps * 32 * U) {
-    float4 v[U], g[U];
+  // K <= 8192 with an RMS norm: x and the norm weights are fetched once, before the block-wide sum of
+  // squares, and reused from registers below (thread -> element mapping and summation order as in rms_inv)
+  const bool single = (PRO == PRO_RMSNORM) && n4 <= kWarps * 32 * U;
+  float4 v[U], g[U];
+  float inv = 1.f;
+  if (single) {
+    float ss = 0.f;
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const int gi = g0 + u * kWarps * 32 + lane;
+      const int gi = u * kWarps * 32 + (int)threadIdx.x;
       v[u] = gi < n4 ? *reinterpret_cast<const float4*>(a.x + 4 * gi) : make_float4(0.f, 0.f, 0.f, 0.f);
-      g[u] = (PRO == PRO_RMSNORM && gi < n4) ? *reinterpret_cast<const float4*>(a.norm_w + 4 * gi) : make_float4(1.f, 1.f, 1.f, 1.f);
+      g[u] = gi < n4 ? *reinterpret_cast<const float4*>(a.norm_w + 4 * gi) : make_float4(1.f, 1.f, 1.f, 1.f);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (u * kWarps * 32 + (int)threadIdx.x < n4) ss += v[u].x * v[u].x + v[u].y * v[u].y + v[u].z * v[u].z + v[u].w * v[u].w;
+    ss = block_sum(ss, red, warp, lane);
+    inv = 1.0f / sqrtf(ss / (float)a.K + a.eps);
+  } else {
+    inv = rms_inv<PRO>(a, red, warp, lane);
+  }
+  for (int g0 = warp * 32; g0 < n4; g0 += kWarps * 32 * U) {
+    if (!single) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int gi = g0 + u * kWarps * 32 + lane;
+        v[u] = gi < n4 ? *reinterpret_cast<const float4*>(a.x + 4 * gi) : make_float4(0.f, 0.f, 0.f, 0.f);
+        g[u] = (PRO == PRO_RMSNORM && gi < n4) ? *reinterpret_cast<const float4*>(a.norm_w + 4 * gi) : make_float4(1.f, 1.f, 1.f, 1.f);
+      }
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -617,8 +673,12 @@ template <class F, int PRO, int EPI>
 cudaError_t launch_t(const GemvArgs& a, cudaStream_t s, bool pdl, int sm_count) {
   auto kern = gemv_kernel<F, PRO, EPI>;
   const size_t smem = smem_bytes<F>(a.K);
-  // per-device attribute, cheap to set: no caching, so one host thread may drive several GPUs
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  // Per-device attribute, cheap to set: no caching, so one host thread may drive several GPUs.  Always the
+  // sm_100 opt-in maximum rather than this launch's size: the same kernel serves matrices with different K,
+  // and a tool that re-launches a captured node (ncu replay) reads the attribute as it stands at that time.
+  constexpr int kMaxOptinSmem = 227 * 1024;
+  if (smem > (size_t)kMaxOptinSmem) return cudaErrorInvalidValue;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxOptinSmem);
   if (e != cudaSuccess) return e;
   const int n_units = a.N / F::R;
   int grid = n_units < sm_count ? n_units : sm_count;  // units are dealt CTA-first (see gemv_kernel)
