@@ -632,6 +632,46 @@ int b200_bench_kernel(b200_engine* h, const char* which, int iters, float* ms, i
   const b200_config& c = e->lc;
   const int d = c.d_model, qd = c.n_heads * kHeadDim, ff = c.d_ffn;
   Layer& L = e->layers[0];
+  if (!strncmp(which, "gemm_", 5)) {
+    // "gemm_<matrix>@<tokens>": the tensor-core GEMM of layer 0's matrix on a synthetic bf16 activation tile
+    // (bf16 models only); *bytes returns the FLOP count of one launch
+    const char* at = strchr(which, '@');
+    const int64_t n = at ? atoll(at + 1) : 512;
+    const std::string m(which + 5, at ? (size_t)(at - which - 5) : strlen(which + 5));
+    const uint16_t* W = nullptr;
+    int64_t rows = 0, K = 0;
+    int type = T_BF16;
+    if (m == "gate_up") { W = (const uint16_t*)L.gate_up; rows = 2 * ff; K = d; type = L.gu_type; }
+    else if (m == "down") { W = (const uint16_t*)L.down; rows = d; K = ff; type = L.down_type; }
+    else if (m == "qkv") { W = (const uint16_t*)L.qkv; rows = qd + 2 * c.n_kv_heads * kHeadDim; K = d; type = L.v ? -1 : L.qkv_type; }
+    else if (m == "attn_output") { W = (const uint16_t*)L.o; rows = d; K = qd; type = L.o_type; }
+    else if (m == "lm_head") { W = (const uint16_t*)e->output; rows = c.vocab; K = d; type = e->output_type; }
+    if (!W || type != T_BF16 || n < 1 || n > 4096 || !gemm_shape_ok(rows, K, n)) {
+      set_error("bench '%s': unknown matrix, not bf16, or unsupported shape", which);
+      return B200_EINVAL;
+    }
+    DevBuf xb, yb;
+    int rc;
+    if ((rc = xb.alloc((size_t)n * K * 2)) || (rc = yb.alloc((size_t)2 * n * rows * 4))) return rc;
+    B200_CUDA(launch_synth(T_BF16, xb.p, n, K, 1234, 77, 1.0f, e->stream));
+    cudaEvent_t e0, e1;
+    B200_CUDA(cudaEventCreate(&e0));
+    B200_CUDA(cudaEventCreate(&e1));
+    int splits = 2;
+    for (int i = -3; i < iters; ++i) {
+      if (i == 0) B200_CUDA(cudaEventRecord(e0, e->stream));
+      splits = 2;
+      B200_CUDA(launch_gemm_bf16_splitk(W, rows, K, xb.as<uint16_t>(), n, yb.as<float>(), rows, n * rows, &splits, e->stream));
+    }
+    B200_CUDA(cudaEventRecord(e1, e->stream));
+    B200_CUDA(cudaStreamSynchronize(e->stream));
+    float total = 0.f;
+    cudaEventElapsedTime(&total, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (ms) *ms = total / iters;
+    if (bytes) *bytes = 2 * n * rows * K;
+    return 0;
+  }
   GemvArgs a = {};
   int type, pro, epi;
   if (!strcmp(which, "gate_up")) {

@@ -8,14 +8,21 @@
 // token counts (batched decode) only shrink N.  The epilogue reads the accumulator with tcgen05.ld
 // (lane = weight row, column = token), so for each token 32 lanes store 32 consecutive floats.
 //
-// Warp roles (192 threads): warp 0 = TMA producer (one elected lane), warp 1 = TMEM allocator + MMA issuer
-// (one elected lane), warps 2..5 = epilogue (TMEM lane quadrant = warp % 4).  A ring of STAGES
-// {A 128x64, B BNx64} tiles is handed between them with full/empty mbarriers; tcgen05.commit releases
-// a stage when the MMAs that read it have retired.  Two CTAs fit per SM (smem <= 113 KB, TMEM 2 x <=256
-// columns), so one CTA's epilogue overlaps the other's main loop.
+// Warp roles: warp 0 = TMA producer (one elected lane), warp 1 = TMEM allocator + MMA issuer (one elected
+// lane), warps 2.. = epilogue (TMEM lane quadrant = warp % 4).  A ring of STAGES {A (MT*128)x64, B BNx64}
+// tiles is handed between them with full/empty mbarriers; tcgen05.commit releases a stage when the MMAs
+// that read it have retired.
+//   MT = 1 (128-row weight tile): two CTAs fit per SM (smem <= 113 KB, TMEM 2 x <=256 columns), so one
+//           CTA's epilogue overlaps the other's main loop.
+//   MT = 2 (256 x 256 output tile, two 128x256 accumulators = all 512 TMEM columns, one CTA per SM): both
+//           MMAs of a K step share the token tile, so a CTA moves 64 KB of operands per 256x256x64 MACs
+//           instead of 48 KB per 128x256x64.  These GEMMs run against the L2 -> SM throughput cap (ncu:
+//           tensor pipe 49 % active at MT = 1), so a third less operand traffic is a third more math.
 //
 // Numerics (oracle mode 1): inputs bf16, products exact, fp32 accumulation in TMEM.
 #include <cuda.h>
+
+#include <cstdlib>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -59,11 +66,14 @@ __host__ __device__ constexpr uint32_t instr_desc(int M, int N) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
-template <int BN>
+template <int BN, int MT>
 struct GemmCfg {
-  static constexpr int STAGES = (BN == 128) ? 3 : 2;
+  static constexpr int STAGES = (MT == 2 || BN == 128) ? 3 : 2;
+  static constexpr int THREADS = 64 + 128 * MT;
+  static constexpr uint32_t AT_BYTES = MT * A_BYTES;
   static constexpr uint32_t B_BYTES = BN * BK * 2;
-  static constexpr uint32_t STAGE = A_BYTES + B_BYTES;
+  static constexpr uint32_t STAGE = AT_BYTES + B_BYTES;
+  static constexpr uint32_t TMEM_COLS = BN * MT;
   static constexpr size_t SMEM = (size_t)STAGES * STAGE + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
@@ -75,10 +85,10 @@ struct GemmArgs {
   long long split_stride;  // floats between the partial outputs of consecutive K splits
 };
 
-template <int BN>
-__global__ void __launch_bounds__(192) gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA,
-                                                         const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
-  using C = GemmCfg<BN>;
+template <int BN, int MT>
+__global__ void __launch_bounds__(64 + 128 * MT) gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                   const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
+  using C = GemmCfg<BN, MT>;
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B tiles must start on 1024-byte boundaries
   const uint32_t raw = smem_u32(smem_raw);
@@ -91,7 +101,7 @@ __global__ void __launch_bounds__(192) gemm_bf16_kernel(const __grid_constant__ 
   const uint32_t full_s = smem_u32(full), empty_s = smem_u32(empty), tfull_s = smem_u32(tmem_full);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+  const int m0 = blockIdx.x * (BM * MT), n0 = blockIdx.y * BN;
   const int kb0 = blockIdx.z * g.k_blocks;  // split-K: this CTA's first K block
 
   if (threadIdx.x == 0) {
@@ -102,8 +112,8 @@ __global__ void __launch_bounds__(192) gemm_bf16_kernel(const __grid_constant__ 
     mbar_init(tfull_s, 1);
     mbar_fence_init();
   }
-  if (warp == 1) {  // whole warp: allocate BN TMEM columns (power of two >= 32), then give up the permit
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(BN) : "memory");
+  if (warp == 1) {  // whole warp: allocate the TMEM columns (power of two >= 32), then give up the permit
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(C::TMEM_COLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   tc_fence_before();
@@ -119,8 +129,9 @@ __global__ void __launch_bounds__(192) gemm_bf16_kernel(const __grid_constant__ 
         mbar_wait(empty_s + 8 * s, ph ^ 1);
         const uint32_t dst = tiles + s * C::STAGE;
         mbar_expect_tx(full_s + 8 * s, C::STAGE);
-        tma_load_2d(dst, &tmA, (kb0 + kb) * BK, m0, full_s + 8 * s);
-        tma_load_2d(dst + A_BYTES, &tmB, (kb0 + kb) * BK, n0, full_s + 8 * s);
+#pragma unroll
+        for (int t = 0; t < MT; ++t) tma_load_2d(dst + t * A_BYTES, &tmA, (kb0 + kb) * BK, m0 + t * BM, full_s + 8 * s);
+        tma_load_2d(dst + C::AT_BYTES, &tmB, (kb0 + kb) * BK, n0, full_s + 8 * s);
         if (++s == C::STAGES) { s = 0; ph ^= 1; }
       }
     }
@@ -133,10 +144,13 @@ __global__ void __launch_bounds__(192) gemm_bf16_kernel(const __grid_constant__ 
         mbar_wait(full_s + 8 * s, ph);
         tc_fence_after();
         const uint64_t ad = smem_desc_sw128(tiles + s * C::STAGE);
-        const uint64_t bd = smem_desc_sw128(tiles + s * C::STAGE + A_BYTES);
+        const uint64_t bd = smem_desc_sw128(tiles + s * C::STAGE + C::AT_BYTES);
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k)  // UMMA_K = 16 bf16 = 32 B: advance the start address by 2 (x16 B)
-          tc_mma(tmem_base, ad + 2 * k, bd + 2 * k, idesc, (uint32_t)(kb | k));
+        for (int k = 0; k < BK / 16; ++k) {  // UMMA_K = 16 bf16 = 32 B: advance the start address by 2 (x16 B)
+#pragma unroll
+          for (int t = 0; t < MT; ++t)  // accumulator t: TMEM columns [t*BN, (t+1)*BN), weight rows [128t, 128t+128)
+            tc_mma(tmem_base + t * BN, ad + t * (A_BYTES >> 4) + 2 * k, bd + 2 * k, idesc, (uint32_t)(kb | k));
+        }
         tc_commit(empty_s + 8 * s);  // stage reusable once these MMAs have read it
         if (++s == C::STAGES) { s = 0; ph ^= 1; }
       }
@@ -146,11 +160,12 @@ __global__ void __launch_bounds__(192) gemm_bf16_kernel(const __grid_constant__ 
     mbar_wait(tfull_s, 0);
     tc_fence_after();
     const int quad = warp & 3;  // a warp may only touch TMEM lanes [32*(warp%4), +32)
-    const int row = m0 + quad * 32 + lane;
+    const int mt = (warp - 2) >> 2;  // which accumulator (MT = 2: warps 2..5 -> 0, warps 6..9 -> 1)
+    const int row = m0 + mt * BM + quad * 32 + lane;
 #pragma unroll 1
     for (int c = 0; c < BN / 32; ++c) {
       uint32_t v[32];
-      const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(c * 32);
+      const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(mt * BN + c * 32);
       asm volatile(
           "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
           "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
@@ -169,7 +184,7 @@ __global__ void __launch_bounds__(192) gemm_bf16_kernel(const __grid_constant__ 
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(BN) : "memory");
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(C::TMEM_COLS) : "memory");
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -199,20 +214,27 @@ bool make_map(CUtensorMap* m, const void* base, uint64_t rows, uint64_t K, uint3
             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-template <int BN>
+template <int BN, int MT>
 cudaError_t launch_bn(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y, int64_t ldy,
                       int splits, int64_t split_stride, cudaStream_t s) {
+  using C = GemmCfg<BN, MT>;
   CUtensorMap ma, mb;
   if (!make_map(&ma, W, (uint64_t)rows, (uint64_t)K, BM) || !make_map(&mb, X, (uint64_t)n_tokens, (uint64_t)K, BN))
     return cudaErrorInvalidValue;
-  auto kern = gemm_bf16_kernel<BN>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GemmCfg<BN>::SMEM);
+  auto kern = gemm_bf16_kernel<BN, MT>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM);
   if (e != cudaSuccess) return e;
   GemmArgs g;
   g.y = Y; g.ldy = (int)ldy; g.n_tokens = (int)n_tokens; g.k_blocks = (int)(K / BK) / splits; g.split_stride = split_stride;
-  dim3 grid((unsigned)(rows / BM), (unsigned)((n_tokens + BN - 1) / BN), (unsigned)splits);
-  kern<<<grid, 192, GemmCfg<BN>::SMEM, s>>>(ma, mb, g);
+  dim3 grid((unsigned)(rows / (BM * MT)), (unsigned)((n_tokens + BN - 1) / BN), (unsigned)splits);
+  kern<<<grid, C::THREADS, C::SMEM, s>>>(ma, mb, g);
   return cudaGetLastError();
+}
+
+// B200_GEMM_M256 = 0 never / 1 whenever the shape allows / unset: the heuristic below (experiments only)
+int m256_override() {
+  const char* e = getenv("B200_GEMM_M256");
+  return e ? atoi(e) : -1;
 }
 
 }  // namespace
@@ -239,9 +261,18 @@ cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, 
   const int64_t tiles128 = (rows / BM) * ((n_tokens + 127) / 128);
   int use = 1;
   if (*splits >= 2 && tiles128 < 296 && tiles128 >= 32 && (K / BK) % 2 == 0 && K >= 2048) use = 2;
+  // 256 x 256 tiles (one CTA per SM): for matrices with enough 256-row tiles to occupy most SMs
+  const int64_t tiles_m256 = (rows / (2 * BM)) * ((n_tokens + 255) / 256);
+  bool m256 = rows % (2 * BM) == 0 && n_tokens > 128 && tiles_m256 >= 100;
+  if (m256_override() == 0) m256 = false;
+  if (m256_override() == 1) m256 = rows % (2 * BM) == 0 && n_tokens > 128;
+  if (m256) {
+    *splits = 1;
+    return launch_bn<256, 2>(W, rows, K, X, n_tokens, Y, ldy, 1, 0, s);
+  }
   *splits = use;
-  if (n_tokens > 128 && tiles256 >= 296) return launch_bn<256>(W, rows, K, X, n_tokens, Y, ldy, 1, 0, s);
-  return launch_bn<128>(W, rows, K, X, n_tokens, Y, ldy, use, split_stride, s);
+  if (n_tokens > 128 && tiles256 >= 296) return launch_bn<256, 1>(W, rows, K, X, n_tokens, Y, ldy, 1, 0, s);
+  return launch_bn<128, 1>(W, rows, K, X, n_tokens, Y, ldy, use, split_stride, s);
 }
 
 }  // namespace b200

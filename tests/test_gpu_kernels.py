@@ -148,6 +148,24 @@ def test_gemm_tcgen05(pkg, wtype, rows, cols, n):
     assert (err <= 1e-5 * budget + 1e-30).all(), float((err / (budget + 1e-30)).max())
 
 
+# the 256 x 256-tile variant (two accumulators filling TMEM), forced for shapes the heuristic leaves to the
+# 128-row kernel; ragged token counts exercise the zero-filled part of the token tile
+@pytest.mark.parametrize("rows,cols,n", [(256, 64, 129), (512, 2048, 256), (1024, 4096, 300), (3584, 1024, 513)])
+def test_gemm_tcgen05_m256(pkg, rows, cols, n, monkeypatch):
+    monkeypatch.setenv("B200_GEMM_M256", "1")
+    rng = np.random.default_rng(7 * rows + cols + n)
+    W = random_tensor(rng, orc.BF16, rows, cols)
+    X = rng.standard_normal((n, cols)).astype(np.float32)
+    got = pkg.gemm(orc.BF16, W, rows, cols, X)
+    want = orc.matmul(orc.BF16, W, rows, cols, X, mode=1)
+    Wf = orc.bf16_to_f32(W).reshape(rows, cols)
+    budget = np.abs(X).astype(np.float64) @ np.abs(Wf).astype(np.float64).T
+    err = np.abs(got.astype(np.float64) - want)
+    assert (err <= 1e-5 * budget + 1e-30).all(), float((err / (budget + 1e-30)).max())
+    monkeypatch.setenv("B200_GEMM_M256", "0")
+    assert np.array_equal(got, pkg.gemm(orc.BF16, W, rows, cols, X))  # same K order: same bits as the 128-row tiles
+
+
 def test_gemm_rejects_bad_shapes(pkg):
     with pytest.raises(pkg.B200Error):
         pkg.gemm(orc.BF16, np.zeros((100, 64), np.uint16), 100, 64, np.zeros((1, 64), np.float32))
