@@ -652,15 +652,15 @@ int b200_bench_kernel(b200_engine* h, const char* which, int iters, float* ms, i
     }
     DevBuf xb, yb;
     int rc;
-    if ((rc = xb.alloc((size_t)n * K * 2)) || (rc = yb.alloc((size_t)2 * n * rows * 4))) return rc;
+    if ((rc = xb.alloc((size_t)n * K * 2)) || (rc = yb.alloc((size_t)8 * n * rows * 4))) return rc;
     B200_CUDA(launch_synth(T_BF16, xb.p, n, K, 1234, 77, 1.0f, e->stream));
     cudaEvent_t e0, e1;
     B200_CUDA(cudaEventCreate(&e0));
     B200_CUDA(cudaEventCreate(&e1));
-    int splits = 2;
+    int splits = 8;
     for (int i = -3; i < iters; ++i) {
       if (i == 0) B200_CUDA(cudaEventRecord(e0, e->stream));
-      splits = 2;
+      splits = (m == "down" || m == "attn_output") ? 8 : 1;  // as the engine calls them
       B200_CUDA(launch_gemm_bf16_splitk(W, rows, K, xb.as<uint16_t>(), n, yb.as<float>(), rows, n * rows, &splits, e->stream));
     }
     B200_CUDA(cudaEventRecord(e1, e->stream));

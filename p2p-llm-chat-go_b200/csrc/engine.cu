@@ -622,7 +622,8 @@ int Engine::ensure_prefill() {
   const size_t wmax = (size_t)std::max(std::max(d, qd), ff);
   if ((rc = alloc((void**)&pf_x, (size_t)T * d * 4)) || (rc = alloc((void**)&pf_xb, (size_t)T * wmax * 2)) ||
       (rc = alloc((void**)&pf_qkv, (size_t)T * (qd + 2 * kvd) * 4)) || (rc = alloc((void**)&pf_q, (size_t)T * qd * 4)) ||
-      (rc = alloc((void**)&pf_att, (size_t)T * qd * 4)) || (rc = alloc((void**)&pf_proj, (size_t)2 * T * d * 4)) ||
+      (rc = alloc((void**)&pf_att, (size_t)T * qd * 4)) ||
+      (rc = alloc((void**)&pf_proj, (size_t)(pf_proj_floats = (int64_t)std::max(2 * T, 2560) * d) * 4)) ||
       (rc = alloc((void**)&pf_gu, (size_t)T * 2 * ff * 4)) ||
       (rc = alloc((void**)&pf_partial, (size_t)T * attn_partial_floats(c.n_heads, c.n_kv_heads, pf_splits) * 4)) ||
       (rc = alloc((void**)&pf_counters, (size_t)T * c.n_kv_heads * 4)))
@@ -645,7 +646,7 @@ int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_ar
   B200_CUDA(launch_embed_tokens(token_embd, embd_type, d, tokens_dev, n, pf_x, s));
   for (int l = 0; l < c.n_layers; ++l) {
     Layer& L = layers[l];
-    B200_CUDA(launch_add_rmsnorm_bf16(pf_x, l ? pf_proj : nullptr, l ? proj2() : nullptr, L.attn_norm, pf_xb, n, d, c.rms_eps, s));
+    B200_CUDA(launch_add_rmsnorm_bf16(pf_x, l ? pf_proj : nullptr, pf_proj_splits, pf_proj_stride, L.attn_norm, pf_xb, n, d, c.rms_eps, s));
     B200_CUDA(launch_gemm_bf16(L.qkv16, qd + 2 * kvd, d, pf_xb, n, pf_qkv, qd + 2 * kvd, s));
     B200_CUDA(launch_rope_kv(pf_qkv, pf_q, L.k_cache, L.v_cache, table, rope, n, qd, kvd, c.n_kv_heads, 0, pos_arr, slot_arr, pages_per_seq, s));
     if (!pos_arr && use_fa_prefill) {  // one sequence, causal: tensor-core attention, bf16 straight into the GEMM operand
@@ -659,15 +660,17 @@ int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_ar
       B200_CUDA(launch_attn_decode(t, s, false));
       B200_CUDA(launch_f32_to_bf16(pf_att, pf_xb, (int64_t)n * qd, s));
     }
-    // o and down have few output tiles (d_model/128 x tokens/128): split K in two when that under-fills the GPU
-    pf_proj_splits = tp_size > 1 ? 1 : 2;
-    B200_CUDA(launch_gemm_bf16_splitk(L.o16, d, qd, pf_xb, n, pf_proj, d, (int64_t)pf_rows * d, &pf_proj_splits, s));
+    // o and down have few output tiles (d_model/256 x tokens/256): K is split when that under-fills the GPU; the
+    // partials sit n*d floats apart in pf_proj and the next consumer adds them in a fixed order
+    pf_proj_splits = max_proj_splits(n);
+    pf_proj_stride = (int64_t)n * d;
+    B200_CUDA(launch_gemm_bf16_splitk(L.o16, d, qd, pf_xb, n, pf_proj, d, pf_proj_stride, &pf_proj_splits, s));
     if (tp_size > 1) { int rc = tp_allreduce_sum(pf_proj, (size_t)n * d, s); if (rc) return rc; }
-    B200_CUDA(launch_add_rmsnorm_bf16(pf_x, pf_proj, proj2(), L.ffn_norm, pf_xb, n, d, c.rms_eps, s));
+    B200_CUDA(launch_add_rmsnorm_bf16(pf_x, pf_proj, pf_proj_splits, pf_proj_stride, L.ffn_norm, pf_xb, n, d, c.rms_eps, s));
     B200_CUDA(launch_gemm_bf16(L.gu16, 2 * ff, d, pf_xb, n, pf_gu, 2 * ff, s));
     B200_CUDA(launch_swiglu_bf16(pf_gu, pf_xb, (int64_t)n * ff, s));
-    pf_proj_splits = tp_size > 1 ? 1 : 2;
-    B200_CUDA(launch_gemm_bf16_splitk(L.down16, d, ff, pf_xb, n, pf_proj, d, (int64_t)pf_rows * d, &pf_proj_splits, s));
+    pf_proj_splits = max_proj_splits(n);
+    B200_CUDA(launch_gemm_bf16_splitk(L.down16, d, ff, pf_xb, n, pf_proj, d, pf_proj_stride, &pf_proj_splits, s));
     if (tp_size > 1) { int rc = tp_allreduce_sum(pf_proj, (size_t)n * d, s); if (rc) return rc; }
   }
   return 0;
@@ -680,7 +683,7 @@ int Engine::prefill_gemm(int n) {
   int rc0 = forward_gemm(n, prompt_dev, nullptr, nullptr, nullptr);
   if (rc0) return rc0;
   // hand the last position over to the batch-1 path: residual stream, then lm_head (mode 0) + token pick
-  B200_CUDA(launch_take_row(pf_x, pf_proj, proj2(), d, n - 1, x, s));
+  B200_CUDA(launch_take_row(pf_x, pf_proj, pf_proj_splits, pf_proj_stride, d, n - 1, x, s));
   int n_tail = 0;
   int rc = enqueue_tail(s, false, &n_tail);
   if (rc) return rc;

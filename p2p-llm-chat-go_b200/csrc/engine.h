@@ -114,8 +114,14 @@ struct Engine {
   unsigned int* pf_counters = nullptr;
   int pf_splits = 4;
   int pf_rows = 0;             // rows the work buffers were sized for
-  int pf_proj_splits = 1;      // split-K partials currently sitting in pf_proj (consumers add them)
-  const float* proj2() const { return pf_proj_splits == 2 ? pf_proj + (size_t)pf_rows * cfg.d_model : nullptr; }
+  int pf_proj_splits = 1;      // split-K partials currently sitting in pf_proj (consumers add them) ...
+  int64_t pf_proj_stride = 0;  // ... this many floats apart
+  int64_t pf_proj_floats = 0;  // capacity of pf_proj
+  // most K splits a projection over n rows may use: every partial is [n][d_model] and all must fit pf_proj
+  int max_proj_splits(int n) const {
+    const int64_t fit = pf_proj_floats / ((int64_t)n * lc.d_model);
+    return tp_size > 1 ? 1 : (int)(fit < 1 ? 1 : (fit > 8 ? 8 : fit));
+  }
 
   // sequence slots (continuous batching): slot s statically owns block-table row s
   struct Seq {

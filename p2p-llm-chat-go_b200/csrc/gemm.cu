@@ -250,26 +250,32 @@ cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const u
   return launch_gemm_bf16_splitk(W, rows, K, X, n_tokens, Y, ldy, 0, &splits, s);
 }
 
-// Same, but a GEMM with too few output tiles to fill the GPU may split K in two: partial p is written to
-// Y + p*split_stride and the caller adds the partials (deterministically) where it consumes Y.
-// *splits: in = maximum allowed (1 or 2), out = what was used.
+// Same, but a GEMM with too few output tiles to fill the GPU may split K: partial p is written to
+// Y + p*split_stride and the caller adds the partials (deterministically, ascending p) where it consumes Y.
+// *splits: in = maximum allowed (1..8), out = what was used.
 cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
                                     int64_t ldy, int64_t split_stride, int* splits, cudaStream_t s) {
   if (!gemm_shape_ok(rows, K, n_tokens)) return cudaErrorInvalidValue;
-  // token tile: 256 when that still yields >= 2 CTAs per SM of work, else 128 (more, smaller tiles)
+  const int max_splits = *splits < 1 ? 1 : (*splits > 8 ? 8 : *splits);
+  const int64_t kb = K / BK;
+  const int ov = m256_override();
+  // 256 x 256 tiles, one CTA per SM: the fewest operand bytes per MAC.  Taken when, with K split up to
+  // max_splits ways (each split keeps >= 24 K blocks: shorter loops do not amortise the CTA set-up), the grid comes to 96..148 CTAs, or has several waves.
+  if (rows % (2 * BM) == 0 && n_tokens > 128 && ov != 0) {
+    const int64_t tiles = (rows / (2 * BM)) * ((n_tokens + 255) / 256);
+    int use = 1;
+    for (int sp = 2; sp <= max_splits; sp *= 2)
+      if (kb % sp == 0 && kb / sp >= 24 && tiles * sp <= 148) use = sp;
+    if (tiles * use >= 96 || ov == 1) {
+      *splits = use;
+      return launch_bn<256, 2>(W, rows, K, X, n_tokens, Y, ldy, use, split_stride, s);
+    }
+  }
+  // 128-row tiles, two CTAs per SM; token tile 256 when that still yields >= 2 CTAs per SM of work, else 128
   const int64_t tiles256 = (rows / BM) * ((n_tokens + 255) / 256);
   const int64_t tiles128 = (rows / BM) * ((n_tokens + 127) / 128);
   int use = 1;
-  if (*splits >= 2 && tiles128 < 296 && tiles128 >= 32 && (K / BK) % 2 == 0 && K >= 2048) use = 2;
-  // 256 x 256 tiles (one CTA per SM): for matrices with enough 256-row tiles to occupy most SMs
-  const int64_t tiles_m256 = (rows / (2 * BM)) * ((n_tokens + 255) / 256);
-  bool m256 = rows % (2 * BM) == 0 && n_tokens > 128 && tiles_m256 >= 100;
-  if (m256_override() == 0) m256 = false;
-  if (m256_override() == 1) m256 = rows % (2 * BM) == 0 && n_tokens > 128;
-  if (m256) {
-    *splits = 1;
-    return launch_bn<256, 2>(W, rows, K, X, n_tokens, Y, ldy, 1, 0, s);
-  }
+  if (max_splits >= 2 && tiles128 < 296 && tiles128 >= 32 && kb % 2 == 0 && K >= 2048) use = 2;
   *splits = use;
   if (n_tokens > 128 && tiles256 >= 296) return launch_bn<256, 1>(W, rows, K, X, n_tokens, Y, ldy, 1, 0, s);
   return launch_bn<128, 1>(W, rows, K, X, n_tokens, Y, ldy, use, split_stride, s);

@@ -174,8 +174,9 @@ cudaError_t launch_attn_prefill(const float* q, const uint16_t* k_cache, const u
 
 // element-wise kernels of the prefill / batched pass (prefill.cu)
 cudaError_t launch_embed_tokens(const uint8_t* embd, int embd_type, int d_model, const int32_t* tokens_dev, int n, float* x, cudaStream_t s);
-cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, const float* add2, const float* w, uint16_t* xb, int tokens, int d, float eps,
-                                    cudaStream_t s);
+// `add`: n_parts split-K partials of [tokens][d], part_stride floats apart, summed in ascending order
+cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, int n_parts, int64_t part_stride, const float* w, uint16_t* xb, int tokens,
+                                    int d, float eps, cudaStream_t s);
 cudaError_t launch_rope_kv(const float* qkv, float* q, uint16_t* k_cache, uint16_t* v_cache, const int32_t* block_table, const float* rope,
                            int tokens, int q_rows, int kv_rows, int n_kv_heads, int pos0, const int32_t* pos_arr, const int32_t* slot_arr,
                            int pages_per_seq, cudaStream_t s);
@@ -183,6 +184,6 @@ cudaError_t launch_argmax_rows(const float* logits, int rows, int vocab, int32_t
 cudaError_t launch_append_history(const int32_t* next, const int32_t* slot_arr, const int32_t* pos_arr, int32_t* history, int max_ctx, int rows,
                                   cudaStream_t s);
 cudaError_t launch_swiglu_bf16(const float* gu, uint16_t* h, int64_t n_pairs, cudaStream_t s);
-cudaError_t launch_take_row(const float* x, const float* add, const float* add2, int d, int row, float* out, cudaStream_t s);
+cudaError_t launch_take_row(const float* x, const float* add, int n_parts, int64_t part_stride, int d, int row, float* out, cudaStream_t s);
 
 }  // namespace b200

@@ -21,19 +21,20 @@ DEVINL float block_sum256(float v, float* red) {
   return t;
 }
 
-// x[t][:] (+= add[t][:]) ; xb[t][:] = bf16( (x * inv_rms) * w )        grid = tokens, block = 256
-__global__ void add_rmsnorm_bf16_kernel(float* x, const float* add, const float* add2, const float* w, uint16_t* xb, int d, float eps) {
+// x[t][:] (+= sum of the split-K partials add[p][t][:], p ascending) ; xb[t][:] = bf16( (x * inv_rms) * w )
+// grid = tokens, block = 256
+__global__ void add_rmsnorm_bf16_kernel(float* x, const float* add, int n_parts, long long part_stride, const float* w, uint16_t* xb, int d,
+                                        float eps) {
   __shared__ float red[8];
   float* xr = x + (size_t)blockIdx.x * d;
-  const float* ar = add ? add + (size_t)blockIdx.x * d : nullptr;
-  const float* ar2 = add2 ? add2 + (size_t)blockIdx.x * d : nullptr;  // second split-K partial
+  const float* ar = (add && n_parts > 0) ? add + (size_t)blockIdx.x * d : nullptr;
   float ss = 0.f;
   for (int k = threadIdx.x * 4; k < d; k += 1024) {
     float4 v = *reinterpret_cast<const float4*>(xr + k);
     if (ar) {
       float4 a = *reinterpret_cast<const float4*>(ar + k);
-      if (ar2) {
-        const float4 b = *reinterpret_cast<const float4*>(ar2 + k);
+      for (int p = 1; p < n_parts; ++p) {
+        const float4 b = *reinterpret_cast<const float4*>(ar + (size_t)p * part_stride + k);
         a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
       }
       v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
@@ -97,11 +98,12 @@ __global__ void swiglu_bf16_kernel(const float* gu, uint16_t* h, int64_t n_pairs
   }
 }
 
-// out[:] = x[row][:] + add[row][:]   (residual of the last prompt position -> the decode path's stream)
-__global__ void take_row_kernel(const float* x, const float* add, const float* add2, int d, int row, float* out) {
+// out[:] = x[row][:] + sum of the partials add[p][row][:]   (residual of the last prompt position -> the
+// decode path's stream)
+__global__ void take_row_kernel(const float* x, const float* add, int n_parts, long long part_stride, int d, int row, float* out) {
   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < d; k += gridDim.x * blockDim.x) {
     float a = add[(size_t)row * d + k];
-    if (add2) a += add2[(size_t)row * d + k];
+    for (int p = 1; p < n_parts; ++p) a += add[(size_t)p * part_stride + (size_t)row * d + k];
     out[k] = x[(size_t)row * d + k] + a;
   }
 }
@@ -145,10 +147,10 @@ cudaError_t launch_append_history(const int32_t* next, const int32_t* slot_arr, 
   return cudaGetLastError();
 }
 
-cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, const float* add2, const float* w, uint16_t* xb, int tokens, int d, float eps,
-                                    cudaStream_t s) {
-  if (d % 4) return cudaErrorInvalidValue;
-  add_rmsnorm_bf16_kernel<<<tokens, 256, 0, s>>>(x, add, add2, w, xb, d, eps);
+cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, int n_parts, int64_t part_stride, const float* w, uint16_t* xb, int tokens,
+                                    int d, float eps, cudaStream_t s) {
+  if (d % 4 || part_stride % 4) return cudaErrorInvalidValue;
+  add_rmsnorm_bf16_kernel<<<tokens, 256, 0, s>>>(x, add, n_parts, (long long)part_stride, w, xb, d, eps);
   return cudaGetLastError();
 }
 cudaError_t launch_rope_kv(const float* qkv, float* q, uint16_t* k_cache, uint16_t* v_cache, const int32_t* block_table, const float* rope,
@@ -162,8 +164,8 @@ cudaError_t launch_swiglu_bf16(const float* gu, uint16_t* h, int64_t n_pairs, cu
   swiglu_bf16_kernel<<<1184, 256, 0, s>>>(gu, h, n_pairs);
   return cudaGetLastError();
 }
-cudaError_t launch_take_row(const float* x, const float* add, const float* add2, int d, int row, float* out, cudaStream_t s) {
-  take_row_kernel<<<8, 256, 0, s>>>(x, add, add2, d, row, out);
+cudaError_t launch_take_row(const float* x, const float* add, int n_parts, int64_t part_stride, int d, int row, float* out, cudaStream_t s) {
+  take_row_kernel<<<8, 256, 0, s>>>(x, add, n_parts, (long long)part_stride, d, row, out);
   return cudaGetLastError();
 }
 

@@ -164,6 +164,23 @@ def test_prefill_gemm_logits(pkg, fmt, n):
         assert ids.tolist() == want_ids.tolist(), (ids, want_ids, margins.min())
 
 
+@pytest.mark.parametrize("n", [200, 300])
+def test_prefill_gemm_logits_m256_splitk(pkg, n, monkeypatch):
+    """The 256 x 256-tile GEMM with K split up to 8 ways (what the 8B shapes select for o / down / gate-up),
+    forced here on the parity model; its partials are summed by the next consumer in a fixed order."""
+    monkeypatch.setenv("B200_GEMM_M256", "1")
+    eng, ora, cfg = engine_and_oracle(pkg, 0, n_layers=2, seed=53, source="synth", max_ctx=512)
+    with eng:
+        toks = _prompt(cfg, n, 9)
+        got = eng.forward_logits(toks, pkg.MODE_GEMM)
+        ora.reset()
+        want = ora.forward(toks, mode=1)
+        err = np.abs(got - want).max()
+        assert err <= PREFILL_LOGIT_TOL * max(1.0, np.abs(want).max()), (n, err)
+        again = eng.forward_logits(toks, pkg.MODE_GEMM)
+        assert np.array_equal(got, again)  # deterministic: no atomics in the split-K reduction
+
+
 def test_prefill_gemm_matches_gemv_prefill_closely(pkg):
     """Two numerics modes, one model: the logits after a 64-token prompt agree to bf16-input precision."""
     eng, ora, cfg = engine_and_oracle(pkg, 0, n_layers=2, seed=52, source="synth")
