@@ -178,6 +178,161 @@ __global__ void __launch_bounds__(G * 32) attn_prefill_kernel(const float* __res
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------
+// Batched decode: one query position per sequence (continuous batching), many sequences per launch.
+//
+// grid = (n_kv_heads, n_queries), 128 threads.  The G query heads that share a KV head are rows 0..G-1 of
+// the 16-row MMA tile (rows G..15 are zero), so every K/V row a CTA stages is used by all G heads and the
+// dot products run on the tensor cores: the CUDA-core kernel in attn.cu spends ~3.6 instructions per
+// multiply-add on this shape (46 % of a 256-sequence decode step).  Each 64-token tile is split four ways:
+// warp w owns tokens [16w, 16w+16) of every tile (two 8-token S tiles, one 16-token P.V step) and keeps its
+// own online-softmax state; the four partial results are merged through shared memory at the end.
+// Same numerics as the prefill kernel above (Q and P as bf16 hi + lo, fp32 accumulation).
+template <int G>
+__global__ void __launch_bounds__(128) attn_decode_mma_kernel(const float* __restrict__ q, const uint16_t* __restrict__ k_cache,
+                                                              const uint16_t* __restrict__ v_cache, const int32_t* __restrict__ block_table,
+                                                              const int32_t* __restrict__ q_ctx, const int32_t* __restrict__ q_slot,
+                                                              int pages_per_seq, int q_stride, int n_kv_heads, float* __restrict__ out,
+                                                              uint16_t* __restrict__ out_bf16) {
+  extern __shared__ __align__(128) uint8_t tiles[];  // 2 stages x {K tile 16 KB, V tile 16 KB}
+  const int kvh = blockIdx.x, z = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int ctx = q_ctx[z];
+  const int32_t* bt = block_table + (size_t)q_slot[z] * pages_per_seq;
+  const float scale = 1.0f / sqrtf((float)kHeadDim);
+  const uint32_t tiles_s = smem_u32(tiles);
+
+  auto load_tile = [&](int st, int t0) {
+    const uint32_t kb = tiles_s + st * (2 * kKvTile * 256), vb = kb + kKvTile * 256;
+    for (int item = threadIdx.x; item < kKvTile * 16; item += 128) {
+      const int r = item >> 4, c = item & 15, tok = t0 + r;
+      const bool ok = tok < ctx;
+      const int page = ok ? bt[tok / kPageTokens] : 0;
+      const size_t row = (((size_t)page * n_kv_heads + kvh) * kPageTokens + (ok ? tok % kPageTokens : 0)) * kHeadDim;
+      const uint32_t n = ok ? 16u : 0u;
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(kb + tile_off(r, c)), "l"(k_cache + row + c * 8), "r"(n) : "memory");
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(vb + tile_off(r, c)), "l"(v_cache + row + c * 8), "r"(n) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  load_tile(0, 0);
+
+  // Q fragments: row g = head kvh*G + g for g < G, every other row of the 16 is zero
+  uint32_t qh[8][2], ql[8][2];
+  {
+    const float* qa = q + (size_t)z * q_stride + (size_t)(kvh * G + (g < G ? g : 0)) * kHeadDim;
+#pragma unroll
+    for (int kk = 0; kk < 8; ++kk) {
+      float2 a0 = *reinterpret_cast<const float2*>(qa + 16 * kk + 2 * t), a2 = *reinterpret_cast<const float2*>(qa + 16 * kk + 8 + 2 * t);
+      if (g >= G) a0 = a2 = make_float2(0.f, 0.f);
+      split2(a0.x * scale, a0.y * scale, qh[kk][0], ql[kk][0]);
+      split2(a2.x * scale, a2.y * scale, qh[kk][1], ql[kk][1]);
+    }
+  }
+  float o[16][4];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f;
+  float m = -INFINITY, l = 0.f;
+
+  int stage = 0;
+  for (int t0 = 0; t0 < ctx; t0 += kKvTile, stage ^= 1) {
+    if (t0 + kKvTile < ctx) {
+      load_tile(stage ^ 1, t0 + kKvTile);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");
+    } else {
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+    }
+    __syncthreads();
+    const int tw = t0 + 16 * warp;  // this warp's 16 tokens of the tile
+    if (tw < ctx) {                 // warp-uniform
+      const uint32_t ks = tiles_s + stage * (2 * kKvTile * 256), vs = ks + kKvTile * 256;
+      float s[2][4];
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
+#pragma unroll
+        for (int kk = 0; kk < 8; kk += 2) {
+          uint32_t b[4];
+          ldsm_x4(b, ks + tile_off(16 * warp + 8 * j + (lane & 7), 2 * kk + (lane >> 3)));
+          const uint32_t ah0[4] = {qh[kk][0], 0u, qh[kk][1], 0u}, al0[4] = {ql[kk][0], 0u, ql[kk][1], 0u};
+          const uint32_t ah1[4] = {qh[kk + 1][0], 0u, qh[kk + 1][1], 0u}, al1[4] = {ql[kk + 1][0], 0u, ql[kk + 1][1], 0u};
+          mma_bf16(s[j], ah0, b[0], b[1]);
+          mma_bf16(s[j], al0, b[0], b[1]);
+          mma_bf16(s[j], ah1, b[2], b[3]);
+          mma_bf16(s[j], al1, b[2], b[3]);
+        }
+      }
+      float mx = -INFINITY;
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int tk = tw + 8 * j + 2 * t;
+        if (tk >= ctx) s[j][0] = -INFINITY;
+        if (tk + 1 >= ctx) s[j][1] = -INFINITY;
+        mx = fmaxf(mx, fmaxf(s[j][0], s[j][1]));
+      }
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+      const float mn = fmaxf(m, mx);  // finite: token tw < ctx is visible to every row
+      const float corr = expf(m - mn);  // exp(-inf) = 0 on this warp's first tile
+      m = mn;
+      l *= corr;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) { o[j][0] *= corr; o[j][1] *= corr; }
+      const float p0 = expf(s[0][0] - m), p1 = expf(s[0][1] - m), p2 = expf(s[1][0] - m), p3 = expf(s[1][1] - m);
+      l += (p0 + p1) + (p2 + p3);
+      uint32_t ph[4] = {0u, 0u, 0u, 0u}, pl[4] = {0u, 0u, 0u, 0u};
+      split2(p0, p1, ph[0], pl[0]);
+      split2(p2, p3, ph[2], pl[2]);
+#pragma unroll
+      for (int jd = 0; jd < 16; jd += 2) {
+        uint32_t b[4];
+        ldsm_x4_trans(b, vs + tile_off(16 * warp + (lane & 7) + ((lane >> 3) & 1) * 8, jd + (lane >> 4)));
+        mma_bf16(o[jd], ph, b[0], b[1]);
+        mma_bf16(o[jd], pl, b[0], b[1]);
+        mma_bf16(o[jd + 1], ph, b[2], b[3]);
+        mma_bf16(o[jd + 1], pl, b[2], b[3]);
+      }
+    }
+    __syncthreads();
+  }
+  // merge the four warps' (m, l, o) through shared memory (the tiles are no longer needed)
+  l += __shfl_xor_sync(0xffffffffu, l, 1);
+  l += __shfl_xor_sync(0xffffffffu, l, 2);
+  float* os = reinterpret_cast<float*>(tiles);            // [4 warps][G][128]
+  float* ms = os + 4 * G * kHeadDim;                       // [4][G]
+  float* ls = ms + 4 * G;                                  // [4][G]
+  if (g < G) {
+#pragma unroll
+    for (int jd = 0; jd < 16; ++jd)
+      *reinterpret_cast<float2*>(os + ((size_t)warp * G + g) * kHeadDim + 8 * jd + 2 * t) = make_float2(o[jd][0], o[jd][1]);
+    if (t == 0) {
+      ms[warp * G + g] = m;
+      ls[warp * G + g] = l;
+    }
+  }
+  __syncthreads();
+  const int dim = threadIdx.x;
+#pragma unroll
+  for (int h = 0; h < G; ++h) {
+    float M = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) M = fmaxf(M, ms[w * G + h]);
+    float num = 0.f, den = 0.f;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const float mw = ms[w * G + h];
+      const float wt = (mw == -INFINITY) ? 0.f : expf(mw - M);  // a warp that saw no token of this sequence
+      num = fmaf(wt, os[((size_t)w * G + h) * kHeadDim + dim], num);
+      den = fmaf(wt, ls[w * G + h], den);
+    }
+    const float r = num / den;
+    const size_t idx = (size_t)z * q_stride + (size_t)(kvh * G + h) * kHeadDim + dim;
+    if (out_bf16) out_bf16[idx] = f32_to_bf16_bits(r);
+    else out[idx] = r;
+  }
+}
+
 }  // namespace
 
 // q: [T][n_heads*128] fp32 (rotated); out: [T][n_heads*128] bf16.  K/V of positions [0, pos0+T) must be in the cache.
@@ -196,6 +351,30 @@ cudaError_t launch_attn_prefill(const float* q, const uint16_t* k_cache, const u
     case 2: LAUNCH(2)(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); } break;
     case 4: LAUNCH(4)(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); } break;
     case 8: LAUNCH(8)(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); } break;
+    default: return cudaErrorInvalidValue;
+  }
+#undef LAUNCH
+  return cudaGetLastError();
+}
+
+// One query per sequence: query z attends to the first a.q_ctx[z] tokens of the sequence in slot a.q_slot[z].
+// Writes bf16 to out_bf16 when given (the o-projection GEMM's operand), else fp32 to a.out.
+cudaError_t launch_attn_decode_batched(const AttnArgs& a, uint16_t* out_bf16, cudaStream_t s) {
+  if (a.n_kv_heads < 1 || a.n_heads % a.n_kv_heads || a.n_queries < 1 || !a.q_ctx || !a.q_slot) return cudaErrorInvalidValue;
+  dim3 grid(a.n_kv_heads, a.n_queries);
+  constexpr int kSmem = 2 * 2 * kKvTile * 256;  // 64 KB
+#define LAUNCH(G_)                                                                                                         \
+  {                                                                                                                        \
+    cudaError_t e_ = cudaFuncSetAttribute(attn_decode_mma_kernel<G_>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem); \
+    if (e_ != cudaSuccess) return e_;                                                                                      \
+    attn_decode_mma_kernel<G_><<<grid, 128, kSmem, s>>>(a.q, a.k_cache, a.v_cache, a.block_table, a.q_ctx, a.q_slot,       \
+                                                        a.pages_per_seq, a.q_stride, a.n_kv_heads, a.out, out_bf16);        \
+  }
+  switch (a.n_heads / a.n_kv_heads) {
+    case 1: LAUNCH(1) break;
+    case 2: LAUNCH(2) break;
+    case 4: LAUNCH(4) break;
+    case 8: LAUNCH(8) break;
     default: return cudaErrorInvalidValue;
   }
 #undef LAUNCH

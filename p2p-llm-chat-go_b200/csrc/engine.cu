@@ -86,6 +86,7 @@ int Engine::init(const b200_config& c, const void* nccl_id) {
   use_pdl = getenv("B200_NO_PDL") == nullptr;
   use_graph = getenv("B200_NO_GRAPH") == nullptr;
   use_fa_prefill = getenv("B200_NO_FA_PREFILL") == nullptr;
+  use_mma_decode = getenv("B200_NO_MMA_DECODE") == nullptr;
   // measured on B200 (round 1): chaining L2 prefetches of the next kernel's weights made the step SLOWER
   // (bf16 3.18 vs 3.05 ms, Q4_K_M 1.84 vs 1.78 ms), so it is opt-in for experiments only
   use_l2_chain = getenv("B200_L2_CHAIN") != nullptr;
@@ -657,8 +658,12 @@ int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_ar
       t.n_heads = c.n_heads; t.n_kv_heads = c.n_kv_heads; t.out = pf_att; t.partial = pf_partial; t.counters = pf_counters;
       t.n_splits = pf_splits; t.fixed_ctx = 1; t.n_queries = n; t.q_stride = qd;
       t.q_ctx = ctx_arr; t.q_slot = slot_arr; t.pages_per_seq = pages_per_seq;
-      B200_CUDA(launch_attn_decode(t, s, false));
-      B200_CUDA(launch_f32_to_bf16(pf_att, pf_xb, (int64_t)n * qd, s));
+      if (use_mma_decode) {  // tensor cores, bf16 straight into the GEMM operand
+        B200_CUDA(launch_attn_decode_batched(t, pf_xb, s));
+      } else {
+        B200_CUDA(launch_attn_decode(t, s, false));
+        B200_CUDA(launch_f32_to_bf16(pf_att, pf_xb, (int64_t)n * qd, s));
+      }
     }
     // o and down have few output tiles (d_model/256 x tokens/256): K is split when that under-fills the GPU; the
     // partials sit n*d floats apart in pf_proj and the next consumer adds them in a fixed order

@@ -144,7 +144,7 @@ struct Engine {
   uint16_t* output16 = nullptr;     // bf16 lm_head operand of the tensor-core path
 
   cudaGraphExec_t step_graph = nullptr;
-  bool use_pdl = true, use_graph = true, use_l2_chain = false, use_fa_prefill = true;
+  bool use_pdl = true, use_graph = true, use_l2_chain = false, use_fa_prefill = true, use_mma_decode = true;
   int launches_per_step = 0;
   void* flush_buf = nullptr;
   size_t flush_bytes = 0;

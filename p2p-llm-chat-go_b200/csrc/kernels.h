@@ -172,6 +172,9 @@ bool gemm_shape_ok(int64_t rows, int64_t K, int64_t n_tokens);
 cudaError_t launch_attn_prefill(const float* q, const uint16_t* k_cache, const uint16_t* v_cache, const int32_t* block_table, uint16_t* out,
                                 int T, int pos0, int n_heads, int n_kv_heads, cudaStream_t s);
 
+// batched decode (one query per sequence) on the tensor cores; bf16 output when out_bf16 is given, else a.out
+cudaError_t launch_attn_decode_batched(const AttnArgs& a, uint16_t* out_bf16, cudaStream_t s);
+
 // element-wise kernels of the prefill / batched pass (prefill.cu)
 cudaError_t launch_embed_tokens(const uint8_t* embd, int embd_type, int d_model, const int32_t* tokens_dev, int n, float* x, cudaStream_t s);
 // `add`: n_parts split-K partials of [tokens][d], part_stride floats apart, summed in ascending order
