@@ -87,6 +87,7 @@ int Engine::init(const b200_config& c, const void* nccl_id) {
   use_graph = getenv("B200_NO_GRAPH") == nullptr;
   use_fa_prefill = getenv("B200_NO_FA_PREFILL") == nullptr;
   use_mma_decode = getenv("B200_NO_MMA_DECODE") == nullptr;
+  use_mega = getenv("B200_NO_MEGA") == nullptr;
   // measured on B200 (round 1): chaining L2 prefetches of the next kernel's weights made the step SLOWER
   // (bf16 3.18 vs 3.05 ms, Q4_K_M 1.84 vs 1.78 ms), so it is opt-in for experiments only
   use_l2_chain = getenv("B200_L2_CHAIN") != nullptr;
@@ -346,8 +347,7 @@ int Engine::synthesize() {
   return rc;
 }
 
-// lm_head GEMV (logits + argmax), sampler (no-op for greedy requests), finish_step (token hand-over)
-int Engine::enqueue_tail(cudaStream_t s, bool pdl, int* n, bool consume_tp) {
+void Engine::lm_head_args(GemvArgs* out, int* pro_out, bool consume_tp) {
   const b200_config& c = lc;
   GemvArgs lm = {};
   lm.W = output; lm.N = c.vocab; lm.K = c.d_model; lm.x = x; lm.norm_w = output_norm; lm.eps = c.rms_eps;
@@ -359,7 +359,19 @@ int Engine::enqueue_tail(cudaStream_t s, bool pdl, int* n, bool consume_tp) {
   lm.y = logits + (size_t)tp_rank * c.vocab;  // vocab-parallel: this rank's slice of the logits
   lm.row_base = tp_rank * c.vocab;             // global token id of row 0 (argmax key)
   lm.st = st; lm.store_logits = 1; lm.argmax_key = &st->argmax_key;
-  B200_CUDA(launch_gemv(output_type, pro, EPI_LOGITS, lm, s, pdl, sm_count)); ++*n;
+  *out = lm;
+  *pro_out = pro;
+}
+
+// lm_head GEMV (logits + argmax), sampler (no-op for greedy requests), finish_step (token hand-over)
+int Engine::enqueue_tail(cudaStream_t s, bool pdl, int* n, bool consume_tp, bool with_lm_head) {
+  const b200_config& c = lc;
+  if (with_lm_head) {
+    GemvArgs lm;
+    int pro;
+    lm_head_args(&lm, &pro, consume_tp);
+    B200_CUDA(launch_gemv(output_type, pro, EPI_LOGITS, lm, s, pdl, sm_count)); ++*n;
+  }
   if (tp_size > 1) {  // global argmax = max over ranks of the packed (logit, ~id) keys
     int rc = tp_allreduce_max_u64(&st->argmax_key, s);
     if (rc) return rc;
@@ -367,7 +379,7 @@ int Engine::enqueue_tail(cudaStream_t s, bool pdl, int* n, bool consume_tp) {
   }
   SampleArgs sa = {};
   sa.logits = logits; sa.vocab = cfg.vocab; sa.params = sp_dev; sa.history = prompt_dev; sa.st = st; sa.out = &st->sampled; sa.n_hist = -1;
-  B200_CUDA(launch_sample(sa, s, pdl && tp_size == 1)); ++*n;
+  B200_CUDA(launch_sample(sa, s, pdl && tp_size == 1 && with_lm_head)); ++*n;
   FinishArgs f = {};
   f.st = st; f.prompt = prompt_dev; f.out_tokens = out_tokens_dev; f.host_n_out = host_n_out_dev; f.embd = token_embd;
   f.embd_type = embd_type; f.d_model = c.d_model; f.x = x; f.max_ctx = c.max_ctx;
@@ -376,11 +388,96 @@ int Engine::enqueue_tail(cudaStream_t s, bool pdl, int* n, bool consume_tp) {
   return 0;
 }
 
+// Phase table of the persistent decode kernel: the same projections with the same arguments as enqueue_step
+// below (single GPU only).  Leaves mega_ready false — and the per-projection kernels in charge — when a shape
+// is not supported.
+int Engine::ensure_mega() {
+  if (mega_ready || !use_mega || tp_size > 1) return 0;
+  const b200_config& c = lc;
+  const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn;
+  const int G = c.n_heads / c.n_kv_heads;
+  if (G != 1 && G != 2 && G != 4 && G != 8) { use_mega = false; return 0; }
+  int S = sm_count / c.n_kv_heads;
+  if (S > n_splits) S = n_splits;  // the split scratch is sized for n_splits
+  if (S < 1) { use_mega = false; return 0; }
+  std::vector<MegaPhase> ph;
+  auto add_gemv = [&](int wtype, int pro, int epi, const GemvArgs& g) {
+    MegaPhase p = {};
+    if (!mega_plan_gemv(wtype, g.N, g.K, sm_count, &p)) return false;
+    p.pro = pro; p.epi = epi; p.g = g;
+    ph.push_back(p);
+    return true;
+  };
+  bool ok = true;
+  for (int l = 0; l < c.n_layers && ok; ++l) {
+    Layer& L = layers[l];
+    GemvArgs a = {};
+    a.W = L.qkv; a.N = L.v ? qd + kvd : qd + 2 * kvd; a.K = d; a.x = x; a.norm_w = L.attn_norm; a.eps = c.rms_eps; a.y = q;
+    a.row_base = 0; a.q_rows = qd; a.kv_rows = kvd; a.n_kv_heads = c.n_kv_heads; a.rope = rope;
+    a.k_cache = L.k_cache; a.v_cache = L.v_cache; a.block_table = active_table; a.st = st;
+    ok = ok && add_gemv(L.qkv_type, PRO_RMSNORM, EPI_QKV, a);
+    if (L.v) {
+      a.W = L.v; a.N = kvd; a.row_base = qd + kvd;
+      ok = ok && add_gemv(L.v_type, PRO_RMSNORM, EPI_QKV, a);
+    }
+    MegaPhase at = {};
+    at.kind = 1;
+    at.t.q = q; at.t.k_cache = L.k_cache; at.t.v_cache = L.v_cache; at.t.block_table = active_table; at.t.st = st;
+    at.t.n_heads = c.n_heads; at.t.n_kv_heads = c.n_kv_heads; at.t.out = att; at.t.partial = attn_partial; at.t.counters = attn_counters;
+    at.t.n_splits = S; at.t.fixed_ctx = 0;
+    ph.push_back(at);
+    GemvArgs o = {};
+    o.W = L.o; o.N = d; o.K = qd; o.x = att; o.y = x;
+    ok = ok && add_gemv(L.o_type, PRO_COPY, EPI_RESID, o);
+    GemvArgs g = {};
+    g.W = L.gate_up; g.N = 2 * ff; g.K = d; g.x = x; g.norm_w = L.ffn_norm; g.eps = c.rms_eps; g.y = h;
+    ok = ok && add_gemv(L.gu_type, PRO_RMSNORM, EPI_SWIGLU, g);
+    GemvArgs dn = {};
+    dn.W = L.down; dn.N = d; dn.K = ff; dn.x = h; dn.y = x;
+    ok = ok && add_gemv(L.down_type, PRO_COPY, EPI_RESID, dn);
+  }
+  if (ok) {
+    GemvArgs lm;
+    int pro;
+    lm_head_args(&lm, &pro, false);
+    ok = add_gemv(output_type, pro, EPI_LOGITS, lm);
+  }
+  const size_t xb = ok ? mega_x_bytes(ph.data(), (int)ph.size(), G) : 0;
+  if (!ok || xb == 0 || xb + 16 * 2 * 4608 + 1024 > 227 * 1024) { use_mega = false; return 0; }
+  int rc;
+  if ((rc = alloc((void**)&mega_phases, ph.size() * sizeof(MegaPhase))) || (rc = alloc((void**)&mega_sync, 16))) return rc;
+  B200_CUDA(cudaMemcpy(mega_phases, ph.data(), ph.size() * sizeof(MegaPhase), cudaMemcpyHostToDevice));
+  B200_CUDA(cudaMemset(mega_sync, 0, 16));
+  mega.phases = mega_phases; mega.n_phases = (int)ph.size(); mega.lm_head_phase = (int)ph.size() - 1; mega.st = st;
+  mega.bar_count = mega_sync; mega.bar_gen = mega_sync + 1; mega.error = mega_sync + 2;
+  mega.attn_splits = S; mega.x_bytes = (int)xb;
+  mega_group = G;
+  mega_ready = true;
+  return 0;
+}
+
+int Engine::mega_check_error() {
+  if (!mega_ready) return 0;
+  unsigned int flag = 0;
+  B200_CUDA(cudaMemcpy(&flag, mega_sync + 2, 4, cudaMemcpyDeviceToHost));
+  if (!flag) return 0;
+  B200_CUDA(cudaMemset(mega_sync, 0, 16));
+  set_error("persistent decode kernel: a wait timed out (results of that step are void)");
+  return B200_ECUDA;
+}
+
 int Engine::enqueue_step(cudaStream_t s) {
   const b200_config& c = lc;  // per-rank shapes (== cfg without tensor parallelism)
   const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn;
   const bool tp = tp_size > 1;
   int n = 0;
+  if (mega_ready) {  // layers + lm_head in one cooperative launch, then the sampler and the token hand-over
+    B200_CUDA(launch_decode_mega(mega, mega_group, sm_count, s)); ++n;
+    int rc = enqueue_tail(s, false, &n, false, false);
+    if (rc) return rc;
+    launches_per_step = n;
+    return 0;
+  }
   for (int l = 0; l < c.n_layers; ++l) {
     Layer& L = layers[l];
     // fused all-reduce: residual buffers alternate, all-reduce i is consumed from xbuf[i&1] into xbuf[(i+1)&1]
@@ -455,8 +552,12 @@ int Engine::enqueue_step(cudaStream_t s) {
 }
 
 int Engine::ensure_graph() {
-  if (!use_graph || step_graph) return 0;
   if (!all_set()) { set_error("not all tensors are set"); return B200_ESTATE; }
+  {
+    int rc = ensure_mega();
+    if (rc) return rc;
+  }
+  if (!use_graph || step_graph) return 0;
   for (int attempt = 0; attempt < 2; ++attempt) {
     cudaGraph_t g = nullptr;
     cudaError_t e = cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal);
@@ -472,6 +573,10 @@ int Engine::ensure_graph() {
     }
     (void)cudaGetLastError();
     step_graph = nullptr;
+    if (mega_ready) {  // a cooperative launch that cannot be captured: launch the step directly (3 launches per token)
+      use_graph = false;
+      return 0;
+    }
     if (use_pdl) {
       use_pdl = false;  // retry the capture with plain stream-order edges
       continue;
@@ -544,6 +649,7 @@ int Engine::generate_greedy(const int32_t* prompt, int n_prompt, int32_t* ids, i
   cudaError_t e = cudaStreamSynchronize(stream);
   if (!rc && e != cudaSuccess) rc = cuda_fail(e, "generate sync");
   if (!rc) rc = tp_check_error();
+  if (!rc) rc = mega_check_error();
   if (!rc) {
     float a = 0, b = 0;
     cudaEventElapsedTime(&a, e0, e1);

@@ -145,6 +145,14 @@ struct Engine {
 
   cudaGraphExec_t step_graph = nullptr;
   bool use_pdl = true, use_graph = true, use_l2_chain = false, use_fa_prefill = true, use_mma_decode = true;
+  // persistent decode kernel (decode_mega.cu): one cooperative launch per token instead of ~5 per layer
+  bool use_mega = true, mega_ready = false;
+  MegaPhase* mega_phases = nullptr;   // device
+  unsigned int* mega_sync = nullptr;  // device: {barrier count, barrier generation, error}
+  MegaArgs mega = {};
+  int mega_group = 0;
+  int ensure_mega();          // builds the phase table once all tensors are set; leaves mega_ready false if unsupported
+  int mega_check_error();     // after a synchronize: did a wait inside the kernel time out?
   int launches_per_step = 0;
   void* flush_buf = nullptr;
   size_t flush_bytes = 0;
@@ -164,7 +172,9 @@ struct Engine {
   int synthesize();
   bool all_set() const;
 
-  int enqueue_tail(cudaStream_t s, bool pdl, int* n, bool consume_tp = false);  // lm_head + sampler + finish_step
+  // lm_head + sampler + finish_step (with_lm_head = false: the persistent kernel already ran the lm_head)
+  int enqueue_tail(cudaStream_t s, bool pdl, int* n, bool consume_tp = false, bool with_lm_head = true);
+  void lm_head_args(GemvArgs* lm, int* pro, bool consume_tp);
   int enqueue_step(cudaStream_t s);          // launches the kernels of one decode step (capturable)
   int ensure_graph();
   int launch_steps(int n);                   // n graph replays (or direct launches)

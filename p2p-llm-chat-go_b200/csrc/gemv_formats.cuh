@@ -1,0 +1,548 @@
+// gemv_formats.cuh — the weight-format policies (bf16, Q4_K, Q6_K), fused prologues and epilogues of the
+// batch-1 decode mat-vec.  Shared by gemv.cu (one kernel per projection) and decode_mega.cu (one persistent
+// kernel per token); see gemv.cu for the data-movement and numerics description.
+//
+// Activation vectors (x, the residual stream) are read with ld.global.cg: in the persistent kernel they are
+// produced by other SMs earlier in the same launch, and an L1 line from a previous phase would be stale.
+#pragma once
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200 {
+
+namespace {
+
+constexpr int kWarps = 16;  // consumer warps per CTA (each is its own TMA producer); one CTA per SM
+
+// ------------------------------------------------------------------ block helpers
+DEVINL float block_sum(float v, float* red, int warp, int lane) {
+  v = warp_sum(v);
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float t = 0.f;
+#pragma unroll
+  for (int i = 0; i < kWarps; ++i) t += red[i];
+  __syncthreads();
+  return t;
+}
+
+constexpr int kProU = 4;  // float4 per thread kept in registers by the single-fetch prologues (K <= 8192)
+
+template <int PRO>
+DEVINL float rms_inv(const GemvArgs& a, float* red, int warp, int lane) {
+  if (PRO != PRO_RMSNORM) return 1.f;  // (PRO_TP_RMSNORM is bf16-only and has its own prologue)
+  float ss = 0.f;
+  for (int k = threadIdx.x * 4; k < a.K; k += kWarps * 32 * 4) {
+    const float4 v = __ldcg(reinterpret_cast<const float4*>(a.x + k));
+    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+  }
+  ss = block_sum(ss, red, warp, lane);
+  return 1.0f / sqrtf(ss / (float)a.K + a.eps);
+}
+
+// ------------------------------------------------------------------ format policies
+// Each policy states: R rows per unit, CHUNK columns per stage, the stage layout, how lane 0 issues the
+// bulk copies of a stage, how the block prepares x in shared memory, and how a warp consumes a stage.
+
+DEVINL unsigned int ld_acquire_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+DEVINL void st_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Consumer half of the fused all-reduce (see TpLink): wait until every rank's partial of all-reduce
+// `tp_index` has landed in this GPU's receive buffer, x_new = x + sum over ranks (fixed order, so every rank
+// computes the same bits), CTA 0 publishes x_new, and the RMS-normalised x_new goes to shared memory in the
+// GEMV's permuted layout.  A wait that exceeds ~2 s sets the error flag and carries on (no hang).
+DEVINL void tp_prologue(float* xs, const GemvArgs& a, float* red, int warp, int lane) {
+  const TpLink* t = a.tp;
+  const int buf = a.tp_index & 1, size = t->size, d = a.K;
+  const unsigned int seq = *t->epoch * (unsigned int)t->per_step + (unsigned int)a.tp_index + 1u;
+  if (warp == 0 && lane < size) {
+    const unsigned int* f = t->flags + buf * kMaxTp + lane;
+    const long long t0 = clock64();
+    while ((int)(ld_acquire_sys(f) - seq) < 0) {
+      if (clock64() - t0 > 4000000000ll) {
+        *t->error = 1;
+        break;
+      }
+    }
+  }
+  __syncthreads();
+  const float* rv = t->recv[buf];
+  float ss = 0.f;
+  for (int k = threadIdx.x * 4; k < d; k += kWarps * 32 * 4) {
+    float4 v = __ldcg(reinterpret_cast<const float4*>(a.x + k));
+    for (int s = 0; s < size; ++s) {
+      const float4 p = __ldcg(reinterpret_cast<const float4*>(rv + (size_t)s * d + k));
+      v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
+    }
+    if (blockIdx.x == 0) *reinterpret_cast<float4*>(a.x_out + k) = v;
+    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    const int idx = (k & ~255) + ((k >> 2) & 1) * 128 + ((k & 255) >> 3) * 4;
+    *reinterpret_cast<float4*>(xs + idx) = v;
+  }
+  ss = block_sum(ss, red, warp, lane);
+  const float inv = 1.0f / sqrtf(ss / (float)d + a.eps);
+  for (int k = threadIdx.x * 4; k < d; k += kWarps * 32 * 4) {
+    const int idx = (k & ~255) + ((k >> 2) & 1) * 128 + ((k & 255) >> 3) * 4;
+    float4 v = *reinterpret_cast<float4*>(xs + idx);
+    const float4 w = *reinterpret_cast<const float4*>(a.norm_w + k);
+    v.x = __fmul_rn(__fmul_rn(v.x, inv), w.x);
+    v.y = __fmul_rn(__fmul_rn(v.y, inv), w.y);
+    v.z = __fmul_rn(__fmul_rn(v.z, inv), w.z);
+    v.w = __fmul_rn(__fmul_rn(v.w, inv), w.w);
+    *reinterpret_cast<float4*>(xs + idx) = v;
+  }
+  __syncthreads();
+}
+
+template <int KC, int R_>  // KC in {256, 512}; R_ rows per work unit (4, or 2 for matrices with few rows)
+struct FmtBF16 {
+  static constexpr int R = R_, CHUNK = KC, STAGES = (R_ == 4) ? 2 : 3;
+  static constexpr int ROW_STAGE_BYTES = KC * 2;
+  static constexpr int STAGE_BYTES = R * ROW_STAGE_BYTES;
+  static __host__ __device__ size_t x_bytes(int K) { return (size_t)K * 4; }
+  static __host__ __device__ size_t row_bytes(int K) { return (size_t)K * 2; }
+
+  static DEVINL void issue(uint32_t dst, uint32_t bar, const GemvArgs& a, int unit, int c, uint64_t pol) {
+    const uint8_t* src = a.W + ((size_t)unit * R * a.K + (size_t)c * KC) * 2;
+#pragma unroll
+    for (int r = 0; r < R; ++r) bulk_g2s(dst + r * ROW_STAGE_BYTES, src + (size_t)r * a.K * 2, ROW_STAGE_BYTES, bar, pol);
+  }
+
+  // x in shared memory, permuted per 256-group so that lane l's 8 values are two conflict-free float4:
+  // element 8l+j  ->  (j<4 ? 4l+j : 128+4l+(j-4))
+  template <int PRO>
+  static DEVINL void prologue(uint8_t* xs_, const GemvArgs& a, float* red, int warp, int lane) {
+    float* xs = reinterpret_cast<float*>(xs_);
+    if (PRO == PRO_TP_RMSNORM) {
+      tp_prologue(xs, a, red, warp, lane);
+      return;
+    }
+    if (PRO == PRO_RMSNORM && a.K <= kWarps * 32 * 4 * kProU) {
+      // x and the norm weights are fetched once and stay in registers between the sum of squares and the
+      // scaling (same element -> thread mapping and summation order as rms_inv, so the same bits)
+      float4 v[kProU], w[kProU];
+#pragma unroll
+      for (int i = 0; i < kProU; ++i) {
+        const int k = threadIdx.x * 4 + i * kWarps * 32 * 4;
+        const bool on = k < a.K;
+        v[i] = on ? __ldcg(reinterpret_cast<const float4*>(a.x + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        w[i] = on ? *reinterpret_cast<const float4*>(a.norm_w + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      float ss = 0.f;
+#pragma unroll
+      for (int i = 0; i < kProU; ++i)
+        if (threadIdx.x * 4 + i * kWarps * 32 * 4 < a.K) ss += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
+      ss = block_sum(ss, red, warp, lane);
+      const float inv = 1.0f / sqrtf(ss / (float)a.K + a.eps);
+#pragma unroll
+      for (int i = 0; i < kProU; ++i) {
+        const int k = threadIdx.x * 4 + i * kWarps * 32 * 4;
+        if (k < a.K) {
+          float4 o;
+          o.x = __fmul_rn(__fmul_rn(v[i].x, inv), w[i].x);
+          o.y = __fmul_rn(__fmul_rn(v[i].y, inv), w[i].y);
+          o.z = __fmul_rn(__fmul_rn(v[i].z, inv), w[i].z);
+          o.w = __fmul_rn(__fmul_rn(v[i].w, inv), w[i].w);
+          const int idx = (k & ~255) + ((k >> 2) & 1) * 128 + ((k & 255) >> 3) * 4;
+          *reinterpret_cast<float4*>(xs + idx) = o;
+        }
+      }
+      __syncthreads();
+      return;
+    }
+    const float inv = rms_inv<PRO>(a, red, warp, lane);
+    for (int k = threadIdx.x * 4; k < a.K; k += kWarps * 32 * 4) {
+      float4 v = __ldcg(reinterpret_cast<const float4*>(a.x + k));
+      if (PRO == PRO_RMSNORM) {
+        const float4 w = *reinterpret_cast<const float4*>(a.norm_w + k);
+        v.x = __fmul_rn(__fmul_rn(v.x, inv), w.x);
+        v.y = __fmul_rn(__fmul_rn(v.y, inv), w.y);
+        v.z = __fmul_rn(__fmul_rn(v.z, inv), w.z);
+        v.w = __fmul_rn(__fmul_rn(v.w, inv), w.w);
+      }
+      const int idx = (k & ~255) + ((k >> 2) & 1) * 128 + ((k & 255) >> 3) * 4;
+      *reinterpret_cast<float4*>(xs + idx) = v;
+    }
+    __syncthreads();
+  }
+
+  static DEVINL void consume(const uint8_t* st, const uint8_t* xs_, int c, const GemvArgs& a, int lane, float* acc) {
+    const float* xs = reinterpret_cast<const float*>(xs_) + (size_t)c * KC;
+#pragma unroll
+    for (int h = 0; h < KC / 256; ++h) {
+      const float4 xa = *reinterpret_cast<const float4*>(xs + h * 256 + lane * 4);
+      const float4 xb = *reinterpret_cast<const float4*>(xs + h * 256 + 128 + lane * 4);
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        const uint4 w = *reinterpret_cast<const uint4*>(st + r * ROW_STAGE_BYTES + h * 512 + lane * 16);
+        float s = acc[r];
+        s = fmaf(bf16lo(w.x), xa.x, s);
+        s = fmaf(bf16hi(w.x), xa.y, s);
+        s = fmaf(bf16lo(w.y), xa.z, s);
+        s = fmaf(bf16hi(w.y), xa.w, s);
+        s = fmaf(bf16lo(w.z), xb.x, s);
+        s = fmaf(bf16hi(w.z), xb.y, s);
+        s = fmaf(bf16lo(w.w), xb.z, s);
+        s = fmaf(bf16hi(w.w), xb.w, s);
+        acc[r] = s;
+      }
+    }
+  }
+};
+
+// Shared by Q4_K / Q6_K: x -> int16 per 32-block ("Q16_32": d = amax/32767, X = rint(x/d)), kept in shared
+// memory as int16 in a *lane-major* order chosen per weight format, so that every lane fetches the 64
+// activations its 64 weights need with eight conflict-free 16-byte loads:
+//     element k of a 2048-wide chunk  ->  ((i*32 + lane)*8 + r)   where (lane, i, r) = Fmt::xpos(k)
+// The integer dot products use dp2a (two int16 x two int8 per instruction) and are exact.
+// smem: X[K] int16 | dx[K/32] | dxs[K/32]  (dxs = dx * sum(X), used by Q4_K's "min" term)
+struct QActLayout {
+  static __host__ __device__ size_t bytes(int K) { return (size_t)K * 2 + (size_t)(K / 32) * 8; }
+  static DEVINL const uint4* x(const uint8_t* xs) { return reinterpret_cast<const uint4*>(xs); }
+  static DEVINL const float* dx(const uint8_t* xs, int K) { return reinterpret_cast<const float*>(xs + 2 * (size_t)K); }
+  static DEVINL const float* dxs(const uint8_t* xs, int K) { return dx(xs, K) + K / 32; }
+};
+
+DEVINL int dp2a_lo_su(uint32_t x2, uint32_t q4, int c) {  // x2 = 2 x s16, q4 bytes 0,1 unsigned
+  int d;
+  asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(x2), "r"(q4), "r"(c));
+  return d;
+}
+DEVINL int dp2a_hi_su(uint32_t x2, uint32_t q4, int c) {  // q4 bytes 2,3 unsigned
+  int d;
+  asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(x2), "r"(q4), "r"(c));
+  return d;
+}
+DEVINL int dp2a_lo_ss(uint32_t x2, uint32_t q4, int c) {  // q4 bytes 0,1 signed
+  int d;
+  asm("dp2a.lo.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(x2), "r"(q4), "r"(c));
+  return d;
+}
+DEVINL int dp2a_hi_ss(uint32_t x2, uint32_t q4, int c) {
+  int d;
+  asm("dp2a.hi.s32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(x2), "r"(q4), "r"(c));
+  return d;
+}
+// small non-negative integer (< 2^23) -> float without the conversion pipe
+DEVINL float small_u2f(uint32_t v) { return __uint_as_float(0x4B000000u | v) - 8388608.0f; }
+
+template <class F, int PRO>
+DEVINL void q16_prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane) {
+  int16_t* xq = reinterpret_cast<int16_t*>(xs);
+  float* dx = reinterpret_cast<float*>(xs + 2 * (size_t)a.K);
+  float* dxs = dx + a.K / 32;
+  // lane = 4 consecutive elements (one float4), 8 lanes = one 32-element block, a warp = 4 blocks per round;
+  // U rounds of loads are issued before the first dependent shuffle.  ~15 instructions per block instead of
+  // ~120 with one element per lane, which matters because every CTA repeats this for the whole vector.
+  constexpr int U = kProU;
+  const int n4 = a.K / 4;
+  // K <= 8192 with an RMS norm: x and the norm weights are fetched once, before the block-wide sum of
+  // squares, and reused from registers below (thread -> element mapping and summation order as in rms_inv)
+  const bool single = (PRO == PRO_RMSNORM) && n4 <= kWarps * 32 * U;
+  float4 v[U], g[U];
+  float inv = 1.f;
+  if (single) {
+    float ss = 0.f;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int gi = u * kWarps * 32 + (int)threadIdx.x;
+      v[u] = gi < n4 ? __ldcg(reinterpret_cast<const float4*>(a.x + 4 * gi)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      g[u] = gi < n4 ? *reinterpret_cast<const float4*>(a.norm_w + 4 * gi) : make_float4(1.f, 1.f, 1.f, 1.f);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+      if (u * kWarps * 32 + (int)threadIdx.x < n4) ss += v[u].x * v[u].x + v[u].y * v[u].y + v[u].z * v[u].z + v[u].w * v[u].w;
+    ss = block_sum(ss, red, warp, lane);
+    inv = 1.0f / sqrtf(ss / (float)a.K + a.eps);
+  } else {
+    inv = rms_inv<PRO>(a, red, warp, lane);
+  }
+  for (int g0 = warp * 32; g0 < n4; g0 += kWarps * 32 * U) {
+    if (!single) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int gi = g0 + u * kWarps * 32 + lane;
+        v[u] = gi < n4 ? __ldcg(reinterpret_cast<const float4*>(a.x + 4 * gi)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        g[u] = (PRO == PRO_RMSNORM && gi < n4) ? *reinterpret_cast<const float4*>(a.norm_w + 4 * gi) : make_float4(1.f, 1.f, 1.f, 1.f);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int gi = g0 + u * kWarps * 32 + lane;
+      if (g0 + u * kWarps * 32 >= n4) break;  // warp-uniform
+      float4 val = v[u];
+      if (PRO == PRO_RMSNORM) {
+        val.x = __fmul_rn(__fmul_rn(val.x, inv), g[u].x);
+        val.y = __fmul_rn(__fmul_rn(val.y, inv), g[u].y);
+        val.z = __fmul_rn(__fmul_rn(val.z, inv), g[u].z);
+        val.w = __fmul_rn(__fmul_rn(val.w, inv), g[u].w);
+      }
+      float m = fmaxf(fmaxf(fabsf(val.x), fabsf(val.y)), fmaxf(fabsf(val.z), fabsf(val.w)));
+      m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+      m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+      m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
+      const float d = __fmul_rn(m, 1.0f / 32767.0f);
+      const float id = d > 0.f ? __frcp_rn(d) : 0.f;
+      const int X0 = (int)fminf(32767.f, fmaxf(-32767.f, rintf(__fmul_rn(val.x, id))));
+      const int X1 = (int)fminf(32767.f, fmaxf(-32767.f, rintf(__fmul_rn(val.y, id))));
+      const int X2 = (int)fminf(32767.f, fmaxf(-32767.f, rintf(__fmul_rn(val.z, id))));
+      const int X3 = (int)fminf(32767.f, fmaxf(-32767.f, rintf(__fmul_rn(val.w, id))));
+      int xsum = (X0 + X1) + (X2 + X3);
+      xsum += __shfl_xor_sync(0xffffffffu, xsum, 1);
+      xsum += __shfl_xor_sync(0xffffffffu, xsum, 2);
+      xsum += __shfl_xor_sync(0xffffffffu, xsum, 4);
+      if (gi < n4) {
+        const int k = 4 * gi;
+        uint2 pk;
+        pk.x = (uint32_t)(X0 & 0xffff) | ((uint32_t)X1 << 16);
+        pk.y = (uint32_t)(X2 & 0xffff) | ((uint32_t)X3 << 16);
+        *reinterpret_cast<uint2*>(xq + (k & ~2047) + F::xpos(k & 2047)) = pk;
+        if ((lane & 7) == 0) {
+          dx[k >> 5] = d;
+          dxs[k >> 5] = __fmul_rn(d, (float)xsum);
+        }
+      }
+    }
+  }
+  __syncthreads();
+}
+
+// Q4_K: a stage is R rows x 8 super-blocks (GGUF byte order, 144 B each).  lane = (block, j): the 32 qs bytes
+// of sub-block pair (2j, 2j+1) = 64 weights [64j, 64j+64) of that block; both sub-block sums are complete in
+// one lane, so (d*sc)*(dx*isum) is formed exactly as in the oracle.
+template <int R_>
+struct FmtQ4K {
+  static constexpr int R = R_, BLOCKS = 8, CHUNK = BLOCKS * QK_K, STAGES = (R_ == 4) ? 2 : 3;
+  static constexpr int ROW_STAGE_BYTES = BLOCKS * Q4K_BYTES;  // 1152
+  static constexpr int STAGE_BYTES = R * ROW_STAGE_BYTES;
+  static __host__ __device__ size_t x_bytes(int K) { return QActLayout::bytes(K); }
+  static __host__ __device__ size_t row_bytes(int K) { return (size_t)(K / QK_K) * Q4K_BYTES; }
+  // k in [0,2048): block = k>>8, j = (k>>6)&3, i = (k>>3)&7, r = k&7 ; lane = block*4 + j
+  static DEVINL int xpos(int k) { return ((((k >> 3) & 7) * 32 + ((k >> 8) * 4 + ((k >> 6) & 3))) << 3) + (k & 7); }
+
+  static DEVINL void issue(uint32_t dst, uint32_t bar, const GemvArgs& a, int unit, int c, uint64_t pol) {
+    const size_t rb = row_bytes(a.K);
+    const uint8_t* src = a.W + (size_t)unit * R * rb + (size_t)c * ROW_STAGE_BYTES;
+#pragma unroll
+    for (int r = 0; r < R; ++r) bulk_g2s(dst + r * ROW_STAGE_BYTES, src + (size_t)r * rb, ROW_STAGE_BYTES, bar, pol);
+  }
+  template <int PRO>
+  static DEVINL void prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane) {
+    q16_prologue<FmtQ4K<R_>, PRO>(xs, a, red, warp, lane);
+  }
+
+  static DEVINL void consume(const uint8_t* st, const uint8_t* xs, int c, const GemvArgs& a, int lane, float* acc) {
+    const int blk = lane >> 2, j = lane & 3;
+    uint32_t xr[32];  // 64 int16: [0,16) low-nibble sub-block 2j, [16,32) high-nibble sub-block 2j+1
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const uint4 v = QActLayout::x(xs)[(size_t)c * (CHUNK / 8) + i * 32 + lane];
+      xr[4 * i] = v.x; xr[4 * i + 1] = v.y; xr[4 * i + 2] = v.z; xr[4 * i + 3] = v.w;
+    }
+    const int xb = (c * CHUNK + blk * QK_K) / 32 + 2 * j;
+    const float dxA = QActLayout::dx(xs, a.K)[xb], dxB = QActLayout::dx(xs, a.K)[xb + 1];
+    const float dxsA = QActLayout::dxs(xs, a.K)[xb], dxsB = QActLayout::dxs(xs, a.K)[xb + 1];
+    const int sh = (j & 1) * 16;
+    const bool upper = j >= 2;
+    int iA[R], iB[R];
+    uint32_t scp[R], mnp[R], dd[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {  // phase 1: integer work of every row (independent chains)
+      const uint8_t* b = st + r * ROW_STAGE_BYTES + blk * Q4K_BYTES;
+      const uint4 hdr = *reinterpret_cast<const uint4*>(b);
+      const uint4 q0 = *reinterpret_cast<const uint4*>(b + 16 + 32 * j);
+      const uint4 q1 = *reinterpret_cast<const uint4*>(b + 32 + 32 * j);
+      dd[r] = hdr.x;
+      // six-bit (scale, min) of sub-blocks 2j, 2j+1 (ggml get_scale_min_k4), both variants then select
+      const uint32_t u = hdr.y >> sh, v = hdr.z >> sh, t = hdr.w >> sh;
+      const uint32_t sc_lo = u & 0x3F3Fu, mn_lo = v & 0x3F3Fu;
+      const uint32_t sc_hi = (t & 0x0F0Fu) | ((u >> 2) & 0x3030u), mn_hi = ((t >> 4) & 0x0F0Fu) | ((v >> 2) & 0x3030u);
+      scp[r] = upper ? sc_hi : sc_lo;
+      mnp[r] = upper ? mn_hi : mn_lo;
+      const uint32_t qw[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+      int sa = 0, sb = 0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) {
+        const uint32_t lo = qw[w] & 0x0F0F0F0Fu, hi = (qw[w] >> 4) & 0x0F0F0F0Fu;
+        sa = dp2a_lo_su(xr[2 * w], lo, sa);
+        sa = dp2a_hi_su(xr[2 * w + 1], lo, sa);
+        sb = dp2a_lo_su(xr[16 + 2 * w], hi, sb);
+        sb = dp2a_hi_su(xr[17 + 2 * w], hi, sb);
+      }
+      iA[r] = sa;
+      iB[r] = sb;
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {  // phase 2: scales in fp32
+      const float d = __half2float(__ushort_as_half((unsigned short)(dd[r] & 0xffffu)));
+      const float dmin = __half2float(__ushort_as_half((unsigned short)(dd[r] >> 16)));
+      const float scA = small_u2f(scp[r] & 0xFFu), scB = small_u2f(scp[r] >> 8);
+      const float mA = small_u2f(mnp[r] & 0xFFu), mB = small_u2f(mnp[r] >> 8);
+      float t = acc[r];
+      t = fmaf(__fmul_rn(d, scA), __fmul_rn(dxA, (float)iA[r]), t);
+      t = fmaf(__fmul_rn(d, scB), __fmul_rn(dxB, (float)iB[r]), t);
+      t = fmaf(-__fmul_rn(dmin, mA), dxsA, t);
+      t = fmaf(-__fmul_rn(dmin, mB), dxsB, t);
+      acc[r] = t;
+    }
+  }
+};
+
+// Q6_K rows are stored on the device chunk-wise (8 super-blocks = 1680 B, the same bytes as GGUF's eight
+// 210-byte blocks, re-ordered lane-major): [qlA 32x16][qlB 32x16][qh 32x16][scales 32x4][d 8x2].
+// lane = (block, half, lh): l in [16lh,16lh+16) of the four 32-wide runs t=0..3 of that half; every run is
+// exactly one 16-weight scale group.  qlA = ql[half*64 + 16lh..], qlB = ql[half*64 + 32 + 16lh..].
+struct FmtQ6K {
+  static constexpr int R = 2, BLOCKS = 8, CHUNK = BLOCKS * QK_K, STAGES = 2;
+  static constexpr int ROW_STAGE_BYTES = BLOCKS * Q6K_BYTES;  // 1680
+  static constexpr int STAGE_BYTES = R * ROW_STAGE_BYTES;
+  static __host__ __device__ size_t x_bytes(int K) { return QActLayout::bytes(K); }
+  static __host__ __device__ size_t row_bytes(int K) { return (size_t)(K / QK_K) * Q6K_BYTES; }
+  // k in [0,2048): block = k>>8, half = (k>>7)&1, t = (k>>5)&3, lh = (k>>4)&1, u = (k>>3)&1, r = k&7
+  static DEVINL int xpos(int k) {
+    const int lane = (k >> 8) * 4 + ((k >> 7) & 1) * 2 + ((k >> 4) & 1), i = ((k >> 5) & 3) * 2 + ((k >> 3) & 1);
+    return ((i * 32 + lane) << 3) + (k & 7);
+  }
+
+  static DEVINL void issue(uint32_t dst, uint32_t bar, const GemvArgs& a, int unit, int c, uint64_t pol) {
+    const size_t rb = row_bytes(a.K);
+    const uint8_t* src = a.W + (size_t)unit * R * rb + (size_t)c * ROW_STAGE_BYTES;
+#pragma unroll
+    for (int r = 0; r < R; ++r) bulk_g2s(dst + r * ROW_STAGE_BYTES, src + (size_t)r * rb, ROW_STAGE_BYTES, bar, pol);
+  }
+  template <int PRO>
+  static DEVINL void prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane) {
+    q16_prologue<FmtQ6K, PRO>(xs, a, red, warp, lane);
+  }
+
+  static DEVINL void consume(const uint8_t* st, const uint8_t* xs, int c, const GemvArgs& a, int lane, float* acc) {
+    const int blk = lane >> 2, half = (lane >> 1) & 1, lh = lane & 1;
+    uint32_t xr[32];  // run t: xr[8t .. 8t+8) = 16 int16
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const uint4 v = QActLayout::x(xs)[(size_t)c * (CHUNK / 8) + i * 32 + lane];
+      xr[4 * i] = v.x; xr[4 * i + 1] = v.y; xr[4 * i + 2] = v.z; xr[4 * i + 3] = v.w;
+    }
+    float dxt[4];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) dxt[t] = QActLayout::dx(xs, a.K)[(c * CHUNK + blk * QK_K + half * 128) / 32 + t];
+    (void)lh;
+    int is[R][4];
+    uint32_t scw[R];
+    float dv[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const uint8_t* b = st + r * ROW_STAGE_BYTES;
+      const uint4 q0 = *reinterpret_cast<const uint4*>(b + lane * 16);
+      const uint4 q1 = *reinterpret_cast<const uint4*>(b + 512 + lane * 16);
+      const uint4 qh = *reinterpret_cast<const uint4*>(b + 1024 + lane * 16);
+      scw[r] = *reinterpret_cast<const uint32_t*>(b + 1536 + lane * 4);
+      dv[r] = __half2float(__ushort_as_half(*reinterpret_cast<const unsigned short*>(b + 1664 + blk * 2)));
+      const uint32_t a0[4] = {q0.x, q0.y, q0.z, q0.w}, a1[4] = {q1.x, q1.y, q1.z, q1.w}, ah[4] = {qh.x, qh.y, qh.z, qh.w};
+      int s[4] = {0, 0, 0, 0};
+#pragma unroll
+      for (int w = 0; w < 4; ++w) {
+        uint32_t qt[4];
+        qt[0] = (a0[w] & 0x0F0F0F0Fu) | ((ah[w] << 4) & 0x30303030u);
+        qt[1] = (a1[w] & 0x0F0F0F0Fu) | ((ah[w] << 2) & 0x30303030u);
+        qt[2] = ((a0[w] >> 4) & 0x0F0F0F0Fu) | (ah[w] & 0x30303030u);
+        qt[3] = ((a1[w] >> 4) & 0x0F0F0F0Fu) | ((ah[w] >> 2) & 0x30303030u);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const uint32_t qs = __vsub4(qt[t], 0x20202020u);  // bytes q-32 in [-32,31]
+          s[t] = dp2a_lo_ss(xr[8 * t + 2 * w], qs, s[t]);
+          s[t] = dp2a_hi_ss(xr[8 * t + 2 * w + 1], qs, s[t]);
+        }
+      }
+#pragma unroll
+      for (int t = 0; t < 4; ++t) is[r][t] = s[t];
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      float tacc = acc[r];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const float sc = (float)(int)(signed char)((scw[r] >> (8 * t)) & 0xFFu);
+        tacc = fmaf(__fmul_rn(dv[r], sc), __fmul_rn(dxt[t], (float)is[r][t]), tacc);
+      }
+      acc[r] = tacc;
+    }
+  }
+};
+
+// ------------------------------------------------------------------ epilogues
+template <int EPI, int R>
+DEVINL void epilogue(const GemvArgs& a, int unit, int lane, const float* acc, float& bestv, uint32_t& besti) {
+  const int row0 = unit * R;
+  if (EPI == EPI_STORE || EPI == EPI_LOGITS) {
+    if (lane == 0) {
+      if (EPI == EPI_STORE || a.store_logits) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) a.y[row0 + r] = acc[r];
+      }
+      if (EPI == EPI_LOGITS) {
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+          if (acc[r] > bestv) {
+            bestv = acc[r];
+            besti = (uint32_t)(a.row_base + row0 + r);  // row_base: global id of row 0 (vocab-parallel lm_head)
+          }
+      }
+    }
+  } else if (EPI == EPI_TP_PUSH) {  // lane p sends this unit's partial sums to peer p over NVLink
+    const TpLink* t = a.tp;
+    if (lane < t->size) {
+      float* dst = t->peer_recv[a.tp_index & 1][lane] + (size_t)t->rank * t->d + row0;
+#pragma unroll
+      for (int r = 0; r < R; ++r) dst[r] = acc[r];
+    }
+  } else if (EPI == EPI_RESID) {
+    if (lane == 0) {
+#pragma unroll
+      for (int r = 0; r < R; ++r) a.y[row0 + r] = __ldcg(a.y + row0 + r) + acc[r];
+    }
+  } else if (EPI == EPI_SWIGLU) {  // rows interleaved gate,up,gate,up
+#pragma unroll
+    for (int p = 0; p < R / 2; ++p)
+      if (lane == p) {
+        const float g = acc[2 * p], u = acc[2 * p + 1];
+        a.y[row0 / 2 + p] = (g / (1.0f + expf(-g))) * u;
+      }
+  } else if (EPI == EPI_QKV) {
+    const int pos = a.st->pos;
+#pragma unroll
+    for (int p = 0; p < R / 2; ++p)
+      if (lane == p) {
+        const int row = a.row_base + row0 + 2 * p;
+        float x0 = acc[2 * p], x1 = acc[2 * p + 1];
+        if (row < a.q_rows + a.kv_rows) {  // q or k: adjacent-pair rotation
+          const int i = (row & (kHeadDim - 1)) >> 1;
+          const float2 cs = *reinterpret_cast<const float2*>(a.rope + ((size_t)pos * (kHeadDim / 2) + i) * 2);
+          const float r0 = __fsub_rn(__fmul_rn(x0, cs.x), __fmul_rn(x1, cs.y));
+          const float r1 = __fadd_rn(__fmul_rn(x0, cs.y), __fmul_rn(x1, cs.x));
+          x0 = r0;
+          x1 = r1;
+        }
+        if (row < a.q_rows) {
+          *reinterpret_cast<float2*>(a.y + row) = make_float2(x0, x1);
+        } else {
+          const bool isk = row < a.q_rows + a.kv_rows;
+          const int kr = row - a.q_rows - (isk ? 0 : a.kv_rows);
+          const int kvh = kr >> 7, dim = kr & (kHeadDim - 1);
+          const int page = a.block_table[pos / kPageTokens];
+          const size_t idx = (((size_t)page * a.n_kv_heads + kvh) * kPageTokens + (pos % kPageTokens)) * kHeadDim + dim;
+          const uint32_t packed = (uint32_t)f32_to_bf16_bits(x0) | ((uint32_t)f32_to_bf16_bits(x1) << 16);
+          *reinterpret_cast<uint32_t*>((isk ? a.k_cache : a.v_cache) + idx) = packed;
+        }
+      }
+  }
+}
+
+}  // namespace
+}  // namespace b200
