@@ -1,12 +1,12 @@
-// decode_mega.cu — one token of batch-1 decode in ONE persistent kernel, sm_100a.
+// decode_mega.cu — one token of batch-1 decode in ONE persistent kernel, sm_100a.  EXPERIMENT, opt-in
+// (B200_MEGA=1): correct and bit-identical to the default path, but measured slower — see "Result" below.
 //
-// The per-projection kernels of gemv.cu stream their weights at ~96 % of the HBM peak while they stream,
-// but a decode step is 160+ launches and each one pays ~4-6 us of fill/drain around that (launch, RMS-norm /
-// quantisation prologue, first TMA round trip, the tail of the slowest warp).  Here the whole step is one
-// cooperative launch of one CTA per SM; the projections and the attention are *phases* separated by grid
-// barriers (1.3 us measured), and — the point — every warp's TMA ring keeps running across the barriers:
-// when a warp has consumed its last stage of phase p it immediately starts fetching its first stages of the
-// next mat-vec phase, so HBM does not idle while the barrier, the next prologue or the attention run.
+// Idea.  The per-projection kernels of gemv.cu stream their weights at ~96 % of the HBM peak while they
+// stream, but a decode step is 160+ launches and each one pays ~4-6 us of fill/drain around that (launch,
+// RMS-norm / quantisation prologue, first TMA round trip, the tail of the slowest warp).  Here the whole step
+// is one cooperative launch of one CTA per SM; the projections and the attention are *phases* separated by
+// grid barriers, and every warp's TMA ring keeps running across the barriers: when a warp has consumed its
+// last stage of phase p it immediately starts fetching its first stages of the next mat-vec phase.
 //
 // The arithmetic is the very same code as gemv.cu / attn.cu (gemv_formats.cuh, attn_decode.cuh): same
 // per-row accumulation order, same epilogues, so a step through this kernel is bit-identical to a step
@@ -18,6 +18,15 @@
 //
 // Every wait in this kernel is bounded (~2 s): on a time-out it raises MegaArgs::error and carries on, so a
 // bug or a lost CTA produces a wrong token and an error code, never a hung GPU.
+//
+// Result (B200, Llama-3.1-8B, ctx 576; per-phase %globaltimer trace, B200_MEGA_TRACE=<file>):
+//   bf16 3.79 ms/token vs 3.01 with the PDL-chained kernels; Q4_K_M 2.71 vs 1.73.  Per layer the phases cost
+//   qkv 13.7 + attention 14.0 + o 14.6 + gate/up 43.9 + down 27.4 = 113.6 us against 93 us for the chained
+//   kernels.  A grid barrier under load costs 2.2 us after the last arrival (1.3 us in isolation), every phase
+//   still pays its 1.5-2.4 us prologue, and a phase ends with its slowest warp (entry times into the barrier
+//   spread over 2-5 us), so the cross-phase prefetch (19 MB of ring) buys less than the barriers cost; the
+//   programmatic-dependent-launch chain already overlaps the next kernel's weight prefetch with the previous
+//   kernel's tail at a lower fixed cost.  Kept for the next round's experiments (fewer, fatter phases).
 #include "attn_decode.cuh"
 #include "gemv_formats.cuh"
 
@@ -43,8 +52,13 @@ DEVINL unsigned int ld_acquire_gpu(const unsigned int* p) {
 }
 
 // Self-resetting grid barrier (arrival counter + generation).  Cooperative launch guarantees co-residency.
-DEVINL void grid_barrier(const MegaArgs& m) {
+DEVINL void grid_barrier(const MegaArgs& m, int ph = -1) {
   __syncthreads();
+  if (m.trace && ph >= 0 && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    m.trace[(size_t)m.n_phases * 4 + (size_t)ph * 160 + blockIdx.x] = t;
+  }
   if (threadIdx.x == 0) {
     const unsigned int gen = ld_acquire_gpu(m.bar_gen);
     __threadfence();
@@ -75,6 +89,14 @@ DEVINL void mbar_wait_bounded(uint32_t bar, uint32_t parity, unsigned int* error
       dead = true;
       return;
     }
+  }
+}
+
+DEVINL void stamp(const MegaArgs& m, int ph, int k) {
+  if (m.trace && blockIdx.x == 0 && threadIdx.x == 0) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    m.trace[ph * 4 + k] = t;
   }
 }
 
@@ -157,6 +179,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_mega_kernel(const MegaA
   bool dead = false;  // a TMA wait of this warp timed out: stop waiting
   for (int ph = 0; ph < n_ph; ++ph) {
     const MegaPhase* P = m.phases + ph;
+    stamp(m, ph, 0);
     if (P->kind == 1) {  // ---- attention: (KV head, split) items on warps 0..3 of the first n_kv * S CTAs
       const int n_kv = P->t.n_kv_heads, S = m.attn_splits;
       if ((int)blockIdx.x < n_kv * S && warp < 4) {
@@ -164,7 +187,9 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_mega_kernel(const MegaA
         attn_decode_item<G>(t, *reinterpret_cast<AttnSmem<G>*>(xs), (int)blockIdx.x % n_kv, (int)blockIdx.x / n_kv, S, 0, n_kv,
                             (int)threadIdx.x, 1);
       }
-      grid_barrier(m);
+      stamp(m, ph, 2);
+      grid_barrier(m, ph);
+      stamp(m, ph, 3);
       continue;
     }
     // ---- mat-vec phase
@@ -180,6 +205,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_mega_kernel(const MegaA
       if (pro == PRO_RMSNORM) F4::template prologue<PRO_RMSNORM>(xs, a, red, warp, lane);
       else F4::template prologue<PRO_COPY>(xs, a, red, warp, lane);
     }
+    stamp(m, ph, 1);
     const bool r4 = (fmt == MF_BF16_R4 || fmt == MF_Q4K_R4);
     float bestv = -INFINITY;
     uint32_t besti = 0;
@@ -224,7 +250,14 @@ __global__ void __launch_bounds__(kWarps * 32, 1) decode_mega_kernel(const MegaA
       }
     }
     if (epi == EPI_LOGITS && lane == 0 && any) atomicMax(a.argmax_key, argmax_key(bestv, besti));
-    if (ph + 1 < n_ph) grid_barrier(m);
+    stamp(m, ph, 2);
+    if (m.trace && blockIdx.x < 2 && lane == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      m.trace[(size_t)m.n_phases * 4 + (size_t)ph * 160 + 148 + warp % 12] = t;  // (debug) a few warps of CTA 0/1
+    }
+    if (ph + 1 < n_ph) grid_barrier(m, ph);
+    stamp(m, ph, 3);
   }
 }
 

@@ -87,7 +87,9 @@ int Engine::init(const b200_config& c, const void* nccl_id) {
   use_graph = getenv("B200_NO_GRAPH") == nullptr;
   use_fa_prefill = getenv("B200_NO_FA_PREFILL") == nullptr;
   use_mma_decode = getenv("B200_NO_MMA_DECODE") == nullptr;
-  use_mega = getenv("B200_NO_MEGA") == nullptr;
+  // measured on B200 (round 1): the persistent kernel is bit-identical but SLOWER than the PDL-chained kernels
+  // (bf16 3.79 vs 3.01 ms/token, Q4_K_M 2.71 vs 1.73): see decode_mega.cu; opt-in for experiments
+  use_mega = getenv("B200_MEGA") != nullptr;
   // measured on B200 (round 1): chaining L2 prefetches of the next kernel's weights made the step SLOWER
   // (bf16 3.18 vs 3.05 ms, Q4_K_M 1.84 vs 1.78 ms), so it is opt-in for experiments only
   use_l2_chain = getenv("B200_L2_CHAIN") != nullptr;
@@ -451,8 +453,33 @@ int Engine::ensure_mega() {
   mega.phases = mega_phases; mega.n_phases = (int)ph.size(); mega.lm_head_phase = (int)ph.size() - 1; mega.st = st;
   mega.bar_count = mega_sync; mega.bar_gen = mega_sync + 1; mega.error = mega_sync + 2;
   mega.attn_splits = S; mega.x_bytes = (int)xb;
+  if (getenv("B200_MEGA_TRACE")) {
+    if ((rc = alloc((void**)&mega_trace, ph.size() * (32 + 160 * 8)))) return rc;
+    B200_CUDA(cudaMemset(mega_trace, 0, ph.size() * (32 + 160 * 8)));
+    mega.trace = mega_trace;
+  }
   mega_group = G;
   mega_ready = true;
+  return 0;
+}
+
+// debug: the last step's per-phase time stamps of CTA 0 -> "<phase> <kind> <fmt> <epi> t0 t1 t2 t3" lines
+int Engine::dump_mega_trace() {
+  const char* path = getenv("B200_MEGA_TRACE");
+  if (!mega_trace || !path) return 0;
+  std::vector<unsigned long long> t((size_t)mega.n_phases * 164);
+  std::vector<MegaPhase> ph((size_t)mega.n_phases);
+  B200_CUDA(cudaMemcpy(t.data(), mega_trace, t.size() * 8, cudaMemcpyDeviceToHost));
+  B200_CUDA(cudaMemcpy(ph.data(), mega_phases, ph.size() * sizeof(MegaPhase), cudaMemcpyDeviceToHost));
+  FILE* f = fopen(path, "w");
+  if (!f) return 0;
+  for (int i = 0; i < mega.n_phases; ++i)
+  {
+    fprintf(f, "%d %d %d %d %llu %llu %llu %llu", i, ph[i].kind, ph[i].fmt, ph[i].epi, t[4 * i], t[4 * i + 1], t[4 * i + 2], t[4 * i + 3]);
+    for (int k = 0; k < 160; ++k) fprintf(f, " %llu", t[(size_t)mega.n_phases * 4 + (size_t)i * 160 + k]);
+    fprintf(f, "\n");
+  }
+  fclose(f);
   return 0;
 }
 

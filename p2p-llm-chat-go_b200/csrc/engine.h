@@ -146,11 +146,13 @@ struct Engine {
   cudaGraphExec_t step_graph = nullptr;
   bool use_pdl = true, use_graph = true, use_l2_chain = false, use_fa_prefill = true, use_mma_decode = true;
   // persistent decode kernel (decode_mega.cu): one cooperative launch per token instead of ~5 per layer
-  bool use_mega = true, mega_ready = false;
+  bool use_mega = false, mega_ready = false;
   MegaPhase* mega_phases = nullptr;   // device
   unsigned int* mega_sync = nullptr;  // device: {barrier count, barrier generation, error}
   MegaArgs mega = {};
   int mega_group = 0;
+  unsigned long long* mega_trace = nullptr;  // device, 4 stamps per phase (B200_MEGA_TRACE=<file>)
+  int dump_mega_trace();
   int ensure_mega();          // builds the phase table once all tensors are set; leaves mega_ready false if unsupported
   int mega_check_error();     // after a synchronize: did a wait inside the kernel time out?
   int launches_per_step = 0;

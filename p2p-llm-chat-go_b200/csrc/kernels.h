@@ -195,6 +195,7 @@ struct MegaArgs {
   unsigned int* error;          // set to 1 if a wait timed out (a bug or a lost CTA): the step's results are void
   int attn_splits;              // KV splits per KV head in the attention phase (n_kv_heads * attn_splits <= grid)
   int x_bytes;                  // shared-memory bytes reserved for the activation vector / attention working set
+  unsigned long long* trace;    // debug (B200_MEGA_TRACE): CTA 0 stamps %globaltimer 4x per phase, else null
 };
 // fills fmt / n_units / chunks of a mat-vec phase from (wtype, N, K); false if the shape is not supported
 bool mega_plan_gemv(int wtype, int64_t N, int64_t K, int sm_count, MegaPhase* p);
