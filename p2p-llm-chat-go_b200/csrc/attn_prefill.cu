@@ -190,7 +190,7 @@ __global__ void __launch_bounds__(G * 32) attn_prefill_kernel(const float* __res
 // own online-softmax state; the four partial results are merged through shared memory at the end.
 // Same numerics as the prefill kernel above (Q and P as bf16 hi + lo, fp32 accumulation).
 template <int G>
-__global__ void __launch_bounds__(128) attn_decode_mma_kernel(const float* __restrict__ q, const uint16_t* __restrict__ k_cache,
+__global__ void __launch_bounds__(128, 3) attn_decode_mma_kernel(const float* __restrict__ q, const uint16_t* __restrict__ k_cache,
                                                               const uint16_t* __restrict__ v_cache, const int32_t* __restrict__ block_table,
                                                               const int32_t* __restrict__ q_ctx, const int32_t* __restrict__ q_slot,
                                                               int pages_per_seq, int q_stride, int n_kv_heads, float* __restrict__ out,
@@ -203,16 +203,24 @@ __global__ void __launch_bounds__(128) attn_decode_mma_kernel(const float* __res
   const float scale = 1.0f / sqrtf((float)kHeadDim);
   const uint32_t tiles_s = smem_u32(tiles);
 
+  // thread -> 16-byte chunk c = tid & 15 of rows r = (tid >> 4) + 8 i, i = 0..7: a thread's eight rows fall into
+  // the four 16-token pages of the tile two by two, so one block-table read serves two rows
+  const int lc = threadIdx.x & 15, lr = threadIdx.x >> 4;
   auto load_tile = [&](int st, int t0) {
     const uint32_t kb = tiles_s + st * (2 * kKvTile * 256), vb = kb + kKvTile * 256;
-    for (int item = threadIdx.x; item < kKvTile * 16; item += 128) {
-      const int r = item >> 4, c = item & 15, tok = t0 + r;
-      const bool ok = tok < ctx;
-      const int page = ok ? bt[tok / kPageTokens] : 0;
-      const size_t row = (((size_t)page * n_kv_heads + kvh) * kPageTokens + (ok ? tok % kPageTokens : 0)) * kHeadDim;
-      const uint32_t n = ok ? 16u : 0u;
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(kb + tile_off(r, c)), "l"(k_cache + row + c * 8), "r"(n) : "memory");
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(vb + tile_off(r, c)), "l"(v_cache + row + c * 8), "r"(n) : "memory");
+#pragma unroll
+    for (int pg = 0; pg < kKvTile / kPageTokens; ++pg) {
+      const int tok0 = t0 + pg * kPageTokens;
+      const int page = tok0 < ctx ? bt[tok0 / kPageTokens] : 0;
+      const size_t base = ((size_t)page * n_kv_heads + kvh) * kPageTokens * kHeadDim + lc * 8;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int rp = lr + 8 * h, r = pg * kPageTokens + rp;  // row within the page / within the tile
+        const uint32_t n = (tok0 + rp) < ctx ? 16u : 0u;      // src-size 0: zero-fill
+        const size_t row = base + (size_t)rp * kHeadDim;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(kb + tile_off(r, lc)), "l"(k_cache + row), "r"(n) : "memory");
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(vb + tile_off(r, lc)), "l"(v_cache + row), "r"(n) : "memory");
+      }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
@@ -366,6 +374,8 @@ cudaError_t launch_attn_decode_batched(const AttnArgs& a, uint16_t* out_bf16, cu
 #define LAUNCH(G_)                                                                                                         \
   {                                                                                                                        \
     cudaError_t e_ = cudaFuncSetAttribute(attn_decode_mma_kernel<G_>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem); \
+    if (e_ != cudaSuccess) return e_;                                                                                      \
+    e_ = cudaFuncSetAttribute(attn_decode_mma_kernel<G_>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);            \
     if (e_ != cudaSuccess) return e_;                                                                                      \
     attn_decode_mma_kernel<G_><<<grid, 128, kSmem, s>>>(a.q, a.k_cache, a.v_cache, a.block_table, a.q_ctx, a.q_slot,       \
                                                         a.pages_per_seq, a.q_stride, a.n_kv_heads, a.out, out_bf16);        \
