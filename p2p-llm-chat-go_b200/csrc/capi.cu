@@ -562,7 +562,17 @@ int b200_gemm(int type, const void* w, int64_t rows, int64_t cols, const float* 
   }
   B200_CUDA(cudaMemcpy(dxf.p, x, (size_t)n * cols * 4, cudaMemcpyHostToDevice));
   B200_CUDA(launch_f32_to_bf16(dxf.as<float>(), dx16.as<uint16_t>(), n * cols, 0));
-  B200_CUDA(launch_gemm_bf16(w16, rows, cols, dx16.as<uint16_t>(), n, dy.as<float>(), rows, 0));
+  // scratch for the stream-K schedule, as the engine provides it (the heuristic in gemm.cu decides)
+  DevBuf wsb, flb;
+  GemmWorkspace wk = {};
+  cudaDeviceProp prop;
+  B200_CUDA(cudaGetDeviceProperties(&prop, 0));
+  wk.sm_count = prop.multiProcessorCount;
+  wk.ws_bytes = (size_t)wk.sm_count * 256 * 256 * 4;
+  if ((rc = wsb.alloc(wk.ws_bytes)) || (rc = flb.alloc((size_t)(wk.sm_count + 8) * 4))) return rc;
+  B200_CUDA(cudaMemset(flb.p, 0, (size_t)(wk.sm_count + 8) * 4));
+  wk.ws = wsb.as<float>(); wk.flags = flb.as<unsigned int>();
+  B200_CUDA(launch_gemm_bf16(w16, rows, cols, dx16.as<uint16_t>(), n, dy.as<float>(), rows, 0, &wk));
   B200_CUDA(cudaDeviceSynchronize());
   B200_CUDA(cudaMemcpy(y, dy.p, (size_t)n * rows * 4, cudaMemcpyDeviceToHost));
   return 0;
@@ -653,6 +663,7 @@ int b200_bench_kernel(b200_engine* h, const char* which, int iters, float* ms, i
     }
     DevBuf xb, yb;
     int rc;
+    if ((rc = e->ensure_prefill())) return rc;  // the stream-K workspace lives with the prefill buffers
     if ((rc = xb.alloc((size_t)n * K * 2)) || (rc = yb.alloc((size_t)8 * n * rows * 4))) return rc;
     B200_CUDA(launch_synth(T_BF16, xb.p, n, K, 1234, 77, 1.0f, e->stream));
     cudaEvent_t e0, e1;
@@ -661,8 +672,12 @@ int b200_bench_kernel(b200_engine* h, const char* which, int iters, float* ms, i
     int splits = 8;
     for (int i = -3; i < iters; ++i) {
       if (i == 0) B200_CUDA(cudaEventRecord(e0, e->stream));
-      splits = (m == "down" || m == "attn_output") ? 8 : 1;  // as the engine calls them
-      B200_CUDA(launch_gemm_bf16_splitk(W, rows, K, xb.as<uint16_t>(), n, yb.as<float>(), rows, n * rows, &splits, e->stream));
+      if (m == "down" || m == "attn_output") {  // as the engine calls them
+        splits = 8;
+        B200_CUDA(launch_gemm_bf16_splitk(W, rows, K, xb.as<uint16_t>(), n, yb.as<float>(), rows, n * rows, &splits, e->stream));
+      } else {
+        B200_CUDA(launch_gemm_bf16(W, rows, K, xb.as<uint16_t>(), n, yb.as<float>(), rows, e->stream, e->gemm_ws.ws ? &e->gemm_ws : nullptr));
+      }
     }
     B200_CUDA(cudaEventRecord(e1, e->stream));
     B200_CUDA(cudaStreamSynchronize(e->stream));

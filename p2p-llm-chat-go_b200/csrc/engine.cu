@@ -763,6 +763,10 @@ int Engine::ensure_prefill() {
       (rc = alloc((void**)&pf_counters, (size_t)T * c.n_kv_heads * 4)))
     return rc;
   B200_CUDA(cudaMemsetAsync(pf_counters, 0, (size_t)T * c.n_kv_heads * 4, stream));
+  gemm_ws.sm_count = sm_count;
+  gemm_ws.ws_bytes = (size_t)sm_count * 256 * 256 * 4;
+  if ((rc = alloc((void**)&gemm_ws.ws, gemm_ws.ws_bytes)) || (rc = alloc((void**)&gemm_ws.flags, (size_t)(sm_count + 8) * 4))) return rc;
+  B200_CUDA(cudaMemsetAsync(gemm_ws.flags, 0, (size_t)(sm_count + 8) * 4, stream));
   pf_rows = T;
   pf_ready = true;
   return 0;
@@ -805,7 +809,7 @@ int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_ar
     B200_CUDA(launch_gemm_bf16_splitk(L.o16, d, qd, pf_xb, n, pf_proj, d, pf_proj_stride, &pf_proj_splits, s));
     if (tp_size > 1) { int rc = tp_allreduce_sum(pf_proj, (size_t)n * d, s); if (rc) return rc; }
     B200_CUDA(launch_add_rmsnorm_bf16(pf_x, pf_proj, pf_proj_splits, pf_proj_stride, L.ffn_norm, pf_xb, n, d, c.rms_eps, s));
-    B200_CUDA(launch_gemm_bf16(L.gu16, 2 * ff, d, pf_xb, n, pf_gu, 2 * ff, s));
+    B200_CUDA(launch_gemm_bf16(L.gu16, 2 * ff, d, pf_xb, n, pf_gu, 2 * ff, s, &gemm_ws));
     B200_CUDA(launch_swiglu_bf16(pf_gu, pf_xb, (int64_t)n * ff, s));
     pf_proj_splits = max_proj_splits(n);
     B200_CUDA(launch_gemm_bf16_splitk(L.down16, d, ff, pf_xb, n, pf_proj, d, pf_proj_stride, &pf_proj_splits, s));

@@ -117,6 +117,7 @@ struct Engine {
   int pf_proj_splits = 1;      // split-K partials currently sitting in pf_proj (consumers add them) ...
   int64_t pf_proj_stride = 0;  // ... this many floats apart
   int64_t pf_proj_floats = 0;  // capacity of pf_proj
+  GemmWorkspace gemm_ws = {};  // stream-K scratch of the tensor-core GEMMs (gate/up, batched lm_head)
   // most K splits a projection over n rows may use: every partial is [n][d_model] and all must fit pf_proj
   int max_proj_splits(int n) const {
     const int64_t fit = pf_proj_floats / ((int64_t)n * lc.d_model);

@@ -187,6 +187,187 @@ __global__ void __launch_bounds__(64 + 128 * MT) gemm_bf16_kernel(const __grid_c
   if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(C::TMEM_COLS) : "memory");
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Stream-K variant of the 256 x 256 kernel: one persistent CTA per SM, the (tile, K block) work items of the
+// whole GEMM are cut into equal contiguous runs, one per CTA, so the GPU is evenly loaded whatever the tile
+// count (gate/up at 512 tokens is 224 tiles = 1.51 waves of 148).  A run that starts inside a tile computes
+// that tile's remaining K blocks first and leaves its partial accumulator in a per-CTA workspace slot (flag
+// = ready); a run that ends inside a tile holds its first K blocks, computed last, and that CTA is the tile's
+// owner: it adds the partials of the following CTAs in CTA order (deterministic) and stores the tile.  The
+// partial producers run at the start of their timeline and the owner at the end of its own, so nobody waits.
+struct StreamKArgs {
+  float* y;
+  int ldy, n_tokens;
+  int tiles_m;        // weight-row tiles; tile index = n_tile * tiles_m + m_tile (row tile fastest: a CTA's
+                      // consecutive tiles share the token tile, and a row tile's token tiles run close in time)
+  int kb_total;       // K blocks (of 64) per tile
+  int units;          // work items per CTA
+  int total;          // tiles * kb_total
+  float* ws;          // [grid][256 tokens][256 rows] fp32 partials
+  unsigned int* flags;  // [grid]; 1 = that CTA's partial is in ws (the owner clears it)
+};
+
+DEVINL void bar_sync_epi(int n) { asm volatile("bar.sync 1, %0;" ::"r"(n) : "memory"); }
+
+__global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                            const __grid_constant__ CUtensorMap tmB, const StreamKArgs g) {
+  using C = GemmCfg<256, 2>;
+  constexpr int BN = 256;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t tiles = (raw + 1023u) & ~1023u;
+  uint8_t* bar_mem = smem_raw + (tiles - raw) + C::STAGES * C::STAGE;
+  uint64_t* full = reinterpret_cast<uint64_t*>(bar_mem);
+  uint64_t* empty = full + C::STAGES;
+  uint64_t* tmem_full = empty + C::STAGES;
+  uint64_t* tmem_empty = tmem_full + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 1);
+  const uint32_t full_s = smem_u32(full), empty_s = smem_u32(empty), tfull_s = smem_u32(tmem_full), tempty_s = smem_u32(tmem_empty);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int p = blockIdx.x, KB = g.kb_total;
+  const int u_begin = p * g.units, u_end = min(u_begin + g.units, g.total);
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(full_s + 8 * s, 1);
+      mbar_init(empty_s + 8 * s, 1);
+    }
+    mbar_init(tfull_s, 1);
+    mbar_init(tempty_s, 8);  // one arrival per epilogue warp
+    mbar_fence_init();
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(C::TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {  // ===== TMA producer: runs ahead of the MMAs across segment boundaries =====
+      int s = 0;
+      uint32_t ph = 0;
+      for (int u = u_begin; u < u_end;) {
+        const int tile = u / KB, k0 = u - tile * KB, k1 = min(KB, k0 + (u_end - u));
+        const int m0 = (tile % g.tiles_m) * (2 * BM), n0 = (tile / g.tiles_m) * BN;
+        for (int kb = k0; kb < k1; ++kb) {
+          mbar_wait(empty_s + 8 * s, ph ^ 1);
+          const uint32_t dst = tiles + s * C::STAGE;
+          mbar_expect_tx(full_s + 8 * s, C::STAGE);
+          tma_load_2d(dst, &tmA, kb * BK, m0, full_s + 8 * s);
+          tma_load_2d(dst + A_BYTES, &tmA, kb * BK, m0 + BM, full_s + 8 * s);
+          tma_load_2d(dst + C::AT_BYTES, &tmB, kb * BK, n0, full_s + 8 * s);
+          if (++s == C::STAGES) { s = 0; ph ^= 1; }
+        }
+        u += k1 - k0;
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {  // ===== MMA issuer =====
+      constexpr uint32_t idesc = instr_desc(BM, BN);
+      int s = 0, seg = 0;
+      uint32_t ph = 0;
+      for (int u = u_begin; u < u_end; ++seg) {
+        const int tile = u / KB, k0 = u - tile * KB, k1 = min(KB, k0 + (u_end - u));
+        mbar_wait(tempty_s, (uint32_t)((seg & 1) ^ 1));  // the previous segment's accumulators have been read out
+        tc_fence_after();
+        for (int kb = k0; kb < k1; ++kb) {
+          mbar_wait(full_s + 8 * s, ph);
+          tc_fence_after();
+          const uint64_t ad = smem_desc_sw128(tiles + s * C::STAGE);
+          const uint64_t bd = smem_desc_sw128(tiles + s * C::STAGE + C::AT_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            tc_mma(tmem_base, ad + 2 * k, bd + 2 * k, idesc, (uint32_t)((kb - k0) | k));
+            tc_mma(tmem_base + BN, ad + (A_BYTES >> 4) + 2 * k, bd + 2 * k, idesc, (uint32_t)((kb - k0) | k));
+          }
+          tc_commit(empty_s + 8 * s);
+          if (++s == C::STAGES) { s = 0; ph ^= 1; }
+        }
+        tc_commit(tfull_s);
+        u += k1 - k0;
+      }
+    }
+  } else {  // ===== epilogue warps 2..9 =====
+    const int quad = warp & 3, mt = (warp - 2) >> 2;
+    const int rloc = mt * BM + quad * 32 + lane;  // row within the 256-row tile
+    int seg = 0;
+    for (int u = u_begin; u < u_end; ++seg) {
+      const int tile = u / KB, k0 = u - tile * KB, k1 = min(KB, k0 + (u_end - u));
+      const int m0 = (tile % g.tiles_m) * (2 * BM), n0 = (tile / g.tiles_m) * BN;
+      const bool partial = k0 > 0;            // somebody else owns this tile: leave the accumulator in the workspace
+      const bool owner_split = k0 == 0 && k1 < KB;  // this CTA owns the tile and others hold its later K blocks
+      int n_parts = 0;
+      if (owner_split) {  // CTAs p+1 .. p+n_parts hold [k1, KB)
+        n_parts = (KB - k1 + g.units - 1) / g.units;
+        if (threadIdx.x == 64) {
+          for (int j = 1; j <= n_parts; ++j) {
+            const long long t0 = clock64();
+            unsigned int v;
+            do {
+              asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(g.flags + p + j) : "memory");
+            } while (v == 0u && clock64() - t0 < 4000000000ll);  // bounded: a lost CTA must not hang the GPU
+          }
+        }
+        bar_sync_epi(256);
+      }
+      mbar_wait(tfull_s, (uint32_t)(seg & 1));
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t v[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(mt * BN + c * 32);
+        asm volatile(
+            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+            "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+              "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
+              "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+              "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+            : "r"(taddr));
+        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        if (partial) {
+          float* w = g.ws + (size_t)p * (BN * 2 * BM) + (size_t)(c * 32) * (2 * BM) + rloc;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) w[(size_t)j * (2 * BM)] = __uint_as_float(v[j]);
+        } else {
+          for (int q = 1; q <= n_parts; ++q) {  // partials in CTA order; 32 independent loads in flight, then the adds
+            const float* w = g.ws + (size_t)(p + q) * (BN * 2 * BM) + (size_t)(c * 32) * (2 * BM) + rloc;
+            float t[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) t[j] = __ldcg(w + (size_t)j * (2 * BM));
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + t[j]);
+          }
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int tok = n0 + c * 32 + j;
+            if (tok < g.n_tokens) g.y[(size_t)tok * g.ldy + m0 + rloc] = __uint_as_float(v[j]);
+          }
+        }
+      }
+      tc_fence_before();
+      if (lane == 0) mbar_arrive(tempty_s);
+      if (partial) {  // publish the partial
+        __threadfence();
+        bar_sync_epi(256);
+        if (threadIdx.x == 64) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(g.flags + p), "r"(1u) : "memory");
+      }
+      if (owner_split) {  // all reads of the partials are done: re-arm the flags for the next launch
+        bar_sync_epi(256);
+        if (threadIdx.x == 64)
+          for (int j = 1; j <= n_parts; ++j) g.flags[p + j] = 0u;
+      }
+      u += k1 - k0;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(C::TMEM_COLS) : "memory");
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -231,6 +412,26 @@ cudaError_t launch_bn(const uint16_t* W, int64_t rows, int64_t K, const uint16_t
   return cudaGetLastError();
 }
 
+cudaError_t launch_streamk(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y, int64_t ldy,
+                           const GemmWorkspace& wk, cudaStream_t s) {
+  using C = GemmCfg<256, 2>;
+  CUtensorMap ma, mb;
+  if (!make_map(&ma, W, (uint64_t)rows, (uint64_t)K, BM) || !make_map(&mb, X, (uint64_t)n_tokens, (uint64_t)K, 256))
+    return cudaErrorInvalidValue;
+  cudaError_t e = cudaFuncSetAttribute(gemm_streamk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM);
+  if (e != cudaSuccess) return e;
+  StreamKArgs g;
+  g.y = Y; g.ldy = (int)ldy; g.n_tokens = (int)n_tokens;
+  g.tiles_m = (int)(rows / (2 * BM));
+  g.kb_total = (int)(K / BK);
+  g.total = g.tiles_m * (int)((n_tokens + 255) / 256) * g.kb_total;
+  g.units = (g.total + wk.sm_count - 1) / wk.sm_count;
+  g.ws = wk.ws; g.flags = wk.flags;
+  const int grid = (g.total + g.units - 1) / g.units;
+  gemm_streamk_kernel<<<grid, C::THREADS, C::SMEM, s>>>(ma, mb, g);
+  return cudaGetLastError();
+}
+
 // B200_GEMM_M256 = 0 never / 1 whenever the shape allows / unset: the heuristic below (experiments only)
 int m256_override() {
   const char* e = getenv("B200_GEMM_M256");
@@ -245,7 +446,24 @@ bool gemm_shape_ok(int64_t rows, int64_t K, int64_t n_tokens) {
 
 // Y[t*ldy + r] = sum_k X[t][k] W[r][k];  W, X bf16 (K-major, 16-byte aligned rows), Y fp32.
 cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
-                             int64_t ldy, cudaStream_t s) {
+                             int64_t ldy, cudaStream_t s, const GemmWorkspace* wk) {
+  // stream-K schedule (experiment, see below)
+  if (wk && wk->ws && wk->flags && wk->sm_count > 0 && gemm_shape_ok(rows, K, n_tokens) && rows % (2 * BM) == 0 && n_tokens > 128 &&
+      m256_override() != 0 && getenv("B200_NO_STREAMK") == nullptr) {
+    const int64_t tiles = (rows / (2 * BM)) * ((n_tokens + 255) / 256), P = wk->sm_count;
+    const int64_t waves = (tiles + P - 1) / P;
+    const int64_t total = tiles * (K / BK), units = (total + P - 1) / P;
+    // Measured on B200 (round 1): NOT faster than whole tiles in waves — gate/up at 512 tokens 122 us vs 117 us,
+    // at 256 tokens 97 us vs 62 us.  CTAs that run the same K block of neighbouring tiles in lock-step share
+    // their operand fetches in L2 (ncu: 400 MB of DRAM reads per launch in waves, 515 MB with staggered K), and
+    // every CTA pays up to three serialised epilogues.  So the schedule is opt-in: B200_GEMM_STREAMK=1 takes it
+    // for any shape it can express (tests), otherwise it is never chosen.
+    (void)waves;
+    const char* force = getenv("B200_GEMM_STREAMK");
+    const bool want = force && atoi(force) == 1 && units >= 1;
+    if (want && (size_t)P * 256 * 256 * 4 <= wk->ws_bytes)
+      return launch_streamk(W, rows, K, X, n_tokens, Y, ldy, *wk, s);
+  }
   int splits = 1;
   return launch_gemm_bf16_splitk(W, rows, K, X, n_tokens, Y, ldy, 0, &splits, s);
 }

@@ -162,8 +162,16 @@ cudaError_t launch_l2_flush(void* buf, size_t bytes, cudaStream_t s);
 cudaError_t launch_add_inplace(float* x, const float* y, int n, cudaStream_t s);
 
 // tcgen05/TMEM bf16 GEMM (gemm.cu): Y[t*ldy + r] = sum_k X[t][k] W[r][k], fp32 out
+// optional scratch for the stream-K schedule (gemm.cu): sm_count x 256 KB of partial tiles + one flag per SM
+// (flags zeroed once by the owner of the workspace; the kernel re-arms them itself)
+struct GemmWorkspace {
+  float* ws;
+  size_t ws_bytes;
+  unsigned int* flags;
+  int sm_count;
+};
 cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
-                             int64_t ldy, cudaStream_t s);
+                             int64_t ldy, cudaStream_t s, const GemmWorkspace* wk = nullptr);
 cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
                                     int64_t ldy, int64_t split_stride, int* splits, cudaStream_t s);
 bool gemm_shape_ok(int64_t rows, int64_t K, int64_t n_tokens);

@@ -72,7 +72,7 @@ int Engine::batched_step(const std::vector<int>& sl, std::vector<int32_t>* next)
   int rc = forward_gemm(B, b_tok, b_pos, b_ctx, b_slot);
   if (rc) return rc;
   B200_CUDA(launch_add_rmsnorm_bf16(pf_x, pf_proj, pf_proj_splits, pf_proj_stride, output_norm, pf_xb, B, c.d_model, c.rms_eps, stream));
-  B200_CUDA(launch_gemm_bf16(output16, c.vocab, c.d_model, pf_xb, B, b_logits, c.vocab, stream));
+  B200_CUDA(launch_gemm_bf16(output16, c.vocab, c.d_model, pf_xb, B, b_logits, c.vocab, stream, &gemm_ws));
   B200_CUDA(launch_argmax_rows(b_logits, B, c.vocab, b_next, stream));
   for (int i = 0; i < B; ++i) {  // sampled requests: the sampler kernel on that row, writing over the argmax
     const Seq& q = seqs[sl[i]];

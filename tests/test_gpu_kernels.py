@@ -166,6 +166,31 @@ def test_gemm_tcgen05_m256(pkg, rows, cols, n, monkeypatch):
     assert np.array_equal(got, pkg.gemm(orc.BF16, W, rows, cols, X))  # same K order: same bits as the 128-row tiles
 
 
+# stream-K schedule of the 256 x 256 tiles (persistent CTAs, tiles cut across CTAs, partials through a
+# workspace, summed by the tile's owner in CTA order): forced on small shapes, where a tile is shared by up to
+# 32 CTAs; repeated calls must give the same bits (deterministic reduction, flags re-armed by the kernel)
+@pytest.mark.parametrize("rows,cols,n", [(256, 64, 129), (512, 2048, 300), (1024, 4096, 256), (4096, 1024, 513), (28672, 4096, 512)])
+def test_gemm_tcgen05_streamk(pkg, rows, cols, n, monkeypatch):
+    rng = np.random.default_rng(11 * rows + cols + n)
+    W = random_tensor(rng, orc.BF16, rows, cols)
+    X = rng.standard_normal((n, cols)).astype(np.float32)
+    monkeypatch.setenv("B200_GEMM_STREAMK", "1")
+    got = pkg.gemm(orc.BF16, W, rows, cols, X)
+    again = pkg.gemm(orc.BF16, W, rows, cols, X)
+    assert np.array_equal(got, again)
+    monkeypatch.setenv("B200_GEMM_STREAMK", "0")
+    monkeypatch.setenv("B200_NO_STREAMK", "1")
+    plain = pkg.gemm(orc.BF16, W, rows, cols, X)
+    Wf = orc.bf16_to_f32(W).reshape(rows, cols)
+    budget = np.abs(X).astype(np.float64) @ np.abs(Wf).astype(np.float64).T
+    if rows * cols * n <= 1 << 31:  # the oracle in seconds
+        want = orc.matmul(orc.BF16, W, rows, cols, X, mode=1)
+        err = np.abs(got.astype(np.float64) - want)
+        assert (err <= 1e-5 * budget + 1e-30).all(), float((err / (budget + 1e-30)).max())
+    # against the one-CTA-per-tile schedule: same products, fp32 sums grouped differently
+    assert (np.abs(got.astype(np.float64) - plain) <= 1e-5 * budget + 1e-30).all()
+
+
 def test_gemm_rejects_bad_shapes(pkg):
     with pytest.raises(pkg.B200Error):
         pkg.gemm(orc.BF16, np.zeros((100, 64), np.uint16), 100, 64, np.zeros((1, 64), np.float32))
