@@ -244,6 +244,7 @@ def run_tp(args):
     dist.broadcast_object_list(box, src=0)
     cfg = pkg.llama31_70b() if args.model == "70b" else pkg.llama31_8b()
     cfg.device, cfg.max_ctx, cfg.seed, cfg.eos_token = local, 1024, 0, -1
+    cfg.max_seqs = 32  # slots for the bs32 line (b200_bench_batched); requests themselves are served one at a time
     eng = pkg.Engine(cfg, tp_rank=rank, tp_size=world, nccl_id=box[0])
     prompt = synthetic_prompt(cfg.vocab, N_PROMPT)
     for _ in range(max(args.warmup, 3)):
@@ -259,7 +260,23 @@ def run_tp(args):
     wall = time.perf_counter() - t0
     clocks = sampler.stop()
     step_ms, launches = eng.bench_decode(N_PROMPT + N_NEW // 2, 32)
-    dec_ms, wall, ttft_p50, step_ms = max_over_ranks(dist, [dec_ms, wall, statistics.median(ttfts), step_ms], f"cuda:{local}")
+    # bs32: 32 sequences decoding together on the tensor-core path (NCCL all-reduce of [32, d_model] after o and down)
+    bs = 32
+    b_ms, b_ids = eng.bench_batched(bs, N_PROMPT + N_NEW // 2, 16)
+    # the same all-reduces alone (2 per layer, fp32 [32, d_model]) on the same NVLink fabric, device-timed
+    t = torch.zeros(bs * cfg.d_model, dtype=torch.float32, device=f"cuda:{local}")
+    for _ in range(20):
+        dist.all_reduce(t)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(local); dist.barrier()
+    ev0.record()
+    for _ in range(2 * cfg.n_layers):
+        dist.all_reduce(t)
+    ev1.record()
+    torch.cuda.synchronize(local)
+    ar_ms = ev0.elapsed_time(ev1)
+    dec_ms, wall, ttft_p50, step_ms, b_ms, ar_ms = max_over_ranks(
+        dist, [dec_ms, wall, statistics.median(ttfts), step_ms, b_ms, ar_ms], f"cuda:{local}")
     if rank == 0:
         peaks, peak_src = measured_peaks()
         hbm = float(peaks["hbm_gbs"])
@@ -274,6 +291,10 @@ def run_tp(args):
             "step_roofline": {"bound": "hbm", "bytes_per_token_per_gpu": wb + kv, "ms_per_token": step_ms,
                               "achieved": (wb + kv) / (step_ms * 1e-3) / 1e9, "peak": hbm, "unit": "GB/s per GPU",
                               "frac": (wb + kv) / (step_ms * 1e-3) / 1e9 / hbm, "launches_per_token": launches, "peak_source": peak_src},
+            "bs32": {"decode_tok_per_s": bs / (b_ms * 1e-3), "ms_per_step": b_ms, "ctx": N_PROMPT + N_NEW // 2,
+                     "allreduce_ms_per_step": ar_ms, "allreduce_share": ar_ms / b_ms,
+                     "note": "b200_bench_batched: 32 sequences per step, tensor-core GEMMs, NCCL all-reduce of fp32 [32, d_model] x 2 per layer; "
+                             "allreduce_* = the same 2*n_layers all-reduces timed alone"},
             "gpu_launches": args.steps * (N_NEW - 1) * launches, "clocks": clocks}))
     eng.close()
     dist.barrier()

@@ -202,6 +202,10 @@ B200_API int b200_attn_decode_noalloc(const float* q_dev, const uint16_t* k_cach
 /* Runs `n_steps` decode steps (graph replays) starting from the current context; returns the mean step
  * time in milliseconds and the number of kernels launched per step. */
 B200_API int b200_bench_decode(b200_engine* e, int ctx, int n_steps, float* ms_per_step, int* launches_per_step);
+/* `n_seqs` sequences decoding together (the continuous-batching step on the tensor cores) from a context of
+ * `ctx` tokens each, driven synchronously; mean step time in ms; last_ids (may be NULL) receives the n_seqs token
+ * ids of the final step.  Tensor-parallel engines: every rank makes the same call.  No reference counterpart. */
+B200_API int b200_bench_batched(b200_engine* e, int n_seqs, int ctx, int n_steps, float* ms_per_step, int32_t* last_ids);
 /* Times only the dominant kernel (the fused gate/up GEMV of layer 0) `iters` times, L2 flushed between. */
 B200_API int b200_bench_kernel(b200_engine* e, const char* which, int iters, float* ms, int64_t* bytes);
 

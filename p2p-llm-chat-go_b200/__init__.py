@@ -107,6 +107,7 @@ def lib():
         "b200_attn_decode_noalloc": (i32, [vp, vp, vp, vp, i32, i32, i32, vp, vp]),
         "b200_sample": (i32, [vp, i32, smpp, vp, i32, u64, C.POINTER(C.c_int32)]),
         "b200_bench_decode": (i32, [vp, i32, i32, C.POINTER(f32), C.POINTER(i32)]),
+        "b200_bench_batched": (i32, [vp, i32, i32, i32, C.POINTER(f32), vp]),
         "b200_bench_kernel": (i32, [vp, C.c_char_p, i32, C.POINTER(f32), C.POINTER(i64)]),
     }
     for name, (res, args) in sig.items():
@@ -391,6 +392,13 @@ class Engine:
         ms, nl = C.c_float(), C.c_int()
         _check(lib().b200_bench_decode(self.h, ctx, n_steps, C.byref(ms), C.byref(nl)))
         return ms.value, nl.value
+
+    def bench_batched(self, n_seqs, ctx, n_steps):
+        """(ms per step, ids of the last step) of n_seqs sequences decoding together from a ctx-token context."""
+        ms = C.c_float()
+        ids = np.zeros(n_seqs, np.int32)
+        _check(lib().b200_bench_batched(self.h, n_seqs, ctx, n_steps, C.byref(ms), _p(ids)))
+        return ms.value, ids
 
     def bench_kernel(self, which, iters):
         ms, nb = C.c_float(), C.c_int64()

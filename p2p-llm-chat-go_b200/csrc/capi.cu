@@ -547,7 +547,7 @@ int b200_gemm(int type, const void* w, int64_t rows, int64_t cols, const float* 
   if (!w || !x || !y) { set_error("null argument"); return B200_EINVAL; }
   if (type != T_BF16 && type != T_Q4_K && type != T_Q6_K) { set_error("b200_gemm: type must be BF16, Q4_K or Q6_K"); return B200_EINVAL; }
   if (!gemm_shape_ok(rows, cols, n) || (type != T_BF16 && cols % QK_K)) {
-    set_error("gemm shape rows=%lld (need %%128) cols=%lld (need %%64; %%256 for k-quants) n=%lld unsupported", (long long)rows, (long long)cols, (long long)n);
+    set_error("gemm shape rows=%lld (need %%8) cols=%lld (need %%64; %%256 for k-quants) n=%lld unsupported", (long long)rows, (long long)cols, (long long)n);
     return B200_EINVAL;
   }
   DevBuf dw, dw16, dxf, dx16, dy;
@@ -633,6 +633,20 @@ int b200_bench_decode(b200_engine* h, int ctx, int n_steps, float* ms_per_step, 
   if (ms_per_step) *ms_per_step = ms / n_steps;
   if (launches_per_step) *launches_per_step = e->launches_per_step;
   return 0;
+}
+
+int b200_bench_batched(b200_engine* h, int n_seqs, int ctx, int n_steps, float* ms_per_step, int32_t* last_ids) {
+  Engine* e = reinterpret_cast<Engine*>(h);
+  if (!e || n_seqs < 1 || n_seqs > e->cfg.max_seqs || ctx < 1 || n_steps < 1 || ctx + n_steps + 3 > e->cfg.max_ctx) {
+    set_error("bad argument (n_seqs <= max_seqs, ctx + n_steps + 3 <= max_ctx)");
+    return B200_EINVAL;
+  }
+  std::lock_guard<std::mutex> lk(e->mu);
+  B200_CUDA(cudaSetDevice(e->cfg.device));
+  for (auto& q : e->seqs)
+    if (q.r) { set_error("engine is serving requests"); return B200_ESTATE; }
+  e->bs1_owner = -1;
+  return e->bench_batched(n_seqs, ctx, n_steps, ms_per_step, last_ids);
 }
 
 int b200_bench_kernel(b200_engine* h, const char* which, int iters, float* ms, int64_t* bytes) {

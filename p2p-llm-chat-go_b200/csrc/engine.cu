@@ -96,8 +96,8 @@ int Engine::init(const b200_config& c, const void* nccl_id) {
 
   const int tp = tp_size, R = tp_rank;
   if (tp < 1 || R < 0 || R >= tp || c.n_heads % tp || c.n_kv_heads % tp || c.d_ffn % tp || c.vocab % tp ||
-      (tp > 1 && (c.weight_format != B200_WEIGHTS_BF16 || c.max_seqs != 1))) {
-    set_error("tensor parallel degree %d unsupported for this config (heads, kv heads, d_ffn, vocab must divide; bf16, max_seqs 1)", tp);
+      (tp > 1 && c.weight_format != B200_WEIGHTS_BF16)) {
+    set_error("tensor parallel degree %d unsupported for this config (heads, kv heads, d_ffn, vocab must divide; bf16)", tp);
     return B200_EINVAL;
   }
   lc = c;

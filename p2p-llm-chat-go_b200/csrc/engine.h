@@ -76,6 +76,7 @@ struct Engine {
   int tp_init(const void* unique_id);
   int tp_allreduce_sum(float* buf, size_t n, cudaStream_t s);
   int tp_allreduce_max_u64(unsigned long long* buf, cudaStream_t s);
+  int tp_allreduce_max_u64_n(unsigned long long* buf, size_t n, cudaStream_t s);
   int tp_allgather(const float* send, float* recv, size_t n_per_rank, cudaStream_t s);
   int sm_count = 148;
   cudaStream_t stream = nullptr;
@@ -154,6 +155,10 @@ struct Engine {
   int mega_group = 0;
   unsigned long long* mega_trace = nullptr;  // device, 4 stamps per phase (B200_MEGA_TRACE=<file>)
   int dump_mega_trace();
+  // n_seqs sequences decoding together from a context of ctx tokens, synchronously (no scheduler thread): the
+  // batched step of scheduler.cu, tensor-parallel aware (every rank makes the same call)
+  int bench_batched(int n_seqs, int ctx, int n_steps, float* ms_per_step, int32_t* last_ids);
+  unsigned long long* b_keys = nullptr;  // [max_seqs] argmax keys (vocab-parallel lm_head)
   int ensure_mega();          // builds the phase table once all tensors are set; leaves mega_ready false if unsupported
   int mega_check_error();     // after a synchronize: did a wait inside the kernel time out?
   int launches_per_step = 0;

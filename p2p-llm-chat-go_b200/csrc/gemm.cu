@@ -81,6 +81,7 @@ struct GemmArgs {
   float* y;
   int ldy;       // floats between consecutive tokens of y
   int n_tokens;  // valid tokens (TMA zero-fills the rest of a token tile)
+  int n_rows;    // valid weight rows (the last row tile may be ragged: vocab-parallel lm_head shards)
   int k_blocks;  // K / 64 blocks handled by ONE CTA (split-K: blockIdx.z picks which run of them)
   long long split_stride;  // floats between the partial outputs of consecutive K splits
 };
@@ -178,7 +179,7 @@ __global__ void __launch_bounds__(64 + 128 * MT) gemm_bf16_kernel(const __grid_c
 #pragma unroll
       for (int j = 0; j < 32; ++j) {
         const int tok = n0 + c * 32 + j;
-        if (tok < g.n_tokens) g.y[(size_t)blockIdx.z * g.split_stride + (size_t)tok * g.ldy + row] = __uint_as_float(v[j]);
+        if (tok < g.n_tokens && row < g.n_rows) g.y[(size_t)blockIdx.z * g.split_stride + (size_t)tok * g.ldy + row] = __uint_as_float(v[j]);
       }
     }
   }
@@ -406,8 +407,8 @@ cudaError_t launch_bn(const uint16_t* W, int64_t rows, int64_t K, const uint16_t
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM);
   if (e != cudaSuccess) return e;
   GemmArgs g;
-  g.y = Y; g.ldy = (int)ldy; g.n_tokens = (int)n_tokens; g.k_blocks = (int)(K / BK) / splits; g.split_stride = split_stride;
-  dim3 grid((unsigned)(rows / (BM * MT)), (unsigned)((n_tokens + BN - 1) / BN), (unsigned)splits);
+  g.y = Y; g.ldy = (int)ldy; g.n_tokens = (int)n_tokens; g.n_rows = (int)rows; g.k_blocks = (int)(K / BK) / splits; g.split_stride = split_stride;
+  dim3 grid((unsigned)((rows + BM * MT - 1) / (BM * MT)), (unsigned)((n_tokens + BN - 1) / BN), (unsigned)splits);
   kern<<<grid, C::THREADS, C::SMEM, s>>>(ma, mb, g);
   return cudaGetLastError();
 }
@@ -441,7 +442,8 @@ int m256_override() {
 }  // namespace
 
 bool gemm_shape_ok(int64_t rows, int64_t K, int64_t n_tokens) {
-  return rows > 0 && rows % BM == 0 && K > 0 && K % BK == 0 && n_tokens > 0 && n_tokens <= (1 << 20);
+  // rows: any multiple of 8 (ragged last tile: TMA zero-fills, the epilogue masks); K: whole 64-column blocks
+  return rows > 0 && rows % 8 == 0 && K > 0 && K % BK == 0 && n_tokens > 0 && n_tokens <= (1 << 20);
 }
 
 // Y[t*ldy + r] = sum_k X[t][k] W[r][k];  W, X bf16 (K-major, 16-byte aligned rows), Y fp32.
@@ -490,8 +492,8 @@ cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, 
     }
   }
   // 128-row tiles, two CTAs per SM; token tile 256 when that still yields >= 2 CTAs per SM of work, else 128
-  const int64_t tiles256 = (rows / BM) * ((n_tokens + 255) / 256);
-  const int64_t tiles128 = (rows / BM) * ((n_tokens + 127) / 128);
+  const int64_t tiles256 = ((rows + BM - 1) / BM) * ((n_tokens + 255) / 256);
+  const int64_t tiles128 = ((rows + BM - 1) / BM) * ((n_tokens + 127) / 128);
   int use = 1;
   if (max_splits >= 2 && tiles128 < 296 && tiles128 >= 32 && kb % 2 == 0 && K >= 2048) use = 2;
   *splits = use;

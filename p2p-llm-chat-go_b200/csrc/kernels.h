@@ -222,6 +222,9 @@ cudaError_t launch_rope_kv(const float* qkv, float* q, uint16_t* k_cache, uint16
                            int tokens, int q_rows, int kv_rows, int n_kv_heads, int pos0, const int32_t* pos_arr, const int32_t* slot_arr,
                            int pages_per_seq, cudaStream_t s);
 cudaError_t launch_argmax_rows(const float* logits, int rows, int vocab, int32_t* next, cudaStream_t s);
+// vocab-parallel: per-row key of the local maximum (global id = id_base + index), max-all-reduced, then decoded
+cudaError_t launch_argmax_rows_keys(const float* logits, int rows, int vocab, int id_base, unsigned long long* keys, cudaStream_t s);
+cudaError_t launch_keys_to_ids(const unsigned long long* keys, int32_t* next, int rows, cudaStream_t s);
 cudaError_t launch_append_history(const int32_t* next, const int32_t* slot_arr, const int32_t* pos_arr, int32_t* history, int max_ctx, int rows,
                                   cudaStream_t s);
 cudaError_t launch_swiglu_bf16(const float* gu, uint16_t* h, int64_t n_pairs, cudaStream_t s);

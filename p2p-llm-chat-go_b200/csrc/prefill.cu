@@ -109,12 +109,14 @@ __global__ void take_row_kernel(const float* x, const float* add, int n_parts, l
 }
 
 // next[row] = argmax of logits[row][:] (lowest id on ties); one CTA per row
-__global__ void argmax_rows_kernel(const float* logits, int vocab, int32_t* next) {
+// keys != null (vocab-parallel lm_head): instead leave the packed (logit, ~global id) key of the row's maximum,
+// id = id_base + local index, for a max all-reduce over the ranks
+__global__ void argmax_rows_kernel(const float* logits, int vocab, int32_t* next, int id_base, unsigned long long* keys) {
   __shared__ unsigned long long red[32];
   const float* lg = logits + (size_t)blockIdx.x * vocab;
   unsigned long long best = 0;
   for (int i = threadIdx.x; i < vocab; i += blockDim.x) {
-    const unsigned long long k = argmax_key(lg[i], (uint32_t)i);
+    const unsigned long long k = argmax_key(lg[i], (uint32_t)(id_base + i));
     best = k > best ? k : best;
   }
   for (int o = 16; o > 0; o >>= 1) {
@@ -125,8 +127,14 @@ __global__ void argmax_rows_kernel(const float* logits, int vocab, int32_t* next
   __syncthreads();
   if (threadIdx.x == 0) {
     for (int w = 1; w < (int)(blockDim.x >> 5); ++w) best = red[w] > best ? red[w] : best;
-    next[blockIdx.x] = (int32_t)argmax_key_index(best);
+    if (keys) keys[blockIdx.x] = best;
+    else next[blockIdx.x] = (int32_t)argmax_key_index(best);
   }
+}
+
+__global__ void keys_to_ids_kernel(const unsigned long long* keys, int32_t* next, int rows) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < rows) next[r] = (int32_t)argmax_key_index(keys[r]);
 }
 
 // history[slot][pos+1] = next token of every row (the repeat penalty of sampled requests reads it)
@@ -138,7 +146,15 @@ __global__ void append_history_kernel(const int32_t* next, const int32_t* slot_a
 }  // namespace
 
 cudaError_t launch_argmax_rows(const float* logits, int rows, int vocab, int32_t* next, cudaStream_t s) {
-  argmax_rows_kernel<<<rows, 1024, 0, s>>>(logits, vocab, next);
+  argmax_rows_kernel<<<rows, 1024, 0, s>>>(logits, vocab, next, 0, nullptr);
+  return cudaGetLastError();
+}
+cudaError_t launch_argmax_rows_keys(const float* logits, int rows, int vocab, int id_base, unsigned long long* keys, cudaStream_t s) {
+  argmax_rows_kernel<<<rows, 1024, 0, s>>>(logits, vocab, nullptr, id_base, keys);
+  return cudaGetLastError();
+}
+cudaError_t launch_keys_to_ids(const unsigned long long* keys, int32_t* next, int rows, cudaStream_t s) {
+  keys_to_ids_kernel<<<(rows + 255) / 256, 256, 0, s>>>(keys, next, rows);
   return cudaGetLastError();
 }
 cudaError_t launch_append_history(const int32_t* next, const int32_t* slot_arr, const int32_t* pos_arr, int32_t* history, int max_ctx, int rows,

@@ -90,6 +90,49 @@ int Engine::batched_step(const std::vector<int>& sl, std::vector<int32_t>* next)
   return 0;
 }
 
+int Engine::bench_batched(int B, int ctx, int n_steps, float* ms_per_step, int32_t* last_ids) {
+  int rc = ensure_batched();
+  if (rc) return rc;
+  const b200_config& c = lc;  // per-rank shapes
+  if (!b_keys && (rc = alloc((void**)&b_keys, (size_t)cfg.max_seqs * 8))) return rc;
+  std::vector<int32_t> tok(B, 1), pos(B), cx(B), slot(B);
+  for (int i = 0; i < B; ++i) slot[i] = i;
+  B200_CUDA(cudaMemcpyAsync(b_tok, tok.data(), (size_t)B * 4, cudaMemcpyHostToDevice, stream));
+  B200_CUDA(cudaMemcpyAsync(b_slot, slot.data(), (size_t)B * 4, cudaMemcpyHostToDevice, stream));
+  cudaEvent_t e0, e1;
+  B200_CUDA(cudaEventCreate(&e0));
+  B200_CUDA(cudaEventCreate(&e1));
+  const int warm = 3;
+  for (int step = 0; step < warm + n_steps && !rc; ++step) {
+    if (step == warm) B200_CUDA(cudaEventRecord(e0, stream));
+    for (int i = 0; i < B; ++i) { pos[i] = ctx - 1 + step; cx[i] = ctx + step; }
+    B200_CUDA(cudaMemcpyAsync(b_pos, pos.data(), (size_t)B * 4, cudaMemcpyHostToDevice, stream));
+    B200_CUDA(cudaMemcpyAsync(b_ctx, cx.data(), (size_t)B * 4, cudaMemcpyHostToDevice, stream));
+    if ((rc = forward_gemm(B, b_tok, b_pos, b_ctx, b_slot))) break;
+    B200_CUDA(launch_add_rmsnorm_bf16(pf_x, pf_proj, pf_proj_splits, pf_proj_stride, output_norm, pf_xb, B, c.d_model, c.rms_eps, stream));
+    B200_CUDA(launch_gemm_bf16(output16, c.vocab, c.d_model, pf_xb, B, b_logits, c.vocab, stream, &gemm_ws));
+    if (tp_size > 1) {  // vocab-parallel lm_head: per-row (logit, id) keys, max over the ranks
+      B200_CUDA(launch_argmax_rows_keys(b_logits, B, c.vocab, tp_rank * c.vocab, b_keys, stream));
+      if ((rc = tp_allreduce_max_u64_n(b_keys, (size_t)B, stream))) break;
+      B200_CUDA(launch_keys_to_ids(b_keys, b_next, B, stream));
+    } else {
+      B200_CUDA(launch_argmax_rows(b_logits, B, c.vocab, b_next, stream));
+    }
+    B200_CUDA(cudaMemcpyAsync(b_tok, b_next, (size_t)B * 4, cudaMemcpyDeviceToDevice, stream));  // feed the next step
+    B200_CUDA(cudaStreamSynchronize(stream));  // pos / cx are rewritten next iteration (and the scheduler syncs per step too)
+  }
+  cudaEventRecord(e1, stream);
+  cudaError_t ce = cudaStreamSynchronize(stream);
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0); cudaEventDestroy(e1);
+  if (rc) return rc;
+  if (ce != cudaSuccess) return cuda_fail(ce, "bench_batched sync");
+  if (last_ids) B200_CUDA(cudaMemcpy(last_ids, b_next, (size_t)B * 4, cudaMemcpyDeviceToHost));
+  if (ms_per_step) *ms_per_step = ms / n_steps;
+  return 0;
+}
+
 void Engine::deliver(int slot, const int32_t* toks, int n) {
   Seq& q = seqs[slot];
   Request* r = q.r;
@@ -261,6 +304,9 @@ void Engine::worker_loop() {
     // ---- admit waiting requests into free slots; while sequences are decoding, at most a few prefills per
     // iteration so that running requests keep producing tokens (bounded inter-token stall)
     int budget = active.empty() ? (int)seqs.size() : 4;
+    // tensor-parallel engines are driven SPMD (every rank makes the same calls): admission timing would differ
+    // between ranks, so they serve one request at a time; several slots exist only for b200_bench_batched
+    if (tp_size > 1) budget = active.empty() ? 1 : 0;
     for (int s = 0; s < (int)seqs.size() && budget > 0; ++s) {
       if (seqs[s].r) continue;
       --budget;

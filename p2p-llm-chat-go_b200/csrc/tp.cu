@@ -89,6 +89,10 @@ int Engine::tp_allreduce_max_u64(unsigned long long* buf, cudaStream_t s) {
   ncclResult_t r = nccl()->AllReduce(buf, buf, 1, ncclUint64, ncclMax, (ncclComm_t)nccl_comm, s);
   return r == ncclSuccess ? 0 : nccl_fail(r, "ncclAllReduce(max)");
 }
+int Engine::tp_allreduce_max_u64_n(unsigned long long* buf, size_t n, cudaStream_t s) {
+  ncclResult_t r = nccl()->AllReduce(buf, buf, n, ncclUint64, ncclMax, (ncclComm_t)nccl_comm, s);
+  return r == ncclSuccess ? 0 : nccl_fail(r, "ncclAllReduce(max)");
+}
 int Engine::tp_allgather(const float* send, float* recv, size_t n_per_rank, cudaStream_t s) {
   ncclResult_t r = nccl()->AllGather(send, recv, n_per_rank, ncclFloat32, (ncclComm_t)nccl_comm, s);
   return r == ncclSuccess ? 0 : nccl_fail(r, "ncclAllGather");

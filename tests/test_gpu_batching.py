@@ -7,7 +7,7 @@ import pytest
 
 import __graft_entry__ as ge
 from oracle import orc
-from tests.util import engine_and_oracle
+from tests.util import engine_and_oracle, tiny_cfg
 
 pytestmark = pytest.mark.gpu
 TOL = 3e-3  # same logit tolerance as the prefill tests (bf16 GEMM inputs)
@@ -113,3 +113,21 @@ def test_mixed_traffic_completes_and_single_request_uses_fast_path(pkg):
         r = eng.submit(p0, sp)
         assert list(r.tokens()) == want.tolist()
         r.free()
+
+
+def test_bench_batched_hook_is_deterministic(pkg):
+    """b200_bench_batched: the batched step driven synchronously (what bench.py times for BASELINE config 5's
+    bs32 line).  Fresh engine: every sequence sees the same (zero) history, so all rows pick the same token, and a
+    second engine repeats the first one's ids."""
+    def run():
+        cfg = tiny_cfg(pkg, 0, n_layers=2, seed=71, max_ctx=128)
+        cfg.max_seqs = 8
+        with pkg.Engine(cfg) as eng:
+            ms, ids = eng.bench_batched(8, 40, 5)
+            with pytest.raises(pkg.B200Error):
+                eng.bench_batched(9, 40, 5)   # more sequences than slots
+        return ms, ids
+    ms, ids = run()
+    assert ms > 0 and ((0 <= ids) & (ids < 1024)).all()
+    assert len(set(ids.tolist())) == 1
+    assert run()[1].tolist() == ids.tolist()
