@@ -230,6 +230,64 @@ def run_peers(eng, pkg, cfg, n_peers, n_prompt, n_new):
             "request_ms_p50": totals[len(totals) // 2], "note": "TTFT counted from admission into a slot; queueing before it is in request_ms"}
 
 
+def run_http(n_runs=20):
+    """SURVEY 8(d) config 2 as the reference would see it: llmd (the Ollama drop-in) serving the random-init 8B bf16
+    model over HTTP; the web/streamlit_app.py:91-95 request with a 512-token prompt, streamed.  TTFT = request start ->
+    first NDJSON chunk at the client; decode tok/s = eval_count / eval_duration of the final object (server side)."""
+    import socket
+    import subprocess
+    import requests
+    import __graft_entry__ as ge
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    env = dict(os.environ, LLMD_ADDR=f"127.0.0.1:{port}", LLMD_MAX_CTX="1024", LLMD_SEED="0", LLMD_MODEL="llama3.1", LLMD_EOS="-1",
+               LLMD_MAX_SEQS="4")
+    proc = subprocess.Popen([os.path.join(ge.PKG_DIR, "llmd")], env=env, stderr=subprocess.DEVNULL)
+    url = f"http://127.0.0.1:{port}"
+    try:
+        for _ in range(1200):
+            if proc.poll() is not None:
+                raise RuntimeError("llmd exited")
+            try:
+                if requests.get(url + "/", timeout=1).status_code == 200:
+                    break
+            except requests.RequestException:
+                time.sleep(0.1)
+        else:
+            raise RuntimeError("llmd did not come up")
+        # no vocabulary in a random-init engine: ids 0..255 are bytes, so 511 ASCII characters + BOS = 512 tokens
+        text = ("userA: are we still on for friday? userB: yes, 7pm at the usual place. " * 8)[:N_PROMPT - 1]
+        body = {"model": "llama3.1", "prompt": text, "raw": True, "stream": True,
+                "options": {"temperature": 0, "num_predict": N_NEW, "seed": 0}}
+        ttft_c, ttft_s, tps, n_prompt = [], [], [], 0
+        for i in range(n_runs + 2):
+            t0 = time.perf_counter()
+            first, last = None, None
+            with requests.post(url + "/api/generate", json=body, stream=True, timeout=120) as r:
+                r.raise_for_status()
+                for ln in r.iter_lines():
+                    if not ln:
+                        continue
+                    if first is None:
+                        first = time.perf_counter() - t0
+                    last = ln
+            fin = json.loads(last)
+            if i < 2:
+                continue  # warm-up: graph capture, prefill buffers
+            n_prompt = fin["prompt_eval_count"]
+            ttft_c.append(first * 1e3)
+            ttft_s.append((fin["load_duration"] + fin["prompt_eval_duration"]) / 1e6)
+            tps.append(fin["eval_count"] / (fin["eval_duration"] / 1e9))
+        return {"runs": n_runs, "prompt_tokens": n_prompt, "ttft_ms_client_p50": statistics.median(ttft_c),
+                "ttft_ms_server_p50": statistics.median(ttft_s), "decode_tok_per_s_p50": statistics.median(tps),
+                "api": "POST /api/generate (stream) on llmd, 127.0.0.1, requests client"}
+    finally:
+        proc.terminate()
+        try:
+            proc.wait(timeout=20)
+        except Exception:
+            proc.kill()
+
+
 def run_tp(args):
     """BASELINE configs[4]: one model tensor-parallel over all ranks (torchrun), NCCL all-reduce over NVLink.
     Every rank drives its shard with the same calls (SPMD); timing is the max over ranks."""
@@ -394,6 +452,13 @@ def run_ours(args):
             cfg.max_seqs, cfg.max_ctx = 1, 1024
         except Exception as ex:
             extra["peers256"] = {"error": str(ex)}
+        # the same workload through the HTTP boundary the reference actually calls (N=1 only)
+        try:
+            if world > 1 or os.environ.get("B200_BENCH_FAST"):
+                raise RuntimeError("measured at N=1 only")
+            extra["http"] = run_http()  # llmd is its own process with its own engine (ours are closed by now)
+        except Exception as ex:
+            extra["http"] = {"error": str(ex)}
         # CPU baseline: the oracle on this box's host cores, bounded sample of the same workload
         try:
             if world > 1:

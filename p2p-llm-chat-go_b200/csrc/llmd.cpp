@@ -339,8 +339,9 @@ int main() {
   const int tiny = atoi(env("LLMD_TINY", "0").c_str());
   if (tiny > 0) {  // small random-init model of the same architecture (tests)
     g_cfg.n_layers = tiny; g_cfg.d_model = 2048; g_cfg.n_heads = 16; g_cfg.n_kv_heads = 4; g_cfg.d_ffn = 2048; g_cfg.vocab = 1024;
-    g_cfg.rope_orig_ctx = 64; g_cfg.eos_token = atoi(env("LLMD_EOS", "-1").c_str());
+    g_cfg.rope_orig_ctx = 64; g_cfg.eos_token = -1;
   }
+  if (getenv("LLMD_EOS")) g_cfg.eos_token = atoi(env("LLMD_EOS", "-1").c_str());  // benchmarks: -1 = never stop early
   g_cfg.weight_format = env("LLMD_WEIGHTS", "bf16") == "q4_k_m" ? B200_WEIGHTS_Q4_K_M : B200_WEIGHTS_BF16;
   g_cfg.device = atoi(env("LLMD_GPU", "0").c_str());
   g_cfg.max_ctx = atoi(env("LLMD_MAX_CTX", "2048").c_str());
