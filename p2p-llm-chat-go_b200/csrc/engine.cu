@@ -785,8 +785,11 @@ int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_ar
   for (int l = 0; l < c.n_layers; ++l) {
     Layer& L = layers[l];
     B200_CUDA(launch_add_rmsnorm_bf16(pf_x, l ? pf_proj : nullptr, pf_proj_splits, pf_proj_stride, L.attn_norm, pf_xb, n, d, c.rms_eps, s));
-    B200_CUDA(launch_gemm_bf16(L.qkv16, qd + 2 * kvd, d, pf_xb, n, pf_qkv, qd + 2 * kvd, s));
-    B200_CUDA(launch_rope_kv(pf_qkv, pf_q, L.k_cache, L.v_cache, table, rope, n, qd, kvd, c.n_kv_heads, 0, pos_arr, slot_arr, pages_per_seq, s));
+    int qkv_splits = max_wide_splits(n);
+    const int64_t qkv_stride = (int64_t)n * (qd + 2 * kvd);
+    B200_CUDA(launch_gemm_bf16_splitk(L.qkv16, qd + 2 * kvd, d, pf_xb, n, pf_qkv, qd + 2 * kvd, qkv_stride, &qkv_splits, s, &gemm_ws));
+    B200_CUDA(launch_rope_kv(pf_qkv, pf_q, L.k_cache, L.v_cache, table, rope, n, qd, kvd, c.n_kv_heads, 0, pos_arr, slot_arr, pages_per_seq,
+                             qkv_splits, qkv_stride, s));
     if (!pos_arr && use_fa_prefill) {  // one sequence, causal: tensor-core attention, bf16 straight into the GEMM operand
       B200_CUDA(launch_attn_prefill(pf_q, L.k_cache, L.v_cache, table, pf_xb, n, 0, c.n_heads, c.n_kv_heads, s));
     } else {                            // one row per sequence (batched decode): the split-KV decode kernel, a query per z
@@ -806,13 +809,15 @@ int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_ar
     // partials sit n*d floats apart in pf_proj and the next consumer adds them in a fixed order
     pf_proj_splits = max_proj_splits(n);
     pf_proj_stride = (int64_t)n * d;
-    B200_CUDA(launch_gemm_bf16_splitk(L.o16, d, qd, pf_xb, n, pf_proj, d, pf_proj_stride, &pf_proj_splits, s));
+    B200_CUDA(launch_gemm_bf16_splitk(L.o16, d, qd, pf_xb, n, pf_proj, d, pf_proj_stride, &pf_proj_splits, s, &gemm_ws));
     if (tp_size > 1) { int rc = tp_allreduce_sum(pf_proj, (size_t)n * d, s); if (rc) return rc; }
     B200_CUDA(launch_add_rmsnorm_bf16(pf_x, pf_proj, pf_proj_splits, pf_proj_stride, L.ffn_norm, pf_xb, n, d, c.rms_eps, s));
-    B200_CUDA(launch_gemm_bf16(L.gu16, 2 * ff, d, pf_xb, n, pf_gu, 2 * ff, s, &gemm_ws));
-    B200_CUDA(launch_swiglu_bf16(pf_gu, pf_xb, (int64_t)n * ff, s));
+    int gu_splits = max_wide_splits(n);
+    const int64_t gu_stride = (int64_t)n * 2 * ff;
+    B200_CUDA(launch_gemm_bf16_splitk(L.gu16, 2 * ff, d, pf_xb, n, pf_gu, 2 * ff, gu_stride, &gu_splits, s, &gemm_ws));
+    B200_CUDA(launch_swiglu_bf16(pf_gu, pf_xb, (int64_t)n * ff, gu_splits, gu_stride, s));
     pf_proj_splits = max_proj_splits(n);
-    B200_CUDA(launch_gemm_bf16_splitk(L.down16, d, ff, pf_xb, n, pf_proj, d, pf_proj_stride, &pf_proj_splits, s));
+    B200_CUDA(launch_gemm_bf16_splitk(L.down16, d, ff, pf_xb, n, pf_proj, d, pf_proj_stride, &pf_proj_splits, s, &gemm_ws));
     if (tp_size > 1) { int rc = tp_allreduce_sum(pf_proj, (size_t)n * d, s); if (rc) return rc; }
   }
   return 0;

@@ -118,11 +118,14 @@ struct Engine {
   int pf_proj_splits = 1;      // split-K partials currently sitting in pf_proj (consumers add them) ...
   int64_t pf_proj_stride = 0;  // ... this many floats apart
   int64_t pf_proj_floats = 0;  // capacity of pf_proj
+  // K splits the qkv / gate-up GEMMs may use for n rows: their outputs are [pf_rows][width] buffers, every partial
+  // is [n][width] (these two are column-parallel under TP: partials stay local, so TP does not restrict them)
+  int max_wide_splits(int n) const { const int f = pf_rows / (n < 1 ? 1 : n); return f < 1 ? 1 : (f > 16 ? 16 : f); }
   GemmWorkspace gemm_ws = {};  // stream-K scratch of the tensor-core GEMMs (gate/up, batched lm_head)
   // most K splits a projection over n rows may use: every partial is [n][d_model] and all must fit pf_proj
   int max_proj_splits(int n) const {
     const int64_t fit = pf_proj_floats / ((int64_t)n * lc.d_model);
-    return tp_size > 1 ? 1 : (int)(fit < 1 ? 1 : (fit > 8 ? 8 : fit));
+    return tp_size > 1 ? 1 : (int)(fit < 1 ? 1 : (fit > 16 ? 16 : fit));
   }
 
   // sequence slots (continuous batching): slot s statically owns block-table row s

@@ -68,7 +68,7 @@ __host__ __device__ constexpr uint32_t instr_desc(int M, int N) {
 
 template <int BN, int MT>
 struct GemmCfg {
-  static constexpr int STAGES = (MT == 2 || BN == 128) ? 3 : 2;
+  static constexpr int STAGES = (MT == 2 && BN == 128) ? 4 : ((MT == 2 || BN == 128) ? 3 : 2);
   static constexpr int THREADS = 64 + 128 * MT;
   static constexpr uint32_t AT_BYTES = MT * A_BYTES;
   static constexpr uint32_t B_BYTES = BN * BK * 2;
@@ -208,12 +208,14 @@ struct StreamKArgs {
   unsigned int* flags;  // [grid]; 1 = that CTA's partial is in ws (the owner clears it)
 };
 
+constexpr size_t kWsSlot = (size_t)256 * 2 * BM;  // floats per workspace slot: [256 tokens][256 rows]
+
 DEVINL void bar_sync_epi(int n) { asm volatile("bar.sync 1, %0;" ::"r"(n) : "memory"); }
 
+template <int BN>
 __global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmA,
                                                             const __grid_constant__ CUtensorMap tmB, const StreamKArgs g) {
-  using C = GemmCfg<256, 2>;
-  constexpr int BN = 256;
+  using C = GemmCfg<BN, 2>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t tiles = (raw + 1023u) & ~1023u;
@@ -318,6 +320,7 @@ __global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant
       tc_fence_after();
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
+        if (n0 + c * 32 >= g.n_tokens) break;  // token columns past the batch hold zeros: nothing to store or reduce
         uint32_t v[32];
         const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + (uint32_t)(mt * BN + c * 32);
         asm volatile(
@@ -330,12 +333,12 @@ __global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant
             : "r"(taddr));
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         if (partial) {
-          float* w = g.ws + (size_t)p * (BN * 2 * BM) + (size_t)(c * 32) * (2 * BM) + rloc;
+          float* w = g.ws + (size_t)p * kWsSlot + (size_t)(c * 32) * (2 * BM) + rloc;
 #pragma unroll
           for (int j = 0; j < 32; ++j) w[(size_t)j * (2 * BM)] = __uint_as_float(v[j]);
         } else {
           for (int q = 1; q <= n_parts; ++q) {  // partials in CTA order; 32 independent loads in flight, then the adds
-            const float* w = g.ws + (size_t)(p + q) * (BN * 2 * BM) + (size_t)(c * 32) * (2 * BM) + rloc;
+            const float* w = g.ws + (size_t)(p + q) * kWsSlot + (size_t)(c * 32) * (2 * BM) + rloc;
             float t[32];
 #pragma unroll
             for (int j = 0; j < 32; ++j) t[j] = __ldcg(w + (size_t)j * (2 * BM));
@@ -413,24 +416,43 @@ cudaError_t launch_bn(const uint16_t* W, int64_t rows, int64_t K, const uint16_t
   return cudaGetLastError();
 }
 
+template <int BN>
 cudaError_t launch_streamk(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y, int64_t ldy,
                            const GemmWorkspace& wk, cudaStream_t s) {
-  using C = GemmCfg<256, 2>;
+  using C = GemmCfg<BN, 2>;
   CUtensorMap ma, mb;
-  if (!make_map(&ma, W, (uint64_t)rows, (uint64_t)K, BM) || !make_map(&mb, X, (uint64_t)n_tokens, (uint64_t)K, 256))
+  if (!make_map(&ma, W, (uint64_t)rows, (uint64_t)K, BM) || !make_map(&mb, X, (uint64_t)n_tokens, (uint64_t)K, BN))
     return cudaErrorInvalidValue;
-  cudaError_t e = cudaFuncSetAttribute(gemm_streamk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM);
+  cudaError_t e = cudaFuncSetAttribute(gemm_streamk_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM);
   if (e != cudaSuccess) return e;
   StreamKArgs g;
   g.y = Y; g.ldy = (int)ldy; g.n_tokens = (int)n_tokens;
   g.tiles_m = (int)(rows / (2 * BM));
   g.kb_total = (int)(K / BK);
-  g.total = g.tiles_m * (int)((n_tokens + 255) / 256) * g.kb_total;
+  g.total = g.tiles_m * (int)((n_tokens + BN - 1) / BN) * g.kb_total;
   g.units = (g.total + wk.sm_count - 1) / wk.sm_count;
   g.ws = wk.ws; g.flags = wk.flags;
   const int grid = (g.total + g.units - 1) / g.units;
-  gemm_streamk_kernel<<<grid, C::THREADS, C::SMEM, s>>>(ma, mb, g);
+  gemm_streamk_kernel<BN><<<grid, C::THREADS, C::SMEM, s>>>(ma, mb, g);
   return cudaGetLastError();
+}
+
+// One token tile (n_tokens <= 128): the GEMM streams the weights once and is HBM-bound; what matters is that
+// every SM streams the same number of bytes with no per-tile set-up in between.  Whole tiles cannot do that
+// (gate/up: 224 row tiles of 128 on 148 SMs -> 75 us where the batch-1 GEMV needs 42), the stream-K schedule
+// can: 148 persistent CTAs, each an equal run of (256-row tile, K block) items, partial tiles (tokens x 256
+// floats, tiny here) reduced by the tile's owner in CTA order.
+bool streamk_small_n(int64_t rows, int64_t K, int64_t n_tokens, const GemmWorkspace* wk) {
+  if (!wk || !wk->ws || !wk->flags || wk->sm_count <= 0 || getenv("B200_NO_STREAMK")) return false;
+  if (n_tokens > 128 || rows % (2 * BM) || (size_t)wk->sm_count * kWsSlot * 4 > wk->ws_bytes) return false;
+  const int64_t total = (rows / (2 * BM)) * (K / BK);
+  const char* force = getenv("B200_GEMM_STREAMK");  // tests: =1 takes the schedule for every shape it can express
+  if (force && atoi(force) == 1) return true;
+  // Measured (8B, 8 tokens): gate/up 37 us vs 75 us in whole tiles, lm_head 171 vs 232; but matrices with few row
+  // tiles (o, down, qkv: 16-24) are cut into ~10 CTAs per tile and the owner's serial fix-up outweighs the balance
+  // (down 49 vs 23 us), and from 64 tokens up the partial traffic does.  So: at most 32 tokens, and at least half a
+  // row tile per CTA.
+  return n_tokens <= 32 && 2 * (rows / (2 * BM)) >= wk->sm_count && total >= 4 * (int64_t)wk->sm_count;
 }
 
 // B200_GEMM_M256 = 0 never / 1 whenever the shape allows / unset: the heuristic below (experiments only)
@@ -464,19 +486,23 @@ cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const u
     const char* force = getenv("B200_GEMM_STREAMK");
     const bool want = force && atoi(force) == 1 && units >= 1;
     if (want && (size_t)P * 256 * 256 * 4 <= wk->ws_bytes)
-      return launch_streamk(W, rows, K, X, n_tokens, Y, ldy, *wk, s);
+      return launch_streamk<256>(W, rows, K, X, n_tokens, Y, ldy, *wk, s);
   }
   int splits = 1;
-  return launch_gemm_bf16_splitk(W, rows, K, X, n_tokens, Y, ldy, 0, &splits, s);
+  return launch_gemm_bf16_splitk(W, rows, K, X, n_tokens, Y, ldy, 0, &splits, s, wk);
 }
 
 // Same, but a GEMM with too few output tiles to fill the GPU may split K: partial p is written to
 // Y + p*split_stride and the caller adds the partials (deterministically, ascending p) where it consumes Y.
-// *splits: in = maximum allowed (1..8), out = what was used.
+// *splits: in = maximum allowed (1..16), out = what was used.
 cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
-                                    int64_t ldy, int64_t split_stride, int* splits, cudaStream_t s) {
+                                    int64_t ldy, int64_t split_stride, int* splits, cudaStream_t s, const GemmWorkspace* wk) {
   if (!gemm_shape_ok(rows, K, n_tokens)) return cudaErrorInvalidValue;
-  const int max_splits = *splits < 1 ? 1 : (*splits > 8 ? 8 : *splits);
+  if (streamk_small_n(rows, K, n_tokens, wk)) {
+    *splits = 1;
+    return launch_streamk<128>(W, rows, K, X, n_tokens, Y, ldy, *wk, s);
+  }
+  const int max_splits = *splits < 1 ? 1 : (*splits > 16 ? 16 : *splits);
   const int64_t kb = K / BK;
   const int ov = m256_override();
   // 256 x 256 tiles, one CTA per SM: the fewest operand bytes per MAC.  Taken when, with K split up to
@@ -495,7 +521,20 @@ cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, 
   const int64_t tiles256 = ((rows + BM - 1) / BM) * ((n_tokens + 255) / 256);
   const int64_t tiles128 = ((rows + BM - 1) / BM) * ((n_tokens + 127) / 128);
   int use = 1;
-  if (max_splits >= 2 && tiles128 < 296 && tiles128 >= 32 && kb % 2 == 0 && K >= 2048) use = 2;
+  if (n_tokens <= 128 && max_splits >= 2) {
+    // One token tile: the GEMM streams the weights once and is HBM-bound, so what matters is that every SM gets
+    // the same share of the rows (224 row tiles on 148 SMs leave half the GPU waiting for the SMs that got two:
+    // measured 75 us where the batch-1 GEMV takes 42).  Partials are tiny here (tokens x rows), so K is split until
+    // the CTAs deal out evenly: the s (dividing the K blocks, >= 8 blocks per CTA) with the best
+    // CTAs / (rounds x SMs), the smallest such s on ties.
+    double best = 0.0;
+    for (int sp = 1; sp <= max_splits && sp <= 16; ++sp) {
+      if (kb % sp || kb / sp < 8) continue;
+      const int64_t ctas = tiles128 * sp, rounds = (ctas + 147) / 148;
+      const double eff = (double)ctas / (double)(rounds * 148);
+      if (eff > best + 0.02) { best = eff; use = sp; }
+    }
+  } else if (max_splits >= 2 && tiles128 < 296 && tiles128 >= 32 && kb % 2 == 0 && K >= 2048) use = 2;
   *splits = use;
   if (n_tokens > 128 && tiles256 >= 296) return launch_bn<256, 1>(W, rows, K, X, n_tokens, Y, ldy, 1, 0, s);
   return launch_bn<128, 1>(W, rows, K, X, n_tokens, Y, ldy, use, split_stride, s);

@@ -173,7 +173,7 @@ struct GemmWorkspace {
 cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
                              int64_t ldy, cudaStream_t s, const GemmWorkspace* wk = nullptr);
 cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
-                                    int64_t ldy, int64_t split_stride, int* splits, cudaStream_t s);
+                                    int64_t ldy, int64_t split_stride, int* splits, cudaStream_t s, const GemmWorkspace* wk = nullptr);
 bool gemm_shape_ok(int64_t rows, int64_t K, int64_t n_tokens);
 
 // causal attention over a whole prompt on the tensor cores (attn_prefill.cu); out is bf16 [T][n_heads*128]
@@ -220,14 +220,14 @@ cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, int n_parts, int
                                     int d, float eps, cudaStream_t s);
 cudaError_t launch_rope_kv(const float* qkv, float* q, uint16_t* k_cache, uint16_t* v_cache, const int32_t* block_table, const float* rope,
                            int tokens, int q_rows, int kv_rows, int n_kv_heads, int pos0, const int32_t* pos_arr, const int32_t* slot_arr,
-                           int pages_per_seq, cudaStream_t s);
+                           int pages_per_seq, int n_parts, int64_t part_stride, cudaStream_t s);  // qkv: n_parts split-K partials
 cudaError_t launch_argmax_rows(const float* logits, int rows, int vocab, int32_t* next, cudaStream_t s);
 // vocab-parallel: per-row key of the local maximum (global id = id_base + index), max-all-reduced, then decoded
 cudaError_t launch_argmax_rows_keys(const float* logits, int rows, int vocab, int id_base, unsigned long long* keys, cudaStream_t s);
 cudaError_t launch_keys_to_ids(const unsigned long long* keys, int32_t* next, int rows, cudaStream_t s);
 cudaError_t launch_append_history(const int32_t* next, const int32_t* slot_arr, const int32_t* pos_arr, int32_t* history, int max_ctx, int rows,
                                   cudaStream_t s);
-cudaError_t launch_swiglu_bf16(const float* gu, uint16_t* h, int64_t n_pairs, cudaStream_t s);
+cudaError_t launch_swiglu_bf16(const float* gu, uint16_t* h, int64_t n_pairs, int n_parts, int64_t part_stride, cudaStream_t s);
 cudaError_t launch_take_row(const float* x, const float* add, int n_parts, int64_t part_stride, int d, int row, float* out, cudaStream_t s);
 
 }  // namespace b200

@@ -3,6 +3,8 @@
 // append, SwiGLU -> bf16, and the hand-over of the last position's residual to the decode path.
 // All are HBM/L2-bound streaming kernels over [tokens x width] fp32; the bf16 rounding of GEMM inputs
 // happens exactly once, here, with the same RNE recipe as the oracle.
+#include <algorithm>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -60,15 +62,19 @@ __global__ void add_rmsnorm_bf16_kernel(float* x, const float* add, int n_parts,
 // sequence in slot slot_arr[t], whose block table is row slot_arr[t] of `block_table` (pages_per_seq wide).
 __global__ void rope_kv_kernel(const float* qkv, float* q, uint16_t* k_cache, uint16_t* v_cache, const int32_t* block_table,
                                const float* rope, int q_rows, int kv_rows, int n_kv_heads, int pos0, const int32_t* pos_arr,
-                               const int32_t* slot_arr, int pages_per_seq) {
+                               const int32_t* slot_arr, int pages_per_seq, int n_parts, long long part_stride) {
   const int t = blockIdx.x, pos = pos_arr ? pos_arr[t] : pos0 + t;
   const int width = q_rows + 2 * kv_rows;
   const float* in = qkv + (size_t)t * width;
   const int32_t* bt = slot_arr ? block_table + (size_t)slot_arr[t] * pages_per_seq : block_table;
   const int page = bt[pos / kPageTokens];
-  for (int p = threadIdx.x; p < width / 2; p += blockDim.x) {
+  for (int p = blockIdx.y * blockDim.x + threadIdx.x; p < width / 2; p += gridDim.y * blockDim.x) {
     const int row = 2 * p;
     float x0 = in[row], x1 = in[row + 1];
+    for (int sp = 1; sp < n_parts; ++sp) {  // split-K partials of the qkv GEMM, ascending order
+      x0 += in[(size_t)sp * part_stride + row];
+      x1 += in[(size_t)sp * part_stride + row + 1];
+    }
     if (row < q_rows + kv_rows) {
       const int i = (row & (kHeadDim - 1)) >> 1;
       const float2 cs = *reinterpret_cast<const float2*>(rope + ((size_t)pos * (kHeadDim / 2) + i) * 2);
@@ -90,10 +96,15 @@ __global__ void rope_kv_kernel(const float* qkv, float* q, uint16_t* k_cache, ui
 }
 
 // gu[t][2 ff] (rows interleaved gate_i, up_i) -> h[t][ff] = bf16( silu(g) * u )
-__global__ void swiglu_bf16_kernel(const float* gu, uint16_t* h, int64_t n_pairs) {
+// (gu: n_parts split-K partials, part_stride floats apart, summed in ascending order)
+__global__ void swiglu_bf16_kernel(const float* gu, uint16_t* h, int64_t n_pairs, int n_parts, long long part_stride) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_pairs; i += stride) {
-    const float2 v = *reinterpret_cast<const float2*>(gu + 2 * i);
+    float2 v = *reinterpret_cast<const float2*>(gu + 2 * i);
+    for (int sp = 1; sp < n_parts; ++sp) {
+      const float2 w = *reinterpret_cast<const float2*>(gu + (size_t)sp * part_stride + 2 * i);
+      v.x += w.x; v.y += w.y;
+    }
     h[i] = f32_to_bf16_bits((v.x / (1.0f + expf(-v.x))) * v.y);
   }
 }
@@ -171,13 +182,17 @@ cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, int n_parts, int
 }
 cudaError_t launch_rope_kv(const float* qkv, float* q, uint16_t* k_cache, uint16_t* v_cache, const int32_t* block_table, const float* rope,
                            int tokens, int q_rows, int kv_rows, int n_kv_heads, int pos0, const int32_t* pos_arr, const int32_t* slot_arr,
-                           int pages_per_seq, cudaStream_t s) {
-  rope_kv_kernel<<<tokens, 256, 0, s>>>(qkv, q, k_cache, v_cache, block_table, rope, q_rows, kv_rows, n_kv_heads, pos0, pos_arr, slot_arr,
-                                        pages_per_seq);
+                           int pages_per_seq, int n_parts, int64_t part_stride, cudaStream_t s) {
+  // few tokens (batched decode): spread a token's row pairs over several CTAs, above all when partials are summed
+  const int ny = tokens >= 128 ? 1 : (tokens >= 32 ? 2 : 8);
+  rope_kv_kernel<<<dim3(tokens, ny), 256, 0, s>>>(qkv, q, k_cache, v_cache, block_table, rope, q_rows, kv_rows, n_kv_heads, pos0, pos_arr, slot_arr,
+                                        pages_per_seq, n_parts, (long long)part_stride);
   return cudaGetLastError();
 }
-cudaError_t launch_swiglu_bf16(const float* gu, uint16_t* h, int64_t n_pairs, cudaStream_t s) {
-  swiglu_bf16_kernel<<<1184, 256, 0, s>>>(gu, h, n_pairs);
+cudaError_t launch_swiglu_bf16(const float* gu, uint16_t* h, int64_t n_pairs, int n_parts, int64_t part_stride, cudaStream_t s) {
+  if (part_stride % 2) return cudaErrorInvalidValue;
+  const int grid = (int)std::min<int64_t>(1184, (n_pairs + 255) / 256);
+  swiglu_bf16_kernel<<<grid, 256, 0, s>>>(gu, h, n_pairs, n_parts, (long long)part_stride);
   return cudaGetLastError();
 }
 cudaError_t launch_take_row(const float* x, const float* add, int n_parts, int64_t part_stride, int d, int row, float* out, cudaStream_t s) {
