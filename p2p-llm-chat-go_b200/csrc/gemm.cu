@@ -68,7 +68,8 @@ __host__ __device__ constexpr uint32_t instr_desc(int M, int N) {
 
 template <int BN, int MT>
 struct GemmCfg {
-  static constexpr int STAGES = (MT == 2 && BN == 128) ? 4 : ((MT == 2 || BN == 128) ? 3 : 2);
+  // BN = 32 (<= 32 tokens, weight streaming): 20 KB stages, five of them: more weight bytes in flight per CTA
+  static constexpr int STAGES = BN == 32 ? 5 : ((MT == 2 && BN == 128) ? 4 : ((MT == 2 || BN == 128) ? 3 : 2));
   static constexpr int THREADS = 64 + 128 * MT;
   static constexpr uint32_t AT_BYTES = MT * A_BYTES;
   static constexpr uint32_t B_BYTES = BN * BK * 2;
@@ -500,6 +501,7 @@ cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, 
   if (!gemm_shape_ok(rows, K, n_tokens)) return cudaErrorInvalidValue;
   if (streamk_small_n(rows, K, n_tokens, wk)) {
     *splits = 1;
+    if (n_tokens <= 32) return launch_streamk<32>(W, rows, K, X, n_tokens, Y, ldy, *wk, s);
     return launch_streamk<128>(W, rows, K, X, n_tokens, Y, ldy, *wk, s);
   }
   const int max_splits = *splits < 1 ? 1 : (*splits > 16 ? 16 : *splits);
@@ -537,6 +539,7 @@ cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, 
   } else if (max_splits >= 2 && tiles128 < 296 && tiles128 >= 32 && kb % 2 == 0 && K >= 2048) use = 2;
   *splits = use;
   if (n_tokens > 128 && tiles256 >= 296) return launch_bn<256, 1>(W, rows, K, X, n_tokens, Y, ldy, 1, 0, s);
+  if (n_tokens <= 32 && getenv("B200_NO_GEMM_BN32") == nullptr) return launch_bn<32, 1>(W, rows, K, X, n_tokens, Y, ldy, use, split_stride, s);
   return launch_bn<128, 1>(W, rows, K, X, n_tokens, Y, ldy, use, split_stride, s);
 }
 

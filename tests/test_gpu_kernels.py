@@ -136,7 +136,7 @@ def test_attn_decode(pkg, n_ctx, n_heads, n_kv):
 @pytest.mark.parametrize("wtype,rows,cols,n", [
     (orc.BF16, 128, 64, 1), (orc.BF16, 256, 512, 7), (orc.BF16, 1024, 4096, 128), (orc.BF16, 512, 2048, 129),
     (orc.BF16, 6144, 4096, 512), (orc.BF16, 4096, 14336, 300), (orc.Q4_K, 256, 2048, 33), (orc.Q6_K, 256, 2048, 64),
-    (orc.BF16, 200, 256, 40), (orc.BF16, 1032, 512, 300)])  # ragged last row tile (vocab-parallel lm_head shards: 16032 rows)
+    (orc.BF16, 200, 256, 40), (orc.BF16, 1032, 512, 300), (orc.BF16, 6144, 4096, 24)])  # ragged last row tile (vocab-parallel lm_head shards: 16032 rows)
 def test_gemm_tcgen05(pkg, wtype, rows, cols, n):
     rng = np.random.default_rng(rows + cols + n)
     W = random_tensor(rng, wtype, rows, cols)
