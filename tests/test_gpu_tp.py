@@ -70,17 +70,23 @@ def test_tp2_matches_tp1_and_oracle(pkg):
 
 
 def test_tp2_batched_step_ranks_agree(pkg):
-    """b200_bench_batched under tensor parallelism (vocab-parallel lm_head GEMM on a ragged row count, per-row
-    argmax keys max-reduced over the ranks): both ranks must pick the same ids, and the ids of TP-1."""
-    def mk():
-        c = tiny_cfg(pkg, pkg.WEIGHTS_BF16, n_layers=2, seed=82, max_ctx=128)
-        c.max_seqs = 8
-        return c
-    with pkg.Engine(mk()) as e1:
-        _, ids1 = e1.bench_batched(8, 30, 4)
-    res = run_ranks(pkg, mk, 2, lambda eng: eng.bench_batched(8, 30, 4)[1])
-    assert res[0].tolist() == res[1].tolist()
-    assert (res[0] == ids1).mean() >= 0.75, (res[0], ids1)   # fp32 sums regrouped across ranks may flip a near-tie
+    """b200_bench_batched under tensor parallelism (vocab-parallel lm_head GEMM, per-row argmax keys max-reduced over
+    the ranks): both ranks must pick the same ids, and the ids of TP-1.  The hook feeds its own tokens back for seven
+    steps and a random-init model has near-ties, where regrouped fp32 sums may pick the other token and the chain
+    then diverges: so several models, and most of them must agree to the last token."""
+    agree = 0
+    for seed in range(82, 87):
+        def mk():
+            c = tiny_cfg(pkg, pkg.WEIGHTS_BF16, n_layers=2, seed=seed, max_ctx=128)
+            c.max_seqs = 8
+            return c
+        with pkg.Engine(mk()) as e1:
+            _, ids1 = e1.bench_batched(8, 30, 4)
+        res = run_ranks(pkg, mk, 2, lambda eng: eng.bench_batched(8, 30, 4)[1])
+        assert res[0].tolist() == res[1].tolist()
+        assert ((0 <= res[0]) & (res[0] < 1024)).all()
+        agree += int(res[0].tolist() == ids1.tolist())
+    assert agree >= 3, agree
 
 
 def test_tp_rejects_unsupported(pkg):
