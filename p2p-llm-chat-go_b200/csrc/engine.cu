@@ -784,7 +784,7 @@ int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_ar
   B200_CUDA(launch_embed_tokens(token_embd, embd_type, d, tokens_dev, n, pf_x, s));
   for (int l = 0; l < c.n_layers; ++l) {
     Layer& L = layers[l];
-    B200_CUDA(launch_add_rmsnorm_bf16(pf_x, l ? pf_proj : nullptr, pf_proj_splits, pf_proj_stride, L.attn_norm, pf_xb, n, d, c.rms_eps, s));
+    { int rc = add_rmsnorm_proj(L.attn_norm, n, l > 0); if (rc) return rc; }
     int qkv_splits = max_wide_splits(n);
     const int64_t qkv_stride = (int64_t)n * (qd + 2 * kvd);
     B200_CUDA(launch_gemm_bf16_splitk(L.qkv16, qd + 2 * kvd, d, pf_xb, n, pf_qkv, qd + 2 * kvd, qkv_stride, &qkv_splits, s, &gemm_ws));
@@ -810,16 +810,41 @@ int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_ar
     pf_proj_splits = max_proj_splits(n);
     pf_proj_stride = (int64_t)n * d;
     B200_CUDA(launch_gemm_bf16_splitk(L.o16, d, qd, pf_xb, n, pf_proj, d, pf_proj_stride, &pf_proj_splits, s, &gemm_ws));
-    if (tp_size > 1) { int rc = tp_allreduce_sum(pf_proj, (size_t)n * d, s); if (rc) return rc; }
-    B200_CUDA(launch_add_rmsnorm_bf16(pf_x, pf_proj, pf_proj_splits, pf_proj_stride, L.ffn_norm, pf_xb, n, d, c.rms_eps, s));
+    { int rc = reduce_proj(n, pos_arr != nullptr); if (rc) return rc; }
+    { int rc = add_rmsnorm_proj(L.ffn_norm, n, true); if (rc) return rc; }
     int gu_splits = max_wide_splits(n);
     const int64_t gu_stride = (int64_t)n * 2 * ff;
     B200_CUDA(launch_gemm_bf16_splitk(L.gu16, 2 * ff, d, pf_xb, n, pf_gu, 2 * ff, gu_stride, &gu_splits, s, &gemm_ws));
     B200_CUDA(launch_swiglu_bf16(pf_gu, pf_xb, (int64_t)n * ff, gu_splits, gu_stride, s));
     pf_proj_splits = max_proj_splits(n);
     B200_CUDA(launch_gemm_bf16_splitk(L.down16, d, ff, pf_xb, n, pf_proj, d, pf_proj_stride, &pf_proj_splits, s, &gemm_ws));
-    if (tp_size > 1) { int rc = tp_allreduce_sum(pf_proj, (size_t)n * d, s); if (rc) return rc; }
+    { int rc = reduce_proj(n, pos_arr != nullptr); if (rc) return rc; }
   }
+  return 0;
+}
+
+// A row-parallel projection (o, down) has just written its [n][d_model] output (or split-K partials) to pf_proj.
+// One GPU: nothing to do, the consumer adds the partials.  Tensor parallel: batched decode of <= kTpBatchRows rows
+// pushes the partial into every peer's receive buffer (the consumer waits for the flags and adds the tp slots in
+// rank order); anything else is an NCCL all-reduce in place.
+int Engine::reduce_proj(int n, bool decode) {
+  const int d = lc.d_model;
+  pf_proj_src = pf_proj; pf_wait_flags = nullptr;
+  if (tp_size <= 1) return 0;
+  if (decode && tp_fused && tp_batch_push && n <= kTpBatchRows) {
+    const int buf = (int)(tp_bseq & 1u);
+    ++tp_bseq;
+    B200_CUDA(launch_tp_push(tp_batch, pf_proj, (int64_t)n * d, buf, tp_bseq, stream));
+    pf_proj_src = tp_batch.recv[buf]; pf_proj_splits = tp_size; pf_proj_stride = tp_batch.slot_floats;
+    pf_wait_flags = tp_batch.flags + buf * kMaxTp; pf_wait_seq = tp_bseq;
+    return 0;
+  }
+  return tp_allreduce_sum(pf_proj, (size_t)n * d, stream);
+}
+
+int Engine::add_rmsnorm_proj(const float* w, int n, bool have_proj) {
+  B200_CUDA(launch_add_rmsnorm_bf16(pf_x, have_proj ? pf_proj_src : nullptr, pf_proj_splits, pf_proj_stride, w, pf_xb, n, lc.d_model, lc.rms_eps,
+                                    stream, have_proj ? pf_wait_flags : nullptr, tp_size, pf_wait_seq, tp_batch.error));
   return 0;
 }
 
@@ -830,7 +855,7 @@ int Engine::prefill_gemm(int n) {
   int rc0 = forward_gemm(n, prompt_dev, nullptr, nullptr, nullptr);
   if (rc0) return rc0;
   // hand the last position over to the batch-1 path: residual stream, then lm_head (mode 0) + token pick
-  B200_CUDA(launch_take_row(pf_x, pf_proj, pf_proj_splits, pf_proj_stride, d, n - 1, x, s));
+  B200_CUDA(launch_take_row(pf_x, pf_proj_src, pf_proj_splits, pf_proj_stride, d, n - 1, x, s));  // prefill: never the push path
   int n_tail = 0;
   int rc = enqueue_tail(s, false, &n_tail);
   if (rc) return rc;

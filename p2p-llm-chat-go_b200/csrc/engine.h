@@ -71,6 +71,9 @@ struct Engine {
   TpLink tp_link_host{};
   float* x_alt = nullptr;         // second residual buffer (consumers read one, publish into the other)
   std::vector<void*> tp_ipc_opened;
+  TpBatch tp_batch{};             // batched-decode all-reduce over peer memory (see kernels.h)
+  unsigned int tp_bseq = 0;       // all-reduces pushed so far (every rank counts the same calls)
+  bool tp_batch_push = true;      // B200_TP_NCCL: NCCL instead
   int tp_setup_link();
   int tp_check_error();
   int tp_init(const void* unique_id);
@@ -117,6 +120,12 @@ struct Engine {
   int pf_rows = 0;             // rows the work buffers were sized for
   int pf_proj_splits = 1;      // split-K partials currently sitting in pf_proj (consumers add them) ...
   int64_t pf_proj_stride = 0;  // ... this many floats apart
+  const float* pf_proj_src = nullptr;        // where they are (pf_proj, or a peer-memory receive buffer under TP)
+  const unsigned int* pf_wait_flags = nullptr;  // peer-memory path: flags the consumer waits on, and for which value
+  unsigned int pf_wait_seq = 0;
+  // residual += partials; xb = bf16(rmsnorm(residual) * w): the consumer of whatever the last projection left behind
+  int add_rmsnorm_proj(const float* w, int n, bool have_proj);
+  int reduce_proj(int n, bool decode);  // after a row-parallel projection wrote pf_proj: TP all-reduce (push or NCCL); no-op on one GPU
   int64_t pf_proj_floats = 0;  // capacity of pf_proj
   // K splits the qkv / gate-up GEMMs may use for n rows: their outputs are [pf_rows][width] buffers, every partial
   // is [n][width] (these two are column-parallel under TP: partials stay local, so TP does not restrict them)

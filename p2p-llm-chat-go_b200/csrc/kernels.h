@@ -31,6 +31,23 @@ struct TpLink {
   int rank, size, d, per_step;      // per_step = all-reduces per decode step (2 * n_layers)
 };
 
+// Batched decode (<= kTpBatchRows sequences) under tensor parallelism: the all-reduce of the [rows][d] partial
+// products is a push over NVLink peer memory too.  tp_push_kernel copies this rank's partial into slot `rank` of
+// every peer's receive buffer and raises a sequence flag there; the consumer (add_rmsnorm) waits for the `size`
+// flags and adds the slots in rank order, which is the deterministic reduction it already does for split-K.
+constexpr int kTpBatchRows = 32;
+struct TpBatch {
+  float* peer_recv[2][kMaxTp];       // [buffer][peer] -> that peer's [size][kTpBatchRows * d] floats
+  unsigned int* peer_flags[kMaxTp];  // -> that peer's flags [2][kMaxTp]
+  float* recv[2];                    // own buffers
+  unsigned int* flags;               // own flags
+  unsigned int* ticket;              // CTA ticket of the push kernel (self-resetting)
+  int* error;
+  int rank, size;
+  long long slot_floats;             // kTpBatchRows * d
+};
+cudaError_t launch_tp_push(const TpBatch& b, const float* src, int64_t count, int buf, unsigned int seq, cudaStream_t s);
+
 // Device-resident state of the sequence being decoded; every kernel of a step reads it, the last kernel
 // of the step (finish_step) advances it, so one captured CUDA graph serves every position.
 struct StepState {
@@ -216,8 +233,10 @@ cudaError_t launch_attn_decode_batched(const AttnArgs& a, uint16_t* out_bf16, cu
 // element-wise kernels of the prefill / batched pass (prefill.cu)
 cudaError_t launch_embed_tokens(const uint8_t* embd, int embd_type, int d_model, const int32_t* tokens_dev, int n, float* x, cudaStream_t s);
 // `add`: n_parts split-K partials of [tokens][d], part_stride floats apart, summed in ascending order
+// wait_flags != null: every CTA first waits until wait_flags[0..n_wait) have reached wait_seq (tp_push_kernel)
 cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, int n_parts, int64_t part_stride, const float* w, uint16_t* xb, int tokens,
-                                    int d, float eps, cudaStream_t s);
+                                    int d, float eps, cudaStream_t s, const unsigned int* wait_flags = nullptr, int n_wait = 0,
+                                    unsigned int wait_seq = 0, int* wait_error = nullptr);
 cudaError_t launch_rope_kv(const float* qkv, float* q, uint16_t* k_cache, uint16_t* v_cache, const int32_t* block_table, const float* rope,
                            int tokens, int q_rows, int kv_rows, int n_kv_heads, int pos0, const int32_t* pos_arr, const int32_t* slot_arr,
                            int pages_per_seq, int n_parts, int64_t part_stride, cudaStream_t s);  // qkv: n_parts split-K partials

@@ -26,17 +26,28 @@ DEVINL float block_sum256(float v, float* red) {
 // x[t][:] (+= sum of the split-K partials add[p][t][:], p ascending) ; xb[t][:] = bf16( (x * inv_rms) * w )
 // grid = tokens, block = 256
 __global__ void add_rmsnorm_bf16_kernel(float* x, const float* add, int n_parts, long long part_stride, const float* w, uint16_t* xb, int d,
-                                        float eps) {
+                                        float eps, const unsigned int* wait_flags, int n_wait, unsigned int wait_seq, int* wait_error) {
   __shared__ float red[8];
+  if (wait_flags) {  // partials pushed by the peer GPUs: wait for every rank's sequence flag (bounded)
+    if ((int)threadIdx.x < n_wait) {
+      const long long t0 = clock64();
+      unsigned int v;
+      do {
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(wait_flags + threadIdx.x) : "memory");
+        if (clock64() - t0 > 4000000000ll) { *wait_error = 1; break; }
+      } while ((int)(v - wait_seq) < 0);
+    }
+    __syncthreads();
+  }
   float* xr = x + (size_t)blockIdx.x * d;
   const float* ar = (add && n_parts > 0) ? add + (size_t)blockIdx.x * d : nullptr;
   float ss = 0.f;
   for (int k = threadIdx.x * 4; k < d; k += 1024) {
     float4 v = *reinterpret_cast<const float4*>(xr + k);
     if (ar) {
-      float4 a = *reinterpret_cast<const float4*>(ar + k);
+      float4 a = __ldcg(reinterpret_cast<const float4*>(ar + k));
       for (int p = 1; p < n_parts; ++p) {
-        const float4 b = *reinterpret_cast<const float4*>(ar + (size_t)p * part_stride + k);
+        const float4 b = __ldcg(reinterpret_cast<const float4*>(ar + (size_t)p * part_stride + k));
         a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
       }
       v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
@@ -154,7 +165,34 @@ __global__ void append_history_kernel(const int32_t* next, const int32_t* slot_a
   if (r < rows && pos_arr[r] + 1 < max_ctx) history[(size_t)slot_arr[r] * max_ctx + pos_arr[r] + 1] = next[r];
 }
 
+// this rank's partial [count floats] -> slot `rank` of every peer's receive buffer `buf`; the last CTA to finish
+// raises this rank's sequence flag on every peer
+__global__ void tp_push_kernel(const TpBatch b, const float* src, long long count, int buf, unsigned int seq) {
+  const long long n4 = count / 4;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    const float4 v = __ldcg(reinterpret_cast<const float4*>(src) + i);
+    for (int p = 0; p < b.size; ++p) reinterpret_cast<float4*>(b.peer_recv[buf][p] + (size_t)b.rank * b.slot_floats)[i] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    if (atomicAdd(b.ticket, 1u) == gridDim.x - 1) {
+      *b.ticket = 0u;
+      __threadfence_system();
+      for (int p = 0; p < b.size; ++p)
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(b.peer_flags[p] + buf * kMaxTp + b.rank), "r"(seq) : "memory");
+    }
+  }
+}
+
 }  // namespace
+
+cudaError_t launch_tp_push(const TpBatch& b, const float* src, int64_t count, int buf, unsigned int seq, cudaStream_t s) {
+  if (count < 4 || count % 4 || count > b.slot_floats || (buf & ~1)) return cudaErrorInvalidValue;
+  const int grid = (int)std::min<int64_t>(64, (count / 4 + 255) / 256);
+  tp_push_kernel<<<grid, 256, 0, s>>>(b, src, (long long)count, buf, seq);
+  return cudaGetLastError();
+}
 
 cudaError_t launch_argmax_rows(const float* logits, int rows, int vocab, int32_t* next, cudaStream_t s) {
   argmax_rows_kernel<<<rows, 1024, 0, s>>>(logits, vocab, next, 0, nullptr);
@@ -175,9 +213,11 @@ cudaError_t launch_append_history(const int32_t* next, const int32_t* slot_arr, 
 }
 
 cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, int n_parts, int64_t part_stride, const float* w, uint16_t* xb, int tokens,
-                                    int d, float eps, cudaStream_t s) {
-  if (d % 4 || part_stride % 4) return cudaErrorInvalidValue;
-  add_rmsnorm_bf16_kernel<<<tokens, 256, 0, s>>>(x, add, n_parts, (long long)part_stride, w, xb, d, eps);
+                                    int d, float eps, cudaStream_t s, const unsigned int* wait_flags, int n_wait, unsigned int wait_seq,
+                                    int* wait_error) {
+  if (d % 4 || part_stride % 4 || (wait_flags && (n_wait < 1 || n_wait > 256 || !wait_error))) return cudaErrorInvalidValue;
+  add_rmsnorm_bf16_kernel<<<tokens, 256, 0, s>>>(x, add, n_parts, (long long)part_stride, w, xb, d, eps, wait_flags, n_wait, wait_seq,
+                                                 wait_error);
   return cudaGetLastError();
 }
 cudaError_t launch_rope_kv(const float* qkv, float* q, uint16_t* k_cache, uint16_t* v_cache, const int32_t* block_table, const float* rope,

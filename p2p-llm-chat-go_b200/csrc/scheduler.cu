@@ -71,7 +71,7 @@ int Engine::batched_step(const std::vector<int>& sl, std::vector<int32_t>* next)
   B200_CUDA(cudaMemcpyAsync(b_slot, slot.data(), (size_t)B * 4, cudaMemcpyHostToDevice, stream));
   int rc = forward_gemm(B, b_tok, b_pos, b_ctx, b_slot);
   if (rc) return rc;
-  B200_CUDA(launch_add_rmsnorm_bf16(pf_x, pf_proj, pf_proj_splits, pf_proj_stride, output_norm, pf_xb, B, c.d_model, c.rms_eps, stream));
+  if ((rc = add_rmsnorm_proj(output_norm, B, true))) return rc;
   B200_CUDA(launch_gemm_bf16(output16, c.vocab, c.d_model, pf_xb, B, b_logits, c.vocab, stream, &gemm_ws));
   B200_CUDA(launch_argmax_rows(b_logits, B, c.vocab, b_next, stream));
   for (int i = 0; i < B; ++i) {  // sampled requests: the sampler kernel on that row, writing over the argmax
@@ -109,7 +109,7 @@ int Engine::bench_batched(int B, int ctx, int n_steps, float* ms_per_step, int32
     B200_CUDA(cudaMemcpyAsync(b_pos, pos.data(), (size_t)B * 4, cudaMemcpyHostToDevice, stream));
     B200_CUDA(cudaMemcpyAsync(b_ctx, cx.data(), (size_t)B * 4, cudaMemcpyHostToDevice, stream));
     if ((rc = forward_gemm(B, b_tok, b_pos, b_ctx, b_slot))) break;
-    B200_CUDA(launch_add_rmsnorm_bf16(pf_x, pf_proj, pf_proj_splits, pf_proj_stride, output_norm, pf_xb, B, c.d_model, c.rms_eps, stream));
+    if ((rc = add_rmsnorm_proj(output_norm, B, true))) return rc;
     B200_CUDA(launch_gemm_bf16(output16, c.vocab, c.d_model, pf_xb, B, b_logits, c.vocab, stream, &gemm_ws));
     if (tp_size > 1) {  // vocab-parallel lm_head: per-row (logit, id) keys, max over the ranks
       B200_CUDA(launch_argmax_rows_keys(b_logits, B, c.vocab, tp_rank * c.vocab, b_keys, stream));

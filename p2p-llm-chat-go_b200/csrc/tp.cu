@@ -112,6 +112,8 @@ struct TpXchg {
   int device, pad;
   void *recv0, *recv1, *flags;
   cudaIpcMemHandle_t h0, h1, hf;
+  void *brecv0, *brecv1;          // batched-decode receive buffers (flags live in the same small block as `flags`)
+  cudaIpcMemHandle_t hb0, hb1;
 };
 
 int Engine::tp_setup_link() {
@@ -129,6 +131,20 @@ int Engine::tp_setup_link() {
   B200_CUDA(cudaMemset(L.recv[1], 0, (size_t)n * d * 4));
   B200_CUDA(cudaMemset(small, 0, 256));
   L.flags = small; L.epoch = small + 2 * kMaxTp; L.ticket = small + 2 * kMaxTp + 1; L.error = (int*)(small + 2 * kMaxTp + 2);
+  // batched decode: [tp][kTpBatchRows * d] per buffer; flags [2][kMaxTp] and a ticket further into `small`
+  TpBatch& Bt = tp_batch;
+  memset(&Bt, 0, sizeof Bt);
+  Bt.rank = tp_rank; Bt.size = n; Bt.slot_floats = (long long)kTpBatchRows * d;
+  const size_t bbytes = (size_t)n * kTpBatchRows * d * 4;
+  B200_CUDA(cudaMalloc((void**)&Bt.recv[0], bbytes));
+  B200_CUDA(cudaMalloc((void**)&Bt.recv[1], bbytes));
+  allocs.push_back(Bt.recv[0]); allocs.push_back(Bt.recv[1]);
+  B200_CUDA(cudaMemset(Bt.recv[0], 0, bbytes));
+  B200_CUDA(cudaMemset(Bt.recv[1], 0, bbytes));
+  constexpr int kBFlagsOff = 2 * kMaxTp + 8;  // words into `small`
+  static_assert((kBFlagsOff + 2 * kMaxTp + 1) * 4 <= 256, "flag block too small");
+  Bt.flags = small + kBFlagsOff; Bt.ticket = small + kBFlagsOff + 2 * kMaxTp; Bt.error = L.error;
+  tp_batch_push = getenv("B200_TP_NCCL") == nullptr;
   int rc;
   if ((rc = alloc((void**)&x_alt, (size_t)d * 4)) || (rc = alloc((void**)&tp_link, sizeof(TpLink)))) return rc;
 
@@ -138,6 +154,9 @@ int Engine::tp_setup_link() {
   B200_CUDA(cudaIpcGetMemHandle(&mine.h0, L.recv[0]));
   B200_CUDA(cudaIpcGetMemHandle(&mine.h1, L.recv[1]));
   B200_CUDA(cudaIpcGetMemHandle(&mine.hf, small));
+  mine.brecv0 = Bt.recv[0]; mine.brecv1 = Bt.recv[1];
+  B200_CUDA(cudaIpcGetMemHandle(&mine.hb0, Bt.recv[0]));
+  B200_CUDA(cudaIpcGetMemHandle(&mine.hb1, Bt.recv[1]));
   TpXchg* dev_all = nullptr;
   B200_CUDA(cudaMalloc((void**)&dev_all, sizeof(TpXchg) * n));
   B200_CUDA(cudaMemcpy(dev_all + tp_rank, &mine, sizeof mine, cudaMemcpyHostToDevice));
@@ -151,11 +170,14 @@ int Engine::tp_setup_link() {
   for (int p = 0; p < n; ++p) {
     if (p == tp_rank) {
       L.peer_recv[0][p] = L.recv[0]; L.peer_recv[1][p] = L.recv[1]; L.peer_flags[p] = L.flags;
+      Bt.peer_recv[0][p] = Bt.recv[0]; Bt.peer_recv[1][p] = Bt.recv[1]; Bt.peer_flags[p] = Bt.flags;
     } else if (all[p].pid == mine.pid) {  // a thread of this process drives that GPU: map it directly
       e = cudaDeviceEnablePeerAccess(all[p].device, 0);
       if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) return cuda_fail(e, "cudaDeviceEnablePeerAccess");
       (void)cudaGetLastError();
       L.peer_recv[0][p] = (float*)all[p].recv0; L.peer_recv[1][p] = (float*)all[p].recv1; L.peer_flags[p] = (unsigned int*)all[p].flags;
+      Bt.peer_recv[0][p] = (float*)all[p].brecv0; Bt.peer_recv[1][p] = (float*)all[p].brecv1;
+      Bt.peer_flags[p] = (unsigned int*)all[p].flags + kBFlagsOff;
     } else {
       void *a = nullptr, *b = nullptr, *f = nullptr;
       B200_CUDA(cudaIpcOpenMemHandle(&a, all[p].h0, cudaIpcMemLazyEnablePeerAccess));
@@ -163,6 +185,11 @@ int Engine::tp_setup_link() {
       B200_CUDA(cudaIpcOpenMemHandle(&f, all[p].hf, cudaIpcMemLazyEnablePeerAccess));
       tp_ipc_opened.push_back(a); tp_ipc_opened.push_back(b); tp_ipc_opened.push_back(f);
       L.peer_recv[0][p] = (float*)a; L.peer_recv[1][p] = (float*)b; L.peer_flags[p] = (unsigned int*)f;
+      void *ba = nullptr, *bb = nullptr;
+      B200_CUDA(cudaIpcOpenMemHandle(&ba, all[p].hb0, cudaIpcMemLazyEnablePeerAccess));
+      B200_CUDA(cudaIpcOpenMemHandle(&bb, all[p].hb1, cudaIpcMemLazyEnablePeerAccess));
+      tp_ipc_opened.push_back(ba); tp_ipc_opened.push_back(bb);
+      Bt.peer_recv[0][p] = (float*)ba; Bt.peer_recv[1][p] = (float*)bb; Bt.peer_flags[p] = (unsigned int*)f + kBFlagsOff;
     }
   }
   B200_CUDA(cudaMemcpy(tp_link, &L, sizeof L, cudaMemcpyHostToDevice));
