@@ -351,9 +351,9 @@ def run_tp(args):
                               "frac": (wb + kv) / (step_ms * 1e-3) / 1e9 / hbm, "launches_per_token": launches, "peak_source": peak_src},
             "bs32": {"decode_tok_per_s": bs / (b_ms * 1e-3), "ms_per_step": b_ms, "ctx": N_PROMPT + N_NEW // 2,
                      "allreduce_ms_per_step": ar_ms, "allreduce_share": ar_ms / b_ms,
-                     "allreduce": "NCCL" if os.environ.get("B200_TP_NCCL") else "push over NVLink peer memory (tp_push_kernel), reduced by the consumer",
+                     "allreduce": "push over NVLink peer memory (tp_push_kernel), reduced by the consumer" if os.environ.get("B200_TP_PUSH") else "NCCL",
                      "note": "b200_bench_batched: 32 sequences per step, tensor-core GEMMs, all-reduce of fp32 [32, d_model] x 2 per layer; "
-                             "allreduce_* = the same 2*n_layers all-reduces done with NCCL and timed alone (what the push replaces)"},
+                             "allreduce_* = the same 2*n_layers all-reduces timed alone (torch.distributed NCCL on the same fabric)"},
             "gpu_launches": args.steps * (N_NEW - 1) * launches, "clocks": clocks}))
     eng.close()
     dist.barrier()

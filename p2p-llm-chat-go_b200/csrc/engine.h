@@ -73,7 +73,7 @@ struct Engine {
   std::vector<void*> tp_ipc_opened;
   TpBatch tp_batch{};             // batched-decode all-reduce over peer memory (see kernels.h)
   unsigned int tp_bseq = 0;       // all-reduces pushed so far (every rank counts the same calls)
-  bool tp_batch_push = true;      // B200_TP_NCCL: NCCL instead
+  bool tp_batch_push = false;     // B200_TP_PUSH=1 (experiment: slower than NCCL's in-switch reduction at TP-8)
   int tp_setup_link();
   int tp_check_error();
   int tp_init(const void* unique_id);

@@ -189,7 +189,7 @@ __global__ void tp_push_kernel(const TpBatch b, const float* src, long long coun
 
 cudaError_t launch_tp_push(const TpBatch& b, const float* src, int64_t count, int buf, unsigned int seq, cudaStream_t s) {
   if (count < 4 || count % 4 || count > b.slot_floats || (buf & ~1)) return cudaErrorInvalidValue;
-  const int grid = (int)std::min<int64_t>(64, (count / 4 + 255) / 256);
+  const int grid = (int)std::min<int64_t>(296, (count / 4 + 255) / 256);  // one float4 x `size` remote stores per thread
   tp_push_kernel<<<grid, 256, 0, s>>>(b, src, (long long)count, buf, seq);
   return cudaGetLastError();
 }

@@ -69,11 +69,16 @@ def test_tp2_matches_tp1_and_oracle(pkg):
         assert res[0][2].tolist() == want_ids.tolist() == ids1.tolist()
 
 
-def test_tp2_batched_step_ranks_agree(pkg):
+@pytest.mark.parametrize("push", [False, True])
+def test_tp2_batched_step_ranks_agree(pkg, push, monkeypatch):
     """b200_bench_batched under tensor parallelism (vocab-parallel lm_head GEMM, per-row argmax keys max-reduced over
     the ranks): both ranks must pick the same ids, and the ids of TP-1.  The hook feeds its own tokens back for seven
     steps and a random-init model has near-ties, where regrouped fp32 sums may pick the other token and the chain
     then diverges: so several models, and most of them must agree to the last token."""
+    if push:  # the all-reduce as a push over peer memory (opt-in experiment) instead of NCCL
+        monkeypatch.setenv("B200_TP_PUSH", "1")
+    else:
+        monkeypatch.delenv("B200_TP_PUSH", raising=False)
     agree = 0
     for seed in range(82, 87):
         def mk():
