@@ -312,7 +312,8 @@ __global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant
             unsigned int v;
             do {
               asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(g.flags + p + j) : "memory");
-            } while (v == 0u && clock64() - t0 < 4000000000ll);  // bounded: a lost CTA must not hang the GPU
+            } while (v == 0u && clock64() - t0 < 4000000000ll);  // bounded: a lost CTA must not hang the GPU ...
+            if (v == 0u) __trap();                                // ... and must not go unnoticed either: the launch fails
           }
         }
         bar_sync_epi(256);

@@ -6,7 +6,7 @@
 //   POST /api/generate   {"model","prompt","stream"?,"raw"?,"system"?,"options"?{temperature,top_k,top_p,
 //                         repeat_penalty,repeat_last_n,seed,num_predict}}
 //   POST /api/chat       {"model","messages":[{"role","content"}],"stream"?,"options"?}
-//   GET  /               "Ollama is running"      GET /api/version      GET /api/tags
+//   GET  /               "Ollama is running"      GET /api/version      GET /api/tags      GET /metrics (Prometheus)
 // Non-stream replies are one JSON object; stream replies are NDJSON chunks (Transfer-Encoding: chunked),
 // one per token, then a final {"done":true,...} object with Ollama's *_duration / *_count statistics (ns).
 // Errors are a non-200 status with {"error": "..."} — the reference shows "(LLM error)" for any of them
@@ -40,6 +40,9 @@ using mini_json::Value;
 static b200_engine* g_engine = nullptr;
 static b200_config g_cfg;
 static std::string g_model = "llama3.1";
+
+// Prometheus counters (GET /metrics): what an operator watches next to the reference's start_all.sh processes
+static std::atomic<long long> m_requests{0}, m_errors{0}, m_in_flight{0}, m_prompt_tokens{0}, m_eval_tokens{0}, m_prompt_ns{0}, m_eval_ns{0};
 
 static std::string env(const char* k, const char* d) {
   const char* v = getenv(k);
@@ -249,7 +252,9 @@ static void handle_generate(int fd, const Value& req, bool chat) {
   if (sp.num_predict <= 0 || sp.num_predict > room) sp.num_predict = room;
 
   b200_req* r = nullptr;
-  if (b200_submit(g_engine, pb.ids.data(), pb.ids.size(), &sp, &r) != 0) { reply_error(fd, 500, b200_last_error()); return; }
+  ++m_requests;
+  if (b200_submit(g_engine, pb.ids.data(), pb.ids.size(), &sp, &r) != 0) { ++m_errors; reply_error(fd, 500, b200_last_error()); return; }
+  ++m_in_flight;
   const std::string mq = mini_json::quote(g_model);
   auto piece_obj = [&](const std::string& piece, bool final, const b200_stats* st, const std::vector<int32_t>* ctx) {
     std::string o = "{\"model\":" + mq + ",\"created_at\":\"" + now_rfc3339() + "\",";
@@ -297,6 +302,10 @@ static void handle_generate(int fd, const Value& req, bool chat) {
   b200_stats_get(r, &st);
   const std::string err = rc ? b200_last_error() : "";
   b200_free(r);
+  --m_in_flight;
+  if (rc) ++m_errors;
+  m_prompt_tokens += st.prompt_eval_count; m_eval_tokens += st.eval_count;
+  m_prompt_ns += st.load_ns + st.prompt_eval_ns; m_eval_ns += st.eval_ns;
   if (rc != 0 && !stream) { reply_error(fd, 500, err); return; }
   if (stream) {
     if (alive) {
@@ -314,7 +323,17 @@ static void serve(int fd) {
     if (rq.method == "GET" || rq.method == "HEAD") {
       if (rq.path == "/") reply(fd, 200, "text/plain; charset=utf-8", "Ollama is running");
       else if (rq.path == "/api/version") reply(fd, 200, "application/json", std::string("{\"version\":\"0.5.7-b200llm\",\"engine\":") + mini_json::quote(b200_version()) + "}");
-      else if (rq.path == "/api/tags") {
+      else if (rq.path == "/metrics") {
+        char b[1024];
+        snprintf(b, sizeof b,
+                 "# TYPE llmd_requests_total counter\nllmd_requests_total %lld\n# TYPE llmd_request_errors_total counter\nllmd_request_errors_total %lld\n"
+                 "# TYPE llmd_requests_in_flight gauge\nllmd_requests_in_flight %lld\n# TYPE llmd_prompt_tokens_total counter\nllmd_prompt_tokens_total %lld\n"
+                 "# TYPE llmd_generated_tokens_total counter\nllmd_generated_tokens_total %lld\n# TYPE llmd_prompt_seconds_total counter\n"
+                 "llmd_prompt_seconds_total %.6f\n# TYPE llmd_generation_seconds_total counter\nllmd_generation_seconds_total %.6f\n",
+                 m_requests.load(), m_errors.load(), m_in_flight.load(), m_prompt_tokens.load(), m_eval_tokens.load(), m_prompt_ns.load() / 1e9,
+                 m_eval_ns.load() / 1e9);
+        reply(fd, 200, "text/plain; version=0.0.4", b);
+      } else if (rq.path == "/api/tags") {
         const char* q = g_cfg.weight_format == B200_WEIGHTS_Q4_K_M ? "Q4_K_M" : "BF16";
         reply(fd, 200, "application/json",
               "{\"models\":[{\"name\":" + mini_json::quote(g_model + ":latest") + ",\"model\":" + mini_json::quote(g_model + ":latest") +

@@ -129,3 +129,18 @@ def test_concurrent_peers(server):
     same = requests.post(f"{server}/api/generate", json={"model": "llama3.1", "prompt": "peer 3", "stream": False,
                                                           "options": {"temperature": 0, "num_predict": 6}}, timeout=60).json()
     assert same["response"] == out[3].json()["response"]
+
+
+def test_metrics_endpoint_counts_requests(server):
+    """GET /metrics (Prometheus text format): the operational counters of SURVEY 8(f) rank 4."""
+    def scrape():
+        txt = requests.get(f"{server}/metrics", timeout=10).text
+        return {ln.split()[0]: float(ln.split()[1]) for ln in txt.splitlines() if ln and not ln.startswith("#")}
+    before = scrape()
+    body = {"model": "llama3.1", "prompt": "hello", "stream": False, "options": {"temperature": 0, "num_predict": 5}}
+    assert requests.post(f"{server}/api/generate", json=body, timeout=60).status_code == 200
+    after = scrape()
+    assert after["llmd_requests_total"] == before["llmd_requests_total"] + 1
+    assert after["llmd_generated_tokens_total"] >= before["llmd_generated_tokens_total"] + 1
+    assert after["llmd_prompt_tokens_total"] > before["llmd_prompt_tokens_total"]
+    assert after["llmd_requests_in_flight"] == 0 and after["llmd_generation_seconds_total"] >= before["llmd_generation_seconds_total"]
