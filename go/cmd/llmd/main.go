@@ -29,10 +29,14 @@ import (
 	"os"
 	"strconv"
 	"strings"
+	"sync/atomic"
 	"time"
 	"unicode/utf8"
 	"unsafe"
 )
+
+// Prometheus counters served at /metrics
+var mRequests, mErrors, mInFlight, mPromptTokens, mEvalTokens, mPromptNs, mEvalNs atomic.Int64
 
 var (
 	engine *C.b200_engine
@@ -255,12 +259,15 @@ func generate(w http.ResponseWriter, r *http.Request, chat bool) {
 		sp.num_predict = C.int32_t(room)
 	}
 	var h *C.b200_req
+	mRequests.Add(1)
 	// the library copies the ids before b200_submit returns (cgo pointer rules)
 	if C.b200_submit(engine, (*C.int32_t)(unsafe.Pointer(&pb.ids[0])), C.size_t(len(pb.ids)), &sp, &h) != 0 {
+		mErrors.Add(1)
 		writeError(w, http.StatusInternalServerError, lastError().Error())
 		return
 	}
 	defer C.b200_free(h)
+	mInFlight.Add(1)
 
 	piece := func(text string, final bool, st *C.b200_stats, ctx []int32) reply {
 		out := reply{Model: model, CreatedAt: time.Now().UTC().Format(time.RFC3339Nano), Done: final}
@@ -321,7 +328,13 @@ func generate(w http.ResponseWriter, r *http.Request, chat bool) {
 	}
 	var st C.b200_stats
 	C.b200_stats_get(h, &st)
+	mInFlight.Add(-1)
+	mPromptTokens.Add(int64(st.prompt_eval_count))
+	mEvalTokens.Add(int64(st.eval_count))
+	mPromptNs.Add(int64(st.load_ns + st.prompt_eval_ns))
+	mEvalNs.Add(int64(st.eval_ns))
 	if failure != nil {
+		mErrors.Add(1)
 		if !stream {
 			writeError(w, http.StatusInternalServerError, failure.Error())
 		} else {
@@ -391,6 +404,13 @@ func main() {
 			generate(w, r, chat)
 		}
 	}
+	mux.HandleFunc("/metrics", func(w http.ResponseWriter, r *http.Request) {
+		w.Header().Set("Content-Type", "text/plain; version=0.0.4")
+		fmt.Fprintf(w, "llmd_requests_total %d\nllmd_request_errors_total %d\nllmd_requests_in_flight %d\n"+
+			"llmd_prompt_tokens_total %d\nllmd_generated_tokens_total %d\nllmd_prompt_seconds_total %.6f\nllmd_generation_seconds_total %.6f\n",
+			mRequests.Load(), mErrors.Load(), mInFlight.Load(), mPromptTokens.Load(), mEvalTokens.Load(),
+			float64(mPromptNs.Load())/1e9, float64(mEvalNs.Load())/1e9)
+	})
 	mux.HandleFunc("/api/generate", post(false))
 	mux.HandleFunc("/api/chat", post(true))
 
