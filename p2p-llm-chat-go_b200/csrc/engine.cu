@@ -526,11 +526,23 @@ int Engine::enqueue_step(cudaStream_t s) {
       g.next_bytes = std::min<unsigned long long>(pf_cap, (unsigned long long)rows * gemv_row_bytes(type, k)) & ~127ull;
     };
     chain(a, L.o, L.o_type, d, qd);
-    B200_CUDA(launch_gemv(L.qkv_type, qkv_pro, EPI_QKV, a, s, use_pdl, sm_count)); ++n;
-    if (L.v) {
-      a.next_bytes = 0;
-      a.W = L.v; a.N = kvd; a.row_base = qd + kvd;
-      B200_CUDA(launch_gemv(L.v_type, PRO_RMSNORM, EPI_QKV, a, s, use_pdl, sm_count)); ++n;
+    bool dual = false;
+    if (L.v && qkv_pro == PRO_RMSNORM) {  // q,k and a differently-typed v: one launch when the pair is supported
+      GemvArgs bv = a;
+      bv.next_bytes = 0;
+      bv.W = L.v; bv.N = kvd; bv.row_base = qd + kvd;
+      const cudaError_t de = launch_gemv_dual_qkv(L.qkv_type, a, L.v_type, bv, s, use_pdl, sm_count);
+      if (de == cudaSuccess) { dual = true; ++n; }
+      else if (de != cudaErrorNotSupported) return cuda_fail(de, "launch_gemv_dual_qkv");
+      else (void)cudaGetLastError();
+    }
+    if (!dual) {
+      B200_CUDA(launch_gemv(L.qkv_type, qkv_pro, EPI_QKV, a, s, use_pdl, sm_count)); ++n;
+      if (L.v) {
+        a.next_bytes = 0;
+        a.W = L.v; a.N = kvd; a.row_base = qd + kvd;
+        B200_CUDA(launch_gemv(L.v_type, PRO_RMSNORM, EPI_QKV, a, s, use_pdl, sm_count)); ++n;
+      }
     }
     AttnArgs t = {};
     t.q = q; t.k_cache = L.k_cache; t.v_cache = L.v_cache; t.block_table = active_table; t.st = st;

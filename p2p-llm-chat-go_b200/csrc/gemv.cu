@@ -18,6 +18,9 @@
 // Numerics (DESIGN.md "Numerics contract", mirrored by oracle/oracle.cpp mode 0): fp32 activations and
 // accumulation; bf16 weights used exactly; Q4_K/Q6_K weights multiply activations quantised to int16 per
 // 32-element block (dp2a: int16 x int8) with exact integer sub-block sums.
+#include <algorithm>
+#include <cstdlib>
+
 #include "gemv_formats.cuh"
 
 namespace b200 {
@@ -25,8 +28,9 @@ namespace b200 {
 namespace {
 
 // ------------------------------------------------------------------ the kernel
+// cta / n_ctas: this CTA's index among the CTAs working on matrix `a` (the whole grid, or one side of a dual launch)
 template <class F, int PRO, int EPI>
-__global__ void __launch_bounds__(kWarps * 32, 1) gemv_kernel(const GemvArgs a) {
+DEVINL void gemv_body(const GemvArgs& a, int cta, int n_ctas) {
   extern __shared__ __align__(128) uint8_t smem[];
   // warp index through a shuffle so the compiler knows it is warp-uniform: the TMA issue below then takes
   // its addresses from uniform registers instead of a per-lane "waterfall" loop around every UBLKCP
@@ -41,7 +45,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) gemv_kernel(const GemvArgs a) 
   // matrix with fewer units than warps still spreads over every SM
   const int n_units = a.N / F::R;
   const int chunks = a.K / F::CHUNK;
-  const int gwarp = warp * (int)gridDim.x + (int)blockIdx.x, twarps = (int)gridDim.x * kWarps;
+  const int gwarp = warp * n_ctas + cta, twarps = n_ctas * kWarps;
   const int my_units = gwarp < n_units ? (n_units - gwarp + twarps - 1) / twarps : 0;
   const int n_items = my_units * chunks;
   const uint32_t ring_s = smem_u32(ring), bars_s = smem_u32(bars);
@@ -114,7 +118,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) gemv_kernel(const GemvArgs a) 
     __syncthreads();
     if (threadIdx.x == 0) {
       __threadfence_system();
-      if (atomicAdd(t->ticket, 1u) == gridDim.x - 1) {
+      if (atomicAdd(t->ticket, 1u) == (unsigned int)n_ctas - 1) {
         *t->ticket = 0u;
         __threadfence_system();
         const unsigned int seq = *t->epoch * (unsigned int)t->per_step + (unsigned int)a.tp_index + 1u;
@@ -128,6 +132,20 @@ __global__ void __launch_bounds__(kWarps * 32, 1) gemv_kernel(const GemvArgs a) 
     const unsigned long long end = off + per < a.next_bytes ? off + per : a.next_bytes;
     for (; off < end; off += 8192ull) l2_prefetch(a.next_W + off, (uint32_t)((end - off < 8192ull ? end - off : 8192ull) & ~15ull));
   }
+}
+
+template <class F, int PRO, int EPI>
+__global__ void __launch_bounds__(kWarps * 32, 1) gemv_kernel(const GemvArgs a) {
+  gemv_body<F, PRO, EPI>(a, (int)blockIdx.x, (int)gridDim.x);
+}
+
+// Two matrices that read the same input vector in ONE launch: the first a_ctas CTAs stream `a` in format FA, the
+// rest stream `b` in format FB (each CTA runs one body, so the two activation layouts never meet).  Used for the
+// q,k | v projections of Q4_K_M layers whose V is stored in Q6_K: one launch less per such layer (~7 us each).
+template <class FA, class FB, int PRO, int EPI>
+__global__ void __launch_bounds__(kWarps * 32, 1) gemv_dual_kernel(const GemvArgs a, const GemvArgs b, int a_ctas) {
+  if ((int)blockIdx.x < a_ctas) gemv_body<FA, PRO, EPI>(a, (int)blockIdx.x, a_ctas);
+  else gemv_body<FB, PRO, EPI>(b, (int)blockIdx.x - a_ctas, (int)gridDim.x - a_ctas);
 }
 
 template <class F>
@@ -181,7 +199,42 @@ cudaError_t launch_f(int pro, int epi, const GemvArgs& a, cudaStream_t s, bool p
   return cudaErrorInvalidValue;
 }
 
+template <class FA, class FB, int PRO, int EPI>
+cudaError_t launch_dual_t(const GemvArgs& a, const GemvArgs& b, cudaStream_t s, bool pdl, int sm_count) {
+  auto kern = gemv_dual_kernel<FA, FB, PRO, EPI>;
+  const size_t smem = std::max(smem_bytes<FA>(a.K), smem_bytes<FB>(b.K));
+  constexpr int kMaxOptinSmem = 227 * 1024;
+  if (smem > (size_t)kMaxOptinSmem || sm_count < 2) return cudaErrorInvalidValue;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxOptinSmem);
+  if (e != cudaSuccess) return e;
+  // CTAs in proportion to the bytes each side streams
+  const double ba = (double)a.N * (double)FA::row_bytes(a.K), bb = (double)b.N * (double)FB::row_bytes(b.K);
+  int a_ctas = (int)(sm_count * ba / (ba + bb) + 0.5);
+  a_ctas = std::min(std::max(a_ctas, 1), sm_count - 1);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(sm_count);
+  cfg.blockDim = dim3(kWarps * 32);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, a, b, a_ctas);
+}
+
 }  // namespace
+
+// q,k rows in Q4_K and v rows in Q6_K (the Q4_K_M recipe's "more bits" layers), RMS-norm prologue, RoPE / KV-append
+// epilogue, one launch.  Other combinations: cudaErrorNotSupported (the caller launches them one after the other).
+cudaError_t launch_gemv_dual_qkv(int type_a, const GemvArgs& a, int type_b, const GemvArgs& b, cudaStream_t s, bool pdl, int sm_count) {
+  if (type_a != T_Q4_K || type_b != T_Q6_K || getenv("B200_NO_DUAL_QKV")) return cudaErrorNotSupported;
+  if (!gemv_shape_ok(type_a, a.N, a.K, EPI_QKV) || !gemv_shape_ok(type_b, b.N, b.K, EPI_QKV)) return cudaErrorInvalidValue;
+  const bool wide = (a.N / 4) >= sm_count * kWarps;
+  if (wide) return launch_dual_t<FmtQ4K<4>, FmtQ6K, PRO_RMSNORM, EPI_QKV>(a, b, s, pdl, sm_count);
+  return launch_dual_t<FmtQ4K<2>, FmtQ6K, PRO_RMSNORM, EPI_QKV>(a, b, s, pdl, sm_count);
+}
 
 size_t gemv_row_bytes(int wtype, int64_t K) {
   switch (wtype) {

@@ -99,6 +99,8 @@ struct GemvPlan {  // launch geometry chosen on the host
 
 // pdl: launch with programmatic stream serialization (kernel N+1 prefetches weights under kernel N's tail)
 cudaError_t launch_gemv(int wtype, int pro, int epi, const GemvArgs& a, cudaStream_t s, bool pdl, int sm_count);
+// two projections of the same input in one launch (Q4_K q,k + Q6_K v); cudaErrorNotSupported for other type pairs
+cudaError_t launch_gemv_dual_qkv(int type_a, const GemvArgs& a, int type_b, const GemvArgs& b, cudaStream_t s, bool pdl, int sm_count);
 size_t gemv_row_bytes(int wtype, int64_t K);
 bool gemv_shape_ok(int wtype, int64_t N, int64_t K, int epi);
 
