@@ -181,6 +181,25 @@ def test_prefill_gemm_logits_m256_splitk(pkg, n, monkeypatch):
         assert np.array_equal(got, again)  # deterministic: no atomics in the split-K reduction
 
 
+def test_long_context_prefill_and_decode(pkg):
+    """1500-token prompt on the parity model (max_ctx 2048), RoPE far beyond the original context (llama3 scaling
+    bands).  Tensor-core path: prefill attention over 24 KV tiles.  Decode path, token by token: the split-KV decode
+    attention at every context length up to 1500 (several 32-token tiles per split from 640 on)."""
+    eng, ora, cfg = engine_and_oracle(pkg, 0, n_layers=2, seed=54, source="synth", max_ctx=2048)
+    with eng:
+        toks = _prompt(cfg, 1500, 10)
+        got = eng.forward_logits(toks, pkg.MODE_GEMM)
+        ora.reset()
+        want = ora.forward(toks, mode=1)
+        assert np.abs(got - want).max() <= PREFILL_LOGIT_TOL * max(1.0, np.abs(want).max())
+        got0 = eng.forward_logits(toks, pkg.MODE_GEMV)
+        ora.reset()
+        want0 = ora.forward(toks, mode=0)
+        assert np.abs(got0 - want0).max() <= LOGIT_TOL * max(1.0, np.abs(want0).max())
+        ids, _, _ = eng.generate_greedy(toks, 8, pkg.MODE_GEMM)
+        assert ((0 <= ids) & (ids < cfg.vocab)).all()
+
+
 def test_prefill_gemm_matches_gemv_prefill_closely(pkg):
     """Two numerics modes, one model: the logits after a 64-token prompt agree to bf16-input precision."""
     eng, ora, cfg = engine_and_oracle(pkg, 0, n_layers=2, seed=52, source="synth")
