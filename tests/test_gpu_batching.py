@@ -68,6 +68,24 @@ def test_batched_decode_matches_oracle(pkg, fmt):
         assert all(s.eval_count == n_new and s.done_reason == 2 and s.prompt_eval_count == len(p) for s, p in zip(stats, prompts))
 
 
+def test_batched_decode_long_contexts(pkg):
+    """Batched decode with contexts of several hundred to ~1000 tokens and very different lengths in one step: the
+    tensor-core decode attention walks 2..16 KV tiles per sequence (ragged last tiles, per-sequence block tables)."""
+    eng, ora, cfg = engine_and_oracle(pkg, 0, n_layers=2, seed=73, source="synth", max_ctx=1100)
+    eng.close()
+    cfg.max_seqs, cfg.reserved, cfg.seed = 4, 1, 73
+    n_new = 10
+    prompts, wants = decisive_prompts(ora, cfg, [1000, 130, 577, 65], n_new)
+    with pkg.Engine(cfg) as eng:
+        sp = pkg.default_sampling()
+        sp.temperature, sp.num_predict, sp.prefill_mode = 0.0, n_new, pkg.MODE_GEMM
+        reqs = [eng.submit(p, sp) for p in prompts]
+        got = [list(r.tokens()) for r in reqs]
+        [r.free() for r in reqs]
+        for i, (g, w) in enumerate(zip(got, wants)):
+            assert g == w, (i, g, w)
+
+
 def test_mixed_traffic_completes_and_single_request_uses_fast_path(pkg):
     eng, ora, cfg = engine_and_oracle(pkg, 0, n_layers=2, seed=72, source="synth", max_ctx=128)
     eng.close()
