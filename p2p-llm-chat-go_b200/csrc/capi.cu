@@ -593,6 +593,11 @@ int b200_sample(const float* logits, int vocab, const b200_sampling* sp, const i
   SampleArgs a = {};
   a.logits = dl.as<float>(); a.vocab = vocab; a.params = dp.as<SampleParams>(); a.history = dh.as<int32_t>(); a.st = nullptr;
   a.out = dout.as<int32_t>(); a.n_hist = n_hist; a.step = step;
+  DevBuf dpart;  // the engine's two-kernel path (vocab >= 4096); B200_SAMPLE_ONE_KERNEL=1: the single-CTA kernel
+  if (!getenv("B200_SAMPLE_ONE_KERNEL")) {
+    if ((rc = dpart.alloc(sample_part_bytes(vocab)))) return rc;
+    a.part = dpart.as<unsigned long long>();
+  }
   B200_CUDA(launch_sample(a, 0, false));
   B200_CUDA(cudaDeviceSynchronize());
   B200_CUDA(cudaMemcpy(id, dout.p, 4, cudaMemcpyDeviceToHost));

@@ -240,6 +240,7 @@ int Engine::init(const b200_config& c, const void* nccl_id) {
         (rc = alloc((void**)&attn_partial, attn_partial_floats(lc.n_heads, lc.n_kv_heads, n_splits) * 4)) ||
         (rc = alloc((void**)&tp_partial, (size_t)d * 4)) ||
         (rc = alloc((void**)&attn_counters, (size_t)lc.n_kv_heads * 4)) || (rc = alloc((void**)&st, sizeof(StepState))) ||
+        (rc = alloc((void**)&sample_part, sample_part_bytes(cfg.vocab))) ||
         (rc = alloc((void**)&sp_dev, sizeof(SampleParams))) ||
         (rc = alloc((void**)&prompt_dev, (size_t)c.max_ctx * 4)))
       return rc;
@@ -381,7 +382,9 @@ int Engine::enqueue_tail(cudaStream_t s, bool pdl, int* n, bool consume_tp, bool
   }
   SampleArgs sa = {};
   sa.logits = logits; sa.vocab = cfg.vocab; sa.params = sp_dev; sa.history = prompt_dev; sa.st = st; sa.out = &st->sampled; sa.n_hist = -1;
-  B200_CUDA(launch_sample(sa, s, pdl && tp_size == 1 && with_lm_head)); ++*n;
+  sa.part = sample_part;
+  B200_CUDA(launch_sample(sa, s, pdl && tp_size == 1 && with_lm_head));
+  *n += (sample_part && cfg.vocab >= 4096) ? 2 : 1;
   FinishArgs f = {};
   f.st = st; f.prompt = prompt_dev; f.out_tokens = out_tokens_dev; f.host_n_out = host_n_out_dev; f.embd = token_embd;
   f.embd_type = embd_type; f.d_model = c.d_model; f.x = x; f.max_ctx = c.max_ctx;

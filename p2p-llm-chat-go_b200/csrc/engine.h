@@ -130,6 +130,7 @@ struct Engine {
   // K splits the qkv / gate-up GEMMs may use for n rows: their outputs are [pf_rows][width] buffers, every partial
   // is [n][width] (these two are column-parallel under TP: partials stay local, so TP does not restrict them)
   int max_wide_splits(int n) const { const int f = pf_rows / (n < 1 ? 1 : n); return f < 1 ? 1 : (f > 16 ? 16 : f); }
+  unsigned long long* sample_part = nullptr;  // scratch of the two-kernel sampler (per-slice top-k keys)
   GemmWorkspace gemm_ws = {};  // stream-K scratch of the tensor-core GEMMs (gate/up, batched lm_head)
   // most K splits a projection over n rows may use: every partial is [n][d_model] and all must fit pf_proj
   int max_proj_splits(int n) const {

@@ -147,8 +147,10 @@ struct SampleArgs {
   int32_t* out;
   int n_hist;              // >= 0: stand-alone mode (test hook) with explicit history length and step
   unsigned long long step;
+  unsigned long long* part;  // scratch of sample_part_bytes(vocab): two-kernel path (null: one CTA does everything)
 };
-cudaError_t launch_sample(const SampleArgs& a, cudaStream_t s, bool pdl);
+cudaError_t launch_sample(const SampleArgs& a, cudaStream_t s, bool pdl);  // 1 launch, or 2 when a.part is set and vocab >= 4096
+size_t sample_part_bytes(int vocab);
 
 struct FinishArgs {
   StepState* st;

@@ -32,6 +32,8 @@ DEVINL uint64_t splitmix64(uint64_t x) {
   return x ^ (x >> 31);
 }
 
+DEVINL float from_ordered_bits(uint32_t o) { return __uint_as_float((o & 0x80000000u) ? (o ^ 0x80000000u) : ~o); }
+
 struct Smem {
   uint32_t hist[2048];
   uint32_t seen[(1 << 18) / 32];  // token bitmap for the repeat penalty (vocab <= 262144)
@@ -47,18 +49,141 @@ DEVINL float penalised(const float* logits, const uint32_t* seen, int i, float p
   return v;
 }
 
-// Finds in hist[0..nbins) the highest bin b such that count(bins > b) < want <= count(bins >= b).
-DEVINL void pick_bin(Smem& s, int nbins, uint32_t want) {
-  if (threadIdx.x == 0) {
-    uint32_t above = 0;
-    int b = nbins - 1;
-    for (; b > 0; --b) {
-      if (above + s.hist[b] >= want) break;
-      above += s.hist[b];
-    }
-    s.bin = (uint32_t)b;
-    s.above += above;
+// Where the candidates come from: every logit of the vocabulary (one-kernel path) ...
+struct SrcLogits {
+  const float* logits;
+  const uint32_t* seen;
+  float penalty;
+  DEVINL bool get(int i, uint32_t& o, uint32_t& id) const {
+    o = ordered_bits(penalised(logits, seen, i, penalty));
+    id = (uint32_t)i;
+    return true;
   }
+};
+// ... or the per-slice top-k keys left by sample_part_kernel (two-kernel path): slice c, rank r at part[c*kMaxK + r],
+// key = ordered penalised logit << 32 | ~id, 0 = empty slot
+struct SrcKeys {
+  const unsigned long long* part;
+  int k;
+  DEVINL bool get(int i, uint32_t& o, uint32_t& id) const {
+    const unsigned long long key = part[(size_t)(i / k) * kMaxK + (i % k)];
+    o = (uint32_t)(key >> 32);
+    id = 0xffffffffu - (uint32_t)(key & 0xffffffffull);
+    return key != 0ull;
+  }
+};
+
+// Finds in hist[0..nbins) the highest bin b such that count(bins > b) < want <= count(bins >= b), all threads
+// together: thread t owns bins 2t, 2t+1 (nbins <= 2 * kThreads); a block-wide suffix sum gives every thread the
+// count above its bins, and the one thread whose bin straddles `want` publishes it.  (One thread walking the
+// 2048 bins from the top cost ~8 us per pass, three passes per token.)
+DEVINL void pick_bin(Smem& s, int nbins, uint32_t want) {
+  __shared__ uint32_t warp_tot[kThreads / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t h0 = 2 * tid < nbins ? s.hist[2 * tid] : 0u, h1 = 2 * tid + 1 < nbins ? s.hist[2 * tid + 1] : 0u;
+  // suffix sum over threads: sfx = sum of (h0 + h1) of all threads with a higher index
+  uint32_t v = h0 + h1, incl = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t up = __shfl_down_sync(0xffffffffu, incl, o);
+    if (lane + o < 32) incl += up;
+  }
+  if (lane == 0) warp_tot[warp] = incl;  // total of this warp
+  __syncthreads();
+  uint32_t higher_warps = 0;
+  for (int w = warp + 1; w < kThreads / 32; ++w) higher_warps += warp_tot[w];
+  const uint32_t above1 = higher_warps + (incl - v);  // everything above bin 2t+1
+  const uint32_t above0 = above1 + h1;                // everything above bin 2t
+  // bin 0 takes whatever is left (the serial version stopped at b == 0 unconditionally)
+  if (2 * tid + 1 < nbins && above1 < want && want <= above1 + h1) { s.bin = (uint32_t)(2 * tid + 1); s.above += above1; }
+  else if (2 * tid < nbins && above0 < want && (want <= above0 + h0 || tid == 0)) { s.bin = (uint32_t)(2 * tid); s.above += above0; }
+  __syncthreads();
+}
+
+// Exact top-k of the source's candidates, then top-p / temperature / draw.  Needs s.prefix = s.above = s.n_cand =
+// s.n_eq = 0 on entry (one CTA of kThreads threads).
+template <class Src>
+DEVINL void sample_core(Smem& s, const Src& src, int n, int k, const SampleParams& p, uint64_t step, int32_t* out) {
+  const int tid = threadIdx.x;
+  // ---- exact k-th largest ordered value: 11 + 11 + 10 bits
+  const int shifts[3] = {21, 10, 0}, widths[3] = {11, 11, 10};
+  for (int pass = 0; pass < 3; ++pass) {
+    const int nb = 1 << widths[pass];
+    for (int i = tid; i < nb; i += kThreads) s.hist[i] = 0;
+    __syncthreads();
+    const uint32_t pre = s.prefix;
+    const int hi_shift = shifts[pass] + widths[pass];
+    for (int i = tid; i < n; i += kThreads) {
+      uint32_t o, id;
+      if (!src.get(i, o, id)) continue;
+      if (pass == 0 || (o >> hi_shift) == (pre >> hi_shift)) atomicAdd(&s.hist[(o >> shifts[pass]) & (nb - 1)], 1u);
+    }
+    __syncthreads();
+    pick_bin(s, nb, (uint32_t)k - s.above);
+    __syncthreads();
+    if (tid == 0) s.prefix |= s.bin << shifts[pass];
+    __syncthreads();
+  }
+  const uint32_t kth = s.prefix;       // ordered bits of the k-th largest logit
+  const uint32_t above = s.above;      // how many are strictly larger (< k)
+  // ---- gather: everything above the threshold, plus the lowest-id ties at the threshold
+  for (int i = tid; i < n; i += kThreads) {
+    uint32_t o, id;
+    if (!src.get(i, o, id)) continue;
+    if (o > kth) {
+      const uint32_t slot = atomicAdd(&s.n_cand, 1u);
+      s.cand[slot] = ((unsigned long long)o << 32) | (0xffffffffu - id);
+    } else if (o == kth) {
+      const uint32_t slot = atomicAdd(&s.n_eq, 1u);
+      if (slot < kMaxEq) s.eq_idx[slot] = id;
+    }
+  }
+  __syncthreads();
+  const int need = k - (int)above, n_eq = (int)min(s.n_eq, (uint32_t)kMaxEq);
+  for (int e = tid; e < n_eq; e += kThreads) {  // rank the ties by id; the `need` smallest ids join
+    const uint32_t id = s.eq_idx[e];
+    int rank = 0;
+    for (int j = 0; j < n_eq; ++j) rank += s.eq_idx[j] < id;
+    if (rank < need) s.cand[above + rank] = ((unsigned long long)kth << 32) | (0xffffffffu - id);
+  }
+  __syncthreads();
+  for (int e = tid; e < k; e += kThreads) {  // rank sort, descending key
+    const unsigned long long key = s.cand[e];
+    int rank = 0;
+    for (int j = 0; j < k; ++j) rank += s.cand[j] > key;
+    s.sorted[rank] = key;
+  }
+  __syncthreads();
+  if (tid != 0) return;
+  // ---- sequential tail, same operation order as the oracle (orc_sample)
+  // the key holds the penalised logit exactly (ordered_bits is a bijection on the float bits)
+  auto logit_of = [&](int i) { return from_ordered_bits((uint32_t)(s.sorted[i] >> 32)); };
+  if (p.temperature <= 0.f) {  // greedy over the penalised logits (k == 1)
+    *out = (int32_t)(0xffffffffu - (uint32_t)(s.sorted[0] & 0xffffffffull));
+    return;
+  }
+  const float mx = logit_of(0);
+  float sum = 0.f;
+  for (int i = 0; i < k; ++i) sum += expf(logit_of(i) - mx);
+  int keep = k;
+  if (p.top_p < 1.0f) {
+    float cum = 0.f;
+    for (int i = 0; i < k; ++i) {
+      cum += expf(logit_of(i) - mx) / sum;
+      if (cum >= p.top_p) { keep = i + 1; break; }
+    }
+  }
+  float sum2 = 0.f;
+  for (int i = 0; i < keep; ++i) sum2 += expf((logit_of(i) - mx) / p.temperature);
+  const uint64_t r = splitmix64(p.seed + step * 0x9E3779B97F4A7C15ull);
+  const float uu = (float)(r >> 40) * 5.9604644775390625e-8f * sum2;
+  float cum = 0.f;
+  int pick = keep - 1;
+  for (int i = 0; i < keep; ++i) {
+    cum += expf((logit_of(i) - mx) / p.temperature);
+    if (uu < cum) { pick = i; break; }
+  }
+  *out = (int32_t)(0xffffffffu - (uint32_t)(s.sorted[pick] & 0xffffffffull));
 }
 
 __global__ void __launch_bounds__(kThreads) sample_kernel(const SampleArgs a) {
@@ -106,81 +231,79 @@ __global__ void __launch_bounds__(kThreads) sample_kernel(const SampleArgs a) {
 
   int k = p.top_k <= 0 ? kMaxK : min(p.top_k, kMaxK);
   k = min(k, V);
-  // ---- exact k-th largest ordered value: 11 + 11 + 10 bits
-  const int shifts[3] = {21, 10, 0}, widths[3] = {11, 11, 10};
-  for (int pass = 0; pass < 3; ++pass) {
-    const int nb = 1 << widths[pass];
-    for (int i = tid; i < nb; i += kThreads) s.hist[i] = 0;
-    __syncthreads();
-    const uint32_t pre = s.prefix;
-    const int hi_shift = shifts[pass] + widths[pass];
-    for (int i = tid; i < V; i += kThreads) {
-      const uint32_t o = ordered_bits(penalised(a.logits, s.seen, i, p.repeat_penalty));
-      if (pass == 0 || (o >> hi_shift) == (pre >> hi_shift)) atomicAdd(&s.hist[(o >> shifts[pass]) & (nb - 1)], 1u);
-    }
-    __syncthreads();
-    pick_bin(s, nb, (uint32_t)k - s.above);
-    __syncthreads();
-    if (tid == 0) s.prefix |= s.bin << shifts[pass];
-    __syncthreads();
-  }
-  const uint32_t kth = s.prefix;       // ordered bits of the k-th largest logit
-  const uint32_t above = s.above;      // how many are strictly larger (< k)
-  // ---- gather: everything above the threshold, plus the lowest-id ties at the threshold
-  for (int i = tid; i < V; i += kThreads) {
-    const uint32_t o = ordered_bits(penalised(a.logits, s.seen, i, p.repeat_penalty));
-    if (o > kth) {
-      const uint32_t slot = atomicAdd(&s.n_cand, 1u);
-      s.cand[slot] = ((unsigned long long)o << 32) | (0xffffffffu - (uint32_t)i);
-    } else if (o == kth) {
-      const uint32_t slot = atomicAdd(&s.n_eq, 1u);
-      if (slot < kMaxEq) s.eq_idx[slot] = (uint32_t)i;
+  const SrcLogits src = {a.logits, s.seen, p.repeat_penalty};
+  sample_core(s, src, V, k, p, step, a.out);
+}
+
+// ---- two-kernel path: the single CTA above walks the 128 K logits four times (~170 us per sampled token).  Here
+// every 1024-logit slice of the vocabulary is ranked by its own CTA (the global top-k is a subset of the union of the
+// slices' top-k), and one CTA then selects among <= slices * k keys.  Same keys, same order, same tail: same token.
+constexpr int kSlice = 1024;
+
+struct PartSmem {
+  unsigned long long keys[kSlice];
+  uint32_t seen[kSlice / 32];
+};
+
+__global__ void __launch_bounds__(kSlice) sample_part_kernel(const SampleArgs a) {
+  __shared__ PartSmem s;
+  pdl_wait();
+  pdl_launch_dependents();
+  const StepState* st = a.st;
+  if (st != nullptr && (st->greedy || st->pos + 1 < st->n_prompt)) return;
+  const int tid = threadIdx.x, V = a.vocab, base = blockIdx.x * kSlice;
+  const SampleParams p = *a.params;
+  const int n_hist = a.n_hist >= 0 ? a.n_hist : st->pos + 1;
+  int k = p.temperature <= 0.f ? 1 : (p.top_k <= 0 ? kMaxK : min(p.top_k, kMaxK));
+  k = min(k, V);
+  if (tid < kSlice / 32) s.seen[tid] = 0;
+  if (tid < k) a.part[(size_t)blockIdx.x * kMaxK + tid] = 0ull;  // empty slots (a last slice shorter than k)
+  __syncthreads();
+  if (p.repeat_penalty != 1.0f && p.repeat_last_n != 0) {
+    const int from = p.repeat_last_n < 0 ? 0 : max(0, n_hist - p.repeat_last_n);
+    for (int i = from + tid; i < n_hist; i += kSlice) {
+      const int t = a.history[i] - base;
+      if (t >= 0 && t < kSlice) atomicOr(&s.seen[t >> 5], 1u << (t & 31));
     }
   }
   __syncthreads();
-  const int need = k - (int)above, n_eq = (int)min(s.n_eq, (uint32_t)kMaxEq);
-  for (int e = tid; e < n_eq; e += kThreads) {  // rank the ties by id; the `need` smallest ids join
-    const uint32_t id = s.eq_idx[e];
-    int rank = 0;
-    for (int j = 0; j < n_eq; ++j) rank += s.eq_idx[j] < id;
-    if (rank < need) s.cand[above + rank] = ((unsigned long long)kth << 32) | (0xffffffffu - id);
+  const int id = base + tid;
+  unsigned long long key = 0ull;
+  if (id < V) {
+    float v = a.logits[id];
+    if (s.seen[tid >> 5] & (1u << (tid & 31))) v = v > 0.f ? v / p.repeat_penalty : v * p.repeat_penalty;
+    key = ((unsigned long long)ordered_bits(v) << 32) | (0xffffffffu - (uint32_t)id);
   }
+  s.keys[tid] = key;
   __syncthreads();
-  for (int e = tid; e < k; e += kThreads) {  // rank sort, descending key
-    const unsigned long long key = s.cand[e];
-    int rank = 0;
-    for (int j = 0; j < k; ++j) rank += s.cand[j] > key;
-    s.sorted[rank] = key;
-  }
+  if (key == 0ull) return;
+  int rank = 0;
+#pragma unroll 8
+  for (int j = 0; j < kSlice; ++j) rank += s.keys[j] > key;  // broadcast reads; keys are unique
+  if (rank < k) a.part[(size_t)blockIdx.x * kMaxK + rank] = key;
+}
+
+__global__ void __launch_bounds__(kThreads) sample_final_kernel(const SampleArgs a) {
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  Smem& s = *reinterpret_cast<Smem*>(smem_raw);
+  pdl_wait();
+  pdl_launch_dependents();
+  const StepState* st = a.st;
+  if (st != nullptr && (st->greedy || st->pos + 1 < st->n_prompt)) return;
+  const SampleParams p = *a.params;
+  const uint64_t step = a.n_hist >= 0 ? a.step : (uint64_t)st->n_out;
+  int k = p.temperature <= 0.f ? 1 : (p.top_k <= 0 ? kMaxK : min(p.top_k, kMaxK));
+  k = min(k, a.vocab);
+  if (threadIdx.x == 0) { s.prefix = 0; s.above = 0; s.n_cand = 0; s.n_eq = 0; }
   __syncthreads();
-  if (tid != 0) return;
-  // ---- sequential tail, same operation order as the oracle (orc_sample)
-  auto logit_of = [&](int i) { return penalised(a.logits, s.seen, (int)(0xffffffffu - (uint32_t)(s.sorted[i] & 0xffffffffull)), p.repeat_penalty); };
-  const float mx = logit_of(0);
-  float sum = 0.f;
-  for (int i = 0; i < k; ++i) sum += expf(logit_of(i) - mx);
-  int keep = k;
-  if (p.top_p < 1.0f) {
-    float cum = 0.f;
-    for (int i = 0; i < k; ++i) {
-      cum += expf(logit_of(i) - mx) / sum;
-      if (cum >= p.top_p) { keep = i + 1; break; }
-    }
-  }
-  float sum2 = 0.f;
-  for (int i = 0; i < keep; ++i) sum2 += expf((logit_of(i) - mx) / p.temperature);
-  const uint64_t r = splitmix64(p.seed + step * 0x9E3779B97F4A7C15ull);
-  const float uu = (float)(r >> 40) * 5.9604644775390625e-8f * sum2;
-  float cum = 0.f;
-  int pick = keep - 1;
-  for (int i = 0; i < keep; ++i) {
-    cum += expf((logit_of(i) - mx) / p.temperature);
-    if (uu < cum) { pick = i; break; }
-  }
-  *a.out = (int32_t)(0xffffffffu - (uint32_t)(s.sorted[pick] & 0xffffffffull));
+  const int slices = (a.vocab + kSlice - 1) / kSlice;
+  const SrcKeys src = {a.part, k};
+  sample_core(s, src, slices * k, k, p, step, a.out);
 }
 
 }  // namespace
+
+size_t sample_part_bytes(int vocab) { return (size_t)((vocab + kSlice - 1) / kSlice) * kMaxK * sizeof(unsigned long long); }
 
 cudaError_t launch_sample(const SampleArgs& a, cudaStream_t s, bool pdl) {
   if (a.vocab <= 0 || a.vocab > (1 << 18)) return cudaErrorInvalidValue;
@@ -196,6 +319,17 @@ cudaError_t launch_sample(const SampleArgs& a, cudaStream_t s, bool pdl) {
   at[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
   cfg.numAttrs = pdl ? 1 : 0;
+  if (a.part != nullptr && a.vocab >= 4 * kSlice) {  // two kernels: per-slice ranking, then the selection and the draw
+    cudaLaunchConfig_t c1 = cfg;
+    c1.gridDim = dim3((a.vocab + kSlice - 1) / kSlice);
+    c1.blockDim = dim3(kSlice);
+    c1.dynamicSmemBytes = 0;
+    e = cudaLaunchKernelEx(&c1, sample_part_kernel, a);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(sample_final_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+    if (e != cudaSuccess) return e;
+    return cudaLaunchKernelEx(&cfg, sample_final_kernel, a);
+  }
   return cudaLaunchKernelEx(&cfg, sample_kernel, a);
 }
 

@@ -81,6 +81,7 @@ int Engine::batched_step(const std::vector<int>& sl, std::vector<int32_t>* next)
     sa.logits = b_logits + (size_t)i * c.vocab; sa.vocab = c.vocab; sa.params = sp_arr + sl[i];
     sa.history = hist_dev + (size_t)sl[i] * c.max_ctx; sa.st = nullptr; sa.out = b_next + i; sa.n_hist = q.pos + 1;
     sa.step = (unsigned long long)q.delivered;
+    sa.part = sample_part;  // shared scratch: the rows are sampled one after the other on this stream
     B200_CUDA(launch_sample(sa, stream, false));
   }
   B200_CUDA(launch_append_history(b_next, b_slot, b_pos, hist_dev, c.max_ctx, B, stream));

@@ -36,9 +36,15 @@ CASES = [dict(), dict(top_k=1), dict(top_k=256, top_p=1.0), dict(top_k=7, top_p=
          dict(repeat_last_n=3), dict(top_p=0.01)]
 
 
+# vocab >= 4096 takes the two-kernel path (per-slice ranking + final selection) unless B200_SAMPLE_ONE_KERNEL is set;
+# 130000 is not a multiple of the 1024-logit slice (ragged last slice)
 @pytest.mark.parametrize("case", range(len(CASES)))
-@pytest.mark.parametrize("vocab", [1024, 128256])
-def test_sample_token_ids_identical(pkg, case, vocab):
+@pytest.mark.parametrize("vocab,one_kernel", [(1024, False), (128256, False), (128256, True), (130000, False), (4096, False)])
+def test_sample_token_ids_identical(pkg, case, vocab, one_kernel, monkeypatch):
+    if one_kernel:
+        monkeypatch.setenv("B200_SAMPLE_ONE_KERNEL", "1")
+    else:
+        monkeypatch.delenv("B200_SAMPLE_ONE_KERNEL", raising=False)
     rng = np.random.default_rng(case * 7 + vocab)
     for trial in range(6):
         logits = (rng.standard_normal(vocab) * 2.0).astype(np.float32)
