@@ -100,10 +100,11 @@ DEVINL void pick_bin(Smem& s, int nbins, uint32_t want) {
   __syncthreads();
 }
 
-// Exact top-k of the source's candidates, then top-p / temperature / draw.  Needs s.prefix = s.above = s.n_cand =
-// s.n_eq = 0 on entry (one CTA of kThreads threads).
+// Exact top-k of the source's candidates (then, in sample_core, top-p / temperature / draw).  Needs s.prefix =
+// s.above = s.n_cand = s.n_eq = 0 on entry (one CTA of kThreads threads).
+// s.sorted[0..k) <- the k largest keys of the source, descending (k <= number of valid candidates)
 template <class Src>
-DEVINL void sample_core(Smem& s, const Src& src, int n, int k, const SampleParams& p, uint64_t step, int32_t* out) {
+DEVINL void select_topk(Smem& s, const Src& src, int n, int k) {
   const int tid = threadIdx.x;
   // ---- exact k-th largest ordered value: 11 + 11 + 10 bits
   const int shifts[3] = {21, 10, 0}, widths[3] = {11, 11, 10};
@@ -154,7 +155,12 @@ DEVINL void sample_core(Smem& s, const Src& src, int n, int k, const SampleParam
     s.sorted[rank] = key;
   }
   __syncthreads();
-  if (tid != 0) return;
+}
+
+template <class Src>
+DEVINL void sample_core(Smem& s, const Src& src, int n, int k, const SampleParams& p, uint64_t step, int32_t* out) {
+  select_topk(s, src, n, k);
+  if (threadIdx.x != 0) return;
   // ---- sequential tail, same operation order as the oracle (orc_sample)
   // the key holds the penalised logit exactly (ordered_bits is a bijection on the float bits)
   auto logit_of = [&](int i) { return from_ordered_bits((uint32_t)(s.sorted[i] >> 32)); };
@@ -240,13 +246,23 @@ __global__ void __launch_bounds__(kThreads) sample_kernel(const SampleArgs a) {
 // slices' top-k), and one CTA then selects among <= slices * k keys.  Same keys, same order, same tail: same token.
 constexpr int kSlice = 1024;
 
-struct PartSmem {
-  unsigned long long keys[kSlice];
-  uint32_t seen[kSlice / 32];
+// a slice's candidates: the 1024 keys of the slice in shared memory (0 = past the end of the vocabulary)
+struct SrcSlice {
+  const unsigned long long* keys;
+  DEVINL bool get(int i, uint32_t& o, uint32_t& id) const {
+    const unsigned long long key = keys[i];
+    o = (uint32_t)(key >> 32);
+    id = 0xffffffffu - (uint32_t)(key & 0xffffffffull);
+    return key != 0ull;
+  }
 };
+static_assert(kSlice == kThreads, "one logit per thread");
 
 __global__ void __launch_bounds__(kSlice) sample_part_kernel(const SampleArgs a) {
-  __shared__ PartSmem s;
+  extern __shared__ __align__(16) uint8_t smem_raw[];
+  Smem& s = *reinterpret_cast<Smem*>(smem_raw);
+  unsigned long long* keys = reinterpret_cast<unsigned long long*>(s.seen);  // the token bitmap's space: [kSlice] keys + 32 words
+  uint32_t* seen = s.seen + 2 * kSlice;
   pdl_wait();
   pdl_launch_dependents();
   const StepState* st = a.st;
@@ -255,15 +271,16 @@ __global__ void __launch_bounds__(kSlice) sample_part_kernel(const SampleArgs a)
   const SampleParams p = *a.params;
   const int n_hist = a.n_hist >= 0 ? a.n_hist : st->pos + 1;
   int k = p.temperature <= 0.f ? 1 : (p.top_k <= 0 ? kMaxK : min(p.top_k, kMaxK));
-  k = min(k, V);
-  if (tid < kSlice / 32) s.seen[tid] = 0;
-  if (tid < k) a.part[(size_t)blockIdx.x * kMaxK + tid] = 0ull;  // empty slots (a last slice shorter than k)
+  k = min(k, min(V - base, kSlice));  // a short last slice has fewer candidates than k
+  if (tid < kSlice / 32) seen[tid] = 0;
+  if (tid < kMaxK) a.part[(size_t)blockIdx.x * kMaxK + tid] = 0ull;  // empty slots
+  if (tid == 0) { s.prefix = 0; s.above = 0; s.n_cand = 0; s.n_eq = 0; }
   __syncthreads();
   if (p.repeat_penalty != 1.0f && p.repeat_last_n != 0) {
     const int from = p.repeat_last_n < 0 ? 0 : max(0, n_hist - p.repeat_last_n);
     for (int i = from + tid; i < n_hist; i += kSlice) {
       const int t = a.history[i] - base;
-      if (t >= 0 && t < kSlice) atomicOr(&s.seen[t >> 5], 1u << (t & 31));
+      if (t >= 0 && t < kSlice) atomicOr(&seen[t >> 5], 1u << (t & 31));
     }
   }
   __syncthreads();
@@ -271,16 +288,14 @@ __global__ void __launch_bounds__(kSlice) sample_part_kernel(const SampleArgs a)
   unsigned long long key = 0ull;
   if (id < V) {
     float v = a.logits[id];
-    if (s.seen[tid >> 5] & (1u << (tid & 31))) v = v > 0.f ? v / p.repeat_penalty : v * p.repeat_penalty;
+    if (seen[tid >> 5] & (1u << (tid & 31))) v = v > 0.f ? v / p.repeat_penalty : v * p.repeat_penalty;
     key = ((unsigned long long)ordered_bits(v) << 32) | (0xffffffffu - (uint32_t)id);
   }
-  s.keys[tid] = key;
+  keys[tid] = key;
   __syncthreads();
-  if (key == 0ull) return;
-  int rank = 0;
-#pragma unroll 8
-  for (int j = 0; j < kSlice; ++j) rank += s.keys[j] > key;  // broadcast reads; keys are unique
-  if (rank < k) a.part[(size_t)blockIdx.x * kMaxK + rank] = key;
+  const SrcSlice src = {keys};
+  select_topk(s, src, kSlice, k);
+  if (tid < k) a.part[(size_t)blockIdx.x * kMaxK + tid] = s.sorted[tid];
 }
 
 __global__ void __launch_bounds__(kThreads) sample_final_kernel(const SampleArgs a) {
@@ -323,7 +338,8 @@ cudaError_t launch_sample(const SampleArgs& a, cudaStream_t s, bool pdl) {
     cudaLaunchConfig_t c1 = cfg;
     c1.gridDim = dim3((a.vocab + kSlice - 1) / kSlice);
     c1.blockDim = dim3(kSlice);
-    c1.dynamicSmemBytes = 0;
+    e = cudaFuncSetAttribute(sample_part_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+    if (e != cudaSuccess) return e;
     e = cudaLaunchKernelEx(&c1, sample_part_kernel, a);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(sample_final_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
