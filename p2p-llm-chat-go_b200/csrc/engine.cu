@@ -846,10 +846,6 @@ int Engine::reduce_proj(int n, bool decode) {
   const int d = lc.d_model;
   pf_proj_src = pf_proj; pf_wait_flags = nullptr;
   if (tp_size <= 1) return 0;
-  if (pf_proj_splits > 1) {  // local split-K partials -> one partial per rank
-    B200_CUDA(launch_sum_partials(pf_proj, pf_proj_splits, pf_proj_stride, (int64_t)n * d, stream));
-    pf_proj_splits = 1;
-  }
   if (decode && tp_fused && tp_batch_push && n <= kTpBatchRows) {
     const int buf = (int)(tp_bseq & 1u);
     ++tp_bseq;

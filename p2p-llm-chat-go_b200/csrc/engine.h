@@ -135,9 +135,7 @@ struct Engine {
   // most K splits a projection over n rows may use: every partial is [n][d_model] and all must fit pf_proj
   int max_proj_splits(int n) const {
     const int64_t fit = pf_proj_floats / ((int64_t)n * lc.d_model);
-    // tensor parallel: only the weight-streaming regime (<= 32 rows) splits K; the partials are folded before the all-reduce
-    if (tp_size > 1 && n > 32) return 1;
-    return (int)(fit < 1 ? 1 : (fit > 16 ? 16 : fit));
+    return tp_size > 1 ? 1 : (int)(fit < 1 ? 1 : (fit > 16 ? 16 : fit));
   }
 
   // sequence slots (continuous batching): slot s statically owns block-table row s

@@ -46,7 +46,6 @@ struct TpBatch {
   int rank, size;
   long long slot_floats;             // kTpBatchRows * d
 };
-cudaError_t launch_sum_partials(float* x, int n_parts, int64_t stride, int64_t count, cudaStream_t s);
 cudaError_t launch_tp_push(const TpBatch& b, const float* src, int64_t count, int buf, unsigned int seq, cudaStream_t s);
 
 // Device-resident state of the sequence being decoded; every kernel of a step reads it, the last kernel

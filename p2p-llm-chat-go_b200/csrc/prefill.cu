@@ -165,19 +165,6 @@ __global__ void append_history_kernel(const int32_t* next, const int32_t* slot_a
   if (r < rows && pos_arr[r] + 1 < max_ctx) history[(size_t)slot_arr[r] * max_ctx + pos_arr[r] + 1] = next[r];
 }
 
-// x[0][i] += x[1][i] + ... + x[n_parts-1][i] (ascending): split-K partials folded before a tensor-parallel all-reduce
-__global__ void sum_partials_kernel(float* x, int n_parts, long long stride, long long count) {
-  const long long n4 = count / 4;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
-    float4 a = reinterpret_cast<const float4*>(x)[i];
-    for (int p = 1; p < n_parts; ++p) {
-      const float4 b = *reinterpret_cast<const float4*>(x + (size_t)p * stride + 4 * i);
-      a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
-    }
-    reinterpret_cast<float4*>(x)[i] = a;
-  }
-}
-
 // this rank's partial [count floats] -> slot `rank` of every peer's receive buffer `buf`; the last CTA to finish
 // raises this rank's sequence flag on every peer
 __global__ void tp_push_kernel(const TpBatch b, const float* src, long long count, int buf, unsigned int seq) {
@@ -199,14 +186,6 @@ __global__ void tp_push_kernel(const TpBatch b, const float* src, long long coun
 }
 
 }  // namespace
-
-cudaError_t launch_sum_partials(float* x, int n_parts, int64_t stride, int64_t count, cudaStream_t s) {
-  if (count % 4 || stride % 4) return cudaErrorInvalidValue;
-  if (n_parts <= 1) return cudaSuccess;
-  const int grid = (int)std::min<int64_t>(296, (count / 4 + 255) / 256);
-  sum_partials_kernel<<<grid, 256, 0, s>>>(x, n_parts, (long long)stride, (long long)count);
-  return cudaGetLastError();
-}
 
 cudaError_t launch_tp_push(const TpBatch& b, const float* src, int64_t count, int buf, unsigned int seq, cudaStream_t s) {
   if (count < 4 || count % 4 || count > b.slot_floats || (buf & ~1)) return cudaErrorInvalidValue;
