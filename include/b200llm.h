@@ -142,6 +142,10 @@ B200_API int b200_tok_load_gguf(const char* path, b200_tok** out);
 B200_API void b200_tok_free(b200_tok* t);
 B200_API int b200_tok_encode(const b200_tok* t, const char* utf8, size_t n, int add_bos, int32_t* ids, size_t cap, size_t* n_out);
 B200_API int b200_tok_decode(const b200_tok* t, const int32_t* ids, size_t n, char* buf, size_t cap, size_t* n_out);
+/* The pre-tokenisation step on its own (needs no vocabulary): the Llama-3 ("llama-bpe") regex evaluated on Unicode code
+ * points; ends[i] = byte offset one past piece i, pieces are consecutive and cover the text.  Replaces the regex split
+ * Ollama / llama.cpp apply before BPE; exposed so tests can compare it with a regex engine. */
+B200_API int b200_pretokenize(const char* utf8, size_t n, int32_t* ends, size_t cap, size_t* n_out);
 
 /* ---- generation (replaces: the body of Ollama's /api/generate that web/streamlit_app.py:91 waits on) - */
 B200_API int b200_submit(b200_engine* e, const int32_t* prompt_ids, size_t n, const b200_sampling* s,

@@ -90,6 +90,7 @@ def lib():
         "b200_tok_load_gguf": (i32, [C.c_char_p, C.POINTER(vp)]),
         "b200_tok_free": (None, [vp]),
         "b200_tok_encode": (i32, [vp, C.c_char_p, sz, i32, vp, sz, C.POINTER(sz)]),
+        "b200_pretokenize": (i32, [C.c_char_p, sz, vp, sz, C.POINTER(sz)]),
         "b200_tok_decode": (i32, [vp, vp, sz, vp, sz, C.POINTER(sz)]),
         "b200_submit": (i32, [vp, vp, sz, smpp, C.POINTER(vp)]),
         "b200_next": (i32, [vp, C.POINTER(C.c_int32), C.POINTER(i32), i32]),
@@ -254,6 +255,17 @@ def gguf_info(path):
     cfg, a, b, c = Config(), C.c_int64(), C.c_int64(), C.c_int64()
     _check(lib().b200_gguf_info(path.encode(), C.byref(cfg), C.byref(a), C.byref(b), C.byref(c)))
     return cfg, a.value, b.value, c.value
+
+
+def pretokenize(text):
+    """Pieces of the llama-bpe pre-tokeniser (a str in, list of str out); raw bytes are accepted too (list of bytes)."""
+    b = text.encode() if isinstance(text, str) else bytes(text)
+    ends = np.empty(len(b) + 1, np.int32)
+    n = C.c_size_t()
+    _check(lib().b200_pretokenize(b, len(b), _p(ends), ends.size, C.byref(n)))
+    cuts = [0] + ends[:n.value].tolist()
+    pieces = [b[cuts[i]:cuts[i + 1]] for i in range(n.value)]
+    return [p.decode() for p in pieces] if isinstance(text, str) else pieces
 
 
 class Tok:

@@ -354,6 +354,17 @@ int b200_tok_decode(const b200_tok* t, const int32_t* ids, size_t n, char* buf, 
   return tok_decode(h->tok, ids, n, buf, cap, n_out);
 }
 
+int b200_pretokenize(const char* utf8, size_t n, int32_t* ends, size_t cap, size_t* n_out) {
+  if ((!utf8 && n) || !n_out || (!ends && cap)) { set_error("null argument"); return B200_EINVAL; }
+  std::vector<std::string> words;
+  pretokenize(utf8, n, &words);
+  *n_out = words.size();
+  if (words.size() > cap) { set_error("output buffer too small (%zu pieces)", words.size()); return B200_EINVAL; }
+  size_t off = 0;
+  for (size_t i = 0; i < words.size(); ++i) { off += words[i].size(); ends[i] = (int32_t)off; }
+  return 0;
+}
+
 int b200_submit(b200_engine* h, const int32_t* prompt_ids, size_t n, const b200_sampling* s, b200_req** out) {
   Engine* e = reinterpret_cast<Engine*>(h);
   if (!e || !prompt_ids || !out || n == 0) { set_error("null/empty argument"); return B200_EINVAL; }

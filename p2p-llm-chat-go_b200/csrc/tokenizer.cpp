@@ -11,6 +11,7 @@
 
 #include "../../include/b200llm.h"
 #include "gguf.h"
+#include "unicode_tables.h"
 
 namespace b200 {
 void set_error(const char* fmt, ...);
@@ -54,10 +55,58 @@ bool unicode_token_to_bytes(const std::string& s, std::string* out) {
   return true;
 }
 
-inline bool is_letter(unsigned char c) { return (c >= 'a' && c <= 'z') || (c >= 'A' && c <= 'Z') || c >= 0x80; }
-inline bool is_digit(unsigned char c) { return c >= '0' && c <= '9'; }
-inline bool is_space(unsigned char c) { return c == ' ' || c == '\t' || c == '\n' || c == '\r' || c == '\v' || c == '\f'; }
-inline bool is_nl(unsigned char c) { return c == '\n' || c == '\r'; }
+// ---- code-point classes of the Llama-3 pre-tokeniser regex (what llama.cpp's unicode.cpp derives from its tables)
+bool in_ranges(const uint32_t (*r)[2], int n, uint32_t cp) {
+  int lo = 0, hi = n - 1;
+  while (lo <= hi) {
+    const int mid = (lo + hi) / 2;
+    if (cp < r[mid][0]) hi = mid - 1;
+    else if (cp > r[mid][1]) lo = mid + 1;
+    else return true;
+  }
+  return false;
+}
+inline bool is_letter(uint32_t c) {  // \p{L}
+  if (c < 0x80) return (c >= 'a' && c <= 'z') || (c >= 'A' && c <= 'Z');
+  return in_ranges(kUnicodeLetters, kUnicodeLetters_n, c);
+}
+inline bool is_digit(uint32_t c) {  // \p{N}
+  if (c < 0x80) return c >= '0' && c <= '9';
+  return in_ranges(kUnicodeNumbers, kUnicodeNumbers_n, c);
+}
+inline bool is_space(uint32_t c) {  // \s = White_Space
+  return (c >= 0x9 && c <= 0xD) || c == 0x20 || c == 0x85 || c == 0xA0 || c == 0x1680 || (c >= 0x2000 && c <= 0x200A) || c == 0x2028 ||
+         c == 0x2029 || c == 0x202F || c == 0x205F || c == 0x3000;
+}
+inline bool is_nl(uint32_t c) { return c == '\n' || c == '\r'; }
+// lower case for the (?i:...) contractions: ASCII, plus U+017F (long s), which case-folds to 's'
+inline uint32_t fold(uint32_t c) { return c == 0x17F ? 's' : ((c >= 'A' && c <= 'Z') ? c | 0x20 : c); }
+
+struct Cp {
+  uint32_t c;    // code point (0xFFFD class "other" for a byte that is not valid UTF-8)
+  uint32_t off;  // byte offset in the text
+};
+// UTF-8 -> code points with byte offsets; an invalid byte becomes its own symbol so that no input byte is lost
+void decode_utf8(const char* t, size_t n, std::vector<Cp>* out) {
+  size_t i = 0;
+  while (i < n) {
+    const unsigned char b = (unsigned char)t[i];
+    uint32_t c = 0xFFFD;
+    size_t len = 1;
+    auto cont = [&](size_t k) { return i + k < n && ((unsigned char)t[i + k] & 0xC0) == 0x80; };
+    if (b < 0x80) c = b;
+    else if ((b >> 5) == 6 && cont(1)) { c = ((b & 0x1Fu) << 6) | (t[i + 1] & 0x3F); len = 2; if (c < 0x80) { c = 0xFFFD; len = 1; } }
+    else if ((b >> 4) == 14 && cont(1) && cont(2)) {
+      c = ((b & 0x0Fu) << 12) | ((t[i + 1] & 0x3Fu) << 6) | (t[i + 2] & 0x3F); len = 3;
+      if (c < 0x800 || (c >= 0xD800 && c <= 0xDFFF)) { c = 0xFFFD; len = 1; }
+    } else if ((b >> 3) == 30 && cont(1) && cont(2) && cont(3)) {
+      c = ((b & 0x07u) << 18) | ((t[i + 1] & 0x3Fu) << 12) | ((t[i + 2] & 0x3Fu) << 6) | (t[i + 3] & 0x3F); len = 4;
+      if (c < 0x10000 || c > 0x10FFFF) { c = 0xFFFD; len = 1; }
+    }
+    out->push_back({c, (uint32_t)i});
+    i += len;
+  }
+}
 
 std::string merge_key(const std::string& a, const std::string& b) {
   std::string k;
@@ -72,52 +121,60 @@ std::string merge_key(const std::string& a, const std::string& b) {
 }  // namespace
 
 // (?i:'s|'t|'re|'ve|'m|'ll|'d) | [^\r\n\p{L}\p{N}]?\p{L}+ | \p{N}{1,3} | ?[^\s\p{L}\p{N}]+[\r\n]* | \s*[\r\n]+ | \s+(?!\S) | \s+
-void pretokenize(const char* t, size_t n, std::vector<std::string>* words) {
+// evaluated on code points, alternatives in order, each with the regex's greedy / back-tracking outcome
+void pretokenize(const char* t, size_t nbytes, std::vector<std::string>* words) {
+  std::vector<Cp> cp;
+  decode_utf8(t, nbytes, &cp);
+  const size_t n = cp.size();
+  auto C = [&](size_t k) { return cp[k].c; };
+  auto emit = [&](size_t i, size_t j) {  // code points [i, j)
+    const size_t b0 = cp[i].off, b1 = j < n ? cp[j].off : nbytes;
+    words->emplace_back(t + b0, b1 - b0);
+  };
   size_t i = 0;
-  auto U = [&](size_t k) { return (unsigned char)t[k]; };
   while (i < n) {
     size_t j = i;
     // contractions
-    if (U(i) == '\'' && i + 1 < n) {
-      const unsigned char a = U(i + 1) | 0x20, b = i + 2 < n ? (U(i + 2) | 0x20) : 0;
+    if (C(i) == '\'' && i + 1 < n) {
+      const uint32_t a = fold(C(i + 1)), b = i + 2 < n ? fold(C(i + 2)) : 0;
       size_t len = 0;
       if (a == 's' || a == 't' || a == 'm' || a == 'd') len = 2;
       if ((a == 'r' && b == 'e') || (a == 'v' && b == 'e') || (a == 'l' && b == 'l')) len = 3;
-      if (len) { words->emplace_back(t + i, len); i += len; continue; }
+      if (len) { emit(i, i + len); i += len; continue; }
     }
-    // optional single non-letter/digit/newline char, then letters
+    // optional single char that is no letter / number / newline, then letters
     {
       size_t k = i;
-      if (!is_letter(U(k)) && !is_digit(U(k)) && !is_nl(U(k)) && k + 1 < n && is_letter(U(k + 1))) ++k;
-      if (is_letter(U(k))) {
+      if (!is_letter(C(k)) && !is_digit(C(k)) && !is_nl(C(k)) && k + 1 < n && is_letter(C(k + 1))) ++k;
+      if (is_letter(C(k))) {
         j = k;
-        while (j < n && is_letter(U(j))) ++j;
-        words->emplace_back(t + i, j - i); i = j; continue;
+        while (j < n && is_letter(C(j))) ++j;
+        emit(i, j); i = j; continue;
       }
     }
-    if (is_digit(U(i))) {
-      while (j < n && j - i < 3 && is_digit(U(j))) ++j;
-      words->emplace_back(t + i, j - i); i = j; continue;
+    if (is_digit(C(i))) {
+      while (j < n && j - i < 3 && is_digit(C(j))) ++j;
+      emit(i, j); i = j; continue;
     }
-    {  // optional space, punctuation run, trailing newlines
+    {  // optional space, run of "other" characters, trailing newlines
       size_t k = i;
-      if (U(k) == ' ' && k + 1 < n && !is_space(U(k + 1)) && !is_letter(U(k + 1)) && !is_digit(U(k + 1))) ++k;
-      if (!is_space(U(k)) && !is_letter(U(k)) && !is_digit(U(k))) {
+      if (C(k) == ' ' && k + 1 < n && !is_space(C(k + 1)) && !is_letter(C(k + 1)) && !is_digit(C(k + 1))) ++k;
+      if (!is_space(C(k)) && !is_letter(C(k)) && !is_digit(C(k))) {
         j = k;
-        while (j < n && !is_space(U(j)) && !is_letter(U(j)) && !is_digit(U(j))) ++j;
-        while (j < n && is_nl(U(j))) ++j;
-        words->emplace_back(t + i, j - i); i = j; continue;
+        while (j < n && !is_space(C(j)) && !is_letter(C(j)) && !is_digit(C(j))) ++j;
+        while (j < n && is_nl(C(j))) ++j;
+        emit(i, j); i = j; continue;
       }
     }
     // whitespace
-    while (j < n && is_space(U(j))) ++j;
+    while (j < n && is_space(C(j))) ++j;
     size_t last_nl = 0;
     bool has_nl = false;
     for (size_t k = i; k < j; ++k)
-      if (is_nl(U(k))) { has_nl = true; last_nl = k; }
-    if (has_nl) { words->emplace_back(t + i, last_nl + 1 - i); i = last_nl + 1; continue; }  // \s*[\r\n]+
+      if (is_nl(C(k))) { has_nl = true; last_nl = k; }
+    if (has_nl) { emit(i, last_nl + 1); i = last_nl + 1; continue; }  // \s*[\r\n]+
     if (j < n && j - i > 1) --j;  // \s+(?!\S): leave the last space to the following word
-    words->emplace_back(t + i, j - i);
+    emit(i, j);
     i = j;
   }
 }
