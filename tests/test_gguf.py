@@ -127,6 +127,39 @@ def test_bpe_tokenizer_matches_reference_bpe(pkg, model_file):
     assert tok.decode([toks.index("<|eot_id|>"), ord("A")]) == "A"                          # specials render as nothing
 
 
+def test_corrupt_files_are_rejected_not_crashed(pkg, model_file, tmp_path):
+    """Model files are untrusted input: truncations and random byte / length-field damage in the metadata must come
+    back as an error code (or parse, if the damage was harmless), never as a crash or a hang."""
+    import random
+    data = open(model_file[0], "rb").read()
+    hdr_end = data.find(b"tokenizer.ggml.merges") + 4096
+    head = data[:hdr_end + (1 << 16)]           # metadata + the start of the tensor data: cheap to rewrite 150 times
+    rng = random.Random(3)
+    p2 = str(tmp_path / "c.gguf")
+    clean = 0
+    for it in range(150):
+        b = bytearray(head)
+        mode = it % 4
+        if mode == 0:
+            b = b[:rng.randint(0, hdr_end)]
+        elif mode == 1:
+            for _ in range(rng.randint(1, 8)):
+                b[rng.randint(0, hdr_end - 1)] = rng.randint(0, 255)
+        elif mode == 2:
+            pos = rng.randint(0, hdr_end - 9)
+            b[pos:pos + 8] = rng.choice([0, 1, 2**31, 2**63 - 1, 2**64 - 1, 2**40]).to_bytes(8, "little")
+        else:
+            pos = rng.randint(0, hdr_end - 5)
+            b[pos:pos + 4] = rng.choice([0, 9, 13, 255, 2**32 - 1]).to_bytes(4, "little")
+        open(p2, "wb").write(bytes(b))
+        for fn in (lambda: pkg.gguf_info(p2), lambda: pkg.Tok(p2).encode("hello wörld 123")):
+            try:
+                fn()
+            except pkg.B200Error:
+                clean += 1
+    assert clean >= 150        # every file here is at least truncated: gguf_info must have refused each one
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("fmt", [0, 1])
 def test_load_gguf_and_match_oracle(pkg, tmp_path, fmt):
