@@ -401,6 +401,8 @@ int main() {
     const int fd = accept(ls, nullptr, nullptr);
     if (fd < 0) continue;
     setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof one);
+    timeval tv = {30, 0};  // a client that stops sending mid-request must not pin a thread for ever
+    setsockopt(fd, SOL_SOCKET, SO_RCVTIMEO, &tv, sizeof tv);
     std::thread(serve, fd).detach();
   }
 }

@@ -144,3 +144,36 @@ def test_metrics_endpoint_counts_requests(server):
     assert after["llmd_generated_tokens_total"] >= before["llmd_generated_tokens_total"] + 1
     assert after["llmd_prompt_tokens_total"] > before["llmd_prompt_tokens_total"]
     assert after["llmd_requests_in_flight"] == 0 and after["llmd_generation_seconds_total"] >= before["llmd_generation_seconds_total"]
+
+
+def test_malformed_requests_do_not_take_the_server_down(server):
+    """Untrusted network input: broken request lines, wrong lengths, invalid JSON, absurd options.  Each gets an error
+    reply or a closed connection; afterwards the server still serves the reference's request."""
+    host, port = server.replace("http://", "").split(":")
+    raw_cases = [
+        b"", b"\r\n\r\n", b"GARBAGE\r\n\r\n", b"POST /api/generate HTTP/1.1\r\nContent-Length: 999999999999\r\n\r\n{}",
+        b"POST /api/generate HTTP/1.1\r\nContent-Length: -5\r\n\r\n{}", b"POST /api/generate HTTP/1.1\r\nContent-Length: 10\r\n\r\n{",
+        b"POST /api/generate HTTP/1.1\r\n" + b"X: " + b"a" * 100000 + b"\r\n\r\n", b"GET /" + b"a" * 70000 + b" HTTP/1.1\r\n\r\n",
+        b"POST /api/generate HTTP/1.1\r\nContent-Length: 7\r\n\r\n[[[[[[[", b"\x00\xff\xfe" * 100,
+    ]
+    for raw in raw_cases:
+        s = socket.create_connection((host, int(port)), timeout=5)
+        try:
+            s.sendall(raw)
+            s.settimeout(2)
+            try:
+                s.recv(4096)
+            except (socket.timeout, ConnectionError):
+                pass
+        finally:
+            s.close()
+    bad_bodies = ["{", "[]", "null", '{"model":5}', '{"model":"llama3.1"}', '{"model":"llama3.1","prompt":5,"options":"x"}',
+                  '{"model":"llama3.1","prompt":"x","options":{"num_predict":-7,"top_k":-1,"temperature":-3,"top_p":7,"repeat_last_n":99999999}}',
+                  '{"model":"llama3.1","messages":"nope"}', '{"model":"llama3.1","prompt":"' + "z" * 5000 + '"}']
+    for b in bad_bodies:
+        for path in ("/api/generate", "/api/chat"):
+            r = requests.post(server + path, data=b, headers={"Content-Type": "application/json"}, timeout=60)
+            assert r.status_code in (200, 400, 404, 500), (b[:40], r.status_code)
+    ok = requests.post(f"{server}/api/generate", json={"model": "llama3.1", "prompt": "still there?", "stream": False,
+                                                        "options": {"num_predict": 4}}, timeout=60)
+    assert ok.status_code == 200 and ok.json()["done"] is True
