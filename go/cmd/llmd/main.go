@@ -416,5 +416,7 @@ func main() {
 
 	addr := getenv("LLMD_ADDR", getenv("OLLAMA_HOST", "127.0.0.1:11434"))
 	log.Printf("llmd: %s serving model '%s' on %s", C.GoString(C.b200_version()), model, addr)
-	log.Fatal(http.ListenAndServe(addr, mux))
+	// a client that stops sending mid-request must not pin a goroutine for ever (no WriteTimeout: replies stream)
+	srv := &http.Server{Addr: addr, Handler: mux, ReadHeaderTimeout: 30 * time.Second, ReadTimeout: 30 * time.Second}
+	log.Fatal(srv.ListenAndServe())
 }
