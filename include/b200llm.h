@@ -160,6 +160,12 @@ B200_API void b200_free(b200_req* r);
 /* ---- test / parity hooks (host buffers in, host buffers out; each runs the production kernel) ------- */
 /* Teacher-forced logits of the LAST position after running `n` tokens from an empty context. */
 B200_API int b200_forward_logits(b200_engine* e, const int32_t* ids, size_t n, int mode, float* logits);
+/* Teacher-forced logits along a given continuation: the prompt runs in `prefill_mode`, then forced[k] is fed at
+ * position n_prompt + k through the batch-1 decode step (GEMV numerics) regardless of the model's own pick.
+ * logits: (n_forced + 1) rows of `vocab` floats — row 0 after the prompt, row k + 1 after forced[k].  This is how the
+ * parity test follows the CPU reference's 128 greedy tokens (BASELINE.json north_star) step by step. */
+B200_API int b200_forward_logits_forced(b200_engine* e, const int32_t* prompt, size_t n_prompt, int prefill_mode,
+                                        const int32_t* forced, size_t n_forced, float* logits);
 /* Greedy generation with device-timed phases; fills ids[n_new]; ttft_ms/decode_ms may be NULL. */
 B200_API int b200_generate_greedy(b200_engine* e, const int32_t* prompt, size_t n_prompt, int32_t* ids,
                                   size_t n_new, int prefill_mode, float* ttft_ms, float* decode_ms);

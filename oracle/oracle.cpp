@@ -310,18 +310,35 @@ void matmul(int wtype, const void* W, int64_t rows, int64_t cols, const float* X
       dequant_row(wtype, row, cols, wrow.data());
       if (mode == 1 && quant)
         for (int64_t k = 0; k < cols; ++k) wrow[k] = bf16_round(wrow[k]);
-      for (int t = 0; t < n; ++t) {
-        const float* x = Xin + (size_t)t * cols;
-        double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-        int64_t k = 0;
-        for (; k + 3 < cols; k += 4) {
-          a0 += (double)(wrow[k + 0] * x[k + 0]);
-          a1 += (double)(wrow[k + 1] * x[k + 1]);
-          a2 += (double)(wrow[k + 2] * x[k + 2]);
-          a3 += (double)(wrow[k + 3] * x[k + 3]);
+      // fp32 products, double accumulation.  The reduction clause lets the compiler keep one partial sum per vector
+      // lane (the order of a double sum of fp32 products moves the result by ~1e-16 relative: far below fp32);
+      // four tokens per pass share the loads of the weight row.
+      const float* wr = wrow.data();
+      int t = 0;
+      for (; t + 3 < n; t += 4) {
+        const float* x0 = Xin + (size_t)t * cols;
+        const float* x1 = x0 + cols;
+        const float* x2 = x1 + cols;
+        const float* x3 = x2 + cols;
+        double s0 = 0, s1 = 0, s2 = 0, s3 = 0;
+#pragma omp simd reduction(+ : s0, s1, s2, s3)
+        for (int64_t k = 0; k < cols; ++k) {
+          s0 += (double)(wr[k] * x0[k]);
+          s1 += (double)(wr[k] * x1[k]);
+          s2 += (double)(wr[k] * x2[k]);
+          s3 += (double)(wr[k] * x3[k]);
         }
-        for (; k < cols; ++k) a0 += (double)(wrow[k] * x[k]);
-        Y[(size_t)t * ldy + r] = (float)((a0 + a1) + (a2 + a3));
+        Y[(size_t)t * ldy + r] = (float)s0;
+        Y[(size_t)(t + 1) * ldy + r] = (float)s1;
+        Y[(size_t)(t + 2) * ldy + r] = (float)s2;
+        Y[(size_t)(t + 3) * ldy + r] = (float)s3;
+      }
+      for (; t < n; ++t) {
+        const float* x = Xin + (size_t)t * cols;
+        double s0 = 0;
+#pragma omp simd reduction(+ : s0)
+        for (int64_t k = 0; k < cols; ++k) s0 += (double)(wr[k] * x[k]);
+        Y[(size_t)t * ldy + r] = (float)s0;
       }
     }
   }

@@ -98,6 +98,7 @@ def lib():
         "b200_cancel": (None, [vp]),
         "b200_free": (None, [vp]),
         "b200_forward_logits": (i32, [vp, vp, sz, i32, vp]),
+        "b200_forward_logits_forced": (i32, [vp, vp, sz, i32, vp, sz, vp]),
         "b200_generate_greedy": (i32, [vp, vp, sz, vp, sz, i32, C.POINTER(f32), C.POINTER(f32)]),
         "b200_dequant": (i32, [i32, vp, i64, vp]),
         "b200_quant_q16": (i32, [vp, i64, vp, vp]),
@@ -390,6 +391,13 @@ class Engine:
         ids = _c(ids, np.int32)
         out = np.empty(self.cfg.vocab, np.float32)
         _check(lib().b200_forward_logits(self.h, _p(ids), ids.size, mode, _p(out)))
+        return out
+
+    def forward_logits_forced(self, prompt, forced, prefill_mode=MODE_GEMM):
+        """Logits [len(forced) + 1, vocab]: row 0 after the prompt, row k + 1 after forced[k] was fed (teacher forcing)."""
+        prompt, forced = _c(prompt, np.int32), _c(forced, np.int32)
+        out = np.empty((forced.size + 1, self.cfg.vocab), np.float32)
+        _check(lib().b200_forward_logits_forced(self.h, _p(prompt), prompt.size, prefill_mode, _p(forced), forced.size, _p(out)))
         return out
 
     def generate_greedy(self, prompt, n_new, prefill_mode=MODE_GEMM):

@@ -162,6 +162,12 @@ int b200_set_tensor(b200_engine* h, const char* name, int type, const void* data
               (long long)s.full_cols, type, (long long)rows, (long long)cols);
     return B200_EINVAL;
   }
+  for (auto& q : e->seqs)
+    if (q.r) { set_error("b200_set_tensor: the engine is serving requests"); return B200_ESTATE; }
+  {
+    std::lock_guard<std::mutex> ql(e->qmu);
+    if (!e->queue.empty()) { set_error("b200_set_tensor: the engine is serving requests"); return B200_ESTATE; }
+  }
   B200_CUDA(cudaSetDevice(e->cfg.device));
   // the caller always passes the FULL tensor; a tensor-parallel rank keeps its window of it
   const size_t bytes = (size_t)s.full_rows * (s.type == T_F32 ? (size_t)s.full_cols * 4 : gemv_row_bytes(s.type, s.full_cols));
@@ -170,6 +176,7 @@ int b200_set_tensor(b200_engine* h, const char* name, int type, const void* data
   if (rc) return rc;
   B200_CUDA(cudaMemcpyAsync(tmp.p, data, bytes, cudaMemcpyHostToDevice, e->stream));
   if ((rc = e->place_tensor(s, tmp.as<uint8_t>()))) return rc;
+  if ((rc = e->refresh_shadow(name))) return rc;  // k-quant models: the tensor-core path's bf16 copy follows
   B200_CUDA(cudaStreamSynchronize(e->stream));
   s.set = true;
   return 0;
@@ -212,6 +219,13 @@ int b200_get_tensor(b200_engine* h, const char* name, void* buf, int64_t cap) {
 int64_t b200_weight_bytes(const b200_engine* h) { return h ? reinterpret_cast<const Engine*>(h)->weight_bytes : 0; }
 
 static int tok_encode(const Tokenizer& tk, int32_t vocab, const char* utf8, size_t n, int add_bos, int32_t* ids, size_t cap, size_t* n_out) {
+  // n bytes cannot become fewer than n / (longest token) ids: refuse texts that cannot fit `cap` before spending
+  // time on them (a front end passes cap = max_ctx, so an oversized body is rejected without being tokenised)
+  if (cap > 0 && n / tk.max_token_bytes() > cap) {
+    *n_out = n / tk.max_token_bytes();
+    set_error("tokenize: %zu bytes of text cannot fit %zu ids", n, cap);
+    return B200_ERANGE;
+  }
   std::vector<int32_t> v;
   tk.encode(utf8, n, add_bos != 0, vocab, &v);
   *n_out = v.size();
@@ -445,6 +459,15 @@ int b200_forward_logits(b200_engine* h, const int32_t* ids, size_t n, int mode, 
   return e->forward_logits(ids, (int)n, mode, logits);
 }
 
+int b200_forward_logits_forced(b200_engine* h, const int32_t* prompt, size_t n_prompt, int prefill_mode, const int32_t* forced, size_t n_forced,
+                               float* logits) {
+  Engine* e = reinterpret_cast<Engine*>(h);
+  if (!e || !prompt || !logits || n_prompt == 0 || (n_forced && !forced)) { set_error("null/empty argument"); return B200_EINVAL; }
+  std::lock_guard<std::mutex> lk(e->mu);
+  B200_CUDA(cudaSetDevice(e->cfg.device));
+  return e->forward_logits_forced(prompt, (int)n_prompt, prefill_mode, forced, (int)n_forced, logits);
+}
+
 int b200_generate_greedy(b200_engine* h, const int32_t* prompt, size_t n_prompt, int32_t* ids, size_t n_new, int prefill_mode,
                          float* ttft_ms, float* decode_ms) {
   Engine* e = reinterpret_cast<Engine*>(h);
@@ -536,6 +559,8 @@ int b200_attn_decode(const float* q, const float* k, const float* v, int n_ctx, 
 
 int b200_attn_decode_noalloc(const float* q_dev, const uint16_t* k_cache_dev, const uint16_t* v_cache_dev, const int32_t* block_table_dev,
                              int n_ctx, int n_heads, int n_kv_heads, float* out_dev, void* stream) {
+  int rc0 = have_device();
+  if (rc0) return rc0;
   if (!q_dev || !k_cache_dev || !v_cache_dev || !block_table_dev || !out_dev) { set_error("null argument"); return B200_EINVAL; }
   if (n_heads > attn_noalloc_max_heads()) {
     set_error("b200_attn_decode_noalloc: n_heads=%d exceeds the built-in scratch (B200_NOALLOC_MAX_HEADS=%d); use b200_attn_decode",

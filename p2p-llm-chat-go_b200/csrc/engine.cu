@@ -718,11 +718,95 @@ int Engine::forward_logits(const int32_t* ids, int n, int mode, float* logits_ho
   return 0;
 }
 
+// Teacher-forced decode (parity hook): the prompt goes through `prefill_mode`, then forced[k] is fed at position
+// n_prompt + k through the batch-1 decode step whatever the model itself would have picked.  logits_host receives
+// n_forced + 1 rows of `vocab` floats: row 0 after the prompt, row k + 1 after forced[k].
+int Engine::forward_logits_forced(const int32_t* prompt, int n_prompt, int prefill_mode, const int32_t* forced, int n_forced,
+                                  float* logits_host) {
+  int rc = claim_slot0(this);
+  if (rc) return rc;
+  if (tp_size > 1) { set_error("forward_logits_forced: single-GPU engines only"); return B200_ESTATE; }
+  for (int k = 0; k < n_forced; ++k)
+    if (forced[k] < 0 || forced[k] >= cfg.vocab) { set_error("token id %d out of range", forced[k]); return B200_EINVAL; }
+  if ((rc = ensure_graph())) return rc;
+  if ((rc = run_prompt(prompt, n_prompt, n_forced + 1, 1, prefill_mode))) return rc;
+  const size_t row = (size_t)cfg.vocab;
+  B200_CUDA(cudaMemcpyAsync(logits_host, logits, row * 4, cudaMemcpyDeviceToHost, stream));
+  for (int k = 0; k < n_forced; ++k) {
+    // the step about to run processes position n_prompt + k: replace the token the model picked for it
+    B200_CUDA(cudaMemcpyAsync(&st->cur_token, forced + k, 4, cudaMemcpyHostToDevice, stream));
+    B200_CUDA(cudaMemcpyAsync(prompt_dev + n_prompt + k, forced + k, 4, cudaMemcpyHostToDevice, stream));
+    B200_CUDA(launch_embed(token_embd, embd_type, cfg.d_model, &st->cur_token, x, stream));
+    if ((rc = launch_steps(1))) return rc;
+    B200_CUDA(cudaMemcpyAsync(logits_host + (size_t)(k + 1) * row, logits, row * 4, cudaMemcpyDeviceToHost, stream));
+  }
+  B200_CUDA(cudaStreamSynchronize(stream));
+  return mega_check_error();
+}
+
 }  // namespace b200
 
 // ------------------------------------------------------------------------------------------------------
 // Prefill on the tensor cores (GEMM numerics, oracle mode 1).
 namespace b200 {
+
+// bf16 shadow (tensor-core operand) of one GGUF-named matrix, rebuilt from the tensor as it is stored now.
+// Called for every matrix when the shadows are first built and again whenever b200_set_tensor replaces a tensor
+// afterwards, so the GEMM path never runs on stale weights.  No-op for names without a shadow.
+int Engine::refresh_shadow(const std::string& name) {
+  if (!has_shadows) return 0;
+  const b200_config& c = lc;
+  const int qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim;
+  auto it = slots.find(name);
+  if (it == slots.end()) return 0;
+  const Slot& s = it->second;
+  uint16_t* base = nullptr;
+  int64_t row0 = 0, step = 1;
+  if (name == "output.weight") {
+    if (!output16 || output_type == T_BF16) return 0;
+    base = output16;
+  } else if (name.compare(0, 4, "blk.") == 0) {
+    const size_t dot = name.find('.', 4);
+    if (dot == std::string::npos) return 0;
+    const int l = atoi(name.c_str() + 4);
+    if (l < 0 || l >= (int)layers.size()) return 0;
+    Layer& L = layers[l];
+    const std::string t = name.substr(dot + 1);
+    if (t == "attn_q.weight") { base = L.qkv16; }
+    else if (t == "attn_k.weight") { base = L.qkv16; row0 = qd; }
+    else if (t == "attn_v.weight") { base = L.qkv16; row0 = qd + kvd; }
+    else if (t == "attn_output.weight") { base = L.o16; }
+    else if (t == "ffn_gate.weight") { base = L.gu16; step = 2; }
+    else if (t == "ffn_up.weight") { base = L.gu16; row0 = 1; step = 2; }
+    else if (t == "ffn_down.weight") { base = L.down16; }
+    else return 0;
+  } else {
+    return 0;
+  }
+  if (!base) return 0;
+  int rc;
+  if (name == "output.weight") {  // larger than the per-layer staging buffers: its own temporary
+    const size_t bytes = (size_t)s.rows * gemv_row_bytes(s.type, s.cols);
+    uint8_t* tmp = nullptr;
+    B200_CUDA(cudaMalloc((void**)&tmp, bytes));
+    rc = fetch_tensor(s, tmp);
+    cudaError_t e = rc ? cudaSuccess : launch_dequant(s.type, tmp, s.rows * s.cols / QK_K, nullptr, output16, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    cudaFree(tmp);
+    if (rc) return rc;
+    return e == cudaSuccess ? 0 : cuda_fail(e, "lm_head shadow");
+  }
+  if (!shadow_tmp) return 0;  // all-bf16 layers: the "shadows" are the GEMV buffers themselves
+  if ((rc = fetch_tensor(s, shadow_tmp))) return rc;  // GGUF block order
+  const uint16_t* src16 = (const uint16_t*)shadow_tmp;  // bf16 tensors are copied as they are
+  if (s.type != T_BF16) {
+    B200_CUDA(launch_dequant(s.type, shadow_tmp, s.rows * s.cols / QK_K, nullptr, shadow_tmp16, stream));
+    src16 = shadow_tmp16;
+  }
+  B200_CUDA(cudaMemcpy2DAsync(base + (size_t)row0 * s.cols, (size_t)step * s.cols * 2, src16, (size_t)s.cols * 2, (size_t)s.cols * 2,
+                              (size_t)s.rows, cudaMemcpyDeviceToDevice, stream));
+  return 0;
+}
 
 int Engine::ensure_prefill() {
   if (pf_ready) return 0;
@@ -738,30 +822,17 @@ int Engine::ensure_prefill() {
   if (q4) {
     size_t maxb = 0;
     for (auto& kv : slots) maxb = std::max(maxb, (size_t)kv.second.rows * tensor_row_bytes(kv.second.type, kv.second.cols));
-    uint8_t* tmp = nullptr;
-    uint16_t* tmp16 = nullptr;
-    if ((rc = alloc((void**)&tmp, maxb)) || (rc = alloc((void**)&tmp16, (size_t)2 * ff * std::max(d, qd) * 2 + (size_t)d * ff * 2))) return rc;
+    if ((rc = alloc((void**)&shadow_tmp, maxb)) || (rc = alloc((void**)&shadow_tmp16, (size_t)2 * ff * std::max(d, qd) * 2 + (size_t)d * ff * 2))) return rc;
     for (int l = 0; l < c.n_layers; ++l) {
       Layer& L = layers[l];
       if ((rc = alloc((void**)&L.qkv16, (size_t)(qd + 2 * kvd) * d * 2)) || (rc = alloc((void**)&L.o16, (size_t)d * qd * 2)) ||
           (rc = alloc((void**)&L.gu16, (size_t)2 * ff * d * 2)) || (rc = alloc((void**)&L.down16, (size_t)d * ff * 2)))
         return rc;
-      const std::string p = "blk." + std::to_string(l) + ".";
-      struct Dst { const char* name; uint16_t* base; int64_t row0, step; };
-      const Dst dsts[] = {{"attn_q", L.qkv16, 0, 1}, {"attn_k", L.qkv16, qd, 1}, {"attn_v", L.qkv16, qd + kvd, 1}, {"attn_output", L.o16, 0, 1},
-                          {"ffn_gate", L.gu16, 0, 2}, {"ffn_up", L.gu16, 1, 2}, {"ffn_down", L.down16, 0, 1}};
-      for (const Dst& t : dsts) {
-        const Slot& s = slots[p + t.name + ".weight"];
-        if ((rc = fetch_tensor(s, tmp))) return rc;  // GGUF block order
-        const uint16_t* src16 = (const uint16_t*)tmp;  // bf16 tensors are copied as they are
-        if (s.type != T_BF16) {
-          B200_CUDA(launch_dequant(s.type, tmp, s.rows * s.cols / QK_K, nullptr, tmp16, stream));
-          src16 = tmp16;
-        }
-        B200_CUDA(cudaMemcpy2DAsync(t.base + (size_t)t.row0 * s.cols, (size_t)t.step * s.cols * 2, src16, (size_t)s.cols * 2,
-                                    (size_t)s.cols * 2, (size_t)s.rows, cudaMemcpyDeviceToDevice, stream));
-      }
     }
+    has_shadows = true;
+    for (int l = 0; l < c.n_layers; ++l)
+      for (const char* t : {"attn_q", "attn_k", "attn_v", "attn_output", "ffn_gate", "ffn_up", "ffn_down"})
+        if ((rc = refresh_shadow("blk." + std::to_string(l) + "." + t + ".weight"))) return rc;
     B200_CUDA(cudaStreamSynchronize(stream));
   } else {
     for (auto& L : layers) {

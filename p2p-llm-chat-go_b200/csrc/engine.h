@@ -151,6 +151,7 @@ struct Engine {
   int bs1_owner = -1;               // slot whose state currently lives in StepState / prompt_dev
   bool force_batched = false;       // cfg.reserved bit 0: never use the batch-1 path for decode (tests)
   bool batched_ready = false;
+  bool can_batch() const { return tp_size == 1 && cfg.max_seqs > 1; }  // may the scheduler run batched steps at all
   int32_t *b_tok = nullptr, *b_pos = nullptr, *b_ctx = nullptr, *b_slot = nullptr, *b_next = nullptr;  // device [max_seqs]
   int32_t* b_next_host = nullptr;   // pinned
   int32_t* hist_dev = nullptr;      // [max_seqs][max_ctx] token history per slot
@@ -203,7 +204,12 @@ struct Engine {
   int generate_greedy(const int32_t* prompt, int n_prompt, int32_t* ids, int n_new, int prefill_mode, float* ttft_ms,
                       float* decode_ms);
   int forward_logits(const int32_t* ids, int n, int mode, float* logits_host);
+  int forward_logits_forced(const int32_t* prompt, int n_prompt, int prefill_mode, const int32_t* forced, int n_forced, float* logits_host);
   int ensure_prefill();                      // shadow weights + work buffers of the GEMM path
+  int refresh_shadow(const std::string& name);  // re-derive the bf16 shadow of one tensor (after b200_set_tensor)
+  bool has_shadows = false;                  // k-quant model whose bf16 shadows have been built
+  uint8_t* shadow_tmp = nullptr;             // staging of refresh_shadow (largest per-layer tensor, GGUF layout)
+  uint16_t* shadow_tmp16 = nullptr;
   int prefill_gemm(int n_prompt);            // prompt_dev[0..n) -> KV cache, residual of the last position, first token
   // the tensor-core layer stack over n rows: one sequence at positions 0..n-1 (arrays null) or one row per sequence
   int forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_arr, const int32_t* ctx_arr, const int32_t* slot_arr);

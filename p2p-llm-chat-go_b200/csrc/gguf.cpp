@@ -116,8 +116,11 @@ std::string GgufFile::open(const std::string& path) {
     if (!c.ok || nd > 4) return "corrupt GGUF tensor info";
     int64_t n = 1;
     for (uint32_t d = 0; d < nd; ++d) {
-      t.ne.push_back((int64_t)c.get<uint64_t>());
-      n *= t.ne.back();
+      const uint64_t dim = c.get<uint64_t>();
+      // element counts beyond 2^40 cannot be real (and would overflow the product / the byte size)
+      if (!c.ok || dim > (1ull << 40) || (dim != 0 && (uint64_t)n > (1ull << 40) / dim)) return "corrupt GGUF tensor info (dimensions)";
+      t.ne.push_back((int64_t)dim);
+      n *= (int64_t)dim;
     }
     t.type = c.get<uint32_t>();
     t.offset = c.get<uint64_t>();
@@ -125,11 +128,15 @@ std::string GgufFile::open(const std::string& path) {
     if (!c.ok) return "corrupt GGUF tensor info";
   }
   const uint64_t align = get_u("general.alignment", 32);
+  if (align == 0 || (align & (align - 1)) != 0 || align > (1u << 20)) return "corrupt GGUF header (general.alignment must be a power of two)";
   const uint64_t pos = (uint64_t)(c.p - base_);
   data_off_ = (pos + align - 1) / align * align;
+  if (data_off_ > size_) data_off_ = size_;
   for (size_t i = 0; i < tensors_.size(); ++i) {
     const GgufTensor& t = tensors_[i];
-    if (t.nbytes && data_off_ + t.offset + t.nbytes > size_) return "tensor '" + t.name + "' runs past the end of the file";
+    // written so that a huge offset cannot wrap the sum around
+    const uint64_t room = size_ - data_off_;
+    if (t.nbytes && (t.offset > room || t.nbytes > room - t.offset)) return "tensor '" + t.name + "' runs past the end of the file";
     index_[t.name] = i;
   }
   return "";

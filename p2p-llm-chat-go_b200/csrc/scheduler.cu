@@ -41,14 +41,9 @@ int Engine::ensure_batched() {
   B200_CUDA(cudaHostAlloc((void**)&b_next_host, S * 4, cudaHostAllocDefault));
   if (output_type != T_BF16) {  // bf16 shadow of a k-quant lm_head
     const Slot& s = slots["output.weight"];
-    const size_t bytes = (size_t)s.rows * gemv_row_bytes(s.type, s.cols);
-    uint8_t* tmp = nullptr;
-    B200_CUDA(cudaMalloc((void**)&tmp, bytes));
-    if ((rc = alloc((void**)&output16, (size_t)s.rows * s.cols * 2)) || (rc = fetch_tensor(s, tmp))) { cudaFree(tmp); return rc; }
-    cudaError_t e = launch_dequant(s.type, tmp, s.rows * s.cols / QK_K, nullptr, output16, stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
-    cudaFree(tmp);
-    if (e != cudaSuccess) return cuda_fail(e, "lm_head shadow");
+    if ((rc = alloc((void**)&output16, (size_t)s.rows * s.cols * 2))) return rc;
+    has_shadows = true;
+    if ((rc = refresh_shadow("output.weight"))) return rc;
   } else {
     output16 = (uint16_t*)output;
   }
@@ -256,8 +251,10 @@ int Engine::decode_bs1_window(int slot) {
       return 0;
     }
     if (!interrupted) {
+      // a waiting request interrupts the window only if the batched path can take both (can_batch); otherwise
+      // this sequence runs to its end on the batch-1 graph and the queue is served afterwards
       std::lock_guard<std::mutex> lk(qmu);
-      interrupted = !queue.empty() || stopping;
+      interrupted = (can_batch() && !queue.empty()) || stopping;
     }
     if (interrupted) {  // drain what is in flight, then let the scheduler batch
       if (launched == q.delivered) {
@@ -334,7 +331,10 @@ void Engine::worker_loop() {
       std::lock_guard<std::mutex> lk(qmu);
       waiting = !queue.empty();
     }
-    if (active.size() == 1 && !waiting && !force_batched) {
+    // The batched step needs its own state (ensure_batched: per-slot history and sampling options) and is not
+    // tensor-parallel aware: engines with one slot, and TP engines (SPMD, one request at a time), stay on the
+    // batch-1 graph whatever is waiting.
+    if (active.size() == 1 && (!can_batch() || (!waiting && !force_batched))) {
       const int rc = decode_bs1_window(active[0]);
       if (rc && seqs[active[0]].r) finish_request(active[0], rc, 3);
       continue;

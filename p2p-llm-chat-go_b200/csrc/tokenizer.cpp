@@ -7,7 +7,9 @@
 #include "tokenizer.h"
 
 #include <cstdio>
+#include <algorithm>
 #include <cstring>
+#include <queue>
 
 #include "../../include/b200llm.h"
 #include "gguf.h"
@@ -194,6 +196,7 @@ std::string Tokenizer::load(const GgufFile& f) {
     if (tt == 1 && unicode_token_to_bytes(toks->strs[i], &raw)) {  // normal token
       id_to_bytes_[i] = raw;
       bytes_to_id_.emplace(raw, (int32_t)i);
+      max_token_bytes_ = std::max(max_token_bytes_, raw.size());
     } else {
       is_special_[i] = 1;  // control / user-defined / unused: never produced by encode, rendered as nothing
     }
@@ -213,25 +216,52 @@ std::string Tokenizer::load(const GgufFile& f) {
   return "";
 }
 
+// One pre-token -> ids.  As llama.cpp does for "llama-bpe" (ignore_merges) and tiktoken does by construction, a
+// pre-token that is itself a vocabulary entry is emitted as that id without consulting the merge table.  Otherwise
+// the classic BPE loop — merge the adjacent pair of lowest rank, leftmost on ties, until no pair has a rank — run
+// over a linked list of symbols with a priority queue of candidate pairs: O(n log n) per word instead of a full
+// rescan per merge (a \p{L}+ run can be arbitrarily long).
 void Tokenizer::bpe_word(const std::string& w, std::vector<int32_t>* out) const {
-  std::vector<std::string> sym;
-  for (char c : w) sym.emplace_back(1, c);
-  while (sym.size() > 1) {
-    int best = -1, best_rank = 0x7fffffff;
-    for (size_t i = 0; i + 1 < sym.size(); ++i) {
-      auto it = merge_rank_.find(merge_key(sym[i], sym[i + 1]));
-      if (it != merge_rank_.end() && it->second < best_rank) { best_rank = it->second; best = (int)i; }
-    }
-    if (best < 0) break;
-    sym[best] += sym[best + 1];
-    sym.erase(sym.begin() + best + 1);
+  if (w.empty()) return;
+  {
+    auto whole = bytes_to_id_.find(w);
+    if (whole != bytes_to_id_.end()) { out->push_back(whole->second); return; }
   }
-  for (const std::string& s : sym) {
+  struct Sym { int prev, next; uint32_t off, len; };
+  struct Pair { int32_t rank; int left, right; uint32_t llen, rlen; };
+  struct Later {  // priority_queue keeps the "largest": lowest rank first, then the leftmost pair
+    bool operator()(const Pair& a, const Pair& b) const { return a.rank > b.rank || (a.rank == b.rank && a.left > b.left); }
+  };
+  const int n = (int)w.size();
+  std::vector<Sym> sym((size_t)n);
+  for (int i = 0; i < n; ++i) sym[i] = {i - 1, i + 1 < n ? i + 1 : -1, (uint32_t)i, 1u};
+  std::priority_queue<Pair, std::vector<Pair>, Later> pq;
+  auto push = [&](int l, int r) {
+    if (l < 0 || r < 0) return;
+    auto it = merge_rank_.find(merge_key(w.substr(sym[l].off, sym[l].len), w.substr(sym[r].off, sym[r].len)));
+    if (it != merge_rank_.end()) pq.push({it->second, l, r, sym[l].len, sym[r].len});
+  };
+  for (int i = 0; i + 1 < n; ++i) push(i, i + 1);
+  while (!pq.empty()) {
+    const Pair p = pq.top();
+    pq.pop();
+    Sym& L = sym[p.left];
+    Sym& R = sym[p.right];
+    if (L.len != p.llen || R.len != p.rlen || L.next != p.right) continue;  // one side has changed since: stale
+    L.len += R.len;  // symbols are contiguous in w, so the merged symbol is [L.off, L.off + L.len)
+    R.len = 0;
+    L.next = R.next;
+    if (R.next >= 0) sym[R.next].prev = p.left;
+    push(L.prev, p.left);
+    push(p.left, L.next);
+  }
+  for (int i = 0; i >= 0; i = sym[i].next) {
+    const std::string s = w.substr(sym[i].off, sym[i].len);
     auto it = bytes_to_id_.find(s);
     if (it != bytes_to_id_.end()) { out->push_back(it->second); continue; }
     for (char c : s) {  // a merge produced a string that is not a token: fall back to its bytes
-      auto b = bytes_to_id_.find(std::string(1, c));
-      if (b != bytes_to_id_.end()) out->push_back(b->second);
+      auto b2 = bytes_to_id_.find(std::string(1, c));
+      if (b2 != bytes_to_id_.end()) out->push_back(b2->second);
     }
   }
 }

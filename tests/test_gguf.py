@@ -28,16 +28,23 @@ MERGES = [(b"h", b"e"), (b"l", b"l"), (b"he", b"ll"), (b"hell", b"o"), (b" ", b"
           (b" worl", b"d"), (b"1", b"2"), (b"12", b"3"), (b"\xc3", b"\xa9"), (b" ", b"t"), (b" t", b"h"), (b" th", b"e")]
 
 
+WHOLE_WORD = b" xyzzy"
+
+
 def vocab():
     toks = [U(bytes([b])) for b in range(256)]
     for a, b in MERGES:
         toks.append(U(a + b))
+    toks.append(U(WHOLE_WORD))       # in the vocabulary, but no sequence of merges builds it
     toks += ["<|begin_of_text|>", "<|eot_id|>"]
     types = [1] * (len(toks) - 2) + [3, 3]
     return toks, types, [f"{U(a)} {U(b)}" for a, b in MERGES]
 
 
-def py_bpe(word, ranks, tok_id):
+def py_bpe(word, ranks, tok_id, ignore_merges=True):
+    """Textbook BPE; ignore_merges (llama.cpp's setting for llama-bpe): a word that is a token is that token."""
+    if ignore_merges and word in tok_id:
+        return [tok_id[word]]
     sym = [bytes([b]) for b in word]
     while len(sym) > 1:
         best = min(((ranks.get((sym[i], sym[i + 1]), 1 << 30), i) for i in range(len(sym) - 1)))
@@ -120,11 +127,69 @@ def test_bpe_tokenizer_matches_reference_bpe(pkg, model_file):
     assert tok.encode("hello world") == [tok_id[b"hello"], tok_id[b" world"]]
     assert tok.encode("hello") == py_bpe(b"hello", ranks, tok_id)
     assert tok.encode("123456") == [tok_id[b"123"]] + py_bpe(b"456", ranks, tok_id)      # digits split in threes
-    assert tok.encode("the the") == py_bpe(b"the", ranks, tok_id) + py_bpe(b" the", ranks, tok_id)  # lowest rank first: (h,e) wins
+    # " the" is a vocabulary entry: emitted whole (plain BPE would give " t" + "he" because (h,e) has the lowest rank)
+    assert tok.encode("the the") == py_bpe(b"the", ranks, tok_id) + [tok_id[b" the"]]
+    assert py_bpe(b" the", ranks, tok_id, ignore_merges=False) == [tok_id[b" t"], tok_id[b"he"]]
+    assert tok.encode(" thel") == [tok_id[b" t"], tok_id[b"he"], ord("l")]                 # not a token: lowest rank first
     for text in ["hello world", "café 中文!", "it's  1234\n\nnew  line ", "", "a\tb"]:
         assert tok.decode(tok.encode(text)) == text                                        # lossless round trip
     assert tok.encode("x", add_bos=True)[0] == toks.index("<|begin_of_text|>")
     assert tok.decode([toks.index("<|eot_id|>"), ord("A")]) == "A"                          # specials render as nothing
+
+
+def test_bpe_whole_word_lookup_and_long_words(pkg, model_file):
+    """(1) llama-bpe's ignore_merges: a pre-token that is a vocabulary entry is that id, whatever the merge table says
+    (llama.cpp sets ignore_merges for this pre-tokeniser; tiktoken behaves the same).  (2) The merge loop is a
+    priority-queue walk: it must give what the textbook loop gives on words with many competing merges, and a
+    pathological 200k-letter "word" must tokenise in well under a second per 100k letters."""
+    import random
+    import time
+    tok = pkg.Tok(model_file[0])
+    toks, _, _ = vocab()
+    assert tok.encode("a xyzzy") == [ord("a"), toks.index(U(WHOLE_WORD))]
+    assert tok.encode(" xyzz") == [ord(c) for c in " xyzz"]            # its prefixes are not reachable by merges
+    tok_id = {bytes([b]): b for b in range(256)}
+    for i, (a, b) in enumerate(MERGES):
+        tok_id[a + b] = 256 + i
+    ranks = {m: i for i, m in enumerate(MERGES)}
+    rng = random.Random(1)
+    for _ in range(300):
+        word = "".join(rng.choice("helowrdt") for _ in range(rng.randint(1, 40)))
+        assert tok.encode(word) == py_bpe(word.encode(), ranks, tok_id), word
+        assert tok.encode(" " + word) == py_bpe(b" " + word.encode(), ranks, tok_id), word
+    long_word = "hello" * 40000
+    t0 = time.perf_counter()
+    ids = tok.encode(long_word)
+    assert time.perf_counter() - t0 < 5.0
+    assert ids == [tok_id[b"hello"]] * 40000
+
+
+def _mini_gguf(alignment=32, dims=(256,), ttype=0, offset=0, payload=2048):
+    """A hand-packed GGUF v3 file: two metadata keys and one tensor directory entry."""
+    import struct
+    def s(x):
+        return struct.pack("<Q", len(x)) + x
+    b = b"GGUF" + struct.pack("<IQQ", 3, 1, 2)
+    b += s(b"general.architecture") + struct.pack("<I", 8) + s(b"llama")
+    b += s(b"general.alignment") + struct.pack("<II", 4, alignment)
+    b += s(b"token_embd.weight") + struct.pack("<I", len(dims)) + b"".join(struct.pack("<Q", d) for d in dims)
+    b += struct.pack("<IQ", ttype, offset)
+    return b + b"\0" * payload
+
+
+@pytest.mark.parametrize("kw", [dict(alignment=0), dict(alignment=24), dict(offset=2**64 - 64), dict(offset=2**63),
+                                dict(dims=(2**62, 2**62)), dict(dims=(2**33, 2**33, 2**33)), dict(dims=(2**64 - 1,))])
+def test_crafted_headers_are_refused(pkg, tmp_path, kw):
+    """Header values a fuzzer finds first: alignment 0 (division by zero), an offset that wraps the bounds check
+    around 2^64, dimension products that overflow int64.  Each must be an error return, not a signal."""
+    p = str(tmp_path / "m.gguf")
+    open(p, "wb").write(_mini_gguf(**kw))
+    with pytest.raises(pkg.B200Error):
+        pkg.gguf_info(p)
+    # and the same file with sane values is read as far as the reader goes (it then lacks llama.* keys / tensors)
+    open(p, "wb").write(_mini_gguf())
+    with pytest.raises(pkg.B200Error, match="attn_q"):
+        pkg.gguf_info(p)
 
 
 def test_corrupt_files_are_rejected_not_crashed(pkg, model_file, tmp_path):

@@ -149,3 +149,54 @@ def test_bench_batched_hook_is_deterministic(pkg):
     assert ms > 0 and ((0 <= ids) & (ids < 1024)).all()
     assert len(set(ids.tolist())) == 1
     assert run()[1].tolist() == ids.tolist()
+
+
+def test_one_slot_engine_serves_queued_sampled_requests_like_solo_runs(pkg):
+    """An engine with a single sequence slot (LLMD_MAX_SEQS=1) never has the batched path's per-slot state: a
+    request that finds another one waiting behind it must keep decoding on the batch-1 graph, with its own sampling
+    options, exactly as if it were alone.  Two sampled requests queued back to back == the same two run one by one."""
+    cfg = tiny_cfg(pkg, 0, n_layers=2, seed=77, max_ctx=128)
+    cfg.max_seqs = 1
+    prompts = [np.random.default_rng(s).integers(0, cfg.vocab, n).astype(np.int32) for s, n in ((1, 9), (2, 14))]
+
+    def sampling(i):
+        s = pkg.default_sampling()                     # temperature 0.8, top_k 40, top_p 0.9, repeat penalty 1.1
+        s.num_predict, s.seed, s.prefill_mode = 24, 1000 + i, pkg.MODE_GEMM
+        return s
+    with pkg.Engine(cfg) as eng:
+        solo = []
+        for i, p in enumerate(prompts):
+            r = eng.submit(p, sampling(i))
+            solo.append(list(r.tokens()))
+            r.free()
+        reqs = [eng.submit(p, sampling(i)) for i, p in enumerate(prompts)]   # the second waits while the first decodes
+        both = [list(r.tokens()) for r in reqs]
+        [r.free() for r in reqs]
+    assert both == solo
+    assert len(set(solo[0])) > 4                       # really sampled, not a constant
+
+
+def test_set_tensor_after_a_gemm_forward_refreshes_the_tensor_core_copy(pkg):
+    """k-quant engines keep bf16 copies of the matrices for the tensor-core path.  Replacing a tensor after those
+    copies exist must reach both paths: set -> GEMM forward -> set again -> GEMM forward == oracle with the new tensor."""
+    from tests.util import random_tensor
+    eng, ora, cfg = engine_and_oracle(pkg, 1, n_layers=2, seed=78, source="synth", max_ctx=128)
+    with eng:
+        toks = np.random.default_rng(5).integers(0, cfg.vocab, 40).astype(np.int32)
+        before = eng.forward_logits(toks, pkg.MODE_GEMM)          # builds the bf16 shadows
+        rng = np.random.default_rng(6)
+        for name in ("blk.0.ffn_up.weight", "blk.1.attn_v.weight", "blk.1.attn_output.weight"):
+            t, r, c, _ = eng.tensor_info(name)
+            arr = random_tensor(rng, t, r, c)
+            eng.set_tensor(name, t, arr, r, c)
+            ora.set_tensor(name, t, arr, r, c)
+        after = eng.forward_logits(toks, pkg.MODE_GEMM)
+        ora.reset()
+        want = ora.forward(toks, mode=1)
+        assert np.abs(after - want).max() <= TOL * max(1.0, np.abs(want).max())
+        assert np.abs(after - before).max() > 10 * TOL             # the replacement really changed the model
+        gemv = eng.forward_logits(toks, pkg.MODE_GEMV)             # and the decode path sees the same new weights
+        ora.reset()
+        for tk in toks:
+            want0 = ora.forward([tk], mode=0)
+        assert np.abs(gemv - want0).max() <= 1e-3 * max(1.0, np.abs(want0).max())

@@ -231,3 +231,62 @@ def test_full_size_8b_greedy_prefix(pkg):
     if not indecisive.size:
         assert ids.tolist() == want.tolist()
     assert stop >= 4, margins  # the check must actually cover some tokens
+
+
+# ---- parity at the BASELINE config (BASELINE.json configs[1] / configs[2]) ---------------------------------
+def bench_prompt(n, vocab_text=128000, seed=1):
+    """The 512-token synthetic chat-history prompt bench.py times (same generator, same seed)."""
+    return np.random.default_rng(seed).integers(0, vocab_text, n).astype(np.int32)
+
+
+@pytest.mark.parametrize("fmt", [0, 1])
+def test_full_size_8b_512_prompt_128_tokens(pkg, fmt, record_property):
+    """north_star: "greedy decodes must produce an identical first 128 tokens", on the configuration the bench is
+    quoted on: Llama-3.1-8B shape (random-init), the bench's 512-token prompt through the tcgen05 prefill (numerics
+    mode 1), then 128 greedy tokens on the batch-1 decode path (mode 0); bf16 and Q4_K_M.
+
+    The CPU oracle generates its 128 tokens; the engine is then teacher-forced along exactly that continuation
+    (b200_forward_logits_forced), so its logits can be compared at EVERY step, also past a near-tie:
+      * logits within PREFILL_LOGIT_TOL x max|logit| at each of the 128 steps;
+      * the engine's argmax equals the oracle's token at every DECISIVE step (oracle top-1/top-2 margin above 4x the
+        tolerance; random-init logits are flat, so some steps are ties either side may break either way);
+      * the free-running greedy decode (b200_generate_greedy) is identical up to the first indecisive step.
+    The number of decisive steps is reported (record_property + stdout) and must cover most of the 128."""
+    cfg = pkg.llama31_8b()
+    cfg.weight_format, cfg.seed, cfg.max_ctx, cfg.eos_token = fmt, 0, 768, -1
+    n_prompt, n_new = 512, 128
+    with pkg.Engine(cfg) as eng:
+        ora = oracle_from_engine(eng)
+        prompt = bench_prompt(n_prompt)
+        # CPU reference: prefill in mode 1, then token by token in mode 0, keeping every logits row
+        ora.reset()
+        rows = [ora.forward(prompt, mode=1)]
+        want = []
+        for k in range(n_new):
+            tok, _ = orc.argmax(rows[-1])
+            want.append(tok)
+            if k + 1 < n_new:
+                rows.append(ora.forward([tok], mode=0))
+        want = np.array(want, np.int32)
+        ref = np.stack(rows)                                   # [128, vocab]
+        srt = np.sort(ref, axis=1)
+        margins = srt[:, -1] - srt[:, -2]
+        scale = np.abs(ref).max(axis=1)
+        got = eng.forward_logits_forced(prompt, want[:-1], pkg.MODE_GEMM)
+        err = np.abs(got - ref).max(axis=1)
+        assert (err <= PREFILL_LOGIT_TOL * np.maximum(1.0, scale)).all(), (fmt, err.max(), err.argmax(), scale.min())
+        tol_abs = PREFILL_LOGIT_TOL * np.maximum(1.0, scale)
+        decisive = margins > 4 * tol_abs
+        eng_tok = got.argmax(axis=1)
+        assert (eng_tok[decisive] == want[decisive]).all(), (fmt, np.nonzero(eng_tok != want)[0], margins[eng_tok != want])
+        ids, ttft, _ = eng.generate_greedy(prompt, n_new, pkg.MODE_GEMM)
+        first_tie = int(np.nonzero(~decisive)[0][0]) if (~decisive).any() else n_new
+        assert ids[:first_tie].tolist() == want[:first_tie].tolist(), (fmt, ids[:8], want[:8])
+        same = int((ids == want).sum())
+        n_dec = int(decisive.sum())
+        msg = (f"fmt={fmt}: {n_dec}/{n_new} steps decisive (margin > 4 x {PREFILL_LOGIT_TOL} x |logit|max), "
+               f"forced argmax equal on {int((eng_tok == want).sum())}/{n_new}, free-running equal on {same}/{n_new}, "
+               f"max logit err {err.max():.2e} (|logit|max {scale.max():.2f}), min margin {margins.min():.2e}")
+        print("\nPARITY8B " + msg)
+        record_property("parity8b", msg)
+        assert n_dec >= n_new // 2, msg

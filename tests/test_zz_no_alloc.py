@@ -7,8 +7,9 @@ pointers for everything and keeps its scratch in a fixed array inside libb200llm
 
 The file is named so that pytest collects it last: a run that stops at the first failure has then already
 executed every other test.  It passes alone in a fresh process and after the other GPU tests.
-Checked here, through the C ABI: same output as the existing entry point (b200_attn_decode) within the
-attention tolerance the other tests use, on two calls in a row (the second call finds the previous call's
+Checked here, through the C ABI: same output as the existing entry point (b200_attn_decode) AND as the CPU oracle's
+attention (so the check is not CUDA against CUDA only), within the attention tolerance the other tests use, on two
+calls in a row (the second call finds the previous call's
 partials in the shared scratch and must not be disturbed by them), and sizes beyond the built-in maximum are
 refused with a clear error.
 """
@@ -70,6 +71,8 @@ def test_noalloc_matches_existing_entry_point_twice(pkg, n_ctx, n_heads, n_kv):
         got = out.cpu().numpy()
         assert np.isfinite(got).all()
         assert np.abs(got - want).max() <= ATTN_TOL * max(1.0, np.abs(want).max()), (call, n_ctx, n_heads, n_kv)
+        ref = orc.attention(q, K, V, n_heads, n_kv, 128)  # the CPU restatement, same bf16-representable K / V
+        assert np.abs(got - ref).max() <= ATTN_TOL * max(1.0, np.abs(ref).max()), (call, n_ctx, n_heads, n_kv)
         results.append(got)
     assert not np.array_equal(results[0], results[1])  # the two calls really computed different problems
 
