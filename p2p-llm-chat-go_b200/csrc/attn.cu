@@ -26,6 +26,179 @@ __global__ void __launch_bounds__(128) attn_decode_kernel(const AttnArgs a) {
   attn_decode_item<G>(a, sm, blockIdx.x, blockIdx.y, gridDim.y, blockIdx.z, gridDim.x, threadIdx.x, 0);
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Batch-1 decode step variant: the same split-KV work division, with everything that does not depend on the
+// kernel before it (the qkv projection of this layer) moved in front of griddepcontrol.wait.  Under
+// programmatic dependent launch these CTAs (128 threads, ~21 KB of shared memory) become resident next to the
+// still-running projection kernel, so by the time the query vector exists the K / V rows of the context are
+// already in shared memory: block-table look-up and the HBM round trip of the gather (~2.5 us) leave the
+// critical path.  Only the row of the current position — written by that projection — is fetched after the wait.
+//
+// K tile layout: [32 tokens][16 chunks of 16 B], chunk c of token t stored at chunk (c ^ (t & 7)): 16-byte
+// cp.async fills it, and lane = token reads whole chunks (LDS.128) without bank conflicts.
+template <int G>
+struct AttnFastSmem {
+  alignas(16) uint16_t Ks[kTile * kHeadDim];
+  alignas(16) uint16_t Vs[kTile * kHeadDim];
+  alignas(16) float qs[G * kHeadDim];
+  float P[G][kTile];
+  float m_run[G], l_run[G], corr_s[G];
+  int s_last;
+};
+
+DEVINL void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+DEVINL void cp_async_commit_wait_all() {
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
+template <int G>
+__global__ void __launch_bounds__(128) attn_decode_fast_kernel(const AttnArgs a) {
+  __shared__ AttnFastSmem<G> sm;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int kvh = blockIdx.x, split = blockIdx.y, S = gridDim.y;
+  const uint32_t ks_s = smem_u32(sm.Ks), vs_s = smem_u32(sm.Vs);
+  // rows [row_lo, row_hi) of tile `tile` -> shared memory (thread = 16-byte chunk; 4 chunks of K and of V each)
+  auto gather = [&](int tile, int row_lo, int row_hi) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int item = tid + 128 * j, t = item >> 4, c = item & 15;
+      const int tok = tile * kTile + t;
+      if (tok >= row_lo && tok < row_hi) {
+        const int page = a.block_table[tok / kPageTokens];
+        const size_t row = (((size_t)page * a.n_kv_heads + kvh) * kPageTokens + (tok % kPageTokens)) * kHeadDim;
+        cp_async16(ks_s + (uint32_t)(t * kHeadDim * 2 + ((c ^ (t & 7)) << 4)), a.k_cache + row + c * 8);
+        cp_async16(vs_s + (uint32_t)(t * kHeadDim * 2 + (c << 4)), a.v_cache + row + c * 8);
+      }
+    }
+  };
+  // ---- before the dependency: the first tile of this split, every token the cache has room for (rows at or
+  // beyond the current position hold older data; they are masked below, and the current row is re-fetched)
+  gather(split, 0, a.prefetch_tokens);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  if (tid < G) {
+    sm.m_run[tid] = -INFINITY;
+    sm.l_run[tid] = 0.f;
+  }
+  pdl_wait();
+  pdl_launch_dependents();
+  const int pos = a.fixed_ctx > 0 ? a.fixed_ctx - 1 : a.st->pos;
+  const int ctx = pos + 1;
+  const float scale = 1.0f / sqrtf((float)kHeadDim);
+  for (int i = tid; i < G * kHeadDim / 4; i += 128)
+    reinterpret_cast<float4*>(sm.qs)[i] = __ldcg(reinterpret_cast<const float4*>(a.q + (size_t)kvh * G * kHeadDim) + i);
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();  // the prefetched rows have landed before the current row is written over its stale copy
+  {
+    const int lo = pos > a.prefetch_tokens ? a.prefetch_tokens : pos;  // rows not covered by the prefetch, and `pos`
+    gather(split, lo, ctx);
+    cp_async_commit_wait_all();
+  }
+  float acc[G];
+#pragma unroll
+  for (int h = 0; h < G; ++h) acc[h] = 0.f;
+  __syncthreads();
+
+  for (int tile = split; tile * kTile < ctx; tile += S) {
+    const int t0 = tile * kTile;
+    if (tile != split) {  // contexts beyond 32 * n_splits tokens: further tiles, fetched in place
+      gather(tile, 0, ctx);
+      cp_async_commit_wait_all();
+      __syncthreads();
+    }
+    const int n_valid = ctx - t0 < kTile ? ctx - t0 : kTile;
+    for (int h = warp; h < G; h += 4) {  // scores + online softmax: one head per warp, lane = token
+      const uint4* kr = reinterpret_cast<const uint4*>(sm.Ks + lane * kHeadDim);
+      const float4* qh = reinterpret_cast<const float4*>(sm.qs + h * kHeadDim);
+      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+      for (int c = 0; c < 16; ++c) {
+        const uint4 k = kr[c ^ (lane & 7)];
+        const float4 qa = qh[2 * c], qb = qh[2 * c + 1];
+        s0 = fmaf(qa.x, bf16lo(k.x), s0);
+        s1 = fmaf(qa.y, bf16hi(k.x), s1);
+        s2 = fmaf(qa.z, bf16lo(k.y), s2);
+        s3 = fmaf(qa.w, bf16hi(k.y), s3);
+        s0 = fmaf(qb.x, bf16lo(k.z), s0);
+        s1 = fmaf(qb.y, bf16hi(k.z), s1);
+        s2 = fmaf(qb.z, bf16lo(k.w), s2);
+        s3 = fmaf(qb.w, bf16hi(k.w), s3);
+      }
+      float sc = (s0 + s1) + (s2 + s3);
+      const bool valid = lane < n_valid;
+      sc = valid ? sc * scale : -INFINITY;
+      const float m_old = sm.m_run[h];
+      const float m_new = fmaxf(m_old, warp_max(sc));
+      const float p = valid ? expf(sc - m_new) : 0.f;
+      const float l_tile = warp_sum(p);
+      sm.P[h][lane] = p;
+      if (lane == 0) {
+        const float corr = (m_old == -INFINITY) ? 0.f : expf(m_old - m_new);
+        sm.corr_s[h] = corr;
+        sm.l_run[h] = sm.l_run[h] * corr + l_tile;
+        sm.m_run[h] = m_new;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int h = 0; h < G; ++h) acc[h] *= sm.corr_s[h];
+    for (int t = 0; t < n_valid; ++t) {  // P.V: thread = output dim; rows past the context are never touched
+      const float v = __uint_as_float((uint32_t)sm.Vs[t * kHeadDim + tid] << 16);
+#pragma unroll
+      for (int h = 0; h < G; ++h) acc[h] = fmaf(sm.P[h][t], v, acc[h]);
+    }
+    __syncthreads();
+  }
+
+  // ---- split merge: as in attn_decode_item (partials in scratch, the last CTA of a KV head combines them)
+  float* part = a.partial + ((size_t)kvh * S + split) * G * kPart;
+#pragma unroll
+  for (int h = 0; h < G; ++h) part[h * kPart + tid] = acc[h];
+  if (tid < G) {
+    part[tid * kPart + kHeadDim] = sm.m_run[tid];
+    part[tid * kPart + kHeadDim + 1] = sm.l_run[tid];
+  }
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) sm.s_last = (atomicAdd(a.counters + kvh, 1u) == (unsigned)(S - 1));
+  __syncthreads();
+  if (!sm.s_last) return;
+  __threadfence();
+  const float* base = a.partial + (size_t)kvh * S * G * kPart;
+  float* w_s = reinterpret_cast<float*>(sm.Ks);  // [G][kMaxSplits]
+  for (int h = warp; h < G; h += 4) {
+    const bool on = lane < S;
+    const float* ps = base + ((size_t)(on ? lane : 0) * G + h) * kPart;
+    const float ms = on ? __ldcg(ps + kHeadDim) : -INFINITY;
+    const float ls = on ? __ldcg(ps + kHeadDim + 1) : 0.f;
+    const float M = warp_max(ms);
+    const float w = (ms == -INFINITY) ? 0.f : expf(ms - M);
+    const float den = warp_sum(ls * w);
+    w_s[h * kMaxSplits + lane] = w;
+    if (lane == 0) sm.corr_s[h] = 1.0f / den;
+  }
+  __syncthreads();
+  float num[G];
+#pragma unroll
+  for (int h = 0; h < G; ++h) num[h] = 0.f;
+  for (int sp = 0; sp < S; sp += 4) {
+    float p[4][G];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int h = 0; h < G; ++h) p[u][h] = (sp + u < S) ? __ldcg(base + ((size_t)(sp + u) * G + h) * kPart + tid) : 0.f;
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int h = 0; h < G; ++h) num[h] = fmaf(p[u][h], (sp + u < S) ? w_s[h * kMaxSplits + sp + u] : 0.f, num[h]);
+  }
+#pragma unroll
+  for (int h = 0; h < G; ++h) a.out[((size_t)kvh * G + h) * kHeadDim + tid] = num[h] * sm.corr_s[h];
+  if (tid == 0) a.counters[kvh] = 0u;
+}
+
 }  // namespace
 
 size_t attn_partial_floats(int n_heads, int n_kv_heads, int n_splits) {
@@ -43,6 +216,16 @@ cudaError_t launch_attn_decode(const AttnArgs& a, cudaStream_t s, bool pdl) {
   at[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
   cfg.numAttrs = pdl ? 1 : 0;
+  // the batch-1 decode step (one query, the engine's own block table, cache rows readable ahead of the dependency)
+  if (a.prefetch_tokens > 0 && a.n_queries <= 1 && !a.q_ctx && !a.q_slot) {
+    switch (a.n_heads / a.n_kv_heads) {
+      case 1: return cudaLaunchKernelEx(&cfg, attn_decode_fast_kernel<1>, a);
+      case 2: return cudaLaunchKernelEx(&cfg, attn_decode_fast_kernel<2>, a);
+      case 4: return cudaLaunchKernelEx(&cfg, attn_decode_fast_kernel<4>, a);
+      case 8: return cudaLaunchKernelEx(&cfg, attn_decode_fast_kernel<8>, a);
+    }
+    return cudaErrorInvalidValue;
+  }
   switch (a.n_heads / a.n_kv_heads) {
     case 1: return cudaLaunchKernelEx(&cfg, attn_decode_kernel<1>, a);
     case 2: return cudaLaunchKernelEx(&cfg, attn_decode_kernel<2>, a);

@@ -1,5 +1,5 @@
-// attn_decode.cuh — the split-KV decode attention work item (see attn.cu), shared by the stand-alone kernel
-// and the persistent decode kernel (decode_mega.cu).
+// attn_decode.cuh — the split-KV decode attention work item (see attn.cu), used by the stand-alone kernel
+// (a persistent-kernel experiment that also used it now lives in scratch/decode_mega.cu).
 #pragma once
 #include "common.cuh"
 #include "kernels.h"

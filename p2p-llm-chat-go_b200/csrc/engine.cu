@@ -87,9 +87,7 @@ int Engine::init(const b200_config& c, const void* nccl_id) {
   use_graph = getenv("B200_NO_GRAPH") == nullptr;
   use_fa_prefill = getenv("B200_NO_FA_PREFILL") == nullptr;
   use_mma_decode = getenv("B200_NO_MMA_DECODE") == nullptr;
-  // measured on B200 (round 1): the persistent kernel is bit-identical but SLOWER than the PDL-chained kernels
-  // (bf16 3.79 vs 3.01 ms/token, Q4_K_M 2.71 vs 1.73): see decode_mega.cu; opt-in for experiments
-  use_mega = getenv("B200_MEGA") != nullptr;
+  use_attn_prefetch = getenv("B200_NO_ATTN_PREFETCH") == nullptr;
   // measured on B200 (round 1): chaining L2 prefetches of the next kernel's weights made the step SLOWER
   // (bf16 3.18 vs 3.05 ms, Q4_K_M 1.84 vs 1.78 ms), so it is opt-in for experiments only
   use_l2_chain = getenv("B200_L2_CHAIN") != nullptr;
@@ -393,121 +391,11 @@ int Engine::enqueue_tail(cudaStream_t s, bool pdl, int* n, bool consume_tp, bool
   return 0;
 }
 
-// Phase table of the persistent decode kernel: the same projections with the same arguments as enqueue_step
-// below (single GPU only).  Leaves mega_ready false — and the per-projection kernels in charge — when a shape
-// is not supported.
-int Engine::ensure_mega() {
-  if (mega_ready || !use_mega || tp_size > 1) return 0;
-  const b200_config& c = lc;
-  const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn;
-  const int G = c.n_heads / c.n_kv_heads;
-  if (G != 1 && G != 2 && G != 4 && G != 8) { use_mega = false; return 0; }
-  int S = sm_count / c.n_kv_heads;
-  if (S > n_splits) S = n_splits;  // the split scratch is sized for n_splits
-  if (S < 1) { use_mega = false; return 0; }
-  std::vector<MegaPhase> ph;
-  auto add_gemv = [&](int wtype, int pro, int epi, const GemvArgs& g) {
-    MegaPhase p = {};
-    if (!mega_plan_gemv(wtype, g.N, g.K, sm_count, &p)) return false;
-    p.pro = pro; p.epi = epi; p.g = g;
-    ph.push_back(p);
-    return true;
-  };
-  bool ok = true;
-  for (int l = 0; l < c.n_layers && ok; ++l) {
-    Layer& L = layers[l];
-    GemvArgs a = {};
-    a.W = L.qkv; a.N = L.v ? qd + kvd : qd + 2 * kvd; a.K = d; a.x = x; a.norm_w = L.attn_norm; a.eps = c.rms_eps; a.y = q;
-    a.row_base = 0; a.q_rows = qd; a.kv_rows = kvd; a.n_kv_heads = c.n_kv_heads; a.rope = rope;
-    a.k_cache = L.k_cache; a.v_cache = L.v_cache; a.block_table = active_table; a.st = st;
-    ok = ok && add_gemv(L.qkv_type, PRO_RMSNORM, EPI_QKV, a);
-    if (L.v) {
-      a.W = L.v; a.N = kvd; a.row_base = qd + kvd;
-      ok = ok && add_gemv(L.v_type, PRO_RMSNORM, EPI_QKV, a);
-    }
-    MegaPhase at = {};
-    at.kind = 1;
-    at.t.q = q; at.t.k_cache = L.k_cache; at.t.v_cache = L.v_cache; at.t.block_table = active_table; at.t.st = st;
-    at.t.n_heads = c.n_heads; at.t.n_kv_heads = c.n_kv_heads; at.t.out = att; at.t.partial = attn_partial; at.t.counters = attn_counters;
-    at.t.n_splits = S; at.t.fixed_ctx = 0;
-    ph.push_back(at);
-    GemvArgs o = {};
-    o.W = L.o; o.N = d; o.K = qd; o.x = att; o.y = x;
-    ok = ok && add_gemv(L.o_type, PRO_COPY, EPI_RESID, o);
-    GemvArgs g = {};
-    g.W = L.gate_up; g.N = 2 * ff; g.K = d; g.x = x; g.norm_w = L.ffn_norm; g.eps = c.rms_eps; g.y = h;
-    ok = ok && add_gemv(L.gu_type, PRO_RMSNORM, EPI_SWIGLU, g);
-    GemvArgs dn = {};
-    dn.W = L.down; dn.N = d; dn.K = ff; dn.x = h; dn.y = x;
-    ok = ok && add_gemv(L.down_type, PRO_COPY, EPI_RESID, dn);
-  }
-  if (ok) {
-    GemvArgs lm;
-    int pro;
-    lm_head_args(&lm, &pro, false);
-    ok = add_gemv(output_type, pro, EPI_LOGITS, lm);
-  }
-  const size_t xb = ok ? mega_x_bytes(ph.data(), (int)ph.size(), G) : 0;
-  if (!ok || xb == 0 || xb + 16 * 2 * 4608 + 1024 > 227 * 1024) { use_mega = false; return 0; }
-  int rc;
-  if ((rc = alloc((void**)&mega_phases, ph.size() * sizeof(MegaPhase))) || (rc = alloc((void**)&mega_sync, 16))) return rc;
-  B200_CUDA(cudaMemcpy(mega_phases, ph.data(), ph.size() * sizeof(MegaPhase), cudaMemcpyHostToDevice));
-  B200_CUDA(cudaMemset(mega_sync, 0, 16));
-  mega.phases = mega_phases; mega.n_phases = (int)ph.size(); mega.lm_head_phase = (int)ph.size() - 1; mega.st = st;
-  mega.bar_count = mega_sync; mega.bar_gen = mega_sync + 1; mega.error = mega_sync + 2;
-  mega.attn_splits = S; mega.x_bytes = (int)xb;
-  if (getenv("B200_MEGA_TRACE")) {
-    if ((rc = alloc((void**)&mega_trace, ph.size() * (32 + 160 * 8)))) return rc;
-    B200_CUDA(cudaMemset(mega_trace, 0, ph.size() * (32 + 160 * 8)));
-    mega.trace = mega_trace;
-  }
-  mega_group = G;
-  mega_ready = true;
-  return 0;
-}
-
-// debug: the last step's per-phase time stamps of CTA 0 -> "<phase> <kind> <fmt> <epi> t0 t1 t2 t3" lines
-int Engine::dump_mega_trace() {
-  const char* path = getenv("B200_MEGA_TRACE");
-  if (!mega_trace || !path) return 0;
-  std::vector<unsigned long long> t((size_t)mega.n_phases * 164);
-  std::vector<MegaPhase> ph((size_t)mega.n_phases);
-  B200_CUDA(cudaMemcpy(t.data(), mega_trace, t.size() * 8, cudaMemcpyDeviceToHost));
-  B200_CUDA(cudaMemcpy(ph.data(), mega_phases, ph.size() * sizeof(MegaPhase), cudaMemcpyDeviceToHost));
-  FILE* f = fopen(path, "w");
-  if (!f) return 0;
-  for (int i = 0; i < mega.n_phases; ++i)
-  {
-    fprintf(f, "%d %d %d %d %llu %llu %llu %llu", i, ph[i].kind, ph[i].fmt, ph[i].epi, t[4 * i], t[4 * i + 1], t[4 * i + 2], t[4 * i + 3]);
-    for (int k = 0; k < 160; ++k) fprintf(f, " %llu", t[(size_t)mega.n_phases * 4 + (size_t)i * 160 + k]);
-    fprintf(f, "\n");
-  }
-  fclose(f);
-  return 0;
-}
-
-int Engine::mega_check_error() {
-  if (!mega_ready) return 0;
-  unsigned int flag = 0;
-  B200_CUDA(cudaMemcpy(&flag, mega_sync + 2, 4, cudaMemcpyDeviceToHost));
-  if (!flag) return 0;
-  B200_CUDA(cudaMemset(mega_sync, 0, 16));
-  set_error("persistent decode kernel: a wait timed out (results of that step are void)");
-  return B200_ECUDA;
-}
-
 int Engine::enqueue_step(cudaStream_t s) {
   const b200_config& c = lc;  // per-rank shapes (== cfg without tensor parallelism)
   const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn;
   const bool tp = tp_size > 1;
   int n = 0;
-  if (mega_ready) {  // layers + lm_head in one cooperative launch, then the sampler and the token hand-over
-    B200_CUDA(launch_decode_mega(mega, mega_group, sm_count, s)); ++n;
-    int rc = enqueue_tail(s, false, &n, false, false);
-    if (rc) return rc;
-    launches_per_step = n;
-    return 0;
-  }
   for (int l = 0; l < c.n_layers; ++l) {
     Layer& L = layers[l];
     // fused all-reduce: residual buffers alternate, all-reduce i is consumed from xbuf[i&1] into xbuf[(i+1)&1]
@@ -551,6 +439,7 @@ int Engine::enqueue_step(cudaStream_t s) {
     t.q = q; t.k_cache = L.k_cache; t.v_cache = L.v_cache; t.block_table = active_table; t.st = st;
     t.n_heads = c.n_heads; t.n_kv_heads = c.n_kv_heads; t.out = att; t.partial = attn_partial; t.counters = attn_counters;
     t.n_splits = n_splits; t.fixed_ctx = 0;
+    t.prefetch_tokens = use_attn_prefetch ? pages_per_seq * kPageTokens : 0;
     B200_CUDA(launch_attn_decode(t, s, use_pdl)); ++n;
     // row-parallel projections: without TP the residual add is the GEMV epilogue; with TP every rank holds a
     // K-slice, so the partial products are summed over NVLink (NCCL all-reduce) before they join the stream
@@ -595,10 +484,6 @@ int Engine::enqueue_step(cudaStream_t s) {
 
 int Engine::ensure_graph() {
   if (!all_set()) { set_error("not all tensors are set"); return B200_ESTATE; }
-  {
-    int rc = ensure_mega();
-    if (rc) return rc;
-  }
   if (!use_graph || step_graph) return 0;
   for (int attempt = 0; attempt < 2; ++attempt) {
     cudaGraph_t g = nullptr;
@@ -615,10 +500,6 @@ int Engine::ensure_graph() {
     }
     (void)cudaGetLastError();
     step_graph = nullptr;
-    if (mega_ready) {  // a cooperative launch that cannot be captured: launch the step directly (3 launches per token)
-      use_graph = false;
-      return 0;
-    }
     if (use_pdl) {
       use_pdl = false;  // retry the capture with plain stream-order edges
       continue;
@@ -691,7 +572,6 @@ int Engine::generate_greedy(const int32_t* prompt, int n_prompt, int32_t* ids, i
   cudaError_t e = cudaStreamSynchronize(stream);
   if (!rc && e != cudaSuccess) rc = cuda_fail(e, "generate sync");
   if (!rc) rc = tp_check_error();
-  if (!rc) rc = mega_check_error();
   if (!rc) {
     float a = 0, b = 0;
     cudaEventElapsedTime(&a, e0, e1);
@@ -741,7 +621,7 @@ int Engine::forward_logits_forced(const int32_t* prompt, int n_prompt, int prefi
     B200_CUDA(cudaMemcpyAsync(logits_host + (size_t)(k + 1) * row, logits, row * 4, cudaMemcpyDeviceToHost, stream));
   }
   B200_CUDA(cudaStreamSynchronize(stream));
-  return mega_check_error();
+  return 0;
 }
 
 }  // namespace b200

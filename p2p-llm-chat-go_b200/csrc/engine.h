@@ -160,21 +160,11 @@ struct Engine {
   uint16_t* output16 = nullptr;     // bf16 lm_head operand of the tensor-core path
 
   cudaGraphExec_t step_graph = nullptr;
-  bool use_pdl = true, use_graph = true, use_l2_chain = false, use_fa_prefill = true, use_mma_decode = true;
-  // persistent decode kernel (decode_mega.cu): one cooperative launch per token instead of ~5 per layer
-  bool use_mega = false, mega_ready = false;
-  MegaPhase* mega_phases = nullptr;   // device
-  unsigned int* mega_sync = nullptr;  // device: {barrier count, barrier generation, error}
-  MegaArgs mega = {};
-  int mega_group = 0;
-  unsigned long long* mega_trace = nullptr;  // device, 4 stamps per phase (B200_MEGA_TRACE=<file>)
-  int dump_mega_trace();
+  bool use_pdl = true, use_graph = true, use_l2_chain = false, use_fa_prefill = true, use_mma_decode = true, use_attn_prefetch = true;
   // n_seqs sequences decoding together from a context of ctx tokens, synchronously (no scheduler thread): the
   // batched step of scheduler.cu, tensor-parallel aware (every rank makes the same call)
   int bench_batched(int n_seqs, int ctx, int n_steps, float* ms_per_step, int32_t* last_ids);
   unsigned long long* b_keys = nullptr;  // [max_seqs] argmax keys (vocab-parallel lm_head)
-  int ensure_mega();          // builds the phase table once all tensors are set; leaves mega_ready false if unsupported
-  int mega_check_error();     // after a synchronize: did a wait inside the kernel time out?
   int launches_per_step = 0;
   void* flush_buf = nullptr;
   size_t flush_bytes = 0;

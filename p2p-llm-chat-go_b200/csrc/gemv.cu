@@ -38,14 +38,14 @@ DEVINL void gemv_body(const GemvArgs& a, int cta, int n_ctas) {
   const size_t xb = (F::x_bytes(a.K) + 127) & ~(size_t)127;
   uint8_t* xs = smem;
   uint8_t* ring = smem + xb + (size_t)warp * F::STAGES * F::STAGE_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + xb + (size_t)kWarps * F::STAGES * F::STAGE_BYTES) + warp * F::STAGES;
-  float* red = reinterpret_cast<float*>(smem + xb + (size_t)kWarps * F::STAGES * F::STAGE_BYTES + kWarps * F::STAGES * 8);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + xb + (size_t)F::NW * F::STAGES * F::STAGE_BYTES) + warp * F::STAGES;
+  float* red = reinterpret_cast<float*>(smem + xb + (size_t)F::NW * F::STAGES * F::STAGE_BYTES + F::NW * F::STAGES * 8);
 
   // unit u (R rows, full K) -> global warp u % twarps; consecutive units land on consecutive CTAs, so a
   // matrix with fewer units than warps still spreads over every SM
   const int n_units = a.N / F::R;
   const int chunks = a.K / F::CHUNK;
-  const int gwarp = warp * n_ctas + cta, twarps = n_ctas * kWarps;
+  const int gwarp = warp * n_ctas + cta, twarps = n_ctas * F::NW;
   const int my_units = gwarp < n_units ? (n_units - gwarp + twarps - 1) / twarps : 0;
   const int n_items = my_units * chunks;
   const uint32_t ring_s = smem_u32(ring), bars_s = smem_u32(bars);
@@ -92,9 +92,13 @@ DEVINL void gemv_body(const GemvArgs& a, int cta, int n_ctas) {
   float bestv = -INFINITY;
   uint32_t besti = 0;
   for (int u = 0; u < my_units; ++u) {
-    float acc[F::R];
+    float acc[F::R], res[F::R];
 #pragma unroll
     for (int r = 0; r < F::R; ++r) acc[r] = 0.f;
+    if (EPI == EPI_RESID && lane == 0) {  // the residual these rows are added to: fetched now, not after the last chunk
+#pragma unroll
+      for (int r = 0; r < F::R; ++r) res[r] = __ldcg(a.y + (size_t)(gwarp + u * twarps) * F::R + r);
+    }
     for (int c = 0; c < chunks; ++c) {
       mbar_wait(bars_s + 8 * c_stage, c_parity);
       F::consume(ring + (size_t)c_stage * F::STAGE_BYTES, xs, c, a, lane, acc);
@@ -110,6 +114,10 @@ DEVINL void gemv_body(const GemvArgs& a, int cta, int n_ctas) {
     }
 #pragma unroll
     for (int r = 0; r < F::R; ++r) acc[r] = warp_sum(acc[r]);
+    if (EPI == EPI_RESID) {
+#pragma unroll
+      for (int r = 0; r < F::R; ++r) acc[r] = res[r] + acc[r];
+    }
     epilogue<EPI, F::R>(a, gwarp + u * twarps, lane, acc, bestv, besti);
   }
   if (EPI == EPI_LOGITS && lane == 0 && my_units > 0) atomicMax(a.argmax_key, argmax_key(bestv, besti));
@@ -135,7 +143,7 @@ DEVINL void gemv_body(const GemvArgs& a, int cta, int n_ctas) {
 }
 
 template <class F, int PRO, int EPI>
-__global__ void __launch_bounds__(kWarps * 32, 1) gemv_kernel(const GemvArgs a) {
+__global__ void __launch_bounds__(F::NW * 32, F::OCC) gemv_kernel(const GemvArgs a) {
   gemv_body<F, PRO, EPI>(a, (int)blockIdx.x, (int)gridDim.x);
 }
 
@@ -143,7 +151,7 @@ __global__ void __launch_bounds__(kWarps * 32, 1) gemv_kernel(const GemvArgs a) 
 // rest stream `b` in format FB (each CTA runs one body, so the two activation layouts never meet).  Used for the
 // q,k | v projections of Q4_K_M layers whose V is stored in Q6_K: one launch less per such layer (~7 us each).
 template <class FA, class FB, int PRO, int EPI>
-__global__ void __launch_bounds__(kWarps * 32, 1) gemv_dual_kernel(const GemvArgs a, const GemvArgs b, int a_ctas) {
+__global__ void __launch_bounds__(FA::NW * 32, FA::OCC) gemv_dual_kernel(const GemvArgs a, const GemvArgs b, int a_ctas) {
   if ((int)blockIdx.x < a_ctas) gemv_body<FA, PRO, EPI>(a, (int)blockIdx.x, a_ctas);
   else gemv_body<FB, PRO, EPI>(b, (int)blockIdx.x - a_ctas, (int)gridDim.x - a_ctas);
 }
@@ -151,26 +159,35 @@ __global__ void __launch_bounds__(kWarps * 32, 1) gemv_dual_kernel(const GemvArg
 template <class F>
 size_t smem_bytes(int K) {
   const size_t xb = (F::x_bytes(K) + 127) & ~(size_t)127;
-  return xb + (size_t)kWarps * F::STAGES * F::STAGE_BYTES + kWarps * F::STAGES * 8 + kWarps * 4 + 32;
+  return xb + (size_t)F::NW * F::STAGES * F::STAGE_BYTES + F::NW * F::STAGES * 8 + F::NW * 4 + 32;
 }
+
+// Dynamic shared memory a CTA of this shape may use: the sm_100 opt-in maximum, or half an SM (minus the 1 KB the
+// system keeps per CTA) when two CTAs have to fit.
+template <class F>
+constexpr int max_smem() { return F::OCC >= 2 ? (228 * 1024) / 2 - 1024 : 227 * 1024; }
+
+template <class F>
+bool fits(int K) { return smem_bytes<F>(K) <= (size_t)max_smem<F>(); }
 
 template <class F, int PRO, int EPI>
 cudaError_t launch_t(const GemvArgs& a, cudaStream_t s, bool pdl, int sm_count) {
   auto kern = gemv_kernel<F, PRO, EPI>;
   const size_t smem = smem_bytes<F>(a.K);
   // Per-device attribute, cheap to set: no caching, so one host thread may drive several GPUs.  Always the
-  // sm_100 opt-in maximum rather than this launch's size: the same kernel serves matrices with different K,
+  // maximum for this shape rather than this launch's size: the same kernel serves matrices with different K,
   // and a tool that re-launches a captured node (ncu replay) reads the attribute as it stands at that time.
-  constexpr int kMaxOptinSmem = 227 * 1024;
-  if (smem > (size_t)kMaxOptinSmem) return cudaErrorInvalidValue;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxOptinSmem);
+  if (smem > (size_t)max_smem<F>()) return cudaErrorInvalidValue;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem<F>());
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   if (e != cudaSuccess) return e;
   const int n_units = a.N / F::R;
   int grid = n_units < sm_count ? n_units : sm_count;  // units are dealt CTA-first (see gemv_kernel)
   if (grid < 1) grid = 1;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(kWarps * 32);
+  cfg.blockDim = dim3(F::NW * 32);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = s;
   cudaLaunchAttribute at[1];
@@ -191,10 +208,12 @@ cudaError_t launch_f(int pro, int epi, const GemvArgs& a, cudaStream_t s, bool p
   CASE(PRO_RMSNORM, EPI_SWIGLU)
   CASE(PRO_RMSNORM, EPI_QKV)
   CASE(PRO_RMSNORM, EPI_LOGITS)
-  CASE(PRO_COPY, EPI_TP_PUSH)
-  CASE(PRO_TP_RMSNORM, EPI_SWIGLU)
-  CASE(PRO_TP_RMSNORM, EPI_QKV)
-  CASE(PRO_TP_RMSNORM, EPI_LOGITS)
+  if constexpr (F::OCC == 1) {  // tensor parallelism over peer memory: the fat shape only
+    CASE(PRO_COPY, EPI_TP_PUSH)
+    CASE(PRO_TP_RMSNORM, EPI_SWIGLU)
+    CASE(PRO_TP_RMSNORM, EPI_QKV)
+    CASE(PRO_TP_RMSNORM, EPI_LOGITS)
+  }
 #undef CASE
   return cudaErrorInvalidValue;
 }
@@ -202,10 +221,12 @@ cudaError_t launch_f(int pro, int epi, const GemvArgs& a, cudaStream_t s, bool p
 template <class FA, class FB, int PRO, int EPI>
 cudaError_t launch_dual_t(const GemvArgs& a, const GemvArgs& b, cudaStream_t s, bool pdl, int sm_count) {
   auto kern = gemv_dual_kernel<FA, FB, PRO, EPI>;
+  static_assert(FA::NW == FB::NW && FA::OCC == FB::OCC, "both sides of a dual launch share the CTA shape");
   const size_t smem = std::max(smem_bytes<FA>(a.K), smem_bytes<FB>(b.K));
-  constexpr int kMaxOptinSmem = 227 * 1024;
-  if (smem > (size_t)kMaxOptinSmem || sm_count < 2) return cudaErrorInvalidValue;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxOptinSmem);
+  if (smem > (size_t)max_smem<FA>() || sm_count < 2) return cudaErrorInvalidValue;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem<FA>());
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   if (e != cudaSuccess) return e;
   // CTAs in proportion to the bytes each side streams
   const double ba = (double)a.N * (double)FA::row_bytes(a.K), bb = (double)b.N * (double)FB::row_bytes(b.K);
@@ -213,7 +234,7 @@ cudaError_t launch_dual_t(const GemvArgs& a, const GemvArgs& b, cudaStream_t s, 
   a_ctas = std::min(std::max(a_ctas, 1), sm_count - 1);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(sm_count);
-  cfg.blockDim = dim3(kWarps * 32);
+  cfg.blockDim = dim3(FA::NW * 32);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = s;
   cudaLaunchAttribute at[1];
@@ -224,16 +245,45 @@ cudaError_t launch_dual_t(const GemvArgs& a, const GemvArgs& b, cudaStream_t s, 
   return cudaLaunchKernelEx(&cfg, kern, a, b, a_ctas);
 }
 
+// ------------------------------------------------------------------ launch shapes
+// Shape 0: one 16-warp CTA per SM owning up to the whole shared memory (deep rings).
+// Shape 1: 8-warp CTAs that take at most half an SM, so the next kernel of the decode step is resident and
+//          prefetched while this one streams (see GemvCfg).  Chosen per engine through gemv_set_shape / B200_GEMV_SHAPE.
+using S0r4 = GemvCfg<16, 2, 1>;  // 4-row units
+using S0r2 = GemvCfg<16, 3, 1>;  // 2-row units
+using S0q6 = GemvCfg<16, 2, 1>;
+using S1r4 = GemvCfg<8, 2, 2>;
+using S1r2 = GemvCfg<8, 3, 2>;
+using S1q6 = GemvCfg<8, 2, 2>;
+
+int g_shape_wide = -1, g_shape_narrow = -1;  // -1: not read from the environment yet
+void read_shape_env() {
+  if (g_shape_wide >= 0) return;
+  const char* all = getenv("B200_GEMV_SHAPE");
+  const char* w = getenv("B200_GEMV_SHAPE_WIDE");
+  const char* n = getenv("B200_GEMV_SHAPE_NARROW");
+  const int dflt = all ? atoi(all) : 0;
+  g_shape_wide = w ? atoi(w) : dflt;
+  g_shape_narrow = n ? atoi(n) : dflt;
+}
+
 }  // namespace
 
 // q,k rows in Q4_K and v rows in Q6_K (the Q4_K_M recipe's "more bits" layers), RMS-norm prologue, RoPE / KV-append
 // epilogue, one launch.  Other combinations: cudaErrorNotSupported (the caller launches them one after the other).
 cudaError_t launch_gemv_dual_qkv(int type_a, const GemvArgs& a, int type_b, const GemvArgs& b, cudaStream_t s, bool pdl, int sm_count) {
-  if (type_a != T_Q4_K || type_b != T_Q6_K || getenv("B200_NO_DUAL_QKV")) return cudaErrorNotSupported;
+  static const bool off = getenv("B200_NO_DUAL_QKV") != nullptr;
+  if (type_a != T_Q4_K || type_b != T_Q6_K || off) return cudaErrorNotSupported;
   if (!gemv_shape_ok(type_a, a.N, a.K, EPI_QKV) || !gemv_shape_ok(type_b, b.N, b.K, EPI_QKV)) return cudaErrorInvalidValue;
-  const bool wide = (a.N / 4) >= sm_count * kWarps;
-  if (wide) return launch_dual_t<FmtQ4K<4>, FmtQ6K, PRO_RMSNORM, EPI_QKV>(a, b, s, pdl, sm_count);
-  return launch_dual_t<FmtQ4K<2>, FmtQ6K, PRO_RMSNORM, EPI_QKV>(a, b, s, pdl, sm_count);
+  read_shape_env();
+  const bool wide = (a.N / 4) >= sm_count * 16;
+  const int shape = wide ? g_shape_wide : g_shape_narrow;
+  if (shape == 1 && fits<FmtQ4K<4, S1r4>>(a.K) && fits<FmtQ6K<S1q6>>(b.K)) {
+    if (wide) return launch_dual_t<FmtQ4K<4, S1r4>, FmtQ6K<S1q6>, PRO_RMSNORM, EPI_QKV>(a, b, s, pdl, sm_count);
+    return launch_dual_t<FmtQ4K<2, S1r2>, FmtQ6K<S1q6>, PRO_RMSNORM, EPI_QKV>(a, b, s, pdl, sm_count);
+  }
+  if (wide) return launch_dual_t<FmtQ4K<4, S0r4>, FmtQ6K<S0q6>, PRO_RMSNORM, EPI_QKV>(a, b, s, pdl, sm_count);
+  return launch_dual_t<FmtQ4K<2, S0r2>, FmtQ6K<S0q6>, PRO_RMSNORM, EPI_QKV>(a, b, s, pdl, sm_count);
 }
 
 size_t gemv_row_bytes(int wtype, int64_t K) {
@@ -249,25 +299,44 @@ bool gemv_shape_ok(int wtype, int64_t N, int64_t K, int epi) {
   if (N <= 0 || K <= 0 || K > 32768) return false;
   switch (wtype) {
     case T_BF16: return K % 256 == 0 && N % 4 == 0;
-    case T_Q4_K: return K % FmtQ4K<4>::CHUNK == 0 && N % 4 == 0;
-    case T_Q6_K: return K % FmtQ6K::CHUNK == 0 && N % FmtQ6K::R == 0;
+    case T_Q4_K: return K % (8 * QK_K) == 0 && N % 4 == 0;
+    case T_Q6_K: return K % (8 * QK_K) == 0 && N % 2 == 0;
   }
   (void)epi;
   return false;
 }
 
+namespace {
+// the tensor-parallel prologue / epilogue exist for shape 0 only (they are bf16-only, 70B-sized K)
+template <class W, class Nr>
+cudaError_t launch_by_width(bool wide, int pro, int epi, const GemvArgs& a, cudaStream_t s, bool pdl, int sm) {
+  return wide ? launch_f<W>(pro, epi, a, s, pdl, sm) : launch_f<Nr>(pro, epi, a, s, pdl, sm);
+}
+}  // namespace
+
 cudaError_t launch_gemv(int wtype, int pro, int epi, const GemvArgs& a, cudaStream_t s, bool pdl, int sm_count) {
   if (!gemv_shape_ok(wtype, a.N, a.K, epi)) return cudaErrorInvalidValue;
+  read_shape_env();
   // 4 rows per unit amortise the activation loads best; matrices with fewer than one such unit per warp
   // (o / down / qkv: 4096-6144 rows) use 2-row units so that every warp of every SM streams something
-  const bool wide = (a.N / 4) >= sm_count * kWarps;
+  const bool wide = (a.N / 4) >= sm_count * 16;
+  const bool tp = pro == PRO_TP_RMSNORM || epi == EPI_TP_PUSH;
+  const int shape = tp ? 0 : (wide ? g_shape_wide : g_shape_narrow);
   switch (wtype) {
     case T_BF16:
-      if (a.K % 512 == 0)
-        return wide ? launch_f<FmtBF16<512, 4>>(pro, epi, a, s, pdl, sm_count) : launch_f<FmtBF16<512, 2>>(pro, epi, a, s, pdl, sm_count);
-      return wide ? launch_f<FmtBF16<256, 4>>(pro, epi, a, s, pdl, sm_count) : launch_f<FmtBF16<256, 2>>(pro, epi, a, s, pdl, sm_count);
-    case T_Q4_K: return wide ? launch_f<FmtQ4K<4>>(pro, epi, a, s, pdl, sm_count) : launch_f<FmtQ4K<2>>(pro, epi, a, s, pdl, sm_count);
-    case T_Q6_K: return launch_f<FmtQ6K>(pro, epi, a, s, pdl, sm_count);
+      if (a.K % 512 == 0) {
+        if (shape == 1 && fits<FmtBF16<512, 4, S1r4>>(a.K) && fits<FmtBF16<512, 2, S1r2>>(a.K))
+          return launch_by_width<FmtBF16<512, 4, S1r4>, FmtBF16<512, 2, S1r2>>(wide, pro, epi, a, s, pdl, sm_count);
+        return launch_by_width<FmtBF16<512, 4, S0r4>, FmtBF16<512, 2, S0r2>>(wide, pro, epi, a, s, pdl, sm_count);
+      }
+      return launch_by_width<FmtBF16<256, 4, S0r4>, FmtBF16<256, 2, S0r2>>(wide, pro, epi, a, s, pdl, sm_count);
+    case T_Q4_K:
+      if (shape == 1 && fits<FmtQ4K<4, S1r4>>(a.K) && fits<FmtQ4K<2, S1r2>>(a.K))
+        return launch_by_width<FmtQ4K<4, S1r4>, FmtQ4K<2, S1r2>>(wide, pro, epi, a, s, pdl, sm_count);
+      return launch_by_width<FmtQ4K<4, S0r4>, FmtQ4K<2, S0r2>>(wide, pro, epi, a, s, pdl, sm_count);
+    case T_Q6_K:
+      if (shape == 1 && fits<FmtQ6K<S1q6>>(a.K)) return launch_f<FmtQ6K<S1q6>>(pro, epi, a, s, pdl, sm_count);
+      return launch_f<FmtQ6K<S0q6>>(pro, epi, a, s, pdl, sm_count);
   }
   return cudaErrorInvalidValue;
 }

@@ -1,6 +1,6 @@
 // gemv_formats.cuh — the weight-format policies (bf16, Q4_K, Q6_K), fused prologues and epilogues of the
-// batch-1 decode mat-vec.  Shared by gemv.cu (one kernel per projection) and decode_mega.cu (one persistent
-// kernel per token); see gemv.cu for the data-movement and numerics description.
+// batch-1 decode mat-vec.  Used by gemv.cu (one kernel per projection;
+// scratch/decode_mega.cu, a measured-slower persistent-kernel experiment, used them too); see gemv.cu for the data-movement and numerics description.
 //
 // Activation vectors (x, the residual stream) are read with ld.global.cg: in the persistent kernel they are
 // produced by other SMs earlier in the same launch, and an L1 line from a previous phase would be stale.
@@ -12,31 +12,43 @@ namespace b200 {
 
 namespace {
 
-constexpr int kWarps = 16;  // consumer warps per CTA (each is its own TMA producer); one CTA per SM
+// Launch shape of a GEMV kernel: NW consumer warps per CTA (each is its own TMA producer), ST ring stages per warp,
+// OCC CTAs that must fit on an SM.  OCC = 1: one fat CTA per SM owns all of its shared memory.  OCC = 2: a CTA uses
+// at most half of the SM, so under programmatic dependent launch the NEXT kernel's CTA becomes resident beside the
+// running one and has its weight ring full (and its launch latency behind it) before the running kernel ends.
+template <int NW_, int ST_, int OCC_>
+struct GemvCfg {
+  static constexpr int NW = NW_, ST = ST_, OCC = OCC_;
+};
 
 // ------------------------------------------------------------------ block helpers
+template <int NW>
 DEVINL float block_sum(float v, float* red, int warp, int lane) {
   v = warp_sum(v);
   if (lane == 0) red[warp] = v;
   __syncthreads();
   float t = 0.f;
 #pragma unroll
-  for (int i = 0; i < kWarps; ++i) t += red[i];
+  for (int i = 0; i < NW; ++i) t += red[i];
   __syncthreads();
   return t;
 }
 
-constexpr int kProU = 4;  // float4 per thread kept in registers by the single-fetch prologues (K <= 8192)
+// float4 per thread kept in registers by the single-fetch prologues: covers K <= 8192 whatever the CTA width
+template <int NW>
+struct ProU {
+  static constexpr int value = 8192 / (NW * 32 * 4) < 1 ? 1 : 8192 / (NW * 32 * 4);
+};
 
-template <int PRO>
+template <int PRO, int NW>
 DEVINL float rms_inv(const GemvArgs& a, float* red, int warp, int lane) {
   if (PRO != PRO_RMSNORM) return 1.f;  // (PRO_TP_RMSNORM is bf16-only and has its own prologue)
   float ss = 0.f;
-  for (int k = threadIdx.x * 4; k < a.K; k += kWarps * 32 * 4) {
+  for (int k = threadIdx.x * 4; k < a.K; k += NW * 32 * 4) {
     const float4 v = __ldcg(reinterpret_cast<const float4*>(a.x + k));
     ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
   }
-  ss = block_sum(ss, red, warp, lane);
+  ss = block_sum<NW>(ss, red, warp, lane);
   return 1.0f / sqrtf(ss / (float)a.K + a.eps);
 }
 
@@ -57,6 +69,7 @@ DEVINL void st_release_sys(unsigned int* p, unsigned int v) {
 // `tp_index` has landed in this GPU's receive buffer, x_new = x + sum over ranks (fixed order, so every rank
 // computes the same bits), CTA 0 publishes x_new, and the RMS-normalised x_new goes to shared memory in the
 // GEMV's permuted layout.  A wait that exceeds ~2 s sets the error flag and carries on (no hang).
+template <int NW>
 DEVINL void tp_prologue(float* xs, const GemvArgs& a, float* red, int warp, int lane) {
   const TpLink* t = a.tp;
   const int buf = a.tp_index & 1, size = t->size, d = a.K;
@@ -74,7 +87,7 @@ DEVINL void tp_prologue(float* xs, const GemvArgs& a, float* red, int warp, int 
   __syncthreads();
   const float* rv = t->recv[buf];
   float ss = 0.f;
-  for (int k = threadIdx.x * 4; k < d; k += kWarps * 32 * 4) {
+  for (int k = threadIdx.x * 4; k < d; k += NW * 32 * 4) {
     float4 v = __ldcg(reinterpret_cast<const float4*>(a.x + k));
     for (int s = 0; s < size; ++s) {
       const float4 p = __ldcg(reinterpret_cast<const float4*>(rv + (size_t)s * d + k));
@@ -85,9 +98,9 @@ DEVINL void tp_prologue(float* xs, const GemvArgs& a, float* red, int warp, int 
     const int idx = (k & ~255) + ((k >> 2) & 1) * 128 + ((k & 255) >> 3) * 4;
     *reinterpret_cast<float4*>(xs + idx) = v;
   }
-  ss = block_sum(ss, red, warp, lane);
+  ss = block_sum<NW>(ss, red, warp, lane);
   const float inv = 1.0f / sqrtf(ss / (float)d + a.eps);
-  for (int k = threadIdx.x * 4; k < d; k += kWarps * 32 * 4) {
+  for (int k = threadIdx.x * 4; k < d; k += NW * 32 * 4) {
     const int idx = (k & ~255) + ((k >> 2) & 1) * 128 + ((k & 255) >> 3) * 4;
     float4 v = *reinterpret_cast<float4*>(xs + idx);
     const float4 w = *reinterpret_cast<const float4*>(a.norm_w + k);
@@ -100,9 +113,9 @@ DEVINL void tp_prologue(float* xs, const GemvArgs& a, float* red, int warp, int 
   __syncthreads();
 }
 
-template <int KC, int R_>  // KC in {256, 512}; R_ rows per work unit (4, or 2 for matrices with few rows)
+template <int KC, int R_, class C>  // KC in {256, 512}; R_ rows per work unit (4, or 2 for matrices with few rows)
 struct FmtBF16 {
-  static constexpr int R = R_, CHUNK = KC, STAGES = (R_ == 4) ? 2 : 3;
+  static constexpr int R = R_, CHUNK = KC, STAGES = C::ST, NW = C::NW, OCC = C::OCC;
   static constexpr int ROW_STAGE_BYTES = KC * 2;
   static constexpr int STAGE_BYTES = R * ROW_STAGE_BYTES;
   static __host__ __device__ size_t x_bytes(int K) { return (size_t)K * 4; }
@@ -118,18 +131,19 @@ struct FmtBF16 {
   // element 8l+j  ->  (j<4 ? 4l+j : 128+4l+(j-4))
   template <int PRO>
   static DEVINL void prologue(uint8_t* xs_, const GemvArgs& a, float* red, int warp, int lane) {
+    constexpr int kProU = ProU<NW>::value;
     float* xs = reinterpret_cast<float*>(xs_);
     if (PRO == PRO_TP_RMSNORM) {
-      tp_prologue(xs, a, red, warp, lane);
+      tp_prologue<NW>(xs, a, red, warp, lane);
       return;
     }
-    if (PRO == PRO_RMSNORM && a.K <= kWarps * 32 * 4 * kProU) {
+    if (PRO == PRO_RMSNORM && a.K <= NW * 32 * 4 * kProU) {
       // x and the norm weights are fetched once and stay in registers between the sum of squares and the
       // scaling (same element -> thread mapping and summation order as rms_inv, so the same bits)
       float4 v[kProU], w[kProU];
 #pragma unroll
       for (int i = 0; i < kProU; ++i) {
-        const int k = threadIdx.x * 4 + i * kWarps * 32 * 4;
+        const int k = threadIdx.x * 4 + i * NW * 32 * 4;
         const bool on = k < a.K;
         v[i] = on ? __ldcg(reinterpret_cast<const float4*>(a.x + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
         w[i] = on ? *reinterpret_cast<const float4*>(a.norm_w + k) : make_float4(0.f, 0.f, 0.f, 0.f);
@@ -137,12 +151,12 @@ struct FmtBF16 {
       float ss = 0.f;
 #pragma unroll
       for (int i = 0; i < kProU; ++i)
-        if (threadIdx.x * 4 + i * kWarps * 32 * 4 < a.K) ss += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
-      ss = block_sum(ss, red, warp, lane);
+        if (threadIdx.x * 4 + i * NW * 32 * 4 < a.K) ss += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
+      ss = block_sum<NW>(ss, red, warp, lane);
       const float inv = 1.0f / sqrtf(ss / (float)a.K + a.eps);
 #pragma unroll
       for (int i = 0; i < kProU; ++i) {
-        const int k = threadIdx.x * 4 + i * kWarps * 32 * 4;
+        const int k = threadIdx.x * 4 + i * NW * 32 * 4;
         if (k < a.K) {
           float4 o;
           o.x = __fmul_rn(__fmul_rn(v[i].x, inv), w[i].x);
@@ -156,8 +170,8 @@ struct FmtBF16 {
       __syncthreads();
       return;
     }
-    const float inv = rms_inv<PRO>(a, red, warp, lane);
-    for (int k = threadIdx.x * 4; k < a.K; k += kWarps * 32 * 4) {
+    const float inv = rms_inv<PRO, NW>(a, red, warp, lane);
+    for (int k = threadIdx.x * 4; k < a.K; k += NW * 32 * 4) {
       float4 v = __ldcg(reinterpret_cast<const float4*>(a.x + k));
       if (PRO == PRO_RMSNORM) {
         const float4 w = *reinterpret_cast<const float4*>(a.norm_w + k);
@@ -240,42 +254,43 @@ DEVINL void q16_prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, i
   // lane = 4 consecutive elements (one float4), 8 lanes = one 32-element block, a warp = 4 blocks per round;
   // U rounds of loads are issued before the first dependent shuffle.  ~15 instructions per block instead of
   // ~120 with one element per lane, which matters because every CTA repeats this for the whole vector.
-  constexpr int U = kProU;
+  constexpr int NW = F::NW;
+  constexpr int U = ProU<NW>::value;
   const int n4 = a.K / 4;
   // K <= 8192 with an RMS norm: x and the norm weights are fetched once, before the block-wide sum of
   // squares, and reused from registers below (thread -> element mapping and summation order as in rms_inv)
-  const bool single = (PRO == PRO_RMSNORM) && n4 <= kWarps * 32 * U;
+  const bool single = (PRO == PRO_RMSNORM) && n4 <= NW * 32 * U;
   float4 v[U], g[U];
   float inv = 1.f;
   if (single) {
     float ss = 0.f;
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const int gi = u * kWarps * 32 + (int)threadIdx.x;
+      const int gi = u * NW * 32 + (int)threadIdx.x;
       v[u] = gi < n4 ? __ldcg(reinterpret_cast<const float4*>(a.x + 4 * gi)) : make_float4(0.f, 0.f, 0.f, 0.f);
       g[u] = gi < n4 ? *reinterpret_cast<const float4*>(a.norm_w + 4 * gi) : make_float4(1.f, 1.f, 1.f, 1.f);
     }
 #pragma unroll
     for (int u = 0; u < U; ++u)
-      if (u * kWarps * 32 + (int)threadIdx.x < n4) ss += v[u].x * v[u].x + v[u].y * v[u].y + v[u].z * v[u].z + v[u].w * v[u].w;
-    ss = block_sum(ss, red, warp, lane);
+      if (u * NW * 32 + (int)threadIdx.x < n4) ss += v[u].x * v[u].x + v[u].y * v[u].y + v[u].z * v[u].z + v[u].w * v[u].w;
+    ss = block_sum<NW>(ss, red, warp, lane);
     inv = 1.0f / sqrtf(ss / (float)a.K + a.eps);
   } else {
-    inv = rms_inv<PRO>(a, red, warp, lane);
+    inv = rms_inv<PRO, NW>(a, red, warp, lane);
   }
-  for (int g0 = warp * 32; g0 < n4; g0 += kWarps * 32 * U) {
+  for (int g0 = warp * 32; g0 < n4; g0 += NW * 32 * U) {
     if (!single) {
 #pragma unroll
       for (int u = 0; u < U; ++u) {
-        const int gi = g0 + u * kWarps * 32 + lane;
+        const int gi = g0 + u * NW * 32 + lane;
         v[u] = gi < n4 ? __ldcg(reinterpret_cast<const float4*>(a.x + 4 * gi)) : make_float4(0.f, 0.f, 0.f, 0.f);
         g[u] = (PRO == PRO_RMSNORM && gi < n4) ? *reinterpret_cast<const float4*>(a.norm_w + 4 * gi) : make_float4(1.f, 1.f, 1.f, 1.f);
       }
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      const int gi = g0 + u * kWarps * 32 + lane;
-      if (g0 + u * kWarps * 32 >= n4) break;  // warp-uniform
+      const int gi = g0 + u * NW * 32 + lane;
+      if (g0 + u * NW * 32 >= n4) break;  // warp-uniform
       float4 val = v[u];
       if (PRO == PRO_RMSNORM) {
         val.x = __fmul_rn(__fmul_rn(val.x, inv), g[u].x);
@@ -316,9 +331,9 @@ DEVINL void q16_prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, i
 // Q4_K: a stage is R rows x 8 super-blocks (GGUF byte order, 144 B each).  lane = (block, j): the 32 qs bytes
 // of sub-block pair (2j, 2j+1) = 64 weights [64j, 64j+64) of that block; both sub-block sums are complete in
 // one lane, so (d*sc)*(dx*isum) is formed exactly as in the oracle.
-template <int R_>
+template <int R_, class C>
 struct FmtQ4K {
-  static constexpr int R = R_, BLOCKS = 8, CHUNK = BLOCKS * QK_K, STAGES = (R_ == 4) ? 2 : 3;
+  static constexpr int R = R_, BLOCKS = 8, CHUNK = BLOCKS * QK_K, STAGES = C::ST, NW = C::NW, OCC = C::OCC;
   static constexpr int ROW_STAGE_BYTES = BLOCKS * Q4K_BYTES;  // 1152
   static constexpr int STAGE_BYTES = R * ROW_STAGE_BYTES;
   static __host__ __device__ size_t x_bytes(int K) { return QActLayout::bytes(K); }
@@ -334,7 +349,7 @@ struct FmtQ4K {
   }
   template <int PRO>
   static DEVINL void prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane) {
-    q16_prologue<FmtQ4K<R_>, PRO>(xs, a, red, warp, lane);
+    q16_prologue<FmtQ4K<R_, C>, PRO>(xs, a, red, warp, lane);
   }
 
   static DEVINL void consume(const uint8_t* st, const uint8_t* xs, int c, const GemvArgs& a, int lane, float* acc) {
@@ -398,8 +413,9 @@ struct FmtQ4K {
 // 210-byte blocks, re-ordered lane-major): [qlA 32x16][qlB 32x16][qh 32x16][scales 32x4][d 8x2].
 // lane = (block, half, lh): l in [16lh,16lh+16) of the four 32-wide runs t=0..3 of that half; every run is
 // exactly one 16-weight scale group.  qlA = ql[half*64 + 16lh..], qlB = ql[half*64 + 32 + 16lh..].
+template <class C>
 struct FmtQ6K {
-  static constexpr int R = 2, BLOCKS = 8, CHUNK = BLOCKS * QK_K, STAGES = 2;
+  static constexpr int R = 2, BLOCKS = 8, CHUNK = BLOCKS * QK_K, STAGES = C::ST, NW = C::NW, OCC = C::OCC;
   static constexpr int ROW_STAGE_BYTES = BLOCKS * Q6K_BYTES;  // 1680
   static constexpr int STAGE_BYTES = R * ROW_STAGE_BYTES;
   static __host__ __device__ size_t x_bytes(int K) { return QActLayout::bytes(K); }
@@ -418,7 +434,7 @@ struct FmtQ6K {
   }
   template <int PRO>
   static DEVINL void prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane) {
-    q16_prologue<FmtQ6K, PRO>(xs, a, red, warp, lane);
+    q16_prologue<FmtQ6K<C>, PRO>(xs, a, red, warp, lane);
   }
 
   static DEVINL void consume(const uint8_t* st, const uint8_t* xs, int c, const GemvArgs& a, int lane, float* acc) {

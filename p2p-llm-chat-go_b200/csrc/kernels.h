@@ -124,6 +124,10 @@ struct AttnArgs {
   const int32_t* q_ctx;
   const int32_t* q_slot;
   int pages_per_seq;
+  // batch-1 decode step: cache rows [0, prefetch_tokens) of the active sequence may be read before the preceding
+  // kernel has finished (they exist and are not written by it, except the row of the current position, which is
+  // re-read).  0: the plain kernel.
+  int prefetch_tokens;
 };
 cudaError_t launch_attn_decode(const AttnArgs& a, cudaStream_t s, bool pdl);
 size_t attn_partial_floats(int n_heads, int n_kv_heads, int n_splits);
@@ -200,36 +204,6 @@ bool gemm_shape_ok(int64_t rows, int64_t K, int64_t n_tokens);
 // causal attention over a whole prompt on the tensor cores (attn_prefill.cu); out is bf16 [T][n_heads*128]
 cudaError_t launch_attn_prefill(const float* q, const uint16_t* k_cache, const uint16_t* v_cache, const int32_t* block_table, uint16_t* out,
                                 int T, int pos0, int n_heads, int n_kv_heads, cudaStream_t s);
-
-// ---- persistent decode kernel (decode_mega.cu): every projection and the attention of one token in ONE
-// cooperative launch, phases separated by grid barriers; the weight rings keep streaming across phases.
-enum MegaFmt { MF_BF16_R4 = 0, MF_BF16_R2 = 1, MF_Q4K_R4 = 2, MF_Q4K_R2 = 3, MF_Q6K = 4 };
-struct MegaPhase {
-  int kind;       // 0 = mat-vec, 1 = attention
-  int fmt;        // MegaFmt
-  int pro, epi;   // PRO_* / EPI_* of the mat-vec
-  int n_units;    // rows / rows-per-unit
-  int chunks;     // K / columns per stage
-  int pad_[2];
-  GemvArgs g;
-  AttnArgs t;
-};
-struct MegaArgs {
-  const MegaPhase* phases;
-  int n_phases;
-  int lm_head_phase;            // index of the lm_head phase (last), skipped while the prompt is being fed
-  const StepState* st;
-  unsigned int* bar_count;      // grid barrier: arrivals of the current generation (self-resetting)
-  unsigned int* bar_gen;        // grid barrier: generation
-  unsigned int* error;          // set to 1 if a wait timed out (a bug or a lost CTA): the step's results are void
-  int attn_splits;              // KV splits per KV head in the attention phase (n_kv_heads * attn_splits <= grid)
-  int x_bytes;                  // shared-memory bytes reserved for the activation vector / attention working set
-  unsigned long long* trace;    // debug (B200_MEGA_TRACE): CTA 0 stamps %globaltimer 4x per phase, else null
-};
-// fills fmt / n_units / chunks of a mat-vec phase from (wtype, N, K); false if the shape is not supported
-bool mega_plan_gemv(int wtype, int64_t N, int64_t K, int sm_count, MegaPhase* p);
-size_t mega_x_bytes(const MegaPhase* phases, int n, int group);  // smem for activations / attention
-cudaError_t launch_decode_mega(const MegaArgs& m, int group, int sm_count, cudaStream_t s);
 
 // batched decode (one query per sequence) on the tensor cores; bf16 output when out_bf16 is given, else a.out
 cudaError_t launch_attn_decode_batched(const AttnArgs& a, uint16_t* out_bf16, cudaStream_t s);

@@ -246,8 +246,7 @@ int Engine::decode_bs1_window(int slot) {
     else if (q.delivered >= q.max_out) reason = 2;
     if (reason) {
       cudaStreamSynchronize(stream);
-      const int merr = cancelled ? 0 : mega_check_error();
-      finish_request(slot, merr, merr ? 3 : reason);
+      finish_request(slot, 0, reason);
       return 0;
     }
     if (!interrupted) {
