@@ -70,6 +70,8 @@ typedef struct b200_config {
   int32_t eos_token;     /* generation stops on this id (<0: never)                               */
   int32_t reserved;      /* bit 0: decode every step on the batched tensor-core path, even for a single active   */
                          /* sequence (makes the numerics of concurrent requests independent of arrival timing)    */
+                         /* bit 1: no prefix reuse (by default a request whose prompt starts with the tokens a   */
+                         /* free slot's KV cache still holds is prefilled from the first differing token only)    */
 } b200_config;
 
 /* Sampling options = Ollama's `options` object (the reference sends none, web/streamlit_app.py:91-95, so
@@ -130,6 +132,19 @@ B200_API int64_t b200_weight_bytes(const b200_engine* e); /* bytes streamed per 
 B200_API int b200_tokenize(b200_engine* e, const char* utf8, size_t n, int add_bos, int32_t* ids, size_t cap,
                            size_t* n_out);
 B200_API int b200_detokenize(b200_engine* e, const int32_t* ids, size_t n, char* buf, size_t cap, size_t* n_out);
+
+/* What the model file says about chat framing (replaces: Ollama's per-model template and stop parameters, which it
+ * derives from the same GGUF keys — the reference sends a bare prompt, web/streamlit_app.py:93, and relies on them).
+ * b200_chat_template: the raw `tokenizer.chat_template` string ("" / n_out 0 when the engine has none).
+ * b200_stop_ids: every token id that ends a reply (eos, eot, eom, end_of_text, im_end as present in the vocabulary).
+ * b200_special_token: id of a control token by its text ("<|start_header_id|>"), -1 if the vocabulary has none. */
+B200_API int b200_chat_template(b200_engine* e, char* buf, size_t cap, size_t* n_out);
+B200_API int b200_stop_ids(b200_engine* e, int32_t* ids, size_t cap, size_t* n_out);
+B200_API int b200_special_token(b200_engine* e, const char* text);
+/* Longest prefix of `ids` whose K/V a sequence slot of this engine still holds from an earlier request (0 if none
+ * worth reusing).  A front end that spreads sessions over several engines (one per GPU; the reference has a single
+ * OLLAMA_URL, web/streamlit_app.py:27) uses it to send a peer's next suggestion where its chat history is cached. */
+B200_API int b200_prefix_match(b200_engine* e, const int32_t* ids, size_t n);
 
 /* ---- GGUF model files (what `ollama pull llama3.1` leaves on disk, README.md:70) ---------------------- */
 /* Reads shapes, storage types and the tokenizer vocabulary from a GGUF v2/v3 file of architecture "llama"

@@ -1,7 +1,7 @@
 """p2p-llm-chat-go_b200 — Python host side of libb200llm.so (ctypes over the C ABI in include/b200llm.h).
 
 This package holds no arithmetic: every number comes out of the sm_100a kernels in csrc/.  It exists so
-that tests, bench.py and the Python mirror of the reference's caller (`client.ai_suggest`, the function at
+that tests and bench.py (and tests/ref_client.py, the Python mirror of the reference's caller at
 web/streamlit_app.py:89-101) can drive the same entry points `go/cmd/llmd` binds through cgo.
 
 The directory name follows the repo convention and is not a valid Python identifier; load it with
@@ -23,6 +23,7 @@ F32, Q4_K, Q6_K, BF16 = 0, 12, 14, 30
 WEIGHTS_BF16, WEIGHTS_Q4_K_M = 0, 1
 MODE_GEMV, MODE_GEMM = 0, 1
 ENODEV = -2
+ERANGE = -7
 QK_K, Q4K_BYTES, Q6K_BYTES = 256, 144, 210
 
 
@@ -97,6 +98,10 @@ def lib():
         "b200_stats_get": (i32, [vp, C.POINTER(Stats)]),
         "b200_cancel": (None, [vp]),
         "b200_free": (None, [vp]),
+        "b200_chat_template": (i32, [vp, vp, sz, C.POINTER(sz)]),
+        "b200_stop_ids": (i32, [vp, vp, sz, C.POINTER(sz)]),
+        "b200_special_token": (i32, [vp, C.c_char_p]),
+        "b200_prefix_match": (i32, [vp, vp, sz]),
         "b200_forward_logits": (i32, [vp, vp, sz, i32, vp]),
         "b200_forward_logits_forced": (i32, [vp, vp, sz, i32, vp, sz, vp]),
         "b200_generate_greedy": (i32, [vp, vp, sz, vp, sz, i32, C.POINTER(f32), C.POINTER(f32)]),
@@ -377,8 +382,32 @@ class Engine:
         ids = _c(ids, np.int32)
         buf = C.create_string_buffer(max(16, ids.size * 64))
         n = C.c_size_t()
-        _check(lib().b200_detokenize(self.h, _p(ids), ids.size, buf, len(buf), C.byref(n)))
+        rc = lib().b200_detokenize(self.h, _p(ids), ids.size, buf, len(buf), C.byref(n))
+        if rc == ERANGE:                      # a token longer than the guess: n holds the size needed
+            buf = C.create_string_buffer(n.value)
+            rc = lib().b200_detokenize(self.h, _p(ids), ids.size, buf, len(buf), C.byref(n))
+        _check(rc)
         return buf.raw[:n.value].decode(errors="replace")
+
+    def chat_template(self):
+        n = C.c_size_t()
+        lib().b200_chat_template(self.h, None, 0, C.byref(n))
+        buf = C.create_string_buffer(max(1, n.value))
+        _check(lib().b200_chat_template(self.h, buf, n.value, C.byref(n)))
+        return buf.raw[:n.value].decode(errors="replace")
+
+    def stop_ids(self):
+        ids = np.empty(64, np.int32)
+        n = C.c_size_t()
+        _check(lib().b200_stop_ids(self.h, _p(ids), ids.size, C.byref(n)))
+        return ids[:n.value].tolist()
+
+    def special_token(self, text):
+        return lib().b200_special_token(self.h, text.encode())
+
+    def prefix_match(self, ids):
+        ids = _c(ids, np.int32)
+        return lib().b200_prefix_match(self.h, _p(ids), ids.size)
 
     def submit(self, prompt_ids, sampling=None):
         ids = _c(prompt_ids, np.int32)

@@ -177,6 +177,7 @@ int b200_set_tensor(b200_engine* h, const char* name, int type, const void* data
   B200_CUDA(cudaMemcpyAsync(tmp.p, data, bytes, cudaMemcpyHostToDevice, e->stream));
   if ((rc = e->place_tensor(s, tmp.as<uint8_t>()))) return rc;
   if ((rc = e->refresh_shadow(name))) return rc;  // k-quant models: the tensor-core path's bf16 copy follows
+  e->invalidate_prefix_cache();                   // cached K/V were computed with the old weights
   B200_CUDA(cudaStreamSynchronize(e->stream));
   s.set = true;
   return 0;
@@ -251,6 +252,42 @@ int b200_detokenize(b200_engine* h, const int32_t* ids, size_t n, char* buf, siz
   Engine* e = reinterpret_cast<Engine*>(h);
   if (!e || (!ids && n) || !n_out) { set_error("null argument"); return B200_EINVAL; }
   return tok_decode(e->tok, ids, n, buf, cap, n_out);
+}
+
+int b200_prefix_match(b200_engine* h, const int32_t* ids, size_t n) {
+  Engine* e = reinterpret_cast<Engine*>(h);
+  if (!e || !ids || n < 2 || !e->use_prefix_cache) return 0;
+  const std::vector<int32_t> p(ids, ids + n);
+  int best = 0;
+  for (int s = 0; s < (int)e->slot_kv.size(); ++s) best = std::max(best, e->common_prefix(s, p));
+  return best < Engine::kMinReuse ? 0 : best;
+}
+
+int b200_chat_template(b200_engine* h, char* buf, size_t cap, size_t* n_out) {
+  Engine* e = reinterpret_cast<Engine*>(h);
+  if (!e || !n_out) { set_error("null argument"); return B200_EINVAL; }
+  const std::string& t = e->tok.chat_template;
+  *n_out = t.size();
+  if (t.size() > cap || (t.size() && !buf)) { set_error("chat template: need room for %zu bytes", t.size()); return B200_ERANGE; }
+  if (!t.empty()) memcpy(buf, t.data(), t.size());
+  return 0;
+}
+
+int b200_stop_ids(b200_engine* h, int32_t* ids, size_t cap, size_t* n_out) {
+  Engine* e = reinterpret_cast<Engine*>(h);
+  if (!e || !n_out) { set_error("null argument"); return B200_EINVAL; }
+  std::vector<int32_t> v = e->tok.stop_ids;
+  if (v.empty() && e->cfg.eos_token >= 0) v.push_back(e->cfg.eos_token);
+  *n_out = v.size();
+  if (v.size() > cap || (v.size() && !ids)) { set_error("stop ids: need room for %zu", v.size()); return B200_ERANGE; }
+  if (!v.empty()) memcpy(ids, v.data(), v.size() * 4);
+  return 0;
+}
+
+int b200_special_token(b200_engine* h, const char* text) {
+  Engine* e = reinterpret_cast<Engine*>(h);
+  if (!e || !text) return -1;
+  return e->tok.special_id(text);
 }
 
 // ---- GGUF ----------------------------------------------------------------------------------------------
@@ -648,6 +685,7 @@ int b200_bench_decode(b200_engine* h, int ctx, int n_steps, float* ms_per_step, 
   for (auto& q : e->seqs)
     if (q.r) { set_error("engine is serving requests"); return B200_ESTATE; }
   e->bs1_owner = -1;
+  e->invalidate_prefix_cache();
   int rc = e->set_active_slot(0);
   if (rc) return rc;
   if ((rc = e->ensure_graph())) return rc;
@@ -686,6 +724,7 @@ int b200_bench_batched(b200_engine* h, int n_seqs, int ctx, int n_steps, float* 
   for (auto& q : e->seqs)
     if (q.r) { set_error("engine is serving requests"); return B200_ESTATE; }
   e->bs1_owner = -1;
+  e->invalidate_prefix_cache();
   return e->bench_batched(n_seqs, ctx, n_steps, ms_per_step, last_ids);
 }
 

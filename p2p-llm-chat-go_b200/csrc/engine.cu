@@ -88,6 +88,7 @@ int Engine::init(const b200_config& c, const void* nccl_id) {
   use_fa_prefill = getenv("B200_NO_FA_PREFILL") == nullptr;
   use_mma_decode = getenv("B200_NO_MMA_DECODE") == nullptr;
   use_attn_prefetch = getenv("B200_NO_ATTN_PREFETCH") == nullptr;
+  use_prefix_cache = getenv("B200_NO_PREFIX_CACHE") == nullptr && (c.reserved & 2) == 0 && tp_size == 1;
   // measured on B200 (round 1): chaining L2 prefetches of the next kernel's weights made the step SLOWER
   // (bf16 3.18 vs 3.05 ms, Q4_K_M 1.84 vs 1.78 ms), so it is opt-in for experiments only
   use_l2_chain = getenv("B200_L2_CHAIN") != nullptr;
@@ -227,6 +228,7 @@ int Engine::init(const b200_config& c, const void* nccl_id) {
     if ((rc = alloc((void**)&active_table, (size_t)pages_per_seq * 4))) return rc;
     B200_CUDA(cudaMemcpy(active_table, block_table, (size_t)pages_per_seq * 4, cudaMemcpyDeviceToDevice));
     seqs.resize(c.max_seqs);
+    slot_kv.assign(c.max_seqs, {});
   }
   // activations + sequence state
   n_splits = 20;
@@ -549,6 +551,7 @@ static int claim_slot0(Engine* e) {
   for (auto& q : e->seqs)
     if (q.r) { set_error("engine is serving requests; synchronous hooks need an idle engine"); return B200_ESTATE; }
   e->bs1_owner = -1;
+  e->invalidate_prefix_cache(0);  // the hook is about to overwrite slot 0's K/V
   return e->set_active_slot(0);
 }
 
@@ -742,7 +745,7 @@ int Engine::ensure_prefill() {
 // sequence whose block table is `active_table` (prefill).  Otherwise row t is position pos_arr[t] of the
 // sequence in slot slot_arr[t], which then sees ctx_arr[t] tokens (batched decode).
 // Leaves the residual stream of every row in pf_x (+ pf_proj still to be added).
-int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_arr, const int32_t* ctx_arr, const int32_t* slot_arr) {
+int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_arr, const int32_t* ctx_arr, const int32_t* slot_arr, int pos0) {
   const b200_config& c = lc;
   const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn;
   cudaStream_t s = stream;
@@ -754,10 +757,10 @@ int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_ar
     int qkv_splits = max_wide_splits(n);
     const int64_t qkv_stride = (int64_t)n * (qd + 2 * kvd);
     B200_CUDA(launch_gemm_bf16_splitk(L.qkv16, qd + 2 * kvd, d, pf_xb, n, pf_qkv, qd + 2 * kvd, qkv_stride, &qkv_splits, s, &gemm_ws));
-    B200_CUDA(launch_rope_kv(pf_qkv, pf_q, L.k_cache, L.v_cache, table, rope, n, qd, kvd, c.n_kv_heads, 0, pos_arr, slot_arr, pages_per_seq,
+    B200_CUDA(launch_rope_kv(pf_qkv, pf_q, L.k_cache, L.v_cache, table, rope, n, qd, kvd, c.n_kv_heads, pos0, pos_arr, slot_arr, pages_per_seq,
                              qkv_splits, qkv_stride, s));
-    if (!pos_arr && use_fa_prefill) {  // one sequence, causal: tensor-core attention, bf16 straight into the GEMM operand
-      B200_CUDA(launch_attn_prefill(pf_q, L.k_cache, L.v_cache, table, pf_xb, n, 0, c.n_heads, c.n_kv_heads, s));
+    if (!pos_arr && (use_fa_prefill || pos0 > 0)) {  // one sequence, causal: tensor-core attention, bf16 straight into the GEMM operand
+      B200_CUDA(launch_attn_prefill(pf_q, L.k_cache, L.v_cache, table, pf_xb, n, pos0, c.n_heads, c.n_kv_heads, s));
     } else {                            // one row per sequence (batched decode): the split-KV decode kernel, a query per z
       AttnArgs t = {};
       t.q = pf_q; t.k_cache = L.k_cache; t.v_cache = L.v_cache; t.block_table = table; t.st = nullptr;
@@ -814,11 +817,12 @@ int Engine::add_rmsnorm_proj(const float* w, int n, bool have_proj) {
   return 0;
 }
 
-int Engine::prefill_gemm(int n) {
+int Engine::prefill_gemm(int n_prompt, int pos0) {
   const b200_config& c = cfg;
   const int d = c.d_model;
   cudaStream_t s = stream;
-  int rc0 = forward_gemm(n, prompt_dev, nullptr, nullptr, nullptr);
+  const int n = n_prompt - pos0;  // rows to compute: positions pos0 .. n_prompt-1
+  int rc0 = forward_gemm(n, prompt_dev + pos0, nullptr, nullptr, nullptr, pos0);
   if (rc0) return rc0;
   // hand the last position over to the batch-1 path: residual stream, then lm_head (mode 0) + token pick
   B200_CUDA(launch_take_row(pf_x, pf_proj_src, pf_proj_splits, pf_proj_stride, d, n - 1, x, s));  // prefill: never the push path
@@ -830,8 +834,9 @@ int Engine::prefill_gemm(int n) {
 
 // Puts the prompt through the model and produces the first generated token.
 // mode GEMM: tensor-core prefill; mode GEMV (or a 1-token prompt): token by token through the decode graph.
-int Engine::run_prompt(const int32_t* prompt, int n_prompt, int max_out, int greedy, int mode, const b200_sampling* sp) {
+int Engine::run_prompt(const int32_t* prompt, int n_prompt, int max_out, int greedy, int mode, const b200_sampling* sp, int reuse) {
   int rc;
+  if (reuse < 0 || reuse >= n_prompt || mode != B200_MODE_GEMM) reuse = 0;
   if (mode == B200_MODE_GEMM && n_prompt > 1) {
     if ((rc = ensure_prefill())) return rc;
     if ((rc = begin_sequence(prompt, n_prompt, max_out, greedy, sp))) return rc;
@@ -841,7 +846,7 @@ int Engine::run_prompt(const int32_t* prompt, int n_prompt, int max_out, int gre
     s0.greedy = greedy;
     B200_CUDA(cudaMemcpyAsync(st, &s0, sizeof s0, cudaMemcpyHostToDevice, stream));
     B200_CUDA(cudaStreamSynchronize(stream));
-    return prefill_gemm(n_prompt);
+    return prefill_gemm(n_prompt, reuse);
   }
   if ((rc = begin_sequence(prompt, n_prompt, max_out, greedy, sp))) return rc;
   return launch_steps(n_prompt);

@@ -144,9 +144,20 @@ struct Engine {
     int n_prompt = 0, pos = 0, delivered = 0, max_out = 0;  // pos = position of `token` (not yet in the cache)
     int32_t token = 0;
     bool greedy = true;
+    int reused = 0;                // prompt tokens whose K/V were found in the slot's cache (prefix reuse)
+    std::vector<int32_t> gen;      // tokens generated so far (host copy; with the prompt = what the slot's cache holds)
     std::chrono::steady_clock::time_point t0, t_load, t_first;
   };
   std::vector<Seq> seqs;
+  // Prefix reuse (a peer's successive suggestions share the chat history).  slot_kv[s] = the tokens whose
+  // K/V the cache of slot s still holds from the request it served last, positions 0..size-1.  A new request takes the
+  // free slot with the longest common prefix and prefills only the rest of its prompt.
+  std::vector<std::vector<int32_t>> slot_kv;
+  mutable std::mutex kv_mu;         // guards slot_kv (the worker updates it; b200_prefix_match reads it from any thread)
+  bool use_prefix_cache = true;     // off: cfg.reserved bit 1, B200_NO_PREFIX_CACHE, tensor-parallel engines
+  static constexpr int kMinReuse = 16;  // shorter common prefixes are not worth a different code path
+  int common_prefix(int slot, const std::vector<int32_t>& prompt) const;
+  void invalidate_prefix_cache(int slot = -1);  // -1: every slot (weights changed)
   int32_t* active_table = nullptr;  // block-table row used by the batch-1 graph and single-sequence prefill
   int bs1_owner = -1;               // slot whose state currently lives in StepState / prompt_dev
   bool force_batched = false;       // cfg.reserved bit 0: never use the batch-1 path for decode (tests)
@@ -200,9 +211,9 @@ struct Engine {
   bool has_shadows = false;                  // k-quant model whose bf16 shadows have been built
   uint8_t* shadow_tmp = nullptr;             // staging of refresh_shadow (largest per-layer tensor, GGUF layout)
   uint16_t* shadow_tmp16 = nullptr;
-  int prefill_gemm(int n_prompt);            // prompt_dev[0..n) -> KV cache, residual of the last position, first token
+  int prefill_gemm(int n_prompt, int pos0 = 0);  // prompt_dev[pos0..n) -> KV cache (positions below pos0 are already there), first token
   // the tensor-core layer stack over n rows: one sequence at positions 0..n-1 (arrays null) or one row per sequence
-  int forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_arr, const int32_t* ctx_arr, const int32_t* slot_arr);
+  int forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_arr, const int32_t* ctx_arr, const int32_t* slot_arr, int pos0 = 0);
   int set_active_slot(int slot);
   int ensure_batched();
   int batched_step(const std::vector<int>& slots, std::vector<int32_t>* next);
@@ -210,7 +221,8 @@ struct Engine {
   int decode_bs1_window(int slot);           // batch-1 graph steps for the only active sequence
   void finish_request(int slot, int rc, int reason);
   void deliver(int slot, const int32_t* toks, int n);
-  int run_prompt(const int32_t* prompt, int n_prompt, int max_out, int greedy, int mode, const b200_sampling* sp = nullptr);  // either prefill flavour
+  // either prefill flavour; reuse > 0 (GEMM mode): the cache already holds positions [0, reuse) of this prompt
+  int run_prompt(const int32_t* prompt, int n_prompt, int max_out, int greedy, int mode, const b200_sampling* sp = nullptr, int reuse = 0);
   void worker_loop();
 };
 

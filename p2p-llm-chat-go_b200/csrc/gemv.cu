@@ -246,26 +246,13 @@ cudaError_t launch_dual_t(const GemvArgs& a, const GemvArgs& b, cudaStream_t s, 
 }
 
 // ------------------------------------------------------------------ launch shapes
-// Shape 0: one 16-warp CTA per SM owning up to the whole shared memory (deep rings).
-// Shape 1: 8-warp CTAs that take at most half an SM, so the next kernel of the decode step is resident and
-//          prefetched while this one streams (see GemvCfg).  Chosen per engine through gemv_set_shape / B200_GEMV_SHAPE.
+// One 16-warp CTA per SM owning up to the whole shared memory (deep rings).  Measured alternative (round 2, B200):
+// 8-warp CTAs limited to half an SM (GemvCfg<8, 2..3, 2>), so that under programmatic dependent launch the next
+// kernel's CTAs sit resident and prefetched beside the running ones — slower for every matrix class (bf16 3.15 vs
+// 2.82 ms/token, Q4_K_M 2.13 vs 1.51): half the warps per SM hide less latency than the overlap wins back.
 using S0r4 = GemvCfg<16, 2, 1>;  // 4-row units
 using S0r2 = GemvCfg<16, 3, 1>;  // 2-row units
 using S0q6 = GemvCfg<16, 2, 1>;
-using S1r4 = GemvCfg<8, 2, 2>;
-using S1r2 = GemvCfg<8, 3, 2>;
-using S1q6 = GemvCfg<8, 2, 2>;
-
-int g_shape_wide = -1, g_shape_narrow = -1;  // -1: not read from the environment yet
-void read_shape_env() {
-  if (g_shape_wide >= 0) return;
-  const char* all = getenv("B200_GEMV_SHAPE");
-  const char* w = getenv("B200_GEMV_SHAPE_WIDE");
-  const char* n = getenv("B200_GEMV_SHAPE_NARROW");
-  const int dflt = all ? atoi(all) : 0;
-  g_shape_wide = w ? atoi(w) : dflt;
-  g_shape_narrow = n ? atoi(n) : dflt;
-}
 
 }  // namespace
 
@@ -275,13 +262,7 @@ cudaError_t launch_gemv_dual_qkv(int type_a, const GemvArgs& a, int type_b, cons
   static const bool off = getenv("B200_NO_DUAL_QKV") != nullptr;
   if (type_a != T_Q4_K || type_b != T_Q6_K || off) return cudaErrorNotSupported;
   if (!gemv_shape_ok(type_a, a.N, a.K, EPI_QKV) || !gemv_shape_ok(type_b, b.N, b.K, EPI_QKV)) return cudaErrorInvalidValue;
-  read_shape_env();
   const bool wide = (a.N / 4) >= sm_count * 16;
-  const int shape = wide ? g_shape_wide : g_shape_narrow;
-  if (shape == 1 && fits<FmtQ4K<4, S1r4>>(a.K) && fits<FmtQ6K<S1q6>>(b.K)) {
-    if (wide) return launch_dual_t<FmtQ4K<4, S1r4>, FmtQ6K<S1q6>, PRO_RMSNORM, EPI_QKV>(a, b, s, pdl, sm_count);
-    return launch_dual_t<FmtQ4K<2, S1r2>, FmtQ6K<S1q6>, PRO_RMSNORM, EPI_QKV>(a, b, s, pdl, sm_count);
-  }
   if (wide) return launch_dual_t<FmtQ4K<4, S0r4>, FmtQ6K<S0q6>, PRO_RMSNORM, EPI_QKV>(a, b, s, pdl, sm_count);
   return launch_dual_t<FmtQ4K<2, S0r2>, FmtQ6K<S0q6>, PRO_RMSNORM, EPI_QKV>(a, b, s, pdl, sm_count);
 }
@@ -307,7 +288,6 @@ bool gemv_shape_ok(int wtype, int64_t N, int64_t K, int epi) {
 }
 
 namespace {
-// the tensor-parallel prologue / epilogue exist for shape 0 only (they are bf16-only, 70B-sized K)
 template <class W, class Nr>
 cudaError_t launch_by_width(bool wide, int pro, int epi, const GemvArgs& a, cudaStream_t s, bool pdl, int sm) {
   return wide ? launch_f<W>(pro, epi, a, s, pdl, sm) : launch_f<Nr>(pro, epi, a, s, pdl, sm);
@@ -316,27 +296,15 @@ cudaError_t launch_by_width(bool wide, int pro, int epi, const GemvArgs& a, cuda
 
 cudaError_t launch_gemv(int wtype, int pro, int epi, const GemvArgs& a, cudaStream_t s, bool pdl, int sm_count) {
   if (!gemv_shape_ok(wtype, a.N, a.K, epi)) return cudaErrorInvalidValue;
-  read_shape_env();
   // 4 rows per unit amortise the activation loads best; matrices with fewer than one such unit per warp
   // (o / down / qkv: 4096-6144 rows) use 2-row units so that every warp of every SM streams something
   const bool wide = (a.N / 4) >= sm_count * 16;
-  const bool tp = pro == PRO_TP_RMSNORM || epi == EPI_TP_PUSH;
-  const int shape = tp ? 0 : (wide ? g_shape_wide : g_shape_narrow);
   switch (wtype) {
     case T_BF16:
-      if (a.K % 512 == 0) {
-        if (shape == 1 && fits<FmtBF16<512, 4, S1r4>>(a.K) && fits<FmtBF16<512, 2, S1r2>>(a.K))
-          return launch_by_width<FmtBF16<512, 4, S1r4>, FmtBF16<512, 2, S1r2>>(wide, pro, epi, a, s, pdl, sm_count);
-        return launch_by_width<FmtBF16<512, 4, S0r4>, FmtBF16<512, 2, S0r2>>(wide, pro, epi, a, s, pdl, sm_count);
-      }
+      if (a.K % 512 == 0) return launch_by_width<FmtBF16<512, 4, S0r4>, FmtBF16<512, 2, S0r2>>(wide, pro, epi, a, s, pdl, sm_count);
       return launch_by_width<FmtBF16<256, 4, S0r4>, FmtBF16<256, 2, S0r2>>(wide, pro, epi, a, s, pdl, sm_count);
-    case T_Q4_K:
-      if (shape == 1 && fits<FmtQ4K<4, S1r4>>(a.K) && fits<FmtQ4K<2, S1r2>>(a.K))
-        return launch_by_width<FmtQ4K<4, S1r4>, FmtQ4K<2, S1r2>>(wide, pro, epi, a, s, pdl, sm_count);
-      return launch_by_width<FmtQ4K<4, S0r4>, FmtQ4K<2, S0r2>>(wide, pro, epi, a, s, pdl, sm_count);
-    case T_Q6_K:
-      if (shape == 1 && fits<FmtQ6K<S1q6>>(a.K)) return launch_f<FmtQ6K<S1q6>>(pro, epi, a, s, pdl, sm_count);
-      return launch_f<FmtQ6K<S0q6>>(pro, epi, a, s, pdl, sm_count);
+    case T_Q4_K: return launch_by_width<FmtQ4K<4, S0r4>, FmtQ4K<2, S0r2>>(wide, pro, epi, a, s, pdl, sm_count);
+    case T_Q6_K: return launch_f<FmtQ6K<S0q6>>(pro, epi, a, s, pdl, sm_count);
   }
   return cudaErrorInvalidValue;
 }

@@ -518,10 +518,10 @@ DEVINL void epilogue(const GemvArgs& a, int unit, int lane, const float* acc, fl
 #pragma unroll
       for (int r = 0; r < R; ++r) dst[r] = acc[r];
     }
-  } else if (EPI == EPI_RESID) {
+  } else if (EPI == EPI_RESID) {  // acc already holds residual + W.x (the residual was fetched at the start of the unit)
     if (lane == 0) {
 #pragma unroll
-      for (int r = 0; r < R; ++r) a.y[row0 + r] = __ldcg(a.y + row0 + r) + acc[r];
+      for (int r = 0; r < R; ++r) a.y[row0 + r] = acc[r];
     }
   } else if (EPI == EPI_SWIGLU) {  // rows interleaved gate,up,gate,up
 #pragma unroll

@@ -27,6 +27,21 @@ int Engine::set_active_slot(int slot) {
   return 0;
 }
 
+int Engine::common_prefix(int slot, const std::vector<int32_t>& prompt) const {
+  std::lock_guard<std::mutex> lk(kv_mu);
+  const std::vector<int32_t>& have = slot_kv[slot];
+  const size_t lim = std::min(have.size(), prompt.size() - 1);  // at least one prompt token is always evaluated
+  size_t n = 0;
+  while (n < lim && have[n] == prompt[n]) ++n;
+  return (int)n;
+}
+
+void Engine::invalidate_prefix_cache(int slot) {
+  std::lock_guard<std::mutex> lk(kv_mu);
+  if (slot >= 0) { if (slot < (int)slot_kv.size()) slot_kv[slot].clear(); return; }
+  for (auto& v : slot_kv) v.clear();
+}
+
 int Engine::ensure_batched() {
   if (batched_ready) return 0;
   int rc = ensure_prefill();
@@ -136,6 +151,7 @@ void Engine::deliver(int slot, const int32_t* toks, int n) {
   std::lock_guard<std::mutex> lk(r->mu);
   for (int i = 0; i < n; ++i) {
     r->tokens.push_back(toks[i]);
+    q.gen.push_back(toks[i]);
     ++q.delivered;
     if (toks[i] == cfg.eos_token || q.delivered >= q.max_out) r->complete = true;
   }
@@ -152,12 +168,21 @@ void Engine::finish_request(int slot, int rc, int reason) {
     r->stats.prompt_eval_ns = ns_between(q.t_load, q.delivered ? q.t_first : t_end);
     r->stats.eval_ns = q.delivered ? ns_between(q.t_first, t_end) : 0;
     r->stats.total_ns = ns_between(q.t0, t_end);
-    r->stats.prompt_eval_count = q.n_prompt;
+    r->stats.prompt_eval_count = q.n_prompt - q.reused;  // tokens actually evaluated (as Ollama reports with a warm cache)
     r->stats.eval_count = q.delivered;
     r->stats.done_reason = rc ? 3 : reason;
     r->error = rc;
     r->finished = true;
     r->cv.notify_all();
+  }
+  // what this slot's cache holds now: the prompt and every generated token that was fed back (all but the last)
+  {
+    std::lock_guard<std::mutex> lk(kv_mu);
+    slot_kv[slot].clear();
+    if (use_prefix_cache && rc == 0 && q.delivered > 0) {
+      slot_kv[slot] = r->prompt;
+      slot_kv[slot].insert(slot_kv[slot].end(), q.gen.begin(), q.gen.end() - 1);
+    }
   }
   q.r = nullptr;
   if (bs1_owner == slot) bs1_owner = -1;
@@ -183,7 +208,11 @@ int Engine::admit(Request* r, int slot) {
   if (cfg.max_seqs > 1 && (rc = ensure_batched())) return rc;
   if ((rc = set_active_slot(slot))) return rc;
   q.t_load = std::chrono::steady_clock::now();
-  if ((rc = run_prompt(r->prompt.data(), q.n_prompt, max_out, q.greedy ? 1 : 0, r->sp.prefill_mode, &r->sp))) return rc;
+  int reuse = (use_prefix_cache && gemm) ? common_prefix(slot, r->prompt) : 0;
+  if (reuse < kMinReuse) reuse = 0;
+  invalidate_prefix_cache(slot);  // being overwritten from position `reuse` on; re-recorded when the request finishes
+  q.reused = reuse;
+  if ((rc = run_prompt(r->prompt.data(), q.n_prompt, max_out, q.greedy ? 1 : 0, r->sp.prefill_mode, &r->sp, reuse))) return rc;
   bs1_owner = slot;
   if (batched_ready) {  // per-slot history and sampling options for the batched path
     SampleParams sp0 = {};
@@ -304,8 +333,10 @@ void Engine::worker_loop() {
     // tensor-parallel engines are driven SPMD (every rank makes the same calls): admission timing would differ
     // between ranks, so they serve one request at a time; several slots exist only for b200_bench_batched
     if (tp_size > 1) budget = active.empty() ? 1 : 0;
-    for (int s = 0; s < (int)seqs.size() && budget > 0; ++s) {
-      if (seqs[s].r) continue;
+    while (budget > 0) {
+      int n_free = 0;
+      for (auto& q : seqs) n_free += q.r ? 0 : 1;
+      if (n_free == 0) break;
       --budget;
       Request* r = nullptr;
       {
@@ -313,6 +344,18 @@ void Engine::worker_loop() {
         if (queue.empty()) break;
         r = queue.front();
         queue.pop_front();
+      }
+      // the free slot whose cache shares the longest prefix with this prompt; without a usable prefix, a slot that
+      // holds nothing (so other peers' histories stay cached), else the first free one
+      int s = -1, best = -1;
+      for (int i = 0; i < (int)seqs.size(); ++i) {
+        if (seqs[i].r) continue;
+        int score = use_prefix_cache ? common_prefix(i, r->prompt) : 0;
+        if (score < kMinReuse) {
+          std::lock_guard<std::mutex> lk(kv_mu);
+          score = slot_kv[i].empty() ? 1 : 0;
+        }
+        if (score > best) { best = score; s = i; }
       }
       const int rc = admit(r, s);
       if (rc) { if (!seqs[s].r) seqs[s].r = r; finish_request(s, rc, 3); continue; }

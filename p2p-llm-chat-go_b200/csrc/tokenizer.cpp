@@ -199,6 +199,7 @@ std::string Tokenizer::load(const GgufFile& f) {
       max_token_bytes_ = std::max(max_token_bytes_, raw.size());
     } else {
       is_special_[i] = 1;  // control / user-defined / unused: never produced by encode, rendered as nothing
+      special_to_id_.emplace(toks->strs[i], (int32_t)i);
     }
   }
   if (const GgufValue* merges = f.kv("tokenizer.ggml.merges")) {
@@ -213,7 +214,24 @@ std::string Tokenizer::load(const GgufFile& f) {
   }
   bos_id = (int32_t)f.get_u("tokenizer.ggml.bos_token_id", 128000);
   eos_id = (int32_t)f.get_u("tokenizer.ggml.eos_token_id", 128009);
+  chat_template = f.get_s("tokenizer.chat_template", "");
+  stop_ids.clear();
+  auto add_stop = [&](int64_t id) {
+    if (id < 0 || (size_t)id >= V) return;
+    for (int32_t s : stop_ids) if (s == (int32_t)id) return;
+    stop_ids.push_back((int32_t)id);
+  };
+  add_stop(eos_id);
+  for (const char* key : {"tokenizer.ggml.eot_token_id", "tokenizer.ggml.eom_token_id"})
+    if (f.kv(key)) add_stop((int64_t)f.get_u(key, 0));
+  for (const char* text : {"<|eot_id|>", "<|eom_id|>", "<|end_of_text|>", "<|im_end|>", "<|endoftext|>", "<|end|>", "</s>"})
+    add_stop(special_id(text));
   return "";
+}
+
+int32_t Tokenizer::special_id(const std::string& text) const {
+  auto it = special_to_id_.find(text);
+  return it == special_to_id_.end() ? -1 : it->second;
 }
 
 // One pre-token -> ids.  As llama.cpp does for "llama-bpe" (ignore_merges) and tiktoken does by construction, a

@@ -4,8 +4,5 @@ out=gpurun_out/ab.log; : > $out
 for fmt in bf16 q4; do
   python scratch/ab_decode.py $fmt >> $out 2>&1
   B200_NO_ATTN_PREFETCH=1 python scratch/ab_decode.py $fmt >> $out 2>&1
-  B200_GEMV_SHAPE=1 python scratch/ab_decode.py $fmt >> $out 2>&1
-  B200_GEMV_SHAPE_NARROW=1 python scratch/ab_decode.py $fmt >> $out 2>&1
-  B200_GEMV_SHAPE_WIDE=1 python scratch/ab_decode.py $fmt >> $out 2>&1
 done
 grep -E "^AB|Error|error" $out

@@ -1,4 +1,4 @@
-"""Python mirror of the reference's caller, for contract tests and the load generator.
+"""Python mirror of the reference's caller, for the contract tests (test infrastructure, not part of the product).
 
 `ai_suggest` behaves like the function of the same name at web/streamlit_app.py:89-101: same environment
 variables (OLLAMA_URL, LLM_MODEL, web/streamlit_app.py:27-28), same prompt wrapper (:93), same request body

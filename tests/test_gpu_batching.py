@@ -156,7 +156,7 @@ def test_one_slot_engine_serves_queued_sampled_requests_like_solo_runs(pkg):
     request that finds another one waiting behind it must keep decoding on the batch-1 graph, with its own sampling
     options, exactly as if it were alone.  Two sampled requests queued back to back == the same two run one by one."""
     cfg = tiny_cfg(pkg, 0, n_layers=2, seed=77, max_ctx=128)
-    cfg.max_seqs = 1
+    cfg.max_seqs, cfg.reserved = 1, 2   # reserved bit 1: no prefix reuse, so the repeat runs recompute exactly what the solo runs did
     prompts = [np.random.default_rng(s).integers(0, cfg.vocab, n).astype(np.int32) for s, n in ((1, 9), (2, 14))]
 
     def sampling(i):
@@ -200,3 +200,58 @@ def test_set_tensor_after_a_gemm_forward_refreshes_the_tensor_core_copy(pkg):
         for tk in toks:
             want0 = ora.forward([tk], mode=0)
         assert np.abs(gemv - want0).max() <= 1e-3 * max(1.0, np.abs(want0).max())
+
+
+def test_prefix_kv_reuse_across_a_peers_successive_suggestions(pkg):
+    """the UI re-sends the same chat history with one more message per click
+    (web/streamlit_app.py:117-133, :161-165).  A request whose prompt starts with what a free slot's cache still holds
+    is prefilled from the first differing token only: prompt_eval_count drops to the new tokens, the answer is the one
+    a cold engine gives (checked against the CPU oracle), and an unrelated prompt is not affected."""
+    eng, ora, cfg = engine_and_oracle(pkg, 0, n_layers=2, seed=79, source="synth", max_ctx=512)
+    eng.close()
+    cfg.max_seqs, cfg.seed = 2, 79
+    n_new = 10
+    rng = np.random.default_rng(9)
+    history = rng.integers(0, cfg.vocab, 300).astype(np.int32)
+    sp = pkg.default_sampling()
+    sp.temperature, sp.num_predict, sp.prefill_mode = 0.0, n_new, pkg.MODE_GEMM
+
+    def run(eng, prompt):
+        r = eng.submit(prompt, sp)
+        toks = list(r.tokens())
+        st = r.stats()
+        r.free()
+        return toks, st
+
+    def oracle(prompt):  # lone request: tensor-core prefill (mode 1), then the batch-1 decode path (mode 0)
+        w, m = ora.generate_greedy(prompt, n_new, prefill_mode=1)
+        return w.tolist(), m.min()
+    with pkg.Engine(cfg) as eng:
+        first, st1 = run(eng, history)
+        assert st1.prompt_eval_count == 300
+        # same history + the first reply + a new message of 20 tokens
+        longer = np.concatenate([history, np.array(first[:-1], np.int32), rng.integers(0, cfg.vocab, 20).astype(np.int32)])
+        second, st2 = run(eng, longer)
+        assert st2.prompt_eval_count == len(longer) - (300 + n_new - 1), st2.prompt_eval_count   # only the new tokens
+        assert st2.load_ns + st2.prompt_eval_ns < st1.load_ns + st1.prompt_eval_ns                 # and a shorter TTFT
+        want, margin = oracle(longer)
+        if margin > 4 * TOL:
+            assert second == want
+        # an identical prompt again: everything but its last token is cached
+        third, st3 = run(eng, longer)
+        assert st3.prompt_eval_count == 1 and (third == second or margin <= 4 * TOL)
+        # a different peer's prompt shares nothing: full prefill, right answer
+        other = rng.integers(0, cfg.vocab, 120).astype(np.int32)
+        got, st4 = run(eng, other)
+        assert st4.prompt_eval_count == 120
+        want_o, m_o = oracle(other)
+        if m_o > 4 * TOL:
+            assert got == want_o
+        # ... and it went to the other slot, so the first peer's history is still warm
+        again, st5 = run(eng, np.concatenate([longer, np.array(second[:3], np.int32)]))
+        assert st5.prompt_eval_count <= 4
+    cfg.reserved = 2                                   # bit 1: prefix reuse off
+    with pkg.Engine(cfg) as eng:
+        a, s1 = run(eng, history)
+        b, s2 = run(eng, history)
+        assert s2.prompt_eval_count == 300 and a == b == first

@@ -51,8 +51,7 @@ def server():
 def test_reference_request_replay(server):
     """The exact call of web/streamlit_app.py:91-95 and the reads of :96-98."""
     pkg = ge.load_package()
-    from importlib import import_module
-    client = import_module("p2p_llm_chat_go_b200.client")
+    from tests import ref_client as client
     body = client.suggestion_request("Hey! How's it going?")
     assert set(body) == {"model", "prompt", "stream"} and body["stream"] is False and body["model"] == "llama3.1"
     resp = requests.post(f"{server}/api/generate", json=body, timeout=60)
@@ -177,3 +176,135 @@ def test_malformed_requests_do_not_take_the_server_down(server):
     ok = requests.post(f"{server}/api/generate", json={"model": "llama3.1", "prompt": "still there?", "stream": False,
                                                         "options": {"num_predict": 4}}, timeout=60)
     assert ok.status_code == 200 and ok.json()["done"] is True
+
+
+# ---- Ollama request fields beyond what the reference sends ------------------------------
+def _gen(server, **kw):
+    body = {"model": "llama3.1", "prompt": "tell me something", "stream": False, "options": {"temperature": 0, "num_predict": 24}}
+    opts = kw.pop("options", {})
+    body.update(kw)
+    body["options"] = dict(body["options"], **opts)
+    return requests.post(f"{server}/api/generate", json=body, timeout=60)
+
+
+def test_stop_sequences_cut_the_reply(server):
+    base = _gen(server).json()
+    text = base["response"]
+    assert base["done_reason"] == "length" and len(text) > 12
+    stop = text[7:11]
+    cut = text.index(stop)                                 # the first place that sequence occurs
+    for stop_opt in (stop, ["\x00never", stop]):
+        one = _gen(server, options={"stop": stop_opt}).json()
+        assert one["response"] == text[:cut] and one["done_reason"] == "stop" and one["eval_count"] <= base["eval_count"]
+    with requests.post(f"{server}/api/generate", json={"model": "llama3.1", "prompt": "tell me something",
+                       "options": {"temperature": 0, "num_predict": 24, "stop": [stop]}}, stream=True, timeout=60) as r:
+        objs = [json.loads(line) for line in r.iter_lines() if line]
+    assert "".join(o["response"] for o in objs) == text[:cut] and objs[-1]["done_reason"] == "stop"
+    assert _gen(server, options={"stop": 5}).status_code == 400
+
+
+def test_num_ctx_limits_window_and_is_validated(server):
+    assert _gen(server, options={"num_ctx": 100000}).status_code == 400        # beyond LLMD_MAX_CTX=512: refused, not ignored
+    assert _gen(server, options={"num_ctx": "big"}).status_code == 400
+    small = _gen(server, prompt="window test", options={"num_ctx": 64, "num_predict": -1}).json()   # until the 64-token window is full
+    assert small["done_reason"] == "length" and len(small["context"]) == 64 + 1        # 64 in the cache + the last token
+    # a prompt longer than the window is cut from the front (Ollama's behaviour), never an error
+    long = _gen(server, prompt="x" * 400, options={"num_ctx": 64, "num_predict": 8}).json()
+    assert long["done"] is True and long["eval_count"] == 8 and long["prompt_eval_count"] <= 64 - 8
+
+
+def test_context_field_continues_a_conversation(server):
+    first = _gen(server, prompt="first message").json()
+    ctx = first["context"]
+    second = _gen(server, prompt="and then?", context=ctx).json()
+    assert second["context"][:len(ctx)] == ctx and len(second["context"]) > len(ctx) + second["eval_count"] - 1
+    # the earlier turns were still in a slot's KV cache: only the new turn was evaluated
+    assert second["prompt_eval_count"] < len(second["context"]) - second["eval_count"] - len(ctx) + 8
+    assert _gen(server, context=[1, 2, 10 ** 9]).status_code == 400
+    assert _gen(server, context="nope").status_code == 400
+
+
+def test_template_field_and_its_limits(server):
+    a = _gen(server, prompt="P", system="S", template="{{ if .System }}sys={{ .System }};{{ end }}q={{ .Prompt }};a={{ .Response }}ignored").json()
+    b = _gen(server, prompt="sys=S;q=P;a=", raw=True).json()                   # the same text, passed raw
+    assert a["response"] == b["response"] and a["prompt_eval_count"] + 0 >= 1
+    assert a["context"][:12] == list(b"sys=S;q=P;a=")
+    c = _gen(server, prompt="P", template="{{- if .System }}never{{ end -}}  q={{ .Prompt }}").json()
+    assert c["context"][:3] == list(b"q=P")
+    r = _gen(server, template="{{ range .Messages }}x{{ end }}")
+    assert r.status_code == 400 and "unsupported" in r.json()["error"]
+    assert _gen(server, template="{{ if .System }}open").status_code == 400
+
+
+def test_keep_alive_format_and_ps(server):
+    assert _gen(server, keep_alive="10m").status_code == 200 and _gen(server, keep_alive=-1).status_code == 200
+    assert _gen(server, keep_alive="soon").status_code == 400 and _gen(server, keep_alive=[1]).status_code == 400
+    load = requests.post(f"{server}/api/generate", json={"model": "llama3.1", "keep_alive": "1h"}, timeout=10).json()
+    assert load["done"] is True and load["done_reason"] == "load" and load["response"] == ""
+    unload = requests.post(f"{server}/api/generate", json={"model": "llama3.1", "keep_alive": 0}, timeout=10).json()
+    assert unload["done_reason"] == "unload"
+    assert _gen(server).status_code == 200                                     # ... and the model is of course still served
+    ps = requests.get(f"{server}/api/ps", timeout=10).json()["models"][0]
+    assert ps["name"] == "llama3.1:latest" and "expires_at" in ps and ps["size_vram"] > 0
+    fmt = _gen(server, format="json")
+    assert fmt.status_code == 400 and "format" in fmt.json()["error"]
+    assert _gen(server, format="").status_code == 200
+
+
+def test_one_url_spreads_sessions_over_several_engines():
+    """the reference has ONE OLLAMA_URL (web/streamlit_app.py:27); llmd with LLMD_GPUS owns an engine per
+    listed device behind it.  Two engines (both on GPU 0 here: the test box has one): concurrent requests land on
+    both, replies equal a single-engine server's, and a peer's follow-up goes where its history is cached."""
+    def start(gpus):
+        port = _free_port()
+        env = dict(os.environ, LLMD_ADDR=f"127.0.0.1:{port}", LLMD_TINY="2", LLMD_MAX_CTX="512", LLMD_SEED="7", LLMD_GPUS=gpus, LLMD_MAX_SEQS="8")
+        proc = subprocess.Popen([LLMD], env=env, stderr=subprocess.PIPE, text=True)
+        url = f"http://127.0.0.1:{port}"
+        for _ in range(600):
+            if proc.poll() is not None:
+                raise RuntimeError("llmd exited: " + proc.stderr.read())
+            try:
+                if requests.get(url + "/", timeout=1).status_code == 200:
+                    return proc, url
+            except requests.RequestException:
+                time.sleep(0.1)
+        proc.kill()
+        raise RuntimeError("llmd did not come up")
+
+    def metrics(url):
+        out = {}
+        for ln in requests.get(url + "/metrics", timeout=10).text.splitlines():
+            if ln and not ln.startswith("#"):
+                k, v = ln.rsplit(" ", 1)
+                out[k] = float(v)
+        return out
+    one_p, one = start("0")
+    two_p, two = start("0,0")
+    try:
+        prompts = [f"peer {i} says hello to everyone in the room" for i in range(12)]
+        replies = {}
+
+        def peer(url, i):
+            replies[(url, i)] = requests.post(f"{url}/api/generate", json={"model": "llama3.1", "prompt": prompts[i], "stream": False,
+                                              "options": {"temperature": 0, "num_predict": 8}}, timeout=120).json()
+        for url in (one, two):
+            ts = [threading.Thread(target=peer, args=(url, i)) for i in range(12)]
+            [t.start() for t in ts]
+            [t.join() for t in ts]
+        m = metrics(two)
+        assert m["llmd_gpus"] == 2
+        # both engines report device 0 here: the per-GPU line appears once per engine
+        txt = requests.get(two + "/metrics", timeout=10).text
+        counts = [float(ln.rsplit(" ", 1)[1]) for ln in txt.splitlines() if ln.startswith("llmd_gpu_requests_total{")]
+        assert len(counts) == 2 and sum(counts) == 12 and min(counts) >= 3, counts       # spread, not piled on one engine
+        same = sum(replies[(one, i)]["response"] == replies[(two, i)]["response"] for i in range(12))
+        assert same >= 10, same     # batch composition differs between the servers; a near-tie may flip at most rarely
+        # follow-up of peer 5 (history + reply + new text): evaluated where the history is cached -> few new tokens
+        r5 = replies[(two, 5)]
+        follow = requests.post(f"{two}/api/generate", json={"model": "llama3.1", "prompt": "and what next?", "context": r5["context"], "stream": False,
+                               "options": {"temperature": 0, "num_predict": 4}}, timeout=60).json()
+        assert follow["prompt_eval_count"] < len(r5["context"]) // 2, (follow["prompt_eval_count"], len(r5["context"]))
+    finally:
+        for p in (one_p, two_p):
+            p.terminate()
+            p.wait(timeout=10)
