@@ -162,6 +162,16 @@ void Engine::finish_request(int slot, int rc, int reason) {
   Seq& q = seqs[slot];
   Request* r = q.r;
   const auto t_end = std::chrono::steady_clock::now();
+  // what this slot's cache holds now: the prompt and every generated token that was fed back (all but the last).
+  // Before `finished` is raised: from then on the client may free the request
+  {
+    std::lock_guard<std::mutex> lk(kv_mu);
+    slot_kv[slot].clear();
+    if (use_prefix_cache && rc == 0 && q.delivered > 0) {
+      slot_kv[slot] = r->prompt;
+      slot_kv[slot].insert(slot_kv[slot].end(), q.gen.begin(), q.gen.end() - 1);
+    }
+  }
   {
     std::lock_guard<std::mutex> lk(r->mu);
     r->stats.load_ns = ns_between(q.t0, q.t_load);
@@ -174,15 +184,6 @@ void Engine::finish_request(int slot, int rc, int reason) {
     r->error = rc;
     r->finished = true;
     r->cv.notify_all();
-  }
-  // what this slot's cache holds now: the prompt and every generated token that was fed back (all but the last)
-  {
-    std::lock_guard<std::mutex> lk(kv_mu);
-    slot_kv[slot].clear();
-    if (use_prefix_cache && rc == 0 && q.delivered > 0) {
-      slot_kv[slot] = r->prompt;
-      slot_kv[slot].insert(slot_kv[slot].end(), q.gen.begin(), q.gen.end() - 1);
-    }
   }
   q.r = nullptr;
   if (bs1_owner == slot) bs1_owner = -1;
