@@ -88,7 +88,10 @@ typedef struct b200_sampling {
 } b200_sampling;
 #define B200_MAX_TOP_K 256
 
-/* Per-request counters = the *_duration / *_count fields of Ollama's final JSON object (nanoseconds). */
+/* Per-request counters = the *_duration / *_count fields of Ollama's final JSON object (nanoseconds).
+ * Time runs from b200_submit: load_ns = wait for a sequence slot + set-up, prompt_eval_ns = prefill up to the first
+ * token (so load_ns + prompt_eval_ns is the time to first token the caller sees), eval_ns = first to last token.
+ * prompt_eval_count = prompt tokens actually evaluated (less than the prompt when a cached prefix was reused). */
 typedef struct b200_stats {
   int64_t total_ns, load_ns, prompt_eval_ns, eval_ns;
   int32_t prompt_eval_count, eval_count;

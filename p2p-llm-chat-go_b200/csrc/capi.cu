@@ -428,6 +428,7 @@ int b200_submit(b200_engine* h, const int32_t* prompt_ids, size_t n, const b200_
   r->e = e;
   r->prompt.assign(prompt_ids, prompt_ids + n);  // copied: the caller's buffer is free after return
   if (s) r->sp = *s; else b200_default_sampling(&r->sp);
+  r->t_submit = std::chrono::steady_clock::now();
   {
     std::lock_guard<std::mutex> lk(e->qmu);
     e->queue.push_back(r);

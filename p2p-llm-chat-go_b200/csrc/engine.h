@@ -235,6 +235,7 @@ struct Request {
   std::deque<int32_t> tokens;
   bool finished = false, cancelled = false, done_delivered = false;
   bool complete = false;  // the final token (EOS / length) has been queued
+  std::chrono::steady_clock::time_point t_submit;  // b200_submit: durations count from here, so they include queueing
   int error = 0;
   b200_stats stats{};
 };

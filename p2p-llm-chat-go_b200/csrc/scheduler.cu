@@ -195,7 +195,7 @@ int Engine::admit(Request* r, int slot) {
   Seq& q = seqs[slot];
   q = Seq();
   q.r = r;
-  q.t0 = std::chrono::steady_clock::now();
+  q.t0 = r->t_submit;  // the wait for a free slot counts (it is part of what the peer waits for): it lands in load_ns
   q.n_prompt = (int)r->prompt.size();
   int max_out = r->sp.num_predict > 0 ? r->sp.num_predict : cfg.max_ctx;
   if (q.n_prompt + max_out - 1 > cfg.max_ctx) max_out = cfg.max_ctx - q.n_prompt + 1;
