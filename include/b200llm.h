@@ -103,6 +103,9 @@ typedef struct b200_stats {
 B200_API const char* b200_last_error(void);
 B200_API const char* b200_version(void);
 B200_API int b200_device_count(void);
+/* Kernels of this library launched on a GPU by this process so far (graph replays count their kernel nodes):
+ * what bench.py reports as gpu_launches, and a cheap way for a host to see that work really ran on the device. */
+B200_API unsigned long long b200_launch_count(void);
 B200_API void b200_default_sampling(b200_sampling* s);          /* Ollama defaults */
 B200_API void b200_llama31_8b(b200_config* cfg);                /* shapes of Llama-3.1-8B   */
 B200_API void b200_llama31_70b(b200_config* cfg);               /* shapes of Llama-3.1-70B  */

@@ -489,6 +489,13 @@ ORC_API orc_model* orc_model_new(const orc_config* c) {
 ORC_API void orc_model_free(orc_model* m) { delete m; }
 ORC_API void orc_model_reset(orc_model* m) { m->n_past = 0; }
 ORC_API int orc_model_n_past(orc_model* m) { return m->n_past; }
+// Rewind to the first n cached positions (n <= n_past): lets a timed sample decode a few tokens again and again from
+// the same long context without paying its prefill each time.
+ORC_API int orc_model_truncate(orc_model* m, int n) {
+  if (n < 0 || n > m->n_past) return -1;
+  m->n_past = n;
+  return 0;
+}
 
 // Borrow (no copy) a tensor in GGUF naming: token_embd.weight, blk.N.{attn_norm,attn_q,attn_k,attn_v,
 // attn_output,ffn_norm,ffn_gate,ffn_up,ffn_down}.weight, output_norm.weight, output.weight.

@@ -59,6 +59,7 @@ def lib():
         L.orc_model_free.argtypes = [vp]
         L.orc_model_reset.argtypes = [vp]
         L.orc_model_n_past.argtypes = [vp]
+        L.orc_model_truncate.argtypes = [vp, i32]
         L.orc_model_set_tensor.argtypes = [vp, C.c_char_p, i32, vp, i64, i64]
         L.orc_model_forward.argtypes = [vp, vp, i32, i32, vp, i32]
         L.orc_argmax.argtypes = [vp, i32, vp]
@@ -178,6 +179,10 @@ class Model:
 
     def reset(self):
         lib().orc_model_reset(self.h)
+
+    def truncate(self, n):
+        if lib().orc_model_truncate(self.h, n):
+            raise ValueError(f"cannot rewind to {n} positions")
 
     def forward(self, toks, mode, all_logits=False):
         toks = _c(toks, np.int32).reshape(-1)

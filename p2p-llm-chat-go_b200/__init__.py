@@ -98,6 +98,7 @@ def lib():
         "b200_stats_get": (i32, [vp, C.POINTER(Stats)]),
         "b200_cancel": (None, [vp]),
         "b200_free": (None, [vp]),
+        "b200_launch_count": (C.c_ulonglong, []),
         "b200_chat_template": (i32, [vp, vp, sz, C.POINTER(sz)]),
         "b200_stop_ids": (i32, [vp, vp, sz, C.POINTER(sz)]),
         "b200_special_token": (i32, [vp, C.c_char_p]),
@@ -204,6 +205,10 @@ def attn_decode(q, K, V, n_heads, n_kv_heads):
     out = np.empty(n_heads * 128, np.float32)
     _check(lib().b200_attn_decode(_p(q), _p(K), _p(V), n_ctx, n_heads, n_kv_heads, _p(out)))
     return out
+
+
+def launch_count():
+    return int(lib().b200_launch_count())
 
 
 def attn_decode_noalloc(q_ptr, k_cache_ptr, v_cache_ptr, block_table_ptr, n_ctx, n_heads, n_kv_heads, out_ptr, stream=0):

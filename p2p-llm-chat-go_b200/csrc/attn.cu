@@ -219,18 +219,18 @@ cudaError_t launch_attn_decode(const AttnArgs& a, cudaStream_t s, bool pdl) {
   // the batch-1 decode step (one query, the engine's own block table, cache rows readable ahead of the dependency)
   if (a.prefetch_tokens > 0 && a.n_queries <= 1 && !a.q_ctx && !a.q_slot) {
     switch (a.n_heads / a.n_kv_heads) {
-      case 1: return cudaLaunchKernelEx(&cfg, attn_decode_fast_kernel<1>, a);
-      case 2: return cudaLaunchKernelEx(&cfg, attn_decode_fast_kernel<2>, a);
-      case 4: return cudaLaunchKernelEx(&cfg, attn_decode_fast_kernel<4>, a);
-      case 8: return cudaLaunchKernelEx(&cfg, attn_decode_fast_kernel<8>, a);
+      case 1: return count_launch(), cudaLaunchKernelEx(&cfg, attn_decode_fast_kernel<1>, a);
+      case 2: return count_launch(), cudaLaunchKernelEx(&cfg, attn_decode_fast_kernel<2>, a);
+      case 4: return count_launch(), cudaLaunchKernelEx(&cfg, attn_decode_fast_kernel<4>, a);
+      case 8: return count_launch(), cudaLaunchKernelEx(&cfg, attn_decode_fast_kernel<8>, a);
     }
     return cudaErrorInvalidValue;
   }
   switch (a.n_heads / a.n_kv_heads) {
-    case 1: return cudaLaunchKernelEx(&cfg, attn_decode_kernel<1>, a);
-    case 2: return cudaLaunchKernelEx(&cfg, attn_decode_kernel<2>, a);
-    case 4: return cudaLaunchKernelEx(&cfg, attn_decode_kernel<4>, a);
-    case 8: return cudaLaunchKernelEx(&cfg, attn_decode_kernel<8>, a);
+    case 1: return count_launch(), cudaLaunchKernelEx(&cfg, attn_decode_kernel<1>, a);
+    case 2: return count_launch(), cudaLaunchKernelEx(&cfg, attn_decode_kernel<2>, a);
+    case 4: return count_launch(), cudaLaunchKernelEx(&cfg, attn_decode_kernel<4>, a);
+    case 8: return count_launch(), cudaLaunchKernelEx(&cfg, attn_decode_kernel<8>, a);
   }
   return cudaErrorInvalidValue;
 }

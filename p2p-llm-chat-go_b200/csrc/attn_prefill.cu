@@ -353,7 +353,7 @@ cudaError_t launch_attn_prefill(const float* q, const uint16_t* k_cache, const u
   {                                                                                                                  \
     cudaError_t e_ = cudaFuncSetAttribute(attn_prefill_kernel<G_>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem); \
     if (e_ != cudaSuccess) return e_;                                                                                \
-    attn_prefill_kernel<G_><<<grid, G_ * 32, kSmem, s>>>
+    count_launch(); attn_prefill_kernel<G_><<<grid, G_ * 32, kSmem, s>>>
   switch (n_heads / n_kv_heads) {
     case 1: LAUNCH(1)(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); } break;
     case 2: LAUNCH(2)(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); } break;
@@ -377,7 +377,7 @@ cudaError_t launch_attn_decode_batched(const AttnArgs& a, uint16_t* out_bf16, cu
     if (e_ != cudaSuccess) return e_;                                                                                      \
     e_ = cudaFuncSetAttribute(attn_decode_mma_kernel<G_>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);            \
     if (e_ != cudaSuccess) return e_;                                                                                      \
-    attn_decode_mma_kernel<G_><<<grid, 128, kSmem, s>>>(a.q, a.k_cache, a.v_cache, a.block_table, a.q_ctx, a.q_slot,       \
+    count_launch(); attn_decode_mma_kernel<G_><<<grid, 128, kSmem, s>>>(a.q, a.k_cache, a.v_cache, a.block_table, a.q_ctx, a.q_slot,       \
                                                         a.pages_per_seq, a.q_stride, a.n_kv_heads, a.out, out_bf16);        \
   }
   switch (a.n_heads / a.n_kv_heads) {

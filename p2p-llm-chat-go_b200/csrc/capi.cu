@@ -90,6 +90,8 @@ extern "C" {
 const char* b200_last_error(void) { return last_error(); }
 const char* b200_version(void) { return "b200llm 0.1 (sm_100a)"; }
 
+unsigned long long b200_launch_count(void) { return launch_count(); }
+
 int b200_device_count(void) {
   int n = 0;
   if (cudaGetDeviceCount(&n) != cudaSuccess) { (void)cudaGetLastError(); return 0; }

@@ -3,6 +3,7 @@
 // gemv.cu / attn.cu / misc.cu / gemm.cu / sampler.cu.
 #include "engine.h"
 
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdarg>
@@ -13,6 +14,12 @@
 namespace b200 {
 
 void tp_destroy(void* comm);
+
+static std::atomic<unsigned long long> g_launches{0};
+static thread_local bool g_launch_pause = false;
+void count_launch(unsigned long long n) { if (!g_launch_pause) g_launches.fetch_add(n, std::memory_order_relaxed); }
+unsigned long long launch_count() { return g_launches.load(std::memory_order_relaxed); }
+void count_launches_pause(bool on) { g_launch_pause = on; }
 
 static thread_local char g_err[512] = "";
 void set_error(const char* fmt, ...) {
@@ -491,9 +498,13 @@ int Engine::ensure_graph() {
     cudaGraph_t g = nullptr;
     cudaError_t e = cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal);
     if (e != cudaSuccess) return cuda_fail(e, "cudaStreamBeginCapture");
+    count_launches_pause(true);
     int rc = enqueue_step(stream);
+    count_launches_pause(false);
     e = cudaStreamEndCapture(stream, &g);
     if (rc == 0 && e == cudaSuccess) {
+      size_t n_nodes = 0;
+      if (cudaGraphGetNodes(g, nullptr, &n_nodes) == cudaSuccess) step_graph_nodes = (int)n_nodes;
       e = cudaGraphInstantiate(&step_graph, g, 0);
       cudaGraphDestroy(g);
       if (e == cudaSuccess) return 0;
@@ -516,7 +527,7 @@ int Engine::launch_steps(int n) {
   int rc = ensure_graph();
   if (rc) return rc;
   for (int i = 0; i < n; ++i) {
-    if (step_graph) B200_CUDA(cudaGraphLaunch(step_graph, stream));
+    if (step_graph) { B200_CUDA(cudaGraphLaunch(step_graph, stream)); count_launch((unsigned long long)step_graph_nodes); }
     else if ((rc = enqueue_step(stream))) return rc;
   }
   return 0;
@@ -691,10 +702,18 @@ int Engine::refresh_shadow(const std::string& name) {
   return 0;
 }
 
+// Up to 8 prompts (4096 rows) share one pass: at 512 rows the 256 x 256 GEMM tiles of gate/up fill 1.5 waves of the
+// 148 SMs (a quarter of the machine idles in the second), at 2048-4096 rows 6-12 waves.
+int Engine::prefill_rows_cap() const {
+  if (cfg.max_seqs <= 1 || tp_size > 1) return 0;
+  const int64_t want = (int64_t)cfg.max_ctx * std::min(cfg.max_seqs, 8);
+  return (int)std::min<int64_t>(4096, want);
+}
+
 int Engine::ensure_prefill() {
   if (pf_ready) return 0;
   const b200_config& c = lc;
-  const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn, T = std::max(c.max_ctx, c.max_seqs);
+  const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn, T = std::max(std::max(c.max_ctx, c.max_seqs), prefill_rows_cap());
   if (!gemm_shape_ok(qd + 2 * kvd, d, 1) || !gemm_shape_ok(d, qd, 1) || !gemm_shape_ok(2 * ff, d, 1) || !gemm_shape_ok(d, ff, 1)) {
     set_error("model dims not supported by the tensor-core path (rows %%128, K %%64)");
     return B200_EINVAL;
@@ -729,7 +748,8 @@ int Engine::ensure_prefill() {
       (rc = alloc((void**)&pf_proj, (size_t)(pf_proj_floats = (int64_t)std::max(2 * T, 2560) * d) * 4)) ||
       (rc = alloc((void**)&pf_gu, (size_t)T * 2 * ff * 4)) ||
       (rc = alloc((void**)&pf_partial, (size_t)T * attn_partial_floats(c.n_heads, c.n_kv_heads, pf_splits) * 4)) ||
-      (rc = alloc((void**)&pf_counters, (size_t)T * c.n_kv_heads * 4)))
+      (rc = alloc((void**)&pf_counters, (size_t)T * c.n_kv_heads * 4)) || (rc = alloc((void**)&pfb_tok, (size_t)T * 4)) ||
+      (rc = alloc((void**)&pfb_pos, (size_t)T * 4)) || (rc = alloc((void**)&pfb_slot, (size_t)T * 4)))
     return rc;
   B200_CUDA(cudaMemsetAsync(pf_counters, 0, (size_t)T * c.n_kv_heads * 4, stream));
   gemm_ws.sm_count = sm_count;
@@ -745,7 +765,8 @@ int Engine::ensure_prefill() {
 // sequence whose block table is `active_table` (prefill).  Otherwise row t is position pos_arr[t] of the
 // sequence in slot slot_arr[t], which then sees ctx_arr[t] tokens (batched decode).
 // Leaves the residual stream of every row in pf_x (+ pf_proj still to be added).
-int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_arr, const int32_t* ctx_arr, const int32_t* slot_arr, int pos0) {
+int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_arr, const int32_t* ctx_arr, const int32_t* slot_arr, int pos0,
+                         const std::vector<PrefillSeg>* segs) {
   const b200_config& c = lc;
   const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn;
   cudaStream_t s = stream;
@@ -759,7 +780,11 @@ int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_ar
     B200_CUDA(launch_gemm_bf16_splitk(L.qkv16, qd + 2 * kvd, d, pf_xb, n, pf_qkv, qd + 2 * kvd, qkv_stride, &qkv_splits, s, &gemm_ws));
     B200_CUDA(launch_rope_kv(pf_qkv, pf_q, L.k_cache, L.v_cache, table, rope, n, qd, kvd, c.n_kv_heads, pos0, pos_arr, slot_arr, pages_per_seq,
                              qkv_splits, qkv_stride, s));
-    if (!pos_arr && (use_fa_prefill || pos0 > 0)) {  // one sequence, causal: tensor-core attention, bf16 straight into the GEMM operand
+    if (segs) {  // several prompts: causal attention per prompt over its own rows and its own slot's cache
+      for (const PrefillSeg& g : *segs)
+        B200_CUDA(launch_attn_prefill(pf_q + (size_t)g.row0 * qd, L.k_cache, L.v_cache, block_table + (size_t)g.slot * pages_per_seq,
+                                      pf_xb + (size_t)g.row0 * qd, g.n, g.pos0, c.n_heads, c.n_kv_heads, s));
+    } else if (!pos_arr && (use_fa_prefill || pos0 > 0)) {  // one sequence, causal: tensor-core attention, bf16 straight into the GEMM operand
       B200_CUDA(launch_attn_prefill(pf_q, L.k_cache, L.v_cache, table, pf_xb, n, pos0, c.n_heads, c.n_kv_heads, s));
     } else {                            // one row per sequence (batched decode): the split-KV decode kernel, a query per z
       AttnArgs t = {};

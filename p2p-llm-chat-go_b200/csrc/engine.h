@@ -171,6 +171,7 @@ struct Engine {
   uint16_t* output16 = nullptr;     // bf16 lm_head operand of the tensor-core path
 
   cudaGraphExec_t step_graph = nullptr;
+  int step_graph_nodes = 0;  // kernel nodes of the captured step (counted as launches at every replay)
   bool use_pdl = true, use_graph = true, use_l2_chain = false, use_fa_prefill = true, use_mma_decode = true, use_attn_prefetch = true;
   // n_seqs sequences decoding together from a context of ctx tokens, synchronously (no scheduler thread): the
   // batched step of scheduler.cu, tensor-parallel aware (every rank makes the same call)
@@ -213,11 +214,19 @@ struct Engine {
   uint16_t* shadow_tmp16 = nullptr;
   int prefill_gemm(int n_prompt, int pos0 = 0);  // prompt_dev[pos0..n) -> KV cache (positions below pos0 are already there), first token
   // the tensor-core layer stack over n rows: one sequence at positions 0..n-1 (arrays null) or one row per sequence
-  int forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_arr, const int32_t* ctx_arr, const int32_t* slot_arr, int pos0 = 0);
+  // segs != null: the rows are several prompts laid end to end (batched admission); rows [row0, row0+n) of segment i
+  // are positions pos0.. of the sequence in slot `slot` (pos_arr / slot_arr carry the same per row for RoPE / KV append)
+  struct PrefillSeg { int row0, n, pos0, slot; };
+  int forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_arr, const int32_t* ctx_arr, const int32_t* slot_arr, int pos0 = 0,
+                   const std::vector<PrefillSeg>* segs = nullptr);
+  int32_t *pfb_tok = nullptr, *pfb_pos = nullptr, *pfb_slot = nullptr;  // device [pf_rows]: row -> token / position / slot
+  int prefill_rows_cap() const;              // rows one batched prefill may hold
   int set_active_slot(int slot);
   int ensure_batched();
   int batched_step(const std::vector<int>& slots, std::vector<int32_t>* next);
   int admit(Request* r, int slot);           // prefill a new request into a slot, deliver its first token
+  // several waiting requests prefilled in ONE pass of the layer stack (their prompts are the rows of the same GEMMs)
+  void admit_batch(const std::vector<Request*>& rs, const std::vector<int>& slots);
   int decode_bs1_window(int slot);           // batch-1 graph steps for the only active sequence
   void finish_request(int slot, int rc, int reason);
   void deliver(int slot, const int32_t* toks, int n);

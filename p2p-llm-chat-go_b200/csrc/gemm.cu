@@ -414,7 +414,7 @@ cudaError_t launch_bn(const uint16_t* W, int64_t rows, int64_t K, const uint16_t
   GemmArgs g;
   g.y = Y; g.ldy = (int)ldy; g.n_tokens = (int)n_tokens; g.n_rows = (int)rows; g.k_blocks = (int)(K / BK) / splits; g.split_stride = split_stride;
   dim3 grid((unsigned)((rows + BM * MT - 1) / (BM * MT)), (unsigned)((n_tokens + BN - 1) / BN), (unsigned)splits);
-  kern<<<grid, C::THREADS, C::SMEM, s>>>(ma, mb, g);
+  count_launch(); kern<<<grid, C::THREADS, C::SMEM, s>>>(ma, mb, g);
   return cudaGetLastError();
 }
 
@@ -435,7 +435,7 @@ cudaError_t launch_streamk(const uint16_t* W, int64_t rows, int64_t K, const uin
   g.units = (g.total + wk.sm_count - 1) / wk.sm_count;
   g.ws = wk.ws; g.flags = wk.flags;
   const int grid = (g.total + g.units - 1) / g.units;
-  gemm_streamk_kernel<BN><<<grid, C::THREADS, C::SMEM, s>>>(ma, mb, g);
+  count_launch(); gemm_streamk_kernel<BN><<<grid, C::THREADS, C::SMEM, s>>>(ma, mb, g);
   return cudaGetLastError();
 }
 

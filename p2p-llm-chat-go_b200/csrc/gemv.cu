@@ -195,7 +195,7 @@ cudaError_t launch_t(const GemvArgs& a, cudaStream_t s, bool pdl, int sm_count) 
   at[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
   cfg.numAttrs = pdl ? 1 : 0;
-  return cudaLaunchKernelEx(&cfg, kern, a);
+  return count_launch(), cudaLaunchKernelEx(&cfg, kern, a);
 }
 
 template <class F>
@@ -242,7 +242,7 @@ cudaError_t launch_dual_t(const GemvArgs& a, const GemvArgs& b, cudaStream_t s, 
   at[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
   cfg.numAttrs = pdl ? 1 : 0;
-  return cudaLaunchKernelEx(&cfg, kern, a, b, a_ctas);
+  return count_launch(), cudaLaunchKernelEx(&cfg, kern, a, b, a_ctas);
 }
 
 // ------------------------------------------------------------------ launch shapes

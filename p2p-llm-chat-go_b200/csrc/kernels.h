@@ -5,6 +5,12 @@
 
 namespace b200 {
 
+// Kernels this library has put on a GPU in this process: every launcher below counts its launch, a CUDA-graph replay
+// counts the kernel nodes of the graph; launches recorded during stream capture are not counted (they run at replay).
+void count_launch(unsigned long long n = 1);
+unsigned long long launch_count();
+void count_launches_pause(bool on);  // capture in progress on this thread
+
 constexpr int kHeadDim = 128;    // Llama-3.1 8B and 70B
 constexpr int kPageTokens = 16;  // KV page = 16 tokens of one kv head = 4 KB (bf16)
 constexpr int QK_K = 256, Q4K_BYTES = 144, Q6K_BYTES = 210;  // GGUF k-quant super-block

@@ -225,7 +225,7 @@ __global__ void finish_step_kernel(FinishArgs a) {
 cudaError_t launch_dequant(int type, const void* blocks, int64_t n_blocks, float* out_f32, uint16_t* out_bf16, cudaStream_t s) {
   if (type != T_Q4_K && type != T_Q6_K) return cudaErrorInvalidValue;
   if (n_blocks == 0) return cudaSuccess;
-  dequant_kernel<<<(unsigned)n_blocks, 256, 0, s>>>(type, (const uint8_t*)blocks, n_blocks, out_f32, out_bf16);
+  count_launch(); dequant_kernel<<<(unsigned)n_blocks, 256, 0, s>>>(type, (const uint8_t*)blocks, n_blocks, out_f32, out_bf16);
   return cudaGetLastError();
 }
 
@@ -233,7 +233,7 @@ cudaError_t launch_quant_q16(const float* x, int64_t n, int16_t* q, float* d, cu
   if (n % 32) return cudaErrorInvalidValue;
   if (n == 0) return cudaSuccess;
   const int64_t nb = n / 32;
-  quant_q16_kernel<<<(unsigned)((nb + 7) / 8), 256, 0, s>>>(x, n, q, d);
+  count_launch(); quant_q16_kernel<<<(unsigned)((nb + 7) / 8), 256, 0, s>>>(x, n, q, d);
   return cudaGetLastError();
 }
 
@@ -242,39 +242,39 @@ cudaError_t launch_q6k_repack(const uint8_t* src, uint8_t* dst, int64_t rows, in
   for (int64_t r0 = 0; r0 < rows; r0 += 32768) {  // gridDim.y limit
     const int64_t nr = rows - r0 < 32768 ? rows - r0 : 32768;
     dim3 grid((unsigned)nb, (unsigned)nr);
-    q6k_repack_kernel<<<grid, 224, 0, s>>>(src + r0 * nb * Q6K_BYTES, dst + r0 * nb * Q6K_BYTES, nr, nb, to_device);
+    count_launch(); q6k_repack_kernel<<<grid, 224, 0, s>>>(src + r0 * nb * Q6K_BYTES, dst + r0 * nb * Q6K_BYTES, nr, nb, to_device);
   }
   return cudaGetLastError();
 }
 
 cudaError_t launch_synth(int type, void* dst, int64_t rows, int64_t cols, uint64_t seed, uint32_t tensor_id, float sigma, cudaStream_t s) {
-  synth_kernel<<<1184, 256, 0, s>>>(type, (uint8_t*)dst, rows, cols, seed, tensor_id, sigma);
+  count_launch(); synth_kernel<<<1184, 256, 0, s>>>(type, (uint8_t*)dst, rows, cols, seed, tensor_id, sigma);
   return cudaGetLastError();
 }
 
 cudaError_t launch_f32_to_bf16(const float* x, uint16_t* y, int64_t n, cudaStream_t s) {
   if (n == 0) return cudaSuccess;
-  f32_to_bf16_kernel<<<592, 256, 0, s>>>(x, y, n);
+  count_launch(); f32_to_bf16_kernel<<<592, 256, 0, s>>>(x, y, n);
   return cudaGetLastError();
 }
 
 cudaError_t launch_add_inplace(float* x, const float* y, int n, cudaStream_t s) {
-  add_inplace_kernel<<<(n + 1023) / 1024, 256, 0, s>>>(x, y, n);
+  count_launch(); add_inplace_kernel<<<(n + 1023) / 1024, 256, 0, s>>>(x, y, n);
   return cudaGetLastError();
 }
 
 cudaError_t launch_l2_flush(void* buf, size_t bytes, cudaStream_t s) {
-  l2_flush_kernel<<<592, 256, 0, s>>>((uint4*)buf, bytes / 16);
+  count_launch(); l2_flush_kernel<<<592, 256, 0, s>>>((uint4*)buf, bytes / 16);
   return cudaGetLastError();
 }
 
 cudaError_t launch_embed(const uint8_t* embd, int embd_type, int d_model, const int32_t* token_dev, float* x, cudaStream_t s) {
-  embed_kernel<<<1, 256, 0, s>>>(embd, embd_type, d_model, token_dev, x);
+  count_launch(); embed_kernel<<<1, 256, 0, s>>>(embd, embd_type, d_model, token_dev, x);
   return cudaGetLastError();
 }
 
 cudaError_t launch_embed_tokens(const uint8_t* embd, int embd_type, int d_model, const int32_t* tokens_dev, int n, float* x, cudaStream_t s) {
-  embed_tokens_kernel<<<n, 256, 0, s>>>(embd, embd_type, d_model, tokens_dev, x);
+  count_launch(); embed_tokens_kernel<<<n, 256, 0, s>>>(embd, embd_type, d_model, tokens_dev, x);
   return cudaGetLastError();
 }
 
@@ -288,7 +288,7 @@ cudaError_t launch_finish_step(const FinishArgs& a, cudaStream_t s, bool pdl) {
   at[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
   cfg.numAttrs = pdl ? 1 : 0;
-  return cudaLaunchKernelEx(&cfg, finish_step_kernel, a);
+  return count_launch(), cudaLaunchKernelEx(&cfg, finish_step_kernel, a);
 }
 
 }  // namespace b200

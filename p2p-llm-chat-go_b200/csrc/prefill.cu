@@ -190,25 +190,25 @@ __global__ void tp_push_kernel(const TpBatch b, const float* src, long long coun
 cudaError_t launch_tp_push(const TpBatch& b, const float* src, int64_t count, int buf, unsigned int seq, cudaStream_t s) {
   if (count < 4 || count % 4 || count > b.slot_floats || (buf & ~1)) return cudaErrorInvalidValue;
   const int grid = (int)std::min<int64_t>(296, (count / 4 + 255) / 256);  // one float4 x `size` remote stores per thread
-  tp_push_kernel<<<grid, 256, 0, s>>>(b, src, (long long)count, buf, seq);
+  count_launch(); tp_push_kernel<<<grid, 256, 0, s>>>(b, src, (long long)count, buf, seq);
   return cudaGetLastError();
 }
 
 cudaError_t launch_argmax_rows(const float* logits, int rows, int vocab, int32_t* next, cudaStream_t s) {
-  argmax_rows_kernel<<<rows, 1024, 0, s>>>(logits, vocab, next, 0, nullptr);
+  count_launch(); argmax_rows_kernel<<<rows, 1024, 0, s>>>(logits, vocab, next, 0, nullptr);
   return cudaGetLastError();
 }
 cudaError_t launch_argmax_rows_keys(const float* logits, int rows, int vocab, int id_base, unsigned long long* keys, cudaStream_t s) {
-  argmax_rows_kernel<<<rows, 1024, 0, s>>>(logits, vocab, nullptr, id_base, keys);
+  count_launch(); argmax_rows_kernel<<<rows, 1024, 0, s>>>(logits, vocab, nullptr, id_base, keys);
   return cudaGetLastError();
 }
 cudaError_t launch_keys_to_ids(const unsigned long long* keys, int32_t* next, int rows, cudaStream_t s) {
-  keys_to_ids_kernel<<<(rows + 255) / 256, 256, 0, s>>>(keys, next, rows);
+  count_launch(); keys_to_ids_kernel<<<(rows + 255) / 256, 256, 0, s>>>(keys, next, rows);
   return cudaGetLastError();
 }
 cudaError_t launch_append_history(const int32_t* next, const int32_t* slot_arr, const int32_t* pos_arr, int32_t* history, int max_ctx, int rows,
                                   cudaStream_t s) {
-  append_history_kernel<<<(rows + 255) / 256, 256, 0, s>>>(next, slot_arr, pos_arr, history, max_ctx, rows);
+  count_launch(); append_history_kernel<<<(rows + 255) / 256, 256, 0, s>>>(next, slot_arr, pos_arr, history, max_ctx, rows);
   return cudaGetLastError();
 }
 
@@ -216,7 +216,7 @@ cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, int n_parts, int
                                     int d, float eps, cudaStream_t s, const unsigned int* wait_flags, int n_wait, unsigned int wait_seq,
                                     int* wait_error) {
   if (d % 4 || part_stride % 4 || (wait_flags && (n_wait < 1 || n_wait > 256 || !wait_error))) return cudaErrorInvalidValue;
-  add_rmsnorm_bf16_kernel<<<tokens, 256, 0, s>>>(x, add, n_parts, (long long)part_stride, w, xb, d, eps, wait_flags, n_wait, wait_seq,
+  count_launch(); add_rmsnorm_bf16_kernel<<<tokens, 256, 0, s>>>(x, add, n_parts, (long long)part_stride, w, xb, d, eps, wait_flags, n_wait, wait_seq,
                                                  wait_error);
   return cudaGetLastError();
 }
@@ -225,18 +225,18 @@ cudaError_t launch_rope_kv(const float* qkv, float* q, uint16_t* k_cache, uint16
                            int pages_per_seq, int n_parts, int64_t part_stride, cudaStream_t s) {
   // few tokens (batched decode): spread a token's row pairs over several CTAs, above all when partials are summed
   const int ny = tokens >= 128 ? 1 : (tokens >= 32 ? 2 : 8);
-  rope_kv_kernel<<<dim3(tokens, ny), 256, 0, s>>>(qkv, q, k_cache, v_cache, block_table, rope, q_rows, kv_rows, n_kv_heads, pos0, pos_arr, slot_arr,
+  count_launch(); rope_kv_kernel<<<dim3(tokens, ny), 256, 0, s>>>(qkv, q, k_cache, v_cache, block_table, rope, q_rows, kv_rows, n_kv_heads, pos0, pos_arr, slot_arr,
                                         pages_per_seq, n_parts, (long long)part_stride);
   return cudaGetLastError();
 }
 cudaError_t launch_swiglu_bf16(const float* gu, uint16_t* h, int64_t n_pairs, int n_parts, int64_t part_stride, cudaStream_t s) {
   if (part_stride % 2) return cudaErrorInvalidValue;
   const int grid = (int)std::min<int64_t>(1184, (n_pairs + 255) / 256);
-  swiglu_bf16_kernel<<<grid, 256, 0, s>>>(gu, h, n_pairs, n_parts, (long long)part_stride);
+  count_launch(); swiglu_bf16_kernel<<<grid, 256, 0, s>>>(gu, h, n_pairs, n_parts, (long long)part_stride);
   return cudaGetLastError();
 }
 cudaError_t launch_take_row(const float* x, const float* add, int n_parts, int64_t part_stride, int d, int row, float* out, cudaStream_t s) {
-  take_row_kernel<<<8, 256, 0, s>>>(x, add, n_parts, (long long)part_stride, d, row, out);
+  count_launch(); take_row_kernel<<<8, 256, 0, s>>>(x, add, n_parts, (long long)part_stride, d, row, out);
   return cudaGetLastError();
 }
 

@@ -340,13 +340,14 @@ cudaError_t launch_sample(const SampleArgs& a, cudaStream_t s, bool pdl) {
     c1.blockDim = dim3(kSlice);
     e = cudaFuncSetAttribute(sample_part_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
     if (e != cudaSuccess) return e;
+    count_launch();
     e = cudaLaunchKernelEx(&c1, sample_part_kernel, a);
     if (e != cudaSuccess) return e;
     e = cudaFuncSetAttribute(sample_final_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
     if (e != cudaSuccess) return e;
-    return cudaLaunchKernelEx(&cfg, sample_final_kernel, a);
+    return count_launch(), cudaLaunchKernelEx(&cfg, sample_final_kernel, a);
   }
-  return cudaLaunchKernelEx(&cfg, sample_kernel, a);
+  return count_launch(), cudaLaunchKernelEx(&cfg, sample_kernel, a);
 }
 
 }  // namespace b200

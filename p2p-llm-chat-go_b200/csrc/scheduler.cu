@@ -233,6 +233,89 @@ int Engine::admit(Request* r, int slot) {
   return 0;
 }
 
+// Batched admission: the prompts of several waiting requests go through the layer stack together (one set of GEMMs
+// over all their rows, causal attention per prompt), then each gets its first token from the batch-1 tail (mode-0
+// lm_head, sampler) exactly as a lone admission would.  Failures end the affected requests, never the worker.
+void Engine::admit_batch(const std::vector<Request*>& rs, const std::vector<int>& sl) {
+  const int B = (int)rs.size();
+  std::vector<PrefillSeg> segs;
+  std::vector<int32_t> tok, pos, slot;
+  int rc = ensure_prefill();
+  if (!rc) rc = ensure_graph();
+  if (!rc) rc = ensure_batched();
+  const auto t_load = std::chrono::steady_clock::now();
+  for (int i = 0; i < B; ++i) {  // every request owns its slot from here on, so a failure below can end it properly
+    Request* r = rs[i];
+    Seq& q = seqs[sl[i]];
+    q = Seq();
+    q.r = r;
+    q.t0 = r->t_submit;
+    q.t_load = t_load;
+    q.n_prompt = (int)r->prompt.size();
+    int max_out = r->sp.num_predict > 0 ? r->sp.num_predict : cfg.max_ctx;
+    if (q.n_prompt + max_out - 1 > cfg.max_ctx) max_out = cfg.max_ctx - q.n_prompt + 1;
+    q.max_out = max_out;
+    q.greedy = r->sp.temperature <= 0.f;
+    int reuse = use_prefix_cache ? common_prefix(sl[i], r->prompt) : 0;
+    if (reuse < kMinReuse) reuse = 0;
+    invalidate_prefix_cache(sl[i]);
+    q.reused = reuse;
+    PrefillSeg g = {(int)tok.size(), q.n_prompt - reuse, reuse, sl[i]};
+    segs.push_back(g);
+    for (int t = reuse; t < q.n_prompt; ++t) { tok.push_back(r->prompt[t]); pos.push_back(t); slot.push_back(sl[i]); }
+  }
+  const int N = (int)tok.size();
+  auto cu = [&](cudaError_t e, const char* what) { if (!rc && e != cudaSuccess) rc = cuda_fail(e, what); };
+  if (!rc) {
+    cu(cudaMemcpyAsync(pfb_tok, tok.data(), (size_t)N * 4, cudaMemcpyHostToDevice, stream), "batched prefill: tokens");
+    cu(cudaMemcpyAsync(pfb_pos, pos.data(), (size_t)N * 4, cudaMemcpyHostToDevice, stream), "batched prefill: positions");
+    cu(cudaMemcpyAsync(pfb_slot, slot.data(), (size_t)N * 4, cudaMemcpyHostToDevice, stream), "batched prefill: slots");
+  }
+  if (!rc) rc = forward_gemm(N, pfb_tok, pfb_pos, nullptr, pfb_slot, 0, &segs);
+  // the residual stream of every row now sits in pf_x (+ the last down projection still to be added): hand each
+  // prompt's last row to the batch-1 tail
+  const float* proj_src = pf_proj_src;
+  const int proj_splits = pf_proj_splits;
+  const int64_t proj_stride = pf_proj_stride;
+  for (int i = 0; i < B; ++i) {
+    Request* r = rs[i];
+    const int s = sl[i];
+    Seq& q = seqs[s];
+    int rq = rc;
+    if (!rq) rq = set_active_slot(s);
+    if (!rq) rq = begin_sequence(r->prompt.data(), q.n_prompt, q.max_out, q.greedy ? 1 : 0, &r->sp);
+    if (!rq) {
+      StepState s0 = {};
+      s0.pos = q.n_prompt - 1; s0.cur_token = r->prompt[q.n_prompt - 1]; s0.n_prompt = q.n_prompt; s0.max_out = q.max_out; s0.eos = cfg.eos_token;
+      s0.greedy = q.greedy ? 1 : 0;
+      cudaError_t e = cudaMemcpyAsync(st, &s0, sizeof s0, cudaMemcpyHostToDevice, stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+      if (e == cudaSuccess) e = launch_take_row(pf_x, proj_src, proj_splits, proj_stride, cfg.d_model, segs[i].row0 + segs[i].n - 1, x, stream);
+      if (e != cudaSuccess) rq = cuda_fail(e, "batched prefill: hand-over");
+    }
+    int n_tail = 0;
+    if (!rq) rq = enqueue_tail(stream, false, &n_tail);
+    if (!rq) {
+      SampleParams sp0 = {};
+      sp0.temperature = r->sp.temperature; sp0.top_p = r->sp.top_p; sp0.repeat_penalty = r->sp.repeat_penalty;
+      sp0.top_k = r->sp.top_k; sp0.repeat_last_n = r->sp.repeat_last_n; sp0.seed = r->sp.seed;
+      cudaError_t e = cudaMemcpyAsync(sp_arr + s, &sp0, sizeof sp0, cudaMemcpyHostToDevice, stream);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+      if (e != cudaSuccess) rq = cuda_fail(e, "batched prefill: first token");
+      else if (*host_n_out < 1) { set_error("prefill produced no token"); rq = B200_ECUDA; }
+    }
+    if (rq) { finish_request(s, rq, 3); continue; }
+    const int32_t first = out_tokens[0];
+    cudaMemcpyAsync(hist_dev + (size_t)s * cfg.max_ctx, prompt_dev, (size_t)std::min(q.n_prompt + 1, cfg.max_ctx) * 4, cudaMemcpyDeviceToDevice, stream);
+    bs1_owner = s;
+    q.token = first;
+    q.pos = q.n_prompt;
+    deliver(s, &first, 1);
+    if (q.token == cfg.eos_token) finish_request(s, 0, 1);
+    else if (q.delivered >= q.max_out) finish_request(s, 0, 2);
+  }
+}
+
 // The only active sequence decodes on the batch-1 graph.  Returns when it finishes, is cancelled, or another
 // request shows up (the caller then carries on with batched steps).
 int Engine::decode_bs1_window(int slot) {
@@ -334,9 +417,29 @@ void Engine::worker_loop() {
     // tensor-parallel engines are driven SPMD (every rank makes the same calls): admission timing would differ
     // between ranks, so they serve one request at a time; several slots exist only for b200_bench_batched
     if (tp_size > 1) budget = active.empty() ? 1 : 0;
+    std::vector<Request*> batch_r;   // tensor-core prefills gathered this iteration: they share one pass (admit_batch)
+    std::vector<int> batch_s;
+    std::vector<char> taken(seqs.size(), 0);
+    int batch_rows = 0;
+    const int rows_cap = prefill_rows_cap();
+    auto flush_batch = [&] {
+      if (batch_r.size() == 1) {
+        const int s = batch_s[0];
+        const int rc = admit(batch_r[0], s);
+        if (rc) { if (!seqs[s].r) seqs[s].r = batch_r[0]; finish_request(s, rc, 3); }
+        else {
+          Seq& q = seqs[s];
+          if (q.token == cfg.eos_token) finish_request(s, 0, 1);
+          else if (q.delivered >= q.max_out) finish_request(s, 0, 2);
+        }
+      } else if (batch_r.size() > 1) {
+        admit_batch(batch_r, batch_s);
+      }
+      batch_r.clear(); batch_s.clear(); batch_rows = 0;
+    };
     while (budget > 0) {
       int n_free = 0;
-      for (auto& q : seqs) n_free += q.r ? 0 : 1;
+      for (size_t i = 0; i < seqs.size(); ++i) n_free += (seqs[i].r || taken[i]) ? 0 : 1;
       if (n_free == 0) break;
       --budget;
       Request* r = nullptr;
@@ -350,7 +453,7 @@ void Engine::worker_loop() {
       // holds nothing (so other peers' histories stay cached), else the first free one
       int s = -1, best = -1;
       for (int i = 0; i < (int)seqs.size(); ++i) {
-        if (seqs[i].r) continue;
+        if (seqs[i].r || taken[i]) continue;
         int score = use_prefix_cache ? common_prefix(i, r->prompt) : 0;
         if (score < kMinReuse) {
           std::lock_guard<std::mutex> lk(kv_mu);
@@ -358,12 +461,22 @@ void Engine::worker_loop() {
         }
         if (score > best) { best = score; s = i; }
       }
-      const int rc = admit(r, s);
-      if (rc) { if (!seqs[s].r) seqs[s].r = r; finish_request(s, rc, 3); continue; }
-      Seq& q = seqs[s];
-      if (q.token == cfg.eos_token) finish_request(s, 0, 1);
-      else if (q.delivered >= q.max_out) finish_request(s, 0, 2);
+      const int n_prompt = (int)r->prompt.size();
+      int max_out = r->sp.num_predict > 0 ? r->sp.num_predict : cfg.max_ctx;
+      if (n_prompt + max_out - 1 > cfg.max_ctx) max_out = cfg.max_ctx - n_prompt + 1;
+      const bool batchable = rows_cap > 0 && r->sp.prefill_mode == B200_MODE_GEMM && n_prompt > 1 && max_out >= 1 && n_prompt <= rows_cap;
+      if (!batchable) {  // token-by-token prefill, or a request admit() will refuse: on its own
+        flush_batch();
+        batch_r.push_back(r); batch_s.push_back(s);
+        flush_batch();
+        continue;
+      }
+      if (batch_rows + n_prompt > rows_cap) flush_batch();
+      batch_r.push_back(r); batch_s.push_back(s);
+      taken[s] = 1;
+      batch_rows += n_prompt;
     }
+    flush_batch();
     active.clear();
     for (int s = 0; s < (int)seqs.size(); ++s)
       if (seqs[s].r) active.push_back(s);
