@@ -76,6 +76,8 @@ __global__ void __launch_bounds__(128) attn_decode_fast_kernel(const AttnArgs a)
   };
   // ---- before the dependency: the first tile of this split, every token the cache has room for (rows at or
   // beyond the current position hold older data; they are masked below, and the current row is re-fetched)
+  const bool tracer = a.trace != nullptr && kvh == 0 && split == 0 && tid == 0;
+  if (tracer) a.trace[0] = global_timer_ns();
   gather(split, 0, a.prefetch_tokens);
   asm volatile("cp.async.commit_group;" ::: "memory");
   if (tid < G) {
@@ -84,6 +86,7 @@ __global__ void __launch_bounds__(128) attn_decode_fast_kernel(const AttnArgs a)
   }
   pdl_wait();
   pdl_launch_dependents();
+  if (tracer) a.trace[1] = global_timer_ns();
   const int pos = a.fixed_ctx > 0 ? a.fixed_ctx - 1 : a.st->pos;
   const int ctx = pos + 1;
   const float scale = 1.0f / sqrtf((float)kHeadDim);
@@ -152,6 +155,7 @@ __global__ void __launch_bounds__(128) attn_decode_fast_kernel(const AttnArgs a)
     __syncthreads();
   }
 
+  if (tracer) a.trace[2] = global_timer_ns();
   // ---- split merge: as in attn_decode_item (partials in scratch, the last CTA of a KV head combines them)
   float* part = a.partial + ((size_t)kvh * S + split) * G * kPart;
 #pragma unroll
@@ -197,6 +201,7 @@ __global__ void __launch_bounds__(128) attn_decode_fast_kernel(const AttnArgs a)
 #pragma unroll
   for (int h = 0; h < G; ++h) a.out[((size_t)kvh * G + h) * kHeadDim + tid] = num[h] * sm.corr_s[h];
   if (tid == 0) a.counters[kvh] = 0u;
+  if (a.trace != nullptr && tid == 0) atomicMax(a.trace + 3, global_timer_ns());
 }
 
 }  // namespace

@@ -711,6 +711,7 @@ int b200_bench_decode(b200_engine* h, int ctx, int n_steps, float* ms_per_step, 
   cudaEventDestroy(e0); cudaEventDestroy(e1);
   if (rc) return rc;
   if (ce != cudaSuccess) return cuda_fail(ce, "bench_decode sync");
+  e->dump_trace();
   if (ms_per_step) *ms_per_step = ms / n_steps;
   if (launches_per_step) *launches_per_step = e->launches_per_step;
   return 0;

@@ -67,6 +67,12 @@ DEVINL void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" 
 DEVINL void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 DEVINL void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+DEVINL unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
 // ---- number formats ---------------------------------------------------------------------------------
 DEVINL float bf16lo(uint32_t v) { return __uint_as_float(v << 16); }
 DEVINL float bf16hi(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }

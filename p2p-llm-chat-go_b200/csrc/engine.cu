@@ -400,11 +400,35 @@ int Engine::enqueue_tail(cudaStream_t s, bool pdl, int* n, bool consume_tp, bool
   return 0;
 }
 
+int Engine::dump_trace() {
+  const char* path = getenv("B200_TRACE");
+  if (!trace_dev || !path || trace_names.empty()) return 0;
+  std::vector<unsigned long long> t(trace_names.size() * 4);
+  B200_CUDA(cudaMemcpy(t.data(), trace_dev, t.size() * 8, cudaMemcpyDeviceToHost));
+  FILE* f = fopen(path, "w");
+  if (!f) return 0;
+  for (size_t i = 0; i < trace_names.size(); ++i)
+    fprintf(f, "%zu %s %llu %llu %llu %llu\n", i, trace_names[i].c_str(), t[4 * i], t[4 * i + 1], t[4 * i + 2], t[4 * i + 3]);
+  fclose(f);
+  return 0;
+}
+
 int Engine::enqueue_step(cudaStream_t s) {
   const b200_config& c = lc;  // per-rank shapes (== cfg without tensor parallelism)
   const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn;
   const bool tp = tp_size > 1;
   int n = 0;
+  if (getenv("B200_TRACE") && !trace_dev) {
+    int rc = alloc((void**)&trace_dev, (size_t)(6 * c.n_layers + 8) * 4 * 8);
+    if (rc) return rc;
+    B200_CUDA(cudaMemset(trace_dev, 0, (size_t)(6 * c.n_layers + 8) * 4 * 8));
+  }
+  trace_names.clear();
+  auto tr = [&](const char* name) -> unsigned long long* {  // stamps of the launch about to be enqueued
+    if (!trace_dev) return nullptr;
+    trace_names.push_back(name);
+    return trace_dev + (trace_names.size() - 1) * 4;
+  };
   for (int l = 0; l < c.n_layers; ++l) {
     Layer& L = layers[l];
     // fused all-reduce: residual buffers alternate, all-reduce i is consumed from xbuf[i&1] into xbuf[(i+1)&1]
@@ -427,6 +451,7 @@ int Engine::enqueue_step(cudaStream_t s) {
     };
     chain(a, L.o, L.o_type, d, qd);
     bool dual = false;
+    a.trace = tr("qkv");
     if (L.v && qkv_pro == PRO_RMSNORM) {  // q,k and a differently-typed v: one launch when the pair is supported
       GemvArgs bv = a;
       bv.next_bytes = 0;
@@ -441,6 +466,7 @@ int Engine::enqueue_step(cudaStream_t s) {
       if (L.v) {
         a.next_bytes = 0;
         a.W = L.v; a.N = kvd; a.row_base = qd + kvd;
+        a.trace = tr("v");
         B200_CUDA(launch_gemv(L.v_type, PRO_RMSNORM, EPI_QKV, a, s, use_pdl, sm_count)); ++n;
       }
     }
@@ -449,6 +475,7 @@ int Engine::enqueue_step(cudaStream_t s) {
     t.n_heads = c.n_heads; t.n_kv_heads = c.n_kv_heads; t.out = att; t.partial = attn_partial; t.counters = attn_counters;
     t.n_splits = n_splits; t.fixed_ctx = 0;
     t.prefetch_tokens = use_attn_prefetch ? pages_per_seq * kPageTokens : 0;
+    t.trace = tr("attn");
     B200_CUDA(launch_attn_decode(t, s, use_pdl)); ++n;
     // row-parallel projections: without TP the residual add is the GEMV epilogue; with TP every rank holds a
     // K-slice, so the partial products are summed over NVLink (NCCL all-reduce) before they join the stream
@@ -456,6 +483,7 @@ int Engine::enqueue_step(cudaStream_t s) {
     o.W = L.o; o.N = d; o.K = qd; o.x = att; o.y = tp ? tp_partial : x;
     chain(o, L.gate_up, L.gu_type, 2 * ff, d);
     if (fused) { o.tp = tp_link; o.tp_index = 2 * l; o.y = nullptr; }
+    o.trace = tr("o");
     B200_CUDA(launch_gemv(L.o_type, PRO_COPY, fused ? EPI_TP_PUSH : (tp ? EPI_STORE : EPI_RESID), o, s, use_pdl, sm_count)); ++n;
     if (tp && !fused) {
       int rc = tp_allreduce_sum(tp_partial, (size_t)d, s);
@@ -465,6 +493,7 @@ int Engine::enqueue_step(cudaStream_t s) {
     GemvArgs g = {};
     g.W = L.gate_up; g.N = 2 * ff; g.K = d; g.x = x; g.norm_w = L.ffn_norm; g.eps = c.rms_eps; g.y = h;
     chain(g, L.down, L.down_type, d, ff);
+    g.trace = tr("gate_up");
     int gu_pro = PRO_RMSNORM;
     if (fused) {  // consumes this layer's o projection (all-reduce 2l): reads xbuf[0], publishes xbuf[1]
       gu_pro = PRO_TP_RMSNORM;
@@ -476,6 +505,7 @@ int Engine::enqueue_step(cudaStream_t s) {
     if (l + 1 < c.n_layers) chain(dn, layers[l + 1].qkv, layers[l + 1].qkv_type, layers[l + 1].v ? qd + kvd : qd + 2 * kvd, d);
     else chain(dn, output, output_type, c.vocab, d);
     if (fused) { dn.tp = tp_link; dn.tp_index = 2 * l + 1; dn.y = nullptr; }
+    dn.trace = tr("down");
     B200_CUDA(launch_gemv(L.down_type, PRO_COPY, fused ? EPI_TP_PUSH : (tp ? EPI_STORE : EPI_RESID), dn, s, use_pdl, sm_count)); ++n;
     if (tp && !fused) {
       int rc = tp_allreduce_sum(tp_partial, (size_t)d, s);

@@ -178,6 +178,9 @@ struct Engine {
   int bench_batched(int n_seqs, int ctx, int n_steps, float* ms_per_step, int32_t* last_ids);
   unsigned long long* b_keys = nullptr;  // [max_seqs] argmax keys (vocab-parallel lm_head)
   int launches_per_step = 0;
+  unsigned long long* trace_dev = nullptr;   // B200_TRACE=<file>: 4 stamps per launch of the decode step (see GemvArgs::trace)
+  int dump_trace();                          // the last step's stamps -> "<launch> <name> t0 t1 t2 t3" lines (ns)
+  std::vector<std::string> trace_names;
   void* flush_buf = nullptr;
   size_t flush_bytes = 0;
 

@@ -51,6 +51,8 @@ DEVINL void gemv_body(const GemvArgs& a, int cta, int n_ctas) {
   const uint32_t ring_s = smem_u32(ring), bars_s = smem_u32(bars);
   const uint64_t pol = l2_policy_evict_first();
 
+  const bool tracer = a.trace != nullptr && cta == 0 && threadIdx.x == 0;
+  if (tracer) a.trace[0] = global_timer_ns();
   if (EPI == EPI_LOGITS) {  // no prefetch before the dependency: the kernel may be skipped entirely
     pdl_wait();
     if (a.st != nullptr && a.st->pos + 1 < a.st->n_prompt) return;
@@ -84,7 +86,9 @@ DEVINL void gemv_body(const GemvArgs& a, int cta, int n_ctas) {
     pdl_launch_dependents();
     pdl_wait();
   }
+  if (tracer) a.trace[1] = global_timer_ns();
   F::template prologue<PRO>(xs, a, red, warp, lane);
+  if (tracer) a.trace[2] = global_timer_ns();
   if (EPI == EPI_LOGITS) pdl_launch_dependents();
 
   int c_stage = 0;
@@ -121,6 +125,7 @@ DEVINL void gemv_body(const GemvArgs& a, int cta, int n_ctas) {
     epilogue<EPI, F::R>(a, gwarp + u * twarps, lane, acc, bestv, besti);
   }
   if (EPI == EPI_LOGITS && lane == 0 && my_units > 0) atomicMax(a.argmax_key, argmax_key(bestv, besti));
+  if (a.trace != nullptr && threadIdx.x == 0) atomicMax(a.trace + 3, global_timer_ns());
   if (EPI == EPI_TP_PUSH) {  // when the last CTA of the grid has pushed, raise this rank's flag on every peer
     const TpLink* t = a.tp;
     __syncthreads();

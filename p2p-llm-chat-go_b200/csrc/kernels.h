@@ -96,6 +96,9 @@ struct GemvArgs {
   const TpLink* tp;
   int tp_index;        // which all-reduce of the step this kernel produces (EPI_TP_PUSH) / consumes (PRO_TP_RMSNORM)
   float* x_out;        // PRO_TP_RMSNORM: where CTA 0 leaves the updated residual stream (x + sum of partials)
+  // debug (B200_TRACE): 4 x %globaltimer of this launch — CTA 0 at entry, after the dependency wait, after the
+  // prologue; and the latest exit over all CTAs (atomicMax).  null: no stamps
+  unsigned long long* trace;
 };
 
 struct GemvPlan {  // launch geometry chosen on the host
@@ -134,6 +137,7 @@ struct AttnArgs {
   // kernel has finished (they exist and are not written by it, except the row of the current position, which is
   // re-read).  0: the plain kernel.
   int prefetch_tokens;
+  unsigned long long* trace;  // debug (B200_TRACE), as in GemvArgs
 };
 cudaError_t launch_attn_decode(const AttnArgs& a, cudaStream_t s, bool pdl);
 size_t attn_partial_floats(int n_heads, int n_kv_heads, int n_splits);
