@@ -204,7 +204,237 @@ __global__ void __launch_bounds__(128) attn_decode_fast_kernel(const AttnArgs a)
   if (a.trace != nullptr && tid == 0) atomicMax(a.trace + 3, global_timer_ns());
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Cluster variant of the batch-1 decode step: the kCl = 16 splits of one KV head form ONE thread-block cluster, so
+// their partial results are combined over distributed shared memory instead of through global scratch, a fence,
+// an atomic ticket and two rounds of L2 loads by the last CTA (measured with B200_TRACE: that merge was 5.4 us of
+// the kernel's 8 us).  Every CTA keeps (acc[G][128], m[G], l[G]) of its tiles in its own shared memory; after one
+// cluster barrier CTA r combines output dims [8r, 8r+8) of all G heads from the 16 CTAs and stores them; a second
+// barrier keeps every CTA's shared memory alive until its peers have read it.  Needs no scratch and no counters.
+constexpr int kCl = 16;  // cluster size (non-portable: opted in at launch; the launcher falls back if refused)
+
+template <int G>
+struct AttnClSmem {
+  alignas(16) uint16_t Ks[kTile * kHeadDim];
+  alignas(16) uint16_t Vs[kTile * kHeadDim];
+  alignas(16) float qs[G * kHeadDim];
+  float P[G][kTile];
+  float m_run[G], l_run[G], corr_s[G];
+  alignas(16) float accS[G][kHeadDim];   // this CTA's un-normalised partial, read by its cluster peers
+  float mAll[G][kCl], lAll[G][kCl], wAll[G][kCl];
+  float part[G][kCl][kHeadDim / kCl];
+};
+
+DEVINL uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+DEVINL void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// address of `local_smem_addr` (a shared::cta address of this CTA) in CTA `rank` of the cluster
+DEVINL uint32_t map_to_rank(uint32_t local_smem_addr, uint32_t rank) {
+  uint32_t a;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(a) : "r"(local_smem_addr), "r"(rank));
+  return a;
+}
+DEVINL float ld_dsmem(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+  return v;
+}
+
+template <int G>
+__global__ void __launch_bounds__(128) attn_decode_cluster_kernel(const AttnArgs a) {
+  __shared__ AttnClSmem<G> sm;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int kvh = blockIdx.x, split = (int)cluster_ctarank(), S = kCl;
+  const uint32_t ks_s = smem_u32(sm.Ks), vs_s = smem_u32(sm.Vs);
+  auto gather = [&](int tile, int row_lo, int row_hi) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int item = tid + 128 * j, t = item >> 4, c = item & 15;
+      const int tok = tile * kTile + t;
+      if (tok >= row_lo && tok < row_hi) {
+        const int page = a.block_table[tok / kPageTokens];
+        const size_t row = (((size_t)page * a.n_kv_heads + kvh) * kPageTokens + (tok % kPageTokens)) * kHeadDim;
+        cp_async16(ks_s + (uint32_t)(t * kHeadDim * 2 + ((c ^ (t & 7)) << 4)), a.k_cache + row + c * 8);
+        cp_async16(vs_s + (uint32_t)(t * kHeadDim * 2 + (c << 4)), a.v_cache + row + c * 8);
+      }
+    }
+  };
+  const bool tracer = a.trace != nullptr && kvh == 0 && split == 0 && tid == 0;
+  if (tracer) a.trace[0] = global_timer_ns();
+  gather(split, 0, a.prefetch_tokens);  // before the dependency, as in attn_decode_fast_kernel
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  if (tid < G) {
+    sm.m_run[tid] = -INFINITY;
+    sm.l_run[tid] = 0.f;
+  }
+  pdl_wait();
+  pdl_launch_dependents();
+  if (tracer) a.trace[1] = global_timer_ns();
+  const int pos = a.fixed_ctx > 0 ? a.fixed_ctx - 1 : a.st->pos;
+  const int ctx = pos + 1;
+  const float scale = 1.0f / sqrtf((float)kHeadDim);
+  for (int i = tid; i < G * kHeadDim / 4; i += 128)
+    reinterpret_cast<float4*>(sm.qs)[i] = __ldcg(reinterpret_cast<const float4*>(a.q + (size_t)kvh * G * kHeadDim) + i);
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  {
+    const int lo = pos > a.prefetch_tokens ? a.prefetch_tokens : pos;
+    gather(split, lo, ctx);
+    cp_async_commit_wait_all();
+  }
+  float acc[G];
+#pragma unroll
+  for (int h = 0; h < G; ++h) acc[h] = 0.f;
+  __syncthreads();
+
+  for (int tile = split; tile * kTile < ctx; tile += S) {
+    const int t0 = tile * kTile;
+    if (tile != split) {
+      gather(tile, 0, ctx);
+      cp_async_commit_wait_all();
+      __syncthreads();
+    }
+    const int n_valid = ctx - t0 < kTile ? ctx - t0 : kTile;
+    for (int h = warp; h < G; h += 4) {
+      const uint4* kr = reinterpret_cast<const uint4*>(sm.Ks + lane * kHeadDim);
+      const float4* qh = reinterpret_cast<const float4*>(sm.qs + h * kHeadDim);
+      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+      for (int c = 0; c < 16; ++c) {
+        const uint4 k = kr[c ^ (lane & 7)];
+        const float4 qa = qh[2 * c], qb = qh[2 * c + 1];
+        s0 = fmaf(qa.x, bf16lo(k.x), s0);
+        s1 = fmaf(qa.y, bf16hi(k.x), s1);
+        s2 = fmaf(qa.z, bf16lo(k.y), s2);
+        s3 = fmaf(qa.w, bf16hi(k.y), s3);
+        s0 = fmaf(qb.x, bf16lo(k.z), s0);
+        s1 = fmaf(qb.y, bf16hi(k.z), s1);
+        s2 = fmaf(qb.z, bf16lo(k.w), s2);
+        s3 = fmaf(qb.w, bf16hi(k.w), s3);
+      }
+      float sc = (s0 + s1) + (s2 + s3);
+      const bool valid = lane < n_valid;
+      sc = valid ? sc * scale : -INFINITY;
+      const float m_old = sm.m_run[h];
+      const float m_new = fmaxf(m_old, warp_max(sc));
+      const float p = valid ? expf(sc - m_new) : 0.f;
+      const float l_tile = warp_sum(p);
+      sm.P[h][lane] = p;
+      if (lane == 0) {
+        const float corr = (m_old == -INFINITY) ? 0.f : expf(m_old - m_new);
+        sm.corr_s[h] = corr;
+        sm.l_run[h] = sm.l_run[h] * corr + l_tile;
+        sm.m_run[h] = m_new;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int h = 0; h < G; ++h) acc[h] *= sm.corr_s[h];
+    for (int t = 0; t < n_valid; ++t) {
+      const float v = __uint_as_float((uint32_t)sm.Vs[t * kHeadDim + tid] << 16);
+#pragma unroll
+      for (int h = 0; h < G; ++h) acc[h] = fmaf(sm.P[h][t], v, acc[h]);
+    }
+    __syncthreads();
+  }
+  if (tracer) a.trace[2] = global_timer_ns();
+
+  // ---- merge over the cluster
+#pragma unroll
+  for (int h = 0; h < G; ++h) sm.accS[h][tid] = acc[h];
+  cluster_sync_all();  // every CTA's (accS, m_run, l_run) is complete and visible cluster-wide
+  if (tid < G * kCl) {  // (head, source CTA) -> that CTA's running max and sum
+    const int h = tid / kCl, src = tid % kCl;
+    sm.mAll[h][src] = ld_dsmem(map_to_rank(smem_u32(&sm.m_run[h]), (uint32_t)src));
+    sm.lAll[h][src] = ld_dsmem(map_to_rank(smem_u32(&sm.l_run[h]), (uint32_t)src));
+  }
+  // meanwhile: this thread's share of the partial accumulators — source CTA tid / 8, output dim 8 * rank + tid % 8
+  constexpr int kSlice = kHeadDim / kCl;  // 8 output dims per CTA
+  const int src = tid / kSlice, d = tid % kSlice;
+  float pa[G];
+#pragma unroll
+  for (int h = 0; h < G; ++h) pa[h] = ld_dsmem(map_to_rank(smem_u32(&sm.accS[h][split * kSlice + d]), (uint32_t)src));
+  __syncthreads();
+  if (tid < G * kCl) {  // softmax weight of every source for every head
+    const int h = tid / kCl, s_ = tid % kCl;
+    float M = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < kCl; ++j) M = fmaxf(M, sm.mAll[h][j]);
+    const float ms = sm.mAll[h][s_];
+    sm.wAll[h][s_] = (ms == -INFINITY) ? 0.f : expf(ms - M);
+  }
+  __syncthreads();
+#pragma unroll
+  for (int h = 0; h < G; ++h) sm.part[h][src][d] = pa[h] * sm.wAll[h][src];
+  __syncthreads();
+  if (tid < G * kSlice) {
+    const int h = tid / kSlice, dd = tid % kSlice;
+    float num = 0.f, den = 0.f;
+#pragma unroll
+    for (int j = 0; j < kCl; ++j) {
+      num += sm.part[h][j][dd];
+      den = fmaf(sm.lAll[h][j], sm.wAll[h][j], den);
+    }
+    a.out[((size_t)kvh * G + h) * kHeadDim + split * kSlice + dd] = num / den;
+  }
+  cluster_sync_all();  // peers may still be reading this CTA's shared memory
+  if (a.trace != nullptr && tid == 0) atomicMax(a.trace + 3, global_timer_ns());
+}
+
+template <int G>
+cudaError_t launch_cluster_t(const AttnArgs& a, cudaStream_t s, bool pdl) {
+  auto kern = attn_decode_cluster_kernel<G>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+  if (e != cudaSuccess) return e;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(a.n_kv_heads, kCl, 1);
+  cfg.blockDim = dim3(128);
+  cfg.stream = s;
+  cudaLaunchAttribute at[2];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 1; at[0].val.clusterDim.y = kCl; at[0].val.clusterDim.z = 1;
+  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl ? 2 : 1;
+  return count_launch(), cudaLaunchKernelEx(&cfg, kern, a);
+}
+
+// Can a 16-CTA cluster of this kernel be scheduled on the current device at all?  (asked once per group size)
+template <int G>
+bool cluster_ok_t() {
+  auto kern = attn_decode_cluster_kernel<G>;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) { (void)cudaGetLastError(); return false; }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(8, kCl, 1);
+  cfg.blockDim = dim3(128);
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = 1; at[0].val.clusterDim.y = kCl; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) { (void)cudaGetLastError(); return false; }
+  return n >= 1;
+}
+
 }  // namespace
+
+bool attn_cluster_supported(int group) {
+  switch (group) {
+    case 1: return cluster_ok_t<1>();
+    case 2: return cluster_ok_t<2>();
+    case 4: return cluster_ok_t<4>();
+    case 8: return cluster_ok_t<8>();
+  }
+  return false;
+}
 
 size_t attn_partial_floats(int n_heads, int n_kv_heads, int n_splits) {
   return (size_t)n_kv_heads * n_splits * (n_heads / n_kv_heads) * kPart;
@@ -221,7 +451,17 @@ cudaError_t launch_attn_decode(const AttnArgs& a, cudaStream_t s, bool pdl) {
   at[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
   cfg.numAttrs = pdl ? 1 : 0;
-  // the batch-1 decode step (one query, the engine's own block table, cache rows readable ahead of the dependency)
+  // the batch-1 decode step (one query, the engine's own block table, cache rows readable ahead of the dependency):
+  // the cluster kernel when the engine asked for it (a.use_cluster; it checked attn_cluster_supported first)
+  if (a.prefetch_tokens > 0 && a.use_cluster && a.n_queries <= 1 && !a.q_ctx && !a.q_slot) {
+    switch (a.n_heads / a.n_kv_heads) {
+      case 1: return launch_cluster_t<1>(a, s, pdl);
+      case 2: return launch_cluster_t<2>(a, s, pdl);
+      case 4: return launch_cluster_t<4>(a, s, pdl);
+      case 8: return launch_cluster_t<8>(a, s, pdl);
+    }
+    return cudaErrorInvalidValue;
+  }
   if (a.prefetch_tokens > 0 && a.n_queries <= 1 && !a.q_ctx && !a.q_slot) {
     switch (a.n_heads / a.n_kv_heads) {
       case 1: return count_launch(), cudaLaunchKernelEx(&cfg, attn_decode_fast_kernel<1>, a);

@@ -95,6 +95,7 @@ int Engine::init(const b200_config& c, const void* nccl_id) {
   use_fa_prefill = getenv("B200_NO_FA_PREFILL") == nullptr;
   use_mma_decode = getenv("B200_NO_MMA_DECODE") == nullptr;
   use_attn_prefetch = getenv("B200_NO_ATTN_PREFETCH") == nullptr;
+  use_attn_cluster = use_attn_prefetch && getenv("B200_NO_ATTN_CLUSTER") == nullptr && attn_cluster_supported(c.n_heads / c.n_kv_heads);
   use_prefix_cache = getenv("B200_NO_PREFIX_CACHE") == nullptr && (c.reserved & 2) == 0 && tp_size == 1;
   // measured on B200 (round 1): chaining L2 prefetches of the next kernel's weights made the step SLOWER
   // (bf16 3.18 vs 3.05 ms, Q4_K_M 1.84 vs 1.78 ms), so it is opt-in for experiments only
@@ -418,11 +419,6 @@ int Engine::enqueue_step(cudaStream_t s) {
   const int d = c.d_model, qd = c.n_heads * kHeadDim, kvd = c.n_kv_heads * kHeadDim, ff = c.d_ffn;
   const bool tp = tp_size > 1;
   int n = 0;
-  if (getenv("B200_TRACE") && !trace_dev) {
-    int rc = alloc((void**)&trace_dev, (size_t)(6 * c.n_layers + 8) * 4 * 8);
-    if (rc) return rc;
-    B200_CUDA(cudaMemset(trace_dev, 0, (size_t)(6 * c.n_layers + 8) * 4 * 8));
-  }
   trace_names.clear();
   auto tr = [&](const char* name) -> unsigned long long* {  // stamps of the launch about to be enqueued
     if (!trace_dev) return nullptr;
@@ -475,6 +471,7 @@ int Engine::enqueue_step(cudaStream_t s) {
     t.n_heads = c.n_heads; t.n_kv_heads = c.n_kv_heads; t.out = att; t.partial = attn_partial; t.counters = attn_counters;
     t.n_splits = n_splits; t.fixed_ctx = 0;
     t.prefetch_tokens = use_attn_prefetch ? pages_per_seq * kPageTokens : 0;
+    t.use_cluster = use_attn_cluster ? 1 : 0;
     t.trace = tr("attn");
     B200_CUDA(launch_attn_decode(t, s, use_pdl)); ++n;
     // row-parallel projections: without TP the residual add is the GEMV epilogue; with TP every rank holds a
@@ -523,6 +520,12 @@ int Engine::enqueue_step(cudaStream_t s) {
 
 int Engine::ensure_graph() {
   if (!all_set()) { set_error("not all tensors are set"); return B200_ESTATE; }
+  if (getenv("B200_TRACE") && !trace_dev) {  // before any capture: allocation is not allowed inside one
+    const size_t bytes = (size_t)(6 * lc.n_layers + 8) * 4 * 8;
+    int rc = alloc((void**)&trace_dev, bytes);
+    if (rc) return rc;
+    B200_CUDA(cudaMemset(trace_dev, 0, bytes));
+  }
   if (!use_graph || step_graph) return 0;
   for (int attempt = 0; attempt < 2; ++attempt) {
     cudaGraph_t g = nullptr;

@@ -172,7 +172,7 @@ struct Engine {
 
   cudaGraphExec_t step_graph = nullptr;
   int step_graph_nodes = 0;  // kernel nodes of the captured step (counted as launches at every replay)
-  bool use_pdl = true, use_graph = true, use_l2_chain = false, use_fa_prefill = true, use_mma_decode = true, use_attn_prefetch = true;
+  bool use_pdl = true, use_graph = true, use_l2_chain = false, use_fa_prefill = true, use_mma_decode = true, use_attn_prefetch = true, use_attn_cluster = false;
   // n_seqs sequences decoding together from a context of ctx tokens, synchronously (no scheduler thread): the
   // batched step of scheduler.cu, tensor-parallel aware (every rank makes the same call)
   int bench_batched(int n_seqs, int ctx, int n_steps, float* ms_per_step, int32_t* last_ids);

@@ -138,9 +138,11 @@ struct AttnArgs {
   // re-read).  0: the plain kernel.
   int prefetch_tokens;
   unsigned long long* trace;  // debug (B200_TRACE), as in GemvArgs
+  int use_cluster;            // batch-1 decode step: the 16-CTA cluster kernel (merge over distributed shared memory)
 };
 cudaError_t launch_attn_decode(const AttnArgs& a, cudaStream_t s, bool pdl);
 size_t attn_partial_floats(int n_heads, int n_kv_heads, int n_splits);
+bool attn_cluster_supported(int group);  // can the device schedule the 16-CTA cluster kernel for this GQA group size?
 // allocation-free variant: scratch in a static __device__ array inside attn.cu (see there)
 cudaError_t launch_attn_decode_noalloc(const float* q, const uint16_t* k_cache, const uint16_t* v_cache,
                                        const int32_t* block_table, int n_ctx, int n_heads, int n_kv_heads, float* out,
