@@ -90,15 +90,16 @@ __global__ void __launch_bounds__(128) attn_decode_fast_kernel(const AttnArgs a)
   const int pos = a.fixed_ctx > 0 ? a.fixed_ctx - 1 : a.st->pos;
   const int ctx = pos + 1;
   const float scale = 1.0f / sqrtf((float)kHeadDim);
-  for (int i = tid; i < G * kHeadDim / 4; i += 128)
-    reinterpret_cast<float4*>(sm.qs)[i] = __ldcg(reinterpret_cast<const float4*>(a.q + (size_t)kvh * G * kHeadDim) + i);
   asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();  // the prefetched rows have landed before the current row is written over its stale copy
   {
     const int lo = pos > a.prefetch_tokens ? a.prefetch_tokens : pos;  // rows not covered by the prefetch, and `pos`
-    gather(split, lo, ctx);
-    cp_async_commit_wait_all();
+    gather(split, lo, ctx);  // issued first: its round trip overlaps the fetch of the query vector
+    asm volatile("cp.async.commit_group;" ::: "memory");
   }
+  for (int i = tid; i < G * kHeadDim / 4; i += 128)
+    reinterpret_cast<float4*>(sm.qs)[i] = __ldcg(reinterpret_cast<const float4*>(a.q + (size_t)kvh * G * kHeadDim) + i);
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
   float acc[G];
 #pragma unroll
   for (int h = 0; h < G; ++h) acc[h] = 0.f;
@@ -147,8 +148,10 @@ __global__ void __launch_bounds__(128) attn_decode_fast_kernel(const AttnArgs a)
     __syncthreads();
 #pragma unroll
     for (int h = 0; h < G; ++h) acc[h] *= sm.corr_s[h];
-    for (int t = 0; t < n_valid; ++t) {  // P.V: thread = output dim; rows past the context are never touched
-      const float v = __uint_as_float((uint32_t)sm.Vs[t * kHeadDim + tid] << 16);
+#pragma unroll 8
+    for (int t = 0; t < kTile; ++t) {  // P.V: thread = output dim.  Fixed trip count so the loads pipeline; rows past the
+      float v = __uint_as_float((uint32_t)sm.Vs[t * kHeadDim + tid] << 16);  // context hold older data (P is 0 there):
+      v = t < n_valid ? v : 0.f;                                             // forced to 0 so nothing odd can leak in
 #pragma unroll
       for (int h = 0; h < G; ++h) acc[h] = fmaf(sm.P[h][t], v, acc[h]);
     }
@@ -212,13 +215,14 @@ __global__ void __launch_bounds__(128) attn_decode_fast_kernel(const AttnArgs a)
 // cluster barrier CTA r combines output dims [8r, 8r+8) of all G heads from the 16 CTAs and stores them; a second
 // barrier keeps every CTA's shared memory alive until its peers have read it.  Needs no scratch and no counters.
 constexpr int kCl = 16;  // cluster size (non-portable: opted in at launch; the launcher falls back if refused)
+constexpr int kClPre = 2;  // tiles per CTA held in shared memory: 2 x 16 x 32 = contexts up to 1024 tokens need no fetch after the wait
 
 template <int G>
 struct AttnClSmem {
-  alignas(16) uint16_t Ks[kTile * kHeadDim];
-  alignas(16) uint16_t Vs[kTile * kHeadDim];
+  alignas(16) uint16_t Ks[kClPre][kTile * kHeadDim];  // the first kClPre tiles of this split, both fetched ahead of the dependency
+  alignas(16) uint16_t Vs[kClPre][kTile * kHeadDim];
   alignas(16) float qs[G * kHeadDim];
-  float P[G][kTile];
+  float P[G][kTile], P2[G][kTile];  // softmax numerators of the pass's first / second tile
   float m_run[G], l_run[G], corr_s[G];
   alignas(16) float accS[G][kHeadDim];   // this CTA's un-normalised partial, read by its cluster peers
   float mAll[G][kCl], lAll[G][kCl], wAll[G][kCl];
@@ -251,24 +255,45 @@ __global__ void __launch_bounds__(128) attn_decode_cluster_kernel(const AttnArgs
   __shared__ AttnClSmem<G> sm;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int kvh = blockIdx.x, split = (int)cluster_ctarank(), S = kCl;
-  const uint32_t ks_s = smem_u32(sm.Ks), vs_s = smem_u32(sm.Vs);
-  auto gather = [&](int tile, int row_lo, int row_hi) {
+  // thread = one 16-byte chunk of 4 rows per tile: item j -> row t = (tid + 128 j) / 16 of the tile, chunk c = tid % 16
+  const int c = tid & 15;
+  auto row_addr = [&](int page, int tok) {
+    return (((size_t)page * a.n_kv_heads + kvh) * kPageTokens + (tok % kPageTokens)) * kHeadDim + c * 8;
+  };
+  auto gather = [&](int buf, int tile, int row_lo, int row_hi) {  // with block-table look-ups (tiles beyond the first kClPre)
+    const uint32_t ks_s = smem_u32(sm.Ks[buf]), vs_s = smem_u32(sm.Vs[buf]);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const int item = tid + 128 * j, t = item >> 4, c = item & 15;
-      const int tok = tile * kTile + t;
+      const int t = (tid + 128 * j) >> 4, tok = tile * kTile + t;
       if (tok >= row_lo && tok < row_hi) {
-        const int page = a.block_table[tok / kPageTokens];
-        const size_t row = (((size_t)page * a.n_kv_heads + kvh) * kPageTokens + (tok % kPageTokens)) * kHeadDim;
-        cp_async16(ks_s + (uint32_t)(t * kHeadDim * 2 + ((c ^ (t & 7)) << 4)), a.k_cache + row + c * 8);
-        cp_async16(vs_s + (uint32_t)(t * kHeadDim * 2 + (c << 4)), a.v_cache + row + c * 8);
+        const size_t row = row_addr(a.block_table[tok / kPageTokens], tok);
+        cp_async16(ks_s + (uint32_t)(t * kHeadDim * 2 + ((c ^ (t & 7)) << 4)), a.k_cache + row);
+        cp_async16(vs_s + (uint32_t)(t * kHeadDim * 2 + (c << 4)), a.v_cache + row);
       }
     }
   };
   const bool tracer = a.trace != nullptr && kvh == 0 && split == 0 && tid == 0;
   if (tracer) a.trace[0] = global_timer_ns();
-  gather(split, 0, a.prefetch_tokens);  // before the dependency, as in attn_decode_fast_kernel
-  asm volatile("cp.async.commit_group;" ::: "memory");
+  // ---- before the dependency: everything that does not depend on the projection kernel still running.  The page of
+  // every row this thread will fetch (kept in registers), and an L2 prefetch of those rows, so that the real fetch —
+  // issued after the wait, because one of the rows is being written by that kernel — is a single round trip to L2
+  // with no block-table look-up in front of it.
+  int page[kClPre][4];
+#pragma unroll
+  for (int i = 0; i < kClPre; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int t = (tid + 128 * j) >> 4, tok = (split + i * S) * kTile + t;
+      page[i][j] = -1;
+      if (tok < a.prefetch_tokens) {
+        page[i][j] = a.block_table[tok / kPageTokens];
+        if ((c & 7) == 0) {  // one prefetch per 128-byte line
+          const size_t row = row_addr(page[i][j], tok);
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(a.k_cache + row));
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(a.v_cache + row));
+        }
+      }
+    }
   if (tid < G) {
     sm.m_run[tid] = -INFINITY;
     sm.l_run[tid] = 0.f;
@@ -276,56 +301,71 @@ __global__ void __launch_bounds__(128) attn_decode_cluster_kernel(const AttnArgs
   pdl_wait();
   pdl_launch_dependents();
   if (tracer) a.trace[1] = global_timer_ns();
-  const int pos = a.fixed_ctx > 0 ? a.fixed_ctx - 1 : a.st->pos;
-  const int ctx = pos + 1;
-  const float scale = 1.0f / sqrtf((float)kHeadDim);
+  // ---- after the dependency: K/V rows, the query vector and the position, all in flight together
+#pragma unroll
+  for (int i = 0; i < kClPre; ++i) {
+    const uint32_t ks_s = smem_u32(sm.Ks[i]), vs_s = smem_u32(sm.Vs[i]);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int t = (tid + 128 * j) >> 4, tok = (split + i * S) * kTile + t;
+      if (page[i][j] >= 0) {  // rows at or beyond the context hold older data: fetched anyway (no need to know the position yet), masked below
+        const size_t row = row_addr(page[i][j], tok);
+        cp_async16(ks_s + (uint32_t)(t * kHeadDim * 2 + ((c ^ (t & 7)) << 4)), a.k_cache + row);
+        cp_async16(vs_s + (uint32_t)(t * kHeadDim * 2 + (c << 4)), a.v_cache + row);
+      }
+    }
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
   for (int i = tid; i < G * kHeadDim / 4; i += 128)
     reinterpret_cast<float4*>(sm.qs)[i] = __ldcg(reinterpret_cast<const float4*>(a.q + (size_t)kvh * G * kHeadDim) + i);
+  const int pos = a.fixed_ctx > 0 ? a.fixed_ctx - 1 : __ldcg(&a.st->pos);
+  const int ctx = pos + 1;
+  const float scale = 1.0f / sqrtf((float)kHeadDim);
   asm volatile("cp.async.wait_group 0;" ::: "memory");
-  __syncthreads();
-  {
-    const int lo = pos > a.prefetch_tokens ? a.prefetch_tokens : pos;
-    gather(split, lo, ctx);
-    cp_async_commit_wait_all();
-  }
   float acc[G];
 #pragma unroll
   for (int h = 0; h < G; ++h) acc[h] = 0.f;
   __syncthreads();
 
-  for (int tile = split; tile * kTile < ctx; tile += S) {
-    const int t0 = tile * kTile;
-    if (tile != split) {
-      gather(tile, 0, ctx);
+  // Two tiles per pass (this CTA's tiles split + 2pS and split + (2p+1)S, 64 tokens): their scores run as independent
+  // chains in the same loop and share one softmax update and one set of barriers.  Pass 0 uses the rows fetched above.
+  static_assert(kClPre == 2, "a pass covers the two prefetched tiles");
+  for (int pass = 0; (split + 2 * pass * S) * kTile < ctx; ++pass) {
+    const int tileA = split + 2 * pass * S, tileB = tileA + S;
+    if (pass > 0) {  // contexts beyond 1024 tokens: fetched in place
+      gather(0, tileA, 0, ctx);
+      gather(1, tileB, 0, ctx);
       cp_async_commit_wait_all();
       __syncthreads();
     }
-    const int n_valid = ctx - t0 < kTile ? ctx - t0 : kTile;
+    const int nA = min(ctx - tileA * kTile, kTile), nB = max(0, min(ctx - tileB * kTile, kTile));
     for (int h = warp; h < G; h += 4) {
-      const uint4* kr = reinterpret_cast<const uint4*>(sm.Ks + lane * kHeadDim);
+      const uint4* ka = reinterpret_cast<const uint4*>(sm.Ks[0] + lane * kHeadDim);
+      const uint4* kb = reinterpret_cast<const uint4*>(sm.Ks[1] + lane * kHeadDim);
       const float4* qh = reinterpret_cast<const float4*>(sm.qs + h * kHeadDim);
-      float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+      float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f, b0 = 0.f, b1 = 0.f, b2 = 0.f, b3 = 0.f;
 #pragma unroll
       for (int c = 0; c < 16; ++c) {
-        const uint4 k = kr[c ^ (lane & 7)];
+        const uint4 k = ka[c ^ (lane & 7)], j = kb[c ^ (lane & 7)];
         const float4 qa = qh[2 * c], qb = qh[2 * c + 1];
-        s0 = fmaf(qa.x, bf16lo(k.x), s0);
-        s1 = fmaf(qa.y, bf16hi(k.x), s1);
-        s2 = fmaf(qa.z, bf16lo(k.y), s2);
-        s3 = fmaf(qa.w, bf16hi(k.y), s3);
-        s0 = fmaf(qb.x, bf16lo(k.z), s0);
-        s1 = fmaf(qb.y, bf16hi(k.z), s1);
-        s2 = fmaf(qb.z, bf16lo(k.w), s2);
-        s3 = fmaf(qb.w, bf16hi(k.w), s3);
+        a0 = fmaf(qa.x, bf16lo(k.x), a0); b0 = fmaf(qa.x, bf16lo(j.x), b0);
+        a1 = fmaf(qa.y, bf16hi(k.x), a1); b1 = fmaf(qa.y, bf16hi(j.x), b1);
+        a2 = fmaf(qa.z, bf16lo(k.y), a2); b2 = fmaf(qa.z, bf16lo(j.y), b2);
+        a3 = fmaf(qa.w, bf16hi(k.y), a3); b3 = fmaf(qa.w, bf16hi(j.y), b3);
+        a0 = fmaf(qb.x, bf16lo(k.z), a0); b0 = fmaf(qb.x, bf16lo(j.z), b0);
+        a1 = fmaf(qb.y, bf16hi(k.z), a1); b1 = fmaf(qb.y, bf16hi(j.z), b1);
+        a2 = fmaf(qb.z, bf16lo(k.w), a2); b2 = fmaf(qb.z, bf16lo(j.w), b2);
+        a3 = fmaf(qb.w, bf16hi(k.w), a3); b3 = fmaf(qb.w, bf16hi(j.w), b3);
       }
-      float sc = (s0 + s1) + (s2 + s3);
-      const bool valid = lane < n_valid;
-      sc = valid ? sc * scale : -INFINITY;
+      const bool va = lane < nA, vb = lane < nB;
+      const float sa = va ? ((a0 + a1) + (a2 + a3)) * scale : -INFINITY;
+      const float sb = vb ? ((b0 + b1) + (b2 + b3)) * scale : -INFINITY;
       const float m_old = sm.m_run[h];
-      const float m_new = fmaxf(m_old, warp_max(sc));
-      const float p = valid ? expf(sc - m_new) : 0.f;
-      const float l_tile = warp_sum(p);
-      sm.P[h][lane] = p;
+      const float m_new = fmaxf(m_old, warp_max(fmaxf(sa, sb)));
+      const float pa = va ? expf(sa - m_new) : 0.f, pb = vb ? expf(sb - m_new) : 0.f;
+      const float l_tile = warp_sum(pa + pb);
+      sm.P[h][lane] = pa;
+      sm.P2[h][lane] = pb;
       if (lane == 0) {
         const float corr = (m_old == -INFINITY) ? 0.f : expf(m_old - m_new);
         sm.corr_s[h] = corr;
@@ -336,10 +376,21 @@ __global__ void __launch_bounds__(128) attn_decode_cluster_kernel(const AttnArgs
     __syncthreads();
 #pragma unroll
     for (int h = 0; h < G; ++h) acc[h] *= sm.corr_s[h];
-    for (int t = 0; t < n_valid; ++t) {
-      const float v = __uint_as_float((uint32_t)sm.Vs[t * kHeadDim + tid] << 16);
+#pragma unroll 8
+    for (int t = 0; t < kTile; ++t) {  // fixed trip count (loads pipeline); rows past the context are forced to 0
+      float v = __uint_as_float((uint32_t)sm.Vs[0][t * kHeadDim + tid] << 16);
+      v = t < nA ? v : 0.f;
 #pragma unroll
       for (int h = 0; h < G; ++h) acc[h] = fmaf(sm.P[h][t], v, acc[h]);
+    }
+    if (nB > 0) {
+#pragma unroll 8
+      for (int t = 0; t < kTile; ++t) {
+        float v = __uint_as_float((uint32_t)sm.Vs[1][t * kHeadDim + tid] << 16);
+        v = t < nB ? v : 0.f;
+#pragma unroll
+        for (int h = 0; h < G; ++h) acc[h] = fmaf(sm.P2[h][t], v, acc[h]);
+      }
     }
     __syncthreads();
   }
