@@ -79,15 +79,29 @@ DEVINL void gemv_body(const GemvArgs& a, int cta, int n_ctas) {
     }
     if (++p_stage == F::STAGES) p_stage = 0;
   };
+  // Before the dependency: the whole ring.  (Tried, round 2: one stage before the wait and the rest right after the
+  // prologue has issued its activation loads, in case those loads queue behind the ring at the SM's memory port —
+  // no gain for Q4_K, and bf16 ffn_down's prologue went from 1.1 to 2.5 us.)
 #pragma unroll
   for (int s = 0; s < F::STAGES; ++s)
     if (p_item < n_items) produce();
+  auto fill_rest = [] {};
+  // RMS-norm weights do not depend on the previous kernel either: this thread's share (the element -> thread mapping of
+  // the single-fetch prologues, K <= 8192) goes to registers now, so the prologue waits for the activations only
+  constexpr int kPU = ProU<F::NW>::value;
+  float4 nw[kPU];
+#pragma unroll
+  for (int u = 0; u < kPU; ++u) {
+    const int k = 4 * ((int)threadIdx.x + u * F::NW * 32);
+    nw[u] = (PRO == PRO_RMSNORM && k < a.K && a.K <= F::NW * 32 * 4 * kPU) ? __ldg(reinterpret_cast<const float4*>(a.norm_w + k))
+                                                                          : make_float4(1.f, 1.f, 1.f, 1.f);
+  }
   if (EPI != EPI_LOGITS) {
     pdl_launch_dependents();
     pdl_wait();
   }
   if (tracer) a.trace[1] = global_timer_ns();
-  F::template prologue<PRO>(xs, a, red, warp, lane);
+  F::template prologue<PRO>(xs, a, red, warp, lane, nw, fill_rest);
   if (tracer) a.trace[2] = global_timer_ns();
   if (EPI == EPI_LOGITS) pdl_launch_dependents();
 

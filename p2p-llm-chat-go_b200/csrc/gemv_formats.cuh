@@ -129,11 +129,12 @@ struct FmtBF16 {
 
   // x in shared memory, permuted per 256-group so that lane l's 8 values are two conflict-free float4:
   // element 8l+j  ->  (j<4 ? 4l+j : 128+4l+(j-4))
-  template <int PRO>
-  static DEVINL void prologue(uint8_t* xs_, const GemvArgs& a, float* red, int warp, int lane) {
+  template <int PRO, class AfterIssue>
+  static DEVINL void prologue(uint8_t* xs_, const GemvArgs& a, float* red, int warp, int lane, const float4* nw, AfterIssue&& after_issue) {
     constexpr int kProU = ProU<NW>::value;
     float* xs = reinterpret_cast<float*>(xs_);
     if (PRO == PRO_TP_RMSNORM) {
+      after_issue();
       tp_prologue<NW>(xs, a, red, warp, lane);
       return;
     }
@@ -146,8 +147,9 @@ struct FmtBF16 {
         const int k = threadIdx.x * 4 + i * NW * 32 * 4;
         const bool on = k < a.K;
         v[i] = on ? __ldcg(reinterpret_cast<const float4*>(a.x + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
-        w[i] = on ? *reinterpret_cast<const float4*>(a.norm_w + k) : make_float4(0.f, 0.f, 0.f, 0.f);
+        w[i] = nw[i];  // norm weights: fetched before the dependency wait (gemv_body)
       }
+      after_issue();  // the activation loads are on their way: now the rest of the weight ring may queue up behind them
       float ss = 0.f;
 #pragma unroll
       for (int i = 0; i < kProU; ++i)
@@ -170,9 +172,15 @@ struct FmtBF16 {
       __syncthreads();
       return;
     }
+    if (PRO == PRO_RMSNORM) after_issue();
     const float inv = rms_inv<PRO, NW>(a, red, warp, lane);
+    bool issued = PRO == PRO_RMSNORM;
     for (int k = threadIdx.x * 4; k < a.K; k += NW * 32 * 4) {
       float4 v = __ldcg(reinterpret_cast<const float4*>(a.x + k));
+      if (!issued) {  // first activation load of this thread is on its way: now the rest of the weight ring
+        after_issue();
+        issued = true;
+      }
       if (PRO == PRO_RMSNORM) {
         const float4 w = *reinterpret_cast<const float4*>(a.norm_w + k);
         v.x = __fmul_rn(__fmul_rn(v.x, inv), w.x);
@@ -183,6 +191,7 @@ struct FmtBF16 {
       const int idx = (k & ~255) + ((k >> 2) & 1) * 128 + ((k & 255) >> 3) * 4;
       *reinterpret_cast<float4*>(xs + idx) = v;
     }
+    if (!issued) after_issue();  // (a thread with no element of its own)
     __syncthreads();
   }
 
@@ -246,8 +255,8 @@ DEVINL int dp2a_hi_ss(uint32_t x2, uint32_t q4, int c) {
 // small non-negative integer (< 2^23) -> float without the conversion pipe
 DEVINL float small_u2f(uint32_t v) { return __uint_as_float(0x4B000000u | v) - 8388608.0f; }
 
-template <class F, int PRO>
-DEVINL void q16_prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane) {
+template <class F, int PRO, class AfterIssue>
+DEVINL void q16_prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane, const float4* nw, AfterIssue&& after_issue) {
   int16_t* xq = reinterpret_cast<int16_t*>(xs);
   float* dx = reinterpret_cast<float*>(xs + 2 * (size_t)a.K);
   float* dxs = dx + a.K / 32;
@@ -255,7 +264,9 @@ DEVINL void q16_prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, i
   // U rounds of loads are issued before the first dependent shuffle.  ~15 instructions per block instead of
   // ~120 with one element per lane, which matters because every CTA repeats this for the whole vector.
   constexpr int NW = F::NW;
-  constexpr int U = ProU<NW>::value;
+  // float4 per thread and round.  Without a norm there are no weights to hold, so twice as many activations fit in the
+  // same registers: K = 14336 (ffn_down's input) is then ONE round of loads, all in flight before the first shuffle
+  constexpr int U = (PRO == PRO_RMSNORM) ? ProU<NW>::value : 2 * ProU<NW>::value;
   const int n4 = a.K / 4;
   // K <= 8192 with an RMS norm: x and the norm weights are fetched once, before the block-wide sum of
   // squares, and reused from registers below (thread -> element mapping and summation order as in rms_inv)
@@ -268,16 +279,19 @@ DEVINL void q16_prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, i
     for (int u = 0; u < U; ++u) {
       const int gi = u * NW * 32 + (int)threadIdx.x;
       v[u] = gi < n4 ? __ldcg(reinterpret_cast<const float4*>(a.x + 4 * gi)) : make_float4(0.f, 0.f, 0.f, 0.f);
-      g[u] = gi < n4 ? *reinterpret_cast<const float4*>(a.norm_w + 4 * gi) : make_float4(1.f, 1.f, 1.f, 1.f);
+      g[u] = nw[u];  // norm weights: fetched before the dependency wait (gemv_body)
     }
+    after_issue();  // activation loads issued: the rest of the weight ring may now queue up behind them
 #pragma unroll
     for (int u = 0; u < U; ++u)
       if (u * NW * 32 + (int)threadIdx.x < n4) ss += v[u].x * v[u].x + v[u].y * v[u].y + v[u].z * v[u].z + v[u].w * v[u].w;
     ss = block_sum<NW>(ss, red, warp, lane);
     inv = 1.0f / sqrtf(ss / (float)a.K + a.eps);
   } else {
+    if (PRO == PRO_RMSNORM) after_issue();
     inv = rms_inv<PRO, NW>(a, red, warp, lane);
   }
+  bool issued = single || PRO == PRO_RMSNORM;
   for (int g0 = warp * 32; g0 < n4; g0 += NW * 32 * U) {
     if (!single) {
 #pragma unroll
@@ -285,6 +299,10 @@ DEVINL void q16_prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, i
         const int gi = g0 + u * NW * 32 + lane;
         v[u] = gi < n4 ? __ldcg(reinterpret_cast<const float4*>(a.x + 4 * gi)) : make_float4(0.f, 0.f, 0.f, 0.f);
         g[u] = (PRO == PRO_RMSNORM && gi < n4) ? *reinterpret_cast<const float4*>(a.norm_w + 4 * gi) : make_float4(1.f, 1.f, 1.f, 1.f);
+      }
+      if (!issued) {
+        after_issue();
+        issued = true;
       }
     }
 #pragma unroll
@@ -347,9 +365,9 @@ struct FmtQ4K {
 #pragma unroll
     for (int r = 0; r < R; ++r) bulk_g2s(dst + r * ROW_STAGE_BYTES, src + (size_t)r * rb, ROW_STAGE_BYTES, bar, pol);
   }
-  template <int PRO>
-  static DEVINL void prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane) {
-    q16_prologue<FmtQ4K<R_, C>, PRO>(xs, a, red, warp, lane);
+  template <int PRO, class AfterIssue>
+  static DEVINL void prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane, const float4* nw, AfterIssue&& after_issue) {
+    q16_prologue<FmtQ4K<R_, C>, PRO>(xs, a, red, warp, lane, nw, after_issue);
   }
 
   static DEVINL void consume(const uint8_t* st, const uint8_t* xs, int c, const GemvArgs& a, int lane, float* acc) {
@@ -432,9 +450,9 @@ struct FmtQ6K {
 #pragma unroll
     for (int r = 0; r < R; ++r) bulk_g2s(dst + r * ROW_STAGE_BYTES, src + (size_t)r * rb, ROW_STAGE_BYTES, bar, pol);
   }
-  template <int PRO>
-  static DEVINL void prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane) {
-    q16_prologue<FmtQ6K<C>, PRO>(xs, a, red, warp, lane);
+  template <int PRO, class AfterIssue>
+  static DEVINL void prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane, const float4* nw, AfterIssue&& after_issue) {
+    q16_prologue<FmtQ6K<C>, PRO>(xs, a, red, warp, lane, nw, after_issue);
   }
 
   static DEVINL void consume(const uint8_t* st, const uint8_t* xs, int c, const GemvArgs& a, int lane, float* acc) {
