@@ -39,6 +39,7 @@ extern "C" {
 
 /* tensor storage types: ggml / GGUF type ids, so a GGUF loader passes them through unchanged */
 #define B200_TYPE_F32 0
+#define B200_TYPE_F16 1   /* as stored by F16 GGUF files; the tensor-core path rounds it to bf16 */
 #define B200_TYPE_Q4_K 12
 #define B200_TYPE_Q6_K 14
 #define B200_TYPE_BF16 30
@@ -154,7 +155,7 @@ B200_API int b200_prefix_match(b200_engine* e, const int32_t* ids, size_t n);
 
 /* ---- GGUF model files (what `ollama pull llama3.1` leaves on disk, README.md:70) ---------------------- */
 /* Reads shapes, storage types and the tokenizer vocabulary from a GGUF v2/v3 file of architecture "llama"
- * and uploads every tensor (BF16, Q4_K, Q6_K matrices; F32 norms; the file dictates each tensor's type).
+ * and uploads every tensor (BF16, F16, Q4_K, Q6_K matrices; F32 norms; the file dictates each tensor's type).
  * b200_gguf_info needs no GPU.  A stand-alone tokenizer handle is offered for hosts that tokenise elsewhere. */
 typedef struct b200_tok b200_tok;
 B200_API int b200_gguf_info(const char* path, b200_config* cfg, int64_t* n_tensors, int64_t* n_vocab_tokens, int64_t* n_merges);

@@ -39,7 +39,7 @@
 #define ORC_API extern "C" __attribute__((visibility("default")))
 
 // ggml tensor type ids (GGUF spec) — the same codes the C-ABI uses.
-enum { ORC_F32 = 0, ORC_Q4_K = 12, ORC_Q6_K = 14, ORC_BF16 = 30 };
+enum { ORC_F32 = 0, ORC_F16 = 1, ORC_Q4_K = 12, ORC_Q6_K = 14, ORC_BF16 = 30 };
 enum { QK_K = 256, Q4K_BYTES = 144, Q6K_BYTES = 210 };
 
 struct orc_config {
@@ -178,6 +178,7 @@ size_t row_bytes(int wtype, int64_t cols) {
   switch (wtype) {
     case ORC_F32: return (size_t)cols * 4;
     case ORC_BF16: return (size_t)cols * 2;
+    case ORC_F16: return (size_t)cols * 2;
     case ORC_Q4_K: return (size_t)(cols / QK_K) * Q4K_BYTES;
     case ORC_Q6_K: return (size_t)(cols / QK_K) * Q6K_BYTES;
   }
@@ -187,6 +188,13 @@ size_t row_bytes(int wtype, int64_t cols) {
 void dequant_row(int wtype, const uint8_t* row, int64_t cols, float* out) {
   switch (wtype) {
     case ORC_F32: memcpy(out, row, (size_t)cols * 4); break;
+    case ORC_F16:  // IEEE half, as F16 GGUF files store it
+      for (int64_t k = 0; k < cols; ++k) {
+        uint16_t h;
+        memcpy(&h, row + 2 * k, 2);
+        out[k] = fp16_to_f32(h);
+      }
+      break;
     case ORC_BF16:
       for (int64_t k = 0; k < cols; ++k) {
         uint16_t h;
@@ -282,7 +290,7 @@ void matmul(int wtype, const void* W, int64_t rows, int64_t cols, const float* X
 #pragma omp parallel
   {
     std::vector<float> wrow;
-    if (quant || wtype == ORC_F32 || n > 1) wrow.resize(cols);
+    if (quant || wtype == ORC_F32 || wtype == ORC_F16 || n > 1) wrow.resize(cols);
 #pragma omp for schedule(static)
     for (int64_t r = 0; r < rows; ++r) {
       const uint8_t* row = (const uint8_t*)W + (size_t)r * rb;
@@ -308,7 +316,7 @@ void matmul(int wtype, const void* W, int64_t rows, int64_t cols, const float* X
         continue;
       }
       dequant_row(wtype, row, cols, wrow.data());
-      if (mode == 1 && quant)
+      if (mode == 1 && (quant || wtype == ORC_F16))  // GEMM operands are bf16: k-quant and F16 weights are rounded to it
         for (int64_t k = 0; k < cols; ++k) wrow[k] = bf16_round(wrow[k]);
       // fp32 products, double accumulation.  The reduction clause lets the compiler keep one partial sum per vector
       // lane (the order of a double sum of fp32 products moves the result by ~1e-16 relative: far below fp32);
@@ -501,7 +509,7 @@ ORC_API int orc_model_truncate(orc_model* m, int n) {
 // attn_output,ffn_norm,ffn_gate,ffn_up,ffn_down}.weight, output_norm.weight, output.weight.
 ORC_API int orc_model_set_tensor(orc_model* m, const char* name, int type, const void* data, int64_t rows,
                                  int64_t cols) {
-  if (type != ORC_F32 && type != ORC_BF16 && type != ORC_Q4_K && type != ORC_Q6_K) return -1;
+  if (type != ORC_F32 && type != ORC_F16 && type != ORC_BF16 && type != ORC_Q4_K && type != ORC_Q6_K) return -1;
   if ((type == ORC_Q4_K || type == ORC_Q6_K) && cols % QK_K) return -2;
   Tensor t;
   t.type = type;

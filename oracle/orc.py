@@ -11,7 +11,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "_build", "liboracle.so")
 
-F32, Q4_K, Q6_K, BF16 = 0, 12, 14, 30
+F32, F16, Q4_K, Q6_K, BF16 = 0, 1, 12, 14, 30
 QK_K, Q4K_BYTES, Q6K_BYTES = 256, 144, 210
 
 

@@ -19,7 +19,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libb200llm.so")
 HEADER_PATH = os.path.join(os.path.dirname(HERE), "include", "b200llm.h")
 
-F32, Q4_K, Q6_K, BF16 = 0, 12, 14, 30
+F32, F16, Q4_K, Q6_K, BF16 = 0, 1, 12, 14, 30
 WEIGHTS_BF16, WEIGHTS_Q4_K_M = 0, 1
 MODE_GEMV, MODE_GEMM = 0, 1
 ENODEV = -2

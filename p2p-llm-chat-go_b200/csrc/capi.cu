@@ -317,7 +317,8 @@ static int gguf_config(const GgufFile& f, b200_config* cfg, int64_t* n_tensors) 
   cfg->seed = -1;
   const GgufTensor* q = f.tensor("blk.0.attn_q.weight");
   if (!q) { set_error("GGUF file has no blk.0.attn_q.weight"); return B200_EINVAL; }
-  cfg->weight_format = q->type == T_BF16 ? B200_WEIGHTS_BF16 : B200_WEIGHTS_Q4_K_M;
+  // a label only (the file dictates every tensor's storage type): 16-bit float files count as the bf16 recipe
+  cfg->weight_format = (q->type == T_BF16 || q->type == T_F16) ? B200_WEIGHTS_BF16 : B200_WEIGHTS_Q4_K_M;
   if (n_tensors) *n_tensors = (int64_t)f.tensors().size();
   return 0;
 }
@@ -621,8 +622,8 @@ int b200_gemm(int type, const void* w, int64_t rows, int64_t cols, const float* 
   int rc = have_device();
   if (rc) return rc;
   if (!w || !x || !y) { set_error("null argument"); return B200_EINVAL; }
-  if (type != T_BF16 && type != T_Q4_K && type != T_Q6_K) { set_error("b200_gemm: type must be BF16, Q4_K or Q6_K"); return B200_EINVAL; }
-  if (!gemm_shape_ok(rows, cols, n) || (type != T_BF16 && cols % QK_K)) {
+  if (type != T_BF16 && type != T_F16 && type != T_Q4_K && type != T_Q6_K) { set_error("b200_gemm: type must be BF16, F16, Q4_K or Q6_K"); return B200_EINVAL; }
+  if (!gemm_shape_ok(rows, cols, n) || (type != T_BF16 && type != T_F16 && cols % QK_K)) {
     set_error("gemm shape rows=%lld (need %%8) cols=%lld (need %%64; %%256 for k-quants) n=%lld unsupported", (long long)rows, (long long)cols, (long long)n);
     return B200_EINVAL;
   }
@@ -633,7 +634,8 @@ int b200_gemm(int type, const void* w, int64_t rows, int64_t cols, const float* 
   const uint16_t* w16 = dw.as<uint16_t>();
   if (type != T_BF16) {  // GEMM numerics: k-quant weights are dequantised and rounded to bf16
     if ((rc = dw16.alloc((size_t)rows * cols * 2))) return rc;
-    B200_CUDA(launch_dequant(type, dw.p, rows * cols / QK_K, nullptr, dw16.as<uint16_t>(), 0));
+    if (type == T_F16) B200_CUDA(launch_f16_to_bf16(dw.as<uint16_t>(), dw16.as<uint16_t>(), rows * cols, 0));
+    else B200_CUDA(launch_dequant(type, dw.p, rows * cols / QK_K, nullptr, dw16.as<uint16_t>(), 0));
     w16 = dw16.as<uint16_t>();
   }
   B200_CUDA(cudaMemcpy(dxf.p, x, (size_t)n * cols * 4, cudaMemcpyHostToDevice));

@@ -205,7 +205,7 @@ int Engine::init(const b200_config& c, const void* nccl_id) {
     int rc;
     embd_type = ty("token_embd.weight", tmat);
     const int tout = ty("output.weight", tbig);
-    if (embd_type != T_BF16 && d % QK_K) { set_error("d_model must be a multiple of 256 for k-quant embeddings"); return B200_EINVAL; }
+    if (embd_type != T_BF16 && embd_type != T_F16 && embd_type != T_F32 && d % QK_K) { set_error("d_model must be a multiple of 256 for k-quant embeddings"); return B200_EINVAL; }
     if ((rc = need(tout, voc, d, "output"))) return rc;
     if ((rc = alloc((void**)&token_embd, (size_t)c.vocab * tensor_row_bytes(embd_type, d)))) return rc;
     add_slot("token_embd.weight", embd_type, c.vocab, d, token_embd, 0, 1);
@@ -304,7 +304,7 @@ int Engine::place_tensor(const Slot& s, const uint8_t* src) {
   const size_t rb = tensor_row_bytes(s.type, s.cols), full_rb = tensor_row_bytes(s.type, s.full_cols);
   uint8_t* dst = s.base + (size_t)s.row0 * rb;
   const bool window = s.full_rows != s.rows || s.full_cols != s.cols;
-  if (window && s.type != T_BF16 && s.type != T_F32) { set_error("tensor-parallel windows need bf16 / f32 tensors"); return B200_EINVAL; }
+  if (window && s.type != T_BF16 && s.type != T_F16 && s.type != T_F32) { set_error("tensor-parallel windows need bf16 / f32 tensors"); return B200_EINVAL; }
   const uint8_t* from = src + (size_t)s.src_row0 * full_rb + tensor_row_bytes(s.type, s.src_col0);
   if (s.type == T_Q6_K && s.base != token_embd) {
     B200_CUDA(launch_q6k_repack(from, dst, s.rows, s.cols / QK_K, 1, stream));
@@ -717,7 +717,9 @@ int Engine::refresh_shadow(const std::string& name) {
     uint8_t* tmp = nullptr;
     B200_CUDA(cudaMalloc((void**)&tmp, bytes));
     rc = fetch_tensor(s, tmp);
-    cudaError_t e = rc ? cudaSuccess : launch_dequant(s.type, tmp, s.rows * s.cols / QK_K, nullptr, output16, stream);
+    cudaError_t e = rc ? cudaSuccess
+                       : (s.type == T_F16 ? launch_f16_to_bf16((const uint16_t*)tmp, output16, s.rows * s.cols, stream)
+                                          : launch_dequant(s.type, tmp, s.rows * s.cols / QK_K, nullptr, output16, stream));
     if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
     cudaFree(tmp);
     if (rc) return rc;
@@ -726,7 +728,10 @@ int Engine::refresh_shadow(const std::string& name) {
   if (!shadow_tmp) return 0;  // all-bf16 layers: the "shadows" are the GEMV buffers themselves
   if ((rc = fetch_tensor(s, shadow_tmp))) return rc;  // GGUF block order
   const uint16_t* src16 = (const uint16_t*)shadow_tmp;  // bf16 tensors are copied as they are
-  if (s.type != T_BF16) {
+  if (s.type == T_F16) {
+    B200_CUDA(launch_f16_to_bf16((const uint16_t*)shadow_tmp, shadow_tmp16, s.rows * s.cols, stream));
+    src16 = shadow_tmp16;
+  } else if (s.type != T_BF16) {
     B200_CUDA(launch_dequant(s.type, shadow_tmp, s.rows * s.cols / QK_K, nullptr, shadow_tmp16, stream));
     src16 = shadow_tmp16;
   }

@@ -289,6 +289,7 @@ cudaError_t launch_gemv_dual_qkv(int type_a, const GemvArgs& a, int type_b, cons
 size_t gemv_row_bytes(int wtype, int64_t K) {
   switch (wtype) {
     case T_BF16: return (size_t)K * 2;
+    case T_F16: return (size_t)K * 2;
     case T_Q4_K: return (size_t)(K / QK_K) * Q4K_BYTES;
     case T_Q6_K: return (size_t)(K / QK_K) * Q6K_BYTES;
   }
@@ -299,6 +300,7 @@ bool gemv_shape_ok(int wtype, int64_t N, int64_t K, int epi) {
   if (N <= 0 || K <= 0 || K > 32768) return false;
   switch (wtype) {
     case T_BF16: return K % 256 == 0 && N % 4 == 0;
+    case T_F16: return K % 256 == 0 && N % 4 == 0;
     case T_Q4_K: return K % (8 * QK_K) == 0 && N % 4 == 0;
     case T_Q6_K: return K % (8 * QK_K) == 0 && N % 2 == 0;
   }
@@ -322,6 +324,8 @@ cudaError_t launch_gemv(int wtype, int pro, int epi, const GemvArgs& a, cudaStre
     case T_BF16:
       if (a.K % 512 == 0) return launch_by_width<FmtBF16<512, 4, S0r4>, FmtBF16<512, 2, S0r2>>(wide, pro, epi, a, s, pdl, sm_count);
       return launch_by_width<FmtBF16<256, 4, S0r4>, FmtBF16<256, 2, S0r2>>(wide, pro, epi, a, s, pdl, sm_count);
+    case T_F16:  // F16 GGUF files: same data path, the widening is a convert instead of a shift
+      return launch_by_width<FmtBF16<256, 4, S0r4, true>, FmtBF16<256, 2, S0r2, true>>(wide, pro, epi, a, s, pdl, sm_count);
     case T_Q4_K: return launch_by_width<FmtQ4K<4, S0r4>, FmtQ4K<2, S0r2>>(wide, pro, epi, a, s, pdl, sm_count);
     case T_Q6_K: return launch_f<FmtQ6K<S0q6>>(pro, epi, a, s, pdl, sm_count);
   }

@@ -113,8 +113,11 @@ DEVINL void tp_prologue(float* xs, const GemvArgs& a, float* red, int warp, int 
   __syncthreads();
 }
 
-template <int KC, int R_, class C>  // KC in {256, 512}; R_ rows per work unit (4, or 2 for matrices with few rows)
+// 16-bit float weights: bf16 (widening is a shift) or, F16_ = true, IEEE half as stored by F16 GGUF files (a convert)
+template <int KC, int R_, class C, bool F16_ = false>  // KC in {256, 512}; R_ rows per work unit (4, or 2 for matrices with few rows)
 struct FmtBF16 {
+  static DEVINL float lo(uint32_t v) { return F16_ ? __half2float(__ushort_as_half((unsigned short)(v & 0xffffu))) : bf16lo(v); }
+  static DEVINL float hi(uint32_t v) { return F16_ ? __half2float(__ushort_as_half((unsigned short)(v >> 16))) : bf16hi(v); }
   static constexpr int R = R_, CHUNK = KC, STAGES = C::ST, NW = C::NW, OCC = C::OCC;
   static constexpr int ROW_STAGE_BYTES = KC * 2;
   static constexpr int STAGE_BYTES = R * ROW_STAGE_BYTES;
@@ -205,14 +208,14 @@ struct FmtBF16 {
       for (int r = 0; r < R; ++r) {
         const uint4 w = *reinterpret_cast<const uint4*>(st + r * ROW_STAGE_BYTES + h * 512 + lane * 16);
         float s = acc[r];
-        s = fmaf(bf16lo(w.x), xa.x, s);
-        s = fmaf(bf16hi(w.x), xa.y, s);
-        s = fmaf(bf16lo(w.y), xa.z, s);
-        s = fmaf(bf16hi(w.y), xa.w, s);
-        s = fmaf(bf16lo(w.z), xb.x, s);
-        s = fmaf(bf16hi(w.z), xb.y, s);
-        s = fmaf(bf16lo(w.w), xb.z, s);
-        s = fmaf(bf16hi(w.w), xb.w, s);
+        s = fmaf(lo(w.x), xa.x, s);
+        s = fmaf(hi(w.x), xa.y, s);
+        s = fmaf(lo(w.y), xa.z, s);
+        s = fmaf(hi(w.y), xa.w, s);
+        s = fmaf(lo(w.z), xb.x, s);
+        s = fmaf(hi(w.z), xb.y, s);
+        s = fmaf(lo(w.w), xb.z, s);
+        s = fmaf(hi(w.w), xb.w, s);
         acc[r] = s;
       }
     }

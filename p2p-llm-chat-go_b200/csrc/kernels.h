@@ -16,7 +16,7 @@ constexpr int kPageTokens = 16;  // KV page = 16 tokens of one kv head = 4 KB (b
 constexpr int QK_K = 256, Q4K_BYTES = 144, Q6K_BYTES = 210;  // GGUF k-quant super-block
 
 // ggml type ids (== B200_TYPE_*)
-enum { T_F32 = 0, T_Q4_K = 12, T_Q6_K = 14, T_BF16 = 30 };
+enum { T_F32 = 0, T_F16 = 1, T_Q4_K = 12, T_Q6_K = 14, T_BF16 = 30 };
 
 enum { PRO_COPY = 0, PRO_RMSNORM = 1, PRO_TP_RMSNORM = 2 };
 enum { EPI_STORE = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_QKV = 3, EPI_LOGITS = 4, EPI_TP_PUSH = 5 };
@@ -195,6 +195,7 @@ cudaError_t launch_q6k_repack(const uint8_t* src, uint8_t* dst, int64_t rows, in
 cudaError_t launch_synth(int type, void* dst, int64_t rows, int64_t cols, uint64_t seed, uint32_t tensor_id,
                          float sigma, cudaStream_t s);
 cudaError_t launch_f32_to_bf16(const float* x, uint16_t* y, int64_t n, cudaStream_t s);
+cudaError_t launch_f16_to_bf16(const uint16_t* x, uint16_t* y, int64_t n, cudaStream_t s);  // fp16 bits -> bf16 bits (RNE): GEMM operand of F16 tensors
 cudaError_t launch_l2_flush(void* buf, size_t bytes, cudaStream_t s);
 cudaError_t launch_add_inplace(float* x, const float* y, int n, cudaStream_t s);
 

@@ -155,6 +155,11 @@ __global__ void f32_to_bf16_kernel(const float* x, uint16_t* y, int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) y[i] = f32_to_bf16_bits(x[i]);
 }
 
+__global__ void f16_to_bf16_kernel(const uint16_t* x, uint16_t* y, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    y[i] = f32_to_bf16_bits(__half2float(__ushort_as_half(x[i])));
+}
+
 __global__ void add_inplace_kernel(float* x, const float* y, int n) {
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) x[i] += y[i];
 }
@@ -169,6 +174,7 @@ DEVINL void embed_row(const uint8_t* embd, int type, int d_model, int token, flo
   for (int i = threadIdx.x; i < d_model; i += blockDim.x) {
     float v;
     if (type == T_BF16) v = __uint_as_float((uint32_t)reinterpret_cast<const uint16_t*>(embd)[(size_t)token * d_model + i] << 16);
+    else if (type == T_F16) v = __half2float(__ushort_as_half(reinterpret_cast<const unsigned short*>(embd)[(size_t)token * d_model + i]));
     else if (type == T_F32) v = reinterpret_cast<const float*>(embd)[(size_t)token * d_model + i];
     else if (type == T_Q4_K) v = dequant_q4k_elem(embd + ((size_t)token * (d_model / QK_K) + i / QK_K) * Q4K_BYTES, i % QK_K);
     else v = dequant_q6k_elem(embd + ((size_t)token * (d_model / QK_K) + i / QK_K) * Q6K_BYTES, i % QK_K);
@@ -255,6 +261,12 @@ cudaError_t launch_synth(int type, void* dst, int64_t rows, int64_t cols, uint64
 cudaError_t launch_f32_to_bf16(const float* x, uint16_t* y, int64_t n, cudaStream_t s) {
   if (n == 0) return cudaSuccess;
   count_launch(); f32_to_bf16_kernel<<<592, 256, 0, s>>>(x, y, n);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_f16_to_bf16(const uint16_t* x, uint16_t* y, int64_t n, cudaStream_t s) {
+  if (n == 0) return cudaSuccess;
+  count_launch(); f16_to_bf16_kernel<<<592, 256, 0, s>>>(x, y, n);
   return cudaGetLastError();
 }
 

@@ -68,7 +68,7 @@ def write_model(path, fmt, seed=5):
     w.add_bos_token_id(V - 2 if False else toks.index("<|begin_of_text|>")); w.add_eos_token_id(toks.index("<|eot_id|>"))
     rng = np.random.default_rng(seed)
     Q = gguf.GGMLQuantizationType
-    tmat = orc.BF16 if fmt == 0 else orc.Q4_K
+    tmat = {0: orc.BF16, 1: orc.Q4_K, 2: orc.F16}[fmt]      # fmt 2: an F16 file (every matrix IEEE half)
     tensors = {}
 
     def add(name, t, rows, cols):
@@ -78,14 +78,16 @@ def write_model(path, fmt, seed=5):
             w.add_tensor(name, arr.reshape(cols))
         elif t == orc.BF16:
             w.add_tensor(name, arr.view(np.uint8).reshape(rows, cols * 2), raw_dtype=Q.BF16)
+        elif t == orc.F16:
+            w.add_tensor(name, arr.view(np.float16).reshape(rows, cols))
         else:
             w.add_tensor(name, arr.reshape(rows, -1), raw_dtype=Q.Q4_K if t == orc.Q4_K else Q.Q6_K)
     add("token_embd.weight", tmat, V, d)
     add("output_norm.weight", orc.F32, 1, d)
-    add("output.weight", orc.BF16 if fmt == 0 else orc.Q6_K, V, d)
+    add("output.weight", {0: orc.BF16, 1: orc.Q6_K, 2: orc.F16}[fmt], V, d)
     w.add_tensor("rope_freqs.weight", np.ones(64, np.float32))
     for l in range(L):
-        tv = tmat if fmt == 0 else (orc.Q6_K if l == 1 else orc.Q4_K)   # a per-tensor mix, dictated by the file
+        tv = tmat if fmt != 1 else (orc.Q6_K if l == 1 else orc.Q4_K)   # a per-tensor mix, dictated by the file
         for n, t, r, c in (("attn_q", tmat, nh * 128, d), ("attn_k", tmat, nkv * 128, d), ("attn_v", tv, nkv * 128, d),
                            ("attn_output", tmat, d, nh * 128), ("ffn_gate", tmat, ff, d), ("ffn_up", tmat, ff, d), ("ffn_down", tv, d, ff)):
             add(f"blk.{l}.{n}.weight", t, r, c)
@@ -226,7 +228,7 @@ def test_corrupt_files_are_rejected_not_crashed(pkg, model_file, tmp_path):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("fmt", [0, 1])
+@pytest.mark.parametrize("fmt", [0, 1, 2])
 def test_load_gguf_and_match_oracle(pkg, tmp_path, fmt):
     assert pkg.device_count() >= 1
     path = str(tmp_path / f"tiny-{fmt}.gguf")
@@ -247,3 +249,9 @@ def test_load_gguf_and_match_oracle(pkg, tmp_path, fmt):
         out, _, _ = eng.generate_greedy(ids, 8, pkg.MODE_GEMV)
         want_ids, _ = ora.generate_greedy(ids, 8, prefill_mode=0)
         assert out.tolist() == want_ids.tolist()
+        # the tensor-core path on the same file (k-quant and F16 tensors enter it rounded to bf16)
+        long = np.array(eng.tokenize("hello world 123 the the hello " * 4, add_bos=False), np.int32)
+        got1 = eng.forward_logits(long, pkg.MODE_GEMM)
+        ora.reset()
+        want1 = ora.forward(long, mode=1)
+        assert np.abs(got1 - want1).max() <= 3e-3 * max(1.0, np.abs(want1).max())

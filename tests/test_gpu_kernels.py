@@ -69,8 +69,12 @@ def _gemv_case(pkg, wtype, rows, cols, seed, norm=False):
         xin = x
     want = orc.matmul(wtype, W, rows, cols, xin, mode=0)[0]
     # error budget from the magnitude of the terms, not of the (cancelling) result
-    wabs = np.abs(orc.dequant(W, wtype).reshape(rows, cols)) if wtype in (orc.Q4_K, orc.Q6_K) else np.abs(
-        orc.bf16_to_f32(W).reshape(rows, cols))
+    if wtype in (orc.Q4_K, orc.Q6_K):
+        wabs = np.abs(orc.dequant(W, wtype).reshape(rows, cols))
+    elif wtype == orc.F16:
+        wabs = np.abs(W.view(np.float16).astype(np.float32).reshape(rows, cols))
+    else:
+        wabs = np.abs(orc.bf16_to_f32(W).reshape(rows, cols))
     budget = wabs @ np.abs(xin).astype(np.float64)
     err = np.abs(got.astype(np.float64) - want)
     tol = (2 if norm else 1) * GEMV_RTOL * budget  # norm: the fp32 inverse rms differs in the last ulp
@@ -81,6 +85,12 @@ def _gemv_case(pkg, wtype, rows, cols, seed, norm=False):
 @pytest.mark.parametrize("rows,cols", [(4, 256), (64, 512), (1028, 4096), (4096, 14336), (6144, 4096)])
 def test_gemv_bf16(pkg, rows, cols):
     _gemv_case(pkg, orc.BF16, rows, cols, seed=rows + cols)
+
+
+@pytest.mark.parametrize("rows,cols", [(4, 256), (1028, 4096), (4096, 14336)])
+def test_gemv_f16(pkg, rows, cols):
+    """F16 tensors (the matrices of an F16 GGUF file): same kernel, the widening is a convert; used exactly in mode 0."""
+    _gemv_case(pkg, orc.F16, rows, cols, seed=rows + cols + 1)
 
 
 @pytest.mark.parametrize("rows,cols", [(4, 2048), (520, 4096), (4096, 14336)])
@@ -136,7 +146,7 @@ def test_attn_decode(pkg, n_ctx, n_heads, n_kv):
 @pytest.mark.parametrize("wtype,rows,cols,n", [
     (orc.BF16, 128, 64, 1), (orc.BF16, 256, 512, 7), (orc.BF16, 1024, 4096, 128), (orc.BF16, 512, 2048, 129),
     (orc.BF16, 6144, 4096, 512), (orc.BF16, 4096, 14336, 300), (orc.Q4_K, 256, 2048, 33), (orc.Q6_K, 256, 2048, 64),
-    (orc.BF16, 200, 256, 40), (orc.BF16, 1032, 512, 300), (orc.BF16, 6144, 4096, 24)])  # ragged last row tile (vocab-parallel lm_head shards: 16032 rows)
+    (orc.BF16, 200, 256, 40), (orc.BF16, 1032, 512, 300), (orc.BF16, 6144, 4096, 24), (orc.F16, 512, 2048, 129)])  # ragged last row tile (vocab-parallel lm_head shards: 16032 rows)
 def test_gemm_tcgen05(pkg, wtype, rows, cols, n):
     rng = np.random.default_rng(rows + cols + n)
     W = random_tensor(rng, wtype, rows, cols)

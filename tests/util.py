@@ -65,6 +65,8 @@ def random_tensor(rng, wtype, rows, cols, sigma=None):
         return (1.0 + 0.1 * rng.standard_normal(rows * cols)).astype(np.float32)
     if wtype == orc.BF16:
         return orc.f32_to_bf16((rng.standard_normal((rows, cols)) * sigma).astype(np.float32))
+    if wtype == orc.F16:   # IEEE half bits, as F16 GGUF files store them
+        return (rng.standard_normal((rows, cols)) * sigma).astype(np.float16).view(np.uint16)
     nb = rows * cols // 256
     if wtype == orc.Q4_K:
         blk = rng.integers(0, 256, (nb, 144), dtype=np.uint8)
