@@ -153,7 +153,12 @@ def test_gemm_tcgen05(pkg, wtype, rows, cols, n):
     X = rng.standard_normal((n, cols)).astype(np.float32)
     got = pkg.gemm(wtype, W, rows, cols, X)
     want = orc.matmul(wtype, W, rows, cols, X, mode=1)
-    Wf = orc.dequant(W, wtype).reshape(rows, cols) if wtype in (orc.Q4_K, orc.Q6_K) else orc.bf16_to_f32(W).reshape(rows, cols)
+    if wtype in (orc.Q4_K, orc.Q6_K):
+        Wf = orc.dequant(W, wtype).reshape(rows, cols)
+    elif wtype == orc.F16:
+        Wf = W.view(np.float16).astype(np.float32).reshape(rows, cols)
+    else:
+        Wf = orc.bf16_to_f32(W).reshape(rows, cols)
     budget = np.abs(X).astype(np.float64) @ np.abs(Wf).astype(np.float64).T
     err = np.abs(got.astype(np.float64) - want)
     assert (err <= 1e-5 * budget + 1e-30).all(), float((err / (budget + 1e-30)).max())
