@@ -297,3 +297,27 @@ def test_full_size_8b_512_prompt_128_tokens(pkg, fmt, record_property):
         print("\nPARITY8B " + msg)
         record_property("parity8b", msg)
         assert n_dec >= n_new // 4, msg
+
+
+@pytest.mark.parametrize("n_heads,n_kv", [(16, 16), (16, 8), (16, 2)])   # GQA groups 1, 2 and 8 (Llama-3.1-70B has 8); 4 is everywhere else
+def test_gqa_group_sizes_decode_and_prefill(pkg, n_heads, n_kv):
+    """Every attention kernel is instantiated per GQA group size: the batch-1 decode step (16-CTA cluster kernel), the
+    tensor-core prefill and the batched decode attention, each against the oracle, at contexts that span one tile,
+    both prefetched tiles and a ragged tail."""
+    eng, ora, cfg = engine_and_oracle(pkg, 0, n_layers=2, seed=91, source="synth", max_ctx=1200, n_heads=n_heads, n_kv_heads=n_kv)
+    with eng:
+        toks = _prompt(cfg, 1100, 13)
+        for n in (5, 33, 600):
+            got = eng.forward_logits(toks[:n], pkg.MODE_GEMV)          # token by token through the decode step
+            ora.reset()
+            for t in toks[:n]:
+                want = ora.forward([t], mode=0)
+            assert np.abs(got - want).max() <= LOGIT_TOL * max(1.0, np.abs(want).max()), (n_heads, n_kv, n)
+        got = eng.forward_logits(toks, pkg.MODE_GEMM)                   # 1100 tokens: prefill attention, then > 1024-token decode context
+        ora.reset()
+        want = ora.forward(toks, mode=1)
+        assert np.abs(got - want).max() <= PREFILL_LOGIT_TOL * max(1.0, np.abs(want).max()), (n_heads, n_kv)
+        ids, _, _ = eng.generate_greedy(toks, 6, pkg.MODE_GEMM)        # decode steps at ctx 1101.. (third tile fetched in place)
+        want_ids, margins = ora.generate_greedy(toks, 6, prefill_mode=1)
+        if margins.min() > 4 * PREFILL_LOGIT_TOL:
+            assert ids.tolist() == want_ids.tolist()
