@@ -258,72 +258,6 @@ DEVINL int dp2a_hi_ss(uint32_t x2, uint32_t q4, int c) {
 // small non-negative integer (< 2^23) -> float without the conversion pipe
 DEVINL float small_u2f(uint32_t v) { return __uint_as_float(0x4B000000u | v) - 8388608.0f; }
 
-// One float4 of (normalised) activations -> four int16 and this 32-block's scale: 8 lanes hold a block.
-template <class F>
-DEVINL void quant_store(float4 val, int gi, int n4, int lane, int16_t* xq, float* dx, float* dxs) {
-  float m = fmaxf(fmaxf(fabsf(val.x), fabsf(val.y)), fmaxf(fabsf(val.z), fabsf(val.w)));
-  m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
-  m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
-  m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
-  const float d = __fmul_rn(m, 1.0f / 32767.0f);
-  const float id = d > 0.f ? __frcp_rn(d) : 0.f;
-  const int X0 = (int)fminf(32767.f, fmaxf(-32767.f, rintf(__fmul_rn(val.x, id))));
-  const int X1 = (int)fminf(32767.f, fmaxf(-32767.f, rintf(__fmul_rn(val.y, id))));
-  const int X2 = (int)fminf(32767.f, fmaxf(-32767.f, rintf(__fmul_rn(val.z, id))));
-  const int X3 = (int)fminf(32767.f, fmaxf(-32767.f, rintf(__fmul_rn(val.w, id))));
-  int xsum = (X0 + X1) + (X2 + X3);
-  xsum += __shfl_xor_sync(0xffffffffu, xsum, 1);
-  xsum += __shfl_xor_sync(0xffffffffu, xsum, 2);
-  xsum += __shfl_xor_sync(0xffffffffu, xsum, 4);
-  if (gi < n4) {
-    const int k = 4 * gi;
-    uint2 pk;
-    pk.x = (uint32_t)(X0 & 0xffff) | ((uint32_t)X1 << 16);
-    pk.y = (uint32_t)(X2 & 0xffff) | ((uint32_t)X3 << 16);
-    *reinterpret_cast<uint2*>(xq + (k & ~2047) + F::xpos(k & 2047)) = pk;
-    if ((lane & 7) == 0) {
-      dx[k >> 5] = d;
-      dxs[k >> 5] = __fmul_rn(d, (float)xsum);
-    }
-  }
-}
-
-// Vectors beyond the register budget of q16_prologue's one-round path (e.g. ffn_down of the 70B model, K = 28672):
-// several rounds of loads.
-template <class F, int PRO>
-DEVINL void q16_prologue_rounds(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane) {
-  int16_t* xq = reinterpret_cast<int16_t*>(xs);
-  float* dx = reinterpret_cast<float*>(xs + 2 * (size_t)a.K);
-  float* dxs = dx + a.K / 32;
-  constexpr int NW = F::NW;
-  constexpr int U = ProU<NW>::value;
-  const int n4 = a.K / 4;
-  const float inv = rms_inv<PRO, NW>(a, red, warp, lane);
-  for (int g0 = warp * 32; g0 < n4; g0 += NW * 32 * U) {
-    float4 v[U], g[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int gi = g0 + u * NW * 32 + lane;
-      v[u] = gi < n4 ? __ldcg(reinterpret_cast<const float4*>(a.x + 4 * gi)) : make_float4(0.f, 0.f, 0.f, 0.f);
-      g[u] = (PRO == PRO_RMSNORM && gi < n4) ? *reinterpret_cast<const float4*>(a.norm_w + 4 * gi) : make_float4(1.f, 1.f, 1.f, 1.f);
-    }
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int gi = g0 + u * NW * 32 + lane;
-      if (g0 + u * NW * 32 >= n4) break;  // warp-uniform
-      float4 val = v[u];
-      if (PRO == PRO_RMSNORM) {
-        val.x = __fmul_rn(__fmul_rn(val.x, inv), g[u].x);
-        val.y = __fmul_rn(__fmul_rn(val.y, inv), g[u].y);
-        val.z = __fmul_rn(__fmul_rn(val.z, inv), g[u].z);
-        val.w = __fmul_rn(__fmul_rn(val.w, inv), g[u].w);
-      }
-      quant_store<F>(val, gi, n4, lane, xq, dx, dxs);
-    }
-  }
-  __syncthreads();
-}
-
 template <class F, int PRO, class AfterIssue>
 DEVINL void q16_prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, int lane, const float4* nw, AfterIssue&& after_issue) {
   int16_t* xq = reinterpret_cast<int16_t*>(xs);
@@ -339,50 +273,80 @@ DEVINL void q16_prologue(uint8_t* xs, const GemvArgs& a, float* red, int warp, i
   const int n4 = a.K / 4;
   // K <= 8192 with an RMS norm: x and the norm weights are fetched once, before the block-wide sum of
   // squares, and reused from registers below (thread -> element mapping and summation order as in rms_inv)
-  // The usual case — the whole vector fits one round of register-resident loads (K <= 8192 with a norm, <= 16384
-  // without: every matrix of the 8B model).  Kept SHORT on purpose: this code runs right after the dependency wait with
-  // a cold instruction cache (the kernels are 25-37 KB, the SM's L1.5 instruction cache 32 KB, so every launch starts
-  // cold), and measured with B200_TRACE ~2 us of a 3.8 us prologue was instruction fetch.  One copy of the quantise
-  // body (a rolled loop that shifts the register file down by one float4 per round) instead of U unrolled copies.
-  const int rounds = (n4 + NW * 32 - 1) / (NW * 32);
-  if (rounds <= U) {
-    float4 v[U], g[U];
+  const bool single = (PRO == PRO_RMSNORM) && n4 <= NW * 32 * U;
+  float4 v[U], g[U];
+  float inv = 1.f;
+  if (single) {
+    float ss = 0.f;
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int gi = u * NW * 32 + (int)threadIdx.x;
       v[u] = gi < n4 ? __ldcg(reinterpret_cast<const float4*>(a.x + 4 * gi)) : make_float4(0.f, 0.f, 0.f, 0.f);
-      g[u] = (PRO == PRO_RMSNORM && u < ProU<NW>::value) ? nw[u < ProU<NW>::value ? u : 0] : make_float4(1.f, 1.f, 1.f, 1.f);
+      g[u] = nw[u];  // norm weights: fetched before the dependency wait (gemv_body)
     }
-    after_issue();
-    float inv = 1.f;
-    if (PRO == PRO_RMSNORM) {
-      float ss = 0.f;
+    after_issue();  // activation loads issued: the rest of the weight ring may now queue up behind them
 #pragma unroll
-      for (int u = 0; u < U; ++u) ss += v[u].x * v[u].x + v[u].y * v[u].y + v[u].z * v[u].z + v[u].w * v[u].w;  // absent rounds hold zeros
-      ss = block_sum<NW>(ss, red, warp, lane);
-      inv = 1.0f / sqrtf(ss / (float)a.K + a.eps);
-    }
-#pragma unroll 1
-    for (int u = 0; u < rounds; ++u) {
-      float4 val = v[0];
-      if (PRO == PRO_RMSNORM) {
-        val.x = __fmul_rn(__fmul_rn(val.x, inv), g[0].x);
-        val.y = __fmul_rn(__fmul_rn(val.y, inv), g[0].y);
-        val.z = __fmul_rn(__fmul_rn(val.z, inv), g[0].z);
-        val.w = __fmul_rn(__fmul_rn(val.w, inv), g[0].w);
-      }
-#pragma unroll
-      for (int j = 0; j + 1 < U; ++j) {
-        v[j] = v[j + 1];
-        if (PRO == PRO_RMSNORM) g[j] = g[j + 1];
-      }
-      quant_store<F>(val, u * NW * 32 + (int)threadIdx.x, n4, lane, xq, dx, dxs);
-    }
-    __syncthreads();
-    return;
+    for (int u = 0; u < U; ++u)
+      if (u * NW * 32 + (int)threadIdx.x < n4) ss += v[u].x * v[u].x + v[u].y * v[u].y + v[u].z * v[u].z + v[u].w * v[u].w;
+    ss = block_sum<NW>(ss, red, warp, lane);
+    inv = 1.0f / sqrtf(ss / (float)a.K + a.eps);
+  } else {
+    if (PRO == PRO_RMSNORM) after_issue();
+    inv = rms_inv<PRO, NW>(a, red, warp, lane);
   }
-  after_issue();
-  q16_prologue_rounds<F, PRO>(xs, a, red, warp, lane);
+  bool issued = single || PRO == PRO_RMSNORM;
+  for (int g0 = warp * 32; g0 < n4; g0 += NW * 32 * U) {
+    if (!single) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int gi = g0 + u * NW * 32 + lane;
+        v[u] = gi < n4 ? __ldcg(reinterpret_cast<const float4*>(a.x + 4 * gi)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        g[u] = (PRO == PRO_RMSNORM && gi < n4) ? *reinterpret_cast<const float4*>(a.norm_w + 4 * gi) : make_float4(1.f, 1.f, 1.f, 1.f);
+      }
+      if (!issued) {
+        after_issue();
+        issued = true;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int gi = g0 + u * NW * 32 + lane;
+      if (g0 + u * NW * 32 >= n4) break;  // warp-uniform
+      float4 val = v[u];
+      if (PRO == PRO_RMSNORM) {
+        val.x = __fmul_rn(__fmul_rn(val.x, inv), g[u].x);
+        val.y = __fmul_rn(__fmul_rn(val.y, inv), g[u].y);
+        val.z = __fmul_rn(__fmul_rn(val.z, inv), g[u].z);
+        val.w = __fmul_rn(__fmul_rn(val.w, inv), g[u].w);
+      }
+      float m = fmaxf(fmaxf(fabsf(val.x), fabsf(val.y)), fmaxf(fabsf(val.z), fabsf(val.w)));
+      m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+      m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+      m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, 4));
+      const float d = __fmul_rn(m, 1.0f / 32767.0f);
+      const float id = d > 0.f ? __frcp_rn(d) : 0.f;
+      const int X0 = (int)fminf(32767.f, fmaxf(-32767.f, rintf(__fmul_rn(val.x, id))));
+      const int X1 = (int)fminf(32767.f, fmaxf(-32767.f, rintf(__fmul_rn(val.y, id))));
+      const int X2 = (int)fminf(32767.f, fmaxf(-32767.f, rintf(__fmul_rn(val.z, id))));
+      const int X3 = (int)fminf(32767.f, fmaxf(-32767.f, rintf(__fmul_rn(val.w, id))));
+      int xsum = (X0 + X1) + (X2 + X3);
+      xsum += __shfl_xor_sync(0xffffffffu, xsum, 1);
+      xsum += __shfl_xor_sync(0xffffffffu, xsum, 2);
+      xsum += __shfl_xor_sync(0xffffffffu, xsum, 4);
+      if (gi < n4) {
+        const int k = 4 * gi;
+        uint2 pk;
+        pk.x = (uint32_t)(X0 & 0xffff) | ((uint32_t)X1 << 16);
+        pk.y = (uint32_t)(X2 & 0xffff) | ((uint32_t)X3 << 16);
+        *reinterpret_cast<uint2*>(xq + (k & ~2047) + F::xpos(k & 2047)) = pk;
+        if ((lane & 7) == 0) {
+          dx[k >> 5] = d;
+          dxs[k >> 5] = __fmul_rn(d, (float)xsum);
+        }
+      }
+    }
+  }
+  __syncthreads();
 }
 
 // Q4_K: a stage is R rows x 8 super-blocks (GGUF byte order, 144 B each).  lane = (block, j): the 32 qs bytes
