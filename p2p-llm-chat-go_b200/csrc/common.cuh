@@ -61,6 +61,15 @@ DEVINL void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar
 DEVINL void l2_prefetch(const void* p, uint32_t bytes) {
   asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
 }
+// 16-byte read-only load that asks L2 to keep the line (evict_last): small tensors read by every CTA of every step
+// (norm weights) must survive the gigabytes of evict_first weight traffic streaming past them
+DEVINL float4 ldg_keep(const float4* p, uint64_t policy) {
+  float4 v;
+  asm volatile("ld.global.nc.L2::cache_hint.v4.f32 {%0, %1, %2, %3}, [%4], %5;"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p), "l"(policy));
+  return v;
+}
 DEVINL void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // Programmatic dependent launch: everything before pdl_wait() overlaps the previous kernel's tail.

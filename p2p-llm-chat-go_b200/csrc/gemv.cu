@@ -90,10 +90,11 @@ DEVINL void gemv_body(const GemvArgs& a, int cta, int n_ctas) {
   // the single-fetch prologues, K <= 8192) goes to registers now, so the prologue waits for the activations only
   constexpr int kPU = ProU<F::NW>::value;
   float4 nw[kPU];
+  const uint64_t keep = l2_policy_evict_last();
 #pragma unroll
   for (int u = 0; u < kPU; ++u) {
     const int k = 4 * ((int)threadIdx.x + u * F::NW * 32);
-    nw[u] = (PRO == PRO_RMSNORM && k < a.K && a.K <= F::NW * 32 * 4 * kPU) ? __ldg(reinterpret_cast<const float4*>(a.norm_w + k))
+    nw[u] = (PRO == PRO_RMSNORM && k < a.K && a.K <= F::NW * 32 * 4 * kPU) ? ldg_keep(reinterpret_cast<const float4*>(a.norm_w + k), keep)
                                                                           : make_float4(1.f, 1.f, 1.f, 1.f);
   }
   if (EPI != EPI_LOGITS) {
