@@ -23,6 +23,8 @@
 #include <cuda.h>
 
 #include <cstdlib>
+#include <mutex>
+#include <unordered_map>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -389,16 +391,69 @@ EncodeTiledFn encode_fn() {
   return fn;
 }
 
-// bf16 [rows][K] row-major -> 2-D tensor map with a {64 (K), box_rows} box, 128-byte swizzle
+// bf16 [rows][K] row-major -> 2-D tensor map with a {64 (K), box_rows} box, 128-byte swizzle.
+// Encoded once per (buffer, shape, box) and kept: the same few hundred operands (weight matrices, the engine's
+// activation buffers) come back on every prefill and every batched step.
+struct MapKey {
+  const void* base;
+  uint64_t rows, K;
+  uint32_t box_rows;
+  bool operator==(const MapKey& o) const { return base == o.base && rows == o.rows && K == o.K && box_rows == o.box_rows; }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    uint64_t h = (uint64_t)(uintptr_t)k.base * 0x9E3779B97F4A7C15ull;
+    h ^= (k.rows + 0x9E3779B97F4A7C15ull + (h << 6) + (h >> 2));
+    h ^= (k.K * 0xC2B2AE3D27D4EB4Full + (h << 6) + (h >> 2));
+    return (size_t)(h ^ k.box_rows);
+  }
+};
 bool make_map(CUtensorMap* m, const void* base, uint64_t rows, uint64_t K, uint32_t box_rows) {
+  static std::mutex mu;
+  static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+  const MapKey key{base, rows, K, box_rows};
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) { *m = it->second; return true; }
+  }
   EncodeTiledFn fn = encode_fn();
   if (!fn) return false;
   const cuuint64_t dims[2] = {K, rows};
   const cuuint64_t strides[1] = {K * 2};
   const cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
   const cuuint32_t estr[2] = {1, 1};
-  return fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+  if (fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+    return false;
+  std::lock_guard<std::mutex> lk(mu);
+  if (cache.size() > 8192) cache.clear();  // hooks that upload a fresh matrix per call: bounded
+  cache.emplace(key, *m);
+  return true;
+}
+
+// multiprocessors of the current device (asked once per device): the split heuristics deal CTAs out over them
+int sm_count_now() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 148;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n < 1) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+// Environment switches of the schedule heuristics.  They exist for experiments and for the tests, which flip them
+// between calls inside one process, so they are looked up per launch (a handful of getenv calls, ~0.1 us each, on the
+// host thread that is enqueueing ahead of the GPU anyway).
+bool env_set(const char* name) { return getenv(name) != nullptr; }
+#define kNoStreamK env_set("B200_NO_STREAMK")
+#define kNoBn32 env_set("B200_NO_GEMM_BN32")
+int env_int(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return e ? atoi(e) : dflt;
 }
 
 template <int BN, int MT>
@@ -445,11 +500,10 @@ cudaError_t launch_streamk(const uint16_t* W, int64_t rows, int64_t K, const uin
 // can: 148 persistent CTAs, each an equal run of (256-row tile, K block) items, partial tiles (tokens x 256
 // floats, tiny here) reduced by the tile's owner in CTA order.
 bool streamk_small_n(int64_t rows, int64_t K, int64_t n_tokens, const GemmWorkspace* wk) {
-  if (!wk || !wk->ws || !wk->flags || wk->sm_count <= 0 || getenv("B200_NO_STREAMK")) return false;
+  if (!wk || !wk->ws || !wk->flags || wk->sm_count <= 0 || kNoStreamK) return false;
   if (n_tokens > 128 || rows % (2 * BM) || (size_t)wk->sm_count * kWsSlot * 4 > wk->ws_bytes) return false;
   const int64_t total = (rows / (2 * BM)) * (K / BK);
-  const char* force = getenv("B200_GEMM_STREAMK");  // tests: =1 takes the schedule for every shape it can express
-  if (force && atoi(force) == 1) return true;
+  if (env_int("B200_GEMM_STREAMK", 0) == 1) return true;  // tests: takes the schedule for every shape it can express
   // Measured (8B, 8 tokens): gate/up 37 us vs 75 us in whole tiles, lm_head 171 vs 232; but matrices with few row
   // tiles (o, down, qkv: 16-24) are cut into ~10 CTAs per tile and the owner's serial fix-up outweighs the balance
   // (down 49 vs 23 us), and from 64 tokens up the partial traffic does.  So: at most 32 tokens, and at least half a
@@ -458,10 +512,7 @@ bool streamk_small_n(int64_t rows, int64_t K, int64_t n_tokens, const GemmWorksp
 }
 
 // B200_GEMM_M256 = 0 never / 1 whenever the shape allows / unset: the heuristic below (experiments only)
-int m256_override() {
-  const char* e = getenv("B200_GEMM_M256");
-  return e ? atoi(e) : -1;
-}
+int m256_override() { return env_int("B200_GEMM_M256", -1); }
 
 }  // namespace
 
@@ -475,7 +526,7 @@ cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const u
                              int64_t ldy, cudaStream_t s, const GemmWorkspace* wk) {
   // stream-K schedule (experiment, see below)
   if (wk && wk->ws && wk->flags && wk->sm_count > 0 && gemm_shape_ok(rows, K, n_tokens) && rows % (2 * BM) == 0 && n_tokens > 128 &&
-      m256_override() != 0 && getenv("B200_NO_STREAMK") == nullptr) {
+      m256_override() != 0 && !kNoStreamK) {
     const int64_t tiles = (rows / (2 * BM)) * ((n_tokens + 255) / 256), P = wk->sm_count;
     const int64_t waves = (tiles + P - 1) / P;
     const int64_t total = tiles * (K / BK), units = (total + P - 1) / P;
@@ -485,8 +536,7 @@ cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const u
     // every CTA pays up to three serialised epilogues.  So the schedule is opt-in: B200_GEMM_STREAMK=1 takes it
     // for any shape it can express (tests), otherwise it is never chosen.
     (void)waves;
-    const char* force = getenv("B200_GEMM_STREAMK");
-    const bool want = force && atoi(force) == 1 && units >= 1;
+    const bool want = env_int("B200_GEMM_STREAMK", 0) == 1 && units >= 1;
     if (want && (size_t)P * 256 * 256 * 4 <= wk->ws_bytes)
       return launch_streamk<256>(W, rows, K, X, n_tokens, Y, ldy, *wk, s);
   }
@@ -506,16 +556,16 @@ cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, 
     return launch_streamk<128>(W, rows, K, X, n_tokens, Y, ldy, *wk, s);
   }
   const int max_splits = *splits < 1 ? 1 : (*splits > 16 ? 16 : *splits);
-  const int64_t kb = K / BK;
+  const int64_t kb = K / BK, n_sm = wk && wk->sm_count > 0 ? wk->sm_count : sm_count_now();
   const int ov = m256_override();
   // 256 x 256 tiles, one CTA per SM: the fewest operand bytes per MAC.  Taken when, with K split up to
-  // max_splits ways (each split keeps >= 24 K blocks: shorter loops do not amortise the CTA set-up), the grid comes to 96..148 CTAs, or has several waves.
+  // max_splits ways (each split keeps >= 24 K blocks: shorter loops do not amortise the CTA set-up), the grid comes to between two thirds of the SMs and all of them, or has several waves.
   if (rows % (2 * BM) == 0 && n_tokens > 128 && ov != 0) {
     const int64_t tiles = (rows / (2 * BM)) * ((n_tokens + 255) / 256);
     int use = 1;
     for (int sp = 2; sp <= max_splits; sp *= 2)
-      if (kb % sp == 0 && kb / sp >= 24 && tiles * sp <= 148) use = sp;
-    if (tiles * use >= 96 || ov == 1) {
+      if (kb % sp == 0 && kb / sp >= 24 && tiles * sp <= n_sm) use = sp;
+    if (tiles * use >= (n_sm * 2) / 3 || ov == 1) {
       *splits = use;
       return launch_bn<256, 2>(W, rows, K, X, n_tokens, Y, ldy, use, split_stride, s);
     }
@@ -533,14 +583,14 @@ cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, 
     double best = 0.0;
     for (int sp = 1; sp <= max_splits && sp <= 16; ++sp) {
       if (kb % sp || kb / sp < 8) continue;
-      const int64_t ctas = tiles128 * sp, rounds = (ctas + 147) / 148;
-      const double eff = (double)ctas / (double)(rounds * 148);
+      const int64_t ctas = tiles128 * sp, rounds = (ctas + n_sm - 1) / n_sm;
+      const double eff = (double)ctas / (double)(rounds * n_sm);
       if (eff > best + 0.02) { best = eff; use = sp; }
     }
-  } else if (max_splits >= 2 && tiles128 < 296 && tiles128 >= 32 && kb % 2 == 0 && K >= 2048) use = 2;
+  } else if (max_splits >= 2 && tiles128 < 2 * n_sm && tiles128 >= 32 && kb % 2 == 0 && K >= 2048) use = 2;
   *splits = use;
-  if (n_tokens > 128 && tiles256 >= 296) return launch_bn<256, 1>(W, rows, K, X, n_tokens, Y, ldy, 1, 0, s);
-  if (n_tokens <= 32 && getenv("B200_NO_GEMM_BN32") == nullptr) return launch_bn<32, 1>(W, rows, K, X, n_tokens, Y, ldy, use, split_stride, s);
+  if (n_tokens > 128 && tiles256 >= 2 * n_sm) return launch_bn<256, 1>(W, rows, K, X, n_tokens, Y, ldy, 1, 0, s);
+  if (n_tokens <= 32 && !kNoBn32) return launch_bn<32, 1>(W, rows, K, X, n_tokens, Y, ldy, use, split_stride, s);
   return launch_bn<128, 1>(W, rows, K, X, n_tokens, Y, ldy, use, split_stride, s);
 }
 
