@@ -23,11 +23,22 @@ DEVINL float block_sum256(float v, float* red) {
   return t;
 }
 
+DEVINL float block_sum_any(float v, float* red) {  // any block size that is a multiple of 32, red[32]
+  v = warp_sum(v);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float t = 0.f;
+  for (int i = 0; i < nw; ++i) t += red[i];
+  __syncthreads();
+  return t;
+}
+
 // x[t][:] (+= sum of the split-K partials add[p][t][:], p ascending) ; xb[t][:] = bf16( (x * inv_rms) * w )
-// grid = tokens, block = 256
-__global__ void add_rmsnorm_bf16_kernel(float* x, const float* add, int n_parts, long long part_stride, const float* w, uint16_t* xb, int d,
+// grid = tokens, block = 256 .. 1024 (a multiple of 32)
+__global__ void __launch_bounds__(1024) add_rmsnorm_bf16_kernel(float* x, const float* add, int n_parts, long long part_stride, const float* w, uint16_t* xb, int d,
                                         float eps, const unsigned int* wait_flags, int n_wait, unsigned int wait_seq, int* wait_error) {
-  __shared__ float red[8];
+  __shared__ float red[32];
   if (wait_flags) {  // partials pushed by the peer GPUs: wait for every rank's sequence flag (bounded)
     if ((int)threadIdx.x < n_wait) {
       const long long t0 = clock64();
@@ -41,31 +52,69 @@ __global__ void add_rmsnorm_bf16_kernel(float* x, const float* add, int n_parts,
   }
   float* xr = x + (size_t)blockIdx.x * d;
   const float* ar = (add && n_parts > 0) ? add + (size_t)blockIdx.x * d : nullptr;
+  // Each thread owns up to kMaxI = 2 float4 of the row and keeps them (and the norm weights) in registers between the sum
+  // of squares and the scaling: with 1024 threads a row of 4096 is ONE float4 per thread, so the residual, the partials
+  // (summed in ascending order, fetched eight at a time) and the weights are all in flight together.  With few rows
+  // (batched decode) this kernel is a chain of L2 round trips, not bandwidth.
+  constexpr int kMaxI = 2;
+  const int step = (int)blockDim.x * 4;
+  float4 v[kMaxI], g[kMaxI];
   float ss = 0.f;
-  for (int k = threadIdx.x * 4; k < d; k += 1024) {
-    float4 v = *reinterpret_cast<const float4*>(xr + k);
+#pragma unroll
+  for (int i = 0; i < kMaxI; ++i) {
+    const int k = (int)threadIdx.x * 4 + i * step;
+    if (k >= d) break;
+    v[i] = *reinterpret_cast<const float4*>(xr + k);
+    g[i] = *reinterpret_cast<const float4*>(w + k);
+    if (ar) {
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int p0 = 0; p0 < n_parts; p0 += 8) {
+        float4 b[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          b[j] = p0 + j < n_parts ? __ldcg(reinterpret_cast<const float4*>(ar + (size_t)(p0 + j) * part_stride + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (p0 + j < n_parts) {
+            if (p0 + j == 0) a = b[0];
+            else { a.x += b[j].x; a.y += b[j].y; a.z += b[j].z; a.w += b[j].w; }
+          }
+      }
+      v[i].x += a.x; v[i].y += a.y; v[i].z += a.z; v[i].w += a.w;
+      *reinterpret_cast<float4*>(xr + k) = v[i];
+    }
+    ss += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
+  }
+  for (int k = (int)threadIdx.x * 4 + kMaxI * step; k < d; k += step) {  // rows wider than 8 x threads: not held in registers
+    float4 t = *reinterpret_cast<const float4*>(xr + k);
     if (ar) {
       float4 a = __ldcg(reinterpret_cast<const float4*>(ar + k));
       for (int p = 1; p < n_parts; ++p) {
         const float4 b = __ldcg(reinterpret_cast<const float4*>(ar + (size_t)p * part_stride + k));
         a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
       }
-      v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
-      *reinterpret_cast<float4*>(xr + k) = v;
+      t.x += a.x; t.y += a.y; t.z += a.z; t.w += a.w;
+      *reinterpret_cast<float4*>(xr + k) = t;
     }
-    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    ss += t.x * t.x + t.y * t.y + t.z * t.z + t.w * t.w;
   }
-  ss = block_sum256(ss, red);
+  ss = block_sum_any(ss, red);
   const float inv = 1.0f / sqrtf(ss / (float)d + eps);
   uint16_t* o = xb + (size_t)blockIdx.x * d;
-  for (int k = threadIdx.x * 4; k < d; k += 1024) {
-    const float4 v = *reinterpret_cast<const float4*>(xr + k);
-    const float4 g = *reinterpret_cast<const float4*>(w + k);
+  auto put = [&](int k, const float4& t, const float4& gg) {
     uint2 p;
-    p.x = (uint32_t)f32_to_bf16_bits(__fmul_rn(__fmul_rn(v.x, inv), g.x)) | ((uint32_t)f32_to_bf16_bits(__fmul_rn(__fmul_rn(v.y, inv), g.y)) << 16);
-    p.y = (uint32_t)f32_to_bf16_bits(__fmul_rn(__fmul_rn(v.z, inv), g.z)) | ((uint32_t)f32_to_bf16_bits(__fmul_rn(__fmul_rn(v.w, inv), g.w)) << 16);
+    p.x = (uint32_t)f32_to_bf16_bits(__fmul_rn(__fmul_rn(t.x, inv), gg.x)) | ((uint32_t)f32_to_bf16_bits(__fmul_rn(__fmul_rn(t.y, inv), gg.y)) << 16);
+    p.y = (uint32_t)f32_to_bf16_bits(__fmul_rn(__fmul_rn(t.z, inv), gg.z)) | ((uint32_t)f32_to_bf16_bits(__fmul_rn(__fmul_rn(t.w, inv), gg.w)) << 16);
     *reinterpret_cast<uint2*>(o + k) = p;
+  };
+#pragma unroll
+  for (int i = 0; i < kMaxI; ++i) {
+    const int k = (int)threadIdx.x * 4 + i * step;
+    if (k >= d) break;
+    put(k, v[i], g[i]);
   }
+  for (int k = (int)threadIdx.x * 4 + kMaxI * step; k < d; k += step)
+    put(k, *reinterpret_cast<const float4*>(xr + k), *reinterpret_cast<const float4*>(w + k));
 }
 
 // qkv[t][q_rows + 2 kv_rows] fp32 -> q[t][q_rows] (rotated), K/V appended to the paged bf16 cache at pos0+t
@@ -81,10 +130,18 @@ __global__ void rope_kv_kernel(const float* qkv, float* q, uint16_t* k_cache, ui
   const int page = bt[pos / kPageTokens];
   for (int p = blockIdx.y * blockDim.x + threadIdx.x; p < width / 2; p += gridDim.y * blockDim.x) {
     const int row = 2 * p;
-    float x0 = in[row], x1 = in[row + 1];
-    for (int sp = 1; sp < n_parts; ++sp) {  // split-K partials of the qkv GEMM, ascending order
-      x0 += in[(size_t)sp * part_stride + row];
-      x1 += in[(size_t)sp * part_stride + row + 1];
+    float x0 = 0.f, x1 = 0.f;
+    for (int p0 = 0; p0 < n_parts; p0 += 8) {  // split-K partials of the qkv GEMM: summed in ascending order, fetched 8 at a time
+      float2 b[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        b[j] = p0 + j < n_parts ? __ldcg(reinterpret_cast<const float2*>(in + (size_t)(p0 + j) * part_stride + row)) : make_float2(0.f, 0.f);
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (p0 + j < n_parts) {
+          if (p0 + j == 0) { x0 = b[0].x; x1 = b[0].y; }
+          else { x0 += b[j].x; x1 += b[j].y; }
+        }
     }
     if (row < q_rows + kv_rows) {
       const int i = (row & (kHeadDim - 1)) >> 1;
@@ -216,7 +273,8 @@ cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, int n_parts, int
                                     int d, float eps, cudaStream_t s, const unsigned int* wait_flags, int n_wait, unsigned int wait_seq,
                                     int* wait_error) {
   if (d % 4 || part_stride % 4 || (wait_flags && (n_wait < 1 || n_wait > 256 || !wait_error))) return cudaErrorInvalidValue;
-  count_launch(); add_rmsnorm_bf16_kernel<<<tokens, 256, 0, s>>>(x, add, n_parts, (long long)part_stride, w, xb, d, eps, wait_flags, n_wait, wait_seq,
+  const int threads = d >= 4096 ? 1024 : (d >= 2048 ? 512 : 256);
+  count_launch(); add_rmsnorm_bf16_kernel<<<tokens, threads, 0, s>>>(x, add, n_parts, (long long)part_stride, w, xb, d, eps, wait_flags, n_wait, wait_seq,
                                                  wait_error);
   return cudaGetLastError();
 }
@@ -224,7 +282,9 @@ cudaError_t launch_rope_kv(const float* qkv, float* q, uint16_t* k_cache, uint16
                            int tokens, int q_rows, int kv_rows, int n_kv_heads, int pos0, const int32_t* pos_arr, const int32_t* slot_arr,
                            int pages_per_seq, int n_parts, int64_t part_stride, cudaStream_t s) {
   // few tokens (batched decode): spread a token's row pairs over several CTAs, above all when partials are summed
-  const int ny = tokens >= 128 ? 1 : (tokens >= 32 ? 2 : 8);
+  const int pairs = (q_rows + 2 * kv_rows) / 2;
+  const int full = (pairs + 255) / 256;  // CTAs per token at one pair per thread
+  const int ny = tokens >= 256 ? 1 : (tokens >= 64 ? (full < 4 ? full : 4) : full);
   count_launch(); rope_kv_kernel<<<dim3(tokens, ny), 256, 0, s>>>(qkv, q, k_cache, v_cache, block_table, rope, q_rows, kv_rows, n_kv_heads, pos0, pos_arr, slot_arr,
                                         pages_per_seq, n_parts, (long long)part_stride);
   return cudaGetLastError();
