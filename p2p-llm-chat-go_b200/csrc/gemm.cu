@@ -524,22 +524,10 @@ bool gemm_shape_ok(int64_t rows, int64_t K, int64_t n_tokens) {
 // Y[t*ldy + r] = sum_k X[t][k] W[r][k];  W, X bf16 (K-major, 16-byte aligned rows), Y fp32.
 cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
                              int64_t ldy, cudaStream_t s, const GemmWorkspace* wk) {
-  // stream-K schedule (experiment, see below)
-  if (wk && wk->ws && wk->flags && wk->sm_count > 0 && gemm_shape_ok(rows, K, n_tokens) && rows % (2 * BM) == 0 && n_tokens > 128 &&
-      m256_override() != 0 && !kNoStreamK) {
-    const int64_t tiles = (rows / (2 * BM)) * ((n_tokens + 255) / 256), P = wk->sm_count;
-    const int64_t waves = (tiles + P - 1) / P;
-    const int64_t total = tiles * (K / BK), units = (total + P - 1) / P;
-    // Measured on B200 (round 1): NOT faster than whole tiles in waves — gate/up at 512 tokens 122 us vs 117 us,
-    // at 256 tokens 97 us vs 62 us.  CTAs that run the same K block of neighbouring tiles in lock-step share
-    // their operand fetches in L2 (ncu: 400 MB of DRAM reads per launch in waves, 515 MB with staggered K), and
-    // every CTA pays up to three serialised epilogues.  So the schedule is opt-in: B200_GEMM_STREAMK=1 takes it
-    // for any shape it can express (tests), otherwise it is never chosen.
-    (void)waves;
-    const bool want = env_int("B200_GEMM_STREAMK", 0) == 1 && units >= 1;
-    if (want && (size_t)P * 256 * 256 * 4 <= wk->ws_bytes)
-      return launch_streamk<256>(W, rows, K, X, n_tokens, Y, ldy, *wk, s);
-  }
+  // (A stream-K schedule for >= 256 tokens was built and measured in round 1: gate/up at 512 tokens 122 us vs 117 us in
+  // whole tiles, at 256 tokens 97 vs 62 — CTAs that run the same K block of neighbouring tiles in lock-step share their
+  // operand fetches in L2, staggered runs do not.  It was removed from the library; the schedule remains for <= 128
+  // tokens, where it is the faster one: launch_gemm_bf16_splitk.)
   int splits = 1;
   return launch_gemm_bf16_splitk(W, rows, K, X, n_tokens, Y, ldy, 0, &splits, s, wk);
 }

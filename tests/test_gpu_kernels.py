@@ -182,12 +182,11 @@ def test_gemm_tcgen05_m256(pkg, rows, cols, n, monkeypatch):
     assert np.array_equal(got, pkg.gemm(orc.BF16, W, rows, cols, X))  # same K order: same bits as the 128-row tiles
 
 
-# stream-K schedule of the 256 x 256 tiles (persistent CTAs, tiles cut across CTAs, partials through a
-# workspace, summed by the tile's owner in CTA order): forced on small shapes, where a tile is shared by up to
-# 32 CTAs; repeated calls must give the same bits (deterministic reduction, flags re-armed by the kernel)
-@pytest.mark.parametrize("rows,cols,n", [(256, 64, 129), (512, 2048, 300), (1024, 4096, 256), (4096, 1024, 513), (28672, 4096, 512),
-                                         # one token tile (the weight-streaming regime of batched decode): 128-token variant
-                                         (256, 64, 7), (512, 2048, 33), (1024, 4096, 128), (6144, 4096, 1), (28672, 4096, 8)])
+# stream-K schedule of the 256-row tiles for up to 128 tokens (persistent CTAs, tiles cut across CTAs, partials
+# through a workspace, summed by the tile's owner in CTA order): forced on small shapes, where a tile is shared by up
+# to 32 CTAs; repeated calls must give the same bits (deterministic reduction, flags re-armed by the kernel)
+@pytest.mark.parametrize("rows,cols,n", [  # one token tile: the weight-streaming regime of batched decode (32- and 128-token variants)
+    (256, 64, 7), (512, 2048, 33), (1024, 4096, 128), (6144, 4096, 1), (28672, 4096, 8), (4096, 1024, 100), (28672, 4096, 32)])
 def test_gemm_tcgen05_streamk(pkg, rows, cols, n, monkeypatch):
     rng = np.random.default_rng(11 * rows + cols + n)
     W = random_tensor(rng, orc.BF16, rows, cols)
