@@ -547,13 +547,13 @@ cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, 
   const int64_t kb = K / BK, n_sm = wk && wk->sm_count > 0 ? wk->sm_count : sm_count_now();
   const int ov = m256_override();
   // 256 x 256 tiles, one CTA per SM: the fewest operand bytes per MAC.  Taken when, with K split up to
-  // max_splits ways (each split keeps >= 24 K blocks: shorter loops do not amortise the CTA set-up), the grid comes to between two thirds of the SMs and all of them, or has several waves.
+  // max_splits ways (each split keeps >= 24 K blocks: shorter loops do not amortise the CTA set-up), the grid comes to between 65 % of the SMs and all of them, or has several waves.
   if (rows % (2 * BM) == 0 && n_tokens > 128 && ov != 0) {
     const int64_t tiles = (rows / (2 * BM)) * ((n_tokens + 255) / 256);
     int use = 1;
     for (int sp = 2; sp <= max_splits; sp *= 2)
       if (kb % sp == 0 && kb / sp >= 24 && tiles * sp <= n_sm) use = sp;
-    if (tiles * use >= (n_sm * 2) / 3 || ov == 1) {
+    if (tiles * use >= (n_sm * 13) / 20 || ov == 1) {  // 96 of 148: the qkv GEMM at 512 tokens (48 tiles x 2 splits) sits exactly there
       *splits = use;
       return launch_bn<256, 2>(W, rows, K, X, n_tokens, Y, ldy, use, split_stride, s);
     }

@@ -36,7 +36,8 @@ DEVINL float block_sum_any(float v, float* red) {  // any block size that is a m
 
 // x[t][:] (+= sum of the split-K partials add[p][t][:], p ascending) ; xb[t][:] = bf16( (x * inv_rms) * w )
 // grid = tokens, block = 256 .. 1024 (a multiple of 32)
-__global__ void __launch_bounds__(1024) add_rmsnorm_bf16_kernel(float* x, const float* add, int n_parts, long long part_stride, const float* w, uint16_t* xb, int d,
+template <int THREADS, int kMaxI, int MINB>  // <1024, 2, 1>: few rows (batched decode: latency-bound)
+__global__ void __launch_bounds__(THREADS, MINB) add_rmsnorm_bf16_kernel(float* x, const float* add, int n_parts, long long part_stride, const float* w, uint16_t* xb, int d,
                                         float eps, const unsigned int* wait_flags, int n_wait, unsigned int wait_seq, int* wait_error) {
   __shared__ float red[32];
   if (wait_flags) {  // partials pushed by the peer GPUs: wait for every rank's sequence flag (bounded)
@@ -52,11 +53,10 @@ __global__ void __launch_bounds__(1024) add_rmsnorm_bf16_kernel(float* x, const 
   }
   float* xr = x + (size_t)blockIdx.x * d;
   const float* ar = (add && n_parts > 0) ? add + (size_t)blockIdx.x * d : nullptr;
-  // Each thread owns up to kMaxI = 2 float4 of the row and keeps them (and the norm weights) in registers between the sum
+  // Each thread owns up to kMaxI float4 of the row and keeps them (and the norm weights) in registers between the sum
   // of squares and the scaling: with 1024 threads a row of 4096 is ONE float4 per thread, so the residual, the partials
   // (summed in ascending order, fetched eight at a time) and the weights are all in flight together.  With few rows
   // (batched decode) this kernel is a chain of L2 round trips, not bandwidth.
-  constexpr int kMaxI = 2;
   const int step = (int)blockDim.x * 4;
   float4 v[kMaxI], g[kMaxI];
   float ss = 0.f;
@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(1024) add_rmsnorm_bf16_kernel(float* x, const 
     }
     ss += v[i].x * v[i].x + v[i].y * v[i].y + v[i].z * v[i].z + v[i].w * v[i].w;
   }
-  for (int k = (int)threadIdx.x * 4 + kMaxI * step; k < d; k += step) {  // rows wider than 8 x threads: not held in registers
+  for (int k = (int)threadIdx.x * 4 + kMaxI * step; k < d; k += step) {  // rows wider than 4 x kMaxI x threads: not held in registers
     float4 t = *reinterpret_cast<const float4*>(xr + k);
     if (ar) {
       float4 a = __ldcg(reinterpret_cast<const float4*>(ar + k));
@@ -142,6 +142,90 @@ __global__ void rope_kv_kernel(const float* qkv, float* q, uint16_t* k_cache, ui
           if (p0 + j == 0) { x0 = b[0].x; x1 = b[0].y; }
           else { x0 += b[j].x; x1 += b[j].y; }
         }
+    }
+    if (row < q_rows + kv_rows) {
+      const int i = (row & (kHeadDim - 1)) >> 1;
+      const float2 cs = *reinterpret_cast<const float2*>(rope + ((size_t)pos * (kHeadDim / 2) + i) * 2);
+      const float r0 = __fsub_rn(__fmul_rn(x0, cs.x), __fmul_rn(x1, cs.y));
+      const float r1 = __fadd_rn(__fmul_rn(x0, cs.y), __fmul_rn(x1, cs.x));
+      x0 = r0;
+      x1 = r1;
+    }
+    if (row < q_rows) {
+      *reinterpret_cast<float2*>(q + (size_t)t * q_rows + row) = make_float2(x0, x1);
+    } else {
+      const bool isk = row < q_rows + kv_rows;
+      const int kr = row - q_rows - (isk ? 0 : kv_rows);
+      const int kvh = kr >> 7, dim = kr & (kHeadDim - 1);
+      const size_t idx = (((size_t)page * n_kv_heads + kvh) * kPageTokens + (pos % kPageTokens)) * kHeadDim + dim;
+      *reinterpret_cast<uint32_t*>((isk ? k_cache : v_cache) + idx) = (uint32_t)f32_to_bf16_bits(x0) | ((uint32_t)f32_to_bf16_bits(x1) << 16);
+    }
+  }
+}
+
+// The same operation for MANY rows (prefill): plenty of CTAs in flight, so the plain streaming form — 256 threads, the
+// row re-read from L1/L2 for the scaling pass — is the faster one (8.8 vs 11.6 us at 512 rows).  grid = tokens, block = 256
+__global__ void add_rmsnorm_bf16_rows_kernel(float* x, const float* add, int n_parts, long long part_stride, const float* w, uint16_t* xb, int d,
+                                        float eps, const unsigned int* wait_flags, int n_wait, unsigned int wait_seq, int* wait_error) {
+  __shared__ float red[8];
+  if (wait_flags) {  // partials pushed by the peer GPUs: wait for every rank's sequence flag (bounded)
+    if ((int)threadIdx.x < n_wait) {
+      const long long t0 = clock64();
+      unsigned int v;
+      do {
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(wait_flags + threadIdx.x) : "memory");
+        if (clock64() - t0 > 4000000000ll) { *wait_error = 1; break; }
+      } while ((int)(v - wait_seq) < 0);
+    }
+    __syncthreads();
+  }
+  float* xr = x + (size_t)blockIdx.x * d;
+  const float* ar = (add && n_parts > 0) ? add + (size_t)blockIdx.x * d : nullptr;
+  float ss = 0.f;
+  for (int k = threadIdx.x * 4; k < d; k += 1024) {
+    float4 v = *reinterpret_cast<const float4*>(xr + k);
+    if (ar) {
+      float4 a = __ldcg(reinterpret_cast<const float4*>(ar + k));
+      for (int p = 1; p < n_parts; ++p) {
+        const float4 b = __ldcg(reinterpret_cast<const float4*>(ar + (size_t)p * part_stride + k));
+        a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+      }
+      v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+      *reinterpret_cast<float4*>(xr + k) = v;
+    }
+    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+  }
+  ss = block_sum256(ss, red);
+  const float inv = 1.0f / sqrtf(ss / (float)d + eps);
+  uint16_t* o = xb + (size_t)blockIdx.x * d;
+  for (int k = threadIdx.x * 4; k < d; k += 1024) {
+    const float4 v = *reinterpret_cast<const float4*>(xr + k);
+    const float4 g = *reinterpret_cast<const float4*>(w + k);
+    uint2 p;
+    p.x = (uint32_t)f32_to_bf16_bits(__fmul_rn(__fmul_rn(v.x, inv), g.x)) | ((uint32_t)f32_to_bf16_bits(__fmul_rn(__fmul_rn(v.y, inv), g.y)) << 16);
+    p.y = (uint32_t)f32_to_bf16_bits(__fmul_rn(__fmul_rn(v.z, inv), g.z)) | ((uint32_t)f32_to_bf16_bits(__fmul_rn(__fmul_rn(v.w, inv), g.w)) << 16);
+    *reinterpret_cast<uint2*>(o + k) = p;
+  }
+}
+
+// Many rows (prefill): the plain loop over the partials (10 vs 17 us at 512 rows with the batched fetch below).
+// qkv[t][q_rows + 2 kv_rows] fp32 -> q[t][q_rows] (rotated), K/V appended to the paged bf16 cache at pos0+t
+// Row t is position pos0+t of one sequence (prefill), or — batched decode — position pos_arr[t] of the
+// sequence in slot slot_arr[t], whose block table is row slot_arr[t] of `block_table` (pages_per_seq wide).
+__global__ void rope_kv_rows_kernel(const float* qkv, float* q, uint16_t* k_cache, uint16_t* v_cache, const int32_t* block_table,
+                               const float* rope, int q_rows, int kv_rows, int n_kv_heads, int pos0, const int32_t* pos_arr,
+                               const int32_t* slot_arr, int pages_per_seq, int n_parts, long long part_stride) {
+  const int t = blockIdx.x, pos = pos_arr ? pos_arr[t] : pos0 + t;
+  const int width = q_rows + 2 * kv_rows;
+  const float* in = qkv + (size_t)t * width;
+  const int32_t* bt = slot_arr ? block_table + (size_t)slot_arr[t] * pages_per_seq : block_table;
+  const int page = bt[pos / kPageTokens];
+  for (int p = blockIdx.y * blockDim.x + threadIdx.x; p < width / 2; p += gridDim.y * blockDim.x) {
+    const int row = 2 * p;
+    float x0 = in[row], x1 = in[row + 1];
+    for (int sp = 1; sp < n_parts; ++sp) {  // split-K partials of the qkv GEMM, ascending order
+      x0 += in[(size_t)sp * part_stride + row];
+      x1 += in[(size_t)sp * part_stride + row + 1];
     }
     if (row < q_rows + kv_rows) {
       const int i = (row & (kHeadDim - 1)) >> 1;
@@ -273,8 +357,12 @@ cudaError_t launch_add_rmsnorm_bf16(float* x, const float* add, int n_parts, int
                                     int d, float eps, cudaStream_t s, const unsigned int* wait_flags, int n_wait, unsigned int wait_seq,
                                     int* wait_error) {
   if (d % 4 || part_stride % 4 || (wait_flags && (n_wait < 1 || n_wait > 256 || !wait_error))) return cudaErrorInvalidValue;
-  const int threads = d >= 4096 ? 1024 : (d >= 2048 ? 512 : 256);
-  count_launch(); add_rmsnorm_bf16_kernel<<<tokens, threads, 0, s>>>(x, add, n_parts, (long long)part_stride, w, xb, d, eps, wait_flags, n_wait, wait_seq,
+  count_launch();
+  if (tokens <= 64 && d >= 2048)  // few rows: one CTA per row is all the parallelism there is, so make it wide
+    add_rmsnorm_bf16_kernel<1024, 2, 1><<<tokens, d >= 4096 ? 1024 : 512, 0, s>>>(x, add, n_parts, (long long)part_stride, w, xb, d, eps, wait_flags, n_wait, wait_seq,
+                                                 wait_error);
+  else
+    add_rmsnorm_bf16_rows_kernel<<<tokens, 256, 0, s>>>(x, add, n_parts, (long long)part_stride, w, xb, d, eps, wait_flags, n_wait, wait_seq,
                                                  wait_error);
   return cudaGetLastError();
 }
@@ -285,7 +373,10 @@ cudaError_t launch_rope_kv(const float* qkv, float* q, uint16_t* k_cache, uint16
   const int pairs = (q_rows + 2 * kv_rows) / 2;
   const int full = (pairs + 255) / 256;  // CTAs per token at one pair per thread
   const int ny = tokens >= 256 ? 1 : (tokens >= 64 ? (full < 4 ? full : 4) : full);
-  count_launch(); rope_kv_kernel<<<dim3(tokens, ny), 256, 0, s>>>(qkv, q, k_cache, v_cache, block_table, rope, q_rows, kv_rows, n_kv_heads, pos0, pos_arr, slot_arr,
+  count_launch();
+  if (tokens < 64) rope_kv_kernel<<<dim3(tokens, ny), 256, 0, s>>>(qkv, q, k_cache, v_cache, block_table, rope, q_rows, kv_rows, n_kv_heads, pos0, pos_arr, slot_arr,
+                                        pages_per_seq, n_parts, (long long)part_stride);
+  else rope_kv_rows_kernel<<<dim3(tokens, ny), 256, 0, s>>>(qkv, q, k_cache, v_cache, block_table, rope, q_rows, kv_rows, n_kv_heads, pos0, pos_arr, slot_arr,
                                         pages_per_seq, n_parts, (long long)part_stride);
   return cudaGetLastError();
 }
