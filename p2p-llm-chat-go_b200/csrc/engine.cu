@@ -97,9 +97,8 @@ int Engine::init(const b200_config& c, const void* nccl_id) {
   use_attn_prefetch = getenv("B200_NO_ATTN_PREFETCH") == nullptr;
   use_attn_cluster = use_attn_prefetch && getenv("B200_NO_ATTN_CLUSTER") == nullptr && attn_cluster_supported(c.n_heads / c.n_kv_heads);
   use_prefix_cache = getenv("B200_NO_PREFIX_CACHE") == nullptr && (c.reserved & 2) == 0 && tp_size == 1;
-  // measured on B200 (round 1): chaining L2 prefetches of the next kernel's weights made the step SLOWER
-  // (bf16 3.18 vs 3.05 ms, Q4_K_M 1.84 vs 1.78 ms), so it is opt-in for experiments only
-  use_l2_chain = getenv("B200_L2_CHAIN") != nullptr;
+  // L2 prefetch chain between the decode GEMVs (see enqueue_step): B200_L2_CHAIN=<MB> overrides the amount, 0 = off
+  l2_chain_mb = getenv("B200_L2_CHAIN") ? atoi(getenv("B200_L2_CHAIN")) : -1;
 
   const int tp = tp_size, R = tp_rank;
   if (tp < 1 || R < 0 || R >= tp || c.n_heads % tp || c.n_kv_heads % tp || c.d_ffn % tp || c.vocab % tp ||
@@ -440,10 +439,15 @@ int Engine::enqueue_step(cudaStream_t s) {
     a.row_base = 0; a.q_rows = qd; a.kv_rows = kvd; a.n_kv_heads = c.n_kv_heads; a.rope = rope;
     a.k_cache = L.k_cache; a.v_cache = L.v_cache; a.block_table = active_table; a.st = st;
     // L2 prefetch chain: qkv -> o (waits in L2 while attention runs), o -> gate/up, gate/up -> down, down -> next qkv
-    const unsigned long long pf_cap = use_l2_chain ? (40ull << 20) : 0ull;
+    // A warp that has streamed its last unit asks L2 for a slice of the first megabytes of the NEXT kernel's weights
+    // (GemvArgs::next_W), so that kernel's first ring fills come from L2 while HBM would otherwise idle across the
+    // kernel boundary.  The amount matters: 40 MB (round 1) made the step slower, 12 MB makes the bf16 step 3.5 %
+    // faster (2.78 -> 2.68 ms), 6 MB the Q4_K_M step 0.5 % (1.461 -> 1.454); more displaces what is about to be used.
     auto chain = [&](GemvArgs& g, const uint8_t* w, int type, int64_t rows, int64_t k) {
+      const unsigned long long cap = l2_chain_mb >= 0 ? (unsigned long long)l2_chain_mb << 20
+                                                      : ((type == T_Q4_K || type == T_Q6_K) ? (6ull << 20) : (12ull << 20));
       g.next_W = w;
-      g.next_bytes = std::min<unsigned long long>(pf_cap, (unsigned long long)rows * gemv_row_bytes(type, k)) & ~127ull;
+      g.next_bytes = std::min<unsigned long long>(cap, (unsigned long long)rows * gemv_row_bytes(type, k)) & ~127ull;
     };
     chain(a, L.o, L.o_type, d, qd);
     bool dual = false;

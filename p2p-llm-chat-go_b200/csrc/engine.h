@@ -172,12 +172,13 @@ struct Engine {
 
   cudaGraphExec_t step_graph = nullptr;
   int step_graph_nodes = 0;  // kernel nodes of the captured step (counted as launches at every replay)
-  bool use_pdl = true, use_graph = true, use_l2_chain = false, use_fa_prefill = true, use_mma_decode = true, use_attn_prefetch = true, use_attn_cluster = false;
+  bool use_pdl = true, use_graph = true, use_fa_prefill = true, use_mma_decode = true, use_attn_prefetch = true, use_attn_cluster = false;
   // n_seqs sequences decoding together from a context of ctx tokens, synchronously (no scheduler thread): the
   // batched step of scheduler.cu, tensor-parallel aware (every rank makes the same call)
   int bench_batched(int n_seqs, int ctx, int n_steps, float* ms_per_step, int32_t* last_ids);
   unsigned long long* b_keys = nullptr;  // [max_seqs] argmax keys (vocab-parallel lm_head)
   int launches_per_step = 0;
+  int l2_chain_mb = -1;  // L2 prefetch chain: MB of the next kernel's weights (-1: per-format default, 0: off)
   unsigned long long* trace_dev = nullptr;   // B200_TRACE=<file>: 4 stamps per launch of the decode step (see GemvArgs::trace)
   int dump_trace();                          // the last step's stamps -> "<launch> <name> t0 t1 t2 t3" lines (ns)
   std::vector<std::string> trace_names;
