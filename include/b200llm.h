@@ -201,6 +201,9 @@ B200_API int b200_gemv_rmsnorm(int type, const void* w, int64_t rows, int64_t co
                                const float* norm_w, float eps, float* y);
 /* Y[n,rows] = X[n,cols] . W^T on the tcgen05/TMEM GEMM (GEMM numerics; W is BF16 or dequantised to it). */
 B200_API int b200_gemm(int type, const void* w, int64_t rows, int64_t cols, const float* x, int64_t n, float* y);
+/* The ffn gate/up GEMM with SwiGLU in its epilogue: rows of W interleaved gate_i, up_i (rows even);
+   H[n, rows/2] = bf16( silu(X.W[2i]) * (X.W[2i+1]) ), bf16 bit patterns. */
+B200_API int b200_gemm_swiglu(int type, const void* w, int64_t rows, int64_t cols, const float* x, int64_t n, uint16_t* h);
 /* One query position of paged GQA decode attention; K,V given as fp32 [n_ctx][n_kv*128], stored as bf16. */
 B200_API int b200_attn_decode(const float* q, const float* k, const float* v, int n_ctx, int n_heads,
                               int n_kv_heads, float* out);

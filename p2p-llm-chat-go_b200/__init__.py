@@ -111,6 +111,7 @@ def lib():
         "b200_gemv": (i32, [i32, vp, i64, i64, vp, vp]),
         "b200_gemv_rmsnorm": (i32, [i32, vp, i64, i64, vp, vp, f32, vp]),
         "b200_gemm": (i32, [i32, vp, i64, i64, vp, i64, vp]),
+        "b200_gemm_swiglu": (i32, [i32, vp, i64, i64, vp, i64, vp]),
         "b200_attn_decode": (i32, [vp, vp, vp, i32, i32, i32, vp]),
         "b200_attn_decode_noalloc": (i32, [vp, vp, vp, vp, i32, i32, i32, vp, vp]),
         "b200_sample": (i32, [vp, i32, smpp, vp, i32, u64, C.POINTER(C.c_int32)]),
@@ -197,6 +198,14 @@ def gemm(wtype, W, rows, cols, X):
     Y = np.empty((X.shape[0], rows), np.float32)
     _check(lib().b200_gemm(wtype, _p(W), rows, cols, _p(X), X.shape[0], _p(Y)))
     return Y
+
+
+def gemm_swiglu(wtype, W, rows, cols, X):
+    """ffn gate/up GEMM with the SwiGLU epilogue; returns bf16 bit patterns [n][rows/2] (uint16)."""
+    W, X = np.ascontiguousarray(W), _c(X, np.float32).reshape(-1, cols)
+    H = np.empty((X.shape[0], rows // 2), np.uint16)
+    _check(lib().b200_gemm_swiglu(wtype, _p(W), rows, cols, _p(X), X.shape[0], _p(H)))
+    return H
 
 
 def attn_decode(q, K, V, n_heads, n_kv_heads):

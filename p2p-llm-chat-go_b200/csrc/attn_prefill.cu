@@ -43,8 +43,17 @@ DEVINL uint32_t tile_off(int r, int c) { return (uint32_t)((r * 16 + (c ^ (r & 7
 template <int G>
 __global__ void __launch_bounds__(G * 32) attn_prefill_kernel(const float* __restrict__ q, const uint16_t* __restrict__ k_cache,
                                                              const uint16_t* __restrict__ v_cache, const int32_t* __restrict__ block_table,
-                                                             uint16_t* __restrict__ out, int T, int pos0, int n_heads, int n_kv_heads) {
+                                                             uint16_t* __restrict__ out, int T, int pos0, int n_heads, int n_kv_heads,
+                                                             const AttnPrefillSegs segs) {
   extern __shared__ __align__(128) uint8_t tiles[];  // 2 stages x {K tile 16 KB, V tile 16 KB}
+  if (segs.n > 0) {  // several prompts in one launch: blockIdx.z picks the prompt, its rows of q/out and its slot's block table
+    const int4 sg = segs.seg[blockIdx.z];
+    q += (size_t)sg.x * n_heads * kHeadDim;
+    out += (size_t)sg.x * n_heads * kHeadDim;
+    block_table += (size_t)sg.w * segs.pages_per_seq;
+    T = sg.y; pos0 = sg.z;
+    if ((int)(gridDim.y - 1 - blockIdx.y) * kQRows >= T) return;  // the grid is sized for the longest prompt
+  }
   // heavy blocks first: under the causal mask the last query block does ~T/64 tiles, the first only one
   const int kvh = blockIdx.x, q0 = (gridDim.y - 1 - blockIdx.y) * kQRows;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
@@ -343,11 +352,11 @@ __global__ void __launch_bounds__(128, 3) attn_decode_mma_kernel(const float* __
 
 }  // namespace
 
-// q: [T][n_heads*128] fp32 (rotated); out: [T][n_heads*128] bf16.  K/V of positions [0, pos0+T) must be in the cache.
-cudaError_t launch_attn_prefill(const float* q, const uint16_t* k_cache, const uint16_t* v_cache, const int32_t* block_table, uint16_t* out,
-                                int T, int pos0, int n_heads, int n_kv_heads, cudaStream_t s) {
+namespace {
+cudaError_t launch_attn_prefill_any(const float* q, const uint16_t* k_cache, const uint16_t* v_cache, const int32_t* block_table, uint16_t* out,
+                                    int T, int pos0, int n_heads, int n_kv_heads, const AttnPrefillSegs& segs, cudaStream_t s) {
   if (T < 1 || n_kv_heads < 1 || n_heads % n_kv_heads) return cudaErrorInvalidValue;
-  dim3 grid(n_kv_heads, (T + kQRows - 1) / kQRows);
+  dim3 grid(n_kv_heads, (T + kQRows - 1) / kQRows, segs.n > 0 ? segs.n : 1);
   constexpr int kSmem = 2 * 2 * kKvTile * 256;  // 64 KB
 #define LAUNCH(G_)                                                                                                   \
   {                                                                                                                  \
@@ -355,14 +364,42 @@ cudaError_t launch_attn_prefill(const float* q, const uint16_t* k_cache, const u
     if (e_ != cudaSuccess) return e_;                                                                                \
     count_launch(); attn_prefill_kernel<G_><<<grid, G_ * 32, kSmem, s>>>
   switch (n_heads / n_kv_heads) {
-    case 1: LAUNCH(1)(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); } break;
-    case 2: LAUNCH(2)(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); } break;
-    case 4: LAUNCH(4)(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); } break;
-    case 8: LAUNCH(8)(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads); } break;
+    case 1: LAUNCH(1)(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads, segs); } break;
+    case 2: LAUNCH(2)(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads, segs); } break;
+    case 4: LAUNCH(4)(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads, segs); } break;
+    case 8: LAUNCH(8)(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads, segs); } break;
     default: return cudaErrorInvalidValue;
   }
 #undef LAUNCH
   return cudaGetLastError();
+}
+}  // namespace
+
+// q: [T][n_heads*128] fp32 (rotated); out: [T][n_heads*128] bf16.  K/V of positions [0, pos0+T) must be in the cache.
+cudaError_t launch_attn_prefill(const float* q, const uint16_t* k_cache, const uint16_t* v_cache, const int32_t* block_table, uint16_t* out,
+                                int T, int pos0, int n_heads, int n_kv_heads, cudaStream_t s) {
+  AttnPrefillSegs none = {};
+  return launch_attn_prefill_any(q, k_cache, v_cache, block_table, out, T, pos0, n_heads, n_kv_heads, none, s);
+}
+
+// Several prompts packed row-wise into q/out (segment i: rows [seg.x, seg.x + seg.y), first position seg.z, cache slot
+// seg.w): one launch, grid.z = prompt, so short and long prompts fill the GPU together instead of one after the other.
+cudaError_t launch_attn_prefill_segs(const float* q, const uint16_t* k_cache, const uint16_t* v_cache, const int32_t* block_table,
+                                     int pages_per_seq, uint16_t* out, const int4* segs, int n_segs, int n_heads, int n_kv_heads, cudaStream_t s) {
+  for (int i0 = 0; i0 < n_segs; i0 += AttnPrefillSegs::kMax) {
+    AttnPrefillSegs a = {};
+    a.n = n_segs - i0 < AttnPrefillSegs::kMax ? n_segs - i0 : AttnPrefillSegs::kMax;
+    a.pages_per_seq = pages_per_seq;
+    int t_max = 1;
+    for (int i = 0; i < a.n; ++i) {
+      a.seg[i] = segs[i0 + i];
+      if (segs[i0 + i].y < 1) return cudaErrorInvalidValue;
+      if (segs[i0 + i].y > t_max) t_max = segs[i0 + i].y;
+    }
+    cudaError_t e = launch_attn_prefill_any(q, k_cache, v_cache, block_table, out, t_max, 0, n_heads, n_kv_heads, a, s);
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
 }
 
 // One query per sequence: query z attends to the first a.q_ctx[z] tokens of the sequence in slot a.q_slot[z].

@@ -618,10 +618,11 @@ int b200_attn_decode_noalloc(const float* q_dev, const uint16_t* k_cache_dev, co
   return 0;
 }
 
-int b200_gemm(int type, const void* w, int64_t rows, int64_t cols, const float* x, int64_t n, float* y) {
+// y != null: Y fp32 [n][rows].  h != null: ffn gate/up with the SwiGLU epilogue, H bf16 [n][rows/2].
+static int gemm_common(int type, const void* w, int64_t rows, int64_t cols, const float* x, int64_t n, float* y, uint16_t* h) {
   int rc = have_device();
   if (rc) return rc;
-  if (!w || !x || !y) { set_error("null argument"); return B200_EINVAL; }
+  if (!w || !x || (!y && !h)) { set_error("null argument"); return B200_EINVAL; }
   if (type != T_BF16 && type != T_F16 && type != T_Q4_K && type != T_Q6_K) { set_error("b200_gemm: type must be BF16, F16, Q4_K or Q6_K"); return B200_EINVAL; }
   if (!gemm_shape_ok(rows, cols, n) || (type != T_BF16 && type != T_F16 && cols % QK_K)) {
     set_error("gemm shape rows=%lld (need %%8) cols=%lld (need %%64; %%256 for k-quants) n=%lld unsupported", (long long)rows, (long long)cols, (long long)n);
@@ -629,7 +630,11 @@ int b200_gemm(int type, const void* w, int64_t rows, int64_t cols, const float* 
   }
   DevBuf dw, dw16, dxf, dx16, dy;
   const size_t wbytes = (size_t)rows * gemv_row_bytes(type, cols);
-  if ((rc = dw.alloc(wbytes)) || (rc = dxf.alloc((size_t)n * cols * 4)) || (rc = dx16.alloc((size_t)n * cols * 2)) || (rc = dy.alloc((size_t)n * rows * 4))) return rc;
+  if (h && rows % 2) { set_error("b200_gemm_swiglu: rows must be even (gate_i, up_i interleaved)"); return B200_EINVAL; }
+  const int max_splits = 4;  // what the scratch below is sized for when the SwiGLU path has to split K
+  if ((rc = dw.alloc(wbytes)) || (rc = dxf.alloc((size_t)n * cols * 4)) || (rc = dx16.alloc((size_t)n * cols * 2)) ||
+      (rc = dy.alloc((size_t)n * rows * 4 * (h ? max_splits : 1))))
+    return rc;
   B200_CUDA(cudaMemcpy(dw.p, w, wbytes, cudaMemcpyHostToDevice));
   const uint16_t* w16 = dw.as<uint16_t>();
   if (type != T_BF16) {  // GEMM numerics: k-quant weights are dequantised and rounded to bf16
@@ -650,10 +655,28 @@ int b200_gemm(int type, const void* w, int64_t rows, int64_t cols, const float* 
   if ((rc = wsb.alloc(wk.ws_bytes)) || (rc = flb.alloc((size_t)(wk.sm_count + 8) * 4))) return rc;
   B200_CUDA(cudaMemset(flb.p, 0, (size_t)(wk.sm_count + 8) * 4));
   wk.ws = wsb.as<float>(); wk.flags = flb.as<unsigned int>();
+  if (h) {
+    DevBuf dh;
+    if ((rc = dh.alloc((size_t)n * (rows / 2) * 2))) return rc;
+    B200_CUDA(launch_gemm_bf16_swiglu(w16, rows, cols, dx16.as<uint16_t>(), n, dh.as<uint16_t>(), rows / 2, dy.as<float>(), max_splits, 0, &wk));
+    B200_CUDA(cudaDeviceSynchronize());
+    B200_CUDA(cudaMemcpy(h, dh.p, (size_t)n * (rows / 2) * 2, cudaMemcpyDeviceToHost));
+    return 0;
+  }
   B200_CUDA(launch_gemm_bf16(w16, rows, cols, dx16.as<uint16_t>(), n, dy.as<float>(), rows, 0, &wk));
   B200_CUDA(cudaDeviceSynchronize());
   B200_CUDA(cudaMemcpy(y, dy.p, (size_t)n * rows * 4, cudaMemcpyDeviceToHost));
   return 0;
+}
+
+int b200_gemm(int type, const void* w, int64_t rows, int64_t cols, const float* x, int64_t n, float* y) {
+  if (!y) { set_error("null argument"); return B200_EINVAL; }
+  return gemm_common(type, w, rows, cols, x, n, y, nullptr);
+}
+
+int b200_gemm_swiglu(int type, const void* w, int64_t rows, int64_t cols, const float* x, int64_t n, uint16_t* h) {
+  if (!h) { set_error("null argument"); return B200_EINVAL; }
+  return gemm_common(type, w, rows, cols, x, n, nullptr, h);
 }
 
 int b200_sample(const float* logits, int vocab, const b200_sampling* sp, const int32_t* history, int n_hist, uint64_t step, int32_t* id) {

@@ -92,6 +92,9 @@ DEVINL uint16_t f32_to_bf16_bits(float f) {  // RNE, same integer recipe as the 
   return (uint16_t)(u >> 16);
 }
 DEVINL float bf16_round(float f) { return __uint_as_float((uint32_t)f32_to_bf16_bits(f) << 16); }
+// silu(g) * u for the tensor-core (bf16) path: ex2.approx + approximate divide, ~1e-6 relative, far inside the bf16
+// rounding that follows; in a GEMM epilogue the accurate expf / divide (~40 instructions) sat on the CTA's critical path.
+DEVINL float silu_mul_fast(float g, float u) { return __fdividef(g, 1.0f + __expf(-g)) * u; }
 DEVINL float fp16_bits_to_f32(uint16_t h) { return __half2float(__ushort_as_half(h)); }
 
 DEVINL float warp_sum(float v) {

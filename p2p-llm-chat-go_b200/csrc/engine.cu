@@ -788,7 +788,7 @@ int Engine::ensure_prefill() {
       (rc = alloc((void**)&pf_qkv, (size_t)T * (qd + 2 * kvd) * 4)) || (rc = alloc((void**)&pf_q, (size_t)T * qd * 4)) ||
       (rc = alloc((void**)&pf_att, (size_t)T * qd * 4)) ||
       (rc = alloc((void**)&pf_proj, (size_t)(pf_proj_floats = (int64_t)std::max(2 * T, 2560) * d) * 4)) ||
-      (rc = alloc((void**)&pf_gu, (size_t)T * 2 * ff * 4)) ||
+      (rc = alloc((void**)&pf_gu, (size_t)T * 2 * ff * 4)) || (rc = alloc((void**)&pf_hb, (size_t)T * ff * 2)) ||
       (rc = alloc((void**)&pf_partial, (size_t)T * attn_partial_floats(c.n_heads, c.n_kv_heads, pf_splits) * 4)) ||
       (rc = alloc((void**)&pf_counters, (size_t)T * c.n_kv_heads * 4)) || (rc = alloc((void**)&pfb_tok, (size_t)T * 4)) ||
       (rc = alloc((void**)&pfb_pos, (size_t)T * 4)) || (rc = alloc((void**)&pfb_slot, (size_t)T * 4)))
@@ -823,9 +823,9 @@ int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_ar
     B200_CUDA(launch_rope_kv(pf_qkv, pf_q, L.k_cache, L.v_cache, table, rope, n, qd, kvd, c.n_kv_heads, pos0, pos_arr, slot_arr, pages_per_seq,
                              qkv_splits, qkv_stride, s));
     if (segs) {  // several prompts: causal attention per prompt over its own rows and its own slot's cache
-      for (const PrefillSeg& g : *segs)
-        B200_CUDA(launch_attn_prefill(pf_q + (size_t)g.row0 * qd, L.k_cache, L.v_cache, block_table + (size_t)g.slot * pages_per_seq,
-                                      pf_xb + (size_t)g.row0 * qd, g.n, g.pos0, c.n_heads, c.n_kv_heads, s));
+      static_assert(sizeof(PrefillSeg) == sizeof(int4), "PrefillSeg is passed to the kernel as int4 (row0, n, pos0, slot)");
+      B200_CUDA(launch_attn_prefill_segs(pf_q, L.k_cache, L.v_cache, block_table, pages_per_seq, pf_xb,
+                                         reinterpret_cast<const int4*>(segs->data()), (int)segs->size(), c.n_heads, c.n_kv_heads, s));
     } else if (!pos_arr && (use_fa_prefill || pos0 > 0)) {  // one sequence, causal: tensor-core attention, bf16 straight into the GEMM operand
       B200_CUDA(launch_attn_prefill(pf_q, L.k_cache, L.v_cache, table, pf_xb, n, pos0, c.n_heads, c.n_kv_heads, s));
     } else {                            // one row per sequence (batched decode): the split-KV decode kernel, a query per z
@@ -848,12 +848,10 @@ int Engine::forward_gemm(int n, const int32_t* tokens_dev, const int32_t* pos_ar
     B200_CUDA(launch_gemm_bf16_splitk(L.o16, d, qd, pf_xb, n, pf_proj, d, pf_proj_stride, &pf_proj_splits, s, &gemm_ws));
     { int rc = reduce_proj(n, pos_arr != nullptr); if (rc) return rc; }
     { int rc = add_rmsnorm_proj(L.ffn_norm, n, true); if (rc) return rc; }
-    int gu_splits = max_wide_splits(n);
-    const int64_t gu_stride = (int64_t)n * 2 * ff;
-    B200_CUDA(launch_gemm_bf16_splitk(L.gu16, 2 * ff, d, pf_xb, n, pf_gu, 2 * ff, gu_stride, &gu_splits, s, &gemm_ws));
-    B200_CUDA(launch_swiglu_bf16(pf_gu, pf_xb, (int64_t)n * ff, gu_splits, gu_stride, s));
+    // gate/up with SwiGLU in the GEMM's epilogue: bf16 h leaves the kernel (pf_gu only when K had to be split)
+    B200_CUDA(launch_gemm_bf16_swiglu(L.gu16, 2 * ff, d, pf_xb, n, pf_hb, ff, pf_gu, max_wide_splits(n), s, &gemm_ws));
     pf_proj_splits = max_proj_splits(n);
-    B200_CUDA(launch_gemm_bf16_splitk(L.down16, d, ff, pf_xb, n, pf_proj, d, pf_proj_stride, &pf_proj_splits, s, &gemm_ws));
+    B200_CUDA(launch_gemm_bf16_splitk(L.down16, d, ff, pf_hb, n, pf_proj, d, pf_proj_stride, &pf_proj_splits, s, &gemm_ws));
     { int rc = reduce_proj(n, pos_arr != nullptr); if (rc) return rc; }
   }
   return 0;

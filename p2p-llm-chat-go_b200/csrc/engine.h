@@ -113,7 +113,7 @@ struct Engine {
   // prefill (GEMM path) work buffers, sized for max_ctx tokens, allocated on first use
   bool pf_ready = false;
   float *pf_x = nullptr, *pf_qkv = nullptr, *pf_q = nullptr, *pf_att = nullptr, *pf_proj = nullptr, *pf_gu = nullptr;
-  uint16_t* pf_xb = nullptr;
+  uint16_t *pf_xb = nullptr, *pf_hb = nullptr;  // bf16 GEMM operands: normalised rows / attention output; ffn hidden
   float* pf_partial = nullptr;
   unsigned int* pf_counters = nullptr;
   int pf_splits = 4;

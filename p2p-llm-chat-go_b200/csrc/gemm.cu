@@ -80,8 +80,41 @@ struct GemmCfg {
   static constexpr size_t SMEM = (size_t)STAGES * STAGE + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
+// Epilogues.  GEPI_F32: Y[tok][row] fp32.  GEPI_SWIGLU: the weight rows are interleaved gate_i, up_i (the ffn
+// gate/up matrix), so a row pair sits in neighbouring TMEM lanes = neighbouring threads of the epilogue warp:
+// H[tok][row/2] = bf16(silu(gate) * up) leaves the kernel instead of two fp32 values that a separate kernel
+// would read back (same arithmetic as swiglu_bf16_kernel in prefill.cu, which stays for split-K outputs).
+enum { GEPI_F32 = 0, GEPI_SWIGLU = 1 };
+
+// One accumulator chunk: v[j] = (row, token tok0 + j) for j = 0..31 of this thread's weight row.
+template <int EPI>
+DEVINL void epi_store_chunk(const uint32_t (&v)[32], int tok0, int n_tokens, int row, bool row_ok, int lane, float* y, size_t ldy,
+                            uint16_t* h, size_t ldh) {
+  if (EPI == GEPI_F32) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+      const int tok = tok0 + j;
+      if (tok < n_tokens && row_ok) y[(size_t)tok * ldy + row] = __uint_as_float(v[j]);
+    }
+  } else {
+    // even lane = gate row, odd lane = up row.  The even lane finishes token j, the odd lane token j + 1: one
+    // exchange per token pair hands each the half it lacks.
+    const bool odd = lane & 1;
+#pragma unroll
+    for (int j = 0; j < 32; j += 2) {
+      const float x = __shfl_xor_sync(0xffffffffu, __uint_as_float(odd ? v[j] : v[j + 1]), 1);
+      const float gate = odd ? x : __uint_as_float(v[j]);
+      const float up = odd ? __uint_as_float(v[j + 1]) : x;
+      const int tok = tok0 + j + (odd ? 1 : 0);
+      if (tok < n_tokens && row_ok) h[(size_t)tok * ldh + (row >> 1)] = f32_to_bf16_bits(silu_mul_fast(gate, up));
+    }
+  }
+}
+
 struct GemmArgs {
   float* y;
+  uint16_t* h;   // GEPI_SWIGLU: bf16 output [tok][rows / 2], ldh elements between tokens
+  int ldh;
   int ldy;       // floats between consecutive tokens of y
   int n_tokens;  // valid tokens (TMA zero-fills the rest of a token tile)
   int n_rows;    // valid weight rows (the last row tile may be ragged: vocab-parallel lm_head shards)
@@ -89,7 +122,7 @@ struct GemmArgs {
   long long split_stride;  // floats between the partial outputs of consecutive K splits
 };
 
-template <int BN, int MT>
+template <int BN, int MT, int EPI>
 __global__ void __launch_bounds__(64 + 128 * MT) gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA,
                                                                    const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
   using C = GemmCfg<BN, MT>;
@@ -179,11 +212,8 @@ __global__ void __launch_bounds__(64 + 128 * MT) gemm_bf16_kernel(const __grid_c
             "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
           : "r"(taddr));
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const int tok = n0 + c * 32 + j;
-        if (tok < g.n_tokens && row < g.n_rows) g.y[(size_t)blockIdx.z * g.split_stride + (size_t)tok * g.ldy + row] = __uint_as_float(v[j]);
-      }
+      epi_store_chunk<EPI>(v, n0 + c * 32, g.n_tokens, row, row < g.n_rows, lane, g.y + (size_t)blockIdx.z * g.split_stride, (size_t)g.ldy, g.h,
+                           (size_t)g.ldh);
     }
   }
   tc_fence_before();
@@ -201,6 +231,8 @@ __global__ void __launch_bounds__(64 + 128 * MT) gemm_bf16_kernel(const __grid_c
 // partial producers run at the start of their timeline and the owner at the end of its own, so nobody waits.
 struct StreamKArgs {
   float* y;
+  uint16_t* h;        // GEPI_SWIGLU output
+  int ldh;
   int ldy, n_tokens;
   int tiles_m;        // weight-row tiles; tile index = n_tile * tiles_m + m_tile (row tile fastest: a CTA's
                       // consecutive tiles share the token tile, and a row tile's token tiles run close in time)
@@ -212,10 +244,28 @@ struct StreamKArgs {
 };
 
 constexpr size_t kWsSlot = (size_t)256 * 2 * BM;  // floats per workspace slot: [256 tokens][256 rows]
+constexpr int kFixBufs = 4;                      // staging buffers of the fix-up, in the operand ring (>= 128 KB in every configuration)
+constexpr uint32_t kFixBytes = 32 * 2 * BM * 4;  // one chunk of a partial: 32 tokens x 256 rows fp32
+
+// The work of CTA p as a sequence of segments (tile, K blocks [k0, k1)).  The producer, the MMA issuer and the
+// epilogue warps each walk their own copy.
+struct SegIter {
+  int KB, u, u_end;
+  DEVINL SegIter(const StreamKArgs& g, int p) : KB(g.kb_total) {
+    u = p * g.units;
+    u_end = min(u + g.units, g.total);
+  }
+  DEVINL bool next(int& tile, int& k0, int& k1) {
+    if (u >= u_end) return false;
+    tile = u / KB; k0 = u - tile * KB; k1 = min(KB, k0 + (u_end - u));
+    u += k1 - k0;
+    return true;
+  }
+};
 
 DEVINL void bar_sync_epi(int n) { asm volatile("bar.sync 1, %0;" ::"r"(n) : "memory"); }
 
-template <int BN>
+template <int BN, int EPI>
 __global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmA,
                                                             const __grid_constant__ CUtensorMap tmB, const StreamKArgs g) {
   using C = GemmCfg<BN, 2>;
@@ -229,9 +279,9 @@ __global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant
   uint64_t* tmem_empty = tmem_full + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty + 1);
   const uint32_t full_s = smem_u32(full), empty_s = smem_u32(empty), tfull_s = smem_u32(tmem_full), tempty_s = smem_u32(tmem_empty);
+  const uint32_t fix_s = smem_u32(bar_mem + 128);  // kFixBufs barriers of the owner's fix-up (below)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int p = blockIdx.x, KB = g.kb_total;
-  const int u_begin = p * g.units, u_end = min(u_begin + g.units, g.total);
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < C::STAGES; ++s) {
@@ -240,6 +290,7 @@ __global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant
     }
     mbar_init(tfull_s, 1);
     mbar_init(tempty_s, 8);  // one arrival per epilogue warp
+    for (int b = 0; b < kFixBufs; ++b) mbar_init(fix_s + 8 * b, 1);
     mbar_fence_init();
   }
   if (warp == 1) {
@@ -255,8 +306,8 @@ __global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant
     if (lane == 0) {  // ===== TMA producer: runs ahead of the MMAs across segment boundaries =====
       int s = 0;
       uint32_t ph = 0;
-      for (int u = u_begin; u < u_end;) {
-        const int tile = u / KB, k0 = u - tile * KB, k1 = min(KB, k0 + (u_end - u));
+      SegIter it(g, p);
+      for (int tile, k0, k1; it.next(tile, k0, k1);) {
         const int m0 = (tile % g.tiles_m) * (2 * BM), n0 = (tile / g.tiles_m) * BN;
         for (int kb = k0; kb < k1; ++kb) {
           mbar_wait(empty_s + 8 * s, ph ^ 1);
@@ -267,7 +318,6 @@ __global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant
           tma_load_2d(dst + C::AT_BYTES, &tmB, kb * BK, n0, full_s + 8 * s);
           if (++s == C::STAGES) { s = 0; ph ^= 1; }
         }
-        u += k1 - k0;
       }
     }
   } else if (warp == 1) {
@@ -275,8 +325,8 @@ __global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant
       constexpr uint32_t idesc = instr_desc(BM, BN);
       int s = 0, seg = 0;
       uint32_t ph = 0;
-      for (int u = u_begin; u < u_end; ++seg) {
-        const int tile = u / KB, k0 = u - tile * KB, k1 = min(KB, k0 + (u_end - u));
+      SegIter it(g, p);
+      for (int tile, k0, k1; it.next(tile, k0, k1); ++seg) {
         mbar_wait(tempty_s, (uint32_t)((seg & 1) ^ 1));  // the previous segment's accumulators have been read out
         tc_fence_after();
         for (int kb = k0; kb < k1; ++kb) {
@@ -293,15 +343,14 @@ __global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant
           if (++s == C::STAGES) { s = 0; ph ^= 1; }
         }
         tc_commit(tfull_s);
-        u += k1 - k0;
       }
     }
   } else {  // ===== epilogue warps 2..9 =====
     const int quad = warp & 3, mt = (warp - 2) >> 2;
     const int rloc = mt * BM + quad * 32 + lane;  // row within the 256-row tile
     int seg = 0;
-    for (int u = u_begin; u < u_end; ++seg) {
-      const int tile = u / KB, k0 = u - tile * KB, k1 = min(KB, k0 + (u_end - u));
+    SegIter it(g, p);
+    for (int tile, k0, k1; it.next(tile, k0, k1); ++seg) {
       const int m0 = (tile % g.tiles_m) * (2 * BM), n0 = (tile / g.tiles_m) * BN;
       const bool partial = k0 > 0;            // somebody else owns this tile: leave the accumulator in the workspace
       const bool owner_split = k0 == 0 && k1 < KB;  // this CTA owns the tile and others hold its later K blocks
@@ -322,6 +371,22 @@ __global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant
       }
       mbar_wait(tfull_s, (uint32_t)(seg & 1));
       tc_fence_after();
+      // The owner's fix-up: the other CTAs' partials come in through the TMA unit, 32 KB (32 tokens x 256 rows) at a
+      // time, into the operand ring — idle now: the owned segment is the last of this CTA's run and its MMAs have
+      // retired.  (Plain loads, 32 per thread in flight, took 1.6 us per 32 KB round under load: 27-50 us for one or
+      // two partials of a 256 x 256 tile.)  Item i = chunk i / n_parts of partial i % n_parts + 1.
+      const int n_chunks = min(BN / 32, (g.n_tokens - n0 + 31) / 32);
+      const int n_items = n_parts * n_chunks;
+      auto fix_issue = [&](int i) {
+        const int c = i / n_parts, q = i % n_parts + 1, b = i % kFixBufs;
+        mbar_expect_tx(fix_s + 8 * b, kFixBytes);
+        bulk_g2s(tiles + (uint32_t)b * kFixBytes, g.ws + (size_t)(p + q) * kWsSlot + (size_t)(c * 32) * (2 * BM), kFixBytes, fix_s + 8 * b,
+                 l2_policy_evict_first());
+      };
+      if (n_items > 0 && threadIdx.x == 64) {
+        asm volatile("fence.proxy.async;" ::: "memory");  // the partials were written with ordinary stores (acquired above)
+        for (int i = 0; i < min(kFixBufs, n_items); ++i) fix_issue(i);
+      }
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         if (n0 + c * 32 >= g.n_tokens) break;  // token columns past the batch hold zeros: nothing to store or reduce
@@ -341,19 +406,19 @@ __global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant
 #pragma unroll
           for (int j = 0; j < 32; ++j) w[(size_t)j * (2 * BM)] = __uint_as_float(v[j]);
         } else {
-          for (int q = 1; q <= n_parts; ++q) {  // partials in CTA order; 32 independent loads in flight, then the adds
-            const float* w = g.ws + (size_t)(p + q) * kWsSlot + (size_t)(c * 32) * (2 * BM) + rloc;
-            float t[32];
+          for (int q = 1; q <= n_parts; ++q) {  // partials in CTA order
+            const int i = c * n_parts + q - 1, b = i % kFixBufs;
+            mbar_wait(fix_s + 8 * b, (uint32_t)((i / kFixBufs) & 1));
+            const float* w = reinterpret_cast<const float*>(smem_raw + (tiles - raw) + (size_t)b * kFixBytes) + rloc;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) t[j] = __ldcg(w + (size_t)j * (2 * BM));
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + t[j]);
+            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + w[j * (2 * BM)]);
+            bar_sync_epi(256);  // everybody has read buffer b
+            if (threadIdx.x == 64 && i + kFixBufs < n_items) {
+              fence_proxy_async();
+              fix_issue(i + kFixBufs);
+            }
           }
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const int tok = n0 + c * 32 + j;
-            if (tok < g.n_tokens) g.y[(size_t)tok * g.ldy + m0 + rloc] = __uint_as_float(v[j]);
-          }
+          epi_store_chunk<EPI>(v, n0 + c * 32, g.n_tokens, m0 + rloc, true, lane, g.y, (size_t)g.ldy, g.h, (size_t)g.ldh);
         }
       }
       tc_fence_before();
@@ -368,7 +433,6 @@ __global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant
         if (threadIdx.x == 64)
           for (int j = 1; j <= n_parts; ++j) g.flags[p + j] = 0u;
       }
-      u += k1 - k0;
     }
   }
   tc_fence_before();
@@ -456,41 +520,51 @@ int env_int(const char* name, int dflt) {
   return e ? atoi(e) : dflt;
 }
 
-template <int BN, int MT>
-cudaError_t launch_bn(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y, int64_t ldy,
-                      int splits, int64_t split_stride, cudaStream_t s) {
+// Where a launch puts its result: fp32 Y (possibly split-K partials) or, for GEPI_SWIGLU, bf16 H.
+struct GemmOut {
+  float* y = nullptr;
+  int64_t ldy = 0;
+  uint16_t* h = nullptr;
+  int64_t ldh = 0;
+};
+
+template <int BN, int MT, int EPI>
+cudaError_t launch_bn(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, const GemmOut& o, int splits,
+                      int64_t split_stride, cudaStream_t s) {
   using C = GemmCfg<BN, MT>;
   CUtensorMap ma, mb;
   if (!make_map(&ma, W, (uint64_t)rows, (uint64_t)K, BM) || !make_map(&mb, X, (uint64_t)n_tokens, (uint64_t)K, BN))
     return cudaErrorInvalidValue;
-  auto kern = gemm_bf16_kernel<BN, MT>;
+  auto kern = gemm_bf16_kernel<BN, MT, EPI>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM);
   if (e != cudaSuccess) return e;
   GemmArgs g;
-  g.y = Y; g.ldy = (int)ldy; g.n_tokens = (int)n_tokens; g.n_rows = (int)rows; g.k_blocks = (int)(K / BK) / splits; g.split_stride = split_stride;
+  g.y = o.y; g.ldy = (int)o.ldy; g.h = o.h; g.ldh = (int)o.ldh;
+  g.n_tokens = (int)n_tokens; g.n_rows = (int)rows; g.k_blocks = (int)(K / BK) / splits; g.split_stride = split_stride;
   dim3 grid((unsigned)((rows + BM * MT - 1) / (BM * MT)), (unsigned)((n_tokens + BN - 1) / BN), (unsigned)splits);
   count_launch(); kern<<<grid, C::THREADS, C::SMEM, s>>>(ma, mb, g);
   return cudaGetLastError();
 }
 
-template <int BN>
-cudaError_t launch_streamk(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y, int64_t ldy,
+template <int BN, int EPI>
+cudaError_t launch_streamk(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, const GemmOut& o,
                            const GemmWorkspace& wk, cudaStream_t s) {
   using C = GemmCfg<BN, 2>;
   CUtensorMap ma, mb;
   if (!make_map(&ma, W, (uint64_t)rows, (uint64_t)K, BM) || !make_map(&mb, X, (uint64_t)n_tokens, (uint64_t)K, BN))
     return cudaErrorInvalidValue;
-  cudaError_t e = cudaFuncSetAttribute(gemm_streamk_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM);
+  cudaError_t e = cudaFuncSetAttribute(gemm_streamk_kernel<BN, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::SMEM);
   if (e != cudaSuccess) return e;
   StreamKArgs g;
-  g.y = Y; g.ldy = (int)ldy; g.n_tokens = (int)n_tokens;
+  g.y = o.y; g.ldy = (int)o.ldy; g.h = o.h; g.ldh = (int)o.ldh; g.n_tokens = (int)n_tokens;
   g.tiles_m = (int)(rows / (2 * BM));
   g.kb_total = (int)(K / BK);
-  g.total = g.tiles_m * (int)((n_tokens + BN - 1) / BN) * g.kb_total;
+  const int tiles = g.tiles_m * (int)((n_tokens + BN - 1) / BN);
+  g.total = tiles * g.kb_total;
   g.units = (g.total + wk.sm_count - 1) / wk.sm_count;
-  g.ws = wk.ws; g.flags = wk.flags;
   const int grid = (g.total + g.units - 1) / g.units;
-  count_launch(); gemm_streamk_kernel<BN><<<grid, C::THREADS, C::SMEM, s>>>(ma, mb, g);
+  g.ws = wk.ws; g.flags = wk.flags;
+  count_launch(); gemm_streamk_kernel<BN, EPI><<<grid, C::THREADS, C::SMEM, s>>>(ma, mb, g);
   return cudaGetLastError();
 }
 
@@ -521,29 +595,43 @@ bool gemm_shape_ok(int64_t rows, int64_t K, int64_t n_tokens) {
   return rows > 0 && rows % 8 == 0 && K > 0 && K % BK == 0 && n_tokens > 0 && n_tokens <= (1 << 20);
 }
 
-// Y[t*ldy + r] = sum_k X[t][k] W[r][k];  W, X bf16 (K-major, 16-byte aligned rows), Y fp32.
-cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
-                             int64_t ldy, cudaStream_t s, const GemmWorkspace* wk) {
-  // (A stream-K schedule for >= 256 tokens was built and measured in round 1: gate/up at 512 tokens 122 us vs 117 us in
-  // whole tiles, at 256 tokens 97 vs 62 — CTAs that run the same K block of neighbouring tiles in lock-step share their
-  // operand fetches in L2, staggered runs do not.  It was removed from the library; the schedule remains for <= 128
-  // tokens, where it is the faster one: launch_gemm_bf16_splitk.)
-  int splits = 1;
-  return launch_gemm_bf16_splitk(W, rows, K, X, n_tokens, Y, ldy, 0, &splits, s, wk);
+namespace {
+
+// Prefill-sized GEMMs whose 256 x 256 tiles do not come to whole waves: stream-K over all tiles.  Measured on the
+// gate/up matrix (28672 x 4096), whole tiles -> stream-K: 512 tokens (224 tiles = 1.51 waves) 119.7 -> 109 us, 1024
+// tokens 235 -> 187, 2048 tokens 437 -> 409, 4096 tokens (12.1 waves) 835 -> 726 us = 1325 TFLOP/s.  Besides the
+// balance, CTAs at different K positions contend less for L2 than a wave in lock-step (0.67 vs 0.83 us per K block).
+// Not for GEMMs of less than a wave (qkv, o, down at 512 tokens: 32-48 tiles): a CTA's extra epilogues — 5 us to
+// leave a partial, 12 us for the owner to pull one in and add it — outweigh the balance there; split-K stays.
+// (Also measured: whole tiles for the full waves and K runs only for the last, partial wave.  Every CTA then writes
+// its partial and every owner reads at the same moment, the owners wait for the slowest producer: 120-150 us at 512
+// tokens.  Not kept.)   B200_GEMM_SK256 = 0 never / 1 whenever the shape allows (experiments, tests).
+bool streamk_large_n(int64_t rows, int64_t K, int64_t n_tokens, const GemmWorkspace* wk) {
+  if (!wk || !wk->ws || !wk->flags || wk->sm_count <= 0 || kNoStreamK) return false;
+  if (n_tokens <= 128 || rows % (2 * BM) || (size_t)wk->sm_count * kWsSlot * 4 > wk->ws_bytes) return false;
+  const int ov = env_int("B200_GEMM_SK256", -1);
+  if (ov == 0) return false;
+  const int64_t tiles = (rows / (2 * BM)) * ((n_tokens + 255) / 256), rem = tiles % wk->sm_count;
+  if (ov == 1) return true;
+  return tiles >= wk->sm_count && rem != 0 && rem * 20 <= (int64_t)wk->sm_count * 17;
 }
 
-// Same, but a GEMM with too few output tiles to fill the GPU may split K: partial p is written to
-// Y + p*split_stride and the caller adds the partials (deterministically, ascending p) where it consumes Y.
-// *splits: in = maximum allowed (1..16), out = what was used.
-cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
-                                    int64_t ldy, int64_t split_stride, int* splits, cudaStream_t s, const GemmWorkspace* wk) {
+// One schedule for both epilogues.  Returns cudaErrorNotSupported when EPI needs the whole K in one CTA and the
+// schedule that fits the shape splits it (the caller then takes the fp32 path and the separate kernel).
+template <int EPI>
+cudaError_t dispatch(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, const GemmOut& o, int64_t split_stride,
+                     int* splits, cudaStream_t s, const GemmWorkspace* wk) {
   if (!gemm_shape_ok(rows, K, n_tokens)) return cudaErrorInvalidValue;
   if (streamk_small_n(rows, K, n_tokens, wk)) {
     *splits = 1;
-    if (n_tokens <= 32) return launch_streamk<32>(W, rows, K, X, n_tokens, Y, ldy, *wk, s);
-    return launch_streamk<128>(W, rows, K, X, n_tokens, Y, ldy, *wk, s);
+    if (n_tokens <= 32) return launch_streamk<32, EPI>(W, rows, K, X, n_tokens, o, *wk, s);
+    return launch_streamk<128, EPI>(W, rows, K, X, n_tokens, o, *wk, s);
   }
-  const int max_splits = *splits < 1 ? 1 : (*splits > 16 ? 16 : *splits);
+  if (streamk_large_n(rows, K, n_tokens, wk)) {
+    *splits = 1;
+    return launch_streamk<256, EPI>(W, rows, K, X, n_tokens, o, *wk, s);
+  }
+  const int max_splits = EPI != GEPI_F32 ? 1 : (*splits < 1 ? 1 : (*splits > 16 ? 16 : *splits));
   const int64_t kb = K / BK, n_sm = wk && wk->sm_count > 0 ? wk->sm_count : sm_count_now();
   const int ov = m256_override();
   // 256 x 256 tiles, one CTA per SM: the fewest operand bytes per MAC.  Taken when, with K split up to
@@ -555,7 +643,7 @@ cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, 
       if (kb % sp == 0 && kb / sp >= 24 && tiles * sp <= n_sm) use = sp;
     if (tiles * use >= (n_sm * 13) / 20 || ov == 1) {  // 96 of 148: the qkv GEMM at 512 tokens (48 tiles x 2 splits) sits exactly there
       *splits = use;
-      return launch_bn<256, 2>(W, rows, K, X, n_tokens, Y, ldy, use, split_stride, s);
+      return launch_bn<256, 2, EPI>(W, rows, K, X, n_tokens, o, use, split_stride, s);
     }
   }
   // 128-row tiles, two CTAs per SM; token tile 256 when that still yields >= 2 CTAs per SM of work, else 128
@@ -577,9 +665,53 @@ cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, 
     }
   } else if (max_splits >= 2 && tiles128 < 2 * n_sm && tiles128 >= 32 && kb % 2 == 0 && K >= 2048) use = 2;
   *splits = use;
-  if (n_tokens > 128 && tiles256 >= 2 * n_sm) return launch_bn<256, 1>(W, rows, K, X, n_tokens, Y, ldy, 1, 0, s);
-  if (n_tokens <= 32 && !kNoBn32) return launch_bn<32, 1>(W, rows, K, X, n_tokens, Y, ldy, use, split_stride, s);
-  return launch_bn<128, 1>(W, rows, K, X, n_tokens, Y, ldy, use, split_stride, s);
+  if (n_tokens > 128 && tiles256 >= 2 * n_sm) return launch_bn<256, 1, EPI>(W, rows, K, X, n_tokens, o, 1, 0, s);
+  if (n_tokens <= 32 && !kNoBn32) return launch_bn<32, 1, EPI>(W, rows, K, X, n_tokens, o, use, split_stride, s);
+  return launch_bn<128, 1, EPI>(W, rows, K, X, n_tokens, o, use, split_stride, s);
+}
+
+}  // namespace
+
+// Y[t*ldy + r] = sum_k X[t][k] W[r][k];  W, X bf16 (K-major, 16-byte aligned rows), Y fp32.
+cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
+                             int64_t ldy, cudaStream_t s, const GemmWorkspace* wk) {
+  int splits = 1;
+  return launch_gemm_bf16_splitk(W, rows, K, X, n_tokens, Y, ldy, 0, &splits, s, wk);
+}
+
+// Same, but a GEMM with too few output tiles to fill the GPU may split K: partial p is written to
+// Y + p*split_stride and the caller adds the partials (deterministically, ascending p) where it consumes Y.
+// *splits: in = maximum allowed (1..16), out = what was used.
+cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
+                                    int64_t ldy, int64_t split_stride, int* splits, cudaStream_t s, const GemmWorkspace* wk) {
+  GemmOut o;
+  o.y = Y; o.ldy = ldy;
+  return dispatch<GEPI_F32>(W, rows, K, X, n_tokens, o, split_stride, splits, s, wk);
+}
+
+// H[t*ldh + i] = bf16( silu(g) * u ),  g = X[t] . W[2i], u = X[t] . W[2i+1]  (ffn gate/up, rows interleaved).
+// The epilogue does it when one CTA holds a tile's whole K (every schedule except the balance-by-split one at
+// 33..128 tokens); otherwise fp32 partials go to `scratch` ([max_splits][n_tokens][rows]) and swiglu_bf16_kernel
+// finishes.  H must not overlap X.
+cudaError_t launch_gemm_bf16_swiglu(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, uint16_t* H, int64_t ldh,
+                                    float* scratch, int max_splits, cudaStream_t s, const GemmWorkspace* wk) {
+  if (rows % 2) return cudaErrorInvalidValue;
+  if (!env_set("B200_NO_GEMM_SWIGLU")) {
+    // would the F32 schedule split K here?  Only the <= 128-token whole-tile path does, for balance.
+    const bool balance_split = n_tokens <= 128 && max_splits >= 2 && !streamk_small_n(rows, K, n_tokens, wk);
+    if (!balance_split) {
+      GemmOut o;
+      o.h = H; o.ldh = ldh;
+      int one = 1;
+      return dispatch<GEPI_SWIGLU>(W, rows, K, X, n_tokens, o, 0, &one, s, wk);
+    }
+  }
+  if (ldh != rows / 2) return cudaErrorInvalidValue;  // the separate kernel writes H densely
+  int splits = max_splits;
+  const int64_t stride = n_tokens * rows;
+  cudaError_t e = launch_gemm_bf16_splitk(W, rows, K, X, n_tokens, scratch, rows, stride, &splits, s, wk);
+  if (e != cudaSuccess) return e;
+  return launch_swiglu_bf16(scratch, H, n_tokens * (rows / 2), splits, stride, s);
 }
 
 }  // namespace b200

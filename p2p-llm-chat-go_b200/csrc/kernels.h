@@ -212,11 +212,23 @@ cudaError_t launch_gemm_bf16(const uint16_t* W, int64_t rows, int64_t K, const u
                              int64_t ldy, cudaStream_t s, const GemmWorkspace* wk = nullptr);
 cudaError_t launch_gemm_bf16_splitk(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, float* Y,
                                     int64_t ldy, int64_t split_stride, int* splits, cudaStream_t s, const GemmWorkspace* wk = nullptr);
+// ffn gate/up (rows interleaved gate_i, up_i) with SwiGLU: H[t*ldh + i] bf16.  scratch: fp32 [max_splits][n_tokens][rows],
+// used only when the schedule splits K (33..128 tokens); H must not overlap X.
+cudaError_t launch_gemm_bf16_swiglu(const uint16_t* W, int64_t rows, int64_t K, const uint16_t* X, int64_t n_tokens, uint16_t* H, int64_t ldh,
+                                    float* scratch, int max_splits, cudaStream_t s, const GemmWorkspace* wk = nullptr);
 bool gemm_shape_ok(int64_t rows, int64_t K, int64_t n_tokens);
 
 // causal attention over a whole prompt on the tensor cores (attn_prefill.cu); out is bf16 [T][n_heads*128]
 cudaError_t launch_attn_prefill(const float* q, const uint16_t* k_cache, const uint16_t* v_cache, const int32_t* block_table, uint16_t* out,
                                 int T, int pos0, int n_heads, int n_kv_heads, cudaStream_t s);
+// several prompts in one launch: segment = (first row in q/out, rows, first position, cache slot)
+struct AttnPrefillSegs {
+  static constexpr int kMax = 16;
+  int n, pages_per_seq;
+  int4 seg[kMax];
+};
+cudaError_t launch_attn_prefill_segs(const float* q, const uint16_t* k_cache, const uint16_t* v_cache, const int32_t* block_table,
+                                     int pages_per_seq, uint16_t* out, const int4* segs, int n_segs, int n_heads, int n_kv_heads, cudaStream_t s);
 
 // batched decode (one query per sequence) on the tensor cores; bf16 output when out_bf16 is given, else a.out
 cudaError_t launch_attn_decode_batched(const AttnArgs& a, uint16_t* out_bf16, cudaStream_t s);

@@ -186,16 +186,20 @@ def test_gemm_tcgen05_m256(pkg, rows, cols, n, monkeypatch):
 # through a workspace, summed by the tile's owner in CTA order): forced on small shapes, where a tile is shared by up
 # to 32 CTAs; repeated calls must give the same bits (deterministic reduction, flags re-armed by the kernel)
 @pytest.mark.parametrize("rows,cols,n", [  # one token tile: the weight-streaming regime of batched decode (32- and 128-token variants)
-    (256, 64, 7), (512, 2048, 33), (1024, 4096, 128), (6144, 4096, 1), (28672, 4096, 8), (4096, 1024, 100), (28672, 4096, 32)])
+    (256, 64, 7), (512, 2048, 33), (1024, 4096, 128), (6144, 4096, 1), (28672, 4096, 8), (4096, 1024, 100), (28672, 4096, 32),
+    # 256-token tiles (prefill): gate/up at 512 tokens = 224 tiles on 148 CTAs; small shapes forced, ragged token counts
+    (28672, 4096, 512), (1024, 2048, 300), (512, 4096, 700), (28672, 256, 1100)])
 def test_gemm_tcgen05_streamk(pkg, rows, cols, n, monkeypatch):
     rng = np.random.default_rng(11 * rows + cols + n)
     W = random_tensor(rng, orc.BF16, rows, cols)
     X = rng.standard_normal((n, cols)).astype(np.float32)
     monkeypatch.setenv("B200_GEMM_STREAMK", "1")
+    monkeypatch.setenv("B200_GEMM_SK256", "1")
     got = pkg.gemm(orc.BF16, W, rows, cols, X)
     again = pkg.gemm(orc.BF16, W, rows, cols, X)
     assert np.array_equal(got, again)
     monkeypatch.setenv("B200_GEMM_STREAMK", "0")
+    monkeypatch.setenv("B200_GEMM_SK256", "0")
     monkeypatch.setenv("B200_NO_STREAMK", "1")
     plain = pkg.gemm(orc.BF16, W, rows, cols, X)
     Wf = orc.bf16_to_f32(W).reshape(rows, cols)
@@ -206,6 +210,45 @@ def test_gemm_tcgen05_streamk(pkg, rows, cols, n, monkeypatch):
         assert (err <= 1e-5 * budget + 1e-30).all(), float((err / (budget + 1e-30)).max())
     # against the one-CTA-per-tile schedule: same products, fp32 sums grouped differently
     assert (np.abs(got.astype(np.float64) - plain) <= 1e-5 * budget + 1e-30).all()
+
+
+def _swiglu_bf16_ref(gu):
+    """h = bf16(silu(g) * u) from fp32 gate/up columns interleaved g0, u0, g1, u1, ... (fp32 arithmetic, as the kernels)"""
+    g, u = gu[:, 0::2].astype(np.float32), gu[:, 1::2].astype(np.float32)
+    h = (g / (np.float32(1.0) + np.exp(-g, dtype=np.float32))) * u
+    return orc.f32_to_bf16(h.astype(np.float32))
+
+
+# SwiGLU in the GEMM epilogue (gate/up rows interleaved): every schedule that can carry it — 128-row tiles, 256 x 256
+# tiles, stream-K at <= 32 tokens and at >= 256 tokens (tiles cut across CTAs, partials pulled in by the owner) —
+# and the split-K fallback at 33..128 tokens; against the oracle's GEMM + fp32 SwiGLU, and against the unfused GPU path
+@pytest.mark.parametrize("rows,cols,n,env", [
+    (256, 512, 7, {}), (1024, 2048, 129, {}), (3584, 1024, 300, {"B200_GEMM_M256": "1"}), (28672, 4096, 8, {}),
+    (2048, 1024, 100, {}), (28672, 1024, 512, {}), (28672, 512, 700, {}), (4096, 512, 300, {"B200_GEMM_SK256": "1"}), (19456, 256, 2100, {})])
+def test_gemm_swiglu_epilogue(pkg, rows, cols, n, env, monkeypatch):
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    rng = np.random.default_rng(13 * rows + cols + n)
+    W = random_tensor(rng, orc.BF16, rows, cols)
+    X = rng.standard_normal((n, cols)).astype(np.float32)
+    got = pkg.gemm_swiglu(orc.BF16, W, rows, cols, X)
+    assert np.array_equal(got, pkg.gemm_swiglu(orc.BF16, W, rows, cols, X))  # deterministic (flags re-armed, fixed partial order)
+    monkeypatch.setenv("B200_NO_GEMM_SWIGLU", "1")
+    unfused = pkg.gemm_swiglu(orc.BF16, W, rows, cols, X)  # fp32 GEMM (split-K where the schedule wants it) + swiglu_bf16_kernel
+    gu = pkg.gemm(orc.BF16, W, rows, cols, X)
+    a, b, r = orc.bf16_to_f32(got), orc.bf16_to_f32(unfused), orc.bf16_to_f32(_swiglu_bf16_ref(gu))
+    Wf = orc.bf16_to_f32(W).reshape(rows, cols)
+    # the same products everywhere; fp32 sums are grouped differently where K is cut (split-K, stream-K), and
+    # |d h| <= |silu'(g)| |u| dg + |silu(g)| du with dg, du <= 1e-5 x the GEMM's error budget, plus the bf16 rounding of h
+    tol = 2.0 ** -7 * np.abs(r) + 1e-5 * ((np.abs(X) @ np.abs(Wf[0::2]).T) * 1.1 * (np.abs(gu[:, 1::2]) + 1) +
+                                          (np.abs(X) @ np.abs(Wf[1::2]).T) * (np.abs(gu[:, 0::2]) + 1))
+    assert (np.abs(b - r) <= tol).all(), float(np.abs(b - r).max())
+    assert (np.abs(a - r) <= tol).all(), float(np.abs(a - r).max())
+    assert (got == unfused).mean() > 0.98
+    if rows * cols * n <= 1 << 31:
+        want = _swiglu_bf16_ref(orc.matmul(orc.BF16, W, rows, cols, X, mode=1).astype(np.float32))
+        assert (np.abs(a - orc.bf16_to_f32(want)) <= tol).all()
+        assert (got == want).mean() > 0.98
 
 
 def test_gemm_rejects_bad_shapes(pkg):
