@@ -244,8 +244,7 @@ struct StreamKArgs {
 };
 
 constexpr size_t kWsSlot = (size_t)256 * 2 * BM;  // floats per workspace slot: [256 tokens][256 rows]
-constexpr int kFixBufs = 4;                      // staging buffers of the fix-up, in the operand ring (>= 128 KB in every configuration)
-constexpr uint32_t kFixBytes = 32 * 2 * BM * 4;  // one chunk of a partial: 32 tokens x 256 rows fp32
+constexpr uint32_t kFixBytes = 32 * 2 * BM * 4;  // one chunk of a partial: 32 tokens x 256 rows fp32 (the fix-up stages them in the operand ring)
 
 // The work of CTA p as a sequence of segments (tile, K blocks [k0, k1)).  The producer, the MMA issuer and the
 // epilogue warps each walk their own copy.
@@ -269,6 +268,7 @@ template <int BN, int EPI>
 __global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant__ CUtensorMap tmA,
                                                             const __grid_constant__ CUtensorMap tmB, const StreamKArgs g) {
   using C = GemmCfg<BN, 2>;
+  constexpr int kFixBufs = (int)(C::STAGES * C::STAGE / kFixBytes);  // 5 (32-token tiles) or 6: the more partial chunks in flight, the shorter the fix-up (4 -> 5: 107 -> 105 us)
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t tiles = (raw + 1023u) & ~1023u;

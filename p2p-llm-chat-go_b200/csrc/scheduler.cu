@@ -271,7 +271,14 @@ void Engine::admit_batch(const std::vector<Request*>& rs, const std::vector<int>
     cu(cudaMemcpyAsync(pfb_pos, pos.data(), (size_t)N * 4, cudaMemcpyHostToDevice, stream), "batched prefill: positions");
     cu(cudaMemcpyAsync(pfb_slot, slot.data(), (size_t)N * 4, cudaMemcpyHostToDevice, stream), "batched prefill: slots");
   }
+  const bool tr_ = getenv("B200_SCHED_TRACE") != nullptr;  // debug: host-side timeline of a batched admission on stderr (adds a stream sync)
+  auto now_ = [] { return std::chrono::steady_clock::now(); };
+  auto us_ = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) { return std::chrono::duration<double, std::micro>(b - a).count(); };
+  const auto t_a = now_();
   if (!rc) rc = forward_gemm(N, pfb_tok, pfb_pos, nullptr, pfb_slot, 0, &segs);
+  const auto t_b = now_();
+  if (tr_) cudaStreamSynchronize(stream);
+  const auto t_c = now_();
   // the residual stream of every row now sits in pf_x (+ the last down projection still to be added): hand each
   // prompt's last row to the batch-1 tail
   const float* proj_src = pf_proj_src;
@@ -314,6 +321,7 @@ void Engine::admit_batch(const std::vector<Request*>& rs, const std::vector<int>
     if (q.token == cfg.eos_token) finish_request(s, 0, 1);
     else if (q.delivered >= q.max_out) finish_request(s, 0, 2);
   }
+  if (tr_) fprintf(stderr, "SCHED admit_batch B=%d N=%d prep %.0f us, enqueue %.0f us, gpu-wait %.0f us, tails %.0f us\n", B, N, us_(t_load, t_a), us_(t_a, t_b), us_(t_b, t_c), us_(t_c, now_()));
 }
 
 // The only active sequence decodes on the batch-1 graph.  Returns when it finishes, is cancelled, or another
