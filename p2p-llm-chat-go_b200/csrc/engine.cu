@@ -405,7 +405,8 @@ int Engine::dump_trace() {
   if (!trace_dev || !path || trace_names.empty()) return 0;
   std::vector<unsigned long long> t(trace_names.size() * 4);
   B200_CUDA(cudaMemcpy(t.data(), trace_dev, t.size() * 8, cudaMemcpyDeviceToHost));
-  FILE* f = fopen(path, "w");
+  const std::string file = tp_size > 1 ? std::string(path) + ".r" + std::to_string(tp_rank) : std::string(path);  // one file per rank
+  FILE* f = fopen(file.c_str(), "w");
   if (!f) return 0;
   for (size_t i = 0; i < trace_names.size(); ++i)
     fprintf(f, "%zu %s %llu %llu %llu %llu\n", i, trace_names[i].c_str(), t[4 * i], t[4 * i + 1], t[4 * i + 2], t[4 * i + 3]);

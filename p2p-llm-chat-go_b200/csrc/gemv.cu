@@ -141,19 +141,6 @@ DEVINL void gemv_body(const GemvArgs& a, int cta, int n_ctas) {
   }
   if (EPI == EPI_LOGITS && lane == 0 && my_units > 0) atomicMax(a.argmax_key, argmax_key(bestv, besti));
   if (a.trace != nullptr && threadIdx.x == 0) atomicMax(a.trace + 3, global_timer_ns());
-  if (EPI == EPI_TP_PUSH) {  // when the last CTA of the grid has pushed, raise this rank's flag on every peer
-    const TpLink* t = a.tp;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      __threadfence_system();
-      if (atomicAdd(t->ticket, 1u) == (unsigned int)n_ctas - 1) {
-        *t->ticket = 0u;
-        __threadfence_system();
-        const unsigned int seq = *t->epoch * (unsigned int)t->per_step + (unsigned int)a.tp_index + 1u;
-        for (int p = 0; p < t->size; ++p) st_release_sys(t->peer_flags[p] + (a.tp_index & 1) * kMaxTp + t->rank, seq);
-      }
-    }
-  }
   if (a.next_bytes != 0 && lane == 0) {  // this warp's slice of the next kernel's weights -> L2
     const unsigned long long per = ((a.next_bytes / (unsigned long long)twarps) + 127ull) & ~127ull;
     unsigned long long off = per * (unsigned long long)gwarp;

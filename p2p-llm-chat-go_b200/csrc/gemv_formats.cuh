@@ -56,42 +56,42 @@ DEVINL float rms_inv(const GemvArgs& a, float* red, int warp, int lane) {
 // Each policy states: R rows per unit, CHUNK columns per stage, the stage layout, how lane 0 issues the
 // bulk copies of a stage, how the block prepares x in shared memory, and how a warp consumes a stage.
 
-DEVINL unsigned int ld_acquire_sys(const unsigned int* p) {
-  unsigned int v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+DEVINL uint4 ld_relaxed_sys_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
   return v;
 }
-DEVINL void st_release_sys(unsigned int* p, unsigned int v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+DEVINL void st_relaxed_sys_v2(void* p, float v, unsigned int tag) {
+  asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(tag) : "memory");
 }
 
-// Consumer half of the fused all-reduce (see TpLink): wait until every rank's partial of all-reduce
-// `tp_index` has landed in this GPU's receive buffer, x_new = x + sum over ranks (fixed order, so every rank
-// computes the same bits), CTA 0 publishes x_new, and the RMS-normalised x_new goes to shared memory in the
-// GEMV's permuted layout.  A wait that exceeds ~2 s sets the error flag and carries on (no hang).
+// Consumer half of the fused all-reduce (see TpLink): poll every rank's partial of all-reduce `tp_index` in this
+// GPU's receive buffer until each element carries this exchange's number, x_new = x + sum over ranks (fixed order, so
+// every rank computes the same bits), CTA 0 publishes x_new, and the RMS-normalised x_new goes to shared memory in
+// the GEMV's permuted layout.  A wait that exceeds ~2 s sets the error flag and carries on (no hang).
 template <int NW>
 DEVINL void tp_prologue(float* xs, const GemvArgs& a, float* red, int warp, int lane) {
   const TpLink* t = a.tp;
   const int buf = a.tp_index & 1, size = t->size, d = a.K;
   const unsigned int seq = *t->epoch * (unsigned int)t->per_step + (unsigned int)a.tp_index + 1u;
-  if (warp == 0 && lane < size) {
-    const unsigned int* f = t->flags + buf * kMaxTp + lane;
-    const long long t0 = clock64();
-    while ((int)(ld_acquire_sys(f) - seq) < 0) {
-      if (clock64() - t0 > 4000000000ll) {
-        *t->error = 1;
-        break;
-      }
-    }
-  }
-  __syncthreads();
   const float* rv = t->recv[buf];
   float ss = 0.f;
+  const long long t0 = clock64();
   for (int k = threadIdx.x * 4; k < d; k += NW * 32 * 4) {
     float4 v = __ldcg(reinterpret_cast<const float4*>(a.x + k));
     for (int s = 0; s < size; ++s) {
-      const float4 p = __ldcg(reinterpret_cast<const float4*>(rv + (size_t)s * d + k));
-      v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
+      const float* e = rv + ((size_t)s * d + k) * 2;  // four {value, seq} pairs
+      uint4 p0, p1;
+      for (;;) {
+        p0 = ld_relaxed_sys_v4(e);
+        p1 = ld_relaxed_sys_v4(e + 4);
+        if (p0.y == seq && p0.w == seq && p1.y == seq && p1.w == seq) break;
+        if (clock64() - t0 > 4000000000ll) {
+          *t->error = 1;
+          break;
+        }
+      }
+      v.x += __uint_as_float(p0.x); v.y += __uint_as_float(p0.z); v.z += __uint_as_float(p1.x); v.w += __uint_as_float(p1.z);
     }
     if (blockIdx.x == 0) *reinterpret_cast<float4*>(a.x_out + k) = v;
     ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
@@ -535,9 +535,10 @@ DEVINL void epilogue(const GemvArgs& a, int unit, int lane, const float* acc, fl
   } else if (EPI == EPI_TP_PUSH) {  // lane p sends this unit's partial sums to peer p over NVLink
     const TpLink* t = a.tp;
     if (lane < t->size) {
-      float* dst = t->peer_recv[a.tp_index & 1][lane] + (size_t)t->rank * t->d + row0;
+      const unsigned int seq = *t->epoch * (unsigned int)t->per_step + (unsigned int)a.tp_index + 1u;
+      float* dst = t->peer_recv[a.tp_index & 1][lane] + ((size_t)t->rank * t->d + row0) * 2;
 #pragma unroll
-      for (int r = 0; r < R; ++r) dst[r] = acc[r];
+      for (int r = 0; r < R; ++r) st_relaxed_sys_v2(dst + 2 * r, acc[r], seq);
     }
   } else if (EPI == EPI_RESID) {  // acc already holds residual + W.x (the residual was fetched at the start of the unit)
     if (lane == 0) {

@@ -21,13 +21,17 @@ enum { T_F32 = 0, T_F16 = 1, T_Q4_K = 12, T_Q6_K = 14, T_BF16 = 30 };
 enum { PRO_COPY = 0, PRO_RMSNORM = 1, PRO_TP_RMSNORM = 2 };
 enum { EPI_STORE = 0, EPI_RESID = 1, EPI_SWIGLU = 2, EPI_QKV = 3, EPI_LOGITS = 4, EPI_TP_PUSH = 5 };
 
-// Tensor-parallel link of one rank (device-resident): peers' receive buffers and flags, mapped over NVLink.
+// Tensor-parallel link of one rank (device-resident): peers' receive buffers, mapped over NVLink.
 // The row-parallel GEMVs (o, down) push their partial sums straight into every peer's buffer from their
-// epilogue (EPI_TP_PUSH); the next GEMV's prologue (PRO_TP_RMSNORM) waits for the flags, adds the partials in
-// rank order to the residual stream and normalises — the all-reduce costs no launch of its own.
+// epilogue (EPI_TP_PUSH); the next GEMV's prologue (PRO_TP_RMSNORM) adds the partials in rank order to the residual
+// stream and normalises — the all-reduce costs no launch of its own.  Every element is an 8-byte pair
+// {value, sequence number of the exchange}, written with one 8-byte store (which arrives whole), so the consumer
+// needs no separate flag: it polls the elements themselves until they carry its exchange's number.  (The first
+// version pushed plain floats, then system-scope fence -> CTA ticket -> fence -> one release store per peer: ~11 us
+// from the last partial sum to the consumer at TP-2, and a release store per peer on top at TP-8.)
 constexpr int kMaxTp = 8;
 struct TpLink {
-  float* peer_recv[2][kMaxTp];      // [buffer][peer] -> that peer's recv buffer ([size][d] floats, slot = source rank)
+  float* peer_recv[2][kMaxTp];      // [buffer][peer] -> that peer's recv buffer ([size][d] {float, seq} pairs, slot = source rank)
   unsigned int* peer_flags[kMaxTp]; // -> that peer's flags [2][kMaxTp] (sequence number per source rank)
   float* recv[2];                   // this rank's own buffers
   unsigned int* flags;              // this rank's own flags

@@ -314,16 +314,20 @@ __global__ void tp_push_kernel(const TpBatch b, const float* src, long long coun
     const float4 v = __ldcg(reinterpret_cast<const float4*>(src) + i);
     for (int p = 0; p < b.size; ++p) reinterpret_cast<float4*>(b.peer_recv[buf][p] + (size_t)b.rank * b.slot_floats)[i] = v;
   }
+  __shared__ int last_cta;
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence_system();
-    if (atomicAdd(b.ticket, 1u) == gridDim.x - 1) {
+    const bool last = atomicAdd(b.ticket, 1u) == gridDim.x - 1;
+    if (last) {
       *b.ticket = 0u;
       __threadfence_system();
-      for (int p = 0; p < b.size; ++p)
-        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(b.peer_flags[p] + buf * kMaxTp + b.rank), "r"(seq) : "memory");
     }
+    last_cta = last ? 1 : 0;
   }
+  __syncthreads();
+  if (last_cta && threadIdx.x < b.size)  // one lane per peer (see gemv.cu)
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(b.peer_flags[threadIdx.x] + buf * kMaxTp + b.rank), "r"(seq) : "memory");
 }
 
 }  // namespace

@@ -123,12 +123,13 @@ int Engine::tp_setup_link() {
   memset(&L, 0, sizeof L);
   L.rank = tp_rank; L.size = n; L.d = d; L.per_step = 2 * cfg.n_layers;
   unsigned int* small = nullptr;  // flags[2][kMaxTp] | epoch | ticket | error
-  B200_CUDA(cudaMalloc((void**)&L.recv[0], (size_t)n * d * 4));
-  B200_CUDA(cudaMalloc((void**)&L.recv[1], (size_t)n * d * 4));
+  // every float travels with its exchange's sequence number beside it (kernels.h: TpLink), hence 8 bytes per element
+  B200_CUDA(cudaMalloc((void**)&L.recv[0], (size_t)n * d * 8));
+  B200_CUDA(cudaMalloc((void**)&L.recv[1], (size_t)n * d * 8));
   B200_CUDA(cudaMalloc((void**)&small, 256));
   allocs.push_back(L.recv[0]); allocs.push_back(L.recv[1]); allocs.push_back(small);
-  B200_CUDA(cudaMemset(L.recv[0], 0, (size_t)n * d * 4));
-  B200_CUDA(cudaMemset(L.recv[1], 0, (size_t)n * d * 4));
+  B200_CUDA(cudaMemset(L.recv[0], 0, (size_t)n * d * 8));
+  B200_CUDA(cudaMemset(L.recv[1], 0, (size_t)n * d * 8));
   B200_CUDA(cudaMemset(small, 0, 256));
   L.flags = small; L.epoch = small + 2 * kMaxTp; L.ticket = small + 2 * kMaxTp + 1; L.error = (int*)(small + 2 * kMaxTp + 2);
   // batched decode: [tp][kTpBatchRows * d] per buffer; flags [2][kMaxTp] and a ticket further into `small`
