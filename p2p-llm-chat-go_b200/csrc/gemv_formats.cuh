@@ -65,35 +65,77 @@ DEVINL void st_relaxed_sys_v2(void* p, float v, unsigned int tag) {
   asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(__float_as_uint(v)), "r"(tag) : "memory");
 }
 
-// Consumer half of the fused all-reduce (see TpLink): poll every rank's partial of all-reduce `tp_index` in this
-// GPU's receive buffer until each element carries this exchange's number, x_new = x + sum over ranks (fixed order, so
-// every rank computes the same bits), CTA 0 publishes x_new, and the RMS-normalised x_new goes to shared memory in
-// the GEMV's permuted layout.  A wait that exceeds ~2 s sets the error flag and carries on (no hang).
+DEVINL uint4 ld_relaxed_gpu_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.gpu.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+DEVINL void st_relaxed_gpu_v4(void* p, uint4 v) {
+  asm volatile("st.relaxed.gpu.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// Consumer half of the fused all-reduce (see TpLink), in two phases so that no CTA reads more than it must:
+//  1. the residual stream is cut into slices of 64 elements, slice i belongs to CTA i (mod grid): 16 of its threads
+//     poll the `size` partials of their four elements in this GPU's receive buffer (all loads in flight together)
+//     until every pair carries this exchange's number, add them to x in rank order (fixed order: every rank computes
+//     the same bits), store x_new and publish it as {value, seq} pairs in a local buffer;
+//  2. every CTA polls that local buffer for all d elements (8 bytes each instead of 8 x size), and the RMS-normalised
+//     x_new goes to shared memory in the GEMV's permuted layout.
+// (One phase — every CTA polling all partials — read 512 KB per CTA at TP-8, d = 8192: 13.4 us of prologue.)
+// A wait that exceeds ~2 s sets the error flag and carries on (no hang).
 template <int NW>
 DEVINL void tp_prologue(float* xs, const GemvArgs& a, float* red, int warp, int lane) {
   const TpLink* t = a.tp;
   const int buf = a.tp_index & 1, size = t->size, d = a.K;
   const unsigned int seq = *t->epoch * (unsigned int)t->per_step + (unsigned int)a.tp_index + 1u;
   const float* rv = t->recv[buf];
-  float ss = 0.f;
+  float* xsum = t->xsum[buf];
   const long long t0 = clock64();
-  for (int k = threadIdx.x * 4; k < d; k += NW * 32 * 4) {
-    float4 v = __ldcg(reinterpret_cast<const float4*>(a.x + k));
-    for (int s = 0; s < size; ++s) {
-      const float* e = rv + ((size_t)s * d + k) * 2;  // four {value, seq} pairs
-      uint4 p0, p1;
-      for (;;) {
-        p0 = ld_relaxed_sys_v4(e);
-        p1 = ld_relaxed_sys_v4(e + 4);
-        if (p0.y == seq && p0.w == seq && p1.y == seq && p1.w == seq) break;
-        if (clock64() - t0 > 4000000000ll) {
+  if (threadIdx.x < 16) {
+    for (int sl = blockIdx.x; sl < d / 64; sl += gridDim.x) {
+      const int k = sl * 64 + threadIdx.x * 4;
+      float4 v = __ldcg(reinterpret_cast<const float4*>(a.x + k));
+      uint4 p0[kMaxTp], p1[kMaxTp];
+      unsigned int pending = (1u << size) - 1u;
+      while (pending) {
+#pragma unroll
+        for (int s = 0; s < kMaxTp; ++s)
+          if ((pending >> s) & 1u) {
+            const float* e = rv + ((size_t)s * d + k) * 2;  // four {value, seq} pairs
+            p0[s] = ld_relaxed_sys_v4(e);
+            p1[s] = ld_relaxed_sys_v4(e + 4);
+          }
+#pragma unroll
+        for (int s = 0; s < kMaxTp; ++s)
+          if (((pending >> s) & 1u) && p0[s].y == seq && p0[s].w == seq && p1[s].y == seq && p1[s].w == seq) pending &= ~(1u << s);
+        if (pending && clock64() - t0 > 4000000000ll) {
           *t->error = 1;
           break;
         }
       }
-      v.x += __uint_as_float(p0.x); v.y += __uint_as_float(p0.z); v.z += __uint_as_float(p1.x); v.w += __uint_as_float(p1.z);
+#pragma unroll
+      for (int s = 0; s < kMaxTp; ++s)
+        if (s < size) {
+          v.x += __uint_as_float(p0[s].x); v.y += __uint_as_float(p0[s].z); v.z += __uint_as_float(p1[s].x); v.w += __uint_as_float(p1[s].z);
+        }
+      *reinterpret_cast<float4*>(a.x_out + k) = v;
+      st_relaxed_gpu_v4(xsum + 2 * k, make_uint4(__float_as_uint(v.x), seq, __float_as_uint(v.y), seq));
+      st_relaxed_gpu_v4(xsum + 2 * k + 4, make_uint4(__float_as_uint(v.z), seq, __float_as_uint(v.w), seq));
     }
-    if (blockIdx.x == 0) *reinterpret_cast<float4*>(a.x_out + k) = v;
+  }
+  float ss = 0.f;
+  for (int k = threadIdx.x * 4; k < d; k += NW * 32 * 4) {
+    uint4 p0, p1;
+    for (;;) {
+      p0 = ld_relaxed_gpu_v4(xsum + 2 * k);
+      p1 = ld_relaxed_gpu_v4(xsum + 2 * k + 4);
+      if (p0.y == seq && p0.w == seq && p1.y == seq && p1.w == seq) break;
+      if (clock64() - t0 > 4000000000ll) {
+        *t->error = 1;
+        break;
+      }
+    }
+    const float4 v = make_float4(__uint_as_float(p0.x), __uint_as_float(p0.z), __uint_as_float(p1.x), __uint_as_float(p1.z));
     ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
     const int idx = (k & ~255) + ((k >> 2) & 1) * 128 + ((k & 255) >> 3) * 4;
     *reinterpret_cast<float4*>(xs + idx) = v;

@@ -34,6 +34,7 @@ struct TpLink {
   float* peer_recv[2][kMaxTp];      // [buffer][peer] -> that peer's recv buffer ([size][d] {float, seq} pairs, slot = source rank)
   unsigned int* peer_flags[kMaxTp]; // -> that peer's flags [2][kMaxTp] (sequence number per source rank)
   float* recv[2];                   // this rank's own buffers
+  float* xsum[2];                   // local: the reduced residual stream as {value, seq} pairs, [buffer][d] (tp_prologue, phase 2)
   unsigned int* flags;              // this rank's own flags
   unsigned int* epoch;              // decode steps completed (advanced by finish_step)
   unsigned int* ticket;             // CTA ticket of the pushing kernel (self-resetting)

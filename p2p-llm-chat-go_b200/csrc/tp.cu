@@ -131,6 +131,12 @@ int Engine::tp_setup_link() {
   B200_CUDA(cudaMemset(L.recv[0], 0, (size_t)n * d * 8));
   B200_CUDA(cudaMemset(L.recv[1], 0, (size_t)n * d * 8));
   B200_CUDA(cudaMemset(small, 0, 256));
+  if (d % 64) { set_error("tensor parallelism needs d_model %% 64 == 0 (got %d)", d); return B200_EINVAL; }
+  for (int b = 0; b < 2; ++b) {
+    B200_CUDA(cudaMalloc((void**)&L.xsum[b], (size_t)d * 8));
+    allocs.push_back(L.xsum[b]);
+    B200_CUDA(cudaMemset(L.xsum[b], 0, (size_t)d * 8));
+  }
   L.flags = small; L.epoch = small + 2 * kMaxTp; L.ticket = small + 2 * kMaxTp + 1; L.error = (int*)(small + 2 * kMaxTp + 2);
   // batched decode: [tp][kTpBatchRows * d] per buffer; flags [2][kMaxTp] and a ticket further into `small`
   TpBatch& Bt = tp_batch;
