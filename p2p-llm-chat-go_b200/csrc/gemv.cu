@@ -263,13 +263,26 @@ using S0q6 = GemvCfg<16, 2, 1>;
 
 }  // namespace
 
+// 4 rows per unit amortise the activation loads best and keep the most bytes in flight per warp; 2-row units give a
+// matrix with few rows a unit for every warp of every SM.  Which wins was measured per format (B200_GEMV_WIDE_PCT =
+// 4-row units when they cover at least that percentage of the 16 x SMs warps): 16-bit weights 60 % (8B qkv, 6144 rows,
+// 2.685 -> 2.672 ms per token; o / down, 4096 rows = 43 %: 2-row units, 4-row ones cost 2 %), k-quants 40 % (4-row
+// units everywhere: 1.438 -> 1.415 ms).  Where it matters most is the 70B model at TP-8, whose o and down keep all 8192
+// rows with K cut to 1024 / 3584: 2-row units meant two rounds of short units per warp (o 9.0 us, down 10.9 us per
+// layer), 4-row units one round (2.7 / 5.9 us): 189 -> 205 tok/s.
+bool wide_units(int wtype, int64_t n_rows, int sm_count) {
+  static const int env_pct = getenv("B200_GEMV_WIDE_PCT") ? atoi(getenv("B200_GEMV_WIDE_PCT")) : 0;
+  const int pct = env_pct > 0 ? env_pct : ((wtype == T_Q4_K || wtype == T_Q6_K) ? 40 : 60);
+  return (n_rows / 4) * 100 >= (int64_t)sm_count * 16 * pct;
+}
+
 // q,k rows in Q4_K and v rows in Q6_K (the Q4_K_M recipe's "more bits" layers), RMS-norm prologue, RoPE / KV-append
 // epilogue, one launch.  Other combinations: cudaErrorNotSupported (the caller launches them one after the other).
 cudaError_t launch_gemv_dual_qkv(int type_a, const GemvArgs& a, int type_b, const GemvArgs& b, cudaStream_t s, bool pdl, int sm_count) {
   static const bool off = getenv("B200_NO_DUAL_QKV") != nullptr;
   if (type_a != T_Q4_K || type_b != T_Q6_K || off) return cudaErrorNotSupported;
   if (!gemv_shape_ok(type_a, a.N, a.K, EPI_QKV) || !gemv_shape_ok(type_b, b.N, b.K, EPI_QKV)) return cudaErrorInvalidValue;
-  const bool wide = (a.N / 4) >= sm_count * 16;
+  const bool wide = wide_units(type_a, a.N, sm_count);
   if (wide) return launch_dual_t<FmtQ4K<4, S0r4>, FmtQ6K<S0q6>, PRO_RMSNORM, EPI_QKV>(a, b, s, pdl, sm_count);
   return launch_dual_t<FmtQ4K<2, S0r2>, FmtQ6K<S0q6>, PRO_RMSNORM, EPI_QKV>(a, b, s, pdl, sm_count);
 }
@@ -305,9 +318,7 @@ cudaError_t launch_by_width(bool wide, int pro, int epi, const GemvArgs& a, cuda
 
 cudaError_t launch_gemv(int wtype, int pro, int epi, const GemvArgs& a, cudaStream_t s, bool pdl, int sm_count) {
   if (!gemv_shape_ok(wtype, a.N, a.K, epi)) return cudaErrorInvalidValue;
-  // 4 rows per unit amortise the activation loads best; matrices with fewer than one such unit per warp
-  // (o / down / qkv: 4096-6144 rows) use 2-row units so that every warp of every SM streams something
-  const bool wide = (a.N / 4) >= sm_count * 16;
+  const bool wide = wide_units(wtype, a.N, sm_count);
   switch (wtype) {
     case T_BF16:
       if (a.K % 512 == 0) return launch_by_width<FmtBF16<512, 4, S0r4>, FmtBF16<512, 2, S0r2>>(wide, pro, epi, a, s, pdl, sm_count);
