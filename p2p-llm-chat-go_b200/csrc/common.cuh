@@ -92,9 +92,11 @@ DEVINL uint16_t f32_to_bf16_bits(float f) {  // RNE, same integer recipe as the 
   return (uint16_t)(u >> 16);
 }
 DEVINL float bf16_round(float f) { return __uint_as_float((uint32_t)f32_to_bf16_bits(f) << 16); }
-// silu(g) * u for the tensor-core (bf16) path: ex2.approx + approximate divide, ~1e-6 relative, far inside the bf16
-// rounding that follows; in a GEMM epilogue the accurate expf / divide (~40 instructions) sat on the CTA's critical path.
-DEVINL float silu_mul_fast(float g, float u) { return __fdividef(g, 1.0f + __expf(-g)) * u; }
+// silu(g) * u of the tensor-core (bf16) path, the oracle's formula operation for operation (expf, IEEE divide).  The
+// approximate forms (__expf, __fdividef: ~1e-6 relative) save 0.1 ms of a 9.5 ms prefill, but at the BASELINE
+// configuration the Q4_K_M greedy continuation then left the oracle's at token 52 on a near-tie (the tolerance test
+// still passed); with these it is identical for all 128 tokens, so they stay.
+DEVINL float silu_mul(float g, float u) { return (g / (1.0f + expf(-g))) * u; }
 DEVINL float fp16_bits_to_f32(uint16_t h) { return __half2float(__ushort_as_half(h)); }
 
 DEVINL float warp_sum(float v) {

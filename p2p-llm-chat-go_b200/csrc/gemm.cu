@@ -106,7 +106,7 @@ DEVINL void epi_store_chunk(const uint32_t (&v)[32], int tok0, int n_tokens, int
       const float gate = odd ? x : __uint_as_float(v[j]);
       const float up = odd ? __uint_as_float(v[j + 1]) : x;
       const int tok = tok0 + j + (odd ? 1 : 0);
-      if (tok < n_tokens && row_ok) h[(size_t)tok * ldh + (row >> 1)] = f32_to_bf16_bits(silu_mul_fast(gate, up));
+      if (tok < n_tokens && row_ok) h[(size_t)tok * ldh + (row >> 1)] = f32_to_bf16_bits(silu_mul(gate, up));
     }
   }
 }

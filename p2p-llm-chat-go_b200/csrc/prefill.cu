@@ -257,7 +257,7 @@ __global__ void swiglu_bf16_kernel(const float* gu, uint16_t* h, int64_t n_pairs
       const float2 w = *reinterpret_cast<const float2*>(gu + (size_t)sp * part_stride + 2 * i);
       v.x += w.x; v.y += w.y;
     }
-    h[i] = f32_to_bf16_bits(silu_mul_fast(v.x, v.y));  // as the GEMM epilogue (gemm.cu), so every schedule gives the same h
+    h[i] = f32_to_bf16_bits(silu_mul(v.x, v.y));  // as the GEMM epilogue (gemm.cu), so every schedule gives the same h
   }
 }
 
