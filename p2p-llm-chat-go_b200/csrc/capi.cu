@@ -796,7 +796,8 @@ int b200_bench_kernel(b200_engine* h, const char* which, int iters, float* ms, i
       if (i == 0) B200_CUDA(cudaEventRecord(e0, e->stream));
       if (m == "down" || m == "attn_output") {  // as the engine calls them
         splits = 8;
-        B200_CUDA(launch_gemm_bf16_splitk(W, rows, K, xb.as<uint16_t>(), n, yb.as<float>(), rows, n * rows, &splits, e->stream));
+        B200_CUDA(launch_gemm_bf16_splitk(W, rows, K, xb.as<uint16_t>(), n, yb.as<float>(), rows, n * rows, &splits, e->stream,
+                                          e->gemm_ws.ws ? &e->gemm_ws : nullptr));
       } else {
         B200_CUDA(launch_gemm_bf16(W, rows, K, xb.as<uint16_t>(), n, yb.as<float>(), rows, e->stream, e->gemm_ws.ws ? &e->gemm_ws : nullptr));
       }

@@ -112,6 +112,7 @@ DEVINL void epi_store_chunk(const uint32_t (&v)[32], int tok0, int n_tokens, int
 }
 
 struct GemmArgs {
+  int n_fast;     // grid.x = token tiles, grid.y = weight-row tiles (else the other way round)
   float* y;
   uint16_t* h;   // GEPI_SWIGLU: bf16 output [tok][rows / 2], ldh elements between tokens
   int ldh;
@@ -138,7 +139,9 @@ __global__ void __launch_bounds__(64 + 128 * MT) gemm_bf16_kernel(const __grid_c
   const uint32_t full_s = smem_u32(full), empty_s = smem_u32(empty), tfull_s = smem_u32(tmem_full);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.x * (BM * MT), n0 = blockIdx.y * BN;
+  // n_fast: the token tile is the fastest grid dimension, so the CTAs of a wave cover few weight-row tiles x all token
+  // tiles and share the weight fetches in L2 (many token tiles: batched prefill); else the row tile is fastest
+  const int m0 = (g.n_fast ? blockIdx.y : blockIdx.x) * (BM * MT), n0 = (g.n_fast ? blockIdx.x : blockIdx.y) * BN;
   const int kb0 = blockIdx.z * g.k_blocks;  // split-K: this CTA's first K block
 
   if (threadIdx.x == 0) {
@@ -234,6 +237,7 @@ struct StreamKArgs {
   uint16_t* h;        // GEPI_SWIGLU output
   int ldh;
   int ldy, n_tokens;
+  int tiles_n, n_fast;  // token tiles; n_fast: tile index = m_tile * tiles_n + n_tile, else n_tile * tiles_m + m_tile
   int tiles_m;        // weight-row tiles; tile index = n_tile * tiles_m + m_tile (row tile fastest: a CTA's
                       // consecutive tiles share the token tile, and a row tile's token tiles run close in time)
   int kb_total;       // K blocks (of 64) per tile
@@ -308,7 +312,7 @@ __global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant
       uint32_t ph = 0;
       SegIter it(g, p);
       for (int tile, k0, k1; it.next(tile, k0, k1);) {
-        const int m0 = (tile % g.tiles_m) * (2 * BM), n0 = (tile / g.tiles_m) * BN;
+        const int m0 = (g.n_fast ? tile / g.tiles_n : tile % g.tiles_m) * (2 * BM), n0 = (g.n_fast ? tile % g.tiles_n : tile / g.tiles_m) * BN;
         for (int kb = k0; kb < k1; ++kb) {
           mbar_wait(empty_s + 8 * s, ph ^ 1);
           const uint32_t dst = tiles + s * C::STAGE;
@@ -351,7 +355,7 @@ __global__ void __launch_bounds__(320) gemm_streamk_kernel(const __grid_constant
     int seg = 0;
     SegIter it(g, p);
     for (int tile, k0, k1; it.next(tile, k0, k1); ++seg) {
-      const int m0 = (tile % g.tiles_m) * (2 * BM), n0 = (tile / g.tiles_m) * BN;
+      const int m0 = (g.n_fast ? tile / g.tiles_n : tile % g.tiles_m) * (2 * BM), n0 = (g.n_fast ? tile % g.tiles_n : tile / g.tiles_m) * BN;
       const bool partial = k0 > 0;            // somebody else owns this tile: leave the accumulator in the workspace
       const bool owner_split = k0 == 0 && k1 < KB;  // this CTA owns the tile and others hold its later K blocks
       int n_parts = 0;
@@ -520,6 +524,19 @@ int env_int(const char* name, int dflt) {
   return e ? atoi(e) : dflt;
 }
 
+// Which tile dimension runs fastest over the grid of the whole-tile kernel.  With the row tile fastest a wave of 148
+// CTAs covers many weight-row tiles of one or two token tiles, and every further token tile re-reads the weights from
+// HBM; with the token tile fastest a wave covers ~148 / tiles_n row tiles under ALL token tiles, which share the
+// weight fetches in L2.  Measured at 4096 tokens (batched prefill): gate/up 827 -> 729 us, qkv 205 -> 170, o 127 ->
+// 115, down 335 -> 324; at two token tiles (512 tokens) the orders are equivalent and the row tile stays fastest.
+// (B200_GEMM_NFAST = 0 / 1 forces it, for experiments.)
+int n_fast_order(int tiles_m, int tiles_n) {
+  const int ov = env_int("B200_GEMM_NFAST", -1);
+  if (tiles_n <= 1 || tiles_m >= 65535) return 0;
+  if (ov >= 0) return ov;
+  return tiles_n >= 4;
+}
+
 // Where a launch puts its result: fp32 Y (possibly split-K partials) or, for GEPI_SWIGLU, bf16 H.
 struct GemmOut {
   float* y = nullptr;
@@ -541,7 +558,9 @@ cudaError_t launch_bn(const uint16_t* W, int64_t rows, int64_t K, const uint16_t
   GemmArgs g;
   g.y = o.y; g.ldy = (int)o.ldy; g.h = o.h; g.ldh = (int)o.ldh;
   g.n_tokens = (int)n_tokens; g.n_rows = (int)rows; g.k_blocks = (int)(K / BK) / splits; g.split_stride = split_stride;
-  dim3 grid((unsigned)((rows + BM * MT - 1) / (BM * MT)), (unsigned)((n_tokens + BN - 1) / BN), (unsigned)splits);
+  const unsigned tm = (unsigned)((rows + BM * MT - 1) / (BM * MT)), tn = (unsigned)((n_tokens + BN - 1) / BN);
+  g.n_fast = n_fast_order((int)tm, (int)tn);
+  dim3 grid(g.n_fast ? tn : tm, g.n_fast ? tm : tn, (unsigned)splits);
   count_launch(); kern<<<grid, C::THREADS, C::SMEM, s>>>(ma, mb, g);
   return cudaGetLastError();
 }
@@ -558,6 +577,8 @@ cudaError_t launch_streamk(const uint16_t* W, int64_t rows, int64_t K, const uin
   StreamKArgs g;
   g.y = o.y; g.ldy = (int)o.ldy; g.h = o.h; g.ldh = (int)o.ldh; g.n_tokens = (int)n_tokens;
   g.tiles_m = (int)(rows / (2 * BM));
+  g.tiles_n = (int)((n_tokens + BN - 1) / BN);
+  g.n_fast = 0;  // stream-K keeps the row tile fastest (measured: the token-tile order costs it 8-12 % at 512-4096 tokens)
   g.kb_total = (int)(K / BK);
   const int tiles = g.tiles_m * (int)((n_tokens + BN - 1) / BN);
   g.total = tiles * g.kb_total;
@@ -598,9 +619,14 @@ bool gemm_shape_ok(int64_t rows, int64_t K, int64_t n_tokens) {
 namespace {
 
 // Prefill-sized GEMMs whose 256 x 256 tiles do not come to whole waves: stream-K over all tiles.  Measured on the
-// gate/up matrix (28672 x 4096), whole tiles -> stream-K: 512 tokens (224 tiles = 1.51 waves) 119.7 -> 109 us, 1024
-// tokens 235 -> 187, 2048 tokens 437 -> 409, 4096 tokens (12.1 waves) 835 -> 726 us = 1325 TFLOP/s.  Besides the
-// balance, CTAs at different K positions contend less for L2 than a wave in lock-step (0.67 vs 0.83 us per K block).
+// gate/up matrix (28672 x 4096), whole tiles -> stream-K: 512 tokens (224 tiles = 1.51 waves) 119.7 -> 102 us, 1024
+// tokens 235 -> 183, 2048 tokens 433 -> 392, 4096 tokens (12.1 waves) 827 -> 688 us = 1.4 PFLOP/s.  Besides the
+// balance, CTAs at different K positions contend less for L2 than a wave in lock-step (0.63 vs 0.83 us per K block).
+// The other side of that staggering: CTAs that work on the same weight rows are at different K and no longer share
+// the fetch in L2.  So it is taken for matrices with many row tiles (gate/up, lm_head: the CTAs of a moment are on
+// different rows anyway), and otherwise only when K is short and there are between one and one and a half waves of
+// tiles (qkv at 2048 tokens: 113 -> 99 us); ffn_down at 4096 tokens (K = 14336, 16 row tiles x 16 token tiles) went
+// from 324 to 574 us under it — every tile streamed its 7 MB weight slab from HBM on its own.
 // Not for GEMMs of less than a wave (qkv, o, down at 512 tokens: 32-48 tiles): a CTA's extra epilogues — 5 us to
 // leave a partial, 12 us for the owner to pull one in and add it — outweigh the balance there; split-K stays.
 // (Also measured: whole tiles for the full waves and K runs only for the last, partial wave.  Every CTA then writes
@@ -611,9 +637,11 @@ bool streamk_large_n(int64_t rows, int64_t K, int64_t n_tokens, const GemmWorksp
   if (n_tokens <= 128 || rows % (2 * BM) || (size_t)wk->sm_count * kWsSlot * 4 > wk->ws_bytes) return false;
   const int ov = env_int("B200_GEMM_SK256", -1);
   if (ov == 0) return false;
-  const int64_t tiles = (rows / (2 * BM)) * ((n_tokens + 255) / 256), rem = tiles % wk->sm_count;
   if (ov == 1) return true;
-  return tiles >= wk->sm_count && rem != 0 && rem * 20 <= (int64_t)wk->sm_count * 17;
+  const int64_t tiles_m = rows / (2 * BM), tiles = tiles_m * ((n_tokens + 255) / 256), n_sm = wk->sm_count, rem = tiles % n_sm;
+  if (tiles < n_sm || rem == 0) return false;
+  if (tiles_m >= 64) return rem * 20 <= n_sm * 17;
+  return K <= 8192 && tiles < 2 * n_sm && rem * 2 <= n_sm;
 }
 
 // One schedule for both epilogues.  Returns cudaErrorNotSupported when EPI needs the whole K in one CTA and the
