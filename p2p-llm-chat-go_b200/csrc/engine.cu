@@ -53,6 +53,8 @@ Engine::~Engine() {
   if (worker.joinable()) worker.join();
   if (stream) cudaStreamSynchronize(stream);
   if (step_graph) cudaGraphExecDestroy(step_graph);
+  for (auto& g : batch_graphs) cudaGraphExecDestroy(g.second.first);
+  if (b_in_host) cudaFreeHost(b_in_host);
   for (void* p : tp_ipc_opened) cudaIpcCloseMemHandle(p);
   tp_destroy(nccl_comm);
   for (void* p : allocs) cudaFree(p);
@@ -92,6 +94,7 @@ int Engine::init(const b200_config& c, const void* nccl_id) {
   sm_count = prop.multiProcessorCount;
   use_pdl = getenv("B200_NO_PDL") == nullptr;
   use_graph = getenv("B200_NO_GRAPH") == nullptr;
+  use_batch_graph = use_graph && getenv("B200_NO_BATCH_GRAPH") == nullptr;
   use_fa_prefill = getenv("B200_NO_FA_PREFILL") == nullptr;
   use_mma_decode = getenv("B200_NO_MMA_DECODE") == nullptr;
   use_attn_prefetch = getenv("B200_NO_ATTN_PREFETCH") == nullptr;

@@ -165,6 +165,13 @@ struct Engine {
   bool can_batch() const { return tp_size == 1 && cfg.max_seqs > 1; }  // may the scheduler run batched steps at all
   int32_t *b_tok = nullptr, *b_pos = nullptr, *b_ctx = nullptr, *b_slot = nullptr, *b_next = nullptr;  // device [max_seqs]
   int32_t* b_next_host = nullptr;   // pinned
+  int32_t* b_in_host = nullptr;     // pinned [4][max_seqs]: token / position / context / slot of the step being enqueued
+  // the batched step as a CUDA graph per batch size (the launch sequence depends on nothing else); {exec, kernel nodes}
+  std::map<int, std::pair<cudaGraphExec_t, int>> batch_graphs;
+  static constexpr int kBatchGraphAfter = 16;
+  int batch_last = 0, batch_same = 0;  // batch size of the previous step, and for how many steps it has held
+  bool use_batch_graph = true;      // off: B200_NO_BATCH_GRAPH, tensor parallelism (per-step sequence numbers, NCCL calls)
+  int enqueue_batched_body(int B);  // layer stack + lm_head + per-row argmax over the rows described by b_tok/b_pos/b_ctx/b_slot
   int32_t* hist_dev = nullptr;      // [max_seqs][max_ctx] token history per slot
   SampleParams* sp_arr = nullptr;   // [max_seqs]
   float* b_logits = nullptr;        // [max_seqs][vocab]

@@ -54,6 +54,7 @@ int Engine::ensure_batched() {
       (rc = alloc((void**)&sp_arr, S * sizeof(SampleParams))) || (rc = alloc((void**)&b_logits, S * (size_t)c.vocab * 4)))
     return rc;
   B200_CUDA(cudaHostAlloc((void**)&b_next_host, S * 4, cudaHostAllocDefault));
+  B200_CUDA(cudaHostAlloc((void**)&b_in_host, 4 * S * 4, cudaHostAllocDefault));
   if (output_type != T_BF16) {  // bf16 shadow of a k-quant lm_head
     const Slot& s = slots["output.weight"];
     if ((rc = alloc((void**)&output16, (size_t)s.rows * s.cols * 2))) return rc;
@@ -66,24 +67,70 @@ int Engine::ensure_batched() {
   return 0;
 }
 
+int Engine::enqueue_batched_body(int B) {
+  int rc = forward_gemm(B, b_tok, b_pos, b_ctx, b_slot);
+  if (rc) return rc;
+  if ((rc = add_rmsnorm_proj(output_norm, B, true))) return rc;
+  B200_CUDA(launch_gemm_bf16(output16, cfg.vocab, cfg.d_model, pf_xb, B, b_logits, cfg.vocab, stream, &gemm_ws));
+  B200_CUDA(launch_argmax_rows(b_logits, B, cfg.vocab, b_next, stream));
+  return 0;
+}
+
 // One decode step for the sequences in `slots` (one row each): token seqs[s].token at position seqs[s].pos.
+// The ~330 launches of the step depend only on the number of rows, so they are captured once per batch size and
+// replayed; what changes from step to step (tokens, positions, context lengths, slots) sits in device arrays that are
+// refreshed from pinned memory in front of the graph.
 int Engine::batched_step(const std::vector<int>& sl, std::vector<int32_t>* next) {
   const b200_config& c = cfg;
   const int B = (int)sl.size();
-  std::vector<int32_t> tok(B), pos(B), ctx(B), slot(B);
+  const size_t S = (size_t)c.max_seqs;
+  int32_t *tok = b_in_host, *pos = b_in_host + S, *ctx = b_in_host + 2 * S, *slot = b_in_host + 3 * S;
   for (int i = 0; i < B; ++i) {
     const Seq& q = seqs[sl[i]];
     tok[i] = q.token; pos[i] = q.pos; ctx[i] = q.pos + 1; slot[i] = sl[i];
   }
-  B200_CUDA(cudaMemcpyAsync(b_tok, tok.data(), (size_t)B * 4, cudaMemcpyHostToDevice, stream));
-  B200_CUDA(cudaMemcpyAsync(b_pos, pos.data(), (size_t)B * 4, cudaMemcpyHostToDevice, stream));
-  B200_CUDA(cudaMemcpyAsync(b_ctx, ctx.data(), (size_t)B * 4, cudaMemcpyHostToDevice, stream));
-  B200_CUDA(cudaMemcpyAsync(b_slot, slot.data(), (size_t)B * 4, cudaMemcpyHostToDevice, stream));
-  int rc = forward_gemm(B, b_tok, b_pos, b_ctx, b_slot);
-  if (rc) return rc;
-  if ((rc = add_rmsnorm_proj(output_norm, B, true))) return rc;
-  B200_CUDA(launch_gemm_bf16(output16, c.vocab, c.d_model, pf_xb, B, b_logits, c.vocab, stream, &gemm_ws));
-  B200_CUDA(launch_argmax_rows(b_logits, B, c.vocab, b_next, stream));
+  B200_CUDA(cudaMemcpyAsync(b_tok, tok, (size_t)B * 4, cudaMemcpyHostToDevice, stream));
+  B200_CUDA(cudaMemcpyAsync(b_pos, pos, (size_t)B * 4, cudaMemcpyHostToDevice, stream));
+  B200_CUDA(cudaMemcpyAsync(b_ctx, ctx, (size_t)B * 4, cudaMemcpyHostToDevice, stream));
+  B200_CUDA(cudaMemcpyAsync(b_slot, slot, (size_t)B * 4, cudaMemcpyHostToDevice, stream));
+  int rc = 0;
+  // capturing and instantiating the ~330 nodes costs ~25 ms, five steps' worth: only for a batch size that has held for
+  // kBatchGraphAfter steps in a row (a burst ramps through many sizes; a graph then saves ~3.5 % of each later step)
+  batch_same = (B == batch_last) ? batch_same + 1 : 0;
+  batch_last = B;
+  const bool graph_now = use_batch_graph && tp_size == 1 && (batch_same >= kBatchGraphAfter || batch_graphs.count(B));
+  if (graph_now) {
+    auto it = batch_graphs.find(B);
+    if (it == batch_graphs.end()) {
+      cudaGraph_t g = nullptr;
+      cudaGraphExec_t ex = nullptr;
+      cudaError_t e = cudaStreamBeginCapture(stream, cudaStreamCaptureModeThreadLocal);
+      if (e != cudaSuccess) return cuda_fail(e, "cudaStreamBeginCapture (batched step)");
+      count_launches_pause(true);
+      rc = enqueue_batched_body(B);
+      count_launches_pause(false);
+      e = cudaStreamEndCapture(stream, &g);
+      size_t n_nodes = 0;
+      if (rc == 0 && e == cudaSuccess && cudaGraphGetNodes(g, nullptr, &n_nodes) == cudaSuccess) e = cudaGraphInstantiate(&ex, g, 0);
+      if (g) cudaGraphDestroy(g);
+      if (rc) return rc;
+      if (e != cudaSuccess || !ex) {  // no graph for this engine then: plain launches from here on
+        (void)cudaGetLastError();
+        use_batch_graph = false;
+      } else {
+        if (batch_graphs.size() >= 64) {  // batch sizes come and go: bounded
+          for (auto& old : batch_graphs) cudaGraphExecDestroy(old.second.first);
+          batch_graphs.clear();
+        }
+        it = batch_graphs.emplace(B, std::make_pair(ex, (int)n_nodes)).first;
+      }
+    }
+    if (use_batch_graph) {
+      B200_CUDA(cudaGraphLaunch(it->second.first, stream));
+      count_launch((unsigned long long)it->second.second);
+    }
+  }
+  if (!(graph_now && use_batch_graph) && (rc = enqueue_batched_body(B))) return rc;
   for (int i = 0; i < B; ++i) {  // sampled requests: the sampler kernel on that row, writing over the argmax
     const Seq& q = seqs[sl[i]];
     if (q.greedy) continue;
@@ -422,6 +469,14 @@ void Engine::worker_loop() {
     // ---- admit waiting requests into free slots; while sequences are decoding, at most a few prefills per
     // iteration so that running requests keep producing tokens (bounded inter-token stall)
     int budget = active.empty() ? (int)seqs.size() : 4;
+    if (!active.empty()) {
+      // a long queue (>= 16 waiting, B200_ADMIT_DEEP): full prefill batches of 8 prompts, so half as many decode steps
+      // are interleaved while the batch is still small and a step still costs nearly what it costs at full batch
+      // (256 peers: 9,050 -> 9,770 tok/s; the running sequences' inter-token stall goes from ~32 to ~62 ms meanwhile)
+      std::lock_guard<std::mutex> lk(qmu);
+      static const int deep = getenv("B200_ADMIT_DEEP") ? atoi(getenv("B200_ADMIT_DEEP")) : 16;
+      if ((int)queue.size() >= deep) budget = 8;
+    }
     // tensor-parallel engines are driven SPMD (every rank makes the same calls): admission timing would differ
     // between ranks, so they serve one request at a time; several slots exist only for b200_bench_batched
     if (tp_size > 1) budget = active.empty() ? 1 : 0;
