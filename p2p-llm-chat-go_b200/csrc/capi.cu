@@ -794,7 +794,7 @@ int b200_bench_kernel(b200_engine* h, const char* which, int iters, float* ms, i
     int splits = 8;
     for (int i = -3; i < iters; ++i) {
       if (i == 0) B200_CUDA(cudaEventRecord(e0, e->stream));
-      if (m == "down" || m == "attn_output") {  // as the engine calls them
+      if (m == "down" || m == "attn_output" || m == "qkv") {  // as the engine calls them: K may be split
         splits = 8;
         B200_CUDA(launch_gemm_bf16_splitk(W, rows, K, xb.as<uint16_t>(), n, yb.as<float>(), rows, n * rows, &splits, e->stream,
                                           e->gemm_ws.ws ? &e->gemm_ws : nullptr));

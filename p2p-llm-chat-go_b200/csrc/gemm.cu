@@ -119,7 +119,7 @@ struct GemmArgs {
   int ldy;       // floats between consecutive tokens of y
   int n_tokens;  // valid tokens (TMA zero-fills the rest of a token tile)
   int n_rows;    // valid weight rows (the last row tile may be ragged: vocab-parallel lm_head shards)
-  int k_blocks;  // K / 64 blocks handled by ONE CTA (split-K: blockIdx.z picks which run of them)
+  int kb_total;  // K / 64 blocks; split-K: CTA z of gridDim.z takes blocks [kb_total*z/Z, kb_total*(z+1)/Z) (the runs need not be equal)
   long long split_stride;  // floats between the partial outputs of consecutive K splits
 };
 
@@ -142,7 +142,8 @@ __global__ void __launch_bounds__(64 + 128 * MT) gemm_bf16_kernel(const __grid_c
   // n_fast: the token tile is the fastest grid dimension, so the CTAs of a wave cover few weight-row tiles x all token
   // tiles and share the weight fetches in L2 (many token tiles: batched prefill); else the row tile is fastest
   const int m0 = (g.n_fast ? blockIdx.y : blockIdx.x) * (BM * MT), n0 = (g.n_fast ? blockIdx.x : blockIdx.y) * BN;
-  const int kb0 = blockIdx.z * g.k_blocks;  // split-K: this CTA's first K block
+  const int kb0 = (int)((long long)g.kb_total * blockIdx.z / gridDim.z);  // split-K: this CTA's first K block ...
+  const int k_blocks = (int)((long long)g.kb_total * (blockIdx.z + 1) / gridDim.z) - kb0;  // ... and how many
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < C::STAGES; ++s) {
@@ -165,7 +166,7 @@ __global__ void __launch_bounds__(64 + 128 * MT) gemm_bf16_kernel(const __grid_c
     if (lane == 0) {  // ===== TMA producer =====
       int s = 0;
       uint32_t ph = 0;
-      for (int kb = 0; kb < g.k_blocks; ++kb) {
+      for (int kb = 0; kb < k_blocks; ++kb) {
         mbar_wait(empty_s + 8 * s, ph ^ 1);
         const uint32_t dst = tiles + s * C::STAGE;
         mbar_expect_tx(full_s + 8 * s, C::STAGE);
@@ -180,7 +181,7 @@ __global__ void __launch_bounds__(64 + 128 * MT) gemm_bf16_kernel(const __grid_c
       constexpr uint32_t idesc = instr_desc(BM, BN);
       int s = 0;
       uint32_t ph = 0;
-      for (int kb = 0; kb < g.k_blocks; ++kb) {
+      for (int kb = 0; kb < k_blocks; ++kb) {
         mbar_wait(full_s + 8 * s, ph);
         tc_fence_after();
         const uint64_t ad = smem_desc_sw128(tiles + s * C::STAGE);
@@ -557,7 +558,7 @@ cudaError_t launch_bn(const uint16_t* W, int64_t rows, int64_t K, const uint16_t
   if (e != cudaSuccess) return e;
   GemmArgs g;
   g.y = o.y; g.ldy = (int)o.ldy; g.h = o.h; g.ldh = (int)o.ldh;
-  g.n_tokens = (int)n_tokens; g.n_rows = (int)rows; g.k_blocks = (int)(K / BK) / splits; g.split_stride = split_stride;
+  g.n_tokens = (int)n_tokens; g.n_rows = (int)rows; g.kb_total = (int)(K / BK); g.split_stride = split_stride;
   const unsigned tm = (unsigned)((rows + BM * MT - 1) / (BM * MT)), tn = (unsigned)((n_tokens + BN - 1) / BN);
   g.n_fast = n_fast_order((int)tm, (int)tn);
   dim3 grid(g.n_fast ? tn : tm, g.n_fast ? tm : tn, (unsigned)splits);
@@ -682,11 +683,11 @@ cudaError_t dispatch(const uint16_t* W, int64_t rows, int64_t K, const uint16_t*
     // One token tile: the GEMM streams the weights once and is HBM-bound, so what matters is that every SM gets
     // the same share of the rows (224 row tiles on 148 SMs leave half the GPU waiting for the SMs that got two:
     // measured 75 us where the batch-1 GEMV takes 42).  Partials are tiny here (tokens x rows), so K is split until
-    // the CTAs deal out evenly: the s (dividing the K blocks, >= 8 blocks per CTA) with the best
+    // the CTAs deal out evenly: the s (>= 8 blocks per CTA) with the best
     // CTAs / (rounds x SMs), the smallest such s on ties.
     double best = 0.0;
     for (int sp = 1; sp <= max_splits && sp <= 16; ++sp) {
-      if (kb % sp || kb / sp < 8) continue;
+      if (kb / sp < 8) continue;  // (the runs may be unequal: qkv, 48 row tiles x 64 K blocks, takes 3 x 21-22 = 144 CTAs)
       const int64_t ctas = tiles128 * sp, rounds = (ctas + n_sm - 1) / n_sm;
       const double eff = (double)ctas / (double)(rounds * n_sm);
       if (eff > best + 0.02) { best = eff; use = sp; }
