@@ -25,9 +25,11 @@ package main
 import "C"
 
 import (
+	"bytes"
 	"encoding/json"
 	"errors"
 	"fmt"
+	"io"
 	"log"
 	"net/http"
 	"os"
@@ -540,6 +542,91 @@ func route(ids []int32, newTokens int64) (*gpu, int) {
 	return best, bestMatch
 }
 
+// suggest serves POST /suggest — what a node-side handler next to /send (reference go/cmd/node/main.go:219) forwards
+// to (SURVEY 8f-3).  Body {"content": string, "stream": bool (default false, like the reference's blocking call),
+// "options"?}.  It is the reference's own call (web/streamlit_app.py:89-98: that prompt, that model, `.strip()` of the
+// response) behind one route: the request is rewritten into the /api/generate body and handed to `gen`; the reply is
+// rewritten on the way out into {"suggestion": text, ...stats} or, streaming, NDJSON {"delta": piece, "done": false}
+// lines closed by an object that carries the whole suggestion.
+func suggest(gen http.HandlerFunc) http.HandlerFunc {
+	return func(w http.ResponseWriter, r *http.Request) {
+		var body struct {
+			Content *string         `json:"content"`
+			Stream  bool            `json:"stream"`
+			Options json.RawMessage `json:"options"`
+		}
+		if r.Method != http.MethodPost {
+			writeError(w, http.StatusMethodNotAllowed, "method not allowed")
+			return
+		}
+		if err := json.NewDecoder(r.Body).Decode(&body); err != nil || body.Content == nil {
+			writeError(w, http.StatusBadRequest, `body must be {"content": string, "stream": bool}`)
+			return
+		}
+		inner := map[string]any{"model": model, "stream": body.Stream,
+			"prompt": "You are a helpful assistant. Draft a concise, friendly reply to the following message:\n\n" + *body.Content + "\n\nReply:"}
+		if len(body.Options) > 0 {
+			inner["options"] = body.Options
+		}
+		buf, _ := json.Marshal(inner)
+		r2 := r.Clone(r.Context())
+		r2.Body = io.NopCloser(bytes.NewReader(buf))
+		gen(&suggestWriter{w: w}, r2)
+	}
+}
+
+// suggestWriter turns the /api/generate reply lines into the /suggest ones as they are written.
+type suggestWriter struct {
+	w      http.ResponseWriter
+	code   int
+	line   []byte
+	soFar strings.Builder
+}
+
+func (s *suggestWriter) Header() http.Header { return s.w.Header() }
+func (s *suggestWriter) WriteHeader(code int) {
+	s.code = code
+	s.w.WriteHeader(code)
+}
+func (s *suggestWriter) Flush() {
+	if f, ok := s.w.(http.Flusher); ok {
+		f.Flush()
+	}
+}
+func (s *suggestWriter) Write(p []byte) (int, error) {
+	if s.code != 0 && s.code != http.StatusOK { // an error body: passed through as it is
+		return s.w.Write(p)
+	}
+	s.line = append(s.line, p...)
+	for {
+		i := bytes.IndexByte(s.line, '\n')
+		if i < 0 {
+			return len(p), nil
+		}
+		var in map[string]json.RawMessage
+		if err := json.Unmarshal(s.line[:i], &in); err != nil {
+			return 0, err
+		}
+		s.line = s.line[i+1:]
+		var piece string
+		json.Unmarshal(in["response"], &piece)
+		s.soFar.WriteString(piece)
+		out := map[string]any{"done": false, "delta": piece}
+		if string(in["done"]) == "true" {
+			out = map[string]any{"suggestion": strings.TrimSpace(s.soFar.String())}
+			for k, v := range in { // done, done_reason and the *_duration / *_count fields
+				if k != "response" && k != "model" && k != "created_at" && k != "context" {
+					out[k] = v
+				}
+			}
+		}
+		line, _ := json.Marshal(out)
+		if _, err := s.w.Write(append(line, '\n')); err != nil {
+			return 0, err
+		}
+	}
+}
+
 func probeReply(w http.ResponseWriter, chat bool, keepAlive float64) {
 	out := reply{Model: model, CreatedAt: time.Now().UTC().Format(time.RFC3339Nano), Done: true, DoneReason: "load"}
 	if keepAlive == 0 {
@@ -996,6 +1083,7 @@ func main() {
 	})
 	mux.HandleFunc("/api/generate", post(false))
 	mux.HandleFunc("/api/chat", post(true))
+	mux.HandleFunc("/suggest", suggest(post(false)))
 
 	addr := getenv("LLMD_ADDR", getenv("OLLAMA_HOST", "127.0.0.1:11434"))
 	log.Printf("llmd: %s serving model '%s' on %s, %d GPU(s), %d sequences each", C.GoString(C.b200_version()), model, addr, len(gpus), seqs)

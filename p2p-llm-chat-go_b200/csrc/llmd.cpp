@@ -441,7 +441,16 @@ static Gpu* route(const std::vector<int32_t>& ids, long long new_tokens, int* re
 }
 
 // ---- /api/generate and /api/chat ----------------------------------------------------------------------
-static void handle_generate(int fd, const Value& req, bool chat) {
+// The reply text as the reference keeps it: `.strip()` of the response (web/streamlit_app.py:98)
+static std::string strip_ws(const std::string& s) {
+  size_t a = 0, b = s.size();
+  while (a < b && (unsigned char)s[a] <= ' ') ++a;
+  while (b > a && (unsigned char)s[b - 1] <= ' ') --b;
+  return s.substr(a, b - a);
+}
+
+// suggest = true: the request came through POST /suggest (below); same path, another reply shape
+static void handle_generate(int fd, const Value& req, bool chat, bool suggest = false) {
   const std::string model = req.get_str("model");
   if (model != g_model && model != g_model + ":latest") {
     reply_error(fd, 404, "model '" + model + "' not found");
@@ -536,7 +545,13 @@ static void handle_generate(int fd, const Value& req, bool chat) {
   gpu->outstanding += bill;
   ++m_in_flight;
   ++gpu->in_flight;
+  std::string suggestion_so_far;  // /suggest: everything streamed so far (the final object carries the stripped whole)
   auto piece_obj = [&](const std::string& piece, bool final, const b200_stats* st, const std::vector<int32_t>* ctx, const char* reason) {
+    if (suggest) {
+      suggestion_so_far += piece;
+      if (!final) return "{\"delta\":" + mini_json::quote(piece) + ",\"done\":false}";
+      return "{\"suggestion\":" + mini_json::quote(strip_ws(suggestion_so_far)) + "," + stats_json(*st, reason) + "}";
+    }
     std::string o = "{\"model\":" + mq + ",\"created_at\":\"" + now_rfc3339() + "\",";
     if (chat) o += "\"message\":{\"role\":\"assistant\",\"content\":" + mini_json::quote(piece) + "},";
     else o += "\"response\":" + mini_json::quote(piece) + ",";
@@ -678,6 +693,26 @@ static void serve(int fd) {
       Value req;
       if (!mini_json::Parser(rq.body).parse(&req) || req.kind != Value::Obj) reply_error(fd, 400, "invalid JSON body");
       else handle_generate(fd, req, rq.path == "/api/chat");
+    } else if (rq.method == "POST" && rq.path == "/suggest") {
+      // what a node-side `/suggest` next to `/send` (reference go/cmd/node/main.go:219) forwards to.
+      // {"content": <the peer's message>, "stream": bool (default false, like the reference's blocking call), "options"?} ->
+      // the reference's own prompt (web/streamlit_app.py:93) and model; reply {"suggestion": <stripped text>, ...stats}
+      // or, streaming, NDJSON {"delta": ...,"done":false} lines and a final object with the whole suggestion.
+      Value body;
+      if (!mini_json::Parser(rq.body).parse(&body) || body.kind != Value::Obj || !body.get("content") || body.get("content")->kind != Value::Str) {
+        reply_error(fd, 400, "body must be {\"content\": string, \"stream\": bool}");
+      } else {
+        Value req, v;
+        req.kind = Value::Obj;
+        v.kind = Value::Str; v.str = g_model;
+        req.obj.emplace_back("model", v);
+        v.str = "You are a helpful assistant. Draft a concise, friendly reply to the following message:\n\n" + body.get_str("content") + "\n\nReply:";
+        req.obj.emplace_back("prompt", v);
+        v = Value(); v.kind = Value::Bool; v.b = body.get_bool("stream", false);
+        req.obj.emplace_back("stream", v);
+        if (const Value* o = body.get("options")) req.obj.emplace_back("options", *o);  // same meaning as in /api/generate
+        handle_generate(fd, req, false, true);
+      }
     } else {
       reply_error(fd, rq.method == "POST" ? 404 : 405, "not found");
     }

@@ -251,6 +251,33 @@ def test_keep_alive_format_and_ps(server):
     assert _gen(server, format="").status_code == 200
 
 
+def test_suggest_endpoint_is_the_reference_call_behind_one_route(server):
+    """POST /suggest {"content"} = what a node-side handler next to /send would forward.  It must give
+    exactly what the reference's ai_suggest() computes from /api/generate (web/streamlit_app.py:89-98): the same
+    prompt template, the stripped response — blocking and streamed."""
+    from tests import ref_client as client
+    msg = "Are we still on for lunch tomorrow?"
+    opts = {"temperature": 0}
+    want = requests.post(f"{server}/api/generate", json=dict(client.suggestion_request(msg), options=opts), timeout=60).json()["response"].strip()
+    # greedy on both routes (llmd's defaults sample, as Ollama's do): the same text
+    g = requests.post(f"{server}/suggest", json={"content": msg, "options": opts}, timeout=60)
+    assert g.status_code == 200 and g.json()["suggestion"] == want
+    # defaults, as the node-side handler would call it
+    a = requests.post(f"{server}/suggest", json={"content": msg}, timeout=60)
+    assert a.status_code == 200 and isinstance(a.json()["suggestion"], str) and a.json()["done"] is True
+    assert a.json()["suggestion"] == a.json()["suggestion"].strip()
+    assert "eval_count" in a.json() and "total_duration" in a.json()
+    # streamed: deltas concatenate to the final suggestion (up to the strip), one JSON object per line
+    r = requests.post(f"{server}/suggest", json={"content": msg, "stream": True}, timeout=60, stream=True)
+    assert r.status_code == 200 and r.headers["Content-Type"].startswith("application/x-ndjson")
+    lines = [json.loads(l) for l in r.iter_lines() if l]
+    assert lines[-1]["done"] is True and all(not l["done"] for l in lines[:-1])
+    assert "".join(l["delta"] for l in lines[:-1]).strip() == lines[-1]["suggestion"]
+    # malformed bodies
+    assert requests.post(f"{server}/suggest", json={"text": "x"}, timeout=10).status_code == 400
+    assert requests.post(f"{server}/suggest", data="{", timeout=10).status_code == 400
+
+
 def test_one_url_spreads_sessions_over_several_engines():
     """the reference has ONE OLLAMA_URL (web/streamlit_app.py:27); llmd with LLMD_GPUS owns an engine per
     listed device behind it.  Two engines (both on GPU 0 here: the test box has one): concurrent requests land on
