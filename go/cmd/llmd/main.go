@@ -39,6 +39,7 @@ import (
 	"sync"
 	"sync/atomic"
 	"time"
+	"unicode"
 	"unicode/utf8"
 	"unsafe"
 )
@@ -613,7 +614,10 @@ func (s *suggestWriter) Write(p []byte) (int, error) {
 		s.soFar.WriteString(piece)
 		out := map[string]any{"done": false, "delta": piece}
 		if string(in["done"]) == "true" {
-			out = map[string]any{"suggestion": strings.TrimSpace(s.soFar.String())}
+			// Python's str.strip() (web/streamlit_app.py:98): Unicode white space plus 0x1c-0x1f, nothing else
+			out = map[string]any{"suggestion": strings.TrimFunc(s.soFar.String(), func(r rune) bool {
+				return unicode.IsSpace(r) || (r >= 0x1c && r <= 0x1f)
+			})}
 			for k, v := range in { // done, done_reason and the *_duration / *_count fields
 				if k != "response" && k != "model" && k != "created_at" && k != "context" {
 					out[k] = v

@@ -441,11 +441,29 @@ static Gpu* route(const std::vector<int32_t>& ids, long long new_tokens, int* re
 }
 
 // ---- /api/generate and /api/chat ----------------------------------------------------------------------
-// The reply text as the reference keeps it: `.strip()` of the response (web/streamlit_app.py:98)
+// The reply text as the reference keeps it: Python's `str.strip()` of the response (web/streamlit_app.py:98), i.e.
+// without leading / trailing characters for which str.isspace() holds: space, \t \n \v \f \r, 0x1c-0x1f, U+0085,
+// U+00A0, U+1680, U+2000-200A, U+2028, U+2029, U+202F, U+205F, U+3000 — and nothing else (other control bytes stay).
+static size_t py_space_at(const std::string& s, size_t i) {  // bytes of a whitespace character starting at i, or 0
+  const unsigned char c = (unsigned char)s[i];
+  if (c == ' ' || (c >= 0x09 && c <= 0x0d) || (c >= 0x1c && c <= 0x1f)) return 1;
+  auto b = [&](size_t k) { return i + k < s.size() ? (unsigned char)s[i + k] : 0u; };
+  if (c == 0xC2 && (b(1) == 0x85 || b(1) == 0xA0)) return 2;
+  if (c == 0xE1 && b(1) == 0x9A && b(2) == 0x80) return 3;
+  if (c == 0xE2 && b(1) == 0x80 && ((b(2) >= 0x80 && b(2) <= 0x8A) || b(2) == 0xA8 || b(2) == 0xA9 || b(2) == 0xAF)) return 3;
+  if (c == 0xE2 && b(1) == 0x81 && b(2) == 0x9F) return 3;
+  if (c == 0xE3 && b(1) == 0x80 && b(2) == 0x80) return 3;
+  return 0;
+}
 static std::string strip_ws(const std::string& s) {
   size_t a = 0, b = s.size();
-  while (a < b && (unsigned char)s[a] <= ' ') ++a;
-  while (b > a && (unsigned char)s[b - 1] <= ' ') --b;
+  for (size_t n; a < b && (n = py_space_at(s, a)) != 0;) a += n;
+  for (;;) {  // from the end: a whitespace character is 1-3 bytes long
+    bool cut = false;
+    for (size_t n = 1; n <= 3 && n <= b - a; ++n)
+      if (py_space_at(s, b - n) == n) { b -= n; cut = true; break; }
+    if (!cut) break;
+  }
   return s.substr(a, b - a);
 }
 
