@@ -224,9 +224,8 @@ struct AttnClSmem {
   alignas(16) float qs[G * kHeadDim];
   float P[G][kTile], P2[G][kTile];  // softmax numerators of the pass's first / second tile
   float m_run[G], l_run[G], corr_s[G];
-  alignas(16) float accS[G][kHeadDim];   // this CTA's un-normalised partial, read by its cluster peers
   float mAll[G][kCl], lAll[G][kCl], wAll[G][kCl];
-  float part[G][kCl][kHeadDim / kCl];
+  float part[G][kCl][kHeadDim / kCl];   // [head][source CTA][dim]: written by the peers (this CTA's 8 output dims of every partial)
 };
 
 DEVINL uint32_t cluster_ctarank() {
@@ -244,6 +243,9 @@ DEVINL uint32_t map_to_rank(uint32_t local_smem_addr, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(a) : "r"(local_smem_addr), "r"(rank));
   return a;
 }
+DEVINL void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+DEVINL void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+DEVINL void st_dsmem(uint32_t addr, float v) { asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory"); }
 DEVINL float ld_dsmem(uint32_t addr) {
   float v;
   asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
@@ -274,6 +276,7 @@ __global__ void __launch_bounds__(128) attn_decode_cluster_kernel(const AttnArgs
   };
   const bool tracer = a.trace != nullptr && kvh == 0 && split == 0 && tid == 0;
   if (tracer) a.trace[0] = global_timer_ns();
+  cluster_arrive();  // "this CTA has started": waited for just before the merge writes into the peers' shared memory
   // ---- before the dependency: everything that does not depend on the projection kernel still running.  The page of
   // every row this thread will fetch (kept in registers), and an L2 prefetch of those rows, so that the real fetch —
   // issued after the wait, because one of the rows is being written by that kernel — is a single round trip to L2
@@ -396,22 +399,24 @@ __global__ void __launch_bounds__(128) attn_decode_cluster_kernel(const AttnArgs
   }
   if (tracer) a.trace[2] = global_timer_ns();
 
-  // ---- merge over the cluster
-#pragma unroll
-  for (int h = 0; h < G; ++h) sm.accS[h][tid] = acc[h];
-  cluster_sync_all();  // every CTA's (accS, m_run, l_run) is complete and visible cluster-wide
-  if (tid < G * kCl) {  // (head, source CTA) -> that CTA's running max and sum
-    const int h = tid / kCl, src = tid % kCl;
-    sm.mAll[h][src] = ld_dsmem(map_to_rank(smem_u32(&sm.m_run[h]), (uint32_t)src));
-    sm.lAll[h][src] = ld_dsmem(map_to_rank(smem_u32(&sm.l_run[h]), (uint32_t)src));
-  }
-  // meanwhile: this thread's share of the partial accumulators — source CTA tid / 8, output dim 8 * rank + tid % 8
+  // ---- merge over the cluster: every CTA PUSHES what its peers need into their shared memory — CTA r combines output
+  // dims [8r, 8r+8) of all heads, so dim `tid` of this partial goes to CTA tid / 8, and every CTA gets this split's
+  // running max and sum — then ONE cluster barrier, after which each CTA works on local memory only and may exit
+  // without a second barrier (a pull needed one more: peers could still be reading this CTA's memory).
   constexpr int kSlice = kHeadDim / kCl;  // 8 output dims per CTA
-  const int src = tid / kSlice, d = tid % kSlice;
-  float pa[G];
+  cluster_wait();  // every CTA of the cluster has started (arrived at entry): its shared memory exists
+  {
+    const uint32_t dst = (uint32_t)(tid / kSlice);
 #pragma unroll
-  for (int h = 0; h < G; ++h) pa[h] = ld_dsmem(map_to_rank(smem_u32(&sm.accS[h][split * kSlice + d]), (uint32_t)src));
-  __syncthreads();
+    for (int h = 0; h < G; ++h) st_dsmem(map_to_rank(smem_u32(&sm.part[h][split][tid % kSlice]), dst), acc[h]);
+    if (tid < G * kCl) {  // (head, destination CTA)
+      const int h = tid / kCl;
+      const uint32_t to = (uint32_t)(tid % kCl);
+      st_dsmem(map_to_rank(smem_u32(&sm.mAll[h][split]), to), sm.m_run[h]);
+      st_dsmem(map_to_rank(smem_u32(&sm.lAll[h][split]), to), sm.l_run[h]);
+    }
+  }
+  cluster_sync_all();  // all pushes have landed
   if (tid < G * kCl) {  // softmax weight of every source for every head
     const int h = tid / kCl, s_ = tid % kCl;
     float M = -INFINITY;
@@ -421,20 +426,16 @@ __global__ void __launch_bounds__(128) attn_decode_cluster_kernel(const AttnArgs
     sm.wAll[h][s_] = (ms == -INFINITY) ? 0.f : expf(ms - M);
   }
   __syncthreads();
-#pragma unroll
-  for (int h = 0; h < G; ++h) sm.part[h][src][d] = pa[h] * sm.wAll[h][src];
-  __syncthreads();
   if (tid < G * kSlice) {
     const int h = tid / kSlice, dd = tid % kSlice;
     float num = 0.f, den = 0.f;
 #pragma unroll
     for (int j = 0; j < kCl; ++j) {
-      num += sm.part[h][j][dd];
+      num += __fmul_rn(sm.part[h][j][dd], sm.wAll[h][j]);  // product rounded, then added: as when the product was stored first
       den = fmaf(sm.lAll[h][j], sm.wAll[h][j], den);
     }
     a.out[((size_t)kvh * G + h) * kHeadDim + split * kSlice + dd] = num / den;
   }
-  cluster_sync_all();  // peers may still be reading this CTA's shared memory
   if (a.trace != nullptr && tid == 0) atomicMax(a.trace + 3, global_timer_ns());
 }
 
