@@ -66,3 +66,24 @@ def test_product_does_not_touch_the_oracle():
                 if re.search(r"#include[^\n]*oracle|liboracle|-loracle|from oracle|import oracle|\borc_\w+\s*\(|dlopen[^\n]*oracle", txt):
                     bad.append(os.path.join(root, f))
     assert not bad, bad
+
+
+def test_go_twin_binds_declared_symbols_and_serves_the_same_routes():
+    """go/cmd/llmd/main.go cannot be compiled on this image (no Go toolchain), so what can be checked is checked
+    statically: every C.b200_* function it calls is declared in include/b200llm.h (a renamed or removed entry point
+    would otherwise only show up on a maintainer's machine), and it registers the routes csrc/llmd.cpp serves."""
+    root = os.path.dirname(ge.PKG_DIR)
+    go = open(os.path.join(root, "go", "cmd", "llmd", "main.go")).read()
+    hdr = open(os.path.join(root, "include", "b200llm.h")).read()
+    cpp = open(os.path.join(ge.PKG_DIR, "csrc", "llmd.cpp")).read()
+    declared = set(re.findall(r"\b(b200_\w+)\s*\(", hdr)) | set(re.findall(r"\b(b200_\w+)\b(?=\s*;|\s*\{)", hdr))
+    called = set(re.findall(r"\bC\.(b200_\w+)\(", go))
+    assert called, "the twin calls nothing?"
+    missing = sorted(f for f in called if f not in declared)
+    assert not missing, missing
+    for route in ("/api/generate", "/api/chat", "/api/tags", "/api/ps", "/api/version", "/metrics", "/suggest"):
+        assert f'"{route}"' in go, route
+        assert f'"{route}"' in cpp, route
+    # the same environment knobs on both servers
+    for knob in re.findall(r'"(LLMD_[A-Z_]+)"', cpp):
+        assert knob in go, knob
