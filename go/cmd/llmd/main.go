@@ -581,7 +581,7 @@ type suggestWriter struct {
 	w      http.ResponseWriter
 	code   int
 	line   []byte
-	soFar strings.Builder
+	soFar  strings.Builder
 }
 
 func (s *suggestWriter) Header() http.Header { return s.w.Header() }
@@ -607,6 +607,13 @@ func (s *suggestWriter) Write(p []byte) (int, error) {
 		var in map[string]json.RawMessage
 		if err := json.Unmarshal(s.line[:i], &in); err != nil {
 			return 0, err
+		}
+		if _, isErr := in["error"]; isErr { // a failure after the stream began: the line goes out as it is
+			if _, err := s.w.Write(s.line[:i+1]); err != nil {
+				return 0, err
+			}
+			s.line = s.line[i+1:]
+			continue
 		}
 		s.line = s.line[i+1:]
 		var piece string
